@@ -1,0 +1,8 @@
+"""b200det — B200-native detection-head hot path (drop-in for the reference's
+Anchors / FocalLoss / BBoxTransform / ClipBoxes / eval tail).
+
+Imported as ``b200det`` (see ../b200det/__init__.py).  The CUDA library is
+loaded lazily on first use and there is NO CPU fallback: every operator raises
+if ``libk7det.so`` is missing or the tensors are not on a CUDA device.
+"""
+__version__ = "0.1.0"

@@ -1,0 +1,115 @@
+"""Pin the oracle (oracle/restate.py) against fixtures produced by the unmodified
+reference (tests/golden/make_golden.py).  CPU only."""
+import glob
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import restate as R
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def oracle_anchors(kind, kwargs, H, W):
+    kw = dict(kwargs)
+    if kind == "k7":
+        # ksevendet/architecture/anchors.py:14-21: string recipes are eval'd
+        levels = [int(x) for x in kw["pyramid_levels"]]
+        mapper = eval(kw.pop("sizes_mapper"))
+        kw["sizes"] = [mapper(l) for l in levels]
+        kw["scales"] = eval(kw["scales"])
+    if kind == "yx":
+        return R.effdet_anchors(H, W, **kw)
+    if "pyramid_levels" in kw:
+        kw["pyramid_levels"] = [int(x) for x in kw["pyramid_levels"]]
+    return R.retina_anchors(H, W, **kw)
+
+
+with open(os.path.join(GOLDEN, "anchors.json")) as f:
+    ANCHORS = json.load(f)
+
+
+@pytest.mark.parametrize("name", sorted(ANCHORS))
+def test_anchors_bit_exact(name):
+    g = ANCHORS[name]
+    a = oracle_anchors(g["kind"], g["kwargs"], g["height"], g["width"])
+    assert a.dtype == np.float32 and a.shape == (g["count"], 4)
+    assert np.array_equal(a[g["sample_idx"]].astype(np.float64), np.array(g["sample_rows"]))
+    assert _sha(a) == g["sha256"]
+
+
+LOSS = sorted(glob.glob(os.path.join(GOLDEN, "loss_*.npz")))
+
+
+@pytest.mark.parametrize("path", LOSS, ids=[os.path.basename(p)[:-4] for p in LOSS])
+def test_loss_matches_reference(path):
+    g = np.load(path)
+    v = R.RETINA if str(g["variant"]) == "retina" else R.EFFDET
+    cls = torch.from_numpy(g["classifications"]).requires_grad_(True)
+    reg = torch.from_numpy(g["regressions"]).requires_grad_(True)
+    anc = torch.from_numpy(g["anchors"])
+    ann = torch.from_numpy(g["annotations"])
+    out = R.focal_loss(cls, reg, anc, ann, v)
+    # same ATen ops in the same order; only the reduction tree of .sum() depends on the
+    # thread count, hence 1e-6 instead of bit equality
+    np.testing.assert_allclose(out.cls_mean.detach().numpy(), g["cls_loss"], rtol=1e-6)
+    np.testing.assert_allclose(out.reg_mean.detach().numpy(), g["reg_loss"], rtol=1e-6)
+    (out.cls_mean.sum() + out.reg_mean.sum()).backward()
+    np.testing.assert_allclose(cls.grad.numpy(), g["dcls"], rtol=1e-6, atol=1e-12)
+    np.testing.assert_allclose(reg.grad.numpy(), g["dreg"], rtol=1e-6, atol=1e-12)
+    for b, m in enumerate(out.matches):
+        if m is None:
+            assert (g["state"][b] == 1).all() and (g["iou_argmax"][b] == -1).all()
+            continue
+        assert np.array_equal(m.iou_max.numpy(), g["iou_max"][b])
+        assert np.array_equal(m.argmax.numpy(), g["iou_argmax"][b])
+        assert np.array_equal(m.gt_row.numpy(), g["gt_row"][b])
+        assert np.array_equal(m.state.numpy(), g["state"][b])
+        assert m.num_pos == int((g["state"][b] == 2).sum())
+
+
+DET = sorted(glob.glob(os.path.join(GOLDEN, "detect_*.npz")))
+
+
+@pytest.mark.parametrize("use_tv", [True, False], ids=["torchvision", "restated_nms"])
+@pytest.mark.parametrize("path", DET, ids=[os.path.basename(p)[:-4] for p in DET])
+def test_detect_matches_reference(path, use_tv):
+    g = np.load(path)
+    yx = str(g["variant"]) == "effdet"
+    cls = torch.from_numpy(g["classifications"])
+    reg = torch.from_numpy(g["regressions"])
+    anc = torch.from_numpy(g["anchors"])
+    boxes, dets = R.detect_batch(cls, reg, anc, int(g["height"]), int(g["width"]),
+                                 float(g["score_thr"]), float(g["iou_thr"]), yx=yx,
+                                 use_torchvision=use_tv)
+    assert np.array_equal(boxes.numpy(), g["boxes"])
+    for b, d in enumerate(dets):
+        assert np.array_equal(d.survivors.numpy(), g[f"survivors_{b}"])
+        assert np.array_equal(d.keep_rank.numpy(), g[f"keep_rank_{b}"])
+        assert np.array_equal(d.keep_anchor.numpy(), g[f"keep_anchor_{b}"])
+        assert np.array_equal(d.scores.numpy(), g[f"scores_{b}"])
+        assert np.array_equal(d.labels.numpy(), g[f"labels_{b}"])
+        assert np.array_equal(d.boxes.numpy(), g[f"boxes_{b}"])
+
+
+def test_greedy_nms_equals_torchvision_random():
+    from torchvision.ops import nms
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 63, 64, 65, 500):
+        xy = rng.uniform(0, 100, (n, 2)).astype(np.float32)
+        wh = rng.uniform(0, 40, (n, 2)).astype(np.float32)
+        boxes = np.concatenate([xy, xy + wh], 1)
+        boxes[::7, 2:] = boxes[::7, :2]                  # zero-area boxes (0/0 -> NaN -> kept)
+        scores = np.round(rng.uniform(0.05, 1, n), 2).astype(np.float32)   # many ties
+        for thr in (0.3, 0.5):
+            want = nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
+            got = R.greedy_nms(boxes, scores, thr)
+            assert np.array_equal(got, want)
