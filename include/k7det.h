@@ -1,0 +1,193 @@
+/*
+ * k7det.h — C ABI of libk7det.so, the B200 (sm_100a) detection-head hot path.
+ *
+ * This is the drop-in boundary for the reference's detection-head modules
+ * (Kai7/ObjectDetection.Pytorch).  The reference has no FFI of its own — the
+ * path is reached through four nn.Module attributes of every detector and one
+ * helper function — so each entry point below names the
+ * reference callable it replaces; `b200det` (Python) binds them with ctypes
+ * and re-creates those modules on top (INTEGRATION.md shows the binding).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer that is not marked "host"
+ *     is a DEVICE pointer on the current CUDA device
+ *   - the library never allocates or frees: outputs and workspaces come from
+ *     the caller (sizes from the *_workspace_bytes queries)
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*)
+ *     and never synchronises the device
+ *   - return value: K7_OK or a negative K7_E* code; k7_last_error() gives the
+ *     thread-local message of the last failure
+ *   - all float tensors are contiguous float32; `cls`/`dcls` base pointers
+ *     must be 16-byte aligned (they are streamed with bulk async copies)
+ *   - there is no CPU implementation behind this ABI
+ *
+ * Tensor vocabulary (reference names): B images, A anchors per image, C classes,
+ * M annotation rows per image, classifications [B,A,C] (post-sigmoid
+ * probabilities, class innermost), regressions [B,A,4], annotations [B,M,5]
+ * rows (x1,y1,x2,y2,label) with pad rows label == -1.
+ */
+#ifndef K7DET_H_
+#define K7DET_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define K7_ABI_VERSION 1
+
+#define K7_OK 0
+#define K7_EINVAL (-1)     /* bad argument (shape, null pointer, alignment, unsupported size) */
+#define K7_EWORKSPACE (-2) /* workspace too small */
+#define K7_ECUDA (-3)      /* a CUDA runtime call failed */
+
+#define K7_MAX_LEVELS 8
+#define K7_MAX_CELL_ANCHORS 16
+
+#define K7_BOX_XYXY 0 /* architectures/anchors.py, losses.py, utils.py */
+#define K7_BOX_YXYX 1 /* architectures/utils_efficientdet.py, loss_efficientdet.py */
+
+/* Anchor recipe: everything Anchors.forward (architectures/anchors.py:38-60,
+ * generate_anchors :62-97, shift :99-119; yx variant utils_efficientdet.py:74-137)
+ * needs to produce anchor `a` without materialising the [A,4] table:
+ *   coordinate = float32( base[level][k][c] + (i + 0.5) * stride[level] )      (float64 arithmetic)
+ * with anchors ordered level-major, then cell row y, cell column x, then the
+ * in-cell index k (ratio-major/scale-minor for xyxy, scale-major/ratio-minor for yxyx). */
+typedef struct K7AnchorSpec {
+    int32_t num_levels;
+    int32_t cell_anchors;                 /* len(ratios) * len(scales) */
+    int32_t height, width;                /* image size the recipe was instantiated for */
+    int32_t box_order;                    /* K7_BOX_XYXY | K7_BOX_YXYX: layout of base[][][4] and of materialised anchors */
+    int32_t total;                        /* A */
+    int32_t fh[K7_MAX_LEVELS];            /* ceil(height / stride) (anchors.py:43) */
+    int32_t fw[K7_MAX_LEVELS];
+    int32_t offset[K7_MAX_LEVELS + 1];    /* first anchor index of each level; offset[num_levels] == A */
+    double stride[K7_MAX_LEVELS];
+    double base[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS][4];
+} K7AnchorSpec;
+
+/* Every kernel that needs anchors takes BOTH `spec` (host pointer, may be NULL) and
+ * `anchors` (device [A,4] float32 in `box_order` layout, may be NULL).  With a spec the
+ * anchors are generated in registers and never read from memory; with only a tensor
+ * (anchors built by someone else) they are loaded.  One of the two must be given. */
+
+int k7_version(void);
+const char* k7_last_error(void);
+
+/* Replaces Anchors.forward (architectures/anchors.py:38-60; utils_efficientdet.py:74-137):
+ * writes out[A,4] float32. */
+int k7_anchors_materialize(const K7AnchorSpec* spec, float* out, void* stream);
+
+/* ---- training side ------------------------------------------------------------------ */
+
+typedef struct K7MatchParams {
+    float neg_thr; /* IoU_max <  neg_thr -> negative   (losses.py:79: 0.35; loss_efficientdet.py:75: 0.4) */
+    float pos_thr; /* IoU_max >= pos_thr -> positive   (losses.py:80: 0.45; loss_efficientdet.py:77: 0.5) */
+} K7MatchParams;
+
+#define K7_STATE_NEG 0
+#define K7_STATE_IGNORE 1
+#define K7_STATE_POS 2
+/* assign word: bits 0-1 = state, bits 2-31 = annotation row index (0..M-1) of the arg-max GT */
+#define K7_ASSIGN_STATE(w) ((w) & 3)
+#define K7_ASSIGN_ROW(w) ((int32_t)((uint32_t)(w) >> 2))
+
+/* Replaces calc_iou + IoU-max assignment (losses.py:6-23, 49-82).  Outputs:
+ *   assign  [B,A] int32   packed state / GT row (images without a valid row: all IGNORE)
+ *   num_pos [B]   int32   positives per image
+ *   iou_max [B,A] float32 (optional, may be NULL)  bit-identical to torch.max(IoU,1).values
+ *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list */
+int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
+             const float* annotations, int B, int A, int M, const K7MatchParams* params,
+             int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, void* stream);
+
+typedef struct K7LossParams {
+    float alpha;            /* 0.25 (losses.py:31) ; gamma is fixed at 2 (losses.py:32, pow == x*x) */
+    float beta;             /* smooth-L1 switch 1/9 (losses.py:157-159) */
+    float target_div[4];    /* targets / [0.1,0.1,0.2,0.2] (losses.py:148); ones for loss_efficientdet.py */
+    int32_t yx_targets;     /* 0: (dx,dy,dw,dh) (losses.py:144)  1: (dy,dx,dh,dw) (loss_efficientdet.py:127) */
+    int32_t mean_divisor;   /* images the batch mean is taken over: B for one GPU, the GLOBAL batch when sharded */
+} K7LossParams;
+
+size_t k7_loss_workspace_bytes(int B, int A, int C);
+
+/* Replaces FocalLoss.forward after assignment (losses.py:62, 94-168) and, when dcls/dreg
+ * are given, its autograd backward.  Outputs:
+ *   per_image [B,2] float32  (cls_loss_i, reg_loss_i)
+ *   sums      [4]   float32  { sum_i cls_loss_i, sum_i reg_loss_i, sum_i num_pos_i, B }  (the NCCL payload)
+ *   dcls [B,A,C], dreg [B,A,4] (optional, both or neither): d(mean cls loss)/dcls and
+ *   d(mean reg loss)/dreg with the mean taken over params->mean_divisor images.
+ * The batch means of losses.py:168 are sums[0]/B and sums[1]/B. */
+int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
+            const float* cls, const float* reg, const float* annotations,
+            const int32_t* assign, const int32_t* num_pos,
+            int B, int A, int C, int M, const K7LossParams* params,
+            float* per_image, float* sums, float* dcls, float* dreg,
+            void* workspace, size_t workspace_bytes, void* stream);
+
+/* grad *= *scale (device scalar); no-op when *scale == 1.  Used by the autograd backward
+ * when the incoming gradient of a loss output is not 1. */
+int k7_scale_inplace(float* grad, size_t n, const float* scale, void* stream);
+
+/* ---- inference side ----------------------------------------------------------------- */
+
+#define K7_DECODE_RETINA 0 /* utils.py:26-53: (dx,dy,dw,dh) * std + mean around xyxy anchors */
+#define K7_DECODE_EFFDET 1 /* utils_efficientdet.py:8-35: (dy,dx,dh,dw), no mean/std, yxyx anchors */
+
+typedef struct K7DecodeParams {
+    int32_t variant;
+    float mean[4], std[4];
+    int32_t clip;           /* fuse ClipBoxes (utils.py:61-71) */
+    int32_t height, width;
+} K7DecodeParams;
+
+/* Replaces BBoxTransform.forward (+ optionally ClipBoxes.forward): boxes[B,A,4] (x1,y1,x2,y2).
+ * anchor_batch_stride: 0 when `anchors` is [1,A,4] (broadcast), A*4 when it is [B,A,4]. */
+int k7_decode(const K7AnchorSpec* spec, const float* anchors, int box_order, size_t anchor_batch_stride,
+              const float* deltas, int B, int A, const K7DecodeParams* params, float* boxes, void* stream);
+
+/* Replaces ClipBoxes.forward (utils.py:61-71), in place. */
+int k7_clip(float* boxes, int B, int A, int height, int width, void* stream);
+
+typedef struct K7DetectParams {
+    K7DecodeParams decode;  /* clip/height/width are honoured */
+    float score_thr;        /* strict '>' (retinanet.py:302: 0.05) */
+    float iou_thr;          /* strict '>' (torchvision.ops.nms, retinanet.py:314: 0.5) */
+    int32_t pre_nms_topk;   /* 0 = off (reference behaviour) */
+    int32_t max_detections; /* 0 = off; otherwise stop after this many kept boxes per image */
+} K7DetectParams;
+
+size_t k7_detect_workspace_bytes(int B, int A, int C);
+
+/* Replaces the eval tail of the detectors for EVERY image of the batch
+ * (retinanet.py:297-318; batched form utils/utils.py:76-114): fused decode + clip +
+ * max-over-class + score threshold + compaction, then per image a radix sort
+ * (score descending, anchor ascending) and greedy bitmask NMS.  Results stay in the
+ * workspace; `counts` gets {survivors, kept} per image:  counts[B,2] int32. */
+int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order,
+              const float* cls, const float* reg, int B, int A, int C,
+              const K7DetectParams* params, int32_t* counts,
+              void* workspace, size_t workspace_bytes, void* stream);
+
+/* Copies the kept detections of image b to row-major outputs with `cap` rows per image:
+ *   scores [B,cap] f32, labels [B,cap] i64, boxes [B,cap,4] f32,
+ *   anchor_ids [B,cap] i32 (optional), survivor_rank [B,cap] i32 (optional: the index
+ *   torchvision.ops.nms would have returned, i.e. position in the thresholded list).
+ * Rows beyond the image's kept count are left untouched; kept boxes beyond `cap` are dropped. */
+int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B, int A, int C, int cap,
+                     float* scores, int64_t* labels, float* boxes, int32_t* anchor_ids,
+                     int32_t* survivor_rank, void* stream);
+
+/* Stand-alone replacement of torchvision.ops.nms(boxes, scores, thr) for one image
+ * (call sites retinanet.py:314 etc.): keep[n] int64 indices in descending-score order,
+ * count[1] int32.  Workspace: k7_nms_workspace_bytes(n). */
+size_t k7_nms_workspace_bytes(int n);
+int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
+           int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* K7DET_H_ */

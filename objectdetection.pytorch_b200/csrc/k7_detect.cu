@@ -1,0 +1,709 @@
+// Inference side: decode, clip, score threshold, compaction, sort, NMS.
+//
+//   k7_decode / k7_clip     BBoxTransform / ClipBoxes          architectures/utils.py:26-71
+//                                                              (yx variant utils_efficientdet.py:8-50)
+//   k7_detect               eval tail of every detector        architectures/retinanet.py:297-318,
+//                                                              batched form utils/utils.py:76-114
+//   k7_nms                  torchvision.ops.nms call sites     retinanet.py:314, utils/utils.py:93
+//
+// k7_detect is two kernels:
+//   1. k7_score_kernel streams classifications [B*A, C] through the per-warp TMA rings of
+//      k7_stream.cuh; per row it takes the class maximum, and only for rows above the score
+//      threshold (strict '>') finds the first arg-max class, generates the anchor, decodes and
+//      clips the box, and appends a 64-bit key (score descending | anchor id ascending) to the
+//      image's survivor list (warp-aggregated atomic slot allocation).  Regression deltas are read
+//      for survivors only.  Bytes: A*C*4 read per image + 32*S written.
+//   2. k7_sort_nms_kernel, one CTA per image: LSD radix sort of the keys (the order
+//      torchvision.ops.nms's stable descending sort produces, because the anchor id breaks score
+//      ties), then greedy NMS in chunks of 1024 sorted boxes: a chunk is first filtered against
+//      the boxes already kept, then a 1024x1024 bitmask matrix of the chunk is built in shared
+//      memory and scanned by one warp.  The result is identical to the sequential algorithm; the
+//      S x S mask never exists in global memory.
+#include "k7_stream.cuh"
+
+// ------------------------------------------------------------------ stand-alone decode / clip
+template <bool FROM_SPEC>
+__global__ void __launch_bounds__(256)
+k7_decode_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
+                 size_t anchor_batch_stride, const float4* __restrict__ deltas, int A,
+                 const __grid_constant__ K7DecodeParams P, float4* __restrict__ boxes) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
+    if (a >= A) return;
+    float ax1, ay1, ax2, ay2;
+    k7_anchor<FROM_SPEC>(spec, anchors + (FROM_SPEC ? 0 : (size_t)b * anchor_batch_stride), box_order, a, ax1, ay1, ax2, ay2);
+    const float4 d = __ldg(deltas + (size_t)b * A + a);
+    K7Box o = (P.variant == K7_DECODE_RETINA) ? k7_decode_retina(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w, P.mean, P.std)
+                                              : k7_decode_effdet(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w);
+    if (P.clip) o = k7_clip_box(o, P.height, P.width);
+    boxes[(size_t)b * A + a] = make_float4(o.x1, o.y1, o.x2, o.y2);
+}
+
+extern "C" int k7_decode(const K7AnchorSpec* spec, const float* anchors, int box_order, size_t anchor_batch_stride,
+                         const float* deltas, int B, int A, const K7DecodeParams* params, float* boxes, void* stream) {
+    K7_REQUIRE(deltas && params && boxes, "k7_decode: null argument");
+    K7_REQUIRE(spec || anchors, "k7_decode: need an anchor spec or an anchor tensor");
+    K7_REQUIRE(B > 0 && A > 0 && B <= 65535, "k7_decode: bad shape B=%d A=%d", B, A);
+    K7_REQUIRE(params->variant == K7_DECODE_RETINA || params->variant == K7_DECODE_EFFDET, "k7_decode: bad variant");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(deltas) & 15) == 0 && (reinterpret_cast<uintptr_t>(boxes) & 15) == 0,
+               "k7_decode: deltas and boxes must be 16-byte aligned");
+    if (spec) {
+        int rc = k7_check_spec(spec, A);
+        if (rc) return rc;
+    } else {
+        K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_decode: anchors must be 16-byte aligned");
+        K7_REQUIRE(anchor_batch_stride == 0 || anchor_batch_stride == (size_t)A * 4, "k7_decode: bad anchor batch stride");
+    }
+    dim3 grid((A + 255) / 256, B);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    static const K7AnchorSpec kEmpty = {};
+    if (spec)
+        k7_decode_kernel<true><<<grid, 256, 0, st>>>(*spec, nullptr, spec->box_order, 0, reinterpret_cast<const float4*>(deltas),
+                                                     A, *params, reinterpret_cast<float4*>(boxes));
+    else
+        k7_decode_kernel<false><<<grid, 256, 0, st>>>(kEmpty, anchors, box_order, anchor_batch_stride,
+                                                      reinterpret_cast<const float4*>(deltas), A, *params,
+                                                      reinterpret_cast<float4*>(boxes));
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
+__global__ void __launch_bounds__(256) k7_clip_kernel(float4* __restrict__ boxes, size_t n, int height, int width) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 v = boxes[i];
+    K7Box b = {v.x, v.y, v.z, v.w};
+    b = k7_clip_box(b, height, width);
+    boxes[i] = make_float4(b.x1, b.y1, b.x2, b.y2);
+}
+
+extern "C" int k7_clip(float* boxes, int B, int A, int height, int width, void* stream) {
+    K7_REQUIRE(boxes && B > 0 && A > 0, "k7_clip: bad argument");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "k7_clip: boxes must be 16-byte aligned");
+    const size_t n = (size_t)B * A;
+    k7_clip_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<float4*>(boxes), n, height, width);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
+// ------------------------------------------------------------------ workspace of k7_detect
+struct K7DetectWs {
+    int32_t* surv_count;    // [B]
+    int32_t* kept_count;    // [B]
+    uint32_t* bits;         // [B][W32] survivor bitmap by anchor id
+    int32_t* wprefix;       // [B][W32] exclusive popcount prefix of bits
+    uint64_t* keys0;        // [B][A]
+    uint64_t* keys1;        // [B][A]
+    float4* box;            // [B][A] decoded+clipped box of each survivor, by anchor id
+    int32_t* label;         // [B][A] arg-max class of each survivor, by anchor id
+    uint64_t* kept_key;     // [B][A] sort key of each kept box, in keep order
+    float4* kept_box;       // [B][A]
+    size_t bytes;
+    int W32;
+};
+
+static K7DetectWs k7_detect_ws(void* base, int B, int A) {
+    K7DetectWs w;
+    unsigned char* p = static_cast<unsigned char*>(base);
+    size_t o = 0;
+    const size_t BA = (size_t)B * A;
+    w.W32 = (A + 31) / 32;
+    auto take = [&](size_t bytes) {
+        unsigned char* r = p ? p + o : nullptr;
+        o += k7_align_up(bytes, 256);
+        return r;
+    };
+    w.surv_count = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.kept_count = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.bits = reinterpret_cast<uint32_t*>(take(sizeof(uint32_t) * (size_t)B * w.W32));
+    w.wprefix = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * w.W32));
+    w.keys0 = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
+    w.keys1 = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
+    w.box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
+    w.label = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * BA));
+    w.kept_key = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
+    w.kept_box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
+    w.bytes = o;
+    return w;
+}
+
+extern "C" size_t k7_detect_workspace_bytes(int B, int A, int C) {
+    (void)C;
+    if (B <= 0 || A <= 0) return 0;
+    return k7_detect_ws(nullptr, B, A).bytes;
+}
+
+// ------------------------------------------------------------------ kernel 1: score + decode + compaction
+#define K7_SCORE_MAX_THREADS 768
+
+template <int VEC>
+__device__ __forceinline__ float k7_vec_max(const float* __restrict__ p) {
+    if (VEC == 4) {
+        const float4 v = *reinterpret_cast<const float4*>(p);
+        return fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+    } else if (VEC == 2) {
+        const float2 v = *reinterpret_cast<const float2*>(p);
+        return fmaxf(v.x, v.y);
+    }
+    return *p;
+}
+
+template <int VEC, bool FROM_SPEC>
+__global__ void __launch_bounds__(K7_SCORE_MAX_THREADS, 1)
+k7_score_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
+                const float* __restrict__ cls, const float4* __restrict__ reg, int B, int A,
+                const __grid_constant__ K7DetectParams P, const __grid_constant__ K7StreamGeom G,
+                int32_t* __restrict__ surv_count, uint32_t* __restrict__ bits, int W32, uint64_t* __restrict__ keys,
+                float4* __restrict__ box_ws, int32_t* __restrict__ label_ws) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int NS = G.stages;
+    unsigned char* ring = smem + (size_t)warp * NS * G.stage_stride;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)G.warps * NS * G.stage_stride) + warp * NS;
+    const long long gw = (long long)blockIdx.x * G.warps + warp;
+    const long long nW = (long long)gridDim.x * G.warps;
+    if (gw >= G.num_tiles) return;
+    if (lane == 0) {
+        for (int s = 0; s < NS; ++s) k7_mbar_init(bars + s, 1);
+        k7_fence_mbar_init();
+        k7_fence_proxy_async();
+    }
+    __syncwarp();
+    const int PF = NS - 1;
+    if (lane == 0) {
+        for (int k = 0; k < PF; ++k) {
+            const long long t = gw + k * nW;
+            if (t < G.num_tiles) k7_stream_issue(G, cls, nullptr, t, ring + (size_t)(k % NS) * G.stage_stride, bars + (k % NS));
+        }
+    }
+    const int q = lane & (G.lpr - 1);
+    const int rsub = lane >> G.lpr_shift;
+    int clo, chi;
+    k7_class_range(G, q, clo, chi);
+
+    int it = 0;
+    for (long long tile = gw; tile < G.num_tiles; tile += nW, ++it) {
+        const int s = it % NS;
+        unsigned char* stage = ring + (size_t)s * G.stage_stride;
+        if (lane == 0) {
+            const long long t = tile + (long long)PF * nW;
+            if (t < G.num_tiles) {
+                const int sn = (it + PF) % NS;
+                k7_stream_issue(G, cls, nullptr, t, ring + (size_t)sn * G.stage_stride, bars + sn);
+            }
+        }
+        k7_mbar_wait(bars + s, (it / NS) & 1);
+        const long long row0 = tile * (long long)G.T;
+        long long rows_ll = G.total_rows - row0;
+        const int rows = rows_ll > G.T ? G.T : (int)rows_ll;
+        float* tilef = reinterpret_cast<float*>(stage);
+        const uint32_t cls_bytes = (uint32_t)rows * G.C * 4u;
+        const uint32_t rem = cls_bytes & 15u;
+        if (rem) {
+            if (lane == 0) {
+                const uint32_t base = (cls_bytes & ~15u) >> 2;
+                for (uint32_t k = 0; k < (rem >> 2); ++k) tilef[base + k] = cls[row0 * G.C + base + k];
+            }
+            __syncwarp();
+        }
+
+        for (int i = 0; i < G.iters; ++i) {
+            const int r = i * G.rows_per_iter + rsub;
+            const bool rvalid = r < rows;
+            const float* rowp = tilef + (size_t)(rvalid ? r : 0) * G.C;
+            // class maximum of this lane's range, then of the row (torch.max(cls, dim=2), retinanet.py:300)
+            float m = -INFINITY;
+            if (rvalid) {
+                int j = clo;
+                float m1 = -INFINITY;
+                for (; j + 2 * VEC <= chi; j += 2 * VEC) {
+                    m = fmaxf(m, k7_vec_max<VEC>(rowp + j));
+                    m1 = fmaxf(m1, k7_vec_max<VEC>(rowp + j + VEC));
+                }
+                for (; j < chi; j += VEC) m = fmaxf(m, k7_vec_max<VEC>(rowp + j));
+                m = fmaxf(m, m1);
+            }
+            for (int o = G.lpr >> 1; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            const bool pass = rvalid && (m > P.score_thr);   // strict, retinanet.py:302
+            if (__ballot_sync(0xffffffffu, pass) == 0u) continue;   // warp-uniform: nothing survives in these rows
+
+            // first class index attaining the maximum (torch .max(dim=1) on the kept rows, retinanet.py:316)
+            int lab = 0x7fffffff;
+            if (pass) {
+                for (int j = chi - 1; j >= clo; --j)
+                    if (rowp[j] == m) lab = j;
+            }
+            for (int o = G.lpr >> 1; o > 0; o >>= 1) lab = min(lab, __shfl_xor_sync(0xffffffffu, lab, o));
+
+            const bool owner = pass && (q == 0);
+            const long long R = row0 + r;
+            const int b = owner ? (int)(R / A) : 0;
+            const int a = owner ? (int)(R - (long long)b * A) : 0;
+            // slot allocation: one atomic per (warp, image); a tile touches at most two images
+            const int b_first = (int)(row0 / A);
+            const unsigned own0 = __ballot_sync(0xffffffffu, owner && b == b_first);
+            const unsigned own1 = __ballot_sync(0xffffffffu, owner && b != b_first);
+            int base0 = 0, base1 = 0;
+            if (lane == 0) {
+                if (own0) base0 = atomicAdd(surv_count + b_first, __popc(own0));
+                if (own1) base1 = atomicAdd(surv_count + b_first + 1, __popc(own1));
+            }
+            base0 = __shfl_sync(0xffffffffu, base0, 0);
+            base1 = __shfl_sync(0xffffffffu, base1, 0);
+            if (owner) {
+                const unsigned lt = (1u << lane) - 1u;
+                const int slot = (b == b_first) ? base0 + __popc(own0 & lt) : base1 + __popc(own1 & lt);
+                float ax1, ay1, ax2, ay2;
+                k7_anchor<FROM_SPEC>(spec, anchors, box_order, a, ax1, ay1, ax2, ay2);
+                const float4 d = __ldg(reg + R);
+                K7Box o = (P.decode.variant == K7_DECODE_RETINA)
+                              ? k7_decode_retina(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w, P.decode.mean, P.decode.std)
+                              : k7_decode_effdet(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w);
+                if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
+                const size_t oa = (size_t)b * A + a;
+                box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
+                label_ws[oa] = lab;
+                keys[(size_t)b * A + slot] = ((uint64_t)k7_score_key_desc(m) << 32) | (uint32_t)a;
+                atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------ kernel 2: per-image sort + NMS
+#define K7_NMS_THREADS 1024
+#define K7_NMS_CHUNK 1024
+#define K7_NMS_WORDS (K7_NMS_CHUNK / 64)
+#define K7_NMS_PITCH (K7_NMS_CHUNK + 1)   // u64 pitch of a mask word-row: conflict-free for writer and scanner
+
+struct K7SortSmem {
+    unsigned int hist[256];
+    unsigned int base[256];
+    unsigned int wtot[32];
+    int skip;
+    int pad[3];
+    unsigned int warp_cnt[32][256];
+};
+struct K7NmsSmem {
+    float4 box[K7_NMS_CHUNK];
+    float area[K7_NMS_CHUNK];
+    float4 kbox[256];
+    float karea[256];
+    unsigned int alive_bits[K7_NMS_CHUNK / 32];
+    int kept_rows[K7_NMS_CHUNK];
+    int kcount;
+    int pad[3];
+    unsigned long long mask[K7_NMS_WORDS * K7_NMS_PITCH];
+};
+
+// Stable LSD radix sort (8 bits per pass) of n 64-bit keys by one CTA; returns the buffer holding the result.
+__device__ uint64_t* k7_block_radix_sort(uint64_t* a, uint64_t* b, int n, K7SortSmem& S) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = pass * 8;
+        if (tid < 256) S.hist[tid] = 0;
+        if (tid == 0) S.skip = 0;
+        __syncthreads();
+        for (int i = tid; i < n; i += K7_NMS_THREADS) atomicAdd(&S.hist[(unsigned)(a[i] >> shift) & 255u], 1u);
+        __syncthreads();
+        if (tid < 256 && S.hist[tid] == (unsigned)n) S.skip = 1;   // every key has the same digit
+        __syncthreads();
+        if (S.skip) continue;
+        if (warp < 8) {   // exclusive scan of the 256 bins: 8 warps x 32 bins
+            const unsigned v = S.hist[tid];
+            unsigned inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            S.base[tid] = inc - v;
+            if (lane == 31) S.wtot[warp] = inc;
+        }
+        __syncthreads();
+        if (tid < 256) {
+            unsigned off = 0;
+            for (int w = 0; w < (tid >> 5); ++w) off += S.wtot[w];
+            S.base[tid] += off;
+        }
+        __syncthreads();
+        for (int c0 = 0; c0 < n; c0 += K7_NMS_THREADS) {
+            for (int k = tid; k < 32 * 256; k += K7_NMS_THREADS) (&S.warp_cnt[0][0])[k] = 0;
+            __syncthreads();
+            const int i = c0 + tid;
+            const bool valid = i < n;
+            const uint64_t key = valid ? a[i] : 0ull;
+            const unsigned d = valid ? ((unsigned)(key >> shift) & 255u) : 256u;
+            const unsigned peers = __match_any_sync(0xffffffffu, d);
+            const int rank = __popc(peers & ((1u << lane) - 1u));
+            if (valid && rank == 0) S.warp_cnt[warp][d] = __popc(peers);
+            __syncthreads();
+            if (tid < 256) {
+                unsigned run = S.base[tid];
+#pragma unroll 4
+                for (int w = 0; w < 32; ++w) {
+                    const unsigned c = S.warp_cnt[w][tid];
+                    S.warp_cnt[w][tid] = run;
+                    run += c;
+                }
+                S.base[tid] = run;
+            }
+            __syncthreads();
+            if (valid) b[S.warp_cnt[warp][d] + rank] = key;
+            __syncthreads();
+        }
+        uint64_t* t = a;
+        a = b;
+        b = t;
+    }
+    __syncthreads();
+    return a;
+}
+
+__device__ __forceinline__ float k7_key_score(uint64_t key) {
+    uint32_t u = ~(uint32_t)(key >> 32);
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    return __uint_as_float(u);
+}
+
+// Greedy NMS over keys sorted in visiting order; box of key k is boxes[k & 0xffffffff].
+// Writes kept keys/boxes in keep order, returns the number kept.
+__device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const float4* __restrict__ boxes, float thr,
+                            int max_keep, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, K7NmsSmem& S) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int kept0 = 0;
+    for (int c0 = 0; c0 < n && kept0 < max_keep; c0 += K7_NMS_CHUNK) {
+        const int i = c0 + tid;
+        const int cn = min(K7_NMS_CHUNK, n - c0);
+        const bool valid = tid < cn;
+        uint64_t key = 0;
+        float4 bx = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid) {
+            key = keys[i];
+            bx = __ldg(boxes + (uint32_t)(key & 0xffffffffull));
+        }
+        const K7Box me = {bx.x, bx.y, bx.z, bx.w};
+        const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
+        bool alive = valid;
+        // (a) suppression by boxes kept in earlier chunks
+        for (int k0 = 0; k0 < kept0; k0 += 256) {
+            const int kn = min(256, kept0 - k0);
+            __syncthreads();
+            if (tid < kn) {
+                const float4 kb = kept_box[k0 + tid];
+                S.kbox[tid] = kb;
+                S.karea[tid] = k7_area(kb.x, kb.y, kb.z, kb.w);
+            }
+            __syncthreads();
+            if (alive) {
+                for (int k = 0; k < kn; ++k) {
+                    const float4 kb = S.kbox[k];
+                    const K7Box other = {kb.x, kb.y, kb.z, kb.w};
+                    if (fminf(other.x2, me.x2) > fmaxf(other.x1, me.x1) && fminf(other.y2, me.y2) > fmaxf(other.y1, me.y1) &&
+                        k7_nms_suppress(other, S.karea[k], me, area, thr)) {
+                        alive = false;
+                        break;
+                    }
+                }
+            }
+        }
+        // (b) bitmask matrix of the chunk
+        S.box[tid] = bx;
+        S.area[tid] = area;
+        const unsigned ab = __ballot_sync(0xffffffffu, alive);
+        if (lane == 0) S.alive_bits[warp] = ab;
+        if (tid == 0) S.kcount = 0;
+        __syncthreads();
+        if (alive) {
+            for (int w = tid >> 6; w < (cn + 63) >> 6; ++w) {
+                unsigned long long word = 0ull;
+                const int jbeg = max(w * 64, tid + 1), jend = min(w * 64 + 64, cn);
+                for (int j = jbeg; j < jend; ++j) {
+                    const float4 ob = S.box[j];
+                    const K7Box other = {ob.x, ob.y, ob.z, ob.w};
+                    // an empty intersection gives overlap 0 (or NaN), never > thr >= 0: skip the division
+                    if (fminf(me.x2, other.x2) > fmaxf(me.x1, other.x1) && fminf(me.y2, other.y2) > fmaxf(me.y1, other.y1) &&
+                        k7_nms_suppress(me, area, other, S.area[j], thr))
+                        word |= 1ull << (j & 63);
+                }
+                S.mask[w * K7_NMS_PITCH + tid] = word;
+            }
+        }
+        __syncthreads();
+        // (c) sequential scan by warp 0: lane w keeps the removed-word w of the chunk
+        if (warp == 0) {
+            unsigned long long remv = ~0ull;
+            if (lane < K7_NMS_WORDS)
+                remv = ~((unsigned long long)S.alive_bits[2 * lane] | ((unsigned long long)S.alive_bits[2 * lane + 1] << 32));
+            int kc = 0;
+            const int budget = max_keep - kept0;
+            for (int w = 0; w < (cn + 63) >> 6 && kc < budget; ++w) {
+                unsigned long long cur = __shfl_sync(0xffffffffu, remv, w);
+                while (kc < budget) {
+                    const unsigned long long freeb = ~cur;
+                    if (freeb == 0ull) break;
+                    const int bit = __ffsll((long long)freeb) - 1;
+                    const int row = w * 64 + bit;
+                    if (row >= cn) break;
+                    if (lane == 0) S.kept_rows[kc] = row;
+                    ++kc;
+                    if (lane < K7_NMS_WORDS && lane >= w) remv |= S.mask[lane * K7_NMS_PITCH + row];
+                    cur = __shfl_sync(0xffffffffu, remv, w) | (1ull << bit);
+                    // the kept row itself must not be revisited
+                    if (lane == w) remv |= (1ull << bit);
+                }
+            }
+            if (lane == 0) S.kcount = kc;
+        }
+        __syncthreads();
+        const int kc = S.kcount;
+        for (int k = tid; k < kc; k += K7_NMS_THREADS) {
+            const int row = S.kept_rows[k];
+            kept_key[kept0 + k] = keys[c0 + row];
+            kept_box[kept0 + k] = S.box[row];
+        }
+        kept0 += kc;
+        __syncthreads();
+    }
+    return kept0;
+}
+
+union K7SortNmsSmem {
+    K7SortSmem sort;
+    K7NmsSmem nms;
+};
+
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int32_t* __restrict__ surv_count,
+                   int32_t* __restrict__ kept_count, const uint32_t* __restrict__ bits, int32_t* __restrict__ wprefix,
+                   uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws,
+                   uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, int32_t* __restrict__ counts_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
+    __shared__ int s_carry;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_all = surv_count[b];
+    const size_t ob = (size_t)b * A;
+
+    // exclusive popcount prefix over the survivor bitmap: rank of an anchor in the thresholded list
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
+        const int w = w0 + tid;
+        const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) S.sort.wtot[warp] = (unsigned)inc;
+        __syncthreads();
+        int woff = 0;
+        for (int k = 0; k < warp; ++k) woff += (int)S.sort.wtot[k];
+        const int carry = s_carry;
+        if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
+        __syncthreads();
+        if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
+        __syncthreads();
+    }
+
+    uint64_t* sorted = k7_block_radix_sort(keys0 + ob, keys1 + ob, n_all, S.sort);
+    int n = n_all;
+    if (pre_topk > 0 && n > pre_topk) n = pre_topk;
+    const int max_keep = max_det > 0 ? max_det : 0x7fffffff;
+    const int kept = k7_block_nms(sorted, n, box_ws + ob, iou_thr, max_keep, kept_key + ob, kept_box + ob, S.nms);
+    if (tid == 0) {
+        kept_count[b] = kept;
+        if (counts_out) {
+            counts_out[2 * b + 0] = n_all;
+            counts_out[2 * b + 1] = kept;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ gather
+__global__ void __launch_bounds__(256)
+k7_gather_kernel(int A, int W32, int cap, const int32_t* __restrict__ kept_count, const uint64_t* __restrict__ kept_key,
+                 const float4* __restrict__ kept_box, const int32_t* __restrict__ label_ws, const uint32_t* __restrict__ bits,
+                 const int32_t* __restrict__ wprefix, float* __restrict__ scores, int64_t* __restrict__ labels,
+                 float4* __restrict__ boxes, int32_t* __restrict__ anchor_ids, int32_t* __restrict__ ranks) {
+    const int b = blockIdx.y;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int kc = min(kept_count[b], cap);
+    if (k >= kc) return;
+    const size_t ob = (size_t)b * A;
+    const uint64_t key = kept_key[ob + k];
+    const int a = (int)(uint32_t)(key & 0xffffffffull);
+    const size_t o = (size_t)b * cap + k;
+    scores[o] = k7_key_score(key);
+    labels[o] = (int64_t)label_ws[ob + a];
+    boxes[o] = kept_box[ob + k];
+    if (anchor_ids) anchor_ids[o] = a;
+    if (ranks) {
+        const size_t wi = (size_t)b * W32 + (a >> 5);
+        ranks[o] = wprefix[wi] + __popc(bits[wi] & ((1u << (a & 31)) - 1u));
+    }
+}
+
+// ------------------------------------------------------------------ host: k7_detect
+template <int VEC, bool FROM_SPEC>
+static int k7_score_launch(const K7AnchorSpec& spec, const float* anchors, int box_order, const float* cls, const float* reg,
+                           int B, int A, const K7DetectParams& P, const K7StreamGeom& G, const K7DetectWs& w,
+                           cudaStream_t st) {
+    auto kern = k7_score_kernel<VEC, FROM_SPEC>;
+    K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
+    kern<<<G.grid, G.warps * 32, G.smem_bytes, st>>>(spec, anchors, box_order, cls, reinterpret_cast<const float4*>(reg), B, A,
+                                                     P, G, w.surv_count, w.bits, w.W32, w.keys0, w.box, w.label);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
+extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
+                         int B, int A, int C, const K7DetectParams* params, int32_t* counts, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+    K7_REQUIRE(cls && reg && params && workspace, "k7_detect: null argument");
+    K7_REQUIRE(spec || anchors, "k7_detect: need an anchor spec or an anchor tensor");
+    K7_REQUIRE(B > 0 && A >= 32 && C > 0, "k7_detect: bad shape B=%d A=%d C=%d (A >= 32 required)", B, A, C);
+    K7_REQUIRE(params->iou_thr >= 0.0f, "k7_detect: iou_thr must be >= 0");
+    K7_REQUIRE(params->decode.variant == K7_DECODE_RETINA || params->decode.variant == K7_DECODE_EFFDET,
+               "k7_detect: bad decode variant");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(reg) & 15) == 0,
+               "k7_detect: cls and reg must be 16-byte aligned");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "k7_detect: workspace must be 256-byte aligned");
+    if (spec) {
+        int rc = k7_check_spec(spec, A);
+        if (rc) return rc;
+        box_order = spec->box_order;
+    } else {
+        K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_detect: anchors must be 16-byte aligned");
+        K7_REQUIRE(box_order == K7_BOX_XYXY || box_order == K7_BOX_YXYX, "k7_detect: bad box_order");
+    }
+    const K7DetectWs w = k7_detect_ws(workspace, B, A);
+    if (workspace_bytes < w.bytes) {
+        k7_set_error("k7_detect: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
+        return K7_EWORKSPACE;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    K7StreamGeom G;
+    int rc = k7_stream_geometry((long long)B * A, A, C, 0, 3, K7_SCORE_MAX_THREADS / 32, &G);
+    if (rc) return rc;
+
+    // surv_count, kept_count and the bitmap are contiguous at the start of the workspace
+    K7_CUDA(cudaMemsetAsync(w.surv_count, 0, (size_t)(reinterpret_cast<unsigned char*>(w.wprefix) -
+                                                      reinterpret_cast<unsigned char*>(w.surv_count)), st));
+    static const K7AnchorSpec kEmpty = {};
+    const K7AnchorSpec& sp = spec ? *spec : kEmpty;
+    if (G.vec == 4)
+        rc = spec ? k7_score_launch<4, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                  : k7_score_launch<4, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+    else if (G.vec == 2)
+        rc = spec ? k7_score_launch<2, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                  : k7_score_launch<2, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+    else
+        rc = spec ? k7_score_launch<1, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                  : k7_score_launch<1, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+    if (rc) return rc;
+
+    const size_t smem = sizeof(K7SortNmsSmem);
+    K7_CUDA(cudaFuncSetAttribute(k7_sort_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk, params->max_detections,
+                                                        w.surv_count, w.kept_count, w.bits, w.wprefix, w.keys0, w.keys1, w.box,
+                                                        w.kept_key, w.kept_box, counts);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
+extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B, int A, int C, int cap, float* scores,
+                                int64_t* labels, float* boxes, int32_t* anchor_ids, int32_t* survivor_rank, void* stream) {
+    (void)C;
+    K7_REQUIRE(workspace && scores && labels && boxes, "k7_detect_gather: null argument");
+    K7_REQUIRE(B > 0 && A > 0 && cap > 0, "k7_detect_gather: bad shape");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "k7_detect_gather: boxes must be 16-byte aligned");
+    const K7DetectWs w = k7_detect_ws(const_cast<void*>(workspace), B, A);
+    if (workspace_bytes < w.bytes) {
+        k7_set_error("k7_detect_gather: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
+        return K7_EWORKSPACE;
+    }
+    dim3 grid((cap + 255) / 256, B);
+    k7_gather_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(A, w.W32, cap, w.kept_count, w.kept_key, w.kept_box,
+                                                                         w.label, w.bits, w.wprefix, scores, labels,
+                                                                         reinterpret_cast<float4*>(boxes), anchor_ids,
+                                                                         survivor_rank);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
+// ------------------------------------------------------------------ stand-alone NMS (torchvision.ops.nms)
+struct K7NmsWs {
+    uint64_t* keys0;
+    uint64_t* keys1;
+    uint64_t* kept_key;
+    float4* kept_box;
+    size_t bytes;
+};
+static K7NmsWs k7_nms_ws(void* base, int n) {
+    K7NmsWs w;
+    unsigned char* p = static_cast<unsigned char*>(base);
+    size_t o = 0;
+    auto take = [&](size_t bytes) {
+        unsigned char* r = p ? p + o : nullptr;
+        o += k7_align_up(bytes, 256);
+        return r;
+    };
+    const size_t nn = n > 0 ? n : 1;
+    w.keys0 = reinterpret_cast<uint64_t*>(take(8 * nn));
+    w.keys1 = reinterpret_cast<uint64_t*>(take(8 * nn));
+    w.kept_key = reinterpret_cast<uint64_t*>(take(8 * nn));
+    w.kept_box = reinterpret_cast<float4*>(take(16 * nn));
+    w.bytes = o;
+    return w;
+}
+extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_nms_ws(nullptr, n).bytes; }
+
+__global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keys[i] = ((uint64_t)k7_score_key_desc(scores[i]) << 32) | (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_single_kernel(int n, float iou_thr, uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1,
+                     const float4* __restrict__ boxes, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
+                     int64_t* __restrict__ keep, int32_t* __restrict__ count) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
+    uint64_t* sorted = k7_block_radix_sort(keys0, keys1, n, S.sort);
+    const int kept = k7_block_nms(sorted, n, boxes, iou_thr, 0x7fffffff, kept_key, kept_box, S.nms);
+    __syncthreads();
+    for (int k = threadIdx.x; k < kept; k += K7_NMS_THREADS) keep[k] = (int64_t)(uint32_t)(kept_key[k] & 0xffffffffull);
+    if (threadIdx.x == 0) *count = kept;
+}
+
+extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_thr, int64_t* keep, int32_t* count,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    K7_REQUIRE(count && workspace, "k7_nms: null argument");
+    K7_REQUIRE(n >= 0 && iou_thr >= 0.0f, "k7_nms: bad argument n=%d iou_thr=%f", n, (double)iou_thr);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n == 0) {
+        K7_CUDA(cudaMemsetAsync(count, 0, sizeof(int32_t), st));
+        return K7_OK;
+    }
+    K7_REQUIRE(boxes && scores && keep, "k7_nms: null argument");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
+               "k7_nms: boxes must be 16-byte and workspace 256-byte aligned");
+    const K7NmsWs w = k7_nms_ws(workspace, n);
+    if (workspace_bytes < w.bytes) {
+        k7_set_error("k7_nms: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
+        return K7_EWORKSPACE;
+    }
+    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0);
+    K7_LAUNCH_CHECK();
+    const size_t smem = sizeof(K7SortNmsSmem);
+    K7_CUDA(cudaFuncSetAttribute(k7_nms_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k7_nms_single_kernel<<<1, K7_NMS_THREADS, smem, st>>>(n, iou_thr, w.keys0, w.keys1, reinterpret_cast<const float4*>(boxes),
+                                                          w.kept_key, w.kept_box, keep, count);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
