@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py — images/s of the detection-head hot path (match+loss and decode+NMS) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic head outputs of the
+BASELINE.json shape (default: configs[1], EfficientDet-D0 512x512, batch 64, 90 classes,
+<=100 GT boxes/image, 9 anchors/cell = 49 104 anchors/image):
+    training side   FocalLoss forward + backward (assignment, focal + smooth-L1, gradients)
+    inference side  decode + clip + score threshold + sort + NMS for every image of the batch
+`value` = images/s with inputs resident in HBM (device-timed, max over ranks);
+`e2e`   = the same step from PINNED HOST buffers through the public module API, host->device
+          copies of the inputs and device->host reads of the results inside the timed region;
+`roofline` = the dominant kernel (k7_loss, forward+backward) against the measured HBM peak;
+`cpu_baseline` = the oracle port (oracle/restate.py, torch-CPU, all host threads) on a
+          bounded sample of the same workload (rank 0, N=1 only).
+N > 1 (torchrun): every rank owns a full batch (weak scaling), the loss sums are combined
+with one 16-byte NCCL all-reduce per step.
+`--impl reference` times the reference's CPU algorithm for the same step (the oracle port;
+the reference is pure Python/PyTorch, there is nothing to compile) and prints the same line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "images/s for match+loss and decode+NMS"
+UNIT = "images/s"
+DEFAULT_WORKLOAD = "c2_effdet_d0_512"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
+    ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch (debug)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ CPU arm (oracle port)
+def cpu_step(R, cls, reg, anc, ann, hw):
+    """The reference's algorithm for one step on CPU tensors: FocalLoss fwd+bwd, then the eval tail."""
+    c = cls.detach().requires_grad_(True)
+    r = reg.detach().requires_grad_(True)
+    out = R.focal_loss(c, r, anc, ann)
+    (out.cls_mean + out.reg_mean).sum().backward()
+    with torch.no_grad():
+        R.detect_batch(cls, reg, anc, hw[0], hw[1])
+    return out
+
+
+def cpu_inputs(wl, n_images, seed=0):
+    import b200det
+    from oracle import restate as R
+    cls, reg, ann = b200det.synth.make_inputs(wl, seed=seed, device="cpu", batch=n_images)
+    anc = torch.from_numpy(R.retina_anchors(wl.height, wl.width, **wl.anchor_kwargs()))[None]
+    return R, cls, reg, ann, anc
+
+
+def cpu_baseline(wl, budget_s=15.0):
+    """Oracle port timed on the host cores on a bounded sample of the workload."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    R, cls, reg, ann, anc = cpu_inputs(wl, 1)
+    hw = (wl.height, wl.width)
+    cpu_step(R, cls, reg, anc, ann, hw)                       # warm-up
+    t0 = time.perf_counter()
+    cpu_step(R, cls, reg, anc, ann, hw)
+    per_img = time.perf_counter() - t0
+    n = int(max(1, min(wl.batch, budget_s / max(per_img, 1e-6))))
+    R, cls, reg, ann, anc = cpu_inputs(wl, n)
+    t0 = time.perf_counter()
+    cpu_step(R, cls, reg, anc, ann, hw)
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{n} of {wl.batch} images of {wl.name}, 1 pass (FocalLoss fwd+bwd + decode/NMS), "
+                      f"torch-CPU oracle port of the reference, {cores} threads"}
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    R, cls, reg, ann, anc = cpu_inputs(wl, 1)
+    hw = (wl.height, wl.width)
+    t0 = time.perf_counter()
+    cpu_step(R, cls, reg, anc, ann, hw)
+    per_img = time.perf_counter() - t0
+    total_steps = args.steps + args.warmup
+    # bound the whole run to ~2 minutes
+    n = int(max(1, min(wl.batch, 120.0 / max(per_img * total_steps, 1e-6))))
+    R, cls, reg, ann, anc = cpu_inputs(wl, n)
+    for _ in range(args.warmup):
+        cpu_step(R, cls, reg, anc, ann, hw)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_step(R, cls, reg, anc, ann, hw)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = (f"{n} of {wl.batch} images of {wl.name} per step; oracle port (torch-CPU restatement of the "
+              f"reference, same ATen ops), {cores} threads")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(wl, n, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def workload_config(wl, batch, gpus):
+    return {"workload": wl.name, "image": [wl.height, wl.width], "batch_per_gpu": batch, "global_batch": batch * gpus,
+            "classes": wl.classes, "anchors_per_image": wl.anchors, "max_gt_per_image": wl.max_gt,
+            "step": "FocalLoss fwd+bwd + decode/clip/threshold/sort/NMS on every image",
+            "cache": "inputs (>= 1 GB per step) are larger than the 126 MB L2; no flush needed",
+            "parallelism": f"image-sharded x{gpus}, one 16-byte all-reduce per step" if gpus > 1 else "single GPU"}
+
+
+# ------------------------------------------------------------------------------ B200 arm
+def timed(fn, steps, warmup, stream_sync=True):
+    """Average milliseconds per call over `steps` calls, CUDA events on the current stream."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def run_b200(args, wl):
+    import torch.distributed as dist
+    import b200det
+    from b200det import _lib as L
+    from b200det import losses as BL
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (b200det has no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L.lib()                                                    # fail loudly if libk7det.so is missing
+
+    B = args.batch or wl.batch
+    A, C, M = wl.anchors, wl.classes, wl.max_gt
+    hw = (wl.height, wl.width)
+    cls, reg, ann = b200det.synth.make_inputs(wl, seed=rank, device=dev, batch=B)
+    img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
+    anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
+    loss_mod = b200det.FocalLoss(sharded=world > 1)
+    cls_g = cls.detach().requires_grad_(True)
+    reg_g = reg.detach().requires_grad_(True)
+
+    def train_side():
+        cls_g.grad = None
+        reg_g.grad = None
+        lc, lr = loss_mod(cls_g, reg_g, anchors_mod(img), ann)
+        (lc + lr).sum().backward()
+        return lc, lr
+
+    def eval_side(sync=False):
+        return b200det.detect(cls, reg, anchors_mod(img), hw, sync=sync)
+
+    def step():
+        train_side()
+        eval_side()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+
+    # ---- value: K steps, device resident, barrier + synchronize on both sides, max over ranks
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = float(ms_total.item()) / args.steps
+    value = world * B / (ms_step * 1e-3)
+
+    peak, peak_src = peaks()
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config(wl, B, world),
+        "gpu_launches": 9 * args.steps,
+        "launches_per_step": {"k7_match": 1, "k7_loss(scales+stream+finalize)": 3, "k7_scale_inplace": 2,
+                              "k7_detect(score+sort_nms)": 2, "k7_detect_gather": 1},
+    }
+
+    # ---- parts and the roofline of the dominant kernel (every rank runs them; rank 0 reports)
+    k = max(args.steps, 10)
+    with torch.no_grad():
+        ms_fwd = timed(lambda: loss_mod(cls, reg, anchors_mod(img), ann), k, 3)
+    ms_fb = timed(train_side, k, 3)
+    ms_det = timed(eval_side, k, 3)
+    anc = anchors_mod(img)
+    assign, num_pos = BL.match(anc, ann, A, 0.35, 0.45)
+    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
+    ms_match = timed(lambda: BL.match(anc, ann, A, 0.35, 0.45), k, 3)
+    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, **kw), k, 3)
+    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, **kw), k, 3)
+    surv = int(eval_side(sync=True).survivors.sum())
+    bytes_fwd = B * (A * (4 * C + 16) + 20 * M)
+    bytes_fb = B * (A * (8 * C + 32) + 20 * M)
+    bytes_det = B * A * (4 * C + 16) + 32 * surv
+
+    def gbs(nbytes, ms):
+        return nbytes / (ms * 1e-3) / 1e9
+
+    out["parts"] = {
+        "match_loss_fwd": {"ms": ms_fwd, "images_per_s": B / ms_fwd * 1e3, "hbm_frac": gbs(bytes_fwd, ms_fwd) / peak},
+        "match_loss_fwd_bwd": {"ms": ms_fb, "images_per_s": B / ms_fb * 1e3, "hbm_frac": gbs(bytes_fb, ms_fb) / peak},
+        "decode_nms": {"ms": ms_det, "images_per_s": B / ms_det * 1e3, "hbm_frac": gbs(bytes_det, ms_det) / peak,
+                       "survivors_per_image": surv / B},
+        "k7_match_ms": ms_match, "k7_loss_fwd_ms": ms_k_f, "k7_loss_fwd_bwd_ms": ms_k_fb,
+        "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
+    }
+    ach = gbs(bytes_fb, ms_k_fb)
+    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_kernel<grad> (k7_loss call: scales + stream + finalize)",
+                       "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                       "algorithmic_bytes_per_launch": bytes_fb, "avg_launch_ms": ms_k_fb, "peak_source": peak_src}
+
+    # ---- e2e: pinned host inputs -> H2D -> public modules -> D2H of the results, every step
+    if not args.no_e2e:
+        h_cls, h_reg, h_ann = (t.cpu().pin_memory() for t in (cls, reg, ann))
+        d_cls, d_reg, d_ann = torch.empty_like(cls), torch.empty_like(reg), torch.empty_like(ann)
+        d2h = [0]
+
+        def e2e_step():
+            d_cls.copy_(h_cls, non_blocking=True)
+            d_reg.copy_(h_reg, non_blocking=True)
+            d_ann.copy_(h_ann, non_blocking=True)
+            c = d_cls.detach().requires_grad_(True)
+            r = d_reg.detach().requires_grad_(True)
+            lc, lr = loss_mod(c, r, anchors_mod(img), d_ann)
+            (lc + lr).sum().backward()
+            losses = torch.cat([lc.detach(), lr.detach()]).cpu()
+            det = b200det.detect(d_cls, d_reg, anchors_mod(img), hw, sync=True)
+            kmax = max(int(det.count.max()), 1)
+            res = (det.scores[:, :kmax].cpu(), det.labels[:, :kmax].cpu(), det.boxes[:, :kmax].cpu())
+            d2h[0] = losses.numel() * 4 + B * 2 * 4 + sum(t.numel() * t.element_size() for t in res)
+
+        n_e2e = max(3, min(args.steps, 10))
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        torch.cuda.synchronize()
+        ms_e2e = torch.tensor([(time.perf_counter() - t0) * 1e3 / n_e2e], device=dev)
+        if world > 1:
+            dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+        out["e2e"] = {"value": world * B / (float(ms_e2e.item()) * 1e-3), "unit": UNIT,
+                      "h2d_bytes_per_step": sum(t.numel() * 4 for t in (cls, reg, ann)), "d2h_bytes_per_step": d2h[0],
+                      "ms_per_step": float(ms_e2e.item()), "steps": n_e2e,
+                      "note": "pinned host -> device copies + FocalLoss fwd+bwd + detect + results to host; PCIe-bound"}
+
+    if rank == 0:
+        out["clocks"] = sampler.stop()
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(wl)
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    import b200det
+    wl = b200det.synth.WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_b200(args, wl)
+
+
+if __name__ == "__main__":
+    main()

@@ -38,6 +38,12 @@ extern "C" {
 
 #define K7_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define K7_API __attribute__((visibility("default")))
+#else
+#define K7_API
+#endif
+
 #define K7_OK 0
 #define K7_EINVAL (-1)     /* bad argument (shape, null pointer, alignment, unsupported size) */
 #define K7_EWORKSPACE (-2) /* workspace too small */
@@ -73,12 +79,12 @@ typedef struct K7AnchorSpec {
  * anchors are generated in registers and never read from memory; with only a tensor
  * (anchors built by someone else) they are loaded.  One of the two must be given. */
 
-int k7_version(void);
-const char* k7_last_error(void);
+K7_API int k7_version(void);
+K7_API const char* k7_last_error(void);
 
 /* Replaces Anchors.forward (architectures/anchors.py:38-60; utils_efficientdet.py:74-137):
  * writes out[A,4] float32. */
-int k7_anchors_materialize(const K7AnchorSpec* spec, float* out, void* stream);
+K7_API int k7_anchors_materialize(const K7AnchorSpec* spec, float* out, void* stream);
 
 /* ---- training side ------------------------------------------------------------------ */
 
@@ -99,7 +105,7 @@ typedef struct K7MatchParams {
  *   num_pos [B]   int32   positives per image
  *   iou_max [B,A] float32 (optional, may be NULL)  bit-identical to torch.max(IoU,1).values
  *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list */
-int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
+K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
              const float* annotations, int B, int A, int M, const K7MatchParams* params,
              int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, void* stream);
 
@@ -111,7 +117,7 @@ typedef struct K7LossParams {
     int32_t mean_divisor;   /* images the batch mean is taken over: B for one GPU, the GLOBAL batch when sharded */
 } K7LossParams;
 
-size_t k7_loss_workspace_bytes(int B, int A, int C);
+K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
 
 /* Replaces FocalLoss.forward after assignment (losses.py:62, 94-168) and, when dcls/dreg
  * are given, its autograd backward.  Outputs:
@@ -120,7 +126,7 @@ size_t k7_loss_workspace_bytes(int B, int A, int C);
  *   dcls [B,A,C], dreg [B,A,4] (optional, both or neither): d(mean cls loss)/dcls and
  *   d(mean reg loss)/dreg with the mean taken over params->mean_divisor images.
  * The batch means of losses.py:168 are sums[0]/B and sums[1]/B. */
-int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
+K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
             const float* cls, const float* reg, const float* annotations,
             const int32_t* assign, const int32_t* num_pos,
             int B, int A, int C, int M, const K7LossParams* params,
@@ -129,7 +135,7 @@ int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
 
 /* grad *= *scale (device scalar); no-op when *scale == 1.  Used by the autograd backward
  * when the incoming gradient of a loss output is not 1. */
-int k7_scale_inplace(float* grad, size_t n, const float* scale, void* stream);
+K7_API int k7_scale_inplace(float* grad, size_t n, const float* scale, void* stream);
 
 /* ---- inference side ----------------------------------------------------------------- */
 
@@ -145,11 +151,11 @@ typedef struct K7DecodeParams {
 
 /* Replaces BBoxTransform.forward (+ optionally ClipBoxes.forward): boxes[B,A,4] (x1,y1,x2,y2).
  * anchor_batch_stride: 0 when `anchors` is [1,A,4] (broadcast), A*4 when it is [B,A,4]. */
-int k7_decode(const K7AnchorSpec* spec, const float* anchors, int box_order, size_t anchor_batch_stride,
+K7_API int k7_decode(const K7AnchorSpec* spec, const float* anchors, int box_order, size_t anchor_batch_stride,
               const float* deltas, int B, int A, const K7DecodeParams* params, float* boxes, void* stream);
 
 /* Replaces ClipBoxes.forward (utils.py:61-71), in place. */
-int k7_clip(float* boxes, int B, int A, int height, int width, void* stream);
+K7_API int k7_clip(float* boxes, int B, int A, int height, int width, void* stream);
 
 typedef struct K7DetectParams {
     K7DecodeParams decode;  /* clip/height/width are honoured */
@@ -159,14 +165,14 @@ typedef struct K7DetectParams {
     int32_t max_detections; /* 0 = off; otherwise stop after this many kept boxes per image */
 } K7DetectParams;
 
-size_t k7_detect_workspace_bytes(int B, int A, int C);
+K7_API size_t k7_detect_workspace_bytes(int B, int A, int C);
 
 /* Replaces the eval tail of the detectors for EVERY image of the batch
  * (retinanet.py:297-318; batched form utils/utils.py:76-114): fused decode + clip +
  * max-over-class + score threshold + compaction, then per image a radix sort
  * (score descending, anchor ascending) and greedy bitmask NMS.  Results stay in the
  * workspace; `counts` gets {survivors, kept} per image:  counts[B,2] int32. */
-int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order,
+K7_API int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order,
               const float* cls, const float* reg, int B, int A, int C,
               const K7DetectParams* params, int32_t* counts,
               void* workspace, size_t workspace_bytes, void* stream);
@@ -176,15 +182,15 @@ int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order,
  *   anchor_ids [B,cap] i32 (optional), survivor_rank [B,cap] i32 (optional: the index
  *   torchvision.ops.nms would have returned, i.e. position in the thresholded list).
  * Rows beyond the image's kept count are left untouched; kept boxes beyond `cap` are dropped. */
-int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B, int A, int C, int cap,
+K7_API int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B, int A, int C, int cap,
                      float* scores, int64_t* labels, float* boxes, int32_t* anchor_ids,
                      int32_t* survivor_rank, void* stream);
 
 /* Stand-alone replacement of torchvision.ops.nms(boxes, scores, thr) for one image
  * (call sites retinanet.py:314 etc.): keep[n] int64 indices in descending-score order,
  * count[1] int32.  Workspace: k7_nms_workspace_bytes(n). */
-size_t k7_nms_workspace_bytes(int n);
-int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
+K7_API size_t k7_nms_workspace_bytes(int n);
+K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
            int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus

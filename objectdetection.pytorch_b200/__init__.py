@@ -6,3 +6,9 @@ loaded lazily on first use and there is NO CPU fallback: every operator raises
 if ``libk7det.so`` is missing or the tensors are not on a CUDA device.
 """
 __version__ = "0.1.0"
+
+from .anchors import Anchors, AnchorsYX, spec_of            # noqa: F401
+from .losses import FocalLoss                                # noqa: F401
+from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, detect, nms,  # noqa: F401
+                    postprocess, eval_tail, patch_model)
+from . import synth                                          # noqa: F401

@@ -1,0 +1,170 @@
+"""ctypes binding of libk7det.so (include/k7det.h).
+
+The library is built in-tree by ``csrc/build.sh`` (``__graft_entry__.build()``)
+and loaded lazily.  There is no fallback: if the shared object is missing or a
+call fails, a RuntimeError / ValueError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libk7det.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+K7_MAX_LEVELS = 8
+K7_MAX_CELL_ANCHORS = 16
+BOX_XYXY, BOX_YXYX = 0, 1
+DECODE_RETINA, DECODE_EFFDET = 0, 1
+STATE_NEG, STATE_IGNORE, STATE_POS = 0, 1, 2
+
+
+class K7AnchorSpec(C.Structure):
+    _fields_ = [
+        ("num_levels", C.c_int32),
+        ("cell_anchors", C.c_int32),
+        ("height", C.c_int32),
+        ("width", C.c_int32),
+        ("box_order", C.c_int32),
+        ("total", C.c_int32),
+        ("fh", C.c_int32 * K7_MAX_LEVELS),
+        ("fw", C.c_int32 * K7_MAX_LEVELS),
+        ("offset", C.c_int32 * (K7_MAX_LEVELS + 1)),
+        ("stride", C.c_double * K7_MAX_LEVELS),
+        ("base", ((C.c_double * 4) * K7_MAX_CELL_ANCHORS) * K7_MAX_LEVELS),
+    ]
+
+
+class K7MatchParams(C.Structure):
+    _fields_ = [("neg_thr", C.c_float), ("pos_thr", C.c_float)]
+
+
+class K7LossParams(C.Structure):
+    _fields_ = [
+        ("alpha", C.c_float),
+        ("beta", C.c_float),
+        ("target_div", C.c_float * 4),
+        ("yx_targets", C.c_int32),
+        ("mean_divisor", C.c_int32),
+    ]
+
+
+class K7DecodeParams(C.Structure):
+    _fields_ = [
+        ("variant", C.c_int32),
+        ("mean", C.c_float * 4),
+        ("std", C.c_float * 4),
+        ("clip", C.c_int32),
+        ("height", C.c_int32),
+        ("width", C.c_int32),
+    ]
+
+
+class K7DetectParams(C.Structure):
+    _fields_ = [
+        ("decode", K7DecodeParams),
+        ("score_thr", C.c_float),
+        ("iou_thr", C.c_float),
+        ("pre_nms_topk", C.c_int32),
+        ("max_detections", C.c_int32),
+    ]
+
+
+# every symbol include/k7det.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+SYMBOLS = {
+    "k7_version": (C.c_int, []),
+    "k7_last_error": (C.c_char_p, []),
+    "k7_anchors_materialize": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P]),
+    "k7_match": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, C.c_int, C.c_int, C.c_int,
+                           C.POINTER(K7MatchParams), _P, _P, _P, _P, _P]),
+    "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P,
+                          C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),
+                          _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "k7_scale_inplace": (C.c_int, [_P, C.c_size_t, _P, _P]),
+    "k7_decode": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_size_t, _P, C.c_int, C.c_int,
+                            C.POINTER(K7DecodeParams), _P, _P]),
+    "k7_clip": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "k7_detect_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "k7_detect": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, C.c_int, C.c_int, C.c_int,
+                            C.POINTER(K7DetectParams), _P, _P, C.c_size_t, _P]),
+    "k7_detect_gather": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   _P, _P, _P, _P, _P, _P]),
+    "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+}
+
+_lib = None
+_lock = threading.Lock()
+
+
+def build(verbose: bool = False) -> str:
+    """Compile csrc/*.cu into libk7det.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    cmd = ["bash", os.path.join(CSRC, "build.sh")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building libk7det.so failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stdout.strip())
+    return LIB_PATH
+
+
+def lib():
+    """The loaded library; raises if it has not been built (no CPU fallback exists)."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise RuntimeError(
+                        f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(b200det has no CPU or PyTorch fallback)")
+                l = C.CDLL(LIB_PATH)
+                for name, (res, args) in SYMBOLS.items():
+                    fn = getattr(l, name)
+                    fn.restype = res
+                    fn.argtypes = args
+                if l.k7_version() != 1:
+                    raise RuntimeError("libk7det.so ABI version mismatch; rebuild")
+                _lib = l
+    return _lib
+
+
+def check(rc: int, what: str):
+    if rc == 0:
+        return
+    msg = lib().k7_last_error().decode(errors="replace")
+    if rc == -1:
+        raise ValueError(f"{what}: {msg}")
+    raise RuntimeError(f"{what}: {msg} (code {rc})")
+
+
+def ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr(device=None):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("b200det operators run on CUDA tensors only (there is no CPU path)")
+
+
+def as_f32_contig(t: torch.Tensor) -> torch.Tensor:
+    """float32, contiguous, 16-byte aligned view (copy only when needed)."""
+    if t.dtype != torch.float32:
+        t = t.float()
+    if not t.is_contiguous():
+        t = t.contiguous()
+    if t.data_ptr() % 16:
+        t = t.clone(memory_format=torch.contiguous_format)
+    return t

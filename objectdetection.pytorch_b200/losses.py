@@ -1,0 +1,203 @@
+"""FocalLoss — drop-in for architectures/losses.py:25-168 (and, through ctor kwargs, for
+architectures/loss_efficientdet.py:27-160).
+
+    FocalLoss()(classifications[B,A,C], regressions[B,A,4], anchors[1,A,4], annotations[B,M,5])
+        -> (classification_loss[1], regression_loss[1])        differentiable
+
+Two CUDA stages (csrc/k7_anchor_match.cu, csrc/k7_loss.cu) replace the reference's
+per-image Python loop of ~45 ATen launches: `k7_match` (IoU + assignment, 4 B/anchor out)
+and `k7_loss` (one streaming pass that produces the loss sums and, when an input
+requires grad, d(loss)/d(classifications|regressions) in the same pass).  The
+backward therefore only hands the saved gradients back (scaled on device when the
+incoming gradient is not 1).  No host synchronisation happens in forward or backward.
+
+Sharded training (one process per GPU, images split along dim 0): pass
+``process_group=`` (or call ``b200det.distributed.sharded_focal_loss``): the local
+sums are combined with ONE 4-float all-reduce and gradients are pre-scaled by the
+global batch, so backward needs no collective.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from .anchors import spec_of
+
+
+class _Workspace:
+    """Per-device scratch tensors, grown on demand and reused across calls."""
+
+    def __init__(self):
+        self.bufs = {}
+
+    def get(self, name: str, nbytes: int, device) -> torch.Tensor:
+        key = (name, device)
+        t = self.bufs.get(key)
+        if t is None or t.numel() < nbytes:
+            t = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+            self.bufs[key] = t
+        return t
+
+
+_WS = _Workspace()
+
+
+def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
+          box_order: int = L.BOX_XYXY, debug: bool = False):
+    """Assignment stage.  Returns (assign[B, A(+pad)] int32, num_pos[B] int32[, iou_max, argmax])."""
+    L.require_cuda(annotations)
+    ann = L.as_f32_contig(annotations)
+    B, M = ann.shape[0], ann.shape[1]
+    dev = ann.device
+    spec = spec_of(anchors)
+    anc_t = None
+    if spec is None:
+        anc_t = L.as_f32_contig(anchors.reshape(-1, 4))
+        L.require_cuda(anc_t)
+    else:
+        box_order = spec.box_order
+    # padded so that the streaming kernel may bulk-copy 16-byte multiples
+    assign = torch.empty(B * A + 8, dtype=torch.int32, device=dev)
+    num_pos = torch.empty(B, dtype=torch.int32, device=dev)
+    iou_max = torch.empty((B, A), dtype=torch.float32, device=dev) if debug else None
+    argmax = torch.empty((B, A), dtype=torch.int32, device=dev) if debug else None
+    p = L.K7MatchParams(neg_thr, pos_thr)
+    with torch.cuda.device(dev):
+        L.check(L.lib().k7_match(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
+                                 L.ptr(ann), B, A, M, C.byref(p), L.ptr(assign), L.ptr(num_pos),
+                                 L.ptr(iou_max), L.ptr(argmax), L.stream_ptr(dev)), "k7_match")
+    if debug:
+        return assign, num_pos, iou_max, argmax
+    return assign, num_pos
+
+
+def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
+               mean_divisor, want_grad, box_order=L.BOX_XYXY):
+    """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None)."""
+    B, A, Cn = cls.shape
+    M = ann.shape[1]
+    dev = cls.device
+    spec = spec_of(anchors)
+    anc_t = None
+    if spec is None:
+        anc_t = L.as_f32_contig(anchors.reshape(-1, 4))
+    else:
+        box_order = spec.box_order
+    lib = L.lib()
+    ws_bytes = lib.k7_loss_workspace_bytes(B, A, Cn)
+    ws = _WS.get("loss", ws_bytes, dev)
+    per_image = torch.empty((B, 2), dtype=torch.float32, device=dev)
+    sums = torch.empty(4, dtype=torch.float32, device=dev)
+    dcls = torch.empty_like(cls) if want_grad else None
+    dreg = torch.empty_like(reg) if want_grad else None
+    p = L.K7LossParams()
+    p.alpha, p.beta = alpha, beta
+    for i in range(4):
+        p.target_div[i] = target_div[i]
+    p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
+    with torch.cuda.device(dev):
+        L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
+                            L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(num_pos),
+                            B, A, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), L.ptr(dcls), L.ptr(dreg),
+                            L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_loss")
+    return per_image, sums, dcls, dreg
+
+
+class _FocalLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cls, reg, anchors, ann, cfg):
+        want_grad = cls.requires_grad or reg.requires_grad
+        A = cls.shape[1]
+        assign, num_pos = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"])
+        group = cfg.get("process_group")
+        world = 1
+        if group is not None or cfg.get("sharded"):
+            import torch.distributed as dist
+            world = dist.get_world_size(group)
+        B = cls.shape[0]
+        per_image, sums, dcls, dreg = loss_stage(
+            anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
+            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
+            want_grad=want_grad, box_order=cfg["box_order"])
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective
+        out = sums[:2] / sums[3]                   # mean over (global) images, losses.py:168
+        ctx.save_for_backward(dcls, dreg) if want_grad else None
+        ctx.has_grad = want_grad
+        ctx.mark_non_differentiable(num_pos, per_image, assign)
+        return out[0:1], out[1:2], num_pos, per_image, assign
+
+    @staticmethod
+    def backward(ctx, g_cls, g_reg, *_):
+        if not ctx.has_grad:
+            return None, None, None, None, None
+        dcls, dreg = ctx.saved_tensors
+        lib = L.lib()
+        dev = dcls.device
+        with torch.cuda.device(dev):
+            st = L.stream_ptr(dev)
+            if g_cls is not None:
+                gc = g_cls.reshape(-1).float().contiguous()
+                L.check(lib.k7_scale_inplace(L.ptr(dcls), dcls.numel(), L.ptr(gc), st), "k7_scale_inplace")
+            else:
+                dcls = None
+            if g_reg is not None:
+                gr = g_reg.reshape(-1).float().contiguous()
+                L.check(lib.k7_scale_inplace(L.ptr(dreg), dreg.numel(), L.ptr(gr), st), "k7_scale_inplace")
+            else:
+                dreg = None
+        return dcls, dreg, None, None, None
+
+
+class FocalLoss(nn.Module):
+    """Same call signature as the reference.  Constructor keywords expose the constants the
+    reference hard-codes; defaults are architectures/losses.py's (0.35/0.45, alpha .25,
+    smooth-L1 beta 1/9, targets / [.1,.1,.2,.2], xyxy anchors).  ``FocalLoss.efficientdet()``
+    gives architectures/loss_efficientdet.py's (0.4/0.5, yx anchors, unscaled (dy,dx,dh,dw))."""
+
+    def __init__(self, neg_thr: float = 0.35, pos_thr: float = 0.45, alpha: float = 0.25,
+                 gamma: float = 2.0, beta: float = 1.0 / 9.0, target_std=(0.1, 0.1, 0.2, 0.2),
+                 box_order: str = "xyxy", yx_targets: bool = False, process_group=None,
+                 sharded: bool = False):
+        super().__init__()
+        if gamma != 2.0:
+            raise ValueError("only gamma == 2 (the reference's constant, losses.py:32) is implemented")
+        if box_order not in ("xyxy", "yxyx"):
+            raise ValueError("box_order must be 'xyxy' or 'yxyx'")
+        self.cfg = dict(neg_thr=float(neg_thr), pos_thr=float(pos_thr), alpha=float(alpha), beta=float(beta),
+                        target_div=tuple(float(x) for x in (target_std if target_std is not None else (1, 1, 1, 1))),
+                        box_order=L.BOX_XYXY if box_order == "xyxy" else L.BOX_YXYX,
+                        yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded))
+        self.last_num_positives = None      # [B] int32 device tensor of the last call (for logging)
+        self.last_per_image = None          # [B,2] (cls_i, reg_i)
+
+    @classmethod
+    def efficientdet(cls, **kw):
+        return cls(neg_thr=0.4, pos_thr=0.5, target_std=None, box_order="yxyx", yx_targets=True, **kw)
+
+    def forward(self, classifications, regressions, anchors, annotations, **kwargs):
+        L.require_cuda(classifications, regressions, annotations)
+        if classifications.dim() != 3 or regressions.dim() != 3 or regressions.shape[2] != 4:
+            raise ValueError("classifications must be [B,A,C] and regressions [B,A,4]")
+        if annotations.dim() != 3 or annotations.shape[2] != 5:
+            raise ValueError("annotations must be [B,M,5]")
+        A = classifications.shape[1]
+        sp = spec_of(anchors)
+        n_anchor = sp.total if sp is not None else anchors.reshape(-1, 4).shape[0]
+        if n_anchor != A or regressions.shape[1] != A:
+            raise ValueError(f"anchor count mismatch: anchors {n_anchor}, classifications {A}, "
+                             f"regressions {regressions.shape[1]}")
+        cls = L.as_f32_contig(classifications)
+        reg = L.as_f32_contig(regressions)
+        ann = L.as_f32_contig(annotations)
+        # pass the recipe itself when there is one (a plain ctypes struct, not a tensor)
+        anchor_src = sp if sp is not None else anchors
+        lc, lr, num_pos, per_image, _ = _FocalLossFn.apply(cls, reg, anchor_src, ann, self.cfg)
+        self.last_num_positives = num_pos
+        self.last_per_image = per_image
+        return lc, lr

@@ -1,0 +1,260 @@
+"""Inference-side drop-ins.
+
+  BBoxTransform, ClipBoxes      architectures/utils.py:6-71
+  BBoxTransformYX               architectures/utils_efficientdet.py:7-35
+  detect()                      the eval tail of every detector for the WHOLE batch
+                                (architectures/retinanet.py:297-318, utils/utils.py:76-114)
+  postprocess()                 utils/utils.py:76-114 (same signature, same list-of-dicts return)
+  nms()                         torchvision.ops.nms call sites (retinanet.py:314 ...)
+  eval_tail() / patch_model()   the (scores, labels, boxes) return of model(img, return_loss=False)
+
+All of them call libk7det.so; none has a PyTorch/CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import types
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from .anchors import spec_of
+from .losses import _WS
+
+
+def _decode_params(variant, mean, std, clip, height, width) -> L.K7DecodeParams:
+    p = L.K7DecodeParams()
+    p.variant = variant
+    for i in range(4):
+        p.mean[i] = float(mean[i])
+        p.std[i] = float(std[i])
+    p.clip, p.height, p.width = int(bool(clip)), int(height), int(width)
+    return p
+
+
+def _to4(v, default):
+    if v is None:
+        return default
+    if isinstance(v, torch.Tensor):
+        return [float(x) for x in v.detach().cpu().reshape(-1).tolist()]
+    return [float(x) for x in np.asarray(v).reshape(-1).tolist()]
+
+
+def decode(boxes, deltas: torch.Tensor, *, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0), std=(.1, .1, .2, .2),
+           clip_hw=None) -> torch.Tensor:
+    """k7_decode wrapper: boxes = anchors [1|B,A,4] tensor (or anything carrying a k7_spec)."""
+    L.require_cuda(deltas)
+    d = L.as_f32_contig(deltas)
+    B, A = d.shape[0], d.shape[1]
+    dev = d.device
+    spec = spec_of(boxes)
+    anc_t, stride = None, 0
+    order = L.BOX_YXYX if variant == L.DECODE_EFFDET else L.BOX_XYXY
+    if spec is None:
+        L.require_cuda(boxes)
+        anc_t = L.as_f32_contig(boxes)
+        if anc_t.dim() != 3 or anc_t.shape[1] != A or anc_t.shape[0] not in (1, B):
+            raise ValueError("boxes must be [1,A,4] or [B,A,4] matching deltas [B,A,4]")
+        stride = 0 if anc_t.shape[0] == 1 else A * 4
+    out = torch.empty((B, A, 4), dtype=torch.float32, device=dev)
+    h, w = clip_hw if clip_hw is not None else (0, 0)
+    p = _decode_params(variant, mean, std, clip_hw is not None, h, w)
+    with torch.cuda.device(dev):
+        L.check(L.lib().k7_decode(C.byref(spec) if spec is not None else None, L.ptr(anc_t), order, stride,
+                                  L.ptr(d), B, A, C.byref(p), L.ptr(out), L.stream_ptr(dev)), "k7_decode")
+    return out
+
+
+class BBoxTransform(nn.Module):
+    """architectures/utils.py:6-53.  mean/std are plain attributes (no buffers), as in the reference."""
+
+    def __init__(self, mean=None, std=None):
+        super().__init__()
+        self.mean = torch.from_numpy(np.array([0, 0, 0, 0]).astype(np.float32)) if mean is None else mean
+        self.std = torch.from_numpy(np.array([0.1, 0.1, 0.2, 0.2]).astype(np.float32)) if std is None else std
+        self._mean4 = _to4(self.mean, [0.0] * 4)
+        self._std4 = _to4(self.std, [0.1, 0.1, 0.2, 0.2])
+
+    def forward(self, boxes, deltas):
+        return decode(boxes, deltas, variant=L.DECODE_RETINA, mean=self._mean4, std=self._std4)
+
+
+class BBoxTransformYX(nn.Module):
+    """architectures/utils_efficientdet.py:7-35: anchors (y1,x1,y2,x2), regression (dy,dx,dh,dw)."""
+
+    def forward(self, anchors, regression):
+        return decode(anchors, regression, variant=L.DECODE_EFFDET)
+
+
+class ClipBoxes(nn.Module):
+    """architectures/utils.py:56-71: in place, returns the same tensor."""
+
+    def __init__(self, width=None, height=None):
+        super().__init__()
+
+    def forward(self, boxes, img):
+        L.require_cuda(boxes)
+        if boxes.dtype != torch.float32 or not boxes.is_contiguous() or boxes.data_ptr() % 16:
+            raise ValueError("ClipBoxes works in place on a contiguous float32 [B,A,4] tensor")
+        _, _, height, width = img.shape
+        B, A = boxes.shape[0], boxes.shape[1]
+        with torch.cuda.device(boxes.device):
+            L.check(L.lib().k7_clip(L.ptr(boxes), B, A, int(height), int(width), L.stream_ptr(boxes.device)), "k7_clip")
+        return boxes
+
+
+# ------------------------------------------------------------------ fused eval tail
+@dataclass
+class BatchDetections:
+    """Kept detections of a batch, row-padded to `cap` per image.  count[b] rows are valid."""
+    count: torch.Tensor          # [B] int64 (host)
+    survivors: torch.Tensor      # [B] int64 (host): boxes above the score threshold
+    scores: torch.Tensor         # [B,cap] f32, descending per image
+    labels: torch.Tensor         # [B,cap] i64
+    boxes: torch.Tensor          # [B,cap,4] f32 (x1,y1,x2,y2)
+    anchor_ids: torch.Tensor     # [B,cap] i32
+    survivor_rank: torch.Tensor  # [B,cap] i32: what torchvision.ops.nms would have returned
+
+    def image(self, b: int):
+        k = int(self.count[b])
+        return self.scores[b, :k], self.labels[b, :k], self.boxes[b, :k]
+
+
+def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, image_hw, *,
+           score_thr: float = 0.05, iou_thr: float = 0.5, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0),
+           std=(.1, .1, .2, .2), clip: bool = True, pre_nms_topk: int = 0, max_detections: int = 0,
+           cap: Optional[int] = None, sync: bool = True) -> BatchDetections:
+    """Fused decode + clip + threshold + sort + NMS for every image of the batch."""
+    L.require_cuda(classifications, regressions)
+    cls = L.as_f32_contig(classifications)
+    reg = L.as_f32_contig(regressions)
+    B, A, Cn = cls.shape
+    dev = cls.device
+    spec = spec_of(anchors)
+    anc_t = None
+    order = L.BOX_YXYX if variant == L.DECODE_EFFDET else L.BOX_XYXY
+    if spec is None:
+        L.require_cuda(anchors)
+        anc_t = L.as_f32_contig(anchors.reshape(-1, 4))
+        if anc_t.shape[0] != A:
+            raise ValueError("anchor count mismatch")
+    lib = L.lib()
+    ws_bytes = lib.k7_detect_workspace_bytes(B, A, Cn)
+    ws = _WS.get("detect", ws_bytes, dev)
+    counts = torch.empty((B, 2), dtype=torch.int32, device=dev)
+    p = L.K7DetectParams()
+    p.decode = _decode_params(variant, mean, std, clip, image_hw[0], image_hw[1])
+    p.score_thr, p.iou_thr = float(score_thr), float(iou_thr)
+    p.pre_nms_topk, p.max_detections = int(pre_nms_topk), int(max_detections)
+    if cap is None:
+        cap = max_detections if max_detections > 0 else min(A, 1024)
+    cap = max(1, min(int(cap), A))
+
+    def gather(capn):
+        scores = torch.empty((B, capn), dtype=torch.float32, device=dev)
+        labels = torch.empty((B, capn), dtype=torch.int64, device=dev)
+        boxes = torch.empty((B, capn, 4), dtype=torch.float32, device=dev)
+        aids = torch.empty((B, capn), dtype=torch.int32, device=dev)
+        ranks = torch.empty((B, capn), dtype=torch.int32, device=dev)
+        L.check(lib.k7_detect_gather(L.ptr(ws), ws.numel(), B, A, Cn, capn, L.ptr(scores), L.ptr(labels),
+                                     L.ptr(boxes), L.ptr(aids), L.ptr(ranks), L.stream_ptr(dev)), "k7_detect_gather")
+        return scores, labels, boxes, aids, ranks
+
+    with torch.cuda.device(dev):
+        L.check(lib.k7_detect(C.byref(spec) if spec is not None else None, L.ptr(anc_t), order, L.ptr(cls),
+                              L.ptr(reg), B, A, Cn, C.byref(p), L.ptr(counts), L.ptr(ws), ws.numel(),
+                              L.stream_ptr(dev)), "k7_detect")
+        out = gather(cap)
+        if not sync:
+            return BatchDetections(counts[:, 1], counts[:, 0], *out)
+        host = counts.cpu()                       # the one synchronisation of the eval path
+        kmax = int(host[:, 1].max())
+        if kmax > cap:                            # rare: more kept boxes than the first guess
+            out = gather(kmax)
+    return BatchDetections(host[:, 1].long(), host[:, 0].long(), *out)
+
+
+def nms(boxes: torch.Tensor, scores: torch.Tensor, iou_threshold: float) -> torch.Tensor:
+    """torchvision.ops.nms(boxes, scores, iou_threshold) on device: int64 indices, descending score."""
+    L.require_cuda(boxes, scores)
+    b = L.as_f32_contig(boxes)
+    s = L.as_f32_contig(scores)
+    n = b.shape[0]
+    dev = b.device
+    lib = L.lib()
+    keep = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    ws = _WS.get("nms", lib.k7_nms_workspace_bytes(n), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.k7_nms(L.ptr(b), L.ptr(s), n, float(iou_threshold), L.ptr(keep), L.ptr(count), L.ptr(ws),
+                           ws.numel(), L.stream_ptr(dev)), "k7_nms")
+    return keep[:int(count.item())]
+
+
+def _variant_of(regressBoxes) -> int:
+    return L.DECODE_EFFDET if isinstance(regressBoxes, BBoxTransformYX) or \
+        type(regressBoxes).__module__.endswith("utils_efficientdet") else L.DECODE_RETINA
+
+
+def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes, threshold, iou_threshold):
+    """utils/utils.py:76-114 — same arguments, same return (list of dicts of numpy arrays).  The
+    reference's duplicate empty dict for an all-empty batch (utils.py:83-88) is not reproduced."""
+    variant = _variant_of(regressBoxes)
+    mean = _to4(getattr(regressBoxes, "mean", None), [0.0] * 4)
+    std = _to4(getattr(regressBoxes, "std", None), [0.1, 0.1, 0.2, 0.2])
+    det = detect(classification, regression, anchors, (int(x.shape[2]), int(x.shape[3])), score_thr=threshold,
+                 iou_thr=iou_threshold, variant=variant, mean=mean, std=std, clip=clipBoxes is not None)
+    out = []
+    sc, lb, bx = det.scores.cpu().numpy(), det.labels.cpu().numpy(), det.boxes.cpu().numpy()
+    for b in range(classification.shape[0]):
+        k = int(det.count[b])
+        if k == 0:
+            out.append({'rois': np.array(()), 'class_ids': np.array(()), 'scores': np.array(())})
+        else:
+            out.append({'rois': bx[b, :k], 'class_ids': lb[b, :k], 'scores': sc[b, :k]})
+    return out
+
+
+def eval_tail(classification, regression, anchors, img_batch, regressBoxes=None, score_thr=0.05, iou_thr=0.5):
+    """What model(img, return_loss=False) returns after the heads (retinanet.py:297-318):
+    [scores[K], labels[K] (int64), boxes[K,4]] of IMAGE 0, or the zeros triple when nothing passes."""
+    variant = _variant_of(regressBoxes) if regressBoxes is not None else L.DECODE_RETINA
+    mean = _to4(getattr(regressBoxes, "mean", None), [0.0] * 4)
+    std = _to4(getattr(regressBoxes, "std", None), [0.1, 0.1, 0.2, 0.2])
+    det = detect(classification[:1], regression[:1], anchors, (int(img_batch.shape[2]), int(img_batch.shape[3])),
+                 score_thr=score_thr, iou_thr=iou_thr, variant=variant, mean=mean, std=std)
+    if int(det.survivors[0]) == 0:
+        dev = classification.device                # retinanet.py:308
+        return [torch.zeros([1], device=dev), torch.zeros([1], device=dev), torch.zeros([1, 4], device=dev)]
+    s, l, b = det.image(0)
+    return [s, l, b]
+
+
+def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5):
+    """Swap a reference detector's hot-path attributes for the B200 modules and route its
+    eval branch through eval_tail().  The model must expose the reference's attribute names
+    (anchors, focalLoss, regressBoxes, clipBoxes; retinanet.py:220-230) and a
+    forward(img, annotations=None, return_head=False, return_loss=True)."""
+    from .anchors import Anchors
+    from .losses import FocalLoss
+    old = model.anchors
+    model.anchors = Anchors(pyramid_levels=list(old.pyramid_levels), strides=list(old.strides),
+                            sizes=list(old.sizes), ratios=np.asarray(old.ratios), scales=np.asarray(old.scales))
+    model.focalLoss = FocalLoss()
+    model.regressBoxes = BBoxTransform()
+    model.clipBoxes = ClipBoxes()
+    inner = model.forward
+
+    def forward(self, img_batch, annotations=None, return_head=False, return_loss=True):
+        if return_head or return_loss:
+            return inner(img_batch, annotations, return_head=return_head, return_loss=return_loss)
+        classification, regression = inner(img_batch, annotations, return_head=True)
+        return eval_tail(classification, regression, self.anchors(img_batch), img_batch, self.regressBoxes,
+                         score_thr, iou_thr)
+
+    model.forward = types.MethodType(forward, model)
+    return model

@@ -1,0 +1,327 @@
+"""GPU parity tests: the CUDA path (through the C ABI / the drop-in modules) against the golden
+fixtures produced by the unmodified reference and against the oracle on seeded inputs.
+Bit-exact: anchors, IoU max / arg-max / state, num_pos, survivors, sort order, NMS keep
+(rank and anchor id), labels, scores.  1e-5 relative: losses, gradients, decoded boxes
+(boxes additionally get 2e-4 px absolute slack: x1 = cx - w/2 cancels)."""
+import glob
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import b200det
+from b200det import _lib as L
+from b200det import losses as BL
+from oracle import restate as R
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+DEV = "cuda:0"
+
+with open(os.path.join(GOLDEN, "anchors.json")) as f:
+    ANCHORS = json.load(f)
+
+
+def anchor_module(kind, kwargs):
+    kw = dict(kwargs)
+    if "pyramid_levels" in kw:
+        kw["pyramid_levels"] = [int(x) for x in kw["pyramid_levels"]]
+    return b200det.AnchorsYX(**kw) if kind in ("yx", "effdet") else b200det.Anchors(**kw)
+
+
+@pytest.mark.parametrize("name", sorted(ANCHORS))
+def test_anchors_bit_exact(name):
+    g = ANCHORS[name]
+    img = torch.empty(1, 3, g["height"], g["width"], device=DEV)
+    a = anchor_module(g["kind"], g["kwargs"])(img)
+    assert a.shape == (1, g["count"], 4) and a.dtype == torch.float32 and a.is_cuda
+    assert hashlib.sha256(a[0].cpu().numpy().tobytes()).hexdigest() == g["sha256"]
+
+
+LOSS = sorted(glob.glob(os.path.join(GOLDEN, "loss_*.npz")))
+IDS = [os.path.basename(p)[:-4] for p in LOSS]
+
+
+def load_loss_case(path, from_spec):
+    g = np.load(path)
+    yx = str(g["variant"]) == "effdet"
+    img = torch.empty(1, 3, int(g["height"]), int(g["width"]), device=DEV)
+    if from_spec:
+        anc = anchor_module("yx" if yx else "retina", json.loads(str(g["anchor_kwargs"])))(img)
+        assert torch.equal(anc.cpu(), torch.from_numpy(g["anchors"]))
+    else:
+        anc = torch.from_numpy(g["anchors"]).to(DEV)     # foreign tensor: kernels read it
+    return g, yx, anc
+
+
+@pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
+@pytest.mark.parametrize("path", LOSS, ids=IDS)
+def test_match_bit_exact(path, from_spec):
+    g, yx, anc = load_loss_case(path, from_spec)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    thr = (0.4, 0.5) if yx else (0.35, 0.45)
+    A = g["anchors"].shape[1]
+    assign, num_pos, iou_max, argmax = BL.match(anc, ann, A, thr[0], thr[1],
+                                                L.BOX_YXYX if yx else L.BOX_XYXY, debug=True)
+    B = ann.shape[0]
+    aw = assign[:B * A].view(B, A).cpu().numpy()
+    state, row = aw & 3, aw >> 2
+    assert np.array_equal(state, g["state"])
+    assert np.array_equal(iou_max.cpu().numpy(), g["iou_max"])
+    assert np.array_equal(argmax.cpu().numpy(), g["iou_argmax"])
+    has = g["gt_row"] >= 0
+    assert np.array_equal(row[has], g["gt_row"][has])
+    assert np.array_equal(num_pos.cpu().numpy(), (g["state"] == 2).sum(1))
+
+
+@pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
+@pytest.mark.parametrize("path", LOSS, ids=IDS)
+def test_focal_loss_and_grads(path, from_spec):
+    g, yx, anc = load_loss_case(path, from_spec)
+    cls = torch.from_numpy(g["classifications"]).to(DEV).requires_grad_(True)
+    reg = torch.from_numpy(g["regressions"]).to(DEV).requires_grad_(True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    mod = b200det.FocalLoss.efficientdet() if yx else b200det.FocalLoss()
+    lc, lr = mod(cls, reg, anc, ann)
+    assert lc.shape == (1,) and lr.shape == (1,)
+    np.testing.assert_allclose(lc.detach().cpu().numpy(), g["cls_loss"], rtol=1e-5)
+    np.testing.assert_allclose(lr.detach().cpu().numpy(), g["reg_loss"], rtol=1e-5)
+    # forward without grad gives the same numbers (different kernel instantiation)
+    with torch.no_grad():
+        lc2, lr2 = mod(cls.detach(), reg.detach(), anc, ann)
+    assert torch.equal(lc2, lc.detach()) and torch.equal(lr2, lr.detach())
+    (lc + lr).sum().backward()
+    np.testing.assert_allclose(cls.grad.cpu().numpy(), g["dcls"], rtol=1e-5, atol=1e-10)
+    np.testing.assert_allclose(reg.grad.cpu().numpy(), g["dreg"], rtol=1e-5, atol=1e-9)
+    assert np.array_equal(mod.last_num_positives.cpu().numpy(), (g["state"] == 2).sum(1))
+
+
+def test_backward_scales_by_incoming_gradient():
+    g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_small")], True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV).requires_grad_(True)
+    reg = torch.from_numpy(g["regressions"]).to(DEV).requires_grad_(True)
+    lc, lr = b200det.FocalLoss()(cls, reg, anc, ann)
+    (3.0 * lc + 0.5 * lr).sum().backward()
+    np.testing.assert_allclose(cls.grad.cpu().numpy(), 3.0 * g["dcls"], rtol=1e-5, atol=1e-10)
+    np.testing.assert_allclose(reg.grad.cpu().numpy(), 0.5 * g["dreg"], rtol=1e-5, atol=1e-9)
+
+
+def test_loss_is_bit_reproducible():
+    g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_c90")], True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    outs = [torch.cat(b200det.FocalLoss()(cls, reg, anc, ann)).cpu() for _ in range(5)]
+    assert all(torch.equal(outs[0], o) for o in outs[1:])
+
+
+@pytest.mark.parametrize("shape", [(3, 1, 7), (5, 3, 4), (1, 90, 3), (2, 80, 9), (3, 33, 5), (2, 7, 1), (1, 130, 2)],
+                         ids=lambda s: "B%d_C%d_M%d" % s)
+def test_loss_odd_shapes_vs_oracle(shape):
+    """Shapes whose element count is not a multiple of 4 (scalar tail of the bulk copies), every
+    vector width, lanes-per-row 1/2/4/8, tiles straddling images; anchors as a foreign tensor."""
+    B, C, M = shape
+    H, W = 77, 99
+    anc_np = R.retina_anchors(H, W)
+    A = anc_np.shape[0] - 1 - (B % 2)          # odd/even anchor counts on purpose
+    anc_np = anc_np[:A]
+    gen = torch.Generator().manual_seed(B * 1000 + C * 10 + M)
+    ann = b200det.synth.make_annotations(B, M, C, H, W, gen, gt_min=8.0, gt_max=60.0)
+    cls, reg = b200det.synth.make_head_outputs(B, A, C, gen, logit_mean=-2.0, logit_std=2.0)
+    anc = torch.from_numpy(anc_np)[None]
+    c0, r0 = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    want = R.focal_loss(c0, r0, anc, ann)
+    (want.cls_mean + want.reg_mean).sum().backward()
+    c1, r1 = cls.to(DEV).requires_grad_(True), reg.to(DEV).requires_grad_(True)
+    mod = b200det.FocalLoss()
+    lc, lr = mod(c1, r1, anc.to(DEV), ann.to(DEV))
+    (lc + lr).sum().backward()
+    np.testing.assert_allclose(lc.item(), want.cls_mean.item(), rtol=1e-5)
+    np.testing.assert_allclose(lr.item(), want.reg_mean.item(), rtol=1e-5)
+    np.testing.assert_allclose(mod.last_per_image.cpu().numpy(),
+                               torch.stack([want.cls_per_image, want.reg_per_image], 1).detach().numpy(), rtol=1e-5)
+    assert mod.last_num_positives.cpu().tolist() == want.num_pos
+    np.testing.assert_allclose(c1.grad.cpu().numpy(), c0.grad.numpy(), rtol=1e-5, atol=1e-10)
+    np.testing.assert_allclose(r1.grad.cpu().numpy(), r0.grad.numpy(), rtol=1e-5, atol=1e-9)
+
+
+# ---------------------------------------------------------------------------------- inference
+DET = sorted(glob.glob(os.path.join(GOLDEN, "detect_*.npz")))
+DIDS = [os.path.basename(p)[:-4] for p in DET]
+
+
+def load_det_case(path, from_spec):
+    g = np.load(path)
+    yx = str(g["variant"]) == "effdet"
+    H, W = int(g["height"]), int(g["width"])
+    img = torch.empty(g["classifications"].shape[0], 3, H, W, device=DEV)
+    if from_spec:
+        anc = anchor_module("yx" if yx else "retina", json.loads(str(g["anchor_kwargs"])))(img)
+    else:
+        anc = torch.from_numpy(g["anchors"]).to(DEV)
+    return g, yx, anc, img
+
+
+@pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
+@pytest.mark.parametrize("path", DET, ids=DIDS)
+def test_decode_and_clip_modules(path, from_spec):
+    g, yx, anc, img = load_det_case(path, from_spec)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    rb = b200det.BBoxTransformYX() if yx else b200det.BBoxTransform()
+    boxes = rb(anc, reg)
+    out = b200det.ClipBoxes()(boxes, img)
+    assert out.data_ptr() == boxes.data_ptr()            # in place, same tensor (utils.py:71)
+    np.testing.assert_allclose(out.cpu().numpy(), g["boxes"], rtol=1e-5, atol=2e-4)
+    if not yx:                                           # batched anchors [B,A,4] broadcast form
+        ab = torch.from_numpy(g["anchors"]).to(DEV).expand(reg.shape[0], -1, -1).contiguous()
+        out2 = b200det.ClipBoxes()(rb(ab, reg), img)
+        assert torch.equal(out2, out)
+
+
+@pytest.mark.parametrize("path", DET, ids=DIDS)
+def test_nms_stage_bit_exact_on_reference_boxes(path):
+    """k7_nms on the reference's own boxes/scores must return torchvision's keep exactly."""
+    g = np.load(path)
+    for b in range(g["classifications"].shape[0]):
+        surv = g[f"survivors_{b}"]
+        boxes = torch.from_numpy(g["boxes"][b][surv]).to(DEV)
+        scores = torch.from_numpy(g["classifications"][b].max(axis=1)[surv]).to(DEV)
+        keep = b200det.nms(boxes, scores, float(g["iou_thr"]))
+        assert keep.dtype == torch.int64
+        assert np.array_equal(keep.cpu().numpy(), g[f"keep_rank_{b}"])
+
+
+@pytest.mark.parametrize("n", [1, 2, 63, 64, 65, 1000, 1024, 1025, 2500, 6000])
+def test_nms_random_vs_torchvision(n):
+    from torchvision.ops import nms as tv_nms
+    rng = np.random.default_rng(n)
+    xy = rng.uniform(0, 300, (n, 2)).astype(np.float32)
+    wh = rng.uniform(0, 80, (n, 2)).astype(np.float32)
+    boxes = np.concatenate([xy, xy + wh], 1)
+    boxes[::11, 2:] = boxes[::11, :2]                    # zero-area boxes: 0/0 -> NaN -> never suppressed
+    scores = np.round(rng.uniform(-1, 1, n), 2).astype(np.float32)     # many exact ties, negatives
+    for thr in (0.0, 0.3, 0.5, 0.9):
+        want = tv_nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
+        got = b200det.nms(torch.from_numpy(boxes).to(DEV), torch.from_numpy(scores).to(DEV), thr).cpu().numpy()
+        assert np.array_equal(got, want), (n, thr)
+
+
+def test_nms_empty():
+    keep = b200det.nms(torch.zeros(0, 4, device=DEV), torch.zeros(0, device=DEV), 0.5)
+    assert keep.shape == (0,) and keep.dtype == torch.int64
+
+
+def check_detect(det, g, exact_boxes_from=None):
+    B = g["classifications"].shape[0]
+    for b in range(B):
+        k = int(det.count[b])
+        assert int(det.survivors[b]) == g[f"survivors_{b}"].size
+        assert np.array_equal(det.anchor_ids[b, :k].cpu().numpy(), g[f"keep_anchor_{b}"])
+        assert np.array_equal(det.survivor_rank[b, :k].cpu().numpy(), g[f"keep_rank_{b}"])
+        assert np.array_equal(det.labels[b, :k].cpu().numpy(), g[f"labels_{b}"])
+        assert np.array_equal(det.scores[b, :k].cpu().numpy(), g[f"scores_{b}"])
+        np.testing.assert_allclose(det.boxes[b, :k].cpu().numpy(), g[f"boxes_{b}"], rtol=1e-5, atol=2e-4)
+
+
+@pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
+@pytest.mark.parametrize("path", DET, ids=DIDS)
+def test_detect_end_to_end(path, from_spec):
+    g, yx, anc, img = load_det_case(path, from_spec)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    det = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])), score_thr=float(g["score_thr"]),
+                         iou_thr=float(g["iou_thr"]), variant=L.DECODE_EFFDET if yx else L.DECODE_RETINA, cap=8)
+    check_detect(det, g)
+
+
+@pytest.mark.parametrize("path", DET, ids=DIDS)
+def test_postprocess_signature(path):
+    g, yx, anc, img = load_det_case(path, True)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    rb = b200det.BBoxTransformYX() if yx else b200det.BBoxTransform()
+    out = b200det.postprocess(img, anc, reg, cls, rb, b200det.ClipBoxes(), float(g["score_thr"]), float(g["iou_thr"]))
+    assert len(out) == cls.shape[0]
+    for b, o in enumerate(out):
+        assert np.array_equal(np.asarray(o["class_ids"]).reshape(-1), g[f"labels_{b}"])
+        assert np.array_equal(np.asarray(o["scores"], np.float32).reshape(-1), g[f"scores_{b}"])
+        np.testing.assert_allclose(np.asarray(o["rois"], np.float32).reshape(-1, 4), g[f"boxes_{b}"], rtol=1e-5, atol=2e-4)
+
+
+def test_eval_tail_image0_and_empty_triple():
+    g, yx, anc, img = load_det_case(DET[DIDS.index("detect_retina_small")], True)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    s, l, b = b200det.eval_tail(cls, reg, anc, img)
+    assert np.array_equal(s.cpu().numpy(), g["scores_0"]) and np.array_equal(l.cpu().numpy(), g["labels_0"])
+    assert l.dtype == torch.int64
+    g, yx, anc, img = load_det_case(DET[DIDS.index("detect_retina_empty")], True)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    s, l, b = b200det.eval_tail(cls, reg, anc, img)      # retinanet.py:308: zeros triple
+    assert s.shape == (1,) and l.shape == (1,) and b.shape == (1, 4) and float(s.abs().sum() + b.abs().sum()) == 0.0
+
+
+def test_detect_max_detections_and_topk():
+    g, yx, anc, img = load_det_case(DET[DIDS.index("detect_retina_small")], True)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    det = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])), max_detections=100)
+    for b in range(cls.shape[0]):       # csv_eval.py:107 top-100 of a score-sorted list == prefix
+        assert int(det.count[b]) == 100
+        assert np.array_equal(det.anchor_ids[b, :100].cpu().numpy(), g[f"keep_anchor_{b}"][:100])
+    det = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])), pre_nms_topk=500)
+    _, dets = R.detect_batch(cls.cpu(), reg.cpu(), torch.from_numpy(g["anchors"]), int(g["height"]), int(g["width"]))
+    for b in range(cls.shape[0]):
+        sc = cls[b].max(1)[0].cpu()
+        surv = torch.from_numpy(g[f"survivors_{b}"])
+        order = torch.argsort(-sc[surv], stable=True)[:500]
+        from torchvision.ops import nms as tv_nms
+        keep = tv_nms(torch.from_numpy(g["boxes"][b])[surv][order], sc[surv][order], 0.5)
+        assert np.array_equal(det.anchor_ids[b, :int(det.count[b])].cpu().numpy(), surv[order][keep].numpy())
+
+
+def test_detect_large_vs_oracle():
+    """BASELINE config C1 shape (512x512, 80 classes) with dense scores: tens of chunks of NMS."""
+    wl = b200det.synth.WORKLOADS["c1_retinanet_r50_512"]
+    gen = torch.Generator().manual_seed(4)
+    cls, reg = b200det.synth.make_head_outputs(2, wl.anchors, wl.classes, gen, logit_mean=-6.0, logit_std=1.5)
+    anc_np = R.retina_anchors(wl.height, wl.width)
+    boxes, dets = R.detect_batch(cls, reg, torch.from_numpy(anc_np), wl.height, wl.width)
+    img = torch.empty(2, 3, wl.height, wl.width, device=DEV)
+    det = b200det.detect(cls.to(DEV), reg.to(DEV), b200det.Anchors()(img), (wl.height, wl.width))
+    for b, d in enumerate(dets):
+        k = int(det.count[b])
+        assert int(det.survivors[b]) == d.survivors.numel() and d.survivors.numel() > 2048
+        assert np.array_equal(det.anchor_ids[b, :k].cpu().numpy(), d.keep_anchor.numpy())
+        assert np.array_equal(det.labels[b, :k].cpu().numpy(), d.labels.numpy())
+        np.testing.assert_allclose(det.boxes[b, :k].cpu().numpy(), d.boxes.numpy(), rtol=1e-5, atol=2e-4)
+
+
+def test_loss_full_size_properties():
+    """BASELINE config C2 shape (B=8 of 64): oracle too slow for the full batch in a unit test, so
+    check size-independent properties: per-image losses equal the batch-1 losses (images are
+    independent), the mean is their mean, gradients of untouched (ignored) rows are zero."""
+    wl = b200det.synth.WORKLOADS["c2_effdet_d0_512"]
+    cls, reg, ann = b200det.synth.make_inputs(wl, seed=1, device=DEV, batch=8)
+    img = torch.empty(8, 3, wl.height, wl.width, device=DEV)
+    anc = b200det.Anchors()(img)
+    mod = b200det.FocalLoss()
+    c = cls.clone().requires_grad_(True)
+    lc, lr = mod(c, reg, anc, ann)
+    per = mod.last_per_image.clone()
+    lc.backward()
+    np.testing.assert_allclose(lc.item(), per[:, 0].double().mean().item(), rtol=1e-6)
+    for b in (0, 5):
+        lcb, lrb = mod(cls[b:b + 1], reg[b:b + 1], anc, ann[b:b + 1])
+        np.testing.assert_allclose(lcb.item(), per[b, 0].item(), rtol=1e-6)
+        np.testing.assert_allclose(lrb.item(), per[b, 1].item(), rtol=1e-6)
+    # oracle on one image of the full-size batch
+    want = R.focal_loss(cls[:1].cpu(), reg[:1].cpu(), anc.cpu(), ann[:1].cpu())
+    np.testing.assert_allclose(per[0].cpu().numpy(), [want.cls_mean.item(), want.reg_mean.item()], rtol=1e-5)
+    assert int(mod.last_num_positives[0]) == want.num_pos[0]
