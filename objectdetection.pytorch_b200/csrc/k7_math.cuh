@@ -209,6 +209,7 @@ K7_HD bool k7_nms_suppress(const K7Box& a, float area_a, const K7Box& b, float a
 // Sort key: scores descending, index ascending (stable descending sort of torchvision.ops.nms).
 // Monotone map of IEEE float bits to unsigned, inverted.
 K7_HD uint32_t k7_score_key_desc(float s) {
+    s = K7_FADD(s, 0.0f);   // -0.0 -> +0.0: the two compare equal in torch's sort and must tie
 #if defined(__CUDA_ARCH__)
     uint32_t u = __float_as_uint(s);
 #else
