@@ -101,7 +101,10 @@ typedef struct K7MatchParams {
 #define K7_ASSIGN_ROW(w) ((int32_t)((uint32_t)(w) >> 2))
 
 /* Replaces calc_iou + IoU-max assignment (losses.py:6-23, 49-82).  Outputs:
- *   assign  [B,A] int32   packed state / GT row (images without a valid row: all IGNORE)
+ *   assign  [B,A] int32   packed state / GT row (images without a valid row: all IGNORE).  The
+ *                         buffer must be 16-byte aligned and hold at least B*A + 4 words: k7_loss
+ *                         streams it with 16-byte bulk copies and may read (never use) up to 3 words
+ *                         past the end.
  *   num_pos [B]   int32   positives per image
  *   iou_max [B,A] float32 (optional, may be NULL)  bit-identical to torch.max(IoU,1).values
  *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list */

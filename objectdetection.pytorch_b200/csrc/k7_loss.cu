@@ -3,20 +3,61 @@
 //   k7_loss   FocalLoss.forward after assignment   architectures/losses.py:62, 94-168
 //             (+ loss_efficientdet.py:61-160 through K7LossParams) and its autograd backward.
 //
-// One persistent kernel streams classifications [B*A, C] through per-warp TMA rings
-// (k7_stream.cuh).  Per row the lane(s) owning it read the packed assignment word (staged next
-// to the tile), evaluate every class as a "target 0" element with the polynomial path of
-// k7_math.cuh, then patch the single "target 1" element of positive rows, so the inner loop is
-// branch-free and identical for all rows.  With gradients, d(loss)/d(cls) overwrites the tile in
-// shared memory and leaves through a bulk shared->global copy; d(loss)/d(reg) is one float4 per
-// row.  Loss sums are reduced warp -> tile partial (one float4 per tile, written unconditionally,
-// no atomics) and then per image in float64 in fixed order by the finalize kernel, so results
-// are bit-reproducible run to run and independent of the grid size.
+// The job is "move A*C*4 bytes per image in (and, with gradients, out) at HBM speed"; round-1
+// profiling showed the first version was instruction-issue bound (58 issue slots per element),
+// so this version is organised around the cheapest possible inner loop:
+//
+//   * FLAT TILES.  classifications[b] is a flat array of A*C floats cut into tiles of TILE_F
+//     floats (4 KB), ignoring row boundaries.  Each WARP owns a ring of shared-memory stages fed
+//     by 1-D bulk async copies (TMA, SASS UBLKCP) with one mbarrier per stage; tiles are dealt
+//     round-robin to all warps of a persistent grid (one CTA per SM); warps never wait for each
+//     other.  The assignment words of the rows touching the tile ride along in the same stage.
+//   * FLAT PASS.  Every lane runs LDS.128 -> math -> STS.128 on float4 number lane+32k (conflict
+//     free, perfectly balanced whatever C is).  All elements are evaluated as "target 0"
+//     (negative / non-label class) with packed f32x2 arithmetic (FFMA2/FMUL2, new on sm_100):
+//         p = clamp(x); q = fl(1-p); pp = 1-q; nl = pp*S(pp) ~ -log(q)      (degree-5 minimax)
+//         loss += p*p*nl                                  (x (1-alpha) once per tile)
+//         grad  = (p == x) ? (1-alpha)*scale * p * (2*nl + p/q) : 0          (MUFU.RCP)
+//     about 13 issue slots per element instead of 58.  The polynomial is valid for p <= 0.25; the
+//     pass tracks max(p) and a tile that saw a larger value (rare: confident predictions) is
+//     redone from global memory by an exact scalar path with logf.
+//   * ROW EXCEPTIONS.  Ignored rows (state IGNORE, ~1-2 %) are turned into a bit mask over the
+//     tile before the flat pass (only tiles that have one take the masked variant); the single
+//     "target 1" element of each positive row is patched after the flat pass (its "target 0"
+//     contribution is removed and the focal-positive term / gradient written); smooth-L1 and
+//     d(loss)/d(reg) are handled by the lane owning each row that starts in the tile.
+//   * Gradients overwrite the tile in shared memory and leave through a bulk shared->global copy.
+//   * Loss sums: lane -> warp shuffle -> one float2 per tile (written unconditionally, no
+//     atomics) -> per image in float64 in tile order by the finalize kernel: bit-reproducible run
+//     to run and independent of the grid size.
+//
+// Tiles never straddle images.  When A*C is not a multiple of 4 the image bases are not 16-byte
+// aligned and bulk copies are impossible: a compatibility instantiation moves the tile with plain
+// loads/stores (odd test shapes only; every real head has A*C % 4 == 0).
 //
 // Algorithmic bytes per image: forward A*(4C+16)+20M, forward+backward A*(8C+32)+20M.
-#include "k7_stream.cuh"
+#include <stdlib.h>
 
-#define K7_LOSS_MAX_THREADS 768
+#include "k7_common.cuh"
+
+#define K7_LOSS_MAX_WARPS 16
+#define K7_LOSS_TILE 1024   // floats per tile
+
+struct K7FastDiv {
+    uint32_t m, sh;
+};
+// exact x / d for x < 2^31 (Granlund-Montgomery, round-up multiplier)
+static K7FastDiv k7_fastdiv_make(uint32_t d) {
+    int s = 0;
+    while ((1ull << s) < d) ++s;
+    K7FastDiv f;
+    f.m = (uint32_t)(((1ull << (31 + s)) + d - 1) / d);
+    f.sh = (uint32_t)(31 + s);
+    return f;
+}
+__device__ __forceinline__ uint32_t k7_div(uint32_t x, const K7FastDiv f) {
+    return (uint32_t)(((uint64_t)x * f.m) >> f.sh);
+}
 
 struct K7LossDev {
     float alpha, one_m_alpha;
@@ -25,6 +66,18 @@ struct K7LossDev {
     int use_div;
     int yx_targets;
     int B, A, C, M;
+};
+
+struct K7LossGeom {
+    uint32_t AC;          // elements per image
+    uint32_t tpi;         // tiles per image
+    uint32_t num_tiles;   // B * tpi
+    K7FastDiv div_c, div_tpi;
+    uint32_t side_words;  // assignment words reserved per stage
+    uint32_t stage_stride;
+    int stages, warps, grid;
+    int tma;
+    size_t smem_bytes;
 };
 
 // per-image gradient scales, from the match stage's num_pos:
@@ -41,248 +94,338 @@ __global__ void k7_loss_scales_kernel(const int32_t* __restrict__ num_pos, int B
     scales[b] = s;
 }
 
-template <int VEC>
-struct K7Vec;
-template <>
-struct K7Vec<1> {
-    typedef float T;
-};
-template <>
-struct K7Vec<2> {
-    typedef float2 T;
-};
-template <>
-struct K7Vec<4> {
-    typedef float4 T;
-};
-
-// One vector of VEC classes of a non-ignored row: returns the loss contribution, optionally
-// overwrites the values with gradients.
-template <int VEC, bool GRAD>
-__device__ __forceinline__ float k7_focal_vec(float* __restrict__ ptr, float one_m_alpha, float gscale) {
-    typedef typename K7Vec<VEC>::T V;
-    V raw = *reinterpret_cast<const V*>(ptr);
-    float x[VEC], p[VEC], q[VEC], pp[VEC], nl[VEC];
-#pragma unroll
-    for (int e = 0; e < VEC; ++e) x[e] = reinterpret_cast<const float*>(&raw)[e];
-    bool slow = false;
-#pragma unroll
-    for (int e = 0; e < VEC; ++e) {
-        p[e] = k7_clamp_p(x[e]);
-        q[e] = 1.0f - p[e];
-        pp[e] = 1.0f - q[e];
-        nl[e] = k7_neg_log1m_poly(pp[e]);
-        slow |= pp[e] > K7_POLY_MAX;
-    }
-    if (slow) {
-#pragma unroll
-        for (int e = 0; e < VEC; ++e)
-            if (pp[e] > K7_POLY_MAX) nl[e] = -logf(q[e]);
-    }
-    float acc = 0.0f;
-#pragma unroll
-    for (int e = 0; e < VEC; ++e) acc = fmaf(one_m_alpha * (p[e] * p[e]), nl[e], acc);
-    if (GRAD) {
-        V out;
-#pragma unroll
-        for (int e = 0; e < VEC; ++e) {
-            const float g = k7_focal_neg_grad(p[e], q[e], nl[e], one_m_alpha) * gscale;
-            reinterpret_cast<float*>(&out)[e] = k7_clamp_pass(x[e]) ? g : 0.0f;
-        }
-        *reinterpret_cast<V*>(ptr) = out;
-    }
-    return acc;
+// ------------------------------------------------------------------ element math
+__device__ __forceinline__ float k7_rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
 
-template <int VEC, bool GRAD, bool FROM_SPEC>
-__global__ void __launch_bounds__(K7_LOSS_MAX_THREADS, 1)
+// Two "target 0" elements.  Returns their gradients (GRAD), accumulates p^2 * -log(1-p) into acc
+// and max(p) into pmax.  ign: bit 0 / bit 1 = element belongs to an ignored row.
+template <bool GRAD, bool MASKED>
+__device__ __forceinline__ float2 k7_neg_pair(const float2 x, const uint32_t ign, const float2 sco, float2& acc,
+                                              float& pmax) {
+    float2 p;
+    p.x = fminf(fmaxf(x.x, K7_P_LO), K7_P_HI);
+    p.y = fminf(fmaxf(x.y, K7_P_LO), K7_P_HI);
+    pmax = fmaxf(pmax, fmaxf(p.x, p.y));
+    const float2 one = make_float2(1.0f, 1.0f), neg1 = make_float2(-1.0f, -1.0f);
+    const float2 q = __ffma2_rn(p, neg1, one);     // fl(1 - p), what the reference feeds to log (losses.py:110)
+    const float2 pp = __ffma2_rn(q, neg1, one);    // 1 - q, exact
+    float2 s = make_float2(0.3357100188732147f, 0.3357100188732147f);
+    s = __ffma2_rn(s, pp, make_float2(0.1467030793428421f, 0.1467030793428421f));
+    s = __ffma2_rn(s, pp, make_float2(0.25711026787757874f, 0.25711026787757874f));
+    s = __ffma2_rn(s, pp, make_float2(0.33293071389198303f, 0.33293071389198303f));
+    s = __ffma2_rn(s, pp, make_float2(0.5000072717666626f, 0.5000072717666626f));
+    s = __ffma2_rn(s, pp, one);
+    const float2 nl = __fmul2_rn(pp, s);           // -log(q)
+    float2 t = __fmul2_rn(p, p);
+    if (MASKED) {
+        if (ign & 1u) t.x = 0.0f;
+        if (ign & 2u) t.y = 0.0f;
+    }
+    acc = __ffma2_rn(t, nl, acc);
+    float2 g = make_float2(0.0f, 0.0f);
+    if (GRAD) {
+        float2 r;
+        r.x = k7_rcp_approx(q.x);
+        r.y = k7_rcp_approx(q.y);
+        const float2 u = __fmul2_rn(p, r);                                   // p / (1-p)
+        const float2 v = __ffma2_rn(make_float2(2.0f, 2.0f), nl, u);         // 2*nl + p/(1-p)
+        const float2 w = __fmul2_rn(p, sco);                                 // (1-alpha) * scale * p
+        g = __fmul2_rn(w, v);
+        // torch.clamp passes the gradient on the closed interval  <=>  clamp(x) == x
+        const bool k0 = (p.x == x.x) && !(MASKED && (ign & 1u));
+        const bool k1 = (p.y == x.y) && !(MASKED && (ign & 2u));
+        g.x = k0 ? g.x : 0.0f;
+        g.y = k1 ? g.y : 0.0f;
+    }
+    return g;
+}
+
+template <bool GRAD, bool MASKED>
+__device__ __forceinline__ void k7_flat4(float4* __restrict__ p4, const uint32_t nib, const float2 sco, float2& acc,
+                                         float& pmax) {
+    const float4 x = *p4;
+    const float2 ga = k7_neg_pair<GRAD, MASKED>(make_float2(x.x, x.y), nib & 3u, sco, acc, pmax);
+    const float2 gb = k7_neg_pair<GRAD, MASKED>(make_float2(x.z, x.w), (nib >> 2) & 3u, sco, acc, pmax);
+    if (GRAD) *p4 = make_float4(ga.x, ga.y, gb.x, gb.y);
+}
+
+// The flat pass over n4 float4s of a tile.  mask: one bit per element (set = ignored row).
+template <int TILE_F, bool GRAD, bool MASKED>
+__device__ __forceinline__ void k7_flat_pass(float* __restrict__ tile, const int n4, const uint32_t* __restrict__ mask,
+                                             const int lane, const float sco1, float2& acc, float& pmax) {
+    float4* t4 = reinterpret_cast<float4*>(tile);
+    const float2 sco = make_float2(sco1, sco1);
+    const int sh = (lane & 7) * 4;
+    if (n4 == TILE_F / 4) {
+#pragma unroll
+        for (int k = 0; k < TILE_F / 128; ++k) {
+            uint32_t nib = 0;
+            if (MASKED) nib = (mask[(lane >> 3) + 4 * k] >> sh) & 15u;
+            k7_flat4<GRAD, MASKED>(t4 + lane + 32 * k, nib, sco, acc, pmax);
+        }
+    } else {
+        for (int f = lane; f < n4; f += 32) {
+            uint32_t nib = 0;
+            if (MASKED) nib = (mask[f >> 3] >> sh) & 15u;
+            k7_flat4<GRAD, MASKED>(t4 + f, nib, sco, acc, pmax);
+        }
+    }
+}
+
+// Exact scalar evaluation of one "target 0" element (any p): loss without the (1-alpha) factor,
+// gradient without (1-alpha)*scale.  Used by the redo path and by the label patch.
+__device__ __forceinline__ float k7_neg_exact(const float x, float* grad) {
+    const float p = k7_clamp_p(x);
+    const float q = 1.0f - p;
+    const float nl = k7_neg_log1m(q);
+    if (grad) *grad = (p == x) ? p * fmaf(2.0f, nl, p * k7_rcp_approx(q)) : 0.0f;
+    return (p * p) * nl;
+}
+
+// ------------------------------------------------------------------ tile bookkeeping
+struct K7Tile {
+    uint32_t b, off, n, row_first, rem, nrows;
+};
+__device__ __forceinline__ K7Tile k7_tile_coords(const K7LossGeom& G, const int C, const int TILE_F, const uint32_t g) {
+    K7Tile t;
+    t.b = k7_div(g, G.div_tpi);
+    t.off = (g - t.b * G.tpi) * (uint32_t)TILE_F;
+    t.n = min((uint32_t)TILE_F, G.AC - t.off);
+    t.row_first = k7_div(t.off, G.div_c);
+    t.rem = t.off - t.row_first * (uint32_t)C;
+    t.nrows = k7_div(t.rem + t.n - 1u, G.div_c) + 1u;
+    return t;
+}
+
+template <int TILE_F, bool GRAD, bool FROM_SPEC, bool TMA>
+__global__ void __launch_bounds__(K7_LOSS_MAX_WARPS * 32, 1)
 k7_loss_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
                const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
                const int32_t* __restrict__ assign, const float2* __restrict__ scales,
-               const __grid_constant__ K7LossDev P, const __grid_constant__ K7StreamGeom G,
-               float4* __restrict__ partials, float* __restrict__ dcls, float4* __restrict__ dreg) {
+               const __grid_constant__ K7LossDev P, const __grid_constant__ K7LossGeom G,
+               float2* __restrict__ partials, float* __restrict__ dcls, float4* __restrict__ dreg) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages;
-    // per-warp region: NS stages, then NS mbarriers (kept at the end of the CTA's shared memory)
+    const int C = P.C, A = P.A;
     unsigned char* ring = smem + (size_t)warp * NS * G.stage_stride;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)G.warps * NS * G.stage_stride) + warp * NS;
+    unsigned char* tail = smem + (size_t)G.warps * NS * G.stage_stride;
+    uint32_t* mask = reinterpret_cast<uint32_t*>(tail) + warp * (TILE_F / 32);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tail + (size_t)G.warps * (TILE_F / 8)) + warp * NS;
 
-    const long long gw = (long long)blockIdx.x * G.warps + warp;
-    const long long nW = (long long)gridDim.x * G.warps;
+    const uint32_t gw = blockIdx.x * G.warps + warp;
+    const uint32_t nW = gridDim.x * G.warps;
     if (gw >= G.num_tiles) return;
 
-    if (lane == 0) {
-        for (int s = 0; s < NS; ++s) k7_mbar_init(bars + s, 1);
-        k7_fence_mbar_init();
-        k7_fence_proxy_async();
-    }
-    __syncwarp();
+    // lane 0: issue the bulk copies of tile g into a stage
+    auto issue = [&](const uint32_t g, unsigned char* stage, uint64_t* bar) {
+        const K7Tile t = k7_tile_coords(G, C, TILE_F, g);
+        const size_t g0 = (size_t)t.b * A + t.row_first;
+        const uint32_t lead = (uint32_t)(g0 & 3);
+        const uint32_t side_bytes = ((lead + t.nrows + 3u) & ~3u) * 4u;
+        k7_mbar_expect_tx(bar, t.n * 4u + side_bytes);
+        k7_bulk_g2s(stage, cls + (size_t)t.b * G.AC + t.off, t.n * 4u, bar);
+        k7_bulk_g2s(stage + TILE_F * 4, assign + (g0 - lead), side_bytes, bar);
+    };
 
-    // prefetch distance: with gradients a stage is load -> compute -> store, keep one stage for
+    // prefetch distance: with gradients a stage is load -> compute -> store, one stage is kept for
     // the draining store; without, every stage but the current one can be in flight.
     const int PF = GRAD ? NS - 2 : NS - 1;
-    if (lane == 0) {
-        for (int k = 0; k < PF; ++k) {
-            const long long t = gw + k * nW;
-            if (t < G.num_tiles) k7_stream_issue(G, cls, assign, t, ring + (size_t)(k % NS) * G.stage_stride, bars + (k % NS));
+    if (TMA) {
+        if (lane == 0) {
+            for (int s = 0; s < NS; ++s) k7_mbar_init(bars + s, 1);
+            k7_fence_mbar_init();
+            k7_fence_proxy_async();
+        }
+        __syncwarp();
+        if (lane == 0) {
+            for (int k = 0; k < PF; ++k) {
+                const uint64_t g = (uint64_t)gw + (uint64_t)k * nW;
+                if (g < G.num_tiles) issue((uint32_t)g, ring + (size_t)(k % NS) * G.stage_stride, bars + (k % NS));
+            }
         }
     }
 
-    const int q = lane & (G.lpr - 1);
-    const int rsub = lane >> G.lpr_shift;
-    int clo, chi;
-    k7_class_range(G, q, clo, chi);
     const float oma = P.one_m_alpha;
-
     int it = 0;
-    for (long long tile = gw; tile < G.num_tiles; tile += nW, ++it) {
-        const int s = it % NS;
+    for (uint64_t g64 = gw; g64 < G.num_tiles; g64 += nW, ++it) {
+        const uint32_t g = (uint32_t)g64;
+        const int s = TMA ? it % NS : 0;
         unsigned char* stage = ring + (size_t)s * G.stage_stride;
-        // keep the ring full
-        if (lane == 0) {
-            const long long t = tile + (long long)PF * nW;
-            if (t < G.num_tiles) {
-                const int sn = (it + PF) % NS;
-                if (GRAD) k7_bulk_wait_read<1>();   // the store that last used stage sn has been read out
-                k7_stream_issue(G, cls, assign, t, ring + (size_t)sn * G.stage_stride, bars + sn);
-            }
-        }
-        k7_mbar_wait(bars + s, (it / NS) & 1);
-
-        const long long row0 = tile * (long long)G.T;
-        long long rows_ll = G.total_rows - row0;
-        const int rows = rows_ll > G.T ? G.T : (int)rows_ll;
-        float* tilef = reinterpret_cast<float*>(stage);
-        const int32_t* asg = reinterpret_cast<const int32_t*>(stage + G.tile_bytes);
-        const uint32_t cls_bytes = (uint32_t)rows * G.C * 4u;
-        const uint32_t rem = cls_bytes & 15u;
-        if (rem) {   // only the last tile of a tensor with B*A*C % 4 != 0
+        float* tile = reinterpret_cast<float*>(stage);
+        const K7Tile t = k7_tile_coords(G, C, TILE_F, g);
+        const size_t e0 = (size_t)t.b * G.AC + t.off;     // first element of the tile in cls / dcls
+        const size_t g0 = (size_t)t.b * A + t.row_first;  // first row of the tile in assign / reg / dreg
+        const int n = (int)t.n, nrows = (int)t.nrows, rem = (int)t.rem;
+        const int n4 = (n + 3) >> 2;
+        const int32_t* side;
+        if (TMA) {
             if (lane == 0) {
-                const uint32_t base = (cls_bytes & ~15u) >> 2;
-                for (uint32_t k = 0; k < (rem >> 2); ++k) tilef[base + k] = cls[row0 * G.C + base + k];
+                const uint64_t gn = g64 + (uint64_t)PF * nW;
+                if (gn < G.num_tiles) {
+                    const int sn = (it + PF) % NS;
+                    if (GRAD) k7_bulk_wait_read<1>();   // the store that last used stage sn has been read out
+                    issue((uint32_t)gn, ring + (size_t)sn * G.stage_stride, bars + sn);
+                }
             }
+            k7_mbar_wait(bars + s, (it / NS) & 1);
+            side = reinterpret_cast<const int32_t*>(stage + TILE_F * 4) + (g0 & 3);
+        } else {
+            int32_t* sd = reinterpret_cast<int32_t*>(stage + TILE_F * 4);
+            for (int i = lane; i < 4 * n4; i += 32) tile[i] = (i < n) ? cls[e0 + i] : 0.0f;
+            for (int k = lane; k < nrows; k += 32) sd[k] = assign[g0 + k];
+            side = sd;
             __syncwarp();
         }
 
-        const int b0 = (int)(row0 / P.A);
-        const long long split = (long long)(b0 + 1) * P.A;    // first row of image b0+1
-        const float2 sc0 = __ldg(scales + b0);
-        const float2 sc1 = __ldg(scales + min(b0 + 1, P.B - 1));
-        float cls0 = 0.f, cls1 = 0.f, reg0 = 0.f, reg1 = 0.f;
-
-        for (int i = 0; i < G.iters; ++i) {
-            const int r = i * G.rows_per_iter + rsub;
-            if (r >= rows) break;
-            const long long R = row0 + r;
-            const bool second = R >= split;
-            const float2 sc = second ? sc1 : sc0;
-            const int aw = asg[r];
-            const int state = K7_ASSIGN_STATE(aw);
-            float* rowp = tilef + (size_t)r * G.C;
-            float rs = 0.0f;
-            if (state != K7_STATE_IGNORE) {
-                int label = -1;
-                float xl = 0.0f;
-                const int b = second ? b0 + 1 : b0;
-                const float* arow = annotations + ((size_t)b * P.M + K7_ASSIGN_ROW(aw)) * 5;
-                if (state == K7_STATE_POS) {
-                    label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
-                    if (label >= clo && label < chi) xl = rowp[label]; else label = -1;
-                }
-                float a0 = 0.f, a1 = 0.f;
-                int j = clo;
-                for (; j + 2 * VEC <= chi; j += 2 * VEC) {
-                    a0 += k7_focal_vec<VEC, GRAD>(rowp + j, oma, sc.x);
-                    a1 += k7_focal_vec<VEC, GRAD>(rowp + j + VEC, oma, sc.x);
-                }
-                for (; j < chi; j += VEC) a0 += k7_focal_vec<VEC, GRAD>(rowp + j, oma, sc.x);
-                rs = a0 + a1;
-                if (label >= 0) {
-                    // the label class has target 1: replace its "target 0" term
-                    const float p = k7_clamp_p(xl);
-                    const float qq = 1.0f - p;
-                    const float nl = k7_neg_log1m(qq);
-                    rs += k7_focal_pos(p, P.alpha) - k7_focal_neg(p, nl, oma);
-                    if (GRAD) rowp[label] = k7_clamp_pass(xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
-                }
-                // smooth-L1 on positives, one lane per row
-                if (q == 0) {
-                    float4 gr = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (state == K7_STATE_POS) {
-                        const int a = (int)(R - (long long)b * P.A);
-                        float ax1, ay1, ax2, ay2;
-                        k7_anchor<FROM_SPEC>(spec, anchors, box_order, a, ax1, ay1, ax2, ay2);
-                        const float g0 = __ldg(arow + 0), g1 = __ldg(arow + 1), g2 = __ldg(arow + 2), g3 = __ldg(arow + 3);
-                        const K7Reg4 t = k7_reg_targets(ax1, ay1, ax2, ay2, g0, g1, g2, g3, P.use_div ? P.div : nullptr,
-                                                        P.yx_targets);
-                        const float4 rv = __ldg(reinterpret_cast<const float4*>(reg) + R);
-                        float gx, gy, gz, gw_;
-                        float l = k7_smooth_l1(t.v[0], rv.x, P.beta, P.quad, P.shift, &gx);
-                        l += k7_smooth_l1(t.v[1], rv.y, P.beta, P.quad, P.shift, &gy);
-                        l += k7_smooth_l1(t.v[2], rv.z, P.beta, P.quad, P.shift, &gz);
-                        l += k7_smooth_l1(t.v[3], rv.w, P.beta, P.quad, P.shift, &gw_);
-                        if (second) reg1 += l; else reg0 += l;
-                        gr = make_float4(gx * sc.y, gy * sc.y, gz * sc.y, gw_ * sc.y);
-                    }
-                    if (GRAD) dreg[R] = gr;
-                }
-            } else if (GRAD) {
-                typedef typename K7Vec<VEC>::T V;
-                V z;
+        // ---- ignored rows -> element bit mask (one 32-bit word per lane per 1024 elements)
+        uint32_t mword[TILE_F / 1024];
 #pragma unroll
-                for (int e = 0; e < VEC; ++e) reinterpret_cast<float*>(&z)[e] = 0.0f;
-                for (int j = clo; j < chi; j += VEC) *reinterpret_cast<V*>(rowp + j) = z;
-                if (q == 0) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < TILE_F / 1024; ++j) mword[j] = 0u;
+        bool masked = false;
+        auto mark = [&](int lo, int hi) {   // elements [lo, hi) of the tile are ignored
+#pragma unroll
+            for (int j = 0; j < TILE_F / 1024; ++j) {
+                const int base = 32 * (lane + 32 * j);
+                const int a = max(lo - base, 0), z = min(hi - base, 32);
+                if (z > a) mword[j] |= (z - a == 32) ? 0xffffffffu : (((1u << (z - a)) - 1u) << a);
             }
-            if (second) cls1 += rs; else cls0 += rs;
+        };
+        for (int k0 = 0; k0 < nrows; k0 += 32) {
+            const int k = k0 + lane;
+            const int st = (k < nrows) ? K7_ASSIGN_STATE(side[k]) : K7_STATE_NEG;
+            unsigned ib = __ballot_sync(0xffffffffu, st == K7_STATE_IGNORE);
+            if (ib == 0u) continue;
+            masked = true;
+            if (C == 1) {   // row k is element k: the ballot IS the mask word
+#pragma unroll
+                for (int j = 0; j < TILE_F / 1024; ++j)
+                    if (lane + 32 * j == (k0 >> 5)) mword[j] = ib;
+            } else {
+                while (ib) {
+                    const int kk = k0 + __ffs(ib) - 1;
+                    ib &= ib - 1;
+                    const int lo = kk * C - rem;
+                    mark(max(lo, 0), min(lo + C, n));
+                }
+            }
+        }
+        if (!TMA && (n & 3)) {   // zero padding of the last float4
+            masked = true;
+            mark(n, 4 * n4);
+        }
+        if (masked) {
+#pragma unroll
+            for (int j = 0; j < TILE_F / 1024; ++j) mask[lane + 32 * j] = mword[j];
+            __syncwarp();
         }
 
-        // tile partial: every tile writes its slot (no memset, no atomics)
-        cls0 = k7_warp_sum(cls0);
-        reg0 = k7_warp_sum(reg0);
-        if (row0 + rows > split) {   // warp-uniform: the tile straddles two images
-            cls1 = k7_warp_sum(cls1);
-            reg1 = k7_warp_sum(reg1);
+        // ---- flat pass
+        const float2 sc = __ldg(scales + t.b);
+        const float sco = oma * sc.x;
+        float2 acc = make_float2(0.0f, 0.0f);
+        float pmax = 0.0f;
+        if (masked)
+            k7_flat_pass<TILE_F, GRAD, true>(tile, n4, mask, lane, sco, acc, pmax);
+        else
+            k7_flat_pass<TILE_F, GRAD, false>(tile, n4, mask, lane, sco, acc, pmax);
+        float csum = acc.x + acc.y;
+        if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
+            // a confident prediction: outside the polynomial's range.  Redo the tile exactly.
+            __syncwarp();
+            csum = 0.0f;
+            for (int i = lane; i < n; i += 32) {
+                const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
+                float gr;
+                const float l = k7_neg_exact(__ldg(cls + e0 + i), &gr);
+                if (!ign) csum += l;
+                if (GRAD) tile[i] = ign ? 0.0f : sco * gr;
+            }
         }
-        if (lane == 0) partials[tile] = make_float4(cls0, cls1, reg0, reg1);
+        csum *= oma;
+        __syncwarp();
+
+        // ---- rows: smooth-L1 / d(reg) for rows starting in the tile, label patch for positives
+        float rsum = 0.0f;
+        for (int k = lane; k < nrows; k += 32) {
+            const int aw = side[k];
+            const int i0 = k * C - rem;   // tile-local element index of the row's class 0
+            const bool starts = i0 >= 0;
+            const size_t R = g0 + k;
+            float4 gr = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (K7_ASSIGN_STATE(aw) == K7_STATE_POS) {
+                const float* arow = annotations + ((size_t)t.b * P.M + K7_ASSIGN_ROW(aw)) * 5;
+                if (starts) {
+                    float ax1, ay1, ax2, ay2;
+                    k7_anchor<FROM_SPEC>(spec, anchors, box_order, (int)(t.row_first + k), ax1, ay1, ax2, ay2);
+                    const float g0x = __ldg(arow + 0), g1 = __ldg(arow + 1), g2 = __ldg(arow + 2), g3 = __ldg(arow + 3);
+                    const K7Reg4 tg = k7_reg_targets(ax1, ay1, ax2, ay2, g0x, g1, g2, g3, P.use_div ? P.div : nullptr,
+                                                     P.yx_targets);
+                    const float4 rv = __ldg(reinterpret_cast<const float4*>(reg) + R);
+                    float gx, gy, gz, gw_;
+                    float l = k7_smooth_l1(tg.v[0], rv.x, P.beta, P.quad, P.shift, &gx);
+                    l += k7_smooth_l1(tg.v[1], rv.y, P.beta, P.quad, P.shift, &gy);
+                    l += k7_smooth_l1(tg.v[2], rv.z, P.beta, P.quad, P.shift, &gz);
+                    l += k7_smooth_l1(tg.v[3], rv.w, P.beta, P.quad, P.shift, &gw_);
+                    rsum += l;
+                    gr = make_float4(gx * sc.y, gy * sc.y, gz * sc.y, gw_ * sc.y);
+                }
+                const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
+                const int il = i0 + label;
+                if (label >= 0 && label < C && il >= 0 && il < n) {
+                    // the label class has target 1: replace its "target 0" term
+                    const float xl = __ldg(cls + e0 + il);
+                    const float p = k7_clamp_p(xl);
+                    csum += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
+                    if (GRAD) tile[il] = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
+                }
+            }
+            if (GRAD && starts) dreg[R] = gr;
+        }
+
+        // ---- tile partial: every tile writes its slot (no memset, no atomics)
+        csum = k7_warp_sum(csum);
+        if (__any_sync(0xffffffffu, rsum != 0.0f)) rsum = k7_warp_sum(rsum);
+        if (lane == 0) partials[g] = make_float2(csum, rsum);
 
         if (GRAD) {
-            k7_fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-                float* dst = dcls + row0 * G.C;
-                const uint32_t bulk = cls_bytes & ~15u;
-                if (bulk) k7_bulk_s2g(dst, stage, bulk);
-                k7_bulk_commit();
-                if (rem) {
-                    const uint32_t base = bulk >> 2;
-                    for (uint32_t k = 0; k < (rem >> 2); ++k) dst[base + k] = tilef[base + k];
+            if (TMA) {
+                k7_fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    k7_bulk_s2g(dcls + e0, stage, (uint32_t)n * 4u);
+                    k7_bulk_commit();
                 }
+            } else {
+                __syncwarp();
+                for (int i = lane; i < n; i += 32) dcls[e0 + i] = tile[i];
+                __syncwarp();
             }
         } else {
             __syncwarp();
         }
     }
-    if (GRAD && lane == 0) k7_bulk_wait<0>();
+    if (TMA && GRAD && lane == 0) k7_bulk_wait<0>();
 }
 
 // Per image: sum the tile partials in float64, fixed order; write (cls_loss_i, reg_loss_i).
 // The last block to finish reduces the batch (threadfence + counter).
 __global__ void __launch_bounds__(256)
-k7_loss_finalize_kernel(const float4* __restrict__ partials, const int32_t* __restrict__ num_pos, int B, int A, int T,
+k7_loss_finalize_kernel(const float2* __restrict__ partials, const int32_t* __restrict__ num_pos, int B, uint32_t tpi,
                         float* __restrict__ per_image, float* __restrict__ sums, unsigned int* __restrict__ counter) {
-    __shared__ double s_c[256], s_r[256];
+    __shared__ double s_c[256], s_r[256], s_n[256];
     __shared__ bool s_last;
     const int b = blockIdx.x;
-    const long long first = (long long)b * A, last = first + A - 1;
-    const long long t0 = first / T, t1 = last / T;
+    const float2* pt = partials + (size_t)b * tpi;
     double c = 0.0, r = 0.0;
-    for (long long t = t0 + threadIdx.x; t <= t1; t += blockDim.x) {
-        const float4 p = partials[t];
-        const bool second = (t * (long long)T) < first;   // tile started in image b-1
-        c += second ? p.y : p.x;
-        r += second ? p.w : p.z;
+    for (uint32_t t = threadIdx.x; t < tpi; t += blockDim.x) {
+        const float2 p = pt[t];
+        c += p.x;
+        r += p.y;
     }
     s_c[threadIdx.x] = c;
     s_r[threadIdx.x] = r;
@@ -314,7 +457,6 @@ k7_loss_finalize_kernel(const float4* __restrict__ partials, const int32_t* __re
             rr += (double)__ldcg(per_image + 2 * i + 1);
             nn += (double)num_pos[i];
         }
-        __shared__ double s_n[256];
         s_c[threadIdx.x] = cc;
         s_r[threadIdx.x] = rr;
         s_n[threadIdx.x] = nn;
@@ -361,7 +503,12 @@ extern "C" int k7_scale_inplace(float* grad, size_t n, const float* scale, void*
 }
 
 // ------------------------------------------------------------------ host side
-static size_t k7_loss_ws_layout(int B, long long num_tiles, size_t* off_scales, size_t* off_partials,
+static uint32_t k7_loss_tpi(int A, int C) {
+    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
+    return (uint32_t)((ac + K7_LOSS_TILE - 1) / K7_LOSS_TILE);
+}
+
+static size_t k7_loss_ws_layout(int B, unsigned long long num_tiles, size_t* off_scales, size_t* off_partials,
                                 size_t* off_counter) {
     size_t o = 0;
     *off_counter = o;
@@ -369,24 +516,63 @@ static size_t k7_loss_ws_layout(int B, long long num_tiles, size_t* off_scales, 
     *off_scales = o;
     o += k7_align_up(sizeof(float2) * (size_t)B, 256);
     *off_partials = o;
-    o += k7_align_up(sizeof(float4) * (size_t)num_tiles, 256);
+    o += k7_align_up(sizeof(float2) * (size_t)num_tiles, 256);
     return o;
 }
 
 extern "C" size_t k7_loss_workspace_bytes(int B, int A, int C) {
     if (B <= 0 || A <= 0 || C <= 0) return 0;
-    // worst case for the tile count: the smallest tile the geometry can pick is 4 rows
-    const long long rows = (long long)B * A;
     size_t a, b, c;
-    return k7_loss_ws_layout(B, (rows + 3) / 4, &a, &b, &c);
+    return k7_loss_ws_layout(B, (unsigned long long)B * k7_loss_tpi(A, C), &a, &b, &c);
 }
 
-template <int VEC, bool GRAD, bool FROM_SPEC>
+static int k7_env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    if (!v || !*v) return dflt;
+    return atoi(v);
+}
+
+static int k7_loss_geometry(int B, int A, int C, bool grad, K7LossGeom* g) {
+    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
+    K7_REQUIRE(ac < (1ull << 31) - 2 * K7_LOSS_TILE, "k7_loss: A*C=%llu per image is too large", ac);
+    g->AC = (uint32_t)ac;
+    g->tpi = k7_loss_tpi(A, C);
+    const unsigned long long nt = (unsigned long long)B * g->tpi;
+    K7_REQUIRE(nt < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", nt);
+    g->num_tiles = (uint32_t)nt;
+    g->div_c = k7_fastdiv_make((uint32_t)C);
+    g->div_tpi = k7_fastdiv_make(g->tpi);
+    g->tma = (ac % 4ull) == 0ull;
+    // rows touching a tile: (TILE-1)/C + 2 at most, + 3 words of alignment lead, rounded to 16 bytes
+    g->side_words = (uint32_t)(((K7_LOSS_TILE - 1) / C + 2 + 3 + 3) & ~3);
+    g->stage_stride = (uint32_t)k7_align_up((size_t)K7_LOSS_TILE * 4 + (size_t)g->side_words * 4, 128);
+    int stages = k7_env_int("K7_STAGES", grad ? 4 : 3);
+    if (stages < 3) stages = 3;
+    if (stages > 8) stages = 8;
+    if (!g->tma) stages = 1;
+    g->stages = stages;
+    const size_t budget = 224 * 1024;
+    const size_t per_warp = (size_t)stages * g->stage_stride + K7_LOSS_TILE / 8 + (size_t)stages * 8;
+    int warps = (int)(budget / per_warp);
+    const int cap = k7_env_int("K7_WARPS", K7_LOSS_MAX_WARPS);
+    if (warps > cap) warps = cap;
+    if (warps > K7_LOSS_MAX_WARPS) warps = K7_LOSS_MAX_WARPS;
+    K7_REQUIRE(warps >= 1, "k7_loss: C=%d needs %zu bytes of shared memory per warp", C, per_warp);
+    g->warps = warps;
+    g->smem_bytes = (size_t)warps * per_warp;
+    unsigned long long ctas = (nt + warps - 1) / warps;
+    int grid = k7_sm_count();
+    if (ctas < (unsigned long long)grid) grid = (int)ctas;
+    g->grid = grid < 1 ? 1 : grid;
+    return K7_OK;
+}
+
+template <bool GRAD, bool FROM_SPEC, bool TMA>
 static int k7_loss_launch(const K7AnchorSpec& spec, const float* anchors, int box_order, const float* cls,
                           const float* reg, const float* annotations, const int32_t* assign, const float2* scales,
-                          const K7LossDev& P, const K7StreamGeom& G, float4* partials, float* dcls, float* dreg,
+                          const K7LossDev& P, const K7LossGeom& G, float2* partials, float* dcls, float* dreg,
                           cudaStream_t st) {
-    auto kern = k7_loss_kernel<VEC, GRAD, FROM_SPEC>;
+    auto kern = k7_loss_kernel<K7_LOSS_TILE, GRAD, FROM_SPEC, TMA>;
     K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
     kern<<<G.grid, G.warps * 32, G.smem_bytes, st>>>(spec, anchors, box_order, cls, reg, annotations, assign, scales, P, G,
                                                      partials, dcls, reinterpret_cast<float4*>(dreg));
@@ -402,7 +588,7 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
                "k7_loss: null argument");
     K7_REQUIRE(spec || anchors, "k7_loss: need an anchor spec or an anchor tensor");
     K7_REQUIRE((dcls == nullptr) == (dreg == nullptr), "k7_loss: dcls and dreg must be given together");
-    K7_REQUIRE(B > 0 && A >= 32 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d (A >= 32 required)", B, A, C, M);
+    K7_REQUIRE(B > 0 && A > 0 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d", B, A, C, M);
     K7_REQUIRE(params->mean_divisor > 0, "k7_loss: mean_divisor must be positive");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(reg) & 15) == 0 &&
                    (reinterpret_cast<uintptr_t>(assign) & 15) == 0,
@@ -420,8 +606,8 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool grad = dcls != nullptr;
 
-    K7StreamGeom G;
-    int rc = k7_stream_geometry((long long)B * A, A, C, 4, grad ? 4 : 3, K7_LOSS_MAX_THREADS / 32, &G);
+    K7LossGeom G;
+    int rc = k7_loss_geometry(B, A, C, grad, &G);
     if (rc) return rc;
 
     size_t off_scales, off_partials, off_counter;
@@ -433,7 +619,7 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     unsigned char* ws = static_cast<unsigned char*>(workspace);
     K7_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "k7_loss: workspace must be 256-byte aligned");
     float2* scales = reinterpret_cast<float2*>(ws + off_scales);
-    float4* partials = reinterpret_cast<float4*>(ws + off_partials);
+    float2* partials = reinterpret_cast<float2*>(ws + off_partials);
     unsigned int* counter = reinterpret_cast<unsigned int*>(ws + off_counter);
 
     K7LossDev P;
@@ -460,30 +646,22 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
 
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-#define K7_LOSS_DISPATCH(V)                                                                                              \
-    do {                                                                                                                 \
-        if (grad) {                                                                                                      \
-            rc = spec ? k7_loss_launch<V, true, true>(sp, anchors, box_order, cls, reg, annotations, assign, scales, P, G, \
-                                                      partials, dcls, dreg, st)                                          \
-                      : k7_loss_launch<V, true, false>(sp, anchors, box_order, cls, reg, annotations, assign, scales, P, \
-                                                       G, partials, dcls, dreg, st);                                     \
-        } else {                                                                                                         \
-            rc = spec ? k7_loss_launch<V, false, true>(sp, anchors, box_order, cls, reg, annotations, assign, scales, P, \
-                                                       G, partials, dcls, dreg, st)                                      \
-                      : k7_loss_launch<V, false, false>(sp, anchors, box_order, cls, reg, annotations, assign, scales,   \
-                                                        P, G, partials, dcls, dreg, st);                                 \
-        }                                                                                                                \
-    } while (0)
-    if (G.vec == 4)
-        K7_LOSS_DISPATCH(4);
-    else if (G.vec == 2)
-        K7_LOSS_DISPATCH(2);
-    else
-        K7_LOSS_DISPATCH(1);
-#undef K7_LOSS_DISPATCH
+#define K7_LOSS_ARGS sp, anchors, box_order, cls, reg, annotations, assign, scales, P, G, partials, dcls, dreg, st
+    const int sel = (grad ? 4 : 0) | (spec ? 2 : 0) | (G.tma ? 1 : 0);
+    switch (sel) {
+        case 0: rc = k7_loss_launch<false, false, false>(K7_LOSS_ARGS); break;
+        case 1: rc = k7_loss_launch<false, false, true>(K7_LOSS_ARGS); break;
+        case 2: rc = k7_loss_launch<false, true, false>(K7_LOSS_ARGS); break;
+        case 3: rc = k7_loss_launch<false, true, true>(K7_LOSS_ARGS); break;
+        case 4: rc = k7_loss_launch<true, false, false>(K7_LOSS_ARGS); break;
+        case 5: rc = k7_loss_launch<true, false, true>(K7_LOSS_ARGS); break;
+        case 6: rc = k7_loss_launch<true, true, false>(K7_LOSS_ARGS); break;
+        default: rc = k7_loss_launch<true, true, true>(K7_LOSS_ARGS); break;
+    }
+#undef K7_LOSS_ARGS
     if (rc) return rc;
 
-    k7_loss_finalize_kernel<<<B, 256, 0, st>>>(partials, num_pos, B, A, G.T, per_image, sums, counter);
+    k7_loss_finalize_kernel<<<B, 256, 0, st>>>(partials, num_pos, B, G.tpi, per_image, sums, counter);
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
