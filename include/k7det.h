@@ -107,10 +107,14 @@ typedef struct K7MatchParams {
  *                         past the end.
  *   num_pos [B]   int32   positives per image
  *   iou_max [B,A] float32 (optional, may be NULL)  bit-identical to torch.max(IoU,1).values
- *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list */
+ *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list
+ *   zero_fill4 [B,A,4] float32 (optional, may be NULL) is filled with zeros: the d(reg) buffer a
+ *                         following k7_loss will write positive rows into (the kernel is ALU-bound,
+ *                         so the 16 B/anchor store is free here; see K7LossParams.dreg_prezeroed) */
 K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
              const float* annotations, int B, int A, int M, const K7MatchParams* params,
-             int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, void* stream);
+             int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, float* zero_fill4,
+             void* stream);
 
 typedef struct K7LossParams {
     float alpha;            /* 0.25 (losses.py:31) ; gamma is fixed at 2 (losses.py:32, pow == x*x) */
@@ -118,6 +122,7 @@ typedef struct K7LossParams {
     float target_div[4];    /* targets / [0.1,0.1,0.2,0.2] (losses.py:148); ones for loss_efficientdet.py */
     int32_t yx_targets;     /* 0: (dx,dy,dw,dh) (losses.py:144)  1: (dy,dx,dh,dw) (loss_efficientdet.py:127) */
     int32_t mean_divisor;   /* images the batch mean is taken over: B for one GPU, the GLOBAL batch when sharded */
+    int32_t dreg_prezeroed; /* 1: the caller (k7_match's zero_fill4) already zeroed dreg; 0: k7_loss zeroes it itself */
 } K7LossParams;
 
 K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);

@@ -51,6 +51,7 @@ class K7LossParams(C.Structure):
         ("target_div", C.c_float * 4),
         ("yx_targets", C.c_int32),
         ("mean_divisor", C.c_int32),
+        ("dreg_prezeroed", C.c_int32),
     ]
 
 
@@ -82,7 +83,7 @@ SYMBOLS = {
     "k7_last_error": (C.c_char_p, []),
     "k7_anchors_materialize": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P]),
     "k7_match": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, C.c_int, C.c_int, C.c_int,
-                           C.POINTER(K7MatchParams), _P, _P, _P, _P, _P]),
+                           C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),

@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(K7_MATCH_THREADS)
 k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
                 const float* __restrict__ annotations, int A, int M, float neg_thr, float pos_thr,
                 int32_t* __restrict__ assign, int32_t* __restrict__ num_pos, float* __restrict__ iou_max_out,
-                int32_t* __restrict__ argmax_out) {
+                int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4) {
     extern __shared__ float smem[];
     // SoA of the valid GT rows: x1 | y1 | x2 | y2 | area | row (as int)
     float* gx1 = smem;
@@ -136,6 +136,7 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
         assign[o] = (row << 2) | state;
         if (iou_max_out) iou_max_out[o] = best;
         if (argmax_out) argmax_out[o] = nv > 0 ? besti : -1;
+        if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     const unsigned pb = __ballot_sync(0xffffffffu, pos);
     if (lane == 0) s_pos[warp] = __popc(pb);
@@ -150,12 +151,13 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
 
 extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* annotations,
                         int B, int A, int M, const K7MatchParams* params, int32_t* assign, int32_t* num_pos,
-                        float* iou_max, int32_t* argmax, void* stream) {
+                        float* iou_max, int32_t* argmax, float* zero_fill4, void* stream) {
     K7_REQUIRE(annotations && params && assign && num_pos, "k7_match: null argument");
     K7_REQUIRE(spec || anchors, "k7_match: need an anchor spec or an anchor tensor");
     K7_REQUIRE(B > 0 && A > 0 && M > 0, "k7_match: bad shape B=%d A=%d M=%d", B, A, M);
     K7_REQUIRE(M < (1 << 29), "k7_match: M too large");
     K7_REQUIRE(B <= 65535, "k7_match: B > 65535 not supported");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(zero_fill4) & 15) == 0, "k7_match: zero_fill4 must be 16-byte aligned");
     if (spec) {
         int rc = k7_check_spec(spec, A);
         if (rc) return rc;
@@ -174,13 +176,13 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
             K7_CUDA(cudaFuncSetAttribute(k7_match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k7_match_kernel<true><<<grid, K7_MATCH_THREADS, smem, st>>>(*spec, nullptr, spec->box_order, annotations, A, M,
                                                                     params->neg_thr, params->pos_thr, assign, num_pos,
-                                                                    iou_max, argmax);
+                                                                    iou_max, argmax, reinterpret_cast<float4*>(zero_fill4));
     } else {
         if (smem > 48 * 1024)
             K7_CUDA(cudaFuncSetAttribute(k7_match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k7_match_kernel<false><<<grid, K7_MATCH_THREADS, smem, st>>>(kEmpty, anchors, box_order, annotations, A, M,
                                                                      params->neg_thr, params->pos_thr, assign, num_pos,
-                                                                     iou_max, argmax);
+                                                                     iou_max, argmax, reinterpret_cast<float4*>(zero_fill4));
     }
     K7_LAUNCH_CHECK();
     return K7_OK;

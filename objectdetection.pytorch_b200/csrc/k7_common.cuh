@@ -123,6 +123,22 @@ __device__ __forceinline__ void k7_mbar_expect_tx(uint64_t* bar, uint32_t bytes)
 __device__ __forceinline__ void k7_mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(k7_smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void k7_mbar_wait_u32(uint32_t bar_smem_addr, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "K7_WAITA_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra K7_DONEA_%=;\n"
+        "bra K7_WAITA_%=;\n"
+        "K7_DONEA_%=:\n"
+        "}\n" ::"r"(bar_smem_addr),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void k7_mbar_arrive_u32(uint32_t bar_smem_addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_smem_addr) : "memory");
+}
 __device__ __forceinline__ void k7_mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
         "{\n"

@@ -362,6 +362,37 @@ __device__ uint64_t* k7_block_radix_sort(uint64_t* a, uint64_t* b, int n, K7Sort
     return a;
 }
 
+// Bitonic sort of n <= K7_BITONIC_MAX keys in shared memory (keys are unique: the low word is the
+// anchor id), result written to `out`.  ~log2(N)^2/2 barrier-separated steps; for the usual few
+// hundred to few thousand survivors per image this replaces six to eight radix passes.
+#define K7_BITONIC_MAX 4096
+__device__ void k7_block_bitonic_sort(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int n,
+                                      unsigned long long* sk) {
+    const int tid = threadIdx.x;
+    int N = 64;
+    while (N < n) N <<= 1;
+    for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < n) ? in[i] : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (N >> 1); t += K7_NMS_THREADS) {
+                // t-th pair of this step: i has bit j clear
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int l = i | j;
+                const unsigned long long a = sk[i], b = sk[l];
+                const bool up = (i & k) == 0;
+                if ((a > b) == up) {
+                    sk[i] = b;
+                    sk[l] = a;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = tid; i < n; i += K7_NMS_THREADS) out[i] = sk[i];
+    __syncthreads();
+}
+
 __device__ __forceinline__ float k7_key_score(uint64_t key) {
     uint32_t u = ~(uint32_t)(key >> 32);
     u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
@@ -416,44 +447,88 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
         if (lane == 0) S.alive_bits[warp] = ab;
         if (tid == 0) S.kcount = 0;
         __syncthreads();
-        if (alive) {
-            for (int w = tid >> 6; w < (cn + 63) >> 6; ++w) {
+        {
+            // work items = (64-row block rb, mask word w >= rb, row r of the block): 64 consecutive
+            // threads share one (rb, w) pair, i.e. read the same 64 column boxes (broadcast), and
+            // every thread gets the same number of items whatever its row (the triangle is balanced)
+            const int nw = (cn + 63) >> 6;
+            const int items = (nw * (nw + 1) / 2) << 6;
+            for (int q = tid; q < items; q += K7_NMS_THREADS) {
+                int p = q >> 6, rb = 0;
+                while (p >= nw - rb) {
+                    p -= nw - rb;
+                    ++rb;
+                }
+                const int w = rb + p;
+                const int row = (rb << 6) | (q & 63);
+                if (row >= cn || !((S.alive_bits[row >> 5] >> (row & 31)) & 1u)) continue;
+                const float4 mb = S.box[row];
+                const K7Box me2 = {mb.x, mb.y, mb.z, mb.w};
+                const float marea = S.area[row];
                 unsigned long long word = 0ull;
-                const int jbeg = max(w * 64, tid + 1), jend = min(w * 64 + 64, cn);
+                const int jbeg = max(w * 64, row + 1), jend = min(w * 64 + 64, cn);
                 for (int j = jbeg; j < jend; ++j) {
                     const float4 ob = S.box[j];
                     const K7Box other = {ob.x, ob.y, ob.z, ob.w};
                     // an empty intersection gives overlap 0 (or NaN), never > thr >= 0: skip the division
-                    if (fminf(me.x2, other.x2) > fmaxf(me.x1, other.x1) && fminf(me.y2, other.y2) > fmaxf(me.y1, other.y1) &&
-                        k7_nms_suppress(me, area, other, S.area[j], thr))
+                    if (fminf(me2.x2, other.x2) > fmaxf(me2.x1, other.x1) && fminf(me2.y2, other.y2) > fmaxf(me2.y1, other.y1) &&
+                        k7_nms_suppress(me2, marea, other, S.area[j], thr))
                         word |= 1ull << (j & 63);
                 }
-                S.mask[w * K7_NMS_PITCH + tid] = word;
+                S.mask[w * K7_NMS_PITCH + row] = word;
             }
         }
         __syncthreads();
-        // (c) sequential scan by warp 0: lane w keeps the removed-word w of the chunk
+        // (c) greedy scan by warp 0, one 64-row block at a time.  Lane L holds the removed-word L.
+        //     Inside a block the decision chain only needs the block's DIAGONAL words (64 x u64,
+        //     two per lane, fetched before the chain starts and passed around with shuffles); the
+        //     kept rows' other words are OR-ed into the later lanes afterwards with independent loads.
         if (warp == 0) {
+            const int nw = (cn + 63) >> 6;
             unsigned long long remv = ~0ull;
             if (lane < K7_NMS_WORDS)
                 remv = ~((unsigned long long)S.alive_bits[2 * lane] | ((unsigned long long)S.alive_bits[2 * lane + 1] << 32));
             int kc = 0;
             const int budget = max_keep - kept0;
-            for (int w = 0; w < (cn + 63) >> 6 && kc < budget; ++w) {
+            for (int w = 0; w < nw && kc < budget; ++w) {
                 unsigned long long cur = __shfl_sync(0xffffffffu, remv, w);
-                while (kc < budget) {
-                    const unsigned long long freeb = ~cur;
-                    if (freeb == 0ull) break;
-                    const int bit = __ffsll((long long)freeb) - 1;
-                    const int row = w * 64 + bit;
-                    if (row >= cn) break;
-                    if (lane == 0) S.kept_rows[kc] = row;
-                    ++kc;
-                    if (lane < K7_NMS_WORDS && lane >= w) remv |= S.mask[lane * K7_NMS_PITCH + row];
-                    cur = __shfl_sync(0xffffffffu, remv, w) | (1ull << bit);
-                    // the kept row itself must not be revisited
-                    if (lane == w) remv |= (1ull << bit);
+                if (cur == ~0ull) continue;
+                const int r0 = w << 6;
+                const unsigned long long dlo = S.mask[w * K7_NMS_PITCH + r0 + lane];
+                const unsigned long long dhi = S.mask[w * K7_NMS_PITCH + r0 + 32 + lane];
+                unsigned long long keptm = 0ull;
+#pragma unroll 8
+                for (int r = 0; r < 64; ++r) {
+                    const unsigned long long d = __shfl_sync(0xffffffffu, r < 32 ? dlo : dhi, r & 31);
+                    if (!((cur >> r) & 1ull)) {   // warp-uniform
+                        keptm |= 1ull << r;
+                        cur |= d;
+                    }
                 }
+                int nk = __popcll(keptm);
+                if (kc + nk > budget) {   // keep only the first (budget - kc) rows of the block
+                    nk = budget - kc;
+                    unsigned long long t = keptm, first = 0ull;
+                    for (int i = 0; i < nk; ++i) {
+                        first |= t & (~t + 1ull);
+                        t &= t - 1ull;
+                    }
+                    keptm = first;
+                }
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = lane + 32 * h;
+                    if ((keptm >> r) & 1ull) S.kept_rows[kc + __popcll(keptm & ((1ull << r) - 1ull))] = r0 + r;
+                }
+                if (lane > w && lane < nw) {
+                    unsigned long long k = keptm;
+                    while (k) {
+                        const int r = __ffsll((long long)k) - 1;
+                        k &= k - 1ull;
+                        remv |= S.mask[lane * K7_NMS_PITCH + r0 + r];
+                    }
+                }
+                kc += nk;
             }
             if (lane == 0) S.kcount = kc;
         }
@@ -473,7 +548,16 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
 union K7SortNmsSmem {
     K7SortSmem sort;
     K7NmsSmem nms;
+    unsigned long long bitonic[K7_BITONIC_MAX];
 };
+
+__device__ __forceinline__ uint64_t* k7_block_sort(uint64_t* a, uint64_t* b, int n, K7SortNmsSmem& S) {
+    if (n <= K7_BITONIC_MAX) {
+        k7_block_bitonic_sort(a, b, n, S.bitonic);
+        return b;
+    }
+    return k7_block_radix_sort(a, b, n, S.sort);
+}
 
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
 k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int32_t* __restrict__ surv_count,
@@ -510,7 +594,7 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
         __syncthreads();
     }
 
-    uint64_t* sorted = k7_block_radix_sort(keys0 + ob, keys1 + ob, n_all, S.sort);
+    uint64_t* sorted = k7_block_sort(keys0 + ob, keys1 + ob, n_all, S);
     int n = n_all;
     if (pre_topk > 0 && n > pre_topk) n = pre_topk;
     const int max_keep = max_det > 0 ? max_det : 0x7fffffff;
@@ -674,7 +758,7 @@ k7_nms_single_kernel(int n, float iou_thr, uint64_t* __restrict__ keys0, uint64_
                      int64_t* __restrict__ keep, int32_t* __restrict__ count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
-    uint64_t* sorted = k7_block_radix_sort(keys0, keys1, n, S.sort);
+    uint64_t* sorted = k7_block_sort(keys0, keys1, n, S);
     const int kept = k7_block_nms(sorted, n, boxes, iou_thr, 0x7fffffff, kept_key, kept_box, S.nms);
     __syncthreads();
     for (int k = threadIdx.x; k < kept; k += K7_NMS_THREADS) keep[k] = (int64_t)(uint32_t)(kept_key[k] & 0xffffffffull);

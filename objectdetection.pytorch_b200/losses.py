@@ -47,8 +47,10 @@ _WS = _Workspace()
 
 
 def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
-          box_order: int = L.BOX_XYXY, debug: bool = False):
-    """Assignment stage.  Returns (assign[B, A(+pad)] int32, num_pos[B] int32[, iou_max, argmax])."""
+          box_order: int = L.BOX_XYXY, debug: bool = False, zero_fill: Optional[torch.Tensor] = None):
+    """Assignment stage.  Returns (assign[B, A(+pad)] int32, num_pos[B] int32[, iou_max, argmax]).
+    zero_fill: optional [B,A,4] float32 tensor the kernel fills with zeros on the way (the d(reg)
+    buffer of the loss stage that follows)."""
     L.require_cuda(annotations)
     ann = L.as_f32_contig(annotations)
     B, M = ann.shape[0], ann.shape[1]
@@ -69,15 +71,16 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
     with torch.cuda.device(dev):
         L.check(L.lib().k7_match(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
                                  L.ptr(ann), B, A, M, C.byref(p), L.ptr(assign), L.ptr(num_pos),
-                                 L.ptr(iou_max), L.ptr(argmax), L.stream_ptr(dev)), "k7_match")
+                                 L.ptr(iou_max), L.ptr(argmax), L.ptr(zero_fill), L.stream_ptr(dev)), "k7_match")
     if debug:
         return assign, num_pos, iou_max, argmax
     return assign, num_pos
 
 
 def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
-               mean_divisor, want_grad, box_order=L.BOX_XYXY):
-    """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None)."""
+               mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None):
+    """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
+    dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a memset pass)."""
     B, A, Cn = cls.shape
     M = ann.shape[1]
     dev = cls.device
@@ -93,8 +96,11 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     per_image = torch.empty((B, 2), dtype=torch.float32, device=dev)
     sums = torch.empty(4, dtype=torch.float32, device=dev)
     dcls = torch.empty_like(cls) if want_grad else None
-    dreg = torch.empty_like(reg) if want_grad else None
+    dreg = None
+    if want_grad:
+        dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
     p = L.K7LossParams()
+    p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
     p.alpha, p.beta = alpha, beta
     for i in range(4):
         p.target_div[i] = target_div[i]
@@ -112,7 +118,8 @@ class _FocalLossFn(torch.autograd.Function):
     def forward(ctx, cls, reg, anchors, ann, cfg):
         want_grad = cls.requires_grad or reg.requires_grad
         A = cls.shape[1]
-        assign, num_pos = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"])
+        dreg0 = torch.empty_like(reg) if want_grad else None
+        assign, num_pos = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
         group = cfg.get("process_group")
         world = 1
         if group is not None or cfg.get("sharded"):
@@ -122,7 +129,7 @@ class _FocalLossFn(torch.autograd.Function):
         per_image, sums, dcls, dreg = loss_stage(
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
-            want_grad=want_grad, box_order=cfg["box_order"])
+            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0)
         if world > 1:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective

@@ -67,7 +67,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layout_matches_header():
     # sizes the C compiler gives (include/k7det.h); a mismatch would corrupt every call
     assert C.sizeof(L.K7AnchorSpec) == 6 * 4 + 8 * 4 * 2 + 9 * 4 + 4 + 8 * 8 + 8 * 16 * 4 * 8
-    assert C.sizeof(L.K7LossParams) == 32
+    assert C.sizeof(L.K7LossParams) == 36
     assert C.sizeof(L.K7DecodeParams) == 48
     assert C.sizeof(L.K7DetectParams) == 64
 
