@@ -99,9 +99,14 @@ struct K7DetectWs {
     int32_t* label;         // [B][A] arg-max class of each survivor, by anchor id
     uint64_t* kept_key;     // [B][A] sort key of each kept box, in keep order
     float4* kept_box;       // [B][A]
+    int32_t* nsel;          // [B] survivors handled by the multi-SM NMS path (-1: fallback image)
+    float4* sbox;           // [B][NCAP] boxes in sorted order
+    unsigned long long* M;  // [B][NCAP][NCAP/64] upper-triangular suppression bitmask
     size_t bytes;
     int W32;
 };
+#define K7_NCAP 2048
+#define K7_NCAP_WORDS (K7_NCAP / 64)
 
 static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     K7DetectWs w;
@@ -124,6 +129,9 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.label = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * BA));
     w.kept_key = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.kept_box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
+    w.nsel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * K7_NCAP));
+    w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * K7_NCAP * K7_NCAP_WORDS));
     w.bytes = o;
     return w;
 }
@@ -560,7 +568,7 @@ __device__ __forceinline__ uint64_t* k7_block_sort(uint64_t* a, uint64_t* b, int
 }
 
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int32_t* __restrict__ surv_count,
+k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int skip_upto, int32_t* __restrict__ surv_count,
                    int32_t* __restrict__ kept_count, const uint32_t* __restrict__ bits, int32_t* __restrict__ wprefix,
                    uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws,
                    uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, int32_t* __restrict__ counts_out) {
@@ -569,6 +577,7 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
     __shared__ int s_carry;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n_all = surv_count[b];
+    if (n_all <= skip_upto) return;   // handled by the multi-SM path
     const size_t ob = (size_t)b * A;
 
     // exclusive popcount prefix over the survivor bitmap: rank of an anchor in the thresholded list
@@ -604,6 +613,222 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
         if (counts_out) {
             counts_out[2 * b + 0] = n_all;
             counts_out[2 * b + 1] = kept;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ multi-SM NMS for n <= K7_NCAP survivors
+// Round-1 profile: with one CTA per image the IoU bitmask (n^2/2 pair tests) and the greedy scan
+// ran on 64 of 148 SMs and took longer than streaming the whole classification tensor.  For the
+// usual case (a few hundred to 2048 survivors per image) the work is split into three kernels so
+// every SM takes part and the only serial piece is one warp per image:
+//   k7_sort_kernel   per image: survivor ranks (bitmap prefix), key sort, boxes gathered in order
+//   k7_mask_kernel   grid (G, B): 64x64 blocks of the LOWER-triangular suppression bitmask (row i: the
+//                    higher-scored boxes j < i with IoU > thr), written to global memory (L2 resident)
+//   k7_resolve_kernel  one CTA per image: greedy NMS as a parallel fixed point over that bitmask
+// Images with more survivors fall back to k7_sort_nms_kernel (chunked, bitmask in shared memory).
+union K7SortOnlySmem {
+    K7SortSmem sort;
+    unsigned long long bitonic[K7_BITONIC_MAX];
+};
+
+// nsel[b] = number of sorted survivors the mask/scan kernels must process, or -1 (fallback image)
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_sort_kernel(int A, int W32, int pre_topk, const int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
+               int32_t* __restrict__ wprefix, uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1,
+               const float4* __restrict__ box_ws, float4* __restrict__ sbox, int32_t* __restrict__ nsel) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    K7SortOnlySmem& S = *reinterpret_cast<K7SortOnlySmem*>(smem_raw);
+    __shared__ int s_carry;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_all = surv_count[b];
+    if (n_all > K7_NCAP) {
+        if (tid == 0) nsel[b] = -1;
+        return;
+    }
+    const size_t ob = (size_t)b * A;
+    // exclusive popcount prefix over the survivor bitmap: rank of an anchor in the thresholded list
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
+        const int w = w0 + tid;
+        const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) S.sort.wtot[warp] = (unsigned)inc;
+        __syncthreads();
+        int woff = 0;
+        for (int k = 0; k < warp; ++k) woff += (int)S.sort.wtot[k];
+        const int carry = s_carry;
+        if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
+        __syncthreads();
+        if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
+        __syncthreads();
+    }
+    k7_block_bitonic_sort(keys0 + ob, keys1 + ob, n_all, S.bitonic);   // n_all <= K7_NCAP <= K7_BITONIC_MAX
+    int n = n_all;
+    if (pre_topk > 0 && n > pre_topk) n = pre_topk;
+    for (int i = tid; i < n; i += K7_NMS_THREADS)
+        sbox[(size_t)b * K7_NCAP + i] = __ldg(box_ws + ob + (uint32_t)(keys1[ob + i] & 0xffffffffull));
+    if (tid == 0) nsel[b] = n;
+}
+
+// The exact decision of torchvision.ops.nms, inter / (area_i + area_j - inter) > thr, without the
+// IEEE division for the clear cases: fl(thr * u) carries 2^-24 relative error, so outside a
+// 2^-20 band around it the comparison of the quotient is decided; inside the band (or for a
+// degenerate union) the division is done.
+__device__ __forceinline__ bool k7_nms_suppress_fast(const K7Box& a, float area_a, const float4 b, float area_b,
+                                                     float thr, float thr_lo, float thr_hi) {
+    const float w = K7_FSUB(fminf(a.x2, b.z), fmaxf(a.x1, b.x));
+    const float h = K7_FSUB(fminf(a.y2, b.w), fmaxf(a.y1, b.y));
+    const bool ok = (w > 0.0f) && (h > 0.0f);   // else inter == 0 (or NaN): quotient 0 or NaN, never > thr >= 0
+    const float inter = K7_FMUL(w, h);
+    const float u = K7_FSUB(K7_FADD(area_a, area_b), inter);
+    const bool hi = inter > K7_FMUL(thr_hi, u), lo = inter < K7_FMUL(thr_lo, u);
+    bool res = ok && hi;
+    if (ok && !((hi || lo) && u > 1e-30f && thr_lo > 1e-6f)) res = K7_FDIV(inter, u) > thr;   // rare: ambiguous band
+    return res;
+}
+
+#define K7_MASK_THREADS 256
+__global__ void __launch_bounds__(K7_MASK_THREADS)
+k7_mask_kernel(float thr, const int32_t* __restrict__ nsel, const float4* __restrict__ sbox,
+               unsigned long long* __restrict__ M) {
+    __shared__ float4 cbox[K7_MASK_THREADS / 64][64];
+    __shared__ float carea[K7_MASK_THREADS / 64][64];
+    const int b = blockIdx.y;
+    const int n = nsel[b];
+    if (n <= 0) return;
+    const int nw = (n + 63) >> 6;
+    const int pairs = nw * (nw + 1) / 2;
+    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
+    const int groups = gridDim.x * (K7_MASK_THREADS / 64);
+    const float thr_lo = thr * (1.0f - 9.5367431640625e-7f), thr_hi = thr * (1.0f + 9.5367431640625e-7f);
+    const float4* bx = sbox + (size_t)b * K7_NCAP;
+    for (int p0 = blockIdx.x * (K7_MASK_THREADS / 64); p0 < pairs; p0 += groups) {   // block-uniform trip count
+        int p = p0 + grp, rb = 0;
+        const bool live = p < pairs;
+        if (live)
+            while (p > rb) {   // row-block rb owns words 0..rb (the boxes that come BEFORE its rows)
+                p -= rb + 1;
+                ++rb;
+            }
+        const int w = p, col = w * 64 + t;   // p is now the word index inside row-block rb: w <= rb
+        __syncthreads();
+        if (live && col < n) {
+            const float4 c = __ldg(bx + col);
+            cbox[grp][t] = c;
+            carea[grp][t] = k7_area(c.x, c.y, c.z, c.w);
+        }
+        __syncthreads();
+        const int row = rb * 64 + t;
+        if (live && row < n) {
+            const float4 mb = __ldg(bx + row);
+            const K7Box me = {mb.x, mb.y, mb.z, mb.w};
+            const float marea = k7_area(mb.x, mb.y, mb.z, mb.w);
+            unsigned long long word = 0ull;
+            const int jend = min(64, row - w * 64);   // columns j < row only
+#pragma unroll 4
+            for (int j = 0; j < jend; ++j)
+                word |= (unsigned long long)k7_nms_suppress_fast(me, marea, cbox[grp][j], carea[grp][j], thr, thr_lo, thr_hi) << j;
+            M[((size_t)b * K7_NCAP + row) * K7_NCAP_WORDS + w] = word;
+        }
+    }
+}
+
+// Greedy NMS as a fixed point, one CTA per image.  M[i] holds the boxes j < i (higher score) that
+// overlap box i above the threshold.  Box i is REMOVED as soon as one of them is known KEPT, and
+// KEPT as soon as all of them are known removed; the lowest undecided box can always be decided,
+// so the iteration ends, and by induction over i its result is exactly the sequential greedy
+// answer of torchvision.ops.nms.  The kept/removed sets only grow, so threads may read them
+// while others update them; a round costs one barrier.  Dependency chains between overlapping
+// boxes are short, so a handful of rounds replace the n-step sequential scan.
+#define K7_RESOLVE_THREADS 1024
+__global__ void __launch_bounds__(K7_RESOLVE_THREADS)
+k7_resolve_kernel(int A, int max_det, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
+                  const uint64_t* __restrict__ sorted_keys, const float4* __restrict__ sbox,
+                  const unsigned long long* __restrict__ M, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
+                  int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out) {
+    __shared__ unsigned long long s_kept[K7_NCAP_WORDS], s_rem[K7_NCAP_WORDS];
+    __shared__ int s_prefix[K7_NCAP_WORDS + 1];
+    __shared__ int s_undecided;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n = nsel[b];
+    if (n < 0) return;   // fallback image
+    const size_t ob = (size_t)b * A;
+    const unsigned long long* Mb = M + (size_t)b * K7_NCAP * K7_NCAP_WORDS;
+    if (tid < K7_NCAP_WORDS) s_kept[tid] = s_rem[tid] = 0ull;
+    constexpr int PER = K7_NCAP / K7_RESOLVE_THREADS;
+    bool open_[PER];
+#pragma unroll
+    for (int k = 0; k < PER; ++k) open_[k] = tid + k * K7_RESOLVE_THREADS < n;
+    for (int round = 0; round < K7_NCAP; ++round) {
+        if (tid == 0) s_undecided = 0;
+        __syncthreads();
+        bool still = false;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            if (!open_[k]) continue;
+            const int i = tid + k * K7_RESOLVE_THREADS;
+            const int wi = i >> 6;
+            const unsigned long long* row = Mb + (size_t)i * K7_NCAP_WORDS;
+            bool any_kept = false, all_removed = true;
+            for (int w = 0; w <= wi; ++w) {
+                const unsigned long long l = __ldg(row + w);
+                const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
+                const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
+                any_kept |= (l & kp) != 0ull;
+                all_removed &= (l & ~rm) == 0ull;
+            }
+            if (any_kept) {
+                atomicOr(&s_rem[wi], 1ull << (i & 63));
+                open_[k] = false;
+            } else if (all_removed) {
+                atomicOr(&s_kept[wi], 1ull << (i & 63));
+                open_[k] = false;
+            } else {
+                still = true;
+            }
+        }
+        if (still) s_undecided = 1;
+        __syncthreads();
+        if (s_undecided == 0) break;
+        __syncthreads();
+    }
+    // compact the kept set in sorted order
+    if (tid == 0) {
+        int run = 0;
+        for (int w = 0; w < K7_NCAP_WORDS; ++w) {
+            s_prefix[w] = run;
+            run += __popcll(s_kept[w]);
+        }
+        s_prefix[K7_NCAP_WORDS] = run;
+    }
+    __syncthreads();
+    const int budget = max_det > 0 ? max_det : 0x7fffffff;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+        const int i = tid + k * K7_RESOLVE_THREADS;
+        if (i >= n) continue;
+        const unsigned long long kw = s_kept[i >> 6];
+        if (!((kw >> (i & 63)) & 1ull)) continue;
+        const int pos = s_prefix[i >> 6] + __popcll(kw & ((1ull << (i & 63)) - 1ull));
+        if (pos >= budget) continue;
+        const uint64_t key = sorted_keys[ob + i];
+        kept_key[ob + pos] = key;
+        kept_box[ob + pos] = sbox[(size_t)b * K7_NCAP + i];
+        if (keep_idx_out) keep_idx_out[pos] = (int64_t)(uint32_t)(key & 0xffffffffull);
+    }
+    if (tid == 0) {
+        const int kc = min(s_prefix[K7_NCAP_WORDS], budget);
+        kept_count[b] = kc;
+        if (counts_out) {
+            counts_out[2 * b + 0] = surv_count[b];
+            counts_out[2 * b + 1] = kc;
         }
     }
 }
@@ -691,11 +916,32 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
                   : k7_score_launch<1, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
     if (rc) return rc;
 
-    const size_t smem = sizeof(K7SortNmsSmem);
-    K7_CUDA(cudaFuncSetAttribute(k7_sort_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk, params->max_detections,
-                                                        w.surv_count, w.kept_count, w.bits, w.wprefix, w.keys0, w.keys1, w.box,
-                                                        w.kept_key, w.kept_box, counts);
+    // NMS: images with <= K7_NCAP survivors go through sort -> mask (all SMs) -> scan (one warp each),
+    // the others through the chunked single-CTA kernel.  Each kernel decides per image on the device.
+    {
+        const size_t smem_sort = sizeof(K7SortOnlySmem);
+        K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
+        k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.surv_count, w.bits, w.wprefix,
+                                                             w.keys0, w.keys1, w.box, w.sbox, w.nsel);
+        K7_LAUNCH_CHECK();
+        int gx = (4 * k7_sm_count() + B - 1) / B;   // about four CTAs per SM over the batch
+        const int gx_max = (K7_NCAP_WORDS * (K7_NCAP_WORDS + 1) / 2 + 3) / 4;
+        if (gx > gx_max) gx = gx_max;
+        if (gx < 1) gx = 1;
+        k7_mask_kernel<<<dim3(gx, B), K7_MASK_THREADS, 0, st>>>(params->iou_thr, w.nsel, w.sbox, w.M);
+        K7_LAUNCH_CHECK();
+        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, 0, st>>>(A, params->max_detections, w.nsel, w.surv_count, w.keys1, w.sbox, w.M,
+                                         w.kept_key, w.kept_box, w.kept_count, counts, nullptr);
+        K7_LAUNCH_CHECK();
+    }
+    if (A > K7_NCAP) {   // an image can exceed the cap only then
+        const size_t smem = sizeof(K7SortNmsSmem);
+        K7_CUDA(cudaFuncSetAttribute(k7_sort_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk,
+                                                            params->max_detections, K7_NCAP, w.surv_count, w.kept_count,
+                                                            w.bits, w.wprefix, w.keys0, w.keys1, w.box, w.kept_key,
+                                                            w.kept_box, counts);
+    }
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
@@ -726,6 +972,9 @@ struct K7NmsWs {
     uint64_t* keys1;
     uint64_t* kept_key;
     float4* kept_box;
+    int32_t* small;            // {n, nsel, kept_count}
+    float4* sbox;              // multi-SM path (n <= K7_NCAP)
+    unsigned long long* M;
     size_t bytes;
 };
 static K7NmsWs k7_nms_ws(void* base, int n) {
@@ -742,13 +991,22 @@ static K7NmsWs k7_nms_ws(void* base, int n) {
     w.keys1 = reinterpret_cast<uint64_t*>(take(8 * nn));
     w.kept_key = reinterpret_cast<uint64_t*>(take(8 * nn));
     w.kept_box = reinterpret_cast<float4*>(take(16 * nn));
+    w.small = reinterpret_cast<int32_t*>(take(64));
+    w.sbox = w.kept_box;
+    w.M = nullptr;
+    if (n <= K7_NCAP) {
+        w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * K7_NCAP));
+        w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)K7_NCAP * K7_NCAP_WORDS));
+    }
     w.bytes = o;
     return w;
 }
 extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_nms_ws(nullptr, n).bytes; }
 
-__global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys) {
+__global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys,
+                                   int32_t* __restrict__ n_dev) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *n_dev = n;
     if (i < n) keys[i] = ((uint64_t)k7_score_key_desc(scores[i]) << 32) | (uint32_t)i;
 }
 
@@ -782,8 +1040,24 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
         k7_set_error("k7_nms: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
         return K7_EWORKSPACE;
     }
-    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0);
+    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.small);
     K7_LAUNCH_CHECK();
+    if (n <= K7_NCAP) {   // sort -> bitmask on all SMs -> one-warp scan (same kernels as k7_detect, B = 1)
+        const float4* b4 = reinterpret_cast<const float4*>(boxes);
+        const size_t smem_sort = sizeof(K7SortOnlySmem);
+        K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
+        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.small, nullptr, nullptr, w.keys0, w.keys1, b4, w.sbox,
+                                                             w.small + 1);
+        K7_LAUNCH_CHECK();
+        const int nwords = (n + 63) / 64;
+        int gx = (nwords * (nwords + 1) / 2 + 3) / 4;
+        k7_mask_kernel<<<dim3(gx, 1), K7_MASK_THREADS, 0, st>>>(iou_thr, w.small + 1, w.sbox, w.M);
+        K7_LAUNCH_CHECK();
+        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, 0, st>>>(n, 0, w.small + 1, w.small, w.keys1, w.sbox, w.M, w.kept_key, w.kept_box, count,
+                                         nullptr, keep);
+        K7_LAUNCH_CHECK();
+        return K7_OK;
+    }
     const size_t smem = sizeof(K7SortNmsSmem);
     K7_CUDA(cudaFuncSetAttribute(k7_nms_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k7_nms_single_kernel<<<1, K7_NMS_THREADS, smem, st>>>(n, iou_thr, w.keys0, w.keys1, reinterpret_cast<const float4*>(boxes),

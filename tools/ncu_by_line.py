@@ -43,7 +43,10 @@ def main():
         tot += n
         ts += sm
     print(f"total executed {tot}, samples {ts}")
-    for loc, n in per_line.most_common(60):
+    by_samples = len(sys.argv) > 5 and sys.argv[5] == 'samples'
+    order = per_line_s.most_common(40) if by_samples else per_line.most_common(60)
+    for loc, _ in order:
+        n = per_line[loc]
         print(f"{str(loc):40s} exec {n:11d} {100*n/tot:5.1f}%   samples {100*per_line_s[loc]/max(ts,1):5.1f}%")
 
 
