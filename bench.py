@@ -58,6 +58,21 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
 
 
+def ncu_traffic(workload, batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the committed
+    `ncu --set full` capture of this workload (profiles/traffic.json); None if there is none."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            t = json.load(f)
+        e = t.get(workload)
+        if e and e.get("batch") == batch:
+            return e["k7_loss_pipe_kernel_grad_bytes"]
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -261,9 +276,9 @@ def run_b200(args, wl):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
-        "gpu_launches": 9 * args.steps,
-        "launches_per_step": {"k7_match": 1, "k7_loss(scales+stream+finalize)": 3, "k7_scale_inplace": 2,
-                              "k7_detect(score+sort_nms)": 2, "k7_detect_gather": 1},
+        "gpu_launches": 12 * args.steps,
+        "launches_per_step": {"k7_match": 1, "k7_loss(scales+pipe+finalize)": 3, "k7_scale_inplace": 2,
+                              "k7_detect(score+sort+mask+resolve+fallback)": 5, "k7_detect_gather": 1},
     }
 
     # ---- parts and the roofline of the dominant kernel (every rank runs them; rank 0 reports)
@@ -276,7 +291,9 @@ def run_b200(args, wl):
     assign, num_pos = BL.match(anc, ann, A, 0.35, 0.45)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
     ms_match = timed(lambda: BL.match(anc, ann, A, 0.35, 0.45), k, 3)
-    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, **kw), k, 3)
+    dreg0 = torch.zeros_like(reg)     # what k7_match(zero_fill4=) hands over in the module path
+    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0, **kw),
+                    k, 3)
     ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, **kw), k, 3)
     surv = int(eval_side(sync=True).survivors.sum())
     bytes_fwd = B * (A * (4 * C + 16) + 20 * M)
@@ -295,8 +312,9 @@ def run_b200(args, wl):
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
     ach = gbs(bytes_fb, ms_k_fb)
-    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_kernel<grad> (k7_loss call: scales + stream + finalize)",
-                       "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: scales + pipe + finalize)",
+                       "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                       "traffic": ncu_traffic(wl.name, B),
                        "algorithmic_bytes_per_launch": bytes_fb, "avg_launch_ms": ms_k_fb, "peak_source": peak_src}
 
     # ---- e2e: pinned host inputs -> H2D -> public modules -> D2H of the results, every step
