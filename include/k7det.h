@@ -96,7 +96,10 @@ typedef struct K7MatchParams {
 #define K7_STATE_NEG 0
 #define K7_STATE_IGNORE 1
 #define K7_STATE_POS 2
-/* assign word: bits 0-1 = state, bits 2-31 = annotation row index (0..M-1) of the arg-max GT */
+/* assign word: bits 0-1 = state, bits 2-31 = annotation row index (0..M-1) of the arg-max GT.
+ * The row is the reference's IoU_argmax for POSITIVE anchors (the only ones the reference uses it
+ * for, losses.py:94-97, 125); for the others it is exact only when iou_max/argmax are requested
+ * (without them the kernel skips ground-truth boxes that provably stay below neg_thr). */
 #define K7_ASSIGN_STATE(w) ((w) & 3)
 #define K7_ASSIGN_ROW(w) ((int32_t)((uint32_t)(w) >> 2))
 

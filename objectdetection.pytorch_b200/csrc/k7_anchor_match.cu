@@ -15,6 +15,8 @@
 // None of this changes a result bit: skipped pairs have IoU == 0, the running maximum starts at
 // (0, index 0) and is only replaced on a strictly greater value, which is torch.max's
 // first-index-on-ties rule (verified against the reference in tests/golden).
+#include <string.h>
+
 #include "k7_common.cuh"
 
 // ------------------------------------------------------------------ anchors
@@ -42,19 +44,67 @@ extern "C" int k7_anchors_materialize(const K7AnchorSpec* spec, float* out, void
 // ------------------------------------------------------------------ match
 #define K7_MATCH_THREADS 256
 
-template <bool FROM_SPEC>
+// Host-computed helpers for the spec path: exact divisions by multiply-shift, and per level the
+// extremes of the in-cell anchor shapes (used by the culling bound below).
+struct K7MatchAux {
+    K7FastDiv div_k;                      // / cell_anchors
+    K7FastDiv div_fw[K7_MAX_LEVELS];      // / fw[level]
+    float amin[K7_MAX_LEVELS], amax[K7_MAX_LEVELS];   // smallest / largest anchor area of the level
+    float wmax[K7_MAX_LEVELS], hmax[K7_MAX_LEVELS];   // largest anchor width / height of the level
+};
+
+__device__ __forceinline__ int k7_level_of(const K7AnchorSpec& s, int a) {
+    int l = 0;
+#pragma unroll
+    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+        if (i < s.num_levels && a >= s.offset[i]) l = i;
+    return l;
+}
+
+// k7_anchor_from_spec with the three integer divisions done by multiply-shift
+__device__ __forceinline__ void k7_anchor_fast(const K7AnchorSpec& s, const K7MatchAux& x, int a, int l, float& x1,
+                                               float& y1, float& x2, float& y2) {
+    const uint32_t r = (uint32_t)(a - s.offset[l]);
+    const uint32_t cell = k7_div(r, x.div_k);
+    const int k = (int)(r - cell * (uint32_t)s.cell_anchors);
+    const uint32_t yy = k7_div(cell, x.div_fw[l]);
+    const uint32_t xx = cell - yy * (uint32_t)s.fw[l];
+    const double st = s.stride[l];
+    const double sx = __dmul_rn(__dadd_rn((double)xx, 0.5), st);
+    const double sy = __dmul_rn(__dadd_rn((double)yy, 0.5), st);
+    const double* b = s.base[l][k];
+    if (s.box_order == K7_BOX_XYXY) {
+        x1 = __double2float_rn(__dadd_rn(b[0], sx));
+        y1 = __double2float_rn(__dadd_rn(b[1], sy));
+        x2 = __double2float_rn(__dadd_rn(b[2], sx));
+        y2 = __double2float_rn(__dadd_rn(b[3], sy));
+    } else {
+        y1 = __double2float_rn(__dadd_rn(b[0], sy));
+        x1 = __double2float_rn(__dadd_rn(b[1], sx));
+        y2 = __double2float_rn(__dadd_rn(b[2], sy));
+        x2 = __double2float_rn(__dadd_rn(b[3], sx));
+    }
+}
+
+// One CTA = one image x a strided set of 256-anchor chunks, so the annotation rows are compacted
+// once per CTA and reused.  CULL (production mode, no debug outputs): a GT can only change an
+// anchor's state or a positive's arg-max if IoU >= neg_thr, which needs
+//     neg_thr * area_a <= area_g <= area_a / neg_thr        and
+//     inter_ub * (1 + neg_thr) >= neg_thr * (area_a + area_g),
+// inter_ub = min(overlap_x(hull, g), wmax) * min(overlap_y(hull, g), hmax) >= inter(a, g) for every
+// anchor a of the warp (a lies inside the hull).  Both are tested with a 1e-4 relative margin
+// (float rounding is 1e-7), so no pair that reaches the threshold is ever skipped and the state /
+// positive arg-max stay bit-exact; only the (unused) arg-max of negative anchors is unspecified.
+template <bool FROM_SPEC, bool CULL>
 __global__ void __launch_bounds__(K7_MATCH_THREADS)
-k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
-                const float* __restrict__ annotations, int A, int M, float neg_thr, float pos_thr,
-                int32_t* __restrict__ assign, int32_t* __restrict__ num_pos, float* __restrict__ iou_max_out,
-                int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4) {
+k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7MatchAux aux,
+                const float* __restrict__ anchors, int box_order, const float* __restrict__ annotations, int A, int M,
+                float neg_thr, float pos_thr, int32_t* __restrict__ assign, int32_t* __restrict__ num_pos,
+                float* __restrict__ iou_max_out, int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4) {
     extern __shared__ float smem[];
-    // SoA of the valid GT rows: x1 | y1 | x2 | y2 | area | row (as int)
-    float* gx1 = smem;
-    float* gy1 = gx1 + M;
-    float* gx2 = gy1 + M;
-    float* gy2 = gx2 + M;
-    float* gar = gy2 + M;
+    // valid GT rows: (x1,y1,x2,y2) as float4 | area | row (as int)
+    float4* gbox = reinterpret_cast<float4*>(smem);
+    float* gar = smem + 4 * M;
     int* grow = reinterpret_cast<int*>(gar + M);
     __shared__ int s_valid;
     __shared__ int s_pos[K7_MATCH_THREADS / 32];
@@ -77,7 +127,7 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
             const unsigned bal = __ballot_sync(0xffffffffu, ok);
             if (ok) {
                 const int p = base + __popc(bal & ((1u << lane) - 1u));
-                gx1[p] = r0; gy1[p] = r1; gx2[p] = r2; gy2[p] = r3;
+                gbox[p] = make_float4(r0, r1, r2, r3);
                 gar[p] = k7_area(r0, r1, r2, r3);
                 grow[p] = m;
             }
@@ -87,65 +137,138 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
     }
     __syncthreads();
     const int nv = s_valid;
+    const float c_lo = neg_thr * (1.0f - 1e-4f);                      // area window / bound, with margin
+    const float c_in = neg_thr / (1.0f + neg_thr) * (1.0f - 1e-4f);
+    int pos_total = 0;
 
-    const int a = blockIdx.x * K7_MATCH_THREADS + threadIdx.x;
-    const bool live = a < A;
-    float ax1 = 0.f, ay1 = 0.f, ax2 = 0.f, ay2 = 0.f;
-    if (live) k7_anchor<FROM_SPEC>(spec, anchors, box_order, a, ax1, ay1, ax2, ay2);
-    const float area_a = k7_area(ax1, ay1, ax2, ay2);
-
-    float best = 0.0f;
-    int besti = 0;
-    if (nv > 0) {
-        // hull of the warp's anchors (dead lanes contribute an empty hull)
-        float hx1 = live ? ax1 : 3.0e38f, hy1 = live ? ay1 : 3.0e38f;
-        float hx2 = live ? ax2 : -3.0e38f, hy2 = live ? ay2 : -3.0e38f;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            hx1 = fminf(hx1, __shfl_xor_sync(0xffffffffu, hx1, o));
-            hy1 = fminf(hy1, __shfl_xor_sync(0xffffffffu, hy1, o));
-            hx2 = fmaxf(hx2, __shfl_xor_sync(0xffffffffu, hx2, o));
-            hy2 = fmaxf(hy2, __shfl_xor_sync(0xffffffffu, hy2, o));
+    for (int a0 = blockIdx.x * K7_MATCH_THREADS; a0 < A; a0 += gridDim.x * K7_MATCH_THREADS) {
+        const int a = a0 + threadIdx.x;
+        const bool live = a < A;
+        float ax1 = 0.f, ay1 = 0.f, ax2 = 0.f, ay2 = 0.f;
+        int lvl = 0;
+        if (live) {
+            if (FROM_SPEC) {
+                lvl = k7_level_of(spec, a);
+                k7_anchor_fast(spec, aux, a, lvl, ax1, ay1, ax2, ay2);
+            } else {
+                k7_anchor_from_tensor(anchors, box_order, a, ax1, ay1, ax2, ay2);
+            }
         }
-        for (int g0 = 0; g0 < nv; g0 += 32) {
-            const int g = g0 + lane;
-            bool cand = false;
-            if (g < nv) cand = (gx2[g] > hx1) && (gx1[g] < hx2) && (gy2[g] > hy1) && (gy1[g] < hy2);
-            unsigned cm = __ballot_sync(0xffffffffu, cand);
-            while (cm) {
-                const int j = g0 + __ffs(cm) - 1;
-                cm &= cm - 1;
-                const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, area_a, gx1[j], gy1[j], gx2[j], gy2[j], gar[j]);
-                if (iou > best) {
-                    best = iou;
-                    besti = j;
+        const float area_a = k7_area(ax1, ay1, ax2, ay2);
+
+        float best = 0.0f;
+        int besti = 0;
+        if (nv > 0) {
+            // hull of the warp's anchors (dead lanes contribute an empty hull)
+            float hx1 = live ? ax1 : 3.0e38f, hy1 = live ? ay1 : 3.0e38f;
+            float hx2 = live ? ax2 : -3.0e38f, hy2 = live ? ay2 : -3.0e38f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                hx1 = fminf(hx1, __shfl_xor_sync(0xffffffffu, hx1, o));
+                hy1 = fminf(hy1, __shfl_xor_sync(0xffffffffu, hy1, o));
+                hx2 = fmaxf(hx2, __shfl_xor_sync(0xffffffffu, hx2, o));
+                hy2 = fmaxf(hy2, __shfl_xor_sync(0xffffffffu, hy2, o));
+            }
+            float amin = 0.f, amax = 3.0e38f, wmax = 3.0e38f, hmax = 3.0e38f;
+            if (CULL) {
+                if (FROM_SPEC) {
+                    // a warp's anchors lie in at most two adjacent levels: those of its first and last lane
+                    const int l0 = __shfl_sync(0xffffffffu, lvl, 0);
+                    const int l1 = k7_level_of(spec, min(a0 + (warp << 5) + 31, A - 1));
+                    amin = fminf(aux.amin[l0], aux.amin[l1]);
+                    amax = fmaxf(aux.amax[l0], aux.amax[l1]);
+                    wmax = fmaxf(aux.wmax[l0], aux.wmax[l1]);
+                    hmax = fmaxf(aux.hmax[l0], aux.hmax[l1]);
+                } else {
+                    amin = live ? area_a : 3.0e38f;
+                    amax = live ? area_a : 0.0f;
+                    wmax = live ? ax2 - ax1 : 0.0f;
+                    hmax = live ? ay2 - ay1 : 0.0f;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        amin = fminf(amin, __shfl_xor_sync(0xffffffffu, amin, o));
+                        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                        wmax = fmaxf(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+                        hmax = fmaxf(hmax, __shfl_xor_sync(0xffffffffu, hmax, o));
+                    }
+                }
+            }
+            for (int g0 = 0; g0 < nv; g0 += 32) {
+                const int g = g0 + lane;
+                bool cand = false;
+                if (g < nv) {
+                    const float4 gb = gbox[g];
+                    const float ow = fminf(hx2, gb.z) - fmaxf(hx1, gb.x), oh = fminf(hy2, gb.w) - fmaxf(hy1, gb.y);
+                    cand = (ow > 0.0f) && (oh > 0.0f);
+                    if (CULL) {
+                        const float ag = gar[g];
+                        const float ub = fminf(ow, wmax) * fminf(oh, hmax);
+                        cand = cand && (ag >= c_lo * amin) && (ag * c_lo <= amax) && (ub >= c_in * (amin + ag));
+                    }
+                }
+                unsigned cm = __ballot_sync(0xffffffffu, cand);
+                while (cm) {
+                    const int j = g0 + __ffs(cm) - 1;
+                    cm &= cm - 1;
+                    const float4 gb = gbox[j];
+                    const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, area_a, gb.x, gb.y, gb.z, gb.w, gar[j]);
+                    if (iou > best) {
+                        best = iou;
+                        besti = j;
+                    }
                 }
             }
         }
+
+        int state = K7_STATE_IGNORE;
+        if (nv > 0) {
+            if (best < neg_thr) state = K7_STATE_NEG;
+            if (best >= pos_thr) state = K7_STATE_POS;
+        }
+        if (live) {
+            const size_t o = (size_t)b * A + a;
+            const int row = nv > 0 ? grow[besti] : 0;
+            assign[o] = (row << 2) | state;
+            if (iou_max_out) iou_max_out[o] = best;
+            if (argmax_out) argmax_out[o] = nv > 0 ? besti : -1;
+            if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        pos_total += (live && state == K7_STATE_POS) ? 1 : 0;
     }
 
-    int state = K7_STATE_IGNORE;
-    if (nv > 0) {
-        if (best < neg_thr) state = K7_STATE_NEG;
-        if (best >= pos_thr) state = K7_STATE_POS;
-    }
-    const bool pos = live && state == K7_STATE_POS;
-    if (live) {
-        const size_t o = (size_t)b * A + a;
-        const int row = nv > 0 ? grow[besti] : 0;
-        assign[o] = (row << 2) | state;
-        if (iou_max_out) iou_max_out[o] = best;
-        if (argmax_out) argmax_out[o] = nv > 0 ? besti : -1;
-        if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    const unsigned pb = __ballot_sync(0xffffffffu, pos);
-    if (lane == 0) s_pos[warp] = __popc(pb);
+    pos_total = k7_warp_sum(pos_total);
+    if (lane == 0) s_pos[warp] = pos_total;
     __syncthreads();
     if (threadIdx.x == 0) {
         int t = 0;
 #pragma unroll
         for (int w = 0; w < K7_MATCH_THREADS / 32; ++w) t += s_pos[w];
         if (t) atomicAdd(num_pos + b, t);   // integer: order independent, exact
+    }
+}
+
+static void k7_match_aux(const K7AnchorSpec* s, K7MatchAux* x) {
+    memset(x, 0, sizeof(*x));
+    x->div_k = k7_fastdiv_make((uint32_t)s->cell_anchors);
+    for (int l = 0; l < s->num_levels; ++l) {
+        x->div_fw[l] = k7_fastdiv_make((uint32_t)(s->fw[l] > 0 ? s->fw[l] : 1));
+        double amin = 1e300, amax = 0, wmax = 0, hmax = 0;
+        for (int k = 0; k < s->cell_anchors; ++k) {
+            const double* b = s->base[l][k];
+            // extents are the same for both storage orders up to naming; take both and keep the extremes
+            const double d0 = b[2] - b[0], d1 = b[3] - b[1];
+            const double w = s->box_order == K7_BOX_XYXY ? d0 : d1, h = s->box_order == K7_BOX_XYXY ? d1 : d0;
+            const double ar = w * h;
+            if (ar < amin) amin = ar;
+            if (ar > amax) amax = ar;
+            if (w > wmax) wmax = w;
+            if (h > hmax) hmax = h;
+        }
+        // outward rounding: the device compares float areas of float-rounded anchors against these
+        x->amin[l] = (float)(amin * (1.0 - 1e-5));
+        x->amax[l] = (float)(amax * (1.0 + 1e-5));
+        x->wmax[l] = (float)(wmax * (1.0 + 1e-5) + 1e-3);
+        x->hmax[l] = (float)(hmax * (1.0 + 1e-5) + 1e-3);
     }
 }
 
@@ -158,9 +281,13 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     K7_REQUIRE(M < (1 << 29), "k7_match: M too large");
     K7_REQUIRE(B <= 65535, "k7_match: B > 65535 not supported");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(zero_fill4) & 15) == 0, "k7_match: zero_fill4 must be 16-byte aligned");
+    K7MatchAux aux;
+    memset(&aux, 0, sizeof(aux));
     if (spec) {
         int rc = k7_check_spec(spec, A);
         if (rc) return rc;
+        k7_match_aux(spec, &aux);
+        box_order = spec->box_order;
     } else {
         K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_match: anchors must be 16-byte aligned");
         K7_REQUIRE(box_order == K7_BOX_XYXY || box_order == K7_BOX_YXYX, "k7_match: bad box_order");
@@ -169,21 +296,28 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     const size_t smem = (size_t)M * 6 * sizeof(float);
     K7_REQUIRE(smem <= 200 * 1024, "k7_match: M=%d annotation rows exceed shared memory", M);
     K7_CUDA(cudaMemsetAsync(num_pos, 0, sizeof(int32_t) * B, st));
-    dim3 grid((A + K7_MATCH_THREADS - 1) / K7_MATCH_THREADS, B);
+    const int chunks = (A + K7_MATCH_THREADS - 1) / K7_MATCH_THREADS;
+    int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
+    if (gx > chunks) gx = chunks;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, B);
+    // the exact arg-max of every anchor is only needed for the debug outputs; thresholds outside (0,1) disable culling
+    const bool cull = !iou_max && !argmax && params->neg_thr > 1e-3f && params->neg_thr < 1.0f &&
+                      params->pos_thr >= params->neg_thr;
     static const K7AnchorSpec kEmpty = {};
-    if (spec) {
-        if (smem > 48 * 1024)
-            K7_CUDA(cudaFuncSetAttribute(k7_match_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k7_match_kernel<true><<<grid, K7_MATCH_THREADS, smem, st>>>(*spec, nullptr, spec->box_order, annotations, A, M,
-                                                                    params->neg_thr, params->pos_thr, assign, num_pos,
-                                                                    iou_max, argmax, reinterpret_cast<float4*>(zero_fill4));
-    } else {
-        if (smem > 48 * 1024)
-            K7_CUDA(cudaFuncSetAttribute(k7_match_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k7_match_kernel<false><<<grid, K7_MATCH_THREADS, smem, st>>>(kEmpty, anchors, box_order, annotations, A, M,
-                                                                     params->neg_thr, params->pos_thr, assign, num_pos,
-                                                                     iou_max, argmax, reinterpret_cast<float4*>(zero_fill4));
-    }
+    const K7AnchorSpec& sp = spec ? *spec : kEmpty;
+#define K7_MATCH_LAUNCH(SP, CU)                                                                                          \
+    do {                                                                                                                 \
+        auto kern = k7_match_kernel<SP, CU>;                                                                             \
+        if (smem > 48 * 1024)                                                                                            \
+            K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                 \
+        kern<<<grid, K7_MATCH_THREADS, smem, st>>>(sp, aux, anchors, box_order, annotations, A, M, params->neg_thr,      \
+                                                   params->pos_thr, assign, num_pos, iou_max, argmax,                    \
+                                                   reinterpret_cast<float4*>(zero_fill4));                               \
+    } while (0)
+    if (spec) { if (cull) K7_MATCH_LAUNCH(true, true); else K7_MATCH_LAUNCH(true, false); }
+    else      { if (cull) K7_MATCH_LAUNCH(false, true); else K7_MATCH_LAUNCH(false, false); }
+#undef K7_MATCH_LAUNCH
     K7_LAUNCH_CHECK();
     return K7_OK;
 }

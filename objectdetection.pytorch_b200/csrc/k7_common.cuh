@@ -37,6 +37,23 @@ int k7_sm_count();
 
 static inline size_t k7_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// ------------------------------------------------------------------ division by a runtime constant
+struct K7FastDiv {
+    uint32_t m, sh;
+};
+// exact x / d for x < 2^31 (Granlund-Montgomery, round-up multiplier)
+static inline K7FastDiv k7_fastdiv_make(uint32_t d) {
+    int s = 0;
+    while ((1ull << s) < d) ++s;
+    K7FastDiv f;
+    f.m = (uint32_t)(((1ull << (31 + s)) + d - 1) / d);
+    f.sh = (uint32_t)(31 + s);
+    return f;
+}
+__device__ __forceinline__ uint32_t k7_div(uint32_t x, const K7FastDiv f) {
+    return (uint32_t)(((uint64_t)x * f.m) >> f.sh);
+}
+
 // ------------------------------------------------------------------ anchors on the fly
 // Anchor `a` of the recipe, returned as (x1,y1,x2,y2) whatever the recipe's storage order.
 // float64 arithmetic then ONE rounding to float32, exactly like

@@ -45,22 +45,6 @@
 #define K7_LOSS_MAX_WARPS 16
 #define K7_LOSS_TILE 1024   // floats per tile
 
-struct K7FastDiv {
-    uint32_t m, sh;
-};
-// exact x / d for x < 2^31 (Granlund-Montgomery, round-up multiplier)
-static K7FastDiv k7_fastdiv_make(uint32_t d) {
-    int s = 0;
-    while ((1ull << s) < d) ++s;
-    K7FastDiv f;
-    f.m = (uint32_t)(((1ull << (31 + s)) + d - 1) / d);
-    f.sh = (uint32_t)(31 + s);
-    return f;
-}
-__device__ __forceinline__ uint32_t k7_div(uint32_t x, const K7FastDiv f) {
-    return (uint32_t)(((uint64_t)x * f.m) >> f.sh);
-}
-
 struct K7LossDev {
     float alpha, one_m_alpha;
     float beta, quad, shift;

@@ -80,6 +80,27 @@ def test_match_bit_exact(path, from_spec):
 
 @pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
 @pytest.mark.parametrize("path", LOSS, ids=IDS)
+def test_match_production_mode_bit_exact(path, from_spec):
+    """Without the debug outputs the kernel culls ground-truth boxes that provably stay below neg_thr:
+    states, num_pos and the GT row of every POSITIVE anchor must still be the reference's."""
+    g, yx, anc = load_loss_case(path, from_spec)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    thr = (0.4, 0.5) if yx else (0.35, 0.45)
+    A = g["anchors"].shape[1]
+    B = ann.shape[0]
+    zf = torch.full((B, A, 4), 7.0, device=DEV)
+    assign, num_pos = BL.match(anc, ann, A, thr[0], thr[1], L.BOX_YXYX if yx else L.BOX_XYXY, zero_fill=zf)
+    aw = assign[:B * A].view(B, A).cpu().numpy()
+    state, row = aw & 3, aw >> 2
+    assert np.array_equal(state, g["state"])
+    pos = g["state"] == 2
+    assert np.array_equal(row[pos], g["gt_row"][pos])
+    assert np.array_equal(num_pos.cpu().numpy(), pos.sum(1))
+    assert float(zf.abs().sum()) == 0.0          # the d(reg) buffer was zero-filled on the way
+
+
+@pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
+@pytest.mark.parametrize("path", LOSS, ids=IDS)
 def test_focal_loss_and_grads(path, from_spec):
     g, yx, anc = load_loss_case(path, from_spec)
     cls = torch.from_numpy(g["classifications"]).to(DEV).requires_grad_(True)
