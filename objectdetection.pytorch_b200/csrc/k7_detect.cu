@@ -97,6 +97,7 @@ struct K7DetectWs {
     uint64_t* keys1;        // [B][A]
     float4* box;            // [B][A] decoded+clipped box of each survivor, by anchor id
     int32_t* label;         // [B][A] arg-max class of each survivor, by anchor id
+    float* score;           // [B][A] class maximum of each survivor, by anchor id
     uint64_t* kept_key;     // [B][A] sort key of each kept box, in keep order
     float4* kept_box;       // [B][A]
     int32_t* nsel;          // [B] survivors handled by the multi-SM NMS path (-1: fallback image)
@@ -127,6 +128,7 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.keys1 = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
     w.label = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * BA));
+    w.score = reinterpret_cast<float*>(take(sizeof(float) * BA));
     w.kept_key = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.kept_box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
     w.nsel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
@@ -162,8 +164,8 @@ __global__ void __launch_bounds__(K7_SCORE_MAX_THREADS, 1)
 k7_score_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
                 const float* __restrict__ cls, const float4* __restrict__ reg, int B, int A,
                 const __grid_constant__ K7DetectParams P, const __grid_constant__ K7StreamGeom G,
-                int32_t* __restrict__ surv_count, uint32_t* __restrict__ bits, int W32, uint64_t* __restrict__ keys,
-                float4* __restrict__ box_ws, int32_t* __restrict__ label_ws) {
+                uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws, int32_t* __restrict__ label_ws,
+                float* __restrict__ score_ws) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages;
@@ -248,20 +250,7 @@ k7_score_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
             const long long R = row0 + r;
             const int b = owner ? (int)(R / A) : 0;
             const int a = owner ? (int)(R - (long long)b * A) : 0;
-            // slot allocation: one atomic per (warp, image); a tile touches at most two images
-            const int b_first = (int)(row0 / A);
-            const unsigned own0 = __ballot_sync(0xffffffffu, owner && b == b_first);
-            const unsigned own1 = __ballot_sync(0xffffffffu, owner && b != b_first);
-            int base0 = 0, base1 = 0;
-            if (lane == 0) {
-                if (own0) base0 = atomicAdd(surv_count + b_first, __popc(own0));
-                if (own1) base1 = atomicAdd(surv_count + b_first + 1, __popc(own1));
-            }
-            base0 = __shfl_sync(0xffffffffu, base0, 0);
-            base1 = __shfl_sync(0xffffffffu, base1, 0);
             if (owner) {
-                const unsigned lt = (1u << lane) - 1u;
-                const int slot = (b == b_first) ? base0 + __popc(own0 & lt) : base1 + __popc(own1 & lt);
                 float ax1, ay1, ax2, ay2;
                 k7_anchor<FROM_SPEC>(spec, anchors, box_order, a, ax1, ay1, ax2, ay2);
                 const float4 d = __ldg(reg + R);
@@ -272,12 +261,263 @@ k7_score_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restri
                 const size_t oa = (size_t)b * A + a;
                 box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
                 label_ws[oa] = lab;
-                keys[(size_t)b * A + slot] = ((uint64_t)k7_score_key_desc(m) << 32) | (uint32_t)a;
+                score_ws[oa] = m;
                 atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
             }
         }
         __syncwarp();
     }
+}
+
+// ------------------------------------------------------------------ kernel 1, pipelined (A*C % 4 == 0)
+// Same warp-specialised TMA pipeline as k7_loss_pipe_kernel (producer warp + 16 consumer warps,
+// 32 KB stages, flat tiles that ignore row boundaries), with an even lighter consumer: a row
+// survives iff ANY of its elements exceeds the threshold, so the flat pass is LDS.128 + three
+// max + one compare per float4.  Every element above the threshold is a REPORT: the warp takes the
+// report's row from the tile in shared memory, reduces its maximum and FIRST arg-max, and the
+// report that sits exactly on the arg-max element queues the survivor - every surviving row has
+// exactly one such element, so there is no duplicate and no atomic slot allocation.  The queue
+// (shared memory, per warp) is drained at the end, one survivor per lane: anchor, regression
+// deltas, decode + clip, and the records by anchor id (bitmap bit, score, label, box) from which
+// k7_sort_kernel later ranks the survivors.  Nothing with a long latency sits between a stage
+// becoming full and its release.
+struct K7ScoreGeom {
+    uint32_t AC, tile_f, tpi, num_tiles;
+    K7FastDiv div_c, div_tpi;
+    uint32_t stage_stride, off_desc, off_bars, off_queue;
+    int stages, cw, grid;
+    size_t smem_bytes;
+};
+struct K7ScoreDesc {
+    uint32_t n, b, off, pad;
+};
+#define K7_SPIPE_SLICE 512
+#define K7_SPIPE_MAX_CW 16
+#define K7_SPIPE_QCAP 96    // queued survivors per consumer warp
+
+template <bool FROM_SPEC>
+__global__ void __launch_bounds__((K7_SPIPE_MAX_CW + 1) * 32, 1)
+k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
+                     const float* __restrict__ cls, const float4* __restrict__ reg, int A, int C,
+                     const __grid_constant__ K7DetectParams P, const __grid_constant__ K7ScoreGeom G,
+                     uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws, int32_t* __restrict__ label_ws,
+                     float* __restrict__ score_ws) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int NS = G.stages, CW = G.cw;
+    constexpr int SL = K7_SPIPE_SLICE;
+    K7ScoreDesc* desc = reinterpret_cast<K7ScoreDesc*>(smem + G.off_desc);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + G.off_bars);
+    uint64_t* done = full + NS;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; ++s) {
+            k7_mbar_init(full + s, 1);
+            k7_mbar_init(done + s, (uint32_t)CW);
+        }
+        k7_fence_mbar_init();
+        k7_fence_proxy_async();
+    }
+    __syncthreads();
+    if (blockIdx.x >= G.num_tiles) return;
+    const uint32_t ntl = (G.num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+    if (warp == CW) {   // ---------------------------------------------------------------- producer
+        if (lane != 0) return;
+        auto load = [&](const uint32_t j) {
+            const uint32_t g = blockIdx.x + j * gridDim.x;
+            const int s = (int)(j % (uint32_t)NS);
+            K7ScoreDesc d;
+            d.b = k7_div(g, G.div_tpi);
+            d.off = (g - d.b * G.tpi) * G.tile_f;
+            d.n = min(G.tile_f, G.AC - d.off);
+            d.pad = 0;
+            desc[s] = d;
+            k7_mbar_expect_tx(full + s, d.n * 4u);
+            k7_bulk_g2s(smem + (size_t)s * G.stage_stride, cls + (size_t)d.b * G.AC + d.off, d.n * 4u, full + s);
+        };
+        uint32_t jl = 0;
+        for (; jl < ntl && jl < (uint32_t)NS; ++jl) load(jl);
+        int s = 0;
+        uint32_t phase = 0;
+        for (uint32_t j = 0; j < ntl; ++j) {
+            k7_mbar_wait(done + s, phase);
+            if (jl < ntl) load(jl++);
+            if (++s == NS) {
+                s = 0;
+                phase ^= 1u;
+            }
+        }
+        return;
+    }
+    if (warp > CW) return;
+
+    // ------------------------------------------------------------------------------------ consumers
+    const float thr = P.score_thr;
+    const uint32_t full_u32 = k7_smem_u32(full), done_u32 = k7_smem_u32(done);
+    const int i_lo = warp * SL;
+    // queue entry: x = image (bit 31: row still unresolved), y = anchor (or element index inside the
+    // image when unresolved), z = label, w = score bits
+    uint4* queue = reinterpret_cast<uint4*>(smem + G.off_queue) + warp * K7_SPIPE_QCAP;
+    int qn = 0;
+
+    // Deferred emission, one queue entry per lane: anchor, regression deltas, decode + clip, and the
+    // by-anchor records.  Unresolved entries (rows straddling two tiles) first take their row from
+    // global memory.
+    auto drain = [&]() {
+        __syncwarp();
+        for (int base = 0; base < qn; base += 32) {
+            if (base + lane >= qn) continue;
+            const uint4 ent = queue[base + lane];
+            const uint32_t b = ent.x & 0x7fffffffu;
+            uint32_t a = ent.y;
+            int idx = (int)ent.z;
+            float m = __uint_as_float(ent.w);
+            if (ent.x >> 31) {
+                a = k7_div(ent.y, G.div_c);
+                const int c = (int)(ent.y - a * (uint32_t)C);
+                const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
+                m = -INFINITY;
+                idx = 0;
+#pragma unroll 8
+                for (int q = 0; q < C; ++q) {
+                    const float v = __ldg(row + q);
+                    if (v > m) {
+                        m = v;
+                        idx = q;
+                    }
+                }
+                if (idx != c) continue;
+            }
+            float ax1, ay1, ax2, ay2;
+            k7_anchor<FROM_SPEC>(spec, anchors, box_order, (int)a, ax1, ay1, ax2, ay2);
+            const size_t oa = (size_t)b * A + a;
+            const float4 dl = __ldg(reg + oa);
+            K7Box o = (P.decode.variant == K7_DECODE_RETINA)
+                          ? k7_decode_retina(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w, P.decode.mean, P.decode.std)
+                          : k7_decode_effdet(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w);
+            if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
+            box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
+            label_ws[oa] = idx;
+            score_ws[oa] = m;
+            atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
+        }
+        __syncwarp();
+        qn = 0;
+    };
+
+    int s = -1;
+    uint32_t phase = 1u;
+    for (uint32_t j = 0; j < ntl; ++j) {
+        if (++s == NS) s = 0;
+        if (s == 0) phase ^= 1u;
+        const float* tile = reinterpret_cast<const float*>(smem + (size_t)s * G.stage_stride);
+        k7_mbar_wait_u32(full_u32 + 8u * s, phase);
+        const uint4 d = *reinterpret_cast<const uint4*>(desc + s);   // n, b, off
+        const int n = (int)d.x;
+        if (i_lo < n) {
+            const int len = min(n - i_lo, SL), n4 = len >> 2;
+            const float4* t4 = reinterpret_cast<const float4*>(tile + i_lo);
+            uint32_t hits = 0u;   // bit k: float4 lane+32k holds an element above the threshold
+            if (n4 == SL / 4) {
+#pragma unroll
+                for (int k = 0; k < SL / 128; ++k) {
+                    const float4 v = t4[lane + 32 * k];
+                    if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) > thr) hits |= 1u << k;
+                }
+            } else {
+                for (int k = 0; lane + 32 * k < n4; ++k) {
+                    const float4 v = t4[lane + 32 * k];
+                    if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) > thr) hits |= 1u << k;
+                }
+            }
+            if (__any_sync(0xffffffffu, hits != 0u)) {   // ~1 slice in 10
+                // Every element above the threshold is a report.  The warp resolves it at once from the
+                // tile: class maximum and FIRST arg-max of its row (torch.max, retinanet.py:300,316);
+                // the report that sits on the arg-max element queues the survivor.
+                for (int k = 0; k < SL / 128; ++k) {
+                    const bool mine = (hits >> k) & 1u;
+                    if (!__any_sync(0xffffffffu, mine)) continue;
+                    float v[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                    if (mine) {
+                        const float4 t = t4[lane + 32 * k];
+                        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        unsigned mb = __ballot_sync(0xffffffffu, v[e] > thr);
+                        while (mb) {
+                            const int src = __ffs(mb) - 1;
+                            mb &= mb - 1;
+                            const int i = i_lo + 4 * (src + 32 * k) + e;      // tile-local element index
+                            const uint32_t ge = d.z + (uint32_t)i;            // element index inside the image
+                            const uint32_t a = k7_div(ge, G.div_c);
+                            const int c = (int)(ge - a * (uint32_t)C);
+                            const int i0 = i - c;                             // tile-local index of the row's class 0
+                            if (qn == K7_SPIPE_QCAP) drain();
+                            if (i0 < 0 || i0 + C > n) {                       // row straddles two tiles: resolve later
+                                if (lane == 0) queue[qn] = make_uint4(d.y | 0x80000000u, ge, 0u, 0u);
+                                ++qn;
+                                continue;
+                            }
+                            const float* row = tile + i0;
+                            float m = -INFINITY;
+                            int idx = 0x7fffffff;
+                            for (int q = lane; q < C; q += 32) {
+                                const float x = row[q];
+                                if (x > m) {
+                                    m = x;
+                                    idx = q;
+                                }
+                            }
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) {
+                                const float om = __shfl_xor_sync(0xffffffffu, m, o);
+                                const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+                                if (om > m || (om == m && oi < idx)) {
+                                    m = om;
+                                    idx = oi;
+                                }
+                            }
+                            if (idx != c) continue;   // warp-uniform
+                            if (lane == 0) queue[qn] = make_uint4(d.y, a, (uint32_t)idx, __float_as_uint(m));
+                            ++qn;
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) k7_mbar_arrive_u32(done_u32 + 8u * s);
+    }
+    drain();
+}
+
+static int k7_score_geometry(int B, int A, int C, K7ScoreGeom* g) {
+    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
+    K7_REQUIRE(ac < (1ull << 30), "k7_detect: A*C=%llu per image is too large", ac);
+    g->AC = (uint32_t)ac;
+    g->cw = K7_SPIPE_MAX_CW;
+    g->tile_f = (uint32_t)g->cw * K7_SPIPE_SLICE;
+    g->tpi = (uint32_t)((ac + g->tile_f - 1) / g->tile_f);
+    const unsigned long long nt = (unsigned long long)B * g->tpi;
+    K7_REQUIRE(nt < (1ull << 31), "k7_detect: %llu tiles exceed the 32-bit tile index", nt);
+    g->num_tiles = (uint32_t)nt;
+    g->div_c = k7_fastdiv_make((uint32_t)C);
+    g->div_tpi = k7_fastdiv_make(g->tpi);
+    g->stage_stride = g->tile_f * 4;
+    g->stages = 6;
+    size_t o = (size_t)g->stages * g->stage_stride;
+    g->off_desc = (uint32_t)o;
+    o += (size_t)g->stages * sizeof(K7ScoreDesc);
+    g->off_bars = (uint32_t)o;
+    o += (size_t)g->stages * 16;
+    g->off_queue = (uint32_t)o;
+    o += (size_t)g->cw * K7_SPIPE_QCAP * sizeof(uint4);
+    g->smem_bytes = o;
+    int grid = k7_sm_count();
+    if (nt < (unsigned long long)grid) grid = (int)nt;
+    g->grid = grid < 1 ? 1 : grid;
+    return K7_OK;
 }
 
 // ------------------------------------------------------------------ kernel 2: per-image sort + NMS
@@ -374,13 +614,9 @@ __device__ uint64_t* k7_block_radix_sort(uint64_t* a, uint64_t* b, int n, K7Sort
 // anchor id), result written to `out`.  ~log2(N)^2/2 barrier-separated steps; for the usual few
 // hundred to few thousand survivors per image this replaces six to eight radix passes.
 #define K7_BITONIC_MAX 4096
-__device__ void k7_block_bitonic_sort(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int n,
-                                      unsigned long long* sk) {
+// sorts sk[0..N) ascending; N = power of two >= 64, entries beyond the n real keys hold ~0
+__device__ void k7_bitonic_sort_smem(unsigned long long* sk, int N) {
     const int tid = threadIdx.x;
-    int N = 64;
-    while (N < n) N <<= 1;
-    for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < n) ? in[i] : ~0ull;
-    __syncthreads();
     for (int k = 2; k <= N; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int t = tid; t < (N >> 1); t += K7_NMS_THREADS) {
@@ -397,6 +633,19 @@ __device__ void k7_block_bitonic_sort(const uint64_t* __restrict__ in, uint64_t*
             __syncthreads();
         }
     }
+}
+__device__ __forceinline__ int k7_bitonic_size(int n) {
+    int N = 64;
+    while (N < n) N <<= 1;
+    return N;
+}
+__device__ void k7_block_bitonic_sort(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int n,
+                                      unsigned long long* sk) {
+    const int tid = threadIdx.x;
+    const int N = k7_bitonic_size(n);
+    for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < n) ? in[i] : ~0ull;
+    __syncthreads();
+    k7_bitonic_sort_smem(sk, N);
     for (int i = tid; i < n; i += K7_NMS_THREADS) out[i] = sk[i];
     __syncthreads();
 }
@@ -632,48 +881,86 @@ union K7SortOnlySmem {
     unsigned long long bitonic[K7_BITONIC_MAX];
 };
 
-// nsel[b] = number of sorted survivors the mask/scan kernels must process, or -1 (fallback image)
+// Per image: the survivor list is born here.  The score kernel only marked survivors in a bitmap
+// (and left score / label / box by anchor id); this kernel takes the exclusive popcount prefix of
+// the bitmap (= the index torchvision.ops.nms would return for each survivor), turns every set bit
+// into a 64-bit key (score descending | anchor ascending) and sorts.
+//   bits == nullptr: stand-alone NMS, keys0 already holds surv_count[b] keys.
+// Outputs: surv_count[b]; nsel[b] = survivors the mask/resolve kernels must process, or -1 when the
+// image has more than K7_NCAP of them (then its unsorted keys are left in keys0 for the fallback).
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_sort_kernel(int A, int W32, int pre_topk, const int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
-               int32_t* __restrict__ wprefix, uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1,
-               const float4* __restrict__ box_ws, float4* __restrict__ sbox, int32_t* __restrict__ nsel) {
+k7_sort_kernel(int A, int W32, int pre_topk, int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
+               int32_t* __restrict__ wprefix, const float* __restrict__ score_ws, uint64_t* __restrict__ keys0,
+               uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws, float4* __restrict__ sbox,
+               int32_t* __restrict__ nsel) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     K7SortOnlySmem& S = *reinterpret_cast<K7SortOnlySmem*>(smem_raw);
     __shared__ int s_carry;
+    __shared__ unsigned int s_wtot[32];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n_all = surv_count[b];
-    if (n_all > K7_NCAP) {
+    const size_t ob = (size_t)b * A;
+    int n_all;
+    if (bits) {
+        // exclusive popcount prefix over the survivor bitmap
+        if (tid == 0) s_carry = 0;
+        __syncthreads();
+        for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
+            const int w = w0 + tid;
+            const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            if (lane == 31) s_wtot[warp] = (unsigned)inc;
+            __syncthreads();
+            int woff = 0;
+            for (int k = 0; k < warp; ++k) woff += (int)s_wtot[k];
+            const int carry = s_carry;
+            if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
+            __syncthreads();
+            if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
+            __syncthreads();
+        }
+        n_all = s_carry;
+        if (tid == 0) surv_count[b] = n_all;
+    } else {
+        n_all = surv_count[b];
+    }
+    const bool small = n_all <= K7_NCAP;
+    const int N = k7_bitonic_size(n_all);
+    if (bits) {
+        // one key per set bit, written at its rank: shared memory (small image) or keys0 (fallback image)
+        for (int w = tid; w < W32; w += K7_NMS_THREADS) {
+            uint32_t word = bits[(size_t)b * W32 + w];
+            int slot = wprefix[(size_t)b * W32 + w];
+            while (word) {
+                const int a = (w << 5) + __ffs(word) - 1;
+                word &= word - 1;
+                const uint64_t key = ((uint64_t)k7_score_key_desc(score_ws[ob + a]) << 32) | (uint32_t)a;
+                if (small) S.bitonic[slot] = key; else keys0[ob + slot] = key;
+                ++slot;
+            }
+        }
+        if (small)
+            for (int i = n_all + tid; i < N; i += K7_NMS_THREADS) S.bitonic[i] = ~0ull;
+    } else if (small) {
+        for (int i = tid; i < N; i += K7_NMS_THREADS) S.bitonic[i] = (i < n_all) ? keys0[ob + i] : ~0ull;
+    }
+    if (!small) {
         if (tid == 0) nsel[b] = -1;
         return;
     }
-    const size_t ob = (size_t)b * A;
-    // exclusive popcount prefix over the survivor bitmap: rank of an anchor in the thresholded list
-    if (tid == 0) s_carry = 0;
     __syncthreads();
-    for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
-        const int w = w0 + tid;
-        const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
-        int inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) S.sort.wtot[warp] = (unsigned)inc;
-        __syncthreads();
-        int woff = 0;
-        for (int k = 0; k < warp; ++k) woff += (int)S.sort.wtot[k];
-        const int carry = s_carry;
-        if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
-        __syncthreads();
-        if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
-        __syncthreads();
-    }
-    k7_block_bitonic_sort(keys0 + ob, keys1 + ob, n_all, S.bitonic);   // n_all <= K7_NCAP <= K7_BITONIC_MAX
+    k7_bitonic_sort_smem(S.bitonic, N);
     int n = n_all;
     if (pre_topk > 0 && n > pre_topk) n = pre_topk;
-    for (int i = tid; i < n; i += K7_NMS_THREADS)
-        sbox[(size_t)b * K7_NCAP + i] = __ldg(box_ws + ob + (uint32_t)(keys1[ob + i] & 0xffffffffull));
+    for (int i = tid; i < n; i += K7_NMS_THREADS) {
+        const uint64_t key = S.bitonic[i];
+        keys1[ob + i] = key;
+        sbox[(size_t)b * K7_NCAP + i] = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
+    }
     if (tid == 0) nsel[b] = n;
 }
 
@@ -865,7 +1152,7 @@ static int k7_score_launch(const K7AnchorSpec& spec, const float* anchors, int b
     auto kern = k7_score_kernel<VEC, FROM_SPEC>;
     K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
     kern<<<G.grid, G.warps * 32, G.smem_bytes, st>>>(spec, anchors, box_order, cls, reinterpret_cast<const float4*>(reg), B, A,
-                                                     P, G, w.surv_count, w.bits, w.W32, w.keys0, w.box, w.label);
+                                                     P, G, w.bits, w.W32, w.box, w.label, w.score);
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
@@ -875,7 +1162,7 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
                          size_t workspace_bytes, void* stream) {
     K7_REQUIRE(cls && reg && params && workspace, "k7_detect: null argument");
     K7_REQUIRE(spec || anchors, "k7_detect: need an anchor spec or an anchor tensor");
-    K7_REQUIRE(B > 0 && A >= 32 && C > 0, "k7_detect: bad shape B=%d A=%d C=%d (A >= 32 required)", B, A, C);
+    K7_REQUIRE(B > 0 && A > 0 && C > 0, "k7_detect: bad shape B=%d A=%d C=%d", B, A, C);
     K7_REQUIRE(params->iou_thr >= 0.0f, "k7_detect: iou_thr must be >= 0");
     K7_REQUIRE(params->decode.variant == K7_DECODE_RETINA || params->decode.variant == K7_DECODE_EFFDET,
                "k7_detect: bad decode variant");
@@ -896,25 +1183,43 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
         return K7_EWORKSPACE;
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    K7StreamGeom G;
-    int rc = k7_stream_geometry((long long)B * A, A, C, 0, 3, K7_SCORE_MAX_THREADS / 32, &G);
-    if (rc) return rc;
-
     // surv_count, kept_count and the bitmap are contiguous at the start of the workspace
     K7_CUDA(cudaMemsetAsync(w.surv_count, 0, (size_t)(reinterpret_cast<unsigned char*>(w.wprefix) -
                                                       reinterpret_cast<unsigned char*>(w.surv_count)), st));
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-    if (G.vec == 4)
-        rc = spec ? k7_score_launch<4, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                  : k7_score_launch<4, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-    else if (G.vec == 2)
-        rc = spec ? k7_score_launch<2, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                  : k7_score_launch<2, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-    else
-        rc = spec ? k7_score_launch<1, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                  : k7_score_launch<1, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-    if (rc) return rc;
+    int rc;
+    if ((((unsigned long long)A * C) % 4ull) == 0ull) {
+        K7ScoreGeom GS;
+        rc = k7_score_geometry(B, A, C, &GS);
+        if (rc) return rc;
+#define K7_SPIPE_LAUNCH(SP)                                                                                              \
+    do {                                                                                                                 \
+        auto kern = k7_score_pipe_kernel<SP>;                                                                            \
+        K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS.smem_bytes));            \
+        kern<<<GS.grid, (GS.cw + 1) * 32, GS.smem_bytes, st>>>(sp, anchors, box_order, cls,                              \
+                                                               reinterpret_cast<const float4*>(reg), A, C, *params, GS,  \
+                                                               w.bits, w.W32, w.box, w.label, w.score);                  \
+    } while (0)
+        if (spec) K7_SPIPE_LAUNCH(true); else K7_SPIPE_LAUNCH(false);
+#undef K7_SPIPE_LAUNCH
+        K7_LAUNCH_CHECK();
+    } else {
+        K7_REQUIRE(A >= 32, "k7_detect: A >= 32 required when A*C is not a multiple of 4 (A=%d)", A);
+        K7StreamGeom G;
+        rc = k7_stream_geometry((long long)B * A, A, C, 0, 3, K7_SCORE_MAX_THREADS / 32, &G);
+        if (rc) return rc;
+        if (G.vec == 4)
+            rc = spec ? k7_score_launch<4, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                      : k7_score_launch<4, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+        else if (G.vec == 2)
+            rc = spec ? k7_score_launch<2, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                      : k7_score_launch<2, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+        else
+            rc = spec ? k7_score_launch<1, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
+                      : k7_score_launch<1, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
+        if (rc) return rc;
+    }
 
     // NMS: images with <= K7_NCAP survivors go through sort -> mask (all SMs) -> scan (one warp each),
     // the others through the chunked single-CTA kernel.  Each kernel decides per image on the device.
@@ -922,7 +1227,7 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
         const size_t smem_sort = sizeof(K7SortOnlySmem);
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
         k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.surv_count, w.bits, w.wprefix,
-                                                             w.keys0, w.keys1, w.box, w.sbox, w.nsel);
+                                                             w.score, w.keys0, w.keys1, w.box, w.sbox, w.nsel);
         K7_LAUNCH_CHECK();
         int gx = (4 * k7_sm_count() + B - 1) / B;   // about four CTAs per SM over the batch
         const int gx_max = (K7_NCAP_WORDS * (K7_NCAP_WORDS + 1) / 2 + 3) / 4;
@@ -1046,8 +1351,8 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
         const float4* b4 = reinterpret_cast<const float4*>(boxes);
         const size_t smem_sort = sizeof(K7SortOnlySmem);
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.small, nullptr, nullptr, w.keys0, w.keys1, b4, w.sbox,
-                                                             w.small + 1);
+        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.small, nullptr, nullptr, nullptr, w.keys0, w.keys1, b4,
+                                                             w.sbox, w.small + 1);
         K7_LAUNCH_CHECK();
         const int nwords = (n + 63) / 64;
         int gx = (nwords * (nwords + 1) / 2 + 3) / 4;
