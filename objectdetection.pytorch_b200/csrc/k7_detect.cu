@@ -964,20 +964,20 @@ k7_sort_kernel(int A, int W32, int pre_topk, int32_t* __restrict__ surv_count, c
     if (tid == 0) nsel[b] = n;
 }
 
-// The exact decision of torchvision.ops.nms, inter / (area_i + area_j - inter) > thr, without the
-// IEEE division for the clear cases: fl(thr * u) carries 2^-24 relative error, so outside a
-// 2^-20 band around it the comparison of the quotient is decided; inside the band (or for a
-// degenerate union) the division is done.
+// The exact decision of torchvision.ops.nms, inter / (area_i + area_j - inter) > thr, with the IEEE
+// division only for pairs that can reach the threshold: for u > 0, fl(inter/u) > thr implies
+// inter > thr*u*(1 - 2^-24) >= fl(thr_lo*u) with thr_lo = thr*(1 - 2^-20), so a pair failing
+// inter > fl(thr_lo*u) is certainly not suppressed.  Degenerate unions (u <= 0) pass the filter and
+// get the division, NaN fails both, as in the reference.
 __device__ __forceinline__ bool k7_nms_suppress_fast(const K7Box& a, float area_a, const float4 b, float area_b,
-                                                     float thr, float thr_lo, float thr_hi) {
+                                                     float thr, float thr_lo) {
     const float w = K7_FSUB(fminf(a.x2, b.z), fmaxf(a.x1, b.x));
     const float h = K7_FSUB(fminf(a.y2, b.w), fmaxf(a.y1, b.y));
-    const bool ok = (w > 0.0f) && (h > 0.0f);   // else inter == 0 (or NaN): quotient 0 or NaN, never > thr >= 0
     const float inter = K7_FMUL(w, h);
     const float u = K7_FSUB(K7_FADD(area_a, area_b), inter);
-    const bool hi = inter > K7_FMUL(thr_hi, u), lo = inter < K7_FMUL(thr_lo, u);
-    bool res = ok && hi;
-    if (ok && !((hi || lo) && u > 1e-30f && thr_lo > 1e-6f)) res = K7_FDIV(inter, u) > thr;   // rare: ambiguous band
+    bool res = false;
+    // w,h <= 0: inter == 0 (or NaN): quotient 0 or NaN, never > thr >= 0
+    if ((w > 0.0f) && (h > 0.0f) && (inter > K7_FMUL(thr_lo, u))) res = K7_FDIV(inter, u) > thr;   // ~1 pair in 50
     return res;
 }
 
@@ -994,7 +994,7 @@ k7_mask_kernel(float thr, const int32_t* __restrict__ nsel, const float4* __rest
     const int pairs = nw * (nw + 1) / 2;
     const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
     const int groups = gridDim.x * (K7_MASK_THREADS / 64);
-    const float thr_lo = thr * (1.0f - 9.5367431640625e-7f), thr_hi = thr * (1.0f + 9.5367431640625e-7f);
+    const float thr_lo = thr * (1.0f - 9.5367431640625e-7f);
     const float4* bx = sbox + (size_t)b * K7_NCAP;
     for (int p0 = blockIdx.x * (K7_MASK_THREADS / 64); p0 < pairs; p0 += groups) {   // block-uniform trip count
         int p = p0 + grp, rb = 0;
@@ -1021,7 +1021,7 @@ k7_mask_kernel(float thr, const int32_t* __restrict__ nsel, const float4* __rest
             const int jend = min(64, row - w * 64);   // columns j < row only
 #pragma unroll 4
             for (int j = 0; j < jend; ++j)
-                word |= (unsigned long long)k7_nms_suppress_fast(me, marea, cbox[grp][j], carea[grp][j], thr, thr_lo, thr_hi) << j;
+                word |= (unsigned long long)k7_nms_suppress_fast(me, marea, cbox[grp][j], carea[grp][j], thr, thr_lo) << j;
             M[((size_t)b * K7_NCAP + row) * K7_NCAP_WORDS + w] = word;
         }
     }
@@ -1050,9 +1050,26 @@ k7_resolve_kernel(int A, int max_det, const int32_t* __restrict__ nsel, const in
     const unsigned long long* Mb = M + (size_t)b * K7_NCAP * K7_NCAP_WORDS;
     if (tid < K7_NCAP_WORDS) s_kept[tid] = s_rem[tid] = 0ull;
     constexpr int PER = K7_NCAP / K7_RESOLVE_THREADS;
+    // Round 0 reads the whole row once and remembers which of its words are non-zero (most boxes
+    // overlap few higher-scored ones); later rounds only revisit those.
+    uint32_t nz[PER];
     bool open_[PER];
+    __syncthreads();
 #pragma unroll
-    for (int k = 0; k < PER; ++k) open_[k] = tid + k * K7_RESOLVE_THREADS < n;
+    for (int k = 0; k < PER; ++k) {
+        const int i = tid + k * K7_RESOLVE_THREADS;
+        nz[k] = 0u;
+        open_[k] = i < n;
+        if (!open_[k]) continue;
+        const int wi = i >> 6;
+        const unsigned long long* row = Mb + (size_t)i * K7_NCAP_WORDS;
+        for (int w = 0; w <= wi; ++w)
+            if (__ldg(row + w) != 0ull) nz[k] |= 1u << w;
+        if (nz[k] == 0u) {   // nothing above it overlaps: kept
+            atomicOr(&s_kept[wi], 1ull << (i & 63));
+            open_[k] = false;
+        }
+    }
     for (int round = 0; round < K7_NCAP; ++round) {
         if (tid == 0) s_undecided = 0;
         __syncthreads();
@@ -1064,7 +1081,10 @@ k7_resolve_kernel(int A, int max_det, const int32_t* __restrict__ nsel, const in
             const int wi = i >> 6;
             const unsigned long long* row = Mb + (size_t)i * K7_NCAP_WORDS;
             bool any_kept = false, all_removed = true;
-            for (int w = 0; w <= wi; ++w) {
+            uint32_t m = nz[k];
+            while (m) {
+                const int w = __ffs(m) - 1;
+                m &= m - 1;
                 const unsigned long long l = __ldg(row + w);
                 const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
                 const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
