@@ -126,24 +126,31 @@ def cpu_inputs(wl, n_images, seed=0):
     return R, cls, reg, ann, anc
 
 
-def cpu_baseline(wl, budget_s=15.0):
+def cpu_calibrate(wl, hw, n0=4):
+    """Seconds per image of the CPU arm, measured on a warm pass over n0 images."""
+    n0 = min(n0, wl.batch)
+    R, cls, reg, ann, anc = cpu_inputs(wl, n0)
+    cpu_step(R, cls, reg, anc, ann, hw)                       # warm-up (allocator, thread pool)
+    t0 = time.perf_counter()
+    cpu_step(R, cls, reg, anc, ann, hw)
+    return (time.perf_counter() - t0) / n0
+
+
+def cpu_baseline(wl, budget_s=12.0):
     """Oracle port timed on the host cores on a bounded sample of the workload."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    R, cls, reg, ann, anc = cpu_inputs(wl, 1)
     hw = (wl.height, wl.width)
-    cpu_step(R, cls, reg, anc, ann, hw)                       # warm-up
-    t0 = time.perf_counter()
-    cpu_step(R, cls, reg, anc, ann, hw)
-    per_img = time.perf_counter() - t0
+    per_img = cpu_calibrate(wl, hw)
     n = int(max(1, min(wl.batch, budget_s / max(per_img, 1e-6))))
     R, cls, reg, ann, anc = cpu_inputs(wl, n)
+    cpu_step(R, cls, reg, anc, ann, hw)                       # warm pass at this size
     t0 = time.perf_counter()
     cpu_step(R, cls, reg, anc, ann, hw)
     dt = time.perf_counter() - t0
     return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n} of {wl.batch} images of {wl.name}, 1 pass (FocalLoss fwd+bwd + decode/NMS), "
-                      f"torch-CPU oracle port of the reference, {cores} threads"}
+            "sample": f"{n} of {wl.batch} images of {wl.name}, 1 timed pass after 1 warm pass (FocalLoss fwd+bwd + "
+                      f"decode/NMS), torch-CPU oracle port of the reference, {cores} threads"}
 
 
 def run_reference(args, wl):
@@ -152,14 +159,11 @@ def run_reference(args, wl):
         return
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    R, cls, reg, ann, anc = cpu_inputs(wl, 1)
     hw = (wl.height, wl.width)
-    t0 = time.perf_counter()
-    cpu_step(R, cls, reg, anc, ann, hw)
-    per_img = time.perf_counter() - t0
+    per_img = cpu_calibrate(wl, hw)
     total_steps = args.steps + args.warmup
-    # bound the whole run to ~2 minutes
-    n = int(max(1, min(wl.batch, 120.0 / max(per_img * total_steps, 1e-6))))
+    # bound the whole run to ~2 minutes (large batches run slower per image: 2x margin)
+    n = int(max(1, min(wl.batch, 60.0 / max(per_img * total_steps, 1e-6))))
     R, cls, reg, ann, anc = cpu_inputs(wl, n)
     for _ in range(args.warmup):
         cpu_step(R, cls, reg, anc, ann, hw)
@@ -174,7 +178,7 @@ def run_reference(args, wl):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(wl, n, args.gpus),
+        "config": dict(workload_config(wl, wl.batch, args.gpus), sample_images_per_step=n),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -276,8 +280,8 @@ def run_b200(args, wl):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
-        "gpu_launches": 12 * args.steps,
-        "launches_per_step": {"k7_match": 1, "k7_loss(scales+pipe+finalize)": 3, "k7_scale_inplace": 2,
+        "gpu_launches": 11 * args.steps,
+        "launches_per_step": {"k7_match": 1, "k7_loss(stream+rows)": 2, "k7_scale_inplace": 2,
                               "k7_detect(score+sort+mask+resolve+fallback)": 5, "k7_detect_gather": 1},
     }
 
@@ -288,13 +292,14 @@ def run_b200(args, wl):
     ms_fb = timed(train_side, k, 3)
     ms_det = timed(eval_side, k, 3)
     anc = anchors_mod(img)
-    assign, num_pos = BL.match(anc, ann, A, 0.35, 0.45)
-    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
-    ms_match = timed(lambda: BL.match(anc, ann, A, 0.35, 0.45), k, 3)
     dreg0 = torch.zeros_like(reg)     # what k7_match(zero_fill4=) hands over in the module path
-    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0, **kw),
-                    k, 3)
-    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, **kw), k, 3)
+    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
+    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
+    ms_match = timed(lambda: BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True), k, 3)
+    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0,
+                                          ignore_bits=bits, **kw), k, 3)
+    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw),
+                   k, 3)
     surv = int(eval_side(sync=True).survivors.sum())
     bytes_fwd = B * (A * (4 * C + 16) + 20 * M)
     bytes_fb = B * (A * (8 * C + 32) + 20 * M)
@@ -312,7 +317,7 @@ def run_b200(args, wl):
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
     ach = gbs(bytes_fb, ms_k_fb)
-    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: scales + pipe + finalize)",
+    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: stream kernel + row/reduction kernel)",
                        "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                        "traffic": ncu_traffic(wl.name, B),
                        "algorithmic_bytes_per_launch": bytes_fb, "avg_launch_ms": ms_k_fb, "peak_source": peak_src}

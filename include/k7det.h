@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 1
+#define K7_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -104,20 +104,21 @@ typedef struct K7MatchParams {
 #define K7_ASSIGN_ROW(w) ((int32_t)((uint32_t)(w) >> 2))
 
 /* Replaces calc_iou + IoU-max assignment (losses.py:6-23, 49-82).  Outputs:
- *   assign  [B,A] int32   packed state / GT row (images without a valid row: all IGNORE).  The
- *                         buffer must be 16-byte aligned and hold at least B*A + 4 words: k7_loss
- *                         streams it with 16-byte bulk copies and may read (never use) up to 3 words
- *                         past the end.
+ *   assign  [B,A] int32   packed state / GT row (images without a valid row: all IGNORE).
  *   num_pos [B]   int32   positives per image
  *   iou_max [B,A] float32 (optional, may be NULL)  bit-identical to torch.max(IoU,1).values
  *   argmax  [B,A] int32   (optional, may be NULL)  index into the FILTERED annotation list
  *   zero_fill4 [B,A,4] float32 (optional, may be NULL) is filled with zeros: the d(reg) buffer a
  *                         following k7_loss will write positive rows into (the kernel is ALU-bound,
- *                         so the 16 B/anchor store is free here; see K7LossParams.dreg_prezeroed) */
+ *                         so the 16 B/anchor store is free here; see K7LossParams.dreg_prezeroed)
+ *   ignore_bits [B, K7_IGNORE_WORDS(A)] uint32 (optional, may be NULL; 16-byte aligned) one bit per
+ *                         anchor, set = state IGNORE: bit a%32 of word a/32 of the image's row.  k7_loss
+ *                         streams it instead of the 4-byte words (it derives it itself when not given). */
+#define K7_IGNORE_WORDS(A) (((((size_t)(A)) + 127) >> 7) << 2) /* words per image, a multiple of 16 bytes */
 K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
              const float* annotations, int B, int A, int M, const K7MatchParams* params,
              int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, float* zero_fill4,
-             void* stream);
+             uint32_t* ignore_bits, void* stream);
 
 typedef struct K7LossParams {
     float alpha;            /* 0.25 (losses.py:31) ; gamma is fixed at 2 (losses.py:32, pow == x*x) */
@@ -136,10 +137,12 @@ K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
  *   sums      [4]   float32  { sum_i cls_loss_i, sum_i reg_loss_i, sum_i num_pos_i, B }  (the NCCL payload)
  *   dcls [B,A,C], dreg [B,A,4] (optional, both or neither): d(mean cls loss)/dcls and
  *   d(mean reg loss)/dreg with the mean taken over params->mean_divisor images.
- * The batch means of losses.py:168 are sums[0]/B and sums[1]/B. */
+ * The batch means of losses.py:168 are sums[0]/B and sums[1]/B.
+ * ignore_bits: k7_match's bitmap of the same call (or NULL).  Any B, A, C is streamed with bulk
+ * copies; only the base pointers of cls / dcls / reg / dreg must be 16-byte aligned. */
 K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
             const float* cls, const float* reg, const float* annotations,
-            const int32_t* assign, const int32_t* num_pos,
+            const int32_t* assign, const uint32_t* ignore_bits, const int32_t* num_pos,
             int B, int A, int C, int M, const K7LossParams* params,
             float* per_image, float* sums, float* dcls, float* dreg,
             void* workspace, size_t workspace_bytes, void* stream);

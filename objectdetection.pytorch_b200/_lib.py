@@ -76,6 +76,14 @@ class K7DetectParams(C.Structure):
     ]
 
 
+ABI_VERSION = 2                      # K7_ABI_VERSION of include/k7det.h
+
+
+def ignore_words(A: int) -> int:
+    """K7_IGNORE_WORDS(A): uint32 words per image of the ignore bitmap."""
+    return ((A + 127) >> 7) << 2
+
+
 # every symbol include/k7det.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 SYMBOLS = {
@@ -83,9 +91,9 @@ SYMBOLS = {
     "k7_last_error": (C.c_char_p, []),
     "k7_anchors_materialize": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P]),
     "k7_match": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, C.c_int, C.c_int, C.c_int,
-                           C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P]),
+                           C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
-    "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P,
+    "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),
                           _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "k7_scale_inplace": (C.c_int, [_P, C.c_size_t, _P, _P]),
@@ -131,7 +139,7 @@ def lib():
                     fn = getattr(l, name)
                     fn.restype = res
                     fn.argtypes = args
-                if l.k7_version() != 1:
+                if l.k7_version() != ABI_VERSION:
                     raise RuntimeError("libk7det.so ABI version mismatch; rebuild")
                 _lib = l
     return _lib

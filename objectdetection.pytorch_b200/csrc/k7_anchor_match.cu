@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(K7_MATCH_THREADS)
 k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7MatchAux aux,
                 const float* __restrict__ anchors, int box_order, const float* __restrict__ annotations, int A, int M,
                 float neg_thr, float pos_thr, int32_t* __restrict__ assign, int32_t* __restrict__ num_pos,
-                float* __restrict__ iou_max_out, int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4) {
+                float* __restrict__ iou_max_out, int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4,
+                uint32_t* __restrict__ ignore_bits, int W) {
     extern __shared__ float smem[];
     // valid GT rows: (x1,y1,x2,y2) as float4 | area | row (as int)
     float4* gbox = reinterpret_cast<float4*>(smem);
@@ -234,6 +235,10 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant
             if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         pos_total += (live && state == K7_STATE_POS) ? 1 : 0;
+        if (ignore_bits) {   // a0 is a multiple of 256: every warp owns whole words of the image's bitmap
+            const unsigned ib = __ballot_sync(0xffffffffu, live && state == K7_STATE_IGNORE);
+            if (lane == 0 && live) ignore_bits[(size_t)b * W + (a >> 5)] = ib;
+        }
     }
 
     pos_total = k7_warp_sum(pos_total);
@@ -274,13 +279,14 @@ static void k7_match_aux(const K7AnchorSpec* s, K7MatchAux* x) {
 
 extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* annotations,
                         int B, int A, int M, const K7MatchParams* params, int32_t* assign, int32_t* num_pos,
-                        float* iou_max, int32_t* argmax, float* zero_fill4, void* stream) {
+                        float* iou_max, int32_t* argmax, float* zero_fill4, uint32_t* ignore_bits, void* stream) {
     K7_REQUIRE(annotations && params && assign && num_pos, "k7_match: null argument");
     K7_REQUIRE(spec || anchors, "k7_match: need an anchor spec or an anchor tensor");
     K7_REQUIRE(B > 0 && A > 0 && M > 0, "k7_match: bad shape B=%d A=%d M=%d", B, A, M);
     K7_REQUIRE(M < (1 << 29), "k7_match: M too large");
     K7_REQUIRE(B <= 65535, "k7_match: B > 65535 not supported");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(zero_fill4) & 15) == 0, "k7_match: zero_fill4 must be 16-byte aligned");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(ignore_bits) & 15) == 0, "k7_match: ignore_bits must be 16-byte aligned");
     K7MatchAux aux;
     memset(&aux, 0, sizeof(aux));
     if (spec) {
@@ -313,7 +319,8 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                 \
         kern<<<grid, K7_MATCH_THREADS, smem, st>>>(sp, aux, anchors, box_order, annotations, A, M, params->neg_thr,      \
                                                    params->pos_thr, assign, num_pos, iou_max, argmax,                    \
-                                                   reinterpret_cast<float4*>(zero_fill4));                               \
+                                                   reinterpret_cast<float4*>(zero_fill4), ignore_bits,                   \
+                                                   (int)K7_IGNORE_WORDS(A));                                             \
     } while (0)
     if (spec) { if (cull) K7_MATCH_LAUNCH(true, true); else K7_MATCH_LAUNCH(true, false); }
     else      { if (cull) K7_MATCH_LAUNCH(false, true); else K7_MATCH_LAUNCH(false, false); }

@@ -3,69 +3,84 @@
 //   k7_loss   FocalLoss.forward after assignment   architectures/losses.py:62, 94-168
 //             (+ loss_efficientdet.py:61-160 through K7LossParams) and its autograd backward.
 //
-// The job is "move A*C*4 bytes per image in (and, with gradients, out) at HBM speed".  Profiling
-// history (profiles/): v1 (row-mapped lanes, per-warp rings) was issue-bound at 58 issue slots per
-// element; v2 (flat 4 KB tiles per warp, packed math) reached 27, of which 11 were per-tile
-// bookkeeping; this version (v3) moves the bookkeeping out of the compute warps:
+// The job is "move B*A*C*4 bytes in (and, with gradients, out) at HBM speed".  Profiling history
+// (profiles/): v1 (row-mapped lanes, per-warp rings) was issue-bound at 58 issue slots per element;
+// v2 (flat 4 KB tiles per warp, packed math) reached 27; v3 (warp-specialised CTA pipeline) 13, but
+// its consumer warps still scanned the assignment words of every slice and served the positive rows
+// inline - dependent global loads (annotation row -> label -> classification element) that held a
+// pipeline stage for ~1 us each and left the forward pass at 4.2 TB/s.  This version (v4):
 //
-//   * WARP-SPECIALISED PIPELINE.  One CTA per SM.  A producer warp cuts classifications[b] (a flat
-//     array of A*C floats; row boundaries are ignored) into tiles of 16 x 512 floats and drives a
-//     ring of shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile in, the
-//     assignment words of the rows touching it in, and - once the 16 consumer warps have signalled
-//     the stage done - gradients out.  full[]/done[] mbarriers; no __syncthreads in the loop.
+//   * STREAM KERNEL (k7_loss_pipe_kernel).  One CTA per SM.  classifications is ONE flat array of
+//     B*A*C floats cut into tiles of 16 x 512 floats; tiles ignore row AND image boundaries, so any
+//     shape streams through 16-byte aligned bulk copies (v3 needed A*C % 4 == 0 and fell back to a
+//     slow kernel otherwise - EfficientDet-D3 at 896x896 is such a shape).  A producer warp drives
+//     a ring of shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile in, the
+//     ignore bits of the rows touching it in, and - once the 16 consumer warps have signalled the
+//     stage done - gradients out.  full[]/done[] mbarriers; no __syncthreads in the loop.
 //   * FLAT PASS.  Consumer warp w owns floats [512w, 512w+512) of every tile: LDS.128 -> math ->
-//     STS.128 on float4 number lane+32k (conflict free, perfectly balanced whatever C is).  All
-//     elements are evaluated as "target 0" (negative / non-label class) with packed f32x2
-//     arithmetic (FFMA2/FMUL2, new on sm_100):
+//     STS.128 on float4 number lane+32k (conflict free, balanced whatever C is).  EVERY element is
+//     evaluated as "target 0" (negative / non-label class) with packed f32x2 arithmetic
+//     (FFMA2/FMUL2, new on sm_100):
 //         p = clamp(x); q = fl(1-p); pp = 1-q; nl = pp*S(pp) ~ -log(q)      (degree-5 minimax)
 //         loss += p*p*nl                                  (x (1-alpha) once per image)
 //         grad  = (p == x) ? (1-alpha)*scale * p * (2*nl + p/q) : 0          (MUFU.RCP)
-//     about 13 issue slots per element.  The polynomial is valid for p <= 0.25; the pass tracks
-//     max(p) and a slice that saw a larger value (rare: confident predictions) is redone from
-//     global memory by an exact scalar path with logf.
-//   * ROW EXCEPTIONS.  Ignored rows (state IGNORE, ~1-2 %) are turned into a bit mask over the
-//     slice before the flat pass (only slices that have one take the masked variant); the single
-//     "target 1" element of each positive row is patched after the flat pass (its "target 0"
-//     contribution is removed and the focal-positive term / gradient written); smooth-L1 and
-//     d(loss)/d(reg) are computed by the lane owning a positive row, in the slice where the row
-//     starts.  d(reg) of non-positive rows is zero: pre-zeroed by k7_match or by a memset here.
+//     The polynomial is valid for p <= 0.25; the pass tracks max(p) and a slice that saw a larger
+//     value (rare: confident predictions) is redone by an exact scalar path with logf.
+//   * IGNORED ROWS (IoU between the thresholds, ~1-2 %) come as ONE BIT PER ANCHOR (written by
+//     k7_match with a ballot, or derived from the assignment words by a small kernel here); a slice
+//     fetches the 32-bit window of its rows with two broadcast shared-memory loads and only slices
+//     with a set bit build an element mask and take the masked variant.
+//   * A slice that straddles an image boundary (B-1 of them per batch) or lies in a tile that
+//     spans more than two images (tiny shapes) takes a generic per-element path.
+//   * ROW KERNEL (k7_loss_rows_kernel), after the stream: one thread per anchor re-reads the 4-byte
+//     assignment word; positive anchors (~1-2 %) get smooth-L1 + d(reg), and their label element is
+//     corrected from "target 0" to "target 1" (loss difference into a partial sum, gradient
+//     overwritten in dcls).  Nothing latency-bound is left inside the stream.
 //   * Loss sums stay in registers while a warp works on one image; at an image change they are
-//     reduced with shuffles into one float2 per (image, CTA, warp) slot - no atomics - and summed
-//     per image in float64 in slot order by the finalize kernel: bit-reproducible run to run.
-//
-// Tiles never straddle images.  When A*C is not a multiple of 4 the image bases are not 16-byte
-// aligned and bulk copies are impossible: a compatibility kernel moves 1024-float tiles with plain
-// loads/stores, one warp per tile (odd test shapes only; every real head has A*C % 4 == 0).
+//     reduced with shuffles into one slot per (image, CTA, warp) - no atomics -, folded per CTA at
+//     the end of the stream kernel and summed per image in float64 in CTA order by the last row
+//     block of the image: bit-reproducible run to run.
 //
 // Algorithmic bytes per image: forward A*(4C+16)+20M, forward+backward A*(8C+32)+20M.
 #include <stdlib.h>
 
 #include "k7_common.cuh"
 
-#define K7_LOSS_MAX_WARPS 16
-#define K7_LOSS_TILE 1024   // floats per tile
+#define K7_ROWS_THREADS 256
+#define K7_ROWS_PER 4                                      // anchors per thread and chunk
+#define K7_ROWS_CHUNK (K7_ROWS_THREADS * K7_ROWS_PER)      // anchors per block and chunk
+#define K7_ROWS_MAX_GX 2048
 
 struct K7LossDev {
     float alpha, one_m_alpha;
     float beta, quad, shift;
     float div[4];
+    float mean_div;
     int use_div;
     int yx_targets;
+    int dreg_prezeroed;
     int B, A, C, M;
 };
 
 // per-image gradient scales, from the match stage's num_pos:
 //   x: 1 / (max(num_pos,1) * mean_divisor)      (losses.py:118,168)
 //   y: 1 / (4 * num_pos * mean_divisor) or 0    (losses.py:161,168)
-__global__ void k7_loss_scales_kernel(const int32_t* __restrict__ num_pos, int B, float mean_div,
-                                      float2* __restrict__ scales) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    const int n = num_pos[b];
+__device__ __forceinline__ float2 k7_loss_scales(const int n, const float mean_div) {
     float2 s;
     s.x = 1.0f / (fmaxf((float)n, 1.0f) * mean_div);
     s.y = n > 0 ? 1.0f / (4.0f * (float)n * mean_div) : 0.0f;
-    scales[b] = s;
+    return s;
+}
+
+// One bit per anchor: set = the row is ignored (losses.py:79-82: neither negative nor positive).
+// Layout: image b owns words [b*W, (b+1)*W), W = K7_IGNORE_WORDS(A); bit a%32 of word a/32.
+__global__ void __launch_bounds__(K7_ROWS_THREADS)
+k7_loss_bits_kernel(const int32_t* __restrict__ assign, int A, int W, uint32_t* __restrict__ bits) {
+    const int b = blockIdx.y;
+    const int a = blockIdx.x * K7_ROWS_THREADS + threadIdx.x;
+    const int st = (a < A) ? K7_ASSIGN_STATE(__ldg(assign + (size_t)b * A + a)) : K7_STATE_NEG;
+    const unsigned bal = __ballot_sync(0xffffffffu, st == K7_STATE_IGNORE);
+    if ((threadIdx.x & 31) == 0 && a < A) bits[(size_t)b * W + (a >> 5)] = bal;
 }
 
 // ------------------------------------------------------------------ element math
@@ -188,46 +203,46 @@ __device__ __forceinline__ uint32_t k7_range_bits(int lo, int hi, int base) {
     return (z - a == 32) ? 0xffffffffu : (((1u << (z - a)) - 1u) << a);
 }
 
-// ------------------------------------------------------------------ the pipelined kernel (A*C % 4 == 0)
-// One CTA per SM.  Warp CW is the PRODUCER: one elected lane cuts the image into tiles of
-// CW*512 floats, issues the TMA loads (classification tile + the assignment words of the rows it
-// touches) into a ring of NS stages, and, once the CW consumer warps have signalled a stage
-// done, the TMA store of the gradients.  Warps 0..CW-1 are CONSUMERS: warp w owns floats
-// [512w, 512w+512) of every tile.  full[s] / done[s] are mbarriers; there is no __syncthreads
-// after the prologue.
-#define K7_PIPE_SLICE 512
+// ------------------------------------------------------------------ the stream kernel
+// One CTA per SM.  Warp CW is the PRODUCER: one elected lane cuts the flat batch into tiles of
+// CW*512 floats, issues the TMA loads (classification tile + the ignore bits of the rows it
+// touches) into a ring of NS stages, and, once the CW consumer warps have signalled a stage done,
+// the TMA store of the gradients.  Warps 0..CW-1 are CONSUMERS: warp w owns floats
+// [SL*w, SL*w+SL) of every tile (SL = 512 or 1024).  full[s] / done[s] are mbarriers; there is no
+// __syncthreads after the prologue.
 #define K7_PIPE_MAX_CW 16
 
 struct K7PipeGeom {
-    uint32_t AC;          // elements per image
-    uint32_t tile_f;      // floats per tile = cw * K7_PIPE_SLICE
-    uint32_t tpi;         // tiles per image
-    uint32_t num_tiles;   // B * tpi
-    K7FastDiv div_c, div_tpi;
-    uint32_t side_words;  // assignment words reserved per stage
+    unsigned long long N;    // B*A*C elements
+    unsigned long long N4;   // N & ~3: the part moved by 16-byte bulk copies
+    unsigned long long AC;   // elements per image
+    uint32_t tile_f;         // floats per tile = cw * slice
+    uint32_t slice;          // floats per consumer warp and tile: 512 or 1024
+    uint32_t num_tiles;      // ceil(N4 / tile_f)
+    uint32_t W;              // ignore-bit words per image, K7_IGNORE_WORDS(A)
+    K7FastDiv div_c;         // / C for tile-local indices
+    uint32_t side_words;     // words reserved per ignore-bit part (two parts per stage)
     uint32_t stage_stride;
     uint32_t off_desc, off_mask, off_bars;
     int stages, cw, grid;
     size_t smem_bytes;
 };
 
-struct K7TileDesc {   // written by the producer next to each stage, 32 bytes
-    uint32_t n, rem, lead, b;
-    uint32_t row_first, off, pad0, pad1;
+struct K7TileDesc {   // written by the producer next to each stage, 48 bytes
+    uint32_t n, rem, split, b0;     // floats in the tile | position of float 0 in its row | floats that belong to image b0 | image of float 0
+    uint32_t lead, kA, bit1, a0;    // bit of tile row 0 in part 0 | tile row where image b0+1 starts | bit of that row (part 1) | anchor of tile row 0
+    uint32_t off_lo, off_hi, pad0, pad1;   // flat index of float 0
 };
 
-template <bool GRAD, bool FROM_SPEC>
+template <bool GRAD, int SL>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
-k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
-                    const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
-                    const int32_t* __restrict__ assign, const float2* __restrict__ scales,
+k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ bits, const int32_t* __restrict__ num_pos,
                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7PipeGeom G,
-                    float2* __restrict__ partials, float* __restrict__ dcls, float4* __restrict__ dreg) {
+                    float* __restrict__ partials, float* __restrict__ cta_partials, float* __restrict__ dcls) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
     const int C = P.C, A = P.A;
-    constexpr int SL = K7_PIPE_SLICE;
     K7TileDesc* desc = reinterpret_cast<K7TileDesc*>(smem + G.off_desc);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + G.off_bars);
     uint64_t* done = full + NS;
@@ -241,31 +256,47 @@ k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
         k7_fence_proxy_async();
     }
     __syncthreads();
-    if (blockIdx.x >= G.num_tiles) return;
-    const uint32_t ntl = (G.num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;   // tiles of this CTA
+    if (blockIdx.x >= G.num_tiles && blockIdx.x != 0) return;
+    const uint32_t ntl = blockIdx.x < G.num_tiles ? (G.num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;   // tiles of this CTA
 
     if (warp == CW) {
         // ================================================================ producer
         if (lane != 0) return;
         auto load = [&](const uint32_t j) {
-            const uint32_t g = blockIdx.x + j * gridDim.x;
+            const unsigned long long g = (unsigned long long)blockIdx.x + (unsigned long long)j * gridDim.x;
             const int s = (int)(j % (uint32_t)NS);
             unsigned char* stage = smem + (size_t)s * G.stage_stride;
+            const unsigned long long off = g * G.tile_f;
+            const unsigned long long left = G.N4 - off;
             K7TileDesc d;
-            d.b = k7_div(g, G.div_tpi);
-            d.off = (g - d.b * G.tpi) * G.tile_f;
-            d.n = min(G.tile_f, G.AC - d.off);
-            d.row_first = k7_div(d.off, G.div_c);
-            d.rem = d.off - d.row_first * (uint32_t)C;
+            d.n = left < G.tile_f ? (uint32_t)left : G.tile_f;
+            const unsigned long long r0 = off / (uint32_t)C;   // first row (batch-global) touching the tile
+            d.rem = (uint32_t)(off - r0 * (uint32_t)C);
+            d.b0 = (uint32_t)(r0 / (uint32_t)A);
+            d.a0 = (uint32_t)(r0 - (unsigned long long)d.b0 * (uint32_t)A);
+            const unsigned long long in_img = (unsigned long long)(d.b0 + 1u) * G.AC - off;
+            d.split = in_img < d.n ? (uint32_t)in_img : d.n;
             const uint32_t nrows = k7_div(d.rem + d.n - 1u, G.div_c) + 1u;
-            const size_t g0 = (size_t)d.b * A + d.row_first;
-            d.lead = (uint32_t)(g0 & 3);
-            d.pad0 = d.pad1 = 0;
-            const uint32_t side_bytes = ((d.lead + nrows + 3u) & ~3u) * 4u;
+            d.kA = (uint32_t)A - d.a0;
+            const uint32_t w0 = (d.a0 >> 7) << 2;   // 16-byte aligned first word of part 0
+            d.lead = d.a0 - (w0 << 5);
+            const uint32_t rows0 = nrows < d.kA ? nrows : d.kA;
+            const uint32_t words0 = ((d.lead + rows0 + 127u) >> 7) << 2;
+            uint32_t words1 = 0u;
+            if (nrows > d.kA && d.b0 + 1u < (uint32_t)P.B) {
+                const uint32_t rows1 = min(nrows - d.kA, (uint32_t)A);
+                words1 = ((rows1 + 127u) >> 7) << 2;
+            }
+            d.bit1 = G.side_words * 32u;
+            d.off_lo = (uint32_t)off;
+            d.off_hi = (uint32_t)(off >> 32);
+            d.pad0 = d.pad1 = 0u;
             desc[s] = d;
-            k7_mbar_expect_tx(full + s, d.n * 4u + side_bytes);   // release: orders the descriptor
-            k7_bulk_g2s(stage, cls + (size_t)d.b * G.AC + d.off, d.n * 4u, full + s);
-            k7_bulk_g2s(stage + (size_t)G.tile_f * 4, assign + (g0 - d.lead), side_bytes, full + s);
+            uint32_t* side = reinterpret_cast<uint32_t*>(stage + (size_t)G.tile_f * 4);
+            k7_mbar_expect_tx(full + s, d.n * 4u + (words0 + words1) * 4u);   // release: orders the descriptor
+            k7_bulk_g2s(stage, cls + off, d.n * 4u, full + s);
+            k7_bulk_g2s(side, bits + (size_t)d.b0 * G.W + w0, words0 * 4u, full + s);
+            if (words1) k7_bulk_g2s(side + G.side_words, bits + (size_t)(d.b0 + 1u) * G.W, words1 * 4u, full + s);
         };
         // with gradients one stage is always draining its store
         const uint32_t ahead = (uint32_t)(GRAD ? NS - 1 : NS);
@@ -277,7 +308,8 @@ k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
             k7_mbar_wait(done + s, phase);
             if (GRAD) {
                 const K7TileDesc d = desc[s];
-                k7_bulk_s2g(dcls + (size_t)d.b * G.AC + d.off, smem + (size_t)s * G.stage_stride, d.n * 4u);
+                const unsigned long long off = ((unsigned long long)d.off_hi << 32) | d.off_lo;
+                k7_bulk_s2g(dcls + off, smem + (size_t)s * G.stage_stride, d.n * 4u);
                 k7_bulk_commit();
                 if (jl < ntl) {
                     k7_bulk_wait_read<1>();   // the store of tile j-1 has left its stage
@@ -298,24 +330,35 @@ k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
 
     // ==================================================================== consumers
     uint32_t* mask = reinterpret_cast<uint32_t*>(smem + G.off_mask) + warp * (SL / 32);
-    float2* my_partials = partials + (size_t)blockIdx.x * CW + warp;      // + b * (gridDim.x * CW)
+    float* my_partials = partials + (size_t)blockIdx.x * CW + warp;      // + b * (gridDim.x * CW)
     const size_t pstride = (size_t)gridDim.x * CW;
-    for (int b = lane; b < P.B; b += 32) my_partials[(size_t)b * pstride] = make_float2(0.f, 0.f);
+    for (int b = lane; b < P.B; b += 32) my_partials[(size_t)b * pstride] = 0.0f;
     __syncwarp();
 
     const float oma = P.one_m_alpha;
-    float2 acc = make_float2(0.0f, 0.0f);   // sum p^2 * -log(1-p) of the current image (this lane)
-    float cfix = 0.0f, cslow = 0.0f, rsum = 0.0f;
+    float2 acc = make_float2(0.0f, 0.0f);   // sum p^2 * -log(1-p) of the current image (this lane), polynomial path
+    float cslow = 0.0f;                     // the same from the exact paths
     int cur_b = -1;
-    float2 sc = make_float2(0.f, 0.f);
     float sco = 0.0f;
     auto flush = [&]() {
-        float c = fmaf(oma, (acc.x + acc.y) + cslow, cfix);
+        float c = oma * ((acc.x + acc.y) + cslow);
         c = k7_warp_sum(c);
-        const float r = k7_warp_sum(rsum);
-        if (lane == 0) my_partials[(size_t)cur_b * pstride] = make_float2(c, r);
+        if (lane == 0) my_partials[(size_t)cur_b * pstride] = c;
         acc = make_float2(0.0f, 0.0f);
-        cfix = cslow = rsum = 0.0f;
+        cslow = 0.0f;
+    };
+    // A warp meets the images in increasing order, so every (image, CTA, warp) slot is written once.
+    auto enter = [&](const int b) {
+        if (b == cur_b) return;
+        if (cur_b >= 0) flush();
+        cur_b = b;
+        if (GRAD) sco = oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x;
+    };
+    auto exact = [&](const float x, const bool ign, float* gout) {
+        float gr;
+        const float l = k7_neg_exact(x, &gr);
+        if (!ign) cslow += l;
+        if (GRAD) *gout = ign ? 0.0f : sco * gr;
     };
     const int i_lo = warp * SL;
 
@@ -327,95 +370,95 @@ k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
         if (s == 0) phase ^= 1u;
         unsigned char* stage = smem + (size_t)s * G.stage_stride;
         k7_mbar_wait_u32(full_u32 + 8u * s, phase);
-        const uint4 d0 = *reinterpret_cast<const uint4*>(desc + s);   // n, rem, lead, b
+        const uint4 d0 = *reinterpret_cast<const uint4*>(desc + s);   // n, rem, split, b0
         const int n = (int)d0.x;
-        if ((int)d0.w != cur_b) {
-            if (cur_b >= 0) flush();
-            cur_b = (int)d0.w;
-            sc = __ldg(scales + cur_b);
-            sco = oma * sc.x;
-        }
         if (i_lo < n) {
             const int rem = (int)d0.y;
             const int i_hi = min(n, i_lo + SL);
             const int len = i_hi - i_lo, n4 = len >> 2;
             float* tile = reinterpret_cast<float*>(stage);
             float* slice = tile + i_lo;
-            const int32_t* side = reinterpret_cast<const int32_t*>(stage + (size_t)G.tile_f * 4) + d0.z;
-            const int k_lo = (int)k7_div((uint32_t)(rem + i_lo), G.div_c);
-            const int k_hi = (int)k7_div((uint32_t)(rem + i_hi - 1), G.div_c);
+            const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // lead, kA, bit1, a0
+            // which image does the slice lie in?  bitbase = bit position of tile row 0 of that image's part
+            int img = -1, bitbase = 0;
+            if ((uint32_t)i_hi <= d0.z) {
+                img = (int)d0.w;
+                bitbase = (int)d1.x;
+            } else if ((uint32_t)i_lo >= d0.z && (unsigned long long)i_hi <= (unsigned long long)d0.z + G.AC) {
+                img = (int)d0.w + 1;
+                bitbase = (int)d1.z - (int)d1.y;
+            }
+            if (img >= 0) {
+                enter(img);
+                const uint32_t* side = reinterpret_cast<const uint32_t*>(stage + (size_t)G.tile_f * 4);
+                const int k_lo = (int)k7_div((uint32_t)(rem + i_lo), G.div_c);
+                const int k_hi = (int)k7_div((uint32_t)(rem + i_hi - 1), G.div_c);
 
-            // ---- scan the rows touching the slice: ignored rows -> element mask, any positive row?
-            uint32_t mword = 0u;
-            bool masked = false, any_pos = false;
-            for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {
-                const int k = k0 + lane;
-                const int st = (k <= k_hi) ? K7_ASSIGN_STATE(side[k]) : K7_STATE_NEG;
-                unsigned ib = __ballot_sync(0xffffffffu, st == K7_STATE_IGNORE);
-                any_pos |= __any_sync(0xffffffffu, st == K7_STATE_POS);
-                if (ib == 0u) continue;
-                masked = true;
-                if (C == 1) {   // row k is element k: the ballot IS the mask word
-                    if (lane == ((k0 - k_lo) >> 5)) mword = ib;
-                } else {
-                    while (ib) {
-                        const int kk = k0 + __ffs(ib) - 1;
-                        ib &= ib - 1;
-                        const int lo = kk * C - rem - i_lo;
-                        mword |= k7_range_bits(max(lo, 0), min(lo + C, len), 32 * lane);
+                // ---- ignored rows of the slice -> element mask (warp-uniform window reads)
+                uint32_t mword = 0u;
+                bool masked = false;
+                for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {
+                    const int p = bitbase + k0;
+                    const uint32_t lo = side[p >> 5], hi = side[(p >> 5) + 1];
+                    uint32_t win = __funnelshift_r(lo, hi, (uint32_t)p & 31u);
+                    const int nv = k_hi - k0 + 1;
+                    if (nv < 32) win &= (1u << nv) - 1u;
+                    if (win == 0u) continue;
+                    masked = true;
+                    if (C == 1) {   // row k is element k: the window IS the mask word
+                        if (lane == ((k0 - k_lo) >> 5)) mword = win;
+                    } else {
+                        while (win) {
+                            const int kk = k0 + __ffs(win) - 1;
+                            win &= win - 1u;
+                            const int e_lo = kk * C - rem - i_lo;
+                            mword |= k7_range_bits(max(e_lo, 0), min(e_lo + C, len), 32 * lane);
+                        }
                     }
                 }
-            }
-            if (masked) {
-                if (lane < SL / 32) mask[lane] = mword;
-                __syncwarp();
-            }
-
-            // ---- flat pass
-            const float2 acc0 = acc;
-            float pmax = 0.0f;
-            if (masked)
-                k7_flat_pass<SL, GRAD, true>(slice, n4, mask, lane, sco, acc, pmax);
-            else
-                k7_flat_pass<SL, GRAD, false>(slice, n4, mask, lane, sco, acc, pmax);
-            if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
-                // a confident prediction: outside the polynomial's range.  Redo the slice exactly.
-                __syncwarp();
-                acc = acc0;
-                const float* src = cls + (size_t)d0.w * G.AC + desc[s].off + i_lo;
-                for (int i = lane; i < len; i += 32) {
-                    const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
-                    float gr;
-                    const float l = k7_neg_exact(__ldg(src + i), &gr);
-                    if (!ign) cslow += l;
-                    if (GRAD) slice[i] = ign ? 0.0f : sco * gr;
+                if (masked) {
+                    if (lane < SL / 32) mask[lane] = mword;
+                    __syncwarp();
                 }
-            }
 
-            // ---- positive rows: smooth-L1 / d(reg) where the row starts, label patch where the label lies
-            if (any_pos) {
-                __syncwarp();
-                const uint32_t row_first = desc[s].row_first, off = desc[s].off;
-                const size_t e0 = (size_t)d0.w * G.AC + off;
-                for (int k = k_lo + lane; k <= k_hi; k += 32) {
-                    const int aw = side[k];
-                    if (K7_ASSIGN_STATE(aw) != K7_STATE_POS) continue;
-                    const float* arow = annotations + ((size_t)cur_b * P.M + K7_ASSIGN_ROW(aw)) * 5;
-                    const int i0 = k * C - rem;   // tile-local element index of the row's class 0
-                    if (i0 >= i_lo && i0 < i_hi) {
-                        const int a = (int)row_first + k;
-                        rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, (size_t)cur_b * A + a,
-                                                                  arow, reg, sc.y, dreg);
+                // ---- flat pass
+                const float2 acc0 = acc;
+                float pmax = 0.0f;
+                if (masked)
+                    k7_flat_pass<SL, GRAD, true>(slice, n4, mask, lane, sco, acc, pmax);
+                else
+                    k7_flat_pass<SL, GRAD, false>(slice, n4, mask, lane, sco, acc, pmax);
+                if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
+                    // a confident prediction: outside the polynomial's range.  Redo the slice exactly
+                    // (with gradients the tile already holds them: the inputs come from global memory again).
+                    __syncwarp();
+                    acc = acc0;
+                    const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
+                    const float* src = cls + ((((unsigned long long)d2.y) << 32) | d2.x) + i_lo;
+                    for (int i = lane; i < len; i += 32) {
+                        const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
+                        exact(GRAD ? __ldg(src + i) : slice[i], ign, slice + i);
                     }
-                    const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
-                    const int il = i0 + label;
-                    if (label >= 0 && label < C && il >= i_lo && il < i_hi) {
-                        // the label class has target 1: replace its "target 0" term
-                        const float xl = __ldg(cls + e0 + il);
-                        const float p = k7_clamp_p(xl);
-                        cfix += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
-                        if (GRAD) tile[il] = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
+                }
+            } else {
+                // ---- generic path: the slice straddles an image boundary (or the tile spans > 2 images)
+                const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
+                const unsigned long long off = (((unsigned long long)d2.y) << 32) | d2.x;
+                const unsigned long long r0 = (unsigned long long)d0.w * (uint32_t)A + d1.w;
+                uint32_t i = (uint32_t)i_lo;
+                while (i < (uint32_t)i_hi) {   // warp-uniform: one iteration per image segment
+                    const uint32_t b = (uint32_t)((off + i) / G.AC);
+                    const unsigned long long img_end = (unsigned long long)(b + 1u) * G.AC - off;
+                    const uint32_t seg_end = img_end < (unsigned long long)i_hi ? (uint32_t)img_end : (uint32_t)i_hi;
+                    enter((int)b);
+                    const unsigned long long abase = (unsigned long long)b * (uint32_t)A;
+                    for (uint32_t t = i + lane; t < seg_end; t += 32) {
+                        const uint32_t k = k7_div((uint32_t)rem + t, G.div_c);
+                        const uint32_t a = (uint32_t)(r0 + k - abase);
+                        const bool ign = (__ldg(bits + (size_t)b * G.W + (a >> 5)) >> (a & 31u)) & 1u;
+                        exact(tile[t], ign, tile + t);
                     }
+                    i = seg_end;
                 }
             }
         }
@@ -423,204 +466,222 @@ k7_loss_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
         __syncwarp();
         if (lane == 0) k7_mbar_arrive_u32(done_u32 + 8u * s);
     }
+
+    // the last N % 4 elements cannot be bulk-copied: CTA 0, warp 0 serves them from global memory
+    if (blockIdx.x == 0 && warp == 0 && G.N4 < G.N) {
+        for (unsigned long long e = G.N4; e < G.N; ++e) {
+            const uint32_t b = (uint32_t)(e / G.AC);
+            enter((int)b);
+            if (lane == 0) {
+                const unsigned long long r = e / (uint32_t)C;
+                const uint32_t a = (uint32_t)(r - (unsigned long long)b * (uint32_t)A);
+                const bool ign = (__ldg(bits + (size_t)b * G.W + (a >> 5)) >> (a & 31u)) & 1u;
+                float g = 0.0f;
+                exact(__ldg(cls + e), ign, &g);
+                if (GRAD) dcls[e] = g;
+            }
+        }
+    }
     if (cur_b >= 0) flush();
+
+    // ---- fold the CTA's (image, warp) slots into one value per (image, CTA): consumer warps only
+    asm volatile("bar.sync 1, %0;" ::"r"(CW * 32) : "memory");
+    for (int b = warp; b < P.B; b += CW) {
+        float v = (lane < CW) ? __ldcg(partials + (size_t)b * pstride + (size_t)blockIdx.x * CW + lane) : 0.0f;
+        v = k7_warp_sum(v);
+        if (lane == 0) cta_partials[(size_t)b * gridDim.x + blockIdx.x] = v;
+    }
 }
 
-// ------------------------------------------------------------------ the compatibility kernel (A*C % 4 != 0)
-// Image bases are not 16-byte aligned, so no bulk copies: one warp per 1024-float tile moves it
-// with plain loads/stores.  Same flat pass, same row handling, per-tile partials.
-struct K7Tile {
-    uint32_t b, off, n, row_first, rem, nrows;
-};
-struct K7CompatGeom {
-    uint32_t AC, tpi, num_tiles;
-    K7FastDiv div_c, div_tpi;
-    uint32_t stage_stride;
-    int warps, grid;
-    size_t smem_bytes;
-};
+// ------------------------------------------------------------------ the row kernel
+// After the stream kernel.  A block re-reads the 4-byte assignment words of a chunk of 1024
+// anchors (four independent coalesced loads per thread); the positive anchors (~1-2 %) are queued
+// in shared memory (ballots + a prefix over the 32 ballot counts: anchor order) and then served by
+// dense warps: smooth-L1 + d(reg) (losses.py:122-166) and the
+// correction of the label element from "target 0" (what the stream computed) to "target 1"
+// (losses.py:94-97, 100-112) - the loss difference goes into the block's partial sum, the
+// gradient overwrites the stream's value in dcls.  Other anchors: d(reg) = 0 unless the caller
+// pre-zeroed it.  Grid (gx, B).
+// The reduction is fused behind it: the last block of an image (per-image counter) sums the
+// image's stream slots and row partials in float64 in slot order and writes (cls_loss_i,
+// reg_loss_i); the last image to finish sums the batch in image order.  No float atomics:
+// bit-reproducible run to run.
 
-template <int TILE_F, bool GRAD, bool FROM_SPEC>
-__global__ void __launch_bounds__(K7_LOSS_MAX_WARPS * 32, 1)
-k7_loss_compat_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
-                      const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
-                      const int32_t* __restrict__ assign, const float2* __restrict__ scales,
-                      const __grid_constant__ K7LossDev P, const __grid_constant__ K7CompatGeom G,
-                      float2* __restrict__ partials, float* __restrict__ dcls, float4* __restrict__ dreg) {
-    extern __shared__ __align__(128) unsigned char smem[];
+__device__ __forceinline__ double k7_warp_sum_f64(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Sum of (c, r) over the block, result valid in thread 0.  Fixed order.  s_red: 2 * warps doubles.
+__device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* s_red) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int C = P.C, A = P.A;
-    unsigned char* stage = smem + (size_t)warp * G.stage_stride;
-    float* tile = reinterpret_cast<float*>(stage);
-    int32_t* side = reinterpret_cast<int32_t*>(stage + TILE_F * 4);
-    uint32_t* mask = reinterpret_cast<uint32_t*>(smem + (size_t)G.warps * G.stage_stride) + warp * (TILE_F / 32);
-    const uint32_t nW = gridDim.x * G.warps;
-    const float oma = P.one_m_alpha;
-
-    for (uint64_t g64 = blockIdx.x * G.warps + warp; g64 < G.num_tiles; g64 += nW) {
-        const uint32_t g = (uint32_t)g64;
-        K7Tile t;
-        t.b = k7_div(g, G.div_tpi);
-        t.off = (g - t.b * G.tpi) * (uint32_t)TILE_F;
-        t.n = min((uint32_t)TILE_F, G.AC - t.off);
-        t.row_first = k7_div(t.off, G.div_c);
-        t.rem = t.off - t.row_first * (uint32_t)C;
-        t.nrows = k7_div(t.rem + t.n - 1u, G.div_c) + 1u;
-        const size_t e0 = (size_t)t.b * G.AC + t.off;     // first element of the tile in cls / dcls
-        const size_t g0 = (size_t)t.b * A + t.row_first;  // first row of the tile in assign / reg / dreg
-        const int n = (int)t.n, nrows = (int)t.nrows, rem = (int)t.rem;
-        const int n4 = (n + 3) >> 2;
-        for (int i = lane; i < 4 * n4; i += 32) tile[i] = (i < n) ? cls[e0 + i] : 0.0f;
-        for (int k = lane; k < nrows; k += 32) side[k] = assign[g0 + k];
-        __syncwarp();
-
-        uint32_t mword = 0u;
-        bool masked = false;
-        for (int k0 = 0; k0 < nrows; k0 += 32) {
-            const int k = k0 + lane;
-            const int st = (k < nrows) ? K7_ASSIGN_STATE(side[k]) : K7_STATE_NEG;
-            unsigned ib = __ballot_sync(0xffffffffu, st == K7_STATE_IGNORE);
-            if (ib == 0u) continue;
-            masked = true;
-            while (ib) {
-                const int kk = k0 + __ffs(ib) - 1;
-                ib &= ib - 1;
-                const int lo = kk * C - rem;
-                mword |= k7_range_bits(max(lo, 0), min(lo + C, n), 32 * lane);
-            }
-        }
-        if (n & 3) {   // zero padding of the last float4
-            masked = true;
-            mword |= k7_range_bits(n, 4 * n4, 32 * lane);
-        }
-        if (masked) {
-            mask[lane] = mword;
-            __syncwarp();
-        }
-
-        const float2 sc = __ldg(scales + t.b);
-        const float sco = oma * sc.x;
-        float2 acc = make_float2(0.0f, 0.0f);
-        float pmax = 0.0f;
-        if (masked)
-            k7_flat_pass<TILE_F, GRAD, true>(tile, n4, mask, lane, sco, acc, pmax);
-        else
-            k7_flat_pass<TILE_F, GRAD, false>(tile, n4, mask, lane, sco, acc, pmax);
-        float csum = acc.x + acc.y;
-        if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
-            __syncwarp();
-            csum = 0.0f;
-            for (int i = lane; i < n; i += 32) {
-                const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
-                float gr;
-                const float l = k7_neg_exact(__ldg(cls + e0 + i), &gr);
-                if (!ign) csum += l;
-                if (GRAD) tile[i] = ign ? 0.0f : sco * gr;
-            }
-        }
-        csum *= oma;
-        __syncwarp();
-
-        float rsum = 0.0f;
-        for (int k = lane; k < nrows; k += 32) {
-            const int aw = side[k];
-            const int i0 = k * C - rem;
-            const bool starts = i0 >= 0;
-            const size_t R = g0 + k;
-            bool wrote = false;
-            if (K7_ASSIGN_STATE(aw) == K7_STATE_POS) {
-                const float* arow = annotations + ((size_t)t.b * P.M + K7_ASSIGN_ROW(aw)) * 5;
-                if (starts) {
-                    rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, (int)(t.row_first + k), R, arow,
-                                                              reg, sc.y, dreg);
-                    wrote = true;
-                }
-                const int label = (int)__ldg(arow + 4);
-                const int il = i0 + label;
-                if (label >= 0 && label < C && il >= 0 && il < n) {
-                    const float xl = __ldg(cls + e0 + il);
-                    const float p = k7_clamp_p(xl);
-                    csum += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
-                    if (GRAD) tile[il] = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
-                }
-            }
-            if (GRAD && starts && !wrote) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        csum = k7_warp_sum(csum);
-        rsum = k7_warp_sum(rsum);
-        if (lane == 0) partials[g] = make_float2(csum, rsum);
-        __syncwarp();
-        if (GRAD) {
-            for (int i = lane; i < n; i += 32) dcls[e0 + i] = tile[i];
-            __syncwarp();
+    constexpr int NW = K7_ROWS_THREADS / 32;
+    c = k7_warp_sum_f64(c);
+    r = k7_warp_sum_f64(r);
+    __syncthreads();   // s_red may still be read from a previous use
+    if (lane == 0) {
+        s_red[warp] = c;
+        s_red[NW + warp] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        c = 0.0;
+        r = 0.0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+            c += s_red[w];
+            r += s_red[NW + w];
         }
     }
 }
 
-// Per image: sum the tile partials in float64, fixed order; write (cls_loss_i, reg_loss_i).
-// The last block to finish reduces the batch (threadfence + counter).
-__global__ void __launch_bounds__(256)
-k7_loss_finalize_kernel(const float2* __restrict__ partials, const int32_t* __restrict__ num_pos, int B, uint32_t tpi,
-                        float* __restrict__ per_image, float* __restrict__ sums, unsigned int* __restrict__ counter) {
-    __shared__ double s_c[256], s_r[256], s_n[256];
+template <bool GRAD, bool FROM_SPEC>
+__global__ void __launch_bounds__(K7_ROWS_THREADS)
+k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
+                    const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
+                    const int32_t* __restrict__ assign, const int32_t* __restrict__ num_pos,
+                    const __grid_constant__ K7LossDev P, const float* __restrict__ pipe_partials, uint32_t pipe_slots,
+                    float2* __restrict__ rows_partials, unsigned int* __restrict__ counters /* [B] images, [B] = batch */,
+                    float* __restrict__ per_image, float* __restrict__ sums, float* __restrict__ dcls,
+                    float4* __restrict__ dreg) {
+    constexpr int NW = K7_ROWS_THREADS / 32;
+    __shared__ int s_qa[K7_ROWS_CHUNK], s_qw[K7_ROWS_CHUNK];
+    __shared__ int s_off[K7_ROWS_PER * NW + 1];   // queue offset of every (round, warp) ballot; [last] = total
+    __shared__ double s_red[2 * NW];
     __shared__ bool s_last;
-    const int b = blockIdx.x;
-    const float2* pt = partials + (size_t)b * tpi;
-    double c = 0.0, r = 0.0;
-    for (uint32_t t = threadIdx.x; t < tpi; t += blockDim.x) {
-        const float2 p = pt[t];
-        c += p.x;
-        r += p.y;
+    const int b = blockIdx.y;
+    const int A = P.A, C = P.C;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
+    const float oma = P.one_m_alpha;
+    float cfix = 0.0f, rsum = 0.0f;
+
+    for (int a0 = blockIdx.x * K7_ROWS_CHUNK; a0 < A; a0 += gridDim.x * K7_ROWS_CHUNK) {   // block-uniform
+        // ---- scan: K7_ROWS_PER independent coalesced loads per thread, positives -> queue in anchor order
+        int aw[K7_ROWS_PER];
+        unsigned bal[K7_ROWS_PER];
+#pragma unroll
+        for (int k = 0; k < K7_ROWS_PER; ++k) {
+            const int a = a0 + k * K7_ROWS_THREADS + threadIdx.x;
+            aw[k] = (a < A) ? __ldg(assign + (size_t)b * A + a) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < K7_ROWS_PER; ++k) {
+            const int a = a0 + k * K7_ROWS_THREADS + threadIdx.x;
+            const bool pos = (a < A) && K7_ASSIGN_STATE(aw[k]) == K7_STATE_POS;
+            if (GRAD && !P.dreg_prezeroed && a < A && !pos) dreg[(size_t)b * A + a] = make_float4(0.f, 0.f, 0.f, 0.f);
+            bal[k] = __ballot_sync(0xffffffffu, pos);
+            if (lane == 0) s_off[k * NW + warp] = __popc(bal[k]);
+        }
+        __syncthreads();
+        if (warp == 0) {   // exclusive scan of the K7_ROWS_PER * NW (= 32) counts
+            static_assert(K7_ROWS_PER * NW == 32, "one count per lane");
+            const int cnt = s_off[lane];
+            int inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            s_off[lane] = inc - cnt;
+            if (lane == 31) s_off[32] = inc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < K7_ROWS_PER; ++k) {
+            if ((bal[k] >> lane) & 1u) {
+                const int q = s_off[k * NW + warp] + __popc(bal[k] & ((1u << lane) - 1u));
+                s_qa[q] = a0 + k * K7_ROWS_THREADS + threadIdx.x;
+                s_qw[q] = aw[k];
+            }
+        }
+        __syncthreads();
+        // ---- serve the queue with dense warps: thread t takes entries t, t+256, ...
+        const int qn = s_off[32];
+        for (int i = threadIdx.x; i < qn; i += K7_ROWS_THREADS) {
+            const int a = s_qa[i], w = s_qw[i];
+            const size_t R = (size_t)b * A + a;
+            const float* arow = annotations + ((size_t)b * P.M + K7_ASSIGN_ROW(w)) * 5;
+            rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
+            const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
+            if (label >= 0 && label < C) {
+                const size_t e = R * (size_t)C + (size_t)label;
+                const float xl = __ldg(cls + e);
+                const float p = k7_clamp_p(xl);
+                cfix += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
+                if (GRAD) dcls[e] = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
+            }
+        }
+        __syncthreads();   // the queue is rewritten by the next chunk
     }
-    s_c[threadIdx.x] = c;
-    s_r[threadIdx.x] = r;
-    __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-        if (threadIdx.x < o) {
-            s_c[threadIdx.x] += s_c[threadIdx.x + o];
-            s_r[threadIdx.x] += s_r[threadIdx.x + o];
+
+    double c = (double)cfix, r = (double)rsum;
+    {   // block partial in float32, fixed order (warp tree, then warps in order)
+        float cf = k7_warp_sum(cfix), rf = k7_warp_sum(rsum);
+        __shared__ float s_c[NW], s_r[NW];
+        if (lane == 0) {
+            s_c[warp] = cf;
+            s_r[warp] = rf;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            cf = rf = 0.0f;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                cf += s_c[w];
+                rf += s_r[w];
+            }
+            rows_partials[(size_t)b * gridDim.x + blockIdx.x] = make_float2(cf, rf);
+            __threadfence();
+            s_last = atomicAdd(counters + b, 1u) == gridDim.x - 1u;
         }
         __syncthreads();
     }
+    if (!s_last) return;
+
+    // ---- last block of image b: per-image sums (losses.py:118, 161-166)
+    __threadfence();
+    c = 0.0;
+    r = 0.0;
+    const float* pp = pipe_partials + (size_t)b * pipe_slots;
+    for (uint32_t t = threadIdx.x; t < pipe_slots; t += K7_ROWS_THREADS) c += (double)__ldcg(pp + t);
+    const float2* rp = rows_partials + (size_t)b * gridDim.x;
+    for (uint32_t t = threadIdx.x; t < gridDim.x; t += K7_ROWS_THREADS) {
+        const float2 p = __ldcg(rp + t);
+        c += (double)p.x;
+        r += (double)p.y;
+    }
+    k7_block_sum2_f64(c, r, s_red);
     if (threadIdx.x == 0) {
         const int n = num_pos[b];
-        const float ci = (float)s_c[0] / fmaxf((float)n, 1.0f);
-        const float ri = n > 0 ? (float)(s_r[0] / (4.0 * (double)n)) : 0.0f;
-        per_image[2 * b + 0] = ci;
-        per_image[2 * b + 1] = ri;
+        per_image[2 * b + 0] = (float)c / fmaxf((float)n, 1.0f);
+        per_image[2 * b + 1] = n > 0 ? (float)(r / (4.0 * (double)n)) : 0.0f;
+        counters[b] = 0u;   // re-arm for the next call on this workspace
         __threadfence();
-        const unsigned int done = atomicAdd(counter, 1u);
-        s_last = (done == (unsigned int)(B - 1));
+        s_last = atomicAdd(counters + P.B, 1u) == (unsigned int)(P.B - 1);
     }
     __syncthreads();
-    if (s_last) {
-        __threadfence();
-        // batch sums in image order (deterministic); 256 threads, tree in shared memory
-        double cc = 0.0, rr = 0.0, nn = 0.0;
-        for (int i = threadIdx.x; i < B; i += blockDim.x) {
-            cc += (double)__ldcg(per_image + 2 * i);
-            rr += (double)__ldcg(per_image + 2 * i + 1);
-            nn += (double)num_pos[i];
-        }
-        s_c[threadIdx.x] = cc;
-        s_r[threadIdx.x] = rr;
-        s_n[threadIdx.x] = nn;
-        __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) {
-            if (threadIdx.x < o) {
-                s_c[threadIdx.x] += s_c[threadIdx.x + o];
-                s_r[threadIdx.x] += s_r[threadIdx.x + o];
-                s_n[threadIdx.x] += s_n[threadIdx.x + o];
-            }
-            __syncthreads();
-        }
-        if (threadIdx.x == 0) {
-            sums[0] = (float)s_c[0];
-            sums[1] = (float)s_r[0];
-            sums[2] = (float)s_n[0];
-            sums[3] = (float)B;
-            *counter = 0u;   // re-arm for the next call on this workspace
-        }
+    if (!s_last) return;
+
+    // ---- last image: batch sums in image order
+    __threadfence();
+    c = 0.0;
+    r = 0.0;
+    double nn = 0.0, zero = 0.0;
+    for (int i = threadIdx.x; i < P.B; i += K7_ROWS_THREADS) {
+        c += (double)__ldcg(per_image + 2 * i);
+        r += (double)__ldcg(per_image + 2 * i + 1);
+        nn += (double)num_pos[i];
+    }
+    k7_block_sum2_f64(c, r, s_red);
+    k7_block_sum2_f64(nn, zero, s_red);
+    if (threadIdx.x == 0) {
+        sums[0] = (float)c;
+        sums[1] = (float)r;
+        sums[2] = (float)nn;
+        sums[3] = (float)P.B;
+        counters[P.B] = 0u;
     }
 }
 
@@ -650,29 +711,37 @@ extern "C" int k7_scale_inplace(float* grad, size_t n, const float* scale, void*
 // ------------------------------------------------------------------ host side
 #define K7_LOSS_MAX_GRID 256   // upper bound on CTAs assumed by the workspace query
 
-static uint32_t k7_loss_tpi(int A, int C) {
-    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
-    return (uint32_t)((ac + K7_LOSS_TILE - 1) / K7_LOSS_TILE);
+static int k7_rows_gx(int B, int A) {
+    (void)B;
+    int gx = (A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK;   // one chunk per block unless the image is huge
+    if (gx > K7_ROWS_MAX_GX) gx = K7_ROWS_MAX_GX;
+    return gx < 1 ? 1 : gx;
 }
 
-static size_t k7_loss_ws_layout(int B, unsigned long long slots_per_image, size_t* off_scales, size_t* off_partials,
-                                size_t* off_counter) {
+struct K7LossWs {
+    size_t counter, bits, pipe, cta, rows, total;
+};
+
+static K7LossWs k7_loss_ws_layout(int B, int A, size_t pipe_slots, size_t rows_slots) {
+    K7LossWs w;
     size_t o = 0;
-    *off_counter = o;
-    o += 256;
-    *off_scales = o;
-    o += k7_align_up(sizeof(float2) * (size_t)B, 256);
-    *off_partials = o;
-    o += k7_align_up(sizeof(float2) * (size_t)B * slots_per_image, 256);
-    return o;
+    w.counter = o;   // [B] per-image block counters + 1 batch counter
+    o += k7_align_up(sizeof(unsigned int) * ((size_t)B + 1), 256);
+    w.bits = o;
+    o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(A), 256);
+    w.pipe = o;
+    o += k7_align_up(sizeof(float) * (size_t)B * pipe_slots, 256);
+    w.cta = o;       // [B][grid] stream-kernel partials, one per (image, CTA)
+    o += k7_align_up(sizeof(float) * (size_t)B * K7_LOSS_MAX_GRID, 256);
+    w.rows = o;
+    o += k7_align_up(sizeof(float2) * (size_t)B * rows_slots, 256);
+    w.total = o;
+    return w;
 }
 
 extern "C" size_t k7_loss_workspace_bytes(int B, int A, int C) {
     if (B <= 0 || A <= 0 || C <= 0) return 0;
-    size_t a, b, c;
-    unsigned long long slots = (unsigned long long)K7_LOSS_MAX_GRID * K7_PIPE_MAX_CW;   // pipelined kernel
-    if (((unsigned long long)A * C) % 4ull) slots = k7_loss_tpi(A, C);                  // compatibility kernel
-    return k7_loss_ws_layout(B, slots, &a, &b, &c);
+    return k7_loss_ws_layout(B, A, (size_t)K7_LOSS_MAX_GRID * K7_PIPE_MAX_CW, (size_t)k7_rows_gx(B, A)).total;
 }
 
 static int k7_env_int(const char* name, int dflt) {
@@ -682,27 +751,33 @@ static int k7_env_int(const char* name, int dflt) {
 }
 
 static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
-    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
-    K7_REQUIRE(ac < (1ull << 30), "k7_loss: A*C=%llu per image is too large", ac);
-    g->AC = (uint32_t)ac;
-    int cw = k7_env_int("K7_WARPS", K7_PIPE_MAX_CW);
+    g->AC = (unsigned long long)A * (unsigned long long)C;
+    g->N = g->AC * (unsigned long long)B;
+    g->N4 = g->N & ~3ull;
+    // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass is bound by per-slice bookkeeping and
+    // wants long slices (12 warps x 1024 floats); with gradients the stream is a copy and wants
+    // the most warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
+    int slice = k7_env_int("K7_SLICE", grad ? 512 : 1024);
+    slice = slice >= 1024 ? 1024 : 512;
+    int cw = k7_env_int("K7_WARPS", slice == 1024 ? 12 : K7_PIPE_MAX_CW);
     if (cw > K7_PIPE_MAX_CW) cw = K7_PIPE_MAX_CW;
     if (cw < 1) cw = 1;
     g->cw = cw;
-    g->tile_f = (uint32_t)cw * K7_PIPE_SLICE;
-    g->tpi = (uint32_t)((ac + g->tile_f - 1) / g->tile_f);
-    const unsigned long long nt = (unsigned long long)B * g->tpi;
+    g->slice = (uint32_t)slice;
+    g->tile_f = (uint32_t)cw * (uint32_t)slice;
+    const unsigned long long nt = (g->N4 + g->tile_f - 1) / g->tile_f;
     K7_REQUIRE(nt < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", nt);
     g->num_tiles = (uint32_t)nt;
+    g->W = (uint32_t)K7_IGNORE_WORDS(A);
     g->div_c = k7_fastdiv_make((uint32_t)C);
-    g->div_tpi = k7_fastdiv_make(g->tpi);
-    // rows touching a tile: (tile_f-1)/C + 2 at most, + 3 words of alignment lead, rounded to 16 bytes
-    g->side_words = (uint32_t)(((g->tile_f - 1) / (uint32_t)C + 2 + 3 + 3) & ~3u);
-    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4 + (size_t)g->side_words * 4, 128);
+    // rows touching a tile: (tile_f-1)/C + 2 at most; a part starts up to 127 bits into its first 16 bytes
+    const uint32_t nrows_max = (g->tile_f - 1) / (uint32_t)C + 2;
+    g->side_words = (((nrows_max + 254u) >> 7) + 1u) << 2;
+    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4 + (size_t)(2 * g->side_words + 4) * 4, 128);
     const size_t budget = 226 * 1024;
-    const size_t fixed = 64 /*alignment slack*/ + (size_t)cw * (K7_PIPE_SLICE / 8);
+    const size_t fixed = 64 /*alignment slack*/ + (size_t)cw * (slice / 8);
     int stages = (int)((budget - fixed) / ((size_t)g->stage_stride + sizeof(K7TileDesc) + 16));
-    const int want = k7_env_int("K7_STAGES", 8);
+    const int want = k7_env_int("K7_STAGES", 4);
     if (stages > want) stages = want;
     if (stages > 16) stages = 16;
     K7_REQUIRE(stages >= (grad ? 3 : 2), "k7_loss: C=%d needs %u bytes of shared memory per stage", C, g->stage_stride);
@@ -711,7 +786,7 @@ static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
     g->off_desc = (uint32_t)o;
     o += (size_t)stages * sizeof(K7TileDesc);
     g->off_mask = (uint32_t)o;
-    o += (size_t)cw * (K7_PIPE_SLICE / 8);
+    o += (size_t)cw * (slice / 8);
     o = k7_align_up(o, 16);
     g->off_bars = (uint32_t)o;
     o += (size_t)stages * 16;
@@ -723,44 +798,20 @@ static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
     return K7_OK;
 }
 
-static int k7_compat_geometry(int B, int A, int C, K7CompatGeom* g) {
-    const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
-    K7_REQUIRE(ac < (1ull << 30), "k7_loss: A*C=%llu per image is too large", ac);
-    g->AC = (uint32_t)ac;
-    g->tpi = k7_loss_tpi(A, C);
-    const unsigned long long nt = (unsigned long long)B * g->tpi;
-    K7_REQUIRE(nt < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", nt);
-    g->num_tiles = (uint32_t)nt;
-    g->div_c = k7_fastdiv_make((uint32_t)C);
-    g->div_tpi = k7_fastdiv_make(g->tpi);
-    const uint32_t side_words = (uint32_t)(((K7_LOSS_TILE - 1) / C + 2 + 3) & ~3);
-    g->stage_stride = (uint32_t)k7_align_up((size_t)K7_LOSS_TILE * 4 + (size_t)side_words * 4, 128);
-    const size_t per_warp = (size_t)g->stage_stride + K7_LOSS_TILE / 8;
-    int warps = (int)((200 * 1024) / per_warp);
-    if (warps > K7_LOSS_MAX_WARPS) warps = K7_LOSS_MAX_WARPS;
-    K7_REQUIRE(warps >= 1, "k7_loss: C=%d needs %zu bytes of shared memory per warp", C, per_warp);
-    g->warps = warps;
-    g->smem_bytes = (size_t)warps * per_warp;
-    unsigned long long ctas = (nt + warps - 1) / warps;
-    int grid = k7_sm_count();
-    if (ctas < (unsigned long long)grid) grid = (int)ctas;
-    g->grid = grid < 1 ? 1 : grid;
-    return K7_OK;
-}
-
 extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
-                       const float* annotations, const int32_t* assign, const int32_t* num_pos, int B, int A, int C, int M,
-                       const K7LossParams* params, float* per_image, float* sums, float* dcls, float* dreg,
-                       void* workspace, size_t workspace_bytes, void* stream) {
+                       const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                       const int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
+                       float* sums, float* dcls, float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
     K7_REQUIRE(cls && reg && annotations && assign && num_pos && params && per_image && sums && workspace,
                "k7_loss: null argument");
     K7_REQUIRE(spec || anchors, "k7_loss: need an anchor spec or an anchor tensor");
     K7_REQUIRE((dcls == nullptr) == (dreg == nullptr), "k7_loss: dcls and dreg must be given together");
     K7_REQUIRE(B > 0 && A > 0 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d", B, A, C, M);
+    K7_REQUIRE(B <= 65535, "k7_loss: B > 65535 not supported");
     K7_REQUIRE(params->mean_divisor > 0, "k7_loss: mean_divisor must be positive");
-    K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(reg) & 15) == 0 &&
-                   (reinterpret_cast<uintptr_t>(assign) & 15) == 0,
-               "k7_loss: cls, reg and assign must be 16-byte aligned");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(reg) & 15) == 0,
+               "k7_loss: cls and reg must be 16-byte aligned");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(ignore_bits) & 15) == 0, "k7_loss: ignore_bits must be 16-byte aligned");
     K7_REQUIRE(!dcls || ((reinterpret_cast<uintptr_t>(dcls) & 15) == 0 && (reinterpret_cast<uintptr_t>(dreg) & 15) == 0),
                "k7_loss: dcls and dreg must be 16-byte aligned");
     if (spec) {
@@ -773,25 +824,24 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const bool grad = dcls != nullptr;
-    const bool pipe = (((unsigned long long)A * C) % 4ull) == 0ull;
 
-    K7PipeGeom GP;
-    K7CompatGeom GC;
-    int rc = pipe ? k7_pipe_geometry(B, A, C, grad, &GP) : k7_compat_geometry(B, A, C, &GC);
+    K7PipeGeom G;
+    int rc = k7_pipe_geometry(B, A, C, grad, &G);
     if (rc) return rc;
-    const unsigned long long slots = pipe ? (unsigned long long)GP.grid * GP.cw : GC.tpi;
+    const uint32_t pipe_slots = (uint32_t)G.grid * (uint32_t)G.cw;
+    const int gx = k7_rows_gx(B, A);
 
-    size_t off_scales, off_partials, off_counter;
-    const size_t need = k7_loss_ws_layout(B, slots, &off_scales, &off_partials, &off_counter);
-    if (workspace_bytes < need) {
-        k7_set_error("k7_loss: workspace %zu < %zu bytes", workspace_bytes, need);
+    const K7LossWs L = k7_loss_ws_layout(B, A, pipe_slots, (size_t)gx);
+    if (workspace_bytes < L.total) {
+        k7_set_error("k7_loss: workspace %zu < %zu bytes", workspace_bytes, L.total);
         return K7_EWORKSPACE;
     }
     unsigned char* ws = static_cast<unsigned char*>(workspace);
     K7_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "k7_loss: workspace must be 256-byte aligned");
-    float2* scales = reinterpret_cast<float2*>(ws + off_scales);
-    float2* partials = reinterpret_cast<float2*>(ws + off_partials);
-    unsigned int* counter = reinterpret_cast<unsigned int*>(ws + off_counter);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws + L.counter);
+    float* pipe_partials = reinterpret_cast<float*>(ws + L.pipe);
+    float* cta_partials = reinterpret_cast<float*>(ws + L.cta);
+    float2* rows_partials = reinterpret_cast<float2*>(ws + L.rows);
 
     K7LossDev P;
     P.alpha = params->alpha;
@@ -808,44 +858,46 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
         P.div[i] = params->target_div[i];
         if (params->target_div[i] != 1.0f) P.use_div = 1;
     }
+    P.mean_div = (float)params->mean_divisor;
     P.yx_targets = params->yx_targets;
+    P.dreg_prezeroed = params->dreg_prezeroed;
     P.B = B; P.A = A; P.C = C; P.M = M;
 
-    K7_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned int), st));
-    // the pipelined kernel writes d(reg) of positive rows only
-    if (grad && pipe && !params->dreg_prezeroed) K7_CUDA(cudaMemsetAsync(dreg, 0, sizeof(float) * 4 * (size_t)B * A, st));
-    k7_loss_scales_kernel<<<(B + 127) / 128, 128, 0, st>>>(num_pos, B, (float)params->mean_divisor, scales);
-    K7_LAUNCH_CHECK();
+    K7_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * ((size_t)B + 1), st));
+    if (!ignore_bits) {   // the caller did not keep k7_match's bitmap: derive it from the assignment words
+        uint32_t* bits = reinterpret_cast<uint32_t*>(ws + L.bits);
+        dim3 grid((A + K7_ROWS_THREADS - 1) / K7_ROWS_THREADS, B);
+        k7_loss_bits_kernel<<<grid, K7_ROWS_THREADS, 0, st>>>(assign, A, (int)G.W, bits);
+        K7_LAUNCH_CHECK();
+        ignore_bits = bits;
+    }
+
+    {
+        auto launch = [&](auto kern) -> int {
+            K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(cls, ignore_bits, num_pos, P, G, pipe_partials,
+                                                                  cta_partials, dcls);
+            return K7_OK;
+        };
+        if (G.slice == 1024)
+            rc = grad ? launch(k7_loss_pipe_kernel<true, 1024>) : launch(k7_loss_pipe_kernel<false, 1024>);
+        else
+            rc = grad ? launch(k7_loss_pipe_kernel<true, 512>) : launch(k7_loss_pipe_kernel<false, 512>);
+        if (rc) return rc;
+        K7_LAUNCH_CHECK();
+    }
 
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     float4* dreg4 = reinterpret_cast<float4*>(dreg);
-#define K7_LOSS_ARGS sp, anchors, box_order, cls, reg, annotations, assign, scales, P
-    if (pipe) {
-#define K7_PIPE_LAUNCH(GR, SP)                                                                                        \
-    do {                                                                                                              \
-        auto kern = k7_loss_pipe_kernel<GR, SP>;                                                                      \
-        K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GP.smem_bytes));         \
-        kern<<<GP.grid, (GP.cw + 1) * 32, GP.smem_bytes, st>>>(K7_LOSS_ARGS, GP, partials, dcls, dreg4);              \
-    } while (0)
-        if (grad) { if (spec) K7_PIPE_LAUNCH(true, true); else K7_PIPE_LAUNCH(true, false); }
-        else      { if (spec) K7_PIPE_LAUNCH(false, true); else K7_PIPE_LAUNCH(false, false); }
-#undef K7_PIPE_LAUNCH
-    } else {
-#define K7_COMPAT_LAUNCH(GR, SP)                                                                                      \
-    do {                                                                                                              \
-        auto kern = k7_loss_compat_kernel<K7_LOSS_TILE, GR, SP>;                                                      \
-        K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GC.smem_bytes));         \
-        kern<<<GC.grid, GC.warps * 32, GC.smem_bytes, st>>>(K7_LOSS_ARGS, GC, partials, dcls, dreg4);                 \
-    } while (0)
-        if (grad) { if (spec) K7_COMPAT_LAUNCH(true, true); else K7_COMPAT_LAUNCH(true, false); }
-        else      { if (spec) K7_COMPAT_LAUNCH(false, true); else K7_COMPAT_LAUNCH(false, false); }
-#undef K7_COMPAT_LAUNCH
-    }
-#undef K7_LOSS_ARGS
-    K7_LAUNCH_CHECK();
-
-    k7_loss_finalize_kernel<<<B, 256, 0, st>>>(partials, num_pos, B, (uint32_t)slots, per_image, sums, counter);
+    dim3 rgrid(gx, B);
+#define K7_ROWS_LAUNCH(GR, SP)                                                                                          \
+    k7_loss_rows_kernel<GR, SP><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, anchors, box_order, cls, reg, annotations, assign, \
+                                                                   num_pos, P, cta_partials, (uint32_t)G.grid, rows_partials, \
+                                                                   counters, per_image, sums, dcls, dreg4)
+    if (grad) { if (spec) K7_ROWS_LAUNCH(true, true); else K7_ROWS_LAUNCH(true, false); }
+    else      { if (spec) K7_ROWS_LAUNCH(false, true); else K7_ROWS_LAUNCH(false, false); }
+#undef K7_ROWS_LAUNCH
     K7_LAUNCH_CHECK();
     return K7_OK;
 }

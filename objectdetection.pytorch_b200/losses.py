@@ -47,10 +47,12 @@ _WS = _Workspace()
 
 
 def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
-          box_order: int = L.BOX_XYXY, debug: bool = False, zero_fill: Optional[torch.Tensor] = None):
-    """Assignment stage.  Returns (assign[B, A(+pad)] int32, num_pos[B] int32[, iou_max, argmax]).
+          box_order: int = L.BOX_XYXY, debug: bool = False, zero_fill: Optional[torch.Tensor] = None,
+          with_bits: bool = False):
+    """Assignment stage.  Returns (assign[B*A] int32, num_pos[B] int32[, iou_max, argmax][, ignore_bits]).
     zero_fill: optional [B,A,4] float32 tensor the kernel fills with zeros on the way (the d(reg)
-    buffer of the loss stage that follows)."""
+    buffer of the loss stage that follows).  with_bits: also return the one-bit-per-anchor ignore
+    bitmap [B, K7_IGNORE_WORDS(A)] int32 that the loss stage streams."""
     L.require_cuda(annotations)
     ann = L.as_f32_contig(annotations)
     B, M = ann.shape[0], ann.shape[1]
@@ -62,25 +64,31 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
         L.require_cuda(anc_t)
     else:
         box_order = spec.box_order
-    # padded so that the streaming kernel may bulk-copy 16-byte multiples
-    assign = torch.empty(B * A + 8, dtype=torch.int32, device=dev)
+    assign = torch.empty(B * A, dtype=torch.int32, device=dev)
     num_pos = torch.empty(B, dtype=torch.int32, device=dev)
     iou_max = torch.empty((B, A), dtype=torch.float32, device=dev) if debug else None
     argmax = torch.empty((B, A), dtype=torch.int32, device=dev) if debug else None
+    bits = torch.empty((B, L.ignore_words(A)), dtype=torch.int32, device=dev) if with_bits else None
     p = L.K7MatchParams(neg_thr, pos_thr)
     with torch.cuda.device(dev):
         L.check(L.lib().k7_match(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
                                  L.ptr(ann), B, A, M, C.byref(p), L.ptr(assign), L.ptr(num_pos),
-                                 L.ptr(iou_max), L.ptr(argmax), L.ptr(zero_fill), L.stream_ptr(dev)), "k7_match")
+                                 L.ptr(iou_max), L.ptr(argmax), L.ptr(zero_fill), L.ptr(bits),
+                                 L.stream_ptr(dev)), "k7_match")
+    out = (assign, num_pos)
     if debug:
-        return assign, num_pos, iou_max, argmax
-    return assign, num_pos
+        out += (iou_max, argmax)
+    if with_bits:
+        out += (bits,)
+    return out
 
 
 def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
-               mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None):
+               mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
+               ignore_bits: Optional[torch.Tensor] = None):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
-    dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a memset pass)."""
+    dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a 16 B/anchor store);
+    ignore_bits: match(with_bits=True)'s bitmap (derived from `assign` by a small kernel when absent)."""
     B, A, Cn = cls.shape
     M = ann.shape[1]
     dev = cls.device
@@ -107,7 +115,7 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
-                            L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(num_pos),
+                            L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits), L.ptr(num_pos),
                             B, A, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), L.ptr(dcls), L.ptr(dreg),
                             L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_loss")
     return per_image, sums, dcls, dreg
@@ -119,7 +127,8 @@ class _FocalLossFn(torch.autograd.Function):
         want_grad = cls.requires_grad or reg.requires_grad
         A = cls.shape[1]
         dreg0 = torch.empty_like(reg) if want_grad else None
-        assign, num_pos = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
+        assign, num_pos, bits = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"],
+                                      zero_fill=dreg0, with_bits=True)
         group = cfg.get("process_group")
         world = 1
         if group is not None or cfg.get("sharded"):
@@ -129,7 +138,7 @@ class _FocalLossFn(torch.autograd.Function):
         per_image, sums, dcls, dreg = loss_stage(
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
-            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0)
+            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0, ignore_bits=bits)
         if world > 1:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective

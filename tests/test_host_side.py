@@ -61,7 +61,7 @@ def test_library_exports_every_declared_symbol():
     lib = C.CDLL(L.LIB_PATH)
     for name in declared:
         assert hasattr(lib, name), name
-    assert L.lib().k7_version() == 1
+    assert L.lib().k7_version() == L.ABI_VERSION
 
 
 def test_struct_layout_matches_header():

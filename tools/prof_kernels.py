@@ -1,0 +1,60 @@
+#!/usr/bin/env python
+"""Run every stage of the hot path a few times on one workload — the target of the ncu captures.
+
+    python tools/prof_kernels.py [workload] [--batch B] [--reps R] [--stages match,loss_fwd,loss_fwd_bwd,detect]
+
+Under ncu (B200_PROFILING.md):
+    ncu --set full --clock-control none --import-source on -k regex:k7_ -c 40 -o gpurun_out/X \
+        python tools/prof_kernels.py c2_effdet_d0_512 --reps 2
+Without ncu it prints CUDA-event times per stage (a sanity check, not a bench number)."""
+import argparse
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import b200det                                    # noqa: E402
+from b200det import losses as BL                  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("workload", nargs="?", default="c2_effdet_d0_512")
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--stages", default="match,loss_fwd,loss_fwd_bwd,detect")
+    args = ap.parse_args()
+    wl = b200det.synth.WORKLOADS[args.workload]
+    B = args.batch or wl.batch
+    dev = torch.device("cuda", 0)
+    cls, reg, ann = b200det.synth.make_inputs(wl, seed=0, device=dev, batch=B)
+    img = torch.empty(B, 3, wl.height, wl.width, device=dev)
+    anc = b200det.Anchors(**wl.anchor_kwargs())(img)
+    A = wl.anchors
+    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
+    dreg0 = torch.empty_like(reg)
+    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
+    stages = {
+        "match": lambda: BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True),
+        "loss_fwd": lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw),
+        "loss_fwd_bwd": lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True,
+                                              dreg_zeroed=dreg0, ignore_bits=bits, **kw),
+        "detect": lambda: b200det.detect(cls, reg, anc, (wl.height, wl.width), sync=False),
+    }
+    for name in args.stages.split(","):
+        fn = stages[name]
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        print(f"{args.workload} B={B} {name}: {e0.elapsed_time(e1) / args.reps * 1e3:.1f} us/call")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Sweep the streaming geometry of k7_loss (K7_WARPS x K7_STAGES) on one workload.
+"""Sweep the streaming geometry of k7_loss (K7_SLICE x K7_WARPS x K7_STAGES) on one workload.
 Usage (GPU box): python tools/tune_loss.py [workload]"""
 import itertools
 import os
@@ -35,20 +35,24 @@ def main():
     img = torch.empty(B, 3, wl.height, wl.width, device=dev)
     anc = b200det.Anchors(**wl.anchor_kwargs())(img)
     A, C, M = wl.anchors, wl.classes, wl.max_gt
-    assign, num_pos = BL.match(anc, ann, A, 0.35, 0.45)
+    dreg0 = torch.empty_like(reg)
+    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
     bf = B * (A * (4 * C + 16) + 20 * M)
     bb = B * (A * (8 * C + 32) + 20 * M)
     print(f"{name} B={B} A={A} C={C}: fwd {bf/1e9:.3f} GB, fwd+bwd {bb/1e9:.3f} GB")
-    for warps, stages in itertools.product((8, 10, 12, 13, 16), (3, 4, 5, 6)):
-        os.environ["K7_WARPS"], os.environ["K7_STAGES"] = str(warps), str(stages)
+    combos = [(512, w, s) for w, s in itertools.product((12, 14, 16), (4, 6, 8))]
+    combos += [(1024, w, s) for w, s in itertools.product((6, 8, 10, 12), (3, 4, 6))]
+    for slice_, warps, stages in combos:
+        os.environ["K7_SLICE"], os.environ["K7_WARPS"], os.environ["K7_STAGES"] = str(slice_), str(warps), str(stages)
         try:
-            f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, **kw))
-            g = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, **kw))
+            f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw))
+            g = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0,
+                                            ignore_bits=bits, **kw))
         except Exception as e:                     # geometry that does not fit
-            print(f"warps={warps:2d} stages={stages}: {e}")
+            print(f"slice={slice_} warps={warps:2d} stages={stages}: {e}")
             continue
-        print(f"warps={warps:2d} stages={stages}: fwd {f*1e3:7.1f} us {bf/f/1e6:7.0f} GB/s | "
+        print(f"slice={slice_:4d} warps={warps:2d} stages={stages}: fwd {f*1e3:7.1f} us {bf/f/1e6:7.0f} GB/s | "
               f"fwd+bwd {g*1e3:7.1f} us {bb/g/1e6:7.0f} GB/s")
 
 
