@@ -101,13 +101,17 @@ struct K7DetectWs {
     uint64_t* kept_key;     // [B][A] sort key of each kept box, in keep order
     float4* kept_box;       // [B][A]
     int32_t* nsel;          // [B] survivors handled by the multi-SM NMS path (-1: fallback image)
-    float4* sbox;           // [B][NCAP] boxes in sorted order
-    unsigned long long* M;  // [B][NCAP][NCAP/64] upper-triangular suppression bitmask
+    float4* sbox;           // [B][cap] boxes in spatial order
+    int32_t* srank;         // [B][cap] rank (position in score order) of the box at each spatial index
+    float4* blk;            // [B][cap/32][2] (min x1, max x2, min y1, max y2), (min area, max area, -, -) per 32 boxes
+    int32_t* work;          // [B] work-item counter of the mask kernel
+    unsigned long long* nz; // [B][cap][nzw] which words of a bitmask row were written
+    unsigned long long* M;  // [B][cap][cap/64] suppression bitmask, sparsely written
     size_t bytes;
     int W32;
+    int cap;                // survivors per image the multi-SM NMS path is sized for
 };
-#define K7_NCAP 2048
-#define K7_NCAP_WORDS (K7_NCAP / 64)
+static int k7_nms_cap(int B, int n_max);
 
 static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     K7DetectWs w;
@@ -132,8 +136,14 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.kept_key = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.kept_box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
     w.nsel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
-    w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * K7_NCAP));
-    w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * K7_NCAP * K7_NCAP_WORDS));
+    w.cap = k7_nms_cap(B, A);
+    const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
+    w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * cap));
+    w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
+    w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * (size_t)B * nbw));
+    w.work = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B));
+    w.nz = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * cap * nzw));
+    w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * cap * nbw));
     w.bytes = o;
     return w;
 }
@@ -866,37 +876,58 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
     }
 }
 
-// ------------------------------------------------------------------ multi-SM NMS for n <= K7_NCAP survivors
-// Round-1 profile: with one CTA per image the IoU bitmask (n^2/2 pair tests) and the greedy scan
-// ran on 64 of 148 SMs and took longer than streaming the whole classification tensor.  For the
-// usual case (a few hundred to 2048 survivors per image) the work is split into three kernels so
-// every SM takes part and the only serial piece is one warp per image:
-//   k7_sort_kernel   per image: survivor ranks (bitmap prefix), key sort, boxes gathered in order
-//   k7_mask_kernel   grid (G, B): 64x64 blocks of the LOWER-triangular suppression bitmask (row i: the
-//                    higher-scored boxes j < i with IoU > thr), written to global memory (L2 resident)
-//   k7_resolve_kernel  one CTA per image: greedy NMS as a parallel fixed point over that bitmask
-// Images with more survivors fall back to k7_sort_nms_kernel (chunked, bitmask in shared memory).
-union K7SortOnlySmem {
-    K7SortSmem sort;
-    unsigned long long bitonic[K7_BITONIC_MAX];
-};
+// ------------------------------------------------------------------ multi-SM NMS for n <= cap survivors
+// Round-1 profiles: with one CTA per image the IoU bitmask (n^2/2 pair tests) and the greedy scan
+// ran on 64 of 148 SMs and took longer than streaming the whole classification tensor; and at
+// EfficientDet-D7 (7 500 survivors per image) even a bitmask built on every SM costs 28 M pair
+// tests per image.  The NMS is therefore three kernels, and the bitmask is SPATIALLY indexed:
+//   k7_sort_kernel   per image: survivor ranks (bitmap prefix), key sort by score (= the visiting
+//                    order "rank"), then a second sort of the ranked boxes by (area class, x1) (=
+//                    the "spatial index" p) with a summary (min x1, max x2, min/max area) of every
+//                    block of 64 consecutive boxes;
+//   k7_mask_kernel   grid (G, B): for every pair of 64-blocks that the summaries cannot rule out
+//                    (x ranges overlap and the areas are within 1/thr of each other - IoU <= the
+//                    area ratio), the 64 x 64 pair tests; row p gets the word of bits q "box q
+//                    overlaps p above thr AND ranks before p".  Only non-zero words are written, each
+//                    flagged in a per-row summary, so the n x n/64 matrix is never initialised or read
+//                    as a whole;
+//   k7_resolve_kernel  one CTA per image: greedy NMS as a parallel fixed point over those words.
+// Which boxes share a 64-bit word is irrelevant to the result: every bit still says "a higher
+// scored box overlaps me", so the kept set is exactly torchvision.ops.nms's.  Images with more
+// survivors than the workspace's cap fall back to k7_sort_nms_kernel (chunked, one CTA).
+#define K7_SORT_MAX 16384                       // largest cap: 128 KB of keys in shared memory
+#define K7_NZW_MAX (K7_SORT_MAX / 64 / 64)      // u64 words of the per-row summary
+#define K7_CELLS_MAX 4096                       // grid cells of the spatial order, all area binades together
+
+// upper bound on survivors per image the multi-SM path is sized for (multiple of 64)
+static int k7_nms_cap(int B, int n_max) {
+    long long cap = ((long long)n_max + 63) / 64 * 64;
+    if (cap > K7_SORT_MAX) cap = K7_SORT_MAX;
+    // the bitmask is cap^2/8 bytes per image (sparsely touched): keep the batch under 4 GB
+    const double budget = 4.0 * 1024 * 1024 * 1024;
+    while (cap > 2048 && (double)cap * (double)cap / 8.0 * (double)B > budget) cap -= 64;
+    return (int)cap;
+}
 
 // Per image: the survivor list is born here.  The score kernel only marked survivors in a bitmap
 // (and left score / label / box by anchor id); this kernel takes the exclusive popcount prefix of
 // the bitmap (= the index torchvision.ops.nms would return for each survivor), turns every set bit
 // into a 64-bit key (score descending | anchor ascending) and sorts.
 //   bits == nullptr: stand-alone NMS, keys0 already holds surv_count[b] keys.
-// Outputs: surv_count[b]; nsel[b] = survivors the mask/resolve kernels must process, or -1 when the
-// image has more than K7_NCAP of them (then its unsorted keys are left in keys0 for the fallback).
+// Outputs: surv_count[b]; keys1 = keys in rank order; sbox / srank / blk / nz in spatial order;
+// nsel[b] = survivors the mask/resolve kernels must process, or -1 when the image has more than
+// `cap` of them (then its unsorted keys are left in keys0 for the fallback).
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_sort_kernel(int A, int W32, int pre_topk, int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
+k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
                int32_t* __restrict__ wprefix, const float* __restrict__ score_ws, uint64_t* __restrict__ keys0,
                uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws, float4* __restrict__ sbox,
-               int32_t* __restrict__ nsel) {
+               int32_t* __restrict__ srank, float4* __restrict__ blk, unsigned long long* __restrict__ nz,
+               int32_t* __restrict__ nsel, int32_t* __restrict__ work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    K7SortOnlySmem& S = *reinterpret_cast<K7SortOnlySmem*>(smem_raw);
+    unsigned long long* sk = reinterpret_cast<unsigned long long*>(smem_raw);
     __shared__ int s_carry;
     __shared__ unsigned int s_wtot[32];
+    __shared__ float4 s_wsum[32];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t ob = (size_t)b * A;
     int n_all;
@@ -928,8 +959,8 @@ k7_sort_kernel(int A, int W32, int pre_topk, int32_t* __restrict__ surv_count, c
     } else {
         n_all = surv_count[b];
     }
-    const bool small = n_all <= K7_NCAP;
-    const int N = k7_bitonic_size(n_all);
+    const bool small = n_all <= cap;
+    int N = k7_bitonic_size(n_all);
     if (bits) {
         // one key per set bit, written at its rank: shared memory (small image) or keys0 (fallback image)
         for (int w = tid; w < W32; w += K7_NMS_THREADS) {
@@ -939,199 +970,480 @@ k7_sort_kernel(int A, int W32, int pre_topk, int32_t* __restrict__ surv_count, c
                 const int a = (w << 5) + __ffs(word) - 1;
                 word &= word - 1;
                 const uint64_t key = ((uint64_t)k7_score_key_desc(score_ws[ob + a]) << 32) | (uint32_t)a;
-                if (small) S.bitonic[slot] = key; else keys0[ob + slot] = key;
+                if (small) sk[slot] = key; else keys0[ob + slot] = key;
                 ++slot;
             }
         }
         if (small)
-            for (int i = n_all + tid; i < N; i += K7_NMS_THREADS) S.bitonic[i] = ~0ull;
+            for (int i = n_all + tid; i < N; i += K7_NMS_THREADS) sk[i] = ~0ull;
     } else if (small) {
-        for (int i = tid; i < N; i += K7_NMS_THREADS) S.bitonic[i] = (i < n_all) ? keys0[ob + i] : ~0ull;
+        for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < n_all) ? keys0[ob + i] : ~0ull;
     }
     if (!small) {
         if (tid == 0) nsel[b] = -1;
         return;
     }
     __syncthreads();
-    k7_bitonic_sort_smem(S.bitonic, N);
+    k7_bitonic_sort_smem(sk, N);   // ends with a barrier
     int n = n_all;
     if (pre_topk > 0 && n > pre_topk) n = pre_topk;
-    for (int i = tid; i < n; i += K7_NMS_THREADS) {
-        const uint64_t key = S.bitonic[i];
-        keys1[ob + i] = key;
-        sbox[(size_t)b * K7_NCAP + i] = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
-    }
     if (tid == 0) nsel[b] = n;
+
+    // ---- spatial order: boxes of one area binade, binned on a grid whose cells hold ~16 of them,
+    // cells visited row by row in alternating direction (consecutive cells always touch).  Any
+    // order gives the same NMS result; this one makes 64 consecutive boxes neighbours in the image
+    // (about four cells in a row), so most pairs of 64-blocks are ruled out by their summaries in
+    // k7_mask_kernel.
+    __shared__ int s_cls[256], s_base[257], s_g[256];
+    __shared__ int s_cell[K7_CELLS_MAX + 1];
+    __shared__ float s_bnd[4];
+    if (tid < 256) s_cls[tid] = 0;
+    for (int c = tid; c <= K7_CELLS_MAX; c += K7_NMS_THREADS) s_cell[c] = 0;
+    __syncthreads();
+    float bx0 = 3.0e38f, bx1 = -3.0e38f, by0 = 3.0e38f, by1 = -3.0e38f;
+    for (int i = tid; i < n; i += K7_NMS_THREADS) {
+        const uint64_t key = sk[i];
+        keys1[ob + i] = key;
+        const float4 bx = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
+        const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
+        atomicAdd(&s_cls[(__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu], 1);   // binade of the area
+        bx0 = fminf(bx0, bx.x); bx1 = fmaxf(bx1, bx.x);
+        by0 = fminf(by0, bx.y); by1 = fmaxf(by1, bx.y);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+        bx1 = fmaxf(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+        by0 = fminf(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+        by1 = fmaxf(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+    }
+    if (lane == 0) s_wsum[warp] = make_float4(bx0, bx1, by0, by1);
+    __syncthreads();
+    if (warp == 0) {
+        float4 v = s_wsum[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            v.x = fminf(v.x, __shfl_xor_sync(0xffffffffu, v.x, o));
+            v.y = fmaxf(v.y, __shfl_xor_sync(0xffffffffu, v.y, o));
+            v.z = fminf(v.z, __shfl_xor_sync(0xffffffffu, v.z, o));
+            v.w = fmaxf(v.w, __shfl_xor_sync(0xffffffffu, v.w, o));
+        }
+        if (lane == 0) {
+            s_bnd[0] = v.x;
+            s_bnd[1] = (v.y > v.x) ? 1.0f / (v.y - v.x) : 0.0f;
+            s_bnd[2] = v.z;
+            s_bnd[3] = (v.w > v.z) ? 1.0f / (v.w - v.z) : 0.0f;
+        }
+    }
+    // grid side per binade: g*g cells of ~16 boxes; sum of g*g <= n/16 + 2*sqrt(16n) + 256 <= K7_CELLS_MAX
+    if (tid < 256) {
+        const int c = s_cls[tid];
+        int g = 0;
+        if (c > 0) {
+            g = (int)ceilf(sqrtf((float)c * (1.0f / 16.0f)));
+            g = max(1, min(g, 32));
+        }
+        s_g[tid] = g;
+        int inc = g * g;
+        const int v = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        s_base[tid] = inc - v;
+        if (lane == 31) s_wtot[warp] = (unsigned)inc;
+    }
+    __syncthreads();
+    if (tid < 256) {
+        int off = 0;
+        for (int w = 0; w < warp; ++w) off += (int)s_wtot[w];
+        s_base[tid] += off;
+    }
+    __syncthreads();
+    // cell of every box (kept in sk[i]) and the cell histogram
+    for (int i = tid; i < n; i += K7_NMS_THREADS) {
+        const uint64_t key = sk[i];
+        const float4 bx = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
+        const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
+        const int c8 = (int)((__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu);
+        const int g = s_g[c8];
+        int cx = (int)((bx.x - s_bnd[0]) * s_bnd[1] * (float)g), cy = (int)((bx.y - s_bnd[2]) * s_bnd[3] * (float)g);
+        cx = max(0, min(cx, g - 1));   // also sends NaN to cell 0
+        cy = max(0, min(cy, g - 1));
+        if (cy & 1) cx = g - 1 - cx;   // odd rows run backwards
+        const int cell = min(s_base[c8] + cy * g + cx, K7_CELLS_MAX - 1);
+        sk[i] = (unsigned long long)cell;
+        atomicAdd(&s_cell[cell], 1);
+    }
+    __syncthreads();
+    // exclusive prefix over the cells (K7_CELLS_MAX = 4 * 1024 threads: four cells per thread)
+    {
+        static_assert(K7_CELLS_MAX == 4 * K7_NMS_THREADS, "four cells per thread");
+        int c[4], inc = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            c[k] = s_cell[4 * tid + k];
+            inc += c[k];
+        }
+        const int v = inc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_wtot[warp] = (unsigned)inc;
+        __syncthreads();
+        int run = inc - v;
+        for (int w = 0; w < warp; ++w) run += (int)s_wtot[w];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            s_cell[4 * tid + k] = run;
+            run += c[k];
+        }
+    }
+    __syncthreads();
+    // scatter: the order inside a cell is whatever the atomics give (it does not affect the result)
+    const size_t oc = (size_t)b * cap;
+    const int nzw = (cap / 64 + 63) / 64;
+    for (int i = tid; i < n; i += K7_NMS_THREADS) {
+        const int p = atomicAdd(&s_cell[(int)sk[i]], 1);
+        const uint64_t key = keys1[ob + i];   // written above by this thread
+        sbox[oc + p] = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
+        srank[oc + p] = i;
+        for (int z = 0; z < nzw; ++z) nz[(oc + p) * nzw + z] = 0ull;
+    }
+    if (tid == 0) work[b] = 0;
+    __syncthreads();
+
+    // ---- summaries of every 32 consecutive boxes: x range, y range, area range
+    const int n32 = (n + 31) & ~31;
+    for (int p0 = 0; p0 < n32; p0 += K7_NMS_THREADS) {
+        const int p = p0 + tid;
+        if (p0 + (warp << 5) >= n32) break;   // warp-uniform
+        float x1 = 3.0e38f, x2 = -3.0e38f, y1 = 3.0e38f, y2 = -3.0e38f, amin = 3.0e38f, amax = -3.0e38f;
+        if (p < n) {
+            const float4 bx = __ldcg(sbox + oc + p);   // written by this CTA before the barrier
+            const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
+            x1 = bx.x; y1 = bx.y; x2 = bx.z; y2 = bx.w; amin = area; amax = area;   // a NaN drops out of fminf/fmaxf
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            x1 = fminf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+            x2 = fmaxf(x2, __shfl_xor_sync(0xffffffffu, x2, o));
+            y1 = fminf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+            y2 = fmaxf(y2, __shfl_xor_sync(0xffffffffu, y2, o));
+            amin = fminf(amin, __shfl_xor_sync(0xffffffffu, amin, o));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        }
+        if (lane == 0) {
+            float4* o = blk + 2 * ((size_t)b * (cap / 32) + (p >> 5));
+            o[0] = make_float4(x1, x2, y1, y2);
+            o[1] = make_float4(amin, amax, 0.0f, 0.0f);
+        }
+    }
 }
 
-// The exact decision of torchvision.ops.nms, inter / (area_i + area_j - inter) > thr, with the IEEE
-// division only for pairs that can reach the threshold: for u > 0, fl(inter/u) > thr implies
-// inter > thr*u*(1 - 2^-24) >= fl(thr_lo*u) with thr_lo = thr*(1 - 2^-20), so a pair failing
-// inter > fl(thr_lo*u) is certainly not suppressed.  Degenerate unions (u <= 0) pass the filter and
-// get the division, NaN fails both, as in the reference.
-__device__ __forceinline__ bool k7_nms_suppress_fast(const K7Box& a, float area_a, const float4 b, float area_b,
-                                                     float thr, float thr_lo) {
+// The exact decision of torchvision.ops.nms is fl(inter / (area_i + area_j - inter)) > thr.  The
+// 64 x 64 pair loop only runs a cheap FILTER that no suppressed pair can fail:
+//     w > 0, h > 0  and  inter > fl(c*area_i) + fl(c*area_j),   c = thr/(1+thr) * (1 - 1e-5).
+// Proof: a suppressed pair has w, h > 0 (else inter is 0 or NaN and the quotient is not > thr >= 0),
+// hence a positive union u, and fl(inter/u) > thr gives inter > thr*u*(1 - 2^-24), i.e.
+// inter*(1 + thr') > thr'*(area_i + area_j)*(1 - 2^-23) with thr' = thr*(1 - 2^-23); the float32
+// roundings of the two products and the sum are below 2^-22 relative, far inside the 1e-5 margin.
+// Pairs that pass (about 1 in 50 overlapping ones) are re-tested exactly, division included.
+__device__ __forceinline__ bool k7_nms_filter(const K7Box& a, float ca, const float4 b, float cb) {
     const float w = K7_FSUB(fminf(a.x2, b.z), fmaxf(a.x1, b.x));
     const float h = K7_FSUB(fminf(a.y2, b.w), fmaxf(a.y1, b.y));
-    const float inter = K7_FMUL(w, h);
-    const float u = K7_FSUB(K7_FADD(area_a, area_b), inter);
-    bool res = false;
-    // w,h <= 0: inter == 0 (or NaN): quotient 0 or NaN, never > thr >= 0
-    if ((w > 0.0f) && (h > 0.0f) && (inter > K7_FMUL(thr_lo, u))) res = K7_FDIV(inter, u) > thr;   // ~1 pair in 50
-    return res;
+    return (w > 0.0f) && (h > 0.0f) && (K7_FMUL(w, h) > K7_FADD(ca, cb));
+}
+__device__ __forceinline__ bool k7_nms_suppress_exact(const K7Box& a, float area_a, const float4 b, float area_b,
+                                                      float thr) {
+    const K7Box o = {b.x, b.y, b.z, b.w};
+    return k7_nms_suppress(a, area_a, o, area_b, thr);
 }
 
+// Summary test of two sets of boxes: can they hold a pair with IoU > thr?  Exact in the "no"
+// direction: (x, y) if min x1 of one set >= max x2 of the other (same for y), every pair has a
+// non-positive intersection width -> overlap 0; (area) a pair with intersection > 0 has
+// IoU <= min(area)/max(area), so sets whose areas differ by more than thr (1e-4 margin against
+// float32 rounding) hold no pair above thr.  c_area == 0 (thr == 0) disables the area test.
+struct K7Sum {
+    float4 r;   // min x1, max x2, min y1, max y2
+    float4 a;   // min area, max area
+};
+__device__ __forceinline__ K7Sum k7_sum_load(const float4* __restrict__ bs, int i32) {
+    K7Sum s;
+    s.r = __ldg(bs + 2 * i32);
+    s.a = __ldg(bs + 2 * i32 + 1);
+    return s;
+}
+__device__ __forceinline__ bool k7_sum_may_overlap(const K7Sum& p, const K7Sum& q, float c_area) {
+    return (q.r.x < p.r.y) && (p.r.x < q.r.y) && (q.r.z < p.r.w) && (p.r.z < q.r.w) &&
+           !(q.a.y < c_area * p.a.x) && !(p.a.y < c_area * q.a.x);
+}
+
+// A group of 64 threads (two warps) works on a row-block: thread t keeps box p = 64*rb + t in
+// registers.  Candidate column-blocks cb <= rb are found with the 32-box summaries (64 at a time,
+// one per thread, ballots); for every candidate the group stages the 64 column boxes in shared
+// memory and each warp runs its 32 x 32 sub-blocks that the summaries do not rule out: 32 or 64
+// filter tests per thread, exact re-test of the few pairs that pass.  Every unordered pair is
+// tested ONCE: an overlap found by thread p sets bit q in row p when q ranks before p, otherwise
+// bit p in row q (collected per column in shared memory and written by thread q afterwards).
 #define K7_MASK_THREADS 256
+#define K7_MASK_GROUPS (K7_MASK_THREADS / 64)
 __global__ void __launch_bounds__(K7_MASK_THREADS)
-k7_mask_kernel(float thr, const int32_t* __restrict__ nsel, const float4* __restrict__ sbox,
-               unsigned long long* __restrict__ M) {
-    __shared__ float4 cbox[K7_MASK_THREADS / 64][64];
-    __shared__ float carea[K7_MASK_THREADS / 64][64];
+k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float4* __restrict__ sbox,
+               const int32_t* __restrict__ srank, const float4* __restrict__ blk, unsigned long long* __restrict__ nz,
+               unsigned long long* __restrict__ M, int32_t* __restrict__ work) {
+    __shared__ float4 cbox[K7_MASK_GROUPS][64];
+    __shared__ float carea[K7_MASK_GROUPS][64];
+    __shared__ int crank[K7_MASK_GROUPS][64];
+    __shared__ unsigned long long tword[K7_MASK_GROUPS][64];
+    __shared__ unsigned int cand[K7_MASK_GROUPS][2];
+    __shared__ int s_item[K7_MASK_GROUPS];
     const int b = blockIdx.y;
     const int n = nsel[b];
     if (n <= 0) return;
-    const int nw = (n + 63) >> 6;
-    const int pairs = nw * (nw + 1) / 2;
-    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63;
-    const int groups = gridDim.x * (K7_MASK_THREADS / 64);
-    const float thr_lo = thr * (1.0f - 9.5367431640625e-7f);
-    const float4* bx = sbox + (size_t)b * K7_NCAP;
-    for (int p0 = blockIdx.x * (K7_MASK_THREADS / 64); p0 < pairs; p0 += groups) {   // block-uniform trip count
-        int p = p0 + grp, rb = 0;
-        const bool live = p < pairs;
-        if (live)
-            while (p > rb) {   // row-block rb owns words 0..rb (the boxes that come BEFORE its rows)
-                p -= rb + 1;
-                ++rb;
-            }
-        const int w = p, col = w * 64 + t;   // p is now the word index inside row-block rb: w <= rb
-        __syncthreads();
-        if (live && col < n) {
-            const float4 c = __ldg(bx + col);
-            cbox[grp][t] = c;
-            carea[grp][t] = k7_area(c.x, c.y, c.z, c.w);
-        }
-        __syncthreads();
+    const int nb = (n + 63) >> 6, n32 = (n + 31) >> 5;
+    const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
+    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63, lane = threadIdx.x & 31, half = t >> 5;
+    const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);   // filter constant, see k7_nms_filter
+    const float c_area = thr * (1.0f - 1e-4f);
+    const size_t oc = (size_t)b * cap;
+    const float4* bx = sbox + oc;
+    const float4* bs = blk + 2 * (size_t)b * (cap >> 5);
+    const int bar_id = 1 + grp;
+    // work item = (row-block, share of its candidate column-blocks), handed out by a per-image counter
+    const int csplit = nb >= 64 ? 2 : (nb >= 16 ? 4 : 8);
+    const int items = nb * csplit;
+    for (;;) {
+        if (t == 0) s_item[grp] = atomicAdd(work + b, 1);
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+        const int wi = s_item[grp];
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+        if (wi >= items) break;   // group-uniform
+        // heavy row-blocks (many column-blocks below them) first
+        const int rb = nb - 1 - wi / csplit, sub = wi % csplit;
+        int turn = 0;
         const int row = rb * 64 + t;
-        if (live && row < n) {
-            const float4 mb = __ldg(bx + row);
-            const K7Box me = {mb.x, mb.y, mb.z, mb.w};
-            const float marea = k7_area(mb.x, mb.y, mb.z, mb.w);
-            unsigned long long word = 0ull;
-            const int jend = min(64, row - w * 64);   // columns j < row only
-#pragma unroll 4
-            for (int j = 0; j < jend; ++j)
-                word |= (unsigned long long)k7_nms_suppress_fast(me, marea, cbox[grp][j], carea[grp][j], thr, thr_lo) << j;
-            M[((size_t)b * K7_NCAP + row) * K7_NCAP_WORDS + w] = word;
+        const bool rlive = row < n;
+        const float4 mb = rlive ? __ldg(bx + row) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const K7Box me = {mb.x, mb.y, mb.z, mb.w};
+        const float marea = k7_area(mb.x, mb.y, mb.z, mb.w);
+        const float mca = K7_FMUL(c_flt, marea);
+        const int mrank = rlive ? __ldg(srank + oc + row) : -1;
+        // summaries of the two halves of the row-block; rmine = the half this warp owns
+        const K7Sum r0 = k7_sum_load(bs, 2 * rb);
+        const bool has_r1 = 2 * rb + 1 < n32;
+        const K7Sum r1 = has_r1 ? k7_sum_load(bs, 2 * rb + 1) : r0;
+        const K7Sum rmine = half ? r1 : r0;
+        for (int c0 = 0; c0 <= rb; c0 += 64) {
+            // which of column-blocks c0..c0+63 (<= rb) can hold a pair above thr with this row-block?
+            const int cbt = c0 + t;
+            bool ok = false;
+            if (cbt <= rb) {
+                const K7Sum q0 = k7_sum_load(bs, 2 * cbt);
+                ok = k7_sum_may_overlap(r0, q0, c_area) || (has_r1 && k7_sum_may_overlap(r1, q0, c_area));
+                if (2 * cbt + 1 < n32) {
+                    const K7Sum q1 = k7_sum_load(bs, 2 * cbt + 1);
+                    ok = ok || k7_sum_may_overlap(r0, q1, c_area) || (has_r1 && k7_sum_may_overlap(r1, q1, c_area));
+                }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) cand[grp][half] = bal;
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+            unsigned long long cm = (unsigned long long)cand[grp][0] | ((unsigned long long)cand[grp][1] << 32);
+            while (cm) {   // group-uniform
+                const int cb = c0 + __ffsll((long long)cm) - 1;
+                cm &= cm - 1ull;
+                if (turn++ % csplit != sub) continue;
+                const int col = cb * 64 + t;
+                const bool diag = cb == rb;
+                asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // previous column-block fully consumed
+                if (col < n) {
+                    const float4 c = __ldg(bx + col);
+                    cbox[grp][t] = c;
+                    carea[grp][t] = K7_FMUL(c_flt, k7_area(c.x, c.y, c.z, c.w));
+                    crank[grp][t] = __ldg(srank + oc + col);
+                }
+                tword[grp][t] = 0ull;
+                asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+                const int jend = min(64, n - cb * 64);
+                if (rlive && (!half || has_r1)) {
+                    uint32_t flo = 0u, fhi = 0u;   // pairs that pass the filter
+                    // warp-uniform: this warp's 32 rows against each half of the column-block
+                    if (k7_sum_may_overlap(rmine, k7_sum_load(bs, 2 * cb), c_area)) {
+                        const int je = min(32, jend);
+                        if (je == 32) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) flo |= 1u << j;
+                        } else {
+                            for (int j = 0; j < je; ++j)
+                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) flo |= 1u << j;
+                        }
+                    }
+                    if (jend > 32 && k7_sum_may_overlap(rmine, k7_sum_load(bs, 2 * cb + 1), c_area)) {
+                        if (jend == 64) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j)
+                                if (k7_nms_filter(me, mca, cbox[grp][j + 32], carea[grp][j + 32])) fhi |= 1u << j;
+                        } else {
+                            for (int j = 32; j < jend; ++j)
+                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) fhi |= 1u << (j - 32);
+                        }
+                    }
+                    unsigned long long f = (unsigned long long)flo | ((unsigned long long)fhi << 32);
+                    unsigned long long word = 0ull;
+                    while (f) {   // exact test; the box visited earlier suppresses the other one
+                        const int j = __ffsll((long long)f) - 1;
+                        f &= f - 1ull;
+                        const float4 c = cbox[grp][j];
+                        if (!k7_nms_suppress_exact(me, marea, c, k7_area(c.x, c.y, c.z, c.w), thr)) continue;
+                        if (crank[grp][j] < mrank)
+                            word |= 1ull << j;
+                        else if (!diag)   // in a diagonal block thread q meets this pair itself
+                            atomicOr(&tword[grp][j], 1ull << t);
+                    }
+                    if (word) {
+                        M[(oc + row) * nbw + cb] = word;
+                        atomicOr(nz + (oc + row) * nzw + (cb >> 6), 1ull << (cb & 63));
+                    }
+                }
+                if (!diag) {   // group-uniform: the transposed bits, one column box per thread
+                    asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+                    const unsigned long long tw = tword[grp][t];
+                    if (tw) {
+                        M[(oc + col) * nbw + rb] = tw;
+                        atomicOr(nz + (oc + col) * nzw + (rb >> 6), 1ull << (rb & 63));
+                    }
+                }
+            }
+            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // cand[] is rewritten by the next round
         }
     }
 }
 
-// Greedy NMS as a fixed point, one CTA per image.  M[i] holds the boxes j < i (higher score) that
-// overlap box i above the threshold.  Box i is REMOVED as soon as one of them is known KEPT, and
-// KEPT as soon as all of them are known removed; the lowest undecided box can always be decided,
-// so the iteration ends, and by induction over i its result is exactly the sequential greedy
-// answer of torchvision.ops.nms.  The kept/removed sets only grow, so threads may read them
-// while others update them; a round costs one barrier.  Dependency chains between overlapping
-// boxes are short, so a handful of rounds replace the n-step sequential scan.
+// Greedy NMS as a fixed point, one CTA per image.  Row p holds the boxes q that overlap box p
+// above the threshold and rank before it.  Box p is REMOVED as soon as one of them is known KEPT,
+// and KEPT as soon as all of them are known removed; the undecided box of lowest rank can always be
+// decided, so the iteration ends, and by induction over the rank its result is exactly the
+// sequential greedy answer of torchvision.ops.nms.  The kept/removed sets only grow, so threads may
+// read them while others update them; a round costs one barrier.  Dependency chains between
+// overlapping boxes are short, so a handful of rounds replace the n-step sequential scan; rows
+// without a flagged word (most) are kept in round 0 without touching the matrix.
 #define K7_RESOLVE_THREADS 1024
+#define K7_RESOLVE_PER (K7_SORT_MAX / K7_RESOLVE_THREADS)
 __global__ void __launch_bounds__(K7_RESOLVE_THREADS)
-k7_resolve_kernel(int A, int max_det, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
+k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
                   const uint64_t* __restrict__ sorted_keys, const float4* __restrict__ sbox,
+                  const int32_t* __restrict__ srank, const unsigned long long* __restrict__ nz,
                   const unsigned long long* __restrict__ M, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
                   int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out) {
-    __shared__ unsigned long long s_kept[K7_NCAP_WORDS], s_rem[K7_NCAP_WORDS];
-    __shared__ int s_prefix[K7_NCAP_WORDS + 1];
+    constexpr int WMAX = K7_SORT_MAX / 64;
+    __shared__ unsigned long long s_kept[WMAX], s_rem[WMAX], s_krank[WMAX];
+    __shared__ int s_prefix[WMAX + 1];
     __shared__ int s_undecided;
     const int b = blockIdx.x, tid = threadIdx.x;
     const int n = nsel[b];
     if (n < 0) return;   // fallback image
-    const size_t ob = (size_t)b * A;
-    const unsigned long long* Mb = M + (size_t)b * K7_NCAP * K7_NCAP_WORDS;
-    if (tid < K7_NCAP_WORDS) s_kept[tid] = s_rem[tid] = 0ull;
-    constexpr int PER = K7_NCAP / K7_RESOLVE_THREADS;
-    // Round 0 reads the whole row once and remembers which of its words are non-zero (most boxes
-    // overlap few higher-scored ones); later rounds only revisit those.
-    uint32_t nz[PER];
-    bool open_[PER];
+    const size_t ob = (size_t)b * A, oc = (size_t)b * cap;
+    const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
+    const int nw = (n + 63) >> 6;
+    for (int w = tid; w < WMAX; w += K7_RESOLVE_THREADS) s_kept[w] = s_rem[w] = s_krank[w] = 0ull;
     __syncthreads();
+    uint32_t open_ = 0u;   // bit k: row tid + k*1024 is still undecided
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-        const int i = tid + k * K7_RESOLVE_THREADS;
-        nz[k] = 0u;
-        open_[k] = i < n;
-        if (!open_[k]) continue;
-        const int wi = i >> 6;
-        const unsigned long long* row = Mb + (size_t)i * K7_NCAP_WORDS;
-        for (int w = 0; w <= wi; ++w)
-            if (__ldg(row + w) != 0ull) nz[k] |= 1u << w;
-        if (nz[k] == 0u) {   // nothing above it overlaps: kept
-            atomicOr(&s_kept[wi], 1ull << (i & 63));
-            open_[k] = false;
-        }
+    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        const int p = tid + k * K7_RESOLVE_THREADS;
+        if (p >= n) continue;
+        unsigned long long any = 0ull;
+        for (int z = 0; z < nzw; ++z) any |= __ldcg(nz + (oc + p) * nzw + z);
+        if (any == 0ull)
+            atomicOr(&s_kept[p >> 6], 1ull << (p & 63));   // nothing ranked before it overlaps: kept
+        else
+            open_ |= 1u << k;
     }
-    for (int round = 0; round < K7_NCAP; ++round) {
+    for (int round = 0; round < K7_SORT_MAX; ++round) {
         if (tid == 0) s_undecided = 0;
         __syncthreads();
-        bool still = false;
-#pragma unroll
-        for (int k = 0; k < PER; ++k) {
-            if (!open_[k]) continue;
-            const int i = tid + k * K7_RESOLVE_THREADS;
-            const int wi = i >> 6;
-            const unsigned long long* row = Mb + (size_t)i * K7_NCAP_WORDS;
+        uint32_t o = open_;
+        while (o) {
+            const int k = __ffs(o) - 1;
+            o &= o - 1u;
+            const int p = tid + k * K7_RESOLVE_THREADS;
+            const unsigned long long* row = M + (oc + p) * nbw;
             bool any_kept = false, all_removed = true;
-            uint32_t m = nz[k];
-            while (m) {
-                const int w = __ffs(m) - 1;
-                m &= m - 1;
-                const unsigned long long l = __ldg(row + w);
-                const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
-                const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
-                any_kept |= (l & kp) != 0ull;
-                all_removed &= (l & ~rm) == 0ull;
+            for (int z = 0; z < nzw; ++z) {
+                unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
+                while (m) {
+                    const int w = (z << 6) + __ffsll((long long)m) - 1;
+                    m &= m - 1ull;
+                    const unsigned long long l = __ldcg(row + w);
+                    const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
+                    const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
+                    any_kept |= (l & kp) != 0ull;
+                    all_removed &= (l & ~rm) == 0ull;
+                }
             }
             if (any_kept) {
-                atomicOr(&s_rem[wi], 1ull << (i & 63));
-                open_[k] = false;
+                atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
+                open_ &= ~(1u << k);
             } else if (all_removed) {
-                atomicOr(&s_kept[wi], 1ull << (i & 63));
-                open_[k] = false;
-            } else {
-                still = true;
+                atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
+                open_ &= ~(1u << k);
             }
         }
-        if (still) s_undecided = 1;
+        if (open_) s_undecided = 1;
         __syncthreads();
         if (s_undecided == 0) break;
         __syncthreads();
     }
-    // compact the kept set in sorted order
-    if (tid == 0) {
-        int run = 0;
-        for (int w = 0; w < K7_NCAP_WORDS; ++w) {
-            s_prefix[w] = run;
-            run += __popcll(s_kept[w]);
+    // kept set by rank, then compaction in rank (= visiting) order
+#pragma unroll
+    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        const int p = tid + k * K7_RESOLVE_THREADS;
+        if (p >= n) continue;
+        if ((s_kept[p >> 6] >> (p & 63)) & 1ull) {
+            const int r = srank[oc + p];
+            atomicOr(&s_krank[r >> 6], 1ull << (r & 63));
         }
-        s_prefix[K7_NCAP_WORDS] = run;
+    }
+    __syncthreads();
+    if (tid < 32) {   // exclusive prefix of the popcounts of s_krank[0..nw)
+        int carry = 0;
+        for (int w0 = 0; w0 < nw; w0 += 32) {
+            const int w = w0 + tid;
+            const int v = (w < nw) ? __popcll(s_krank[w]) : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (tid >= o) inc += t;
+            }
+            if (w < nw) s_prefix[w] = carry + inc - v;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (tid == 0) s_prefix[nw] = carry;
     }
     __syncthreads();
     const int budget = max_det > 0 ? max_det : 0x7fffffff;
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-        const int i = tid + k * K7_RESOLVE_THREADS;
-        if (i >= n) continue;
-        const unsigned long long kw = s_kept[i >> 6];
-        if (!((kw >> (i & 63)) & 1ull)) continue;
-        const int pos = s_prefix[i >> 6] + __popcll(kw & ((1ull << (i & 63)) - 1ull));
+    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        const int p = tid + k * K7_RESOLVE_THREADS;
+        if (p >= n) continue;
+        if (!((s_kept[p >> 6] >> (p & 63)) & 1ull)) continue;
+        const int r = srank[oc + p];
+        const int pos = s_prefix[r >> 6] + __popcll(s_krank[r >> 6] & ((1ull << (r & 63)) - 1ull));
         if (pos >= budget) continue;
-        const uint64_t key = sorted_keys[ob + i];
+        const uint64_t key = sorted_keys[ob + r];
         kept_key[ob + pos] = key;
-        kept_box[ob + pos] = sbox[(size_t)b * K7_NCAP + i];
+        kept_box[ob + pos] = sbox[oc + p];
         if (keep_idx_out) keep_idx_out[pos] = (int64_t)(uint32_t)(key & 0xffffffffull);
     }
     if (tid == 0) {
-        const int kc = min(s_prefix[K7_NCAP_WORDS], budget);
+        const int kc = min(s_prefix[nw], budget);
         kept_count[b] = kc;
         if (counts_out) {
             counts_out[2 * b + 0] = surv_count[b];
@@ -1241,29 +1553,33 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
         if (rc) return rc;
     }
 
-    // NMS: images with <= K7_NCAP survivors go through sort -> mask (all SMs) -> scan (one warp each),
+    // NMS: images with <= cap survivors go through sort -> mask (all SMs) -> resolve (one CTA each),
     // the others through the chunked single-CTA kernel.  Each kernel decides per image on the device.
     {
-        const size_t smem_sort = sizeof(K7SortOnlySmem);
+        size_t smem_sort = 64 * 8;
+        while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;   // bitonic size of the largest image
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.surv_count, w.bits, w.wprefix,
-                                                             w.score, w.keys0, w.keys1, w.box, w.sbox, w.nsel);
+        k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.cap, w.surv_count, w.bits,
+                                                             w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
+                                                             w.blk, w.nz, w.nsel, w.work);
         K7_LAUNCH_CHECK();
-        int gx = (4 * k7_sm_count() + B - 1) / B;   // about four CTAs per SM over the batch
-        const int gx_max = (K7_NCAP_WORDS * (K7_NCAP_WORDS + 1) / 2 + 3) / 4;
+        int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
+        const int gx_max = (w.cap / 64 + K7_MASK_GROUPS - 1) / K7_MASK_GROUPS * 4;
         if (gx > gx_max) gx = gx_max;
         if (gx < 1) gx = 1;
-        k7_mask_kernel<<<dim3(gx, B), K7_MASK_THREADS, 0, st>>>(params->iou_thr, w.nsel, w.sbox, w.M);
+        k7_mask_kernel<<<dim3(gx, B), K7_MASK_THREADS, 0, st>>>(params->iou_thr, w.cap, w.nsel, w.sbox, w.srank, w.blk, w.nz,
+                                                                w.M, w.work);
         K7_LAUNCH_CHECK();
-        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, 0, st>>>(A, params->max_detections, w.nsel, w.surv_count, w.keys1, w.sbox, w.M,
-                                         w.kept_key, w.kept_box, w.kept_count, counts, nullptr);
+        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, 0, st>>>(A, params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1,
+                                                            w.sbox, w.srank, w.nz, w.M, w.kept_key, w.kept_box, w.kept_count,
+                                                            counts, nullptr);
         K7_LAUNCH_CHECK();
     }
-    if (A > K7_NCAP) {   // an image can exceed the cap only then
+    if (A > w.cap) {   // an image can exceed the cap only then
         const size_t smem = sizeof(K7SortNmsSmem);
         K7_CUDA(cudaFuncSetAttribute(k7_sort_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk,
-                                                            params->max_detections, K7_NCAP, w.surv_count, w.kept_count,
+                                                            params->max_detections, w.cap, w.surv_count, w.kept_count,
                                                             w.bits, w.wprefix, w.keys0, w.keys1, w.box, w.kept_key,
                                                             w.kept_box, counts);
     }
@@ -1297,9 +1613,13 @@ struct K7NmsWs {
     uint64_t* keys1;
     uint64_t* kept_key;
     float4* kept_box;
-    int32_t* small;            // {n, nsel, kept_count}
-    float4* sbox;              // multi-SM path (n <= K7_NCAP)
+    int32_t* small;            // {n, nsel, kept_count, mask work counter}
+    float4* sbox;              // multi-SM path (n <= K7_SORT_MAX)
+    int32_t* srank;
+    float4* blk;
+    unsigned long long* nz;
     unsigned long long* M;
+    int cap;
     size_t bytes;
 };
 static K7NmsWs k7_nms_ws(void* base, int n) {
@@ -1318,10 +1638,18 @@ static K7NmsWs k7_nms_ws(void* base, int n) {
     w.kept_box = reinterpret_cast<float4*>(take(16 * nn));
     w.small = reinterpret_cast<int32_t*>(take(64));
     w.sbox = w.kept_box;
+    w.srank = nullptr;
+    w.blk = nullptr;
+    w.nz = nullptr;
     w.M = nullptr;
-    if (n <= K7_NCAP) {
-        w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * K7_NCAP));
-        w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)K7_NCAP * K7_NCAP_WORDS));
+    w.cap = k7_nms_cap(1, n);
+    if (n <= w.cap) {
+        const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
+        w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * cap));
+        w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * cap));
+        w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * nbw));
+        w.nz = reinterpret_cast<unsigned long long*>(take(8 * cap * nzw));
+        w.M = reinterpret_cast<unsigned long long*>(take(8 * cap * nbw));
     }
     w.bytes = o;
     return w;
@@ -1367,19 +1695,22 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
     }
     k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.small);
     K7_LAUNCH_CHECK();
-    if (n <= K7_NCAP) {   // sort -> bitmask on all SMs -> one-warp scan (same kernels as k7_detect, B = 1)
+    if (n <= w.cap) {   // sort -> bitmask on all SMs -> fixed-point resolve (same kernels as k7_detect, B = 1)
         const float4* b4 = reinterpret_cast<const float4*>(boxes);
-        const size_t smem_sort = sizeof(K7SortOnlySmem);
+        size_t smem_sort = 64 * 8;
+        while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.small, nullptr, nullptr, nullptr, w.keys0, w.keys1, b4,
-                                                             w.sbox, w.small + 1);
+        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.cap, w.small, nullptr, nullptr, nullptr, w.keys0,
+                                                             w.keys1, b4, w.sbox, w.srank, w.blk, w.nz, w.small + 1, w.small + 3);
         K7_LAUNCH_CHECK();
-        const int nwords = (n + 63) / 64;
-        int gx = (nwords * (nwords + 1) / 2 + 3) / 4;
-        k7_mask_kernel<<<dim3(gx, 1), K7_MASK_THREADS, 0, st>>>(iou_thr, w.small + 1, w.sbox, w.M);
+        const int nb = (n + 63) / 64;
+        int gx = 4 * k7_sm_count();   // one image: spread its row-blocks (and their column shares) over every SM
+        if (gx > nb * nb) gx = nb * nb;
+        k7_mask_kernel<<<dim3(gx, 1), K7_MASK_THREADS, 0, st>>>(iou_thr, w.cap, w.small + 1, w.sbox, w.srank, w.blk, w.nz, w.M,
+                                                                w.small + 3);
         K7_LAUNCH_CHECK();
-        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, 0, st>>>(n, 0, w.small + 1, w.small, w.keys1, w.sbox, w.M, w.kept_key, w.kept_box, count,
-                                         nullptr, keep);
+        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, 0, st>>>(n, 0, w.cap, w.small + 1, w.small, w.keys1, w.sbox, w.srank, w.nz,
+                                                            w.M, w.kept_key, w.kept_box, count, nullptr, keep);
         K7_LAUNCH_CHECK();
         return K7_OK;
     }
