@@ -14,8 +14,9 @@ BASELINE.json shape (default: configs[1], EfficientDet-D0 512x512, batch 64, 90 
 `roofline` = the dominant kernel (k7_loss, forward+backward) against the measured HBM peak;
 `cpu_baseline` = the oracle port (oracle/restate.py, torch-CPU, all host threads) on a
           bounded sample of the same workload (rank 0, N=1 only).
-N > 1 (torchrun): every rank owns a full batch (weak scaling), the loss sums are combined
-with one 16-byte NCCL all-reduce per step.
+N > 1 (torchrun): every rank owns a full batch (weak scaling; `--shard` splits the workload's
+batch over the ranks instead: strong scaling, BASELINE configs[3] and [4]); the loss sums are
+combined with one 16-byte NCCL all-reduce per step.
 `--impl reference` times the reference's CPU algorithm for the same step (the oracle port;
 the reference is pure Python/PyTorch, there is nothing to compile) and prints the same line.
 """
@@ -45,6 +46,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch (debug)")
+    ap.add_argument("--shard", action="store_true",
+                    help="strong scaling: split the workload's batch over the ranks (BASELINE configs[3], [4]) "
+                         "instead of one full batch per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -189,7 +193,9 @@ def workload_config(wl, batch, gpus):
     return {"workload": wl.name, "image": [wl.height, wl.width], "batch_per_gpu": batch, "global_batch": batch * gpus,
             "classes": wl.classes, "anchors_per_image": wl.anchors, "max_gt_per_image": wl.max_gt,
             "step": "FocalLoss fwd+bwd + decode/clip/threshold/sort/NMS on every image",
-            "cache": "inputs (>= 1 GB per step) are larger than the 126 MB L2; no flush needed",
+            "cache": (f"inputs ({batch * wl.anchors * (4 * wl.classes + 16) / 1e9:.2f} GB per rank and pass) are larger than "
+                      "the 126 MB L2; no flush needed") if batch * wl.anchors * (4 * wl.classes + 16) > 4 * 126e6 else
+                     "inputs fit (partly) in the 126 MB L2: L2-warm numbers, not comparable with the HBM roofline",
             "parallelism": f"image-sharded x{gpus}, one 16-byte all-reduce per step" if gpus > 1 else "single GPU"}
 
 
@@ -226,6 +232,10 @@ def run_b200(args, wl):
     L.lib()                                                    # fail loudly if libk7det.so is missing
 
     B = args.batch or wl.batch
+    if args.shard:
+        if B % world:
+            raise SystemExit(f"--shard: batch {B} does not divide over {world} ranks")
+        B //= world                                            # rank r owns images [r*B, (r+1)*B) of the global batch
     A, C, M = wl.anchors, wl.classes, wl.max_gt
     hw = (wl.height, wl.width)
     cls, reg, ann = b200det.synth.make_inputs(wl, seed=rank, device=dev, batch=B)
@@ -278,7 +288,8 @@ def run_b200(args, wl):
     peak, peak_src = peaks()
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.shard else "weak",
+        "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
         "gpu_launches": 11 * args.steps,
         "launches_per_step": {"k7_match": 1, "k7_loss(stream+rows)": 2, "k7_scale_inplace": 2,

@@ -125,6 +125,27 @@ def test_focal_loss_and_grads(path, from_spec):
     assert np.array_equal(mod.last_num_positives.cpu().numpy(), (g["state"] == 2).sum(1))
 
 
+def test_loss_stage_derives_ignore_bits_when_not_given():
+    """k7_loss with the bitmap of k7_match and without it (k7_loss_bits_kernel) is the same computation."""
+    g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_c90")], True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    B, A, _ = cls.shape
+    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, with_bits=True)
+    state = (assign.view(B, A) & 3).cpu().numpy()
+    want_bits = np.zeros((B, L.ignore_words(A) * 32), dtype=bool)
+    want_bits[:, :A] = state == 1
+    got_bits = np.unpackbits(bits.cpu().numpy().view(np.uint8), axis=1, bitorder="little").astype(bool)
+    assert np.array_equal(got_bits[:, :A], want_bits[:, :A])
+    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B,
+              want_grad=True)
+    a = BL.loss_stage(anc, cls, reg, ann, assign, num_pos, ignore_bits=bits, **kw)
+    b = BL.loss_stage(anc, cls, reg, ann, assign, num_pos, **kw)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
 def test_backward_scales_by_incoming_gradient():
     g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_small")], True)
     ann = torch.from_numpy(g["annotations"]).to(DEV)
@@ -232,6 +253,31 @@ def test_nms_random_vs_torchvision(n):
     boxes[::11, 2:] = boxes[::11, :2]                    # zero-area boxes: 0/0 -> NaN -> never suppressed
     scores = np.round(rng.uniform(-1, 1, n), 2).astype(np.float32)     # many exact ties, negatives
     for thr in (0.0, 0.3, 0.5, 0.9):
+        want = tv_nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
+        got = b200det.nms(torch.from_numpy(boxes).to(DEV), torch.from_numpy(scores).to(DEV), thr).cpu().numpy()
+        assert np.array_equal(got, want), (n, thr)
+
+
+@pytest.mark.parametrize("n", [5000, 16384, 16385, 20000])
+def test_nms_multiscale_clusters_vs_torchvision(n):
+    """Boxes of very different sizes (eight area binades) piled up in clusters: long suppression
+    chains for the fixed-point resolve, every cell of the spatial order populated, the 16 384-box
+    cap of the multi-SM path and the single-CTA fallback above it; a few NaN / infinite boxes."""
+    from torchvision.ops import nms as tv_nms
+    rng = np.random.default_rng(n)
+    centers = rng.uniform(0, 1500, (40, 2))
+    which = rng.integers(0, 40, n)
+    size = 2.0 ** rng.uniform(3, 9, n)
+    c = centers[which] + rng.normal(0, 1, (n, 2)) * size[:, None] * 0.4
+    w = size * rng.uniform(0.6, 1.6, n)
+    h = size * rng.uniform(0.6, 1.6, n)
+    boxes = np.stack([c[:, 0] - w / 2, c[:, 1] - h / 2, c[:, 0] + w / 2, c[:, 1] + h / 2], 1).astype(np.float32)
+    boxes[7] = np.nan
+    boxes[11, 2] = np.inf
+    boxes[13] = boxes[12]                                # exact duplicate
+    scores = rng.uniform(0, 1, n).astype(np.float32)
+    scores[13] = scores[12]                              # tie: the lower index wins
+    for thr in (0.5, 0.7):
         want = tv_nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
         got = b200det.nms(torch.from_numpy(boxes).to(DEV), torch.from_numpy(scores).to(DEV), thr).cpu().numpy()
         assert np.array_equal(got, want), (n, thr)
