@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 2
+#define K7_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -127,6 +127,10 @@ typedef struct K7LossParams {
     int32_t yx_targets;     /* 0: (dx,dy,dw,dh) (losses.py:144)  1: (dy,dx,dh,dw) (loss_efficientdet.py:127) */
     int32_t mean_divisor;   /* images the batch mean is taken over: B for one GPU, the GLOBAL batch when sharded */
     int32_t dreg_prezeroed; /* 1: the caller (k7_match's zero_fill4) already zeroed dreg; 0: k7_loss zeroes it itself */
+    int32_t from_logits;    /* 0: cls holds post-sigmoid probabilities (the reference's tensor).  1: cls holds the
+                             * head's pre-sigmoid logits (output_act of retinanet.py:140,159 / header_act of
+                             * simple_head.py:310 removed): the sigmoid is fused into the stream and dcls is
+                             * d(loss)/d(logit).  SURVEY 8(f) row 1. */
 } K7LossParams;
 
 K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
@@ -177,6 +181,8 @@ typedef struct K7DetectParams {
     float iou_thr;          /* strict '>' (torchvision.ops.nms, retinanet.py:314: 0.5) */
     int32_t pre_nms_topk;   /* 0 = off (reference behaviour) */
     int32_t max_detections; /* 0 = off; otherwise stop after this many kept boxes per image */
+    int32_t from_logits;    /* 1: cls holds pre-sigmoid logits; scores are 1/(1+expf(-z)) (torch.sigmoid), the
+                             * threshold and the arg-max ties are decided on those float32 probabilities */
 } K7DetectParams;
 
 K7_API size_t k7_detect_workspace_bytes(int B, int A, int C);

@@ -10,5 +10,5 @@ __version__ = "0.1.0"
 from .anchors import Anchors, AnchorsYX, spec_of            # noqa: F401
 from .losses import FocalLoss                                # noqa: F401
 from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, detect, nms,  # noqa: F401
-                    postprocess, eval_tail, patch_model)
+                    postprocess, eval_tail, patch_model, strip_head_sigmoid)
 from . import synth                                          # noqa: F401

@@ -52,6 +52,7 @@ class K7LossParams(C.Structure):
         ("yx_targets", C.c_int32),
         ("mean_divisor", C.c_int32),
         ("dreg_prezeroed", C.c_int32),
+        ("from_logits", C.c_int32),
     ]
 
 
@@ -73,10 +74,11 @@ class K7DetectParams(C.Structure):
         ("iou_thr", C.c_float),
         ("pre_nms_topk", C.c_int32),
         ("max_detections", C.c_int32),
+        ("from_logits", C.c_int32),
     ]
 
 
-ABI_VERSION = 2                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 3                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:

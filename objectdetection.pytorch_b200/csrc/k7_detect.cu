@@ -6,20 +6,21 @@
 //                                                              batched form utils/utils.py:76-114
 //   k7_nms                  torchvision.ops.nms call sites     retinanet.py:314, utils/utils.py:93
 //
-// k7_detect is two kernels:
-//   1. k7_score_kernel streams classifications [B*A, C] through the per-warp TMA rings of
-//      k7_stream.cuh; per row it takes the class maximum, and only for rows above the score
-//      threshold (strict '>') finds the first arg-max class, generates the anchor, decodes and
-//      clips the box, and appends a 64-bit key (score descending | anchor id ascending) to the
-//      image's survivor list (warp-aggregated atomic slot allocation).  Regression deltas are read
-//      for survivors only.  Bytes: A*C*4 read per image + 32*S written.
-//   2. k7_sort_nms_kernel, one CTA per image: LSD radix sort of the keys (the order
-//      torchvision.ops.nms's stable descending sort produces, because the anchor id breaks score
-//      ties), then greedy NMS in chunks of 1024 sorted boxes: a chunk is first filtered against
-//      the boxes already kept, then a 1024x1024 bitmask matrix of the chunk is built in shared
-//      memory and scanned by one warp.  The result is identical to the sequential algorithm; the
-//      S x S mask never exists in global memory.
-#include "k7_stream.cuh"
+// k7_detect is a chain of kernels (details at each of them):
+//   1. k7_score_pipe_kernel streams classifications (one flat array of B*A*C floats) through a
+//      warp-specialised TMA pipeline; per row it takes the class maximum, and only for rows above
+//      the score threshold (strict '>') finds the first arg-max class, generates the anchor,
+//      decodes and clips the box and records the survivor by anchor id.  Regression deltas are
+//      read for survivors only.  Bytes: A*C*4 read per image + 32*S written.
+//   2. k7_sort_kernel (one CTA per image) ranks the survivors (the order torchvision.ops.nms's
+//      stable descending sort produces, because the anchor id breaks score ties) and lays them out
+//      in a spatial order; k7_mask_kernel (all SMs) builds a sparse suppression bitmask;
+//      k7_resolve_kernel (one CTA per image) resolves greedy NMS as a fixed point.  The result is
+//      identical to the sequential algorithm.  Images with more survivors than the workspace's cap
+//      go through k7_sort_nms_kernel (one CTA, chunks of 1024 boxes).
+#include <math.h>
+
+#include "k7_common.cuh"
 
 // ------------------------------------------------------------------ stand-alone decode / clip
 template <bool FROM_SPEC>
@@ -155,160 +156,44 @@ extern "C" size_t k7_detect_workspace_bytes(int B, int A, int C) {
 }
 
 // ------------------------------------------------------------------ kernel 1: score + decode + compaction
-#define K7_SCORE_MAX_THREADS 768
-
-template <int VEC>
-__device__ __forceinline__ float k7_vec_max(const float* __restrict__ p) {
-    if (VEC == 4) {
-        const float4 v = *reinterpret_cast<const float4*>(p);
-        return fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
-    } else if (VEC == 2) {
-        const float2 v = *reinterpret_cast<const float2*>(p);
-        return fmaxf(v.x, v.y);
-    }
-    return *p;
-}
-
-template <int VEC, bool FROM_SPEC>
-__global__ void __launch_bounds__(K7_SCORE_MAX_THREADS, 1)
-k7_score_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
-                const float* __restrict__ cls, const float4* __restrict__ reg, int B, int A,
-                const __grid_constant__ K7DetectParams P, const __grid_constant__ K7StreamGeom G,
-                uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws, int32_t* __restrict__ label_ws,
-                float* __restrict__ score_ws) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int NS = G.stages;
-    unsigned char* ring = smem + (size_t)warp * NS * G.stage_stride;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)G.warps * NS * G.stage_stride) + warp * NS;
-    const long long gw = (long long)blockIdx.x * G.warps + warp;
-    const long long nW = (long long)gridDim.x * G.warps;
-    if (gw >= G.num_tiles) return;
-    if (lane == 0) {
-        for (int s = 0; s < NS; ++s) k7_mbar_init(bars + s, 1);
-        k7_fence_mbar_init();
-        k7_fence_proxy_async();
-    }
-    __syncwarp();
-    const int PF = NS - 1;
-    if (lane == 0) {
-        for (int k = 0; k < PF; ++k) {
-            const long long t = gw + k * nW;
-            if (t < G.num_tiles) k7_stream_issue(G, cls, nullptr, t, ring + (size_t)(k % NS) * G.stage_stride, bars + (k % NS));
-        }
-    }
-    const int q = lane & (G.lpr - 1);
-    const int rsub = lane >> G.lpr_shift;
-    int clo, chi;
-    k7_class_range(G, q, clo, chi);
-
-    int it = 0;
-    for (long long tile = gw; tile < G.num_tiles; tile += nW, ++it) {
-        const int s = it % NS;
-        unsigned char* stage = ring + (size_t)s * G.stage_stride;
-        if (lane == 0) {
-            const long long t = tile + (long long)PF * nW;
-            if (t < G.num_tiles) {
-                const int sn = (it + PF) % NS;
-                k7_stream_issue(G, cls, nullptr, t, ring + (size_t)sn * G.stage_stride, bars + sn);
-            }
-        }
-        k7_mbar_wait(bars + s, (it / NS) & 1);
-        const long long row0 = tile * (long long)G.T;
-        long long rows_ll = G.total_rows - row0;
-        const int rows = rows_ll > G.T ? G.T : (int)rows_ll;
-        float* tilef = reinterpret_cast<float*>(stage);
-        const uint32_t cls_bytes = (uint32_t)rows * G.C * 4u;
-        const uint32_t rem = cls_bytes & 15u;
-        if (rem) {
-            if (lane == 0) {
-                const uint32_t base = (cls_bytes & ~15u) >> 2;
-                for (uint32_t k = 0; k < (rem >> 2); ++k) tilef[base + k] = cls[row0 * G.C + base + k];
-            }
-            __syncwarp();
-        }
-
-        for (int i = 0; i < G.iters; ++i) {
-            const int r = i * G.rows_per_iter + rsub;
-            const bool rvalid = r < rows;
-            const float* rowp = tilef + (size_t)(rvalid ? r : 0) * G.C;
-            // class maximum of this lane's range, then of the row (torch.max(cls, dim=2), retinanet.py:300)
-            float m = -INFINITY;
-            if (rvalid) {
-                int j = clo;
-                float m1 = -INFINITY;
-                for (; j + 2 * VEC <= chi; j += 2 * VEC) {
-                    m = fmaxf(m, k7_vec_max<VEC>(rowp + j));
-                    m1 = fmaxf(m1, k7_vec_max<VEC>(rowp + j + VEC));
-                }
-                for (; j < chi; j += VEC) m = fmaxf(m, k7_vec_max<VEC>(rowp + j));
-                m = fmaxf(m, m1);
-            }
-            for (int o = G.lpr >> 1; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-            const bool pass = rvalid && (m > P.score_thr);   // strict, retinanet.py:302
-            if (__ballot_sync(0xffffffffu, pass) == 0u) continue;   // warp-uniform: nothing survives in these rows
-
-            // first class index attaining the maximum (torch .max(dim=1) on the kept rows, retinanet.py:316)
-            int lab = 0x7fffffff;
-            if (pass) {
-                for (int j = chi - 1; j >= clo; --j)
-                    if (rowp[j] == m) lab = j;
-            }
-            for (int o = G.lpr >> 1; o > 0; o >>= 1) lab = min(lab, __shfl_xor_sync(0xffffffffu, lab, o));
-
-            const bool owner = pass && (q == 0);
-            const long long R = row0 + r;
-            const int b = owner ? (int)(R / A) : 0;
-            const int a = owner ? (int)(R - (long long)b * A) : 0;
-            if (owner) {
-                float ax1, ay1, ax2, ay2;
-                k7_anchor<FROM_SPEC>(spec, anchors, box_order, a, ax1, ay1, ax2, ay2);
-                const float4 d = __ldg(reg + R);
-                K7Box o = (P.decode.variant == K7_DECODE_RETINA)
-                              ? k7_decode_retina(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w, P.decode.mean, P.decode.std)
-                              : k7_decode_effdet(ax1, ay1, ax2, ay2, d.x, d.y, d.z, d.w);
-                if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
-                const size_t oa = (size_t)b * A + a;
-                box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
-                label_ws[oa] = lab;
-                score_ws[oa] = m;
-                atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
-            }
-        }
-        __syncwarp();
-    }
-}
-
-// ------------------------------------------------------------------ kernel 1, pipelined (A*C % 4 == 0)
-// Same warp-specialised TMA pipeline as k7_loss_pipe_kernel (producer warp + 16 consumer warps,
-// 32 KB stages, flat tiles that ignore row boundaries), with an even lighter consumer: a row
-// survives iff ANY of its elements exceeds the threshold, so the flat pass is LDS.128 + three
-// max + one compare per float4.  Every element above the threshold is a REPORT: the warp takes the
-// report's row from the tile in shared memory, reduces its maximum and FIRST arg-max, and the
-// report that sits exactly on the arg-max element queues the survivor - every surviving row has
-// exactly one such element, so there is no duplicate and no atomic slot allocation.  The queue
-// (shared memory, per warp) is drained at the end, one survivor per lane: anchor, regression
-// deltas, decode + clip, and the records by anchor id (bitmap bit, score, label, box) from which
-// k7_sort_kernel later ranks the survivors.  Nothing with a long latency sits between a stage
-// becoming full and its release.
+// The same warp-specialised TMA pipeline as k7_loss_pipe_kernel: one CTA per SM, a producer warp
+// and 16 consumer warps, 32 KB stages; classifications is ONE flat array of B*A*C floats cut into
+// tiles that ignore row and image boundaries (any shape streams through 16-byte bulk copies).  The
+// consumer is light: a row survives iff ANY of its elements exceeds the threshold, so the flat
+// pass is LDS.128 + three max + one compare per float4.  Every element above the threshold is a
+// REPORT: the warp takes the report's row from the tile in shared memory, reduces its maximum and
+// FIRST arg-max, and the report that sits exactly on the arg-max element queues the survivor -
+// every surviving row has exactly one such element, so there is no duplicate and no atomic slot
+// allocation.  The queue (shared memory, per warp) is drained at the end, one survivor per lane:
+// anchor, regression deltas, decode + clip, and the records by anchor id (bitmap bit, score,
+// label, box) from which k7_sort_kernel later ranks the survivors.  Nothing with a long latency
+// sits between a stage becoming full and its release.
+//
+// LOGITS (K7DetectParams.from_logits): the tensor holds pre-sigmoid logits.  The sigmoid is
+// monotone, so reports are taken against logit(thr) lowered by a safety margin and rows are
+// reduced in logit space; the drain then computes the score 1/(1+expf(-z)) of the row maximum
+// exactly as torch.sigmoid does, re-applies the strict threshold on that float32 probability, and
+// moves the label to an EARLIER class whose logit is lower but rounds to the same probability
+// (what torch.max over the probabilities would return).
 struct K7ScoreGeom {
-    uint32_t AC, tile_f, tpi, num_tiles;
-    K7FastDiv div_c, div_tpi;
+    unsigned long long N, N4;   // B*A*C and its multiple-of-4 part (the last N % 4 floats are served from global memory)
+    uint32_t AC, tile_f, num_tiles;
+    K7FastDiv div_c;
     uint32_t stage_stride, off_desc, off_bars, off_queue;
     int stages, cw, grid;
     size_t smem_bytes;
 };
 struct K7ScoreDesc {
-    uint32_t n, b, off, pad;
+    uint32_t n, b0, ge0, split;   // floats | image of float 0 | its element index inside that image | floats that belong to image b0
 };
 #define K7_SPIPE_SLICE 512
 #define K7_SPIPE_MAX_CW 16
 #define K7_SPIPE_QCAP 96    // queued survivors per consumer warp
 
-template <bool FROM_SPEC>
+template <bool FROM_SPEC, bool LOGITS>
 __global__ void __launch_bounds__((K7_SPIPE_MAX_CW + 1) * 32, 1)
 k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
-                     const float* __restrict__ cls, const float4* __restrict__ reg, int A, int C,
+                     const float* __restrict__ cls, const float4* __restrict__ reg, int A, int C, float report_thr,
                      const __grid_constant__ K7DetectParams P, const __grid_constant__ K7ScoreGeom G,
                      uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws, int32_t* __restrict__ label_ws,
                      float* __restrict__ score_ws) {
@@ -328,22 +213,25 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
         k7_fence_proxy_async();
     }
     __syncthreads();
-    if (blockIdx.x >= G.num_tiles) return;
-    const uint32_t ntl = (G.num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    if (blockIdx.x >= G.num_tiles && blockIdx.x != 0) return;
+    const uint32_t ntl = blockIdx.x < G.num_tiles ? (G.num_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
 
     if (warp == CW) {   // ---------------------------------------------------------------- producer
         if (lane != 0) return;
         auto load = [&](const uint32_t j) {
-            const uint32_t g = blockIdx.x + j * gridDim.x;
+            const unsigned long long g = (unsigned long long)blockIdx.x + (unsigned long long)j * gridDim.x;
             const int s = (int)(j % (uint32_t)NS);
+            const unsigned long long off = g * G.tile_f;
+            const unsigned long long left = G.N4 - off;
             K7ScoreDesc d;
-            d.b = k7_div(g, G.div_tpi);
-            d.off = (g - d.b * G.tpi) * G.tile_f;
-            d.n = min(G.tile_f, G.AC - d.off);
-            d.pad = 0;
+            d.n = left < G.tile_f ? (uint32_t)left : G.tile_f;
+            d.b0 = (uint32_t)(off / G.AC);
+            d.ge0 = (uint32_t)(off - (unsigned long long)d.b0 * G.AC);
+            const uint32_t in_img = G.AC - d.ge0;
+            d.split = in_img < d.n ? in_img : d.n;
             desc[s] = d;
             k7_mbar_expect_tx(full + s, d.n * 4u);
-            k7_bulk_g2s(smem + (size_t)s * G.stage_stride, cls + (size_t)d.b * G.AC + d.off, d.n * 4u, full + s);
+            k7_bulk_g2s(smem + (size_t)s * G.stage_stride, cls + off, d.n * 4u, full + s);
         };
         uint32_t jl = 0;
         for (; jl < ntl && jl < (uint32_t)NS; ++jl) load(jl);
@@ -362,7 +250,7 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
     if (warp > CW) return;
 
     // ------------------------------------------------------------------------------------ consumers
-    const float thr = P.score_thr;
+    const float thr = report_thr;
     const uint32_t full_u32 = k7_smem_u32(full), done_u32 = k7_smem_u32(done);
     const int i_lo = warp * SL;
     // queue entry: x = image (bit 31: row still unresolved), y = anchor (or element index inside the
@@ -371,8 +259,8 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
     int qn = 0;
 
     // Deferred emission, one queue entry per lane: anchor, regression deltas, decode + clip, and the
-    // by-anchor records.  Unresolved entries (rows straddling two tiles) first take their row from
-    // global memory.
+    // by-anchor records.  Unresolved entries (rows straddling two tiles, the unaligned tail) first
+    // take their row from global memory.
     auto drain = [&]() {
         __syncwarp();
         for (int base = 0; base < qn; base += 32) {
@@ -398,6 +286,24 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                 }
                 if (idx != c) continue;
             }
+            if (LOGITS) {
+                const float p = k7_sigmoid_precise(m);
+                if (!(p > P.score_thr)) continue;   // a report inside the safety margin of logit(thr)
+                // torch.max over the PROBABILITIES returns the first class with the maximal float32 value:
+                // an earlier class with a slightly lower logit may round to the same probability.  Such a
+                // logit lies within 2^-23/(1-p) of m; beyond z = 8 the plateau widens, so every earlier
+                // logit above 8 is checked.
+                const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
+                const float lo = fminf(m - 2e-3f, 8.0f);
+                for (int q = 0; q < idx; ++q) {
+                    const float v = __ldg(row + q);
+                    if (v >= lo && k7_sigmoid_precise(v) == p) {
+                        idx = q;
+                        break;
+                    }
+                }
+                m = p;
+            }
             float ax1, ay1, ax2, ay2;
             k7_anchor<FROM_SPEC>(spec, anchors, box_order, (int)a, ax1, ay1, ax2, ay2);
             const size_t oa = (size_t)b * A + a;
@@ -422,7 +328,7 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
         if (s == 0) phase ^= 1u;
         const float* tile = reinterpret_cast<const float*>(smem + (size_t)s * G.stage_stride);
         k7_mbar_wait_u32(full_u32 + 8u * s, phase);
-        const uint4 d = *reinterpret_cast<const uint4*>(desc + s);   // n, b, off
+        const uint4 d = *reinterpret_cast<const uint4*>(desc + s);   // n, b0, ge0, split
         const int n = (int)d.x;
         if (i_lo < n) {
             const int len = min(n - i_lo, SL), n4 = len >> 2;
@@ -459,13 +365,18 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                             const int src = __ffs(mb) - 1;
                             mb &= mb - 1;
                             const int i = i_lo + 4 * (src + 32 * k) + e;      // tile-local element index
-                            const uint32_t ge = d.z + (uint32_t)i;            // element index inside the image
+                            uint32_t bimg = d.y, ge = d.z + (uint32_t)i;      // image, element index inside it
+                            if ((uint32_t)i >= d.w) {                         // the tile runs into the next image(s)
+                                const uint32_t r = (uint32_t)i - d.w, qi = r / G.AC;
+                                bimg = d.y + 1u + qi;
+                                ge = r - qi * G.AC;
+                            }
                             const uint32_t a = k7_div(ge, G.div_c);
                             const int c = (int)(ge - a * (uint32_t)C);
                             const int i0 = i - c;                             // tile-local index of the row's class 0
                             if (qn == K7_SPIPE_QCAP) drain();
                             if (i0 < 0 || i0 + C > n) {                       // row straddles two tiles: resolve later
-                                if (lane == 0) queue[qn] = make_uint4(d.y | 0x80000000u, ge, 0u, 0u);
+                                if (lane == 0) queue[qn] = make_uint4(bimg | 0x80000000u, ge, 0u, 0u);
                                 ++qn;
                                 continue;
                             }
@@ -489,7 +400,7 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                                 }
                             }
                             if (idx != c) continue;   // warp-uniform
-                            if (lane == 0) queue[qn] = make_uint4(d.y, a, (uint32_t)idx, __float_as_uint(m));
+                            if (lane == 0) queue[qn] = make_uint4(bimg, a, (uint32_t)idx, __float_as_uint(m));
                             ++qn;
                         }
                     }
@@ -499,21 +410,32 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
         __syncwarp();
         if (lane == 0) k7_mbar_arrive_u32(done_u32 + 8u * s);
     }
+    // the last N % 4 floats cannot be bulk-copied: CTA 0, warp 0 turns them into unresolved reports
+    if (blockIdx.x == 0 && warp == 0 && G.N4 < G.N) {
+        for (unsigned long long e = G.N4; e < G.N; ++e) {   // warp-uniform
+            if (!(__ldg(cls + e) > thr)) continue;
+            const uint32_t bimg = (uint32_t)(e / G.AC);
+            const uint32_t ge = (uint32_t)(e - (unsigned long long)bimg * G.AC);
+            if (qn == K7_SPIPE_QCAP) drain();
+            if (lane == 0) queue[qn] = make_uint4(bimg | 0x80000000u, ge, 0u, 0u);
+            ++qn;
+        }
+    }
     drain();
 }
 
 static int k7_score_geometry(int B, int A, int C, K7ScoreGeom* g) {
     const unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
-    K7_REQUIRE(ac < (1ull << 30), "k7_detect: A*C=%llu per image is too large", ac);
+    K7_REQUIRE(ac < (1ull << 31), "k7_detect: A*C=%llu per image is too large", ac);
     g->AC = (uint32_t)ac;
+    g->N = ac * (unsigned long long)B;
+    g->N4 = g->N & ~3ull;
     g->cw = K7_SPIPE_MAX_CW;
     g->tile_f = (uint32_t)g->cw * K7_SPIPE_SLICE;
-    g->tpi = (uint32_t)((ac + g->tile_f - 1) / g->tile_f);
-    const unsigned long long nt = (unsigned long long)B * g->tpi;
+    const unsigned long long nt = (g->N4 + g->tile_f - 1) / g->tile_f;
     K7_REQUIRE(nt < (1ull << 31), "k7_detect: %llu tiles exceed the 32-bit tile index", nt);
     g->num_tiles = (uint32_t)nt;
     g->div_c = k7_fastdiv_make((uint32_t)C);
-    g->div_tpi = k7_fastdiv_make(g->tpi);
     g->stage_stride = g->tile_f * 4;
     g->stages = 6;
     size_t o = (size_t)g->stages * g->stage_stride;
@@ -1477,18 +1399,6 @@ k7_gather_kernel(int A, int W32, int cap, const int32_t* __restrict__ kept_count
 }
 
 // ------------------------------------------------------------------ host: k7_detect
-template <int VEC, bool FROM_SPEC>
-static int k7_score_launch(const K7AnchorSpec& spec, const float* anchors, int box_order, const float* cls, const float* reg,
-                           int B, int A, const K7DetectParams& P, const K7StreamGeom& G, const K7DetectWs& w,
-                           cudaStream_t st) {
-    auto kern = k7_score_kernel<VEC, FROM_SPEC>;
-    K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-    kern<<<G.grid, G.warps * 32, G.smem_bytes, st>>>(spec, anchors, box_order, cls, reinterpret_cast<const float4*>(reg), B, A,
-                                                     P, G, w.bits, w.W32, w.box, w.label, w.score);
-    K7_LAUNCH_CHECK();
-    return K7_OK;
-}
-
 extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
                          int B, int A, int C, const K7DetectParams* params, int32_t* counts, void* workspace,
                          size_t workspace_bytes, void* stream) {
@@ -1520,37 +1430,33 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
                                                       reinterpret_cast<unsigned char*>(w.surv_count)), st));
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-    int rc;
-    if ((((unsigned long long)A * C) % 4ull) == 0ull) {
+    {
         K7ScoreGeom GS;
-        rc = k7_score_geometry(B, A, C, &GS);
+        int rc = k7_score_geometry(B, A, C, &GS);
         if (rc) return rc;
-#define K7_SPIPE_LAUNCH(SP)                                                                                              \
+        float report_thr = params->score_thr;
+        if (params->from_logits) {
+            // logit(thr) lowered by a margin: the exact float32 sigmoid decides in the kernel's drain
+            const double t = (double)params->score_thr;
+            if (t <= 0.0) report_thr = -INFINITY;
+            else if (t >= 1.0) report_thr = INFINITY;   // sigmoid <= 1: nothing can pass a strict '>'
+            else {
+                const double z = log(t / (1.0 - t));
+                report_thr = (float)(z - 1e-3 * (1.0 + fabs(z)));
+            }
+        }
+#define K7_SPIPE_LAUNCH(SP, LG)                                                                                          \
     do {                                                                                                                 \
-        auto kern = k7_score_pipe_kernel<SP>;                                                                            \
+        auto kern = k7_score_pipe_kernel<SP, LG>;                                                                        \
         K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS.smem_bytes));            \
         kern<<<GS.grid, (GS.cw + 1) * 32, GS.smem_bytes, st>>>(sp, anchors, box_order, cls,                              \
-                                                               reinterpret_cast<const float4*>(reg), A, C, *params, GS,  \
-                                                               w.bits, w.W32, w.box, w.label, w.score);                  \
+                                                               reinterpret_cast<const float4*>(reg), A, C, report_thr,  \
+                                                               *params, GS, w.bits, w.W32, w.box, w.label, w.score);    \
     } while (0)
-        if (spec) K7_SPIPE_LAUNCH(true); else K7_SPIPE_LAUNCH(false);
+        if (params->from_logits) { if (spec) K7_SPIPE_LAUNCH(true, true); else K7_SPIPE_LAUNCH(false, true); }
+        else                     { if (spec) K7_SPIPE_LAUNCH(true, false); else K7_SPIPE_LAUNCH(false, false); }
 #undef K7_SPIPE_LAUNCH
         K7_LAUNCH_CHECK();
-    } else {
-        K7_REQUIRE(A >= 32, "k7_detect: A >= 32 required when A*C is not a multiple of 4 (A=%d)", A);
-        K7StreamGeom G;
-        rc = k7_stream_geometry((long long)B * A, A, C, 0, 3, K7_SCORE_MAX_THREADS / 32, &G);
-        if (rc) return rc;
-        if (G.vec == 4)
-            rc = spec ? k7_score_launch<4, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                      : k7_score_launch<4, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-        else if (G.vec == 2)
-            rc = spec ? k7_score_launch<2, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                      : k7_score_launch<2, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-        else
-            rc = spec ? k7_score_launch<1, true>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st)
-                      : k7_score_launch<1, false>(sp, anchors, box_order, cls, reg, B, A, *params, G, w, st);
-        if (rc) return rc;
     }
 
     // NMS: images with <= cap survivors go through sort -> mask (all SMs) -> resolve (one CTA each),

@@ -59,6 +59,7 @@ struct K7LossDev {
     int use_div;
     int yx_targets;
     int dreg_prezeroed;
+    int from_logits;
     int B, A, C, M;
 };
 
@@ -90,11 +91,35 @@ __device__ __forceinline__ float k7_rcp_approx(float x) {
     return r;
 }
 
+// sigmoid of two logits for the streaming pass: e = 2^(-z*log2 e) (MUFU.EX2), r = 1/(1+e) (MUFU.RCP);
+// relative error ~3e-7, far inside the 1e-5 contract of the losses (the eval side, where the
+// survivor set must be bit-exact, uses the precise form).  dsig = sigma'(z) = e * r * r.
+__device__ __forceinline__ float k7_ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float2 k7_sigmoid_pair(const float2 z, float2& dsig) {
+    const float2 t = __fmul2_rn(z, make_float2(-1.4426950408889634f, -1.4426950408889634f));
+    float2 e;
+    e.x = k7_ex2_approx(t.x);
+    e.y = k7_ex2_approx(t.y);
+    const float2 d = __fadd2_rn(e, make_float2(1.0f, 1.0f));
+    float2 r;
+    r.x = k7_rcp_approx(d.x);
+    r.y = k7_rcp_approx(d.y);
+    dsig = __fmul2_rn(__fmul2_rn(e, r), r);
+    return r;
+}
+
 // Two "target 0" elements.  Returns their gradients (GRAD), accumulates p^2 * -log(1-p) into acc
-// and max(p) into pmax.  ign: bit 0 / bit 1 = element belongs to an ignored row.
-template <bool GRAD, bool MASKED>
-__device__ __forceinline__ float2 k7_neg_pair(const float2 x, const uint32_t ign, const float2 sco, float2& acc,
+// and max(p) into pmax.  ign: bit 0 / bit 1 = element belongs to an ignored row.  LOGITS: the
+// inputs are pre-sigmoid logits (the head's sigmoid is fused here) and the gradient is d/dz.
+template <bool GRAD, bool MASKED, bool LOGITS>
+__device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t ign, const float2 sco, float2& acc,
                                               float& pmax) {
+    float2 dsig = make_float2(1.0f, 1.0f);
+    const float2 x = LOGITS ? k7_sigmoid_pair(xin, dsig) : xin;
     float2 p;
     p.x = fminf(fmaxf(x.x, K7_P_LO), K7_P_HI);
     p.y = fminf(fmaxf(x.y, K7_P_LO), K7_P_HI);
@@ -122,7 +147,8 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 x, const uint32_t ign
         r.y = k7_rcp_approx(q.y);
         const float2 u = __fmul2_rn(p, r);                                   // p / (1-p)
         const float2 v = __ffma2_rn(make_float2(2.0f, 2.0f), nl, u);         // 2*nl + p/(1-p)
-        const float2 w = __fmul2_rn(p, sco);                                 // (1-alpha) * scale * p
+        float2 w = __fmul2_rn(p, sco);                                       // (1-alpha) * scale * p
+        if (LOGITS) w = __fmul2_rn(w, dsig);                                 // chain rule through the sigmoid
         g = __fmul2_rn(w, v);
         // torch.clamp passes the gradient on the closed interval  <=>  clamp(x) == x
         const bool k0 = (p.x == x.x) && !(MASKED && (ign & 1u));
@@ -133,17 +159,17 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 x, const uint32_t ign
     return g;
 }
 
-template <bool GRAD, bool MASKED>
+template <bool GRAD, bool MASKED, bool LOGITS>
 __device__ __forceinline__ void k7_flat4(float4* __restrict__ p4, const uint32_t nib, const float2 sco, float2& acc,
                                          float& pmax) {
     const float4 x = *p4;
-    const float2 ga = k7_neg_pair<GRAD, MASKED>(make_float2(x.x, x.y), nib & 3u, sco, acc, pmax);
-    const float2 gb = k7_neg_pair<GRAD, MASKED>(make_float2(x.z, x.w), (nib >> 2) & 3u, sco, acc, pmax);
+    const float2 ga = k7_neg_pair<GRAD, MASKED, LOGITS>(make_float2(x.x, x.y), nib & 3u, sco, acc, pmax);
+    const float2 gb = k7_neg_pair<GRAD, MASKED, LOGITS>(make_float2(x.z, x.w), (nib >> 2) & 3u, sco, acc, pmax);
     if (GRAD) *p4 = make_float4(ga.x, ga.y, gb.x, gb.y);
 }
 
 // The flat pass over n4 float4s of a tile.  mask: one bit per element (set = ignored row).
-template <int TILE_F, bool GRAD, bool MASKED>
+template <int TILE_F, bool GRAD, bool MASKED, bool LOGITS>
 __device__ __forceinline__ void k7_flat_pass(float* __restrict__ tile, const int n4, const uint32_t* __restrict__ mask,
                                              const int lane, const float sco1, float2& acc, float& pmax) {
     float4* t4 = reinterpret_cast<float4*>(tile);
@@ -154,24 +180,30 @@ __device__ __forceinline__ void k7_flat_pass(float* __restrict__ tile, const int
         for (int k = 0; k < TILE_F / 128; ++k) {
             uint32_t nib = 0;
             if (MASKED) nib = (mask[(lane >> 3) + 4 * k] >> sh) & 15u;
-            k7_flat4<GRAD, MASKED>(t4 + lane + 32 * k, nib, sco, acc, pmax);
+            k7_flat4<GRAD, MASKED, LOGITS>(t4 + lane + 32 * k, nib, sco, acc, pmax);
         }
     } else {
         for (int f = lane; f < n4; f += 32) {
             uint32_t nib = 0;
             if (MASKED) nib = (mask[f >> 3] >> sh) & 15u;
-            k7_flat4<GRAD, MASKED>(t4 + f, nib, sco, acc, pmax);
+            k7_flat4<GRAD, MASKED, LOGITS>(t4 + f, nib, sco, acc, pmax);
         }
     }
 }
 
 // Exact scalar evaluation of one "target 0" element (any p): loss without the (1-alpha) factor,
 // gradient without (1-alpha)*scale.  Used by the redo path and by the label patch.
-__device__ __forceinline__ float k7_neg_exact(const float x, float* grad) {
+// from_logits: x is a logit; the gradient is then d/dz.
+__device__ __forceinline__ float k7_neg_exact(const float xin, float* grad, const bool from_logits = false) {
+    const float x = from_logits ? k7_sigmoid_precise(xin) : xin;
     const float p = k7_clamp_p(x);
     const float q = 1.0f - p;
     const float nl = k7_neg_log1m(q);
-    if (grad) *grad = (p == x) ? p * fmaf(2.0f, nl, p * k7_rcp_approx(q)) : 0.0f;
+    if (grad) {
+        float g = (p == x) ? p * fmaf(2.0f, nl, p * k7_rcp_approx(q)) : 0.0f;
+        if (from_logits) g *= x * (1.0f - x);
+        *grad = g;
+    }
     return (p * p) * nl;
 }
 
@@ -234,7 +266,7 @@ struct K7TileDesc {   // written by the producer next to each stage, 48 bytes
     uint32_t off_lo, off_hi, pad0, pad1;   // flat index of float 0
 };
 
-template <bool GRAD, int SL>
+template <bool GRAD, int SL, bool LOGITS>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
 k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ bits, const int32_t* __restrict__ num_pos,
                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7PipeGeom G,
@@ -356,7 +388,7 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
     };
     auto exact = [&](const float x, const bool ign, float* gout) {
         float gr;
-        const float l = k7_neg_exact(x, &gr);
+        const float l = k7_neg_exact(x, &gr, LOGITS);
         if (!ign) cslow += l;
         if (GRAD) *gout = ign ? 0.0f : sco * gr;
     };
@@ -425,9 +457,9 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
                 const float2 acc0 = acc;
                 float pmax = 0.0f;
                 if (masked)
-                    k7_flat_pass<SL, GRAD, true>(slice, n4, mask, lane, sco, acc, pmax);
+                    k7_flat_pass<SL, GRAD, true, LOGITS>(slice, n4, mask, lane, sco, acc, pmax);
                 else
-                    k7_flat_pass<SL, GRAD, false>(slice, n4, mask, lane, sco, acc, pmax);
+                    k7_flat_pass<SL, GRAD, false, LOGITS>(slice, n4, mask, lane, sco, acc, pmax);
                 if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
                     // a confident prediction: outside the polynomial's range.  Redo the slice exactly
                     // (with gradients the tile already holds them: the inputs come from global memory again).
@@ -607,10 +639,15 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
             const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
             if (label >= 0 && label < C) {
                 const size_t e = R * (size_t)C + (size_t)label;
-                const float xl = __ldg(cls + e);
+                const float zl = __ldg(cls + e);
+                const float xl = P.from_logits ? k7_sigmoid_precise(zl) : zl;
                 const float p = k7_clamp_p(xl);
                 cfix += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
-                if (GRAD) dcls[e] = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
+                if (GRAD) {
+                    float g = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
+                    if (P.from_logits) g *= xl * (1.0f - xl);   // d/dz through the fused sigmoid
+                    dcls[e] = g;
+                }
             }
         }
         __syncthreads();   // the queue is rewritten by the next chunk
@@ -861,6 +898,7 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     P.mean_div = (float)params->mean_divisor;
     P.yx_targets = params->yx_targets;
     P.dreg_prezeroed = params->dreg_prezeroed;
+    P.from_logits = params->from_logits ? 1 : 0;
     P.B = B; P.A = A; P.C = C; P.M = M;
 
     K7_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * ((size_t)B + 1), st));
@@ -879,10 +917,14 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
                                                                   cta_partials, dcls);
             return K7_OK;
         };
-        if (G.slice == 1024)
-            rc = grad ? launch(k7_loss_pipe_kernel<true, 1024>) : launch(k7_loss_pipe_kernel<false, 1024>);
-        else
-            rc = grad ? launch(k7_loss_pipe_kernel<true, 512>) : launch(k7_loss_pipe_kernel<false, 512>);
+        const bool lg = P.from_logits != 0;
+        if (G.slice == 1024) {
+            if (lg) rc = grad ? launch(k7_loss_pipe_kernel<true, 1024, true>) : launch(k7_loss_pipe_kernel<false, 1024, true>);
+            else    rc = grad ? launch(k7_loss_pipe_kernel<true, 1024, false>) : launch(k7_loss_pipe_kernel<false, 1024, false>);
+        } else {
+            if (lg) rc = grad ? launch(k7_loss_pipe_kernel<true, 512, true>) : launch(k7_loss_pipe_kernel<false, 512, true>);
+            else    rc = grad ? launch(k7_loss_pipe_kernel<true, 512, false>) : launch(k7_loss_pipe_kernel<false, 512, false>);
+        }
         if (rc) return rc;
         K7_LAUNCH_CHECK();
     }

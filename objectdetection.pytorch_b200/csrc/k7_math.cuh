@@ -100,6 +100,8 @@ K7_HD float k7_focal_pos_grad(float p, float alpha) {
     return -alpha * q * fmaf(2.0f, -logf(p), q / p);
 }
 K7_HD float k7_clamp_p(float x) { return fminf(fmaxf(x, K7_P_LO), K7_P_HI); }
+// torch.sigmoid in float32 (ATen: 1 / (1 + exp(-x)) with expf and an IEEE division)
+K7_HD float k7_sigmoid_precise(float z) { return K7_FDIV(1.0f, K7_FADD(1.0f, expf(-z))); }
 // torch.clamp backward passes the gradient on the closed interval
 K7_HD bool k7_clamp_pass(float x) { return x >= K7_P_LO && x <= K7_P_HI; }
 

@@ -85,10 +85,11 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
 
 def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
                mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
-               ignore_bits: Optional[torch.Tensor] = None):
+               ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
     dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a 16 B/anchor store);
-    ignore_bits: match(with_bits=True)'s bitmap (derived from `assign` by a small kernel when absent)."""
+    ignore_bits: match(with_bits=True)'s bitmap (derived from `assign` by a small kernel when absent);
+    from_logits: `cls` holds pre-sigmoid logits, the sigmoid is fused and dcls is d(loss)/d(logit)."""
     B, A, Cn = cls.shape
     M = ann.shape[1]
     dev = cls.device
@@ -113,6 +114,7 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     for i in range(4):
         p.target_div[i] = target_div[i]
     p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
+    p.from_logits = int(from_logits)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
                             L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits), L.ptr(num_pos),
@@ -138,7 +140,8 @@ class _FocalLossFn(torch.autograd.Function):
         per_image, sums, dcls, dreg = loss_stage(
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
-            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0, ignore_bits=bits)
+            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0, ignore_bits=bits,
+            from_logits=cfg.get("from_logits", False))
         if world > 1:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective
@@ -174,12 +177,16 @@ class FocalLoss(nn.Module):
     """Same call signature as the reference.  Constructor keywords expose the constants the
     reference hard-codes; defaults are architectures/losses.py's (0.35/0.45, alpha .25,
     smooth-L1 beta 1/9, targets / [.1,.1,.2,.2], xyxy anchors).  ``FocalLoss.efficientdet()``
-    gives architectures/loss_efficientdet.py's (0.4/0.5, yx anchors, unscaled (dy,dx,dh,dw))."""
+    gives architectures/loss_efficientdet.py's (0.4/0.5, yx anchors, unscaled (dy,dx,dh,dw)).
+    ``from_logits=True``: `classifications` are the head's PRE-sigmoid logits (drop
+    ``output_act`` of retinanet.py:140 / ``header_act`` of simple_head.py:310, see
+    ``b200det.strip_head_sigmoid``); the sigmoid is fused into the streaming kernel and the gradient
+    comes back with respect to the logits, so neither the sigmoid pass nor its backward touch HBM."""
 
     def __init__(self, neg_thr: float = 0.35, pos_thr: float = 0.45, alpha: float = 0.25,
                  gamma: float = 2.0, beta: float = 1.0 / 9.0, target_std=(0.1, 0.1, 0.2, 0.2),
                  box_order: str = "xyxy", yx_targets: bool = False, process_group=None,
-                 sharded: bool = False):
+                 sharded: bool = False, from_logits: bool = False):
         super().__init__()
         if gamma != 2.0:
             raise ValueError("only gamma == 2 (the reference's constant, losses.py:32) is implemented")
@@ -188,7 +195,8 @@ class FocalLoss(nn.Module):
         self.cfg = dict(neg_thr=float(neg_thr), pos_thr=float(pos_thr), alpha=float(alpha), beta=float(beta),
                         target_div=tuple(float(x) for x in (target_std if target_std is not None else (1, 1, 1, 1))),
                         box_order=L.BOX_XYXY if box_order == "xyxy" else L.BOX_YXYX,
-                        yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded))
+                        yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded),
+                        from_logits=bool(from_logits))
         self.last_num_positives = None      # [B] int32 device tensor of the last call (for logging)
         self.last_per_image = None          # [B,2] (cls_i, reg_i)
 

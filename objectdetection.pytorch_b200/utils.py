@@ -127,8 +127,10 @@ class BatchDetections:
 def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, image_hw, *,
            score_thr: float = 0.05, iou_thr: float = 0.5, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0),
            std=(.1, .1, .2, .2), clip: bool = True, pre_nms_topk: int = 0, max_detections: int = 0,
-           cap: Optional[int] = None, sync: bool = True) -> BatchDetections:
-    """Fused decode + clip + threshold + sort + NMS for every image of the batch."""
+           cap: Optional[int] = None, sync: bool = True, from_logits: bool = False) -> BatchDetections:
+    """Fused decode + clip + threshold + sort + NMS for every image of the batch.
+    from_logits: `classifications` are pre-sigmoid logits; scores are torch.sigmoid of the row maxima
+    and threshold / label ties are decided on those float32 probabilities, as the reference would."""
     L.require_cuda(classifications, regressions)
     cls = L.as_f32_contig(classifications)
     reg = L.as_f32_contig(regressions)
@@ -150,6 +152,7 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
     p.decode = _decode_params(variant, mean, std, clip, image_hw[0], image_hw[1])
     p.score_thr, p.iou_thr = float(score_thr), float(iou_thr)
     p.pre_nms_topk, p.max_detections = int(pre_nms_topk), int(max_detections)
+    p.from_logits = int(from_logits)
     if cap is None:
         cap = max_detections if max_detections > 0 else min(A, 1024)
     cap = max(1, min(int(cap), A))
@@ -200,14 +203,16 @@ def _variant_of(regressBoxes) -> int:
         type(regressBoxes).__module__.endswith("utils_efficientdet") else L.DECODE_RETINA
 
 
-def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes, threshold, iou_threshold):
+def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes, threshold, iou_threshold,
+                from_logits: bool = False):
     """utils/utils.py:76-114 — same arguments, same return (list of dicts of numpy arrays).  The
     reference's duplicate empty dict for an all-empty batch (utils.py:83-88) is not reproduced."""
     variant = _variant_of(regressBoxes)
     mean = _to4(getattr(regressBoxes, "mean", None), [0.0] * 4)
     std = _to4(getattr(regressBoxes, "std", None), [0.1, 0.1, 0.2, 0.2])
     det = detect(classification, regression, anchors, (int(x.shape[2]), int(x.shape[3])), score_thr=threshold,
-                 iou_thr=iou_threshold, variant=variant, mean=mean, std=std, clip=clipBoxes is not None)
+                 iou_thr=iou_threshold, variant=variant, mean=mean, std=std, clip=clipBoxes is not None,
+                 from_logits=from_logits)
     out = []
     sc, lb, bx = det.scores.cpu().numpy(), det.labels.cpu().numpy(), det.boxes.cpu().numpy()
     for b in range(classification.shape[0]):
@@ -219,14 +224,15 @@ def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes,
     return out
 
 
-def eval_tail(classification, regression, anchors, img_batch, regressBoxes=None, score_thr=0.05, iou_thr=0.5):
+def eval_tail(classification, regression, anchors, img_batch, regressBoxes=None, score_thr=0.05, iou_thr=0.5,
+              from_logits: bool = False):
     """What model(img, return_loss=False) returns after the heads (retinanet.py:297-318):
     [scores[K], labels[K] (int64), boxes[K,4]] of IMAGE 0, or the zeros triple when nothing passes."""
     variant = _variant_of(regressBoxes) if regressBoxes is not None else L.DECODE_RETINA
     mean = _to4(getattr(regressBoxes, "mean", None), [0.0] * 4)
     std = _to4(getattr(regressBoxes, "std", None), [0.1, 0.1, 0.2, 0.2])
     det = detect(classification[:1], regression[:1], anchors, (int(img_batch.shape[2]), int(img_batch.shape[3])),
-                 score_thr=score_thr, iou_thr=iou_thr, variant=variant, mean=mean, std=std)
+                 score_thr=score_thr, iou_thr=iou_thr, variant=variant, mean=mean, std=std, from_logits=from_logits)
     if int(det.survivors[0]) == 0:
         dev = classification.device                # retinanet.py:308
         return [torch.zeros([1], device=dev), torch.zeros([1], device=dev), torch.zeros([1, 4], device=dev)]
@@ -234,17 +240,33 @@ def eval_tail(classification, regression, anchors, img_batch, regressBoxes=None,
     return [s, l, b]
 
 
-def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5):
+def strip_head_sigmoid(model) -> bool:
+    """Replace the classification head's final sigmoid by the identity so the head returns logits:
+    ``classificationModel.output_act`` (architectures/retinanet.py:140,159) or the shared head's
+    ``header_act`` (ksevendet/architecture/head/simple_head.py:310).  Returns True if one was found."""
+    found = False
+    for mod in model.modules():
+        for name in ("output_act", "header_act"):
+            if isinstance(getattr(mod, name, None), nn.Sigmoid):
+                setattr(mod, name, nn.Identity())
+                found = True
+    return found
+
+
+def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5, fuse_sigmoid: bool = False):
     """Swap a reference detector's hot-path attributes for the B200 modules and route its
     eval branch through eval_tail().  The model must expose the reference's attribute names
     (anchors, focalLoss, regressBoxes, clipBoxes; retinanet.py:220-230) and a
-    forward(img, annotations=None, return_head=False, return_loss=True)."""
+    forward(img, annotations=None, return_head=False, return_loss=True).
+    fuse_sigmoid: also remove the classification head's final sigmoid (strip_head_sigmoid) and run
+    FocalLoss / the eval tail on the logits; ``return_head=True`` then returns logits."""
     from .anchors import Anchors
     from .losses import FocalLoss
+    from_logits = bool(fuse_sigmoid) and strip_head_sigmoid(model)
     old = model.anchors
     model.anchors = Anchors(pyramid_levels=list(old.pyramid_levels), strides=list(old.strides),
                             sizes=list(old.sizes), ratios=np.asarray(old.ratios), scales=np.asarray(old.scales))
-    model.focalLoss = FocalLoss()
+    model.focalLoss = FocalLoss(from_logits=from_logits)
     model.regressBoxes = BBoxTransform()
     model.clipBoxes = ClipBoxes()
     inner = model.forward
@@ -254,7 +276,7 @@ def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5):
             return inner(img_batch, annotations, return_head=return_head, return_loss=return_loss)
         classification, regression = inner(img_batch, annotations, return_head=True)
         return eval_tail(classification, regression, self.anchors(img_batch), img_batch, self.regressBoxes,
-                         score_thr, iou_thr)
+                         score_thr, iou_thr, from_logits=from_logits)
 
     model.forward = types.MethodType(forward, model)
     return model

@@ -405,3 +405,29 @@ def detect_batch(classifications: torch.Tensor, regressions: torch.Tensor,
     dets = [detect_image(classifications[i], boxes[i], score_thr, iou_thr, use_torchvision)
             for i in range(classifications.shape[0])]
     return boxes, dets
+
+
+# --------------------------------------------------------------------------- head outputs
+def head_logits(logits_per_level, num_anchors: int, num_classes: int) -> torch.Tensor:
+    """The layout step of the classification head without its activation
+    (architectures/retinanet.py:162-178, ksevendet/architecture/head/simple_head.py:289-307):
+    per level NCHW [B, num_anchors*num_classes, H, W] -> permute(0,2,3,1) -> [B, H*W*num_anchors, C],
+    levels concatenated along dim 1 (retinanet.py:286).  Anchor order: cell row, cell column, in-cell
+    anchor - the order Anchors.forward generates (anchors.py:99-119)."""
+    out = []
+    for z in logits_per_level:
+        b = z.shape[0]
+        assert z.shape[1] == num_anchors * num_classes
+        out.append(z.permute(0, 2, 3, 1).contiguous().view(b, -1, num_classes))
+    return torch.cat(out, dim=1)
+
+
+def head_probabilities(logits_per_level, num_anchors: int, num_classes: int, act_first: bool = True) -> torch.Tensor:
+    """What the reference hands to FocalLoss / the eval tail: `output_act = nn.Sigmoid()` on the NCHW
+    logits, then the layout (retinanet.py:159-178; act_first=True), or the layout and then `header_act`
+    on the concatenated [B,A,C] tensor (simple_head.py:289-310; act_first=False).  Mathematically the
+    same; on CPU the two orders can differ in the last bit of single elements (ATen's vectorised
+    sigmoid handles the tail of a buffer with another code path), so each is restated in its own order."""
+    if act_first:
+        return head_logits([torch.sigmoid(z) for z in logits_per_level], num_anchors, num_classes)
+    return torch.sigmoid(head_logits(logits_per_level, num_anchors, num_classes))

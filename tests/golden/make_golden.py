@@ -14,6 +14,8 @@ and writes
   tests/golden/anchors.json        sha256 + sampled rows of Anchors()(image) per recipe
   tests/golden/loss_*.npz          inputs, reference losses, autograd grads, IoU max/argmax/state
   tests/golden/detect_*.npz        inputs, decoded+clipped boxes, per-image keep / scores / labels / boxes
+  tests/golden/head_retina.npz     per-level NCHW logits of the reference's ClassificationModel (captured in
+                                   front of its output_act) and the [B,A,C] probabilities it returns
 The reference's hidden intermediates (IoU_max, IoU_argmax, masks) are obtained by
 calling the reference's own calc_iou and repeating losses.py:66,79-82 on its output.
 """
@@ -253,7 +255,30 @@ def gen_detect():
         print(f"detect_{name}: A={A} (survivors, kept)={counts}")
 
 
+def gen_head():
+    """architectures/retinanet.py:119-178: what the classification head hands to the hot path, and the
+    logits it had right before `output_act` (the tensor the from_logits path consumes)."""
+    from architectures.retinanet import ClassificationModel
+    torch.manual_seed(20260411)
+    A_cell, Cn, F = 9, 5, 8
+    head = ClassificationModel(F, num_anchors=A_cell, num_classes=Cn, feature_size=8).eval()
+    with torch.no_grad():                     # spread the logits (the default init gives p ~ 0.01 everywhere)
+        head.output.weight.mul_(40.0)
+        head.output.bias.uniform_(-4.0, 1.0)
+    grabbed = []
+    head.output.register_forward_hook(lambda m, i, o: grabbed.append(o.detach().clone()))
+    feats = [torch.randn(2, F, 6, 5), torch.randn(2, F, 3, 3), torch.randn(2, F, 2, 1)]
+    with torch.no_grad():
+        probs = torch.cat([head(f) for f in feats], dim=1)          # retinanet.py:286
+    rec = {"probs": probs.numpy(), "num_anchors": A_cell, "num_classes": Cn}
+    for i, g in enumerate(grabbed):
+        rec[f"logits_l{i}"] = g.numpy()
+    np.savez_compressed(os.path.join(HERE, "head_retina.npz"), **rec)
+    print("head_retina", probs.shape, float(probs.min()), float(probs.max()))
+
+
 if __name__ == "__main__":
     gen_anchors()
     gen_loss()
     gen_detect()
+    gen_head()

@@ -442,3 +442,106 @@ def test_baseline_shapes_last_image_vs_oracle(name):
     assert np.array_equal(det.labels[b, :k].cpu().numpy(), d.labels.numpy())
     np.testing.assert_array_equal(det.scores[b, :k].cpu().numpy(), d.scores.numpy())
     np.testing.assert_allclose(det.boxes[b, :k].cpu().numpy(), d.boxes.numpy(), rtol=1e-5, atol=2e-4)
+
+
+# ---------------------------------------------------------------------------------- fused sigmoid
+@pytest.mark.parametrize("shape", [(2, 5, 6), (3, 90, 9), (2, 1, 7), (1, 33, 4)], ids=lambda s: "B%d_C%d_M%d" % s)
+def test_focal_loss_from_logits_vs_oracle(shape):
+    """FocalLoss(from_logits=True) on the head's pre-sigmoid logits against the oracle's
+    sigmoid (head activation, retinanet.py:159) + focal loss, gradients taken with respect to the logits."""
+    B, C, M = shape
+    H, W = 96, 128
+    anc_np = R.retina_anchors(H, W)
+    A = anc_np.shape[0]
+    gen = torch.Generator().manual_seed(B * 100 + C)
+    ann = b200det.synth.make_annotations(B, M, C, H, W, gen, gt_min=8.0, gt_max=70.0)
+    z = (torch.randn((B, A, C), generator=gen) * 2.5 - 3.0).contiguous()
+    z[0, :50] = torch.linspace(-12.0, 12.0, 50)[:, None]       # both clamp ends of losses.py:62
+    reg = torch.randn((B, A, 4), generator=gen) * 0.5
+    anc = torch.from_numpy(anc_np)[None]
+    z0, r0 = z.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    want = R.focal_loss(torch.sigmoid(z0), r0, anc, ann)
+    (want.cls_mean + want.reg_mean).sum().backward()
+    z1, r1 = z.to(DEV).requires_grad_(True), reg.to(DEV).requires_grad_(True)
+    mod = b200det.FocalLoss(from_logits=True)
+    lc, lr = mod(z1, r1, anc.to(DEV), ann.to(DEV))
+    (lc + lr).sum().backward()
+    np.testing.assert_allclose(lc.item(), want.cls_mean.item(), rtol=1e-5)
+    np.testing.assert_allclose(lr.item(), want.reg_mean.item(), rtol=1e-5)
+    assert mod.last_num_positives.cpu().tolist() == want.num_pos
+    # 2e-5: the reference's own float32 sigmoid backward p*(1-p) carries a rounding of this size for p -> 1
+    np.testing.assert_allclose(z1.grad.cpu().numpy(), z0.grad.numpy(), rtol=2e-5, atol=1e-10)
+    np.testing.assert_allclose(r1.grad.cpu().numpy(), r0.grad.numpy(), rtol=1e-5, atol=1e-9)
+    # the probability path on sigmoid(z) agrees with the fused path
+    with torch.no_grad():
+        lc2, lr2 = b200det.FocalLoss()(torch.sigmoid(z.to(DEV)), reg.to(DEV), anc.to(DEV), ann.to(DEV))
+    np.testing.assert_allclose(lc2.item(), lc.item(), rtol=1e-5)
+    np.testing.assert_allclose(lr2.item(), lr.item(), rtol=1e-6)
+
+
+def test_detect_from_logits_matches_probability_path():
+    """detect(from_logits=True) == detect on torch.sigmoid(logits): same survivors (strict threshold on
+    the float32 probability), bit-identical scores, labels decided on the probabilities (an earlier
+    class whose lower logit rounds to the same probability wins, saturated logits tie), same keep."""
+    H, W, B, C = 128, 160, 3, 12
+    gen = torch.Generator().manual_seed(5)
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    A = anc.shape[1]
+    z = (torch.randn((B, A, C), generator=gen) * 1.5 - 4.0)
+    reg = torch.randn((B, A, 4), generator=gen) * 0.5
+    thr_z = float(np.log(0.05 / 0.95))
+    z[0, :400, 2] = thr_z + torch.linspace(-2e-6, 2e-6, 400)     # rows sitting on the threshold
+    z[1, 10, 3], z[1, 10, 7] = 9.0, 9.0001                        # plateau of the float32 sigmoid
+    z[1, 11, 5], z[1, 11, 1] = 30.0, 20.0                         # saturation: both are exactly 1.0
+    z[2, 12, 4], z[2, 12, 9] = 2.0, 2.0                           # equal logits
+    zd, rd = z.to(DEV), reg.to(DEV)
+    p = torch.sigmoid(zd)
+    assert float(p[1, 10, 3]) == float(p[1, 10, 7]) and float(p[1, 11, 1]) == 1.0
+    a = b200det.detect(zd, rd, anc, (H, W), from_logits=True)
+    w = b200det.detect(p, rd, anc, (H, W))
+    assert a.survivors.tolist() == w.survivors.tolist() and a.count.tolist() == w.count.tolist()
+    assert 0 < int(w.survivors[0]) and int(w.survivors[0]) < A
+    for b in range(B):
+        k = int(w.count[b])
+        assert torch.equal(a.anchor_ids[b, :k], w.anchor_ids[b, :k])
+        assert torch.equal(a.scores[b, :k], w.scores[b, :k])
+        assert torch.equal(a.labels[b, :k], w.labels[b, :k])
+        assert torch.equal(a.boxes[b, :k], w.boxes[b, :k])
+    # the crafted rows survive with the label torch.max over the probabilities gives
+    for (b, row, lab) in ((1, 10, 3), (1, 11, 1), (2, 12, 4)):
+        pos = (w.anchor_ids[b, :int(w.count[b])] == row).nonzero()
+        if pos.numel():
+            assert int(a.labels[b, int(pos[0])]) == lab == int(p[b, row].argmax())
+    # and against the oracle on the CPU copy of those probabilities
+    _, dets = R.detect_batch(p.cpu(), reg, anc.cpu(), H, W)
+    for b, d in enumerate(dets):
+        k = int(a.count[b])
+        assert np.array_equal(a.anchor_ids[b, :k].cpu().numpy(), d.keep_anchor.numpy())
+        assert np.array_equal(a.labels[b, :k].cpu().numpy(), d.labels.numpy())
+
+
+def test_strip_head_sigmoid_and_head_fixture():
+    """The reference head's logits (golden, captured in front of output_act) through the fused path
+    equal the probability path on the reference's own head output."""
+    g = np.load(os.path.join(GOLDEN, "head_retina.npz"))
+    levels = [torch.from_numpy(g[f"logits_l{i}"]) for i in range(3)]
+    z = R.head_logits(levels, int(g["num_anchors"]), int(g["num_classes"])).to(DEV)
+    probs = torch.from_numpy(g["probs"]).to(DEV)
+    B, A, C = probs.shape
+    gen = torch.Generator().manual_seed(1)
+    anc = torch.rand((A, 2), generator=gen) * 80
+    anc = torch.cat([anc, anc + 8 + torch.rand((A, 2), generator=gen) * 40], 1)[None].to(DEV)
+    ann = b200det.synth.make_annotations(B, 4, C, 128, 128, gen, gt_min=8.0, gt_max=48.0).to(DEV)
+    reg = (torch.randn((B, A, 4), generator=gen) * 0.3).to(DEV)
+    l1 = b200det.FocalLoss(from_logits=True)(z, reg, anc, ann)
+    l0 = b200det.FocalLoss()(probs, reg, anc, ann)
+    np.testing.assert_allclose(l1[0].item(), l0[0].item(), rtol=1e-5)
+    np.testing.assert_allclose(l1[1].item(), l0[1].item(), rtol=1e-6)
+
+    class Head(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.output_act = torch.nn.Sigmoid()
+    m = torch.nn.Sequential(Head())
+    assert b200det.strip_head_sigmoid(m) and isinstance(m[0].output_act, torch.nn.Identity)

@@ -64,12 +64,21 @@ def test_library_exports_every_declared_symbol():
     assert L.lib().k7_version() == L.ABI_VERSION
 
 
-def test_struct_layout_matches_header():
-    # sizes the C compiler gives (include/k7det.h); a mismatch would corrupt every call
-    assert C.sizeof(L.K7AnchorSpec) == 6 * 4 + 8 * 4 * 2 + 9 * 4 + 4 + 8 * 8 + 8 * 16 * 4 * 8
-    assert C.sizeof(L.K7LossParams) == 36
-    assert C.sizeof(L.K7DecodeParams) == 48
-    assert C.sizeof(L.K7DetectParams) == 64
+def test_struct_layout_matches_header(tmp_path):
+    """sizeof of every struct as the C compiler sees include/k7det.h == the ctypes mirror
+    (a mismatch would corrupt every call)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %d\\n",'
+                   'sizeof(K7AnchorSpec),sizeof(K7MatchParams),sizeof(K7LossParams),sizeof(K7DecodeParams),'
+                   'sizeof(K7DetectParams),K7_ABI_VERSION);return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    want = [C.sizeof(L.K7AnchorSpec), C.sizeof(L.K7MatchParams), C.sizeof(L.K7LossParams), C.sizeof(L.K7DecodeParams),
+            C.sizeof(L.K7DetectParams), L.ABI_VERSION]
+    assert got == want
 
 
 def test_no_cpu_fallback():

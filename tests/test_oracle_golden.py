@@ -113,3 +113,16 @@ def test_greedy_nms_equals_torchvision_random():
             want = nms(torch.from_numpy(boxes), torch.from_numpy(scores), thr).numpy()
             got = R.greedy_nms(boxes, scores, thr)
             assert np.array_equal(got, want)
+
+
+def test_head_layout_and_activation():
+    """The oracle's head restatement (layout + sigmoid) reproduces the reference's
+    ClassificationModel output from the logits captured in front of its output_act."""
+    g = np.load(os.path.join(GOLDEN, "head_retina.npz"))
+    levels = [torch.from_numpy(g[f"logits_l{i}"]) for i in range(3)]
+    got = R.head_probabilities(levels, int(g["num_anchors"]), int(g["num_classes"]))
+    assert got.shape == g["probs"].shape
+    assert np.array_equal(got.numpy(), g["probs"])
+    # the shared-head order (layout, then activation: simple_head.py:307-310) agrees to the last bit or one ulp
+    late = R.head_probabilities(levels, int(g["num_anchors"]), int(g["num_classes"]), act_first=False)
+    np.testing.assert_allclose(late.numpy(), g["probs"], rtol=2e-7, atol=0)
