@@ -327,6 +327,26 @@ def run_b200(args, wl):
         "k7_match_ms": ms_match, "k7_loss_fwd_ms": ms_k_f, "k7_loss_fwd_bwd_ms": ms_k_fb,
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
+    # the same stages fed with the head's pre-sigmoid logits (sigmoid fused), next to the
+    # stock elementwise sigmoid pass (and its autograd backward) that they make unnecessary
+    z = torch.logit(cls)
+    z_g = z.detach().requires_grad_(True)
+    loss_lg = b200det.FocalLoss(sharded=world > 1, from_logits=True)
+
+    def train_side_logits():
+        z_g.grad = None
+        reg_g.grad = None
+        lc, lr = loss_lg(z_g, reg_g, anchors_mod(img), ann)
+        (lc + lr).sum().backward()
+
+    ms_fb_lg = timed(train_side_logits, k, 3)
+    ms_det_lg = timed(lambda: b200det.detect(z, reg, anchors_mod(img), hw, sync=False, from_logits=True), k, 3)
+    ms_sig = timed(lambda: torch.sigmoid(z), k, 3)
+    out["parts"]["from_logits"] = {
+        "match_loss_fwd_bwd_ms": ms_fb_lg, "decode_nms_ms": ms_det_lg,
+        "torch_sigmoid_pass_ms_saved_per_side": ms_sig,
+        "note": "FocalLoss(from_logits=True) / detect(from_logits=True): the head's sigmoid runs in registers"}
+    del z, z_g
     ach = gbs(bytes_fb, ms_k_fb)
     out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: stream kernel + row/reduction kernel)",
                        "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,

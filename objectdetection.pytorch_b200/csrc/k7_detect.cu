@@ -268,9 +268,11 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
             const uint4 ent = queue[base + lane];
             const uint32_t b = ent.x & 0x7fffffffu;
             uint32_t a = ent.y;
-            int idx = (int)ent.z;
+            int idx = (int)(ent.z & 0x7fffffffu);
+            bool tie_scan = (ent.z >> 31) != 0u;   // LOGITS: an earlier class may round to the same probability
             float m = __uint_as_float(ent.w);
             if (ent.x >> 31) {
+                tie_scan = true;
                 a = k7_div(ent.y, G.div_c);
                 const int c = (int)(ent.y - a * (uint32_t)C);
                 const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
@@ -293,13 +295,15 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                 // an earlier class with a slightly lower logit may round to the same probability.  Such a
                 // logit lies within 2^-23/(1-p) of m; beyond z = 8 the plateau widens, so every earlier
                 // logit above 8 is checked.
-                const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
-                const float lo = fminf(m - 2e-3f, 8.0f);
-                for (int q = 0; q < idx; ++q) {
-                    const float v = __ldg(row + q);
-                    if (v >= lo && k7_sigmoid_precise(v) == p) {
-                        idx = q;
-                        break;
+                if (tie_scan) {   // rare: flagged when the row was reduced in shared memory
+                    const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
+                    const float lo = fminf(m - 2e-3f, 8.0f);
+                    for (int q = 0; q < idx; ++q) {
+                        const float v = __ldg(row + q);
+                        if (v >= lo && k7_sigmoid_precise(v) == p) {
+                            idx = q;
+                            break;
+                        }
                     }
                 }
                 m = p;
@@ -400,7 +404,14 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                                 }
                             }
                             if (idx != c) continue;   // warp-uniform
-                            if (lane == 0) queue[qn] = make_uint4(bimg, a, (uint32_t)idx, __float_as_uint(m));
+                            uint32_t flag = 0u;
+                            if (LOGITS) {   // does an earlier class sit on the same float32-sigmoid plateau as the maximum?
+                                const float lo = fminf(m - 2e-3f, 8.0f);
+                                bool cnd = false;
+                                for (int q = lane; q < idx; q += 32) cnd |= row[q] >= lo;
+                                flag = __any_sync(0xffffffffu, cnd) ? 0x80000000u : 0u;
+                            }
+                            if (lane == 0) queue[qn] = make_uint4(bimg, a, (uint32_t)idx | flag, __float_as_uint(m));
                             ++qn;
                         }
                     }

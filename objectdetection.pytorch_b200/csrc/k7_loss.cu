@@ -93,13 +93,13 @@ __device__ __forceinline__ float k7_rcp_approx(float x) {
 
 // sigmoid of two logits for the streaming pass: e = 2^(-z*log2 e) (MUFU.EX2), r = 1/(1+e) (MUFU.RCP);
 // relative error ~3e-7, far inside the 1e-5 contract of the losses (the eval side, where the
-// survivor set must be bit-exact, uses the precise form).  dsig = sigma'(z) = e * r * r.
+// survivor set must be bit-exact, uses the precise form).
 __device__ __forceinline__ float k7_ex2_approx(float x) {
     float r;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
-__device__ __forceinline__ float2 k7_sigmoid_pair(const float2 z, float2& dsig) {
+__device__ __forceinline__ float2 k7_sigmoid_pair(const float2 z) {
     const float2 t = __fmul2_rn(z, make_float2(-1.4426950408889634f, -1.4426950408889634f));
     float2 e;
     e.x = k7_ex2_approx(t.x);
@@ -108,8 +108,24 @@ __device__ __forceinline__ float2 k7_sigmoid_pair(const float2 z, float2& dsig) 
     float2 r;
     r.x = k7_rcp_approx(d.x);
     r.y = k7_rcp_approx(d.y);
-    dsig = __fmul2_rn(__fmul2_rn(e, r), r);
     return r;
+}
+// The same with everything the gradient needs from ONE exponential and ONE reciprocal per element:
+// ez = e^z (the exponent is capped so that it stays finite), r = 1/(1+ez) = 1 - sigma,
+// sigma = ez*r, sigma' = sigma*r, and p/(1-p) = ez.
+__device__ __forceinline__ float2 k7_sigmoid_pair_grad(const float2 z, float2& ez, float2& dsig) {
+    float2 t = __fmul2_rn(z, make_float2(1.4426950408889634f, 1.4426950408889634f));
+    t.x = fminf(t.x, 126.0f);
+    t.y = fminf(t.y, 126.0f);
+    ez.x = k7_ex2_approx(t.x);
+    ez.y = k7_ex2_approx(t.y);
+    const float2 d = __fadd2_rn(ez, make_float2(1.0f, 1.0f));
+    float2 r;
+    r.x = k7_rcp_approx(d.x);
+    r.y = k7_rcp_approx(d.y);
+    const float2 sg = __fmul2_rn(ez, r);
+    dsig = __fmul2_rn(sg, r);
+    return sg;
 }
 
 // Two "target 0" elements.  Returns their gradients (GRAD), accumulates p^2 * -log(1-p) into acc
@@ -118,8 +134,8 @@ __device__ __forceinline__ float2 k7_sigmoid_pair(const float2 z, float2& dsig) 
 template <bool GRAD, bool MASKED, bool LOGITS>
 __device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t ign, const float2 sco, float2& acc,
                                               float& pmax) {
-    float2 dsig = make_float2(1.0f, 1.0f);
-    const float2 x = LOGITS ? k7_sigmoid_pair(xin, dsig) : xin;
+    float2 dsig = make_float2(1.0f, 1.0f), ez = make_float2(0.0f, 0.0f);
+    const float2 x = LOGITS ? (GRAD ? k7_sigmoid_pair_grad(xin, ez, dsig) : k7_sigmoid_pair(xin)) : xin;
     float2 p;
     p.x = fminf(fmaxf(x.x, K7_P_LO), K7_P_HI);
     p.y = fminf(fmaxf(x.y, K7_P_LO), K7_P_HI);
@@ -142,10 +158,15 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t i
     acc = __ffma2_rn(t, nl, acc);
     float2 g = make_float2(0.0f, 0.0f);
     if (GRAD) {
-        float2 r;
-        r.x = k7_rcp_approx(q.x);
-        r.y = k7_rcp_approx(q.y);
-        const float2 u = __fmul2_rn(p, r);                                   // p / (1-p)
+        float2 u;                                                            // p / (1-p)
+        if (LOGITS) {
+            u = ez;   // exact identity for an unclamped p; a clamped p gets a zero gradient below anyway
+        } else {
+            float2 r;
+            r.x = k7_rcp_approx(q.x);
+            r.y = k7_rcp_approx(q.y);
+            u = __fmul2_rn(p, r);
+        }
         const float2 v = __ffma2_rn(make_float2(2.0f, 2.0f), nl, u);         // 2*nl + p/(1-p)
         float2 w = __fmul2_rn(p, sco);                                       // (1-alpha) * scale * p
         if (LOGITS) w = __fmul2_rn(w, dsig);                                 // chain rule through the sigmoid

@@ -43,6 +43,16 @@ def main():
                                               dreg_zeroed=dreg0, ignore_bits=bits, **kw),
         "detect": lambda: b200det.detect(cls, reg, anc, (wl.height, wl.width), sync=False),
     }
+    if "logits" in args.stages:
+        z = torch.logit(cls)                      # the head's pre-sigmoid tensor
+        stages.update({
+            "loss_fwd_logits": lambda: BL.loss_stage(anc, z, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits,
+                                                     from_logits=True, **kw),
+            "loss_fwd_bwd_logits": lambda: BL.loss_stage(anc, z, reg, ann, assign, num_pos, want_grad=True,
+                                                         dreg_zeroed=dreg0, ignore_bits=bits, from_logits=True, **kw),
+            "detect_logits": lambda: b200det.detect(z, reg, anc, (wl.height, wl.width), sync=False, from_logits=True),
+            "torch_sigmoid": lambda: torch.sigmoid(z),
+        })
     for name in args.stages.split(","):
         fn = stages[name]
         fn()
