@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 3
+#define K7_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -151,6 +151,20 @@ K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order
             float* per_image, float* sums, float* dcls, float* dreg,
             void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same on the classification head's RAW outputs: one NCHW tensor per pyramid level,
+ * levels[l] = [B, cell_anchors*C, fh[l], fw[l]] float32 (channel = in-cell anchor * C + class), i.e. what the
+ * head's last convolution writes BEFORE permute(0,2,3,1) / view / cat (retinanet.py:162-178, 286;
+ * simple_head.py:289-307) - those passes, and with params->from_logits the sigmoid, never touch memory.
+ * `levels` / `dlevels` are HOST arrays of spec->num_levels device pointers (16-byte aligned); dlevels[l]
+ * (optional, with dreg) receives d(loss)/d(levels[l]) in the same layout.  An anchor spec is required
+ * (the level geometry comes from it); regressions stay [B,A,4]. */
+K7_API size_t k7_loss_levels_workspace_bytes(const K7AnchorSpec* spec, int B, int C);
+K7_API int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
+                   const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                   const int32_t* num_pos, int B, int C, int M, const K7LossParams* params,
+                   float* per_image, float* sums, float* const* dlevels, float* dreg,
+                   void* workspace, size_t workspace_bytes, void* stream);
+
 /* grad *= *scale (device scalar); no-op when *scale == 1.  Used by the autograd backward
  * when the incoming gradient of a loss output is not 1. */
 K7_API int k7_scale_inplace(float* grad, size_t n, const float* scale, void* stream);
@@ -196,6 +210,11 @@ K7_API int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_ord
               const float* cls, const float* reg, int B, int A, int C,
               const K7DetectParams* params, int32_t* counts,
               void* workspace, size_t workspace_bytes, void* stream);
+
+/* k7_detect on the head's per-level NCHW outputs (see k7_loss_levels); same workspace, same results. */
+K7_API int k7_detect_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg, int B, int C,
+                     const K7DetectParams* params, int32_t* counts, void* workspace, size_t workspace_bytes,
+                     void* stream);
 
 /* Copies the kept detections of image b to row-major outputs with `cap` rows per image:
  *   scores [B,cap] f32, labels [B,cap] i64, boxes [B,cap,4] f32,

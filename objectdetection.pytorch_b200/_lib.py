@@ -78,7 +78,7 @@ class K7DetectParams(C.Structure):
     ]
 
 
-ABI_VERSION = 3                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 4                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -98,6 +98,9 @@ SYMBOLS = {
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),
                           _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "k7_loss_levels_workspace_bytes": (C.c_size_t, [C.POINTER(K7AnchorSpec), C.c_int, C.c_int]),
+    "k7_loss_levels": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int,
+                                 C.POINTER(K7LossParams), _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "k7_scale_inplace": (C.c_int, [_P, C.c_size_t, _P, _P]),
     "k7_decode": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_size_t, _P, C.c_int, C.c_int,
                             C.POINTER(K7DecodeParams), _P, _P]),
@@ -105,6 +108,8 @@ SYMBOLS = {
     "k7_detect_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_detect": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, C.c_int, C.c_int, C.c_int,
                             C.POINTER(K7DetectParams), _P, _P, C.c_size_t, _P]),
+    "k7_detect_levels": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P, C.c_int, C.c_int, C.POINTER(K7DetectParams), _P, _P,
+                                   C.c_size_t, _P]),
     "k7_detect_gather": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int,
                                    _P, _P, _P, _P, _P, _P]),
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
@@ -179,3 +184,34 @@ def as_f32_contig(t: torch.Tensor) -> torch.Tensor:
     if t.data_ptr() % 16:
         t = t.clone(memory_format=torch.contiguous_format)
     return t
+
+
+def ptr_array(tensors):
+    """Host array of device pointers (const float* const*) for the per-level entry points; None stays NULL."""
+    if tensors is None:
+        return None
+    return (C.c_void_p * len(tensors))(*[t.data_ptr() if t is not None else None for t in tensors])
+
+
+def check_levels(levels, spec, B=None):
+    """Per-level head outputs [B, cell_anchors*C, fh, fw] (NCHW, float32, contiguous, CUDA).  Returns (B, C)."""
+    if spec is None:
+        raise ValueError("per-level head outputs need anchors built by b200det.Anchors (the level geometry comes from them)")
+    if len(levels) != spec.num_levels:
+        raise ValueError(f"{len(levels)} level tensors for an anchor recipe of {spec.num_levels} levels")
+    Cn = None
+    for l, t in enumerate(levels):
+        require_cuda(t)
+        if t.dim() != 4 or t.dtype != torch.float32 or not t.is_contiguous():
+            raise ValueError("level tensors must be contiguous float32 [B, anchors*classes, H, W]")
+        if B is None:
+            B = t.shape[0]
+        if t.shape[0] != B or t.shape[2] != spec.fh[l] or t.shape[3] != spec.fw[l] or t.shape[1] % spec.cell_anchors:
+            raise ValueError(f"level {l}: shape {tuple(t.shape)} does not match the anchor recipe "
+                             f"({spec.cell_anchors} anchors per cell on a {spec.fh[l]}x{spec.fw[l]} grid)")
+        c = t.shape[1] // spec.cell_anchors
+        if Cn is None:
+            Cn = c
+        if c != Cn:
+            raise ValueError("levels disagree on the number of classes")
+    return B, Cn

@@ -19,6 +19,7 @@
 //      identical to the sequential algorithm.  Images with more survivors than the workspace's cap
 //      go through k7_sort_nms_kernel (one CTA, chunks of 1024 boxes).
 #include <math.h>
+#include <string.h>
 
 #include "k7_common.cuh"
 
@@ -461,6 +462,85 @@ static int k7_score_geometry(int B, int A, int C, K7ScoreGeom* g) {
     if (nt < (unsigned long long)grid) grid = (int)nt;
     g->grid = grid < 1 ? 1 : grid;
     return K7_OK;
+}
+
+// ------------------------------------------------------------------ kernel 1': the same on per-level NCHW head outputs
+// levels[l] = [B, K*C, S_l] (layout in k7_loss.cu): the C scores of anchor (s, k) are
+// S_l floats apart, so one THREAD owns an anchor and walks its classes; consecutive threads own
+// consecutive cells of one in-cell anchor plane, i.e. every load instruction of a warp reads 128
+// contiguous bytes.  Running maximum and FIRST arg-max (strict '>'), then exactly the survivor
+// record of k7_score_pipe_kernel's drain.  Plain loads, eight in flight per thread: the kernel is a
+// pure stream.
+struct K7ScoreLevels {
+    const float* cls[K7_MAX_LEVELS];
+    int S[K7_MAX_LEVELS];
+    int blk_off[K7_MAX_LEVELS + 1];   // first block (of 256 anchors) of each level; [num_levels] = grid.x
+};
+
+template <bool LOGITS>
+__global__ void __launch_bounds__(256)
+k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV,
+                       const float4* __restrict__ reg, int A, int C, float report_thr,
+                       const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
+                       float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+    const int b = blockIdx.y;
+    int l = 0;
+#pragma unroll
+    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+        if (i < spec.num_levels && (int)blockIdx.x >= LV.blk_off[i]) l = i;
+    const int K = spec.cell_anchors, S = LV.S[l];
+    const int t = ((int)blockIdx.x - LV.blk_off[l]) * 256 + (int)threadIdx.x;
+    if (t >= K * S) return;
+    const int k = t / S, s = t - k * S;
+    const float* base = LV.cls[l] + ((size_t)b * K * C + (size_t)k * C) * (size_t)S + (size_t)s;
+    float m = -INFINITY;
+    int idx = 0;
+    int c = 0;
+    for (; c + 8 <= C; c += 8) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __ldg(base + (size_t)(c + j) * S);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            if (v[j] > m) {
+                m = v[j];
+                idx = c + j;
+            }
+    }
+    for (; c < C; ++c) {
+        const float v = __ldg(base + (size_t)c * S);
+        if (v > m) {
+            m = v;
+            idx = c;
+        }
+    }
+    if (!(m > report_thr)) return;
+    if (LOGITS) {
+        const float p = k7_sigmoid_precise(m);
+        if (!(p > P.score_thr)) return;
+        const float lo = fminf(m - 2e-3f, 8.0f);   // see k7_score_pipe_kernel: plateau of the float32 sigmoid
+        for (int q = 0; q < idx; ++q) {
+            const float v = __ldg(base + (size_t)q * S);
+            if (v >= lo && k7_sigmoid_precise(v) == p) {
+                idx = q;
+                break;
+            }
+        }
+        m = p;
+    }
+    const int a = spec.offset[l] + s * K + k;
+    float ax1, ay1, ax2, ay2;
+    k7_anchor_from_spec(spec, a, ax1, ay1, ax2, ay2);
+    const size_t oa = (size_t)b * A + a;
+    const float4 dl = __ldg(reg + oa);
+    K7Box o = (P.decode.variant == K7_DECODE_RETINA)
+                  ? k7_decode_retina(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w, P.decode.mean, P.decode.std)
+                  : k7_decode_effdet(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w);
+    if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
+    box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
+    label_ws[oa] = idx;
+    score_ws[oa] = m;
+    atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
 }
 
 // ------------------------------------------------------------------ kernel 2: per-image sort + NMS
@@ -1410,12 +1490,13 @@ k7_gather_kernel(int A, int W32, int cap, const int32_t* __restrict__ kept_count
 }
 
 // ------------------------------------------------------------------ host: k7_detect
-extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
-                         int B, int A, int C, const K7DetectParams* params, int32_t* counts, void* workspace,
-                         size_t workspace_bytes, void* stream) {
-    K7_REQUIRE(cls && reg && params && workspace, "k7_detect: null argument");
+static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls,
+                         const float* const* levels, const float* reg, int B, int A, int C, const K7DetectParams* params,
+                         int32_t* counts, void* workspace, size_t workspace_bytes, void* stream) {
+    K7_REQUIRE((cls || levels) && reg && params && workspace, "k7_detect: null argument");
     K7_REQUIRE(spec || anchors, "k7_detect: need an anchor spec or an anchor tensor");
     K7_REQUIRE(B > 0 && A > 0 && C > 0, "k7_detect: bad shape B=%d A=%d C=%d", B, A, C);
+    K7_REQUIRE(B <= 65535, "k7_detect: B > 65535 not supported");
     K7_REQUIRE(params->iou_thr >= 0.0f, "k7_detect: iou_thr must be >= 0");
     K7_REQUIRE(params->decode.variant == K7_DECODE_RETINA || params->decode.variant == K7_DECODE_EFFDET,
                "k7_detect: bad decode variant");
@@ -1441,21 +1522,45 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
                                                       reinterpret_cast<unsigned char*>(w.surv_count)), st));
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-    {
+    float report_thr = params->score_thr;
+    if (params->from_logits) {
+        // logit(thr) lowered by a margin: the exact float32 sigmoid decides in the kernel
+        const double t = (double)params->score_thr;
+        if (t <= 0.0) report_thr = -INFINITY;
+        else if (t >= 1.0) report_thr = INFINITY;   // sigmoid <= 1: nothing can pass a strict '>'
+        else {
+            const double z = log(t / (1.0 - t));
+            report_thr = (float)(z - 1e-3 * (1.0 + fabs(z)));
+        }
+    }
+    if (levels) {
+        K7ScoreLevels LV;
+        memset(&LV, 0, sizeof(LV));
+        int blocks = 0;
+        for (int l = 0; l < spec->num_levels; ++l) {
+            const int S = spec->fh[l] * spec->fw[l];
+            K7_REQUIRE(S == 0 || (levels[l] && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0),
+                       "k7_detect_levels: level %d: null or unaligned tensor", l);
+            LV.cls[l] = levels[l];
+            LV.S[l] = S;
+            LV.blk_off[l] = blocks;
+            blocks += (spec->cell_anchors * S + 255) / 256;
+        }
+        for (int l = spec->num_levels; l <= K7_MAX_LEVELS; ++l) LV.blk_off[l] = blocks;
+        if (blocks > 0) {
+            dim3 grid(blocks, B);
+            if (params->from_logits)
+                k7_score_levels_kernel<true><<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr,
+                                                                   *params, w.bits, w.W32, w.box, w.label, w.score);
+            else
+                k7_score_levels_kernel<false><<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr,
+                                                                    *params, w.bits, w.W32, w.box, w.label, w.score);
+            K7_LAUNCH_CHECK();
+        }
+    } else {
         K7ScoreGeom GS;
         int rc = k7_score_geometry(B, A, C, &GS);
         if (rc) return rc;
-        float report_thr = params->score_thr;
-        if (params->from_logits) {
-            // logit(thr) lowered by a margin: the exact float32 sigmoid decides in the kernel's drain
-            const double t = (double)params->score_thr;
-            if (t <= 0.0) report_thr = -INFINITY;
-            else if (t >= 1.0) report_thr = INFINITY;   // sigmoid <= 1: nothing can pass a strict '>'
-            else {
-                const double z = log(t / (1.0 - t));
-                report_thr = (float)(z - 1e-3 * (1.0 + fabs(z)));
-            }
-        }
 #define K7_SPIPE_LAUNCH(SP, LG)                                                                                          \
     do {                                                                                                                 \
         auto kern = k7_score_pipe_kernel<SP, LG>;                                                                        \
@@ -1502,6 +1607,22 @@ extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box
     }
     K7_LAUNCH_CHECK();
     return K7_OK;
+}
+
+extern "C" int k7_detect(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
+                         int B, int A, int C, const K7DetectParams* params, int32_t* counts, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+    K7_REQUIRE(cls, "k7_detect: null argument");
+    return k7_detect_run(spec, anchors, box_order, cls, nullptr, reg, B, A, C, params, counts, workspace, workspace_bytes,
+                         stream);
+}
+
+extern "C" int k7_detect_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg, int B, int C,
+                                const K7DetectParams* params, int32_t* counts, void* workspace, size_t workspace_bytes,
+                                void* stream) {
+    K7_REQUIRE(spec && levels, "k7_detect_levels: an anchor spec and the level tensors are required");
+    return k7_detect_run(spec, nullptr, spec->box_order, nullptr, levels, reg, B, spec->total, C, params, counts, workspace,
+                         workspace_bytes, stream);
 }
 
 extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B, int A, int C, int cap, float* scores,

@@ -43,6 +43,7 @@
 //
 // Algorithmic bytes per image: forward A*(4C+16)+20M, forward+backward A*(8C+32)+20M.
 #include <stdlib.h>
+#include <string.h>
 
 #include "k7_common.cuh"
 
@@ -274,6 +275,7 @@ struct K7PipeGeom {
     uint32_t num_tiles;      // ceil(N4 / tile_f)
     uint32_t W;              // ignore-bit words per image, K7_IGNORE_WORDS(A)
     K7FastDiv div_c;         // / C for tile-local indices
+    uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x] (several launches share one table)
     uint32_t side_words;     // words reserved per ignore-bit part (two parts per stage)
     uint32_t stage_stride;
     uint32_t off_desc, off_mask, off_bars;
@@ -447,20 +449,28 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
                 const int k_lo = (int)k7_div((uint32_t)(rem + i_lo), G.div_c);
                 const int k_hi = (int)k7_div((uint32_t)(rem + i_hi - 1), G.div_c);
 
-                // ---- ignored rows of the slice -> element mask (warp-uniform window reads)
+                // ---- ignored rows of the slice -> element mask
                 uint32_t mword = 0u;
                 bool masked = false;
-                for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {
-                    const int p = bitbase + k0;
-                    const uint32_t lo = side[p >> 5], hi = side[(p >> 5) + 1];
-                    uint32_t win = __funnelshift_r(lo, hi, (uint32_t)p & 31u);
-                    const int nv = k_hi - k0 + 1;
-                    if (nv < 32) win &= (1u << nv) - 1u;
-                    if (win == 0u) continue;
-                    masked = true;
-                    if (C == 1) {   // row k is element k: the window IS the mask word
-                        if (lane == ((k0 - k_lo) >> 5)) mword = win;
-                    } else {
+                if (C == 1) {
+                    // a row is one element: lane L's mask word is 32 consecutive bits of the bitmap
+                    const int k0 = k_lo + 32 * lane;
+                    if (lane < SL / 32 && k0 <= k_hi) {
+                        const int p = bitbase + k0;
+                        mword = __funnelshift_r(side[p >> 5], side[(p >> 5) + 1], (uint32_t)p & 31u);
+                        const int nv = k_hi - k0 + 1;
+                        if (nv < 32) mword &= (1u << nv) - 1u;
+                    }
+                    masked = __any_sync(0xffffffffu, mword != 0u);
+                } else {
+                    for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {   // warp-uniform window reads
+                        const int p = bitbase + k0;
+                        const uint32_t lo = side[p >> 5], hi = side[(p >> 5) + 1];
+                        uint32_t win = __funnelshift_r(lo, hi, (uint32_t)p & 31u);
+                        const int nv = k_hi - k0 + 1;
+                        if (nv < 32) win &= (1u << nv) - 1u;
+                        if (win == 0u) continue;
+                        masked = true;
                         while (win) {
                             const int kk = k0 + __ffs(win) - 1;
                             win &= win - 1u;
@@ -542,7 +552,55 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
     for (int b = warp; b < P.B; b += CW) {
         float v = (lane < CW) ? __ldcg(partials + (size_t)b * pstride + (size_t)blockIdx.x * CW + lane) : 0.0f;
         v = k7_warp_sum(v);
-        if (lane == 0) cta_partials[(size_t)b * gridDim.x + blockIdx.x] = v;
+        if (lane == 0) cta_partials[(size_t)b * G.cta_stride + G.cta_off + blockIdx.x] = v;
+    }
+}
+
+// ------------------------------------------------------------------ head outputs per level
+// levels[l] = [B, K*C, S_l] (NCHW, S_l = fh*fw cells, channel = in-cell anchor k * C + class c): the
+// element of anchor a = offset[l] + s*K + k and class c sits at ((b*K*C + k*C + c) * S_l + s).
+// Seen as a flat stream every element is its own "row", so the stream kernel runs on a level in
+// its C == 1 mode with ONE IGNORE BIT PER ELEMENT, laid out like the tensor: bit (b, ch, s) = the
+// anchor's bit.  k7_bits_expand_kernel writes those words (1/32 of the tensor's bytes) from the
+// anchor-ordered bitmap of k7_match.
+struct K7LevelTable {
+    const float* cls[K7_MAX_LEVELS];
+    float* dcls[K7_MAX_LEVELS];
+    int S[K7_MAX_LEVELS];
+};
+
+// One thread per 32-cell word of an (image, in-cell anchor) plane; the word is the same for all C
+// classes of that anchor.  S % 32 == 0: whole words, written C times.  Otherwise (small levels)
+// one thread per output word gathers its 32 elements individually.
+__global__ void __launch_bounds__(256)
+k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, int level_off, int K, int C, int S,
+                      uint32_t* __restrict__ lbits, int Wl) {
+    const int b = blockIdx.y;
+    const uint32_t* ab = abits + (size_t)b * W;
+    uint32_t* lb = lbits + (size_t)b * Wl;
+    if ((S & 31) == 0) {
+        const int spw = S >> 5;                       // words per plane
+        const int t = blockIdx.x * blockDim.x + threadIdx.x;
+        if (t >= K * spw) return;
+        const int k = t / spw, sw = t - k * spw;
+        uint32_t word = 0u;
+        int a = level_off + (sw << 5) * K + k;
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j, a += K) word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
+        for (int c = 0; c < C; ++c) lb[(size_t)(k * C + c) * spw + sw] = word;
+    } else {
+        const long long nel = (long long)K * C * S;
+        const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (w * 32 >= nel) return;
+        uint32_t word = 0u;
+        for (int j = 0; j < 32; ++j) {
+            const long long e = w * 32 + j;
+            if (e >= nel) break;
+            const int ch = (int)(e / S), s = (int)(e - (long long)ch * S);
+            const int a = level_off + s * K + ch / C;
+            word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
+        }
+        lb[w] = word;
     }
 }
 
@@ -589,9 +647,10 @@ __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* 
     }
 }
 
-template <bool GRAD, bool FROM_SPEC>
+template <bool GRAD, bool FROM_SPEC, bool LEVELS>
 __global__ void __launch_bounds__(K7_ROWS_THREADS)
-k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __restrict__ anchors, int box_order,
+k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7LevelTable LT,
+                    const float* __restrict__ anchors, int box_order,
                     const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
                     const int32_t* __restrict__ assign, const int32_t* __restrict__ num_pos,
                     const __grid_constant__ K7LossDev P, const float* __restrict__ pipe_partials, uint32_t pipe_slots,
@@ -659,15 +718,28 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __re
             rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
             const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
             if (label >= 0 && label < C) {
-                const size_t e = R * (size_t)C + (size_t)label;
-                const float zl = __ldg(cls + e);
+                size_t e = R * (size_t)C + (size_t)label;
+                const float* src = cls;
+                float* dst = dcls;
+                if (LEVELS) {   // NCHW per level: ((b*K*C + k*C + label) * S + cell)
+                    int l = 0;
+#pragma unroll
+                    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+                        if (i < spec.num_levels && a >= spec.offset[i]) l = i;
+                    const int r = a - spec.offset[l], K = spec.cell_anchors;
+                    const int cell = r / K, k = r - cell * K;
+                    e = ((size_t)b * K * C + (size_t)k * C + (size_t)label) * (size_t)LT.S[l] + (size_t)cell;
+                    src = LT.cls[l];
+                    dst = LT.dcls[l];
+                }
+                const float zl = __ldg(src + e);
                 const float xl = P.from_logits ? k7_sigmoid_precise(zl) : zl;
                 const float p = k7_clamp_p(xl);
                 cfix += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
                 if (GRAD) {
                     float g = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
                     if (P.from_logits) g *= xl * (1.0f - xl);   // d/dz through the fused sigmoid
-                    dcls[e] = g;
+                    dst[e] = g;
                 }
             }
         }
@@ -776,30 +848,78 @@ static int k7_rows_gx(int B, int A) {
     return gx < 1 ? 1 : gx;
 }
 
-struct K7LossWs {
-    size_t counter, bits, pipe, cta, rows, total;
+// ------------------------------------------------------------------ workspace + launch plan
+// One plan serves both entry points: k7_loss streams ONE tensor [B,A,C]; k7_loss_levels streams
+// one NCHW tensor per pyramid level in the stream kernel's C == 1 mode (see K7LevelTable).
+struct K7LossPlan {
+    int nstreams;
+    K7PipeGeom G[K7_MAX_LEVELS];
+    int level[K7_MAX_LEVELS];               // pyramid level of each stream (levels mode)
+    size_t off_lbits[K7_MAX_LEVELS];        // expanded ignore bits of the level
+    size_t off_pipe[K7_MAX_LEVELS];         // per-warp slots of the stream
+    size_t off_counter, off_bits, off_cta, off_rows, total;
+    uint32_t cta_stride;
+    int gx;
 };
 
-static K7LossWs k7_loss_ws_layout(int B, int A, size_t pipe_slots, size_t rows_slots) {
-    K7LossWs w;
+static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g);
+
+// levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
+static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
+                        K7LossPlan* p) {
+    p->nstreams = 0;
     size_t o = 0;
-    w.counter = o;   // [B] per-image block counters + 1 batch counter
+    p->off_counter = o;   // [B] per-image block counters + 1 batch counter
     o += k7_align_up(sizeof(unsigned int) * ((size_t)B + 1), 256);
-    w.bits = o;
+    p->off_bits = o;      // anchor-ordered ignore bits when the caller did not keep k7_match's
     o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(A), 256);
-    w.pipe = o;
-    o += k7_align_up(sizeof(float) * (size_t)B * pipe_slots, 256);
-    w.cta = o;       // [B][grid] stream-kernel partials, one per (image, CTA)
-    o += k7_align_up(sizeof(float) * (size_t)B * K7_LOSS_MAX_GRID, 256);
-    w.rows = o;
-    o += k7_align_up(sizeof(float2) * (size_t)B * rows_slots, 256);
-    w.total = o;
-    return w;
+    uint32_t cta = 0;
+    const int nl = levels ? spec->num_levels : 1;
+    for (int l = 0; l < nl; ++l) {
+        long long a_l = A;
+        int c_l = C;
+        if (levels) {
+            a_l = (long long)spec->cell_anchors * C * spec->fh[l] * spec->fw[l];   // elements per image, each its own row
+            c_l = 1;
+            if (a_l == 0) continue;
+            K7_REQUIRE(a_l < (1ll << 31), "k7_loss_levels: level %d has %lld elements per image", l, a_l);
+        }
+        const int i = p->nstreams++;
+        int rc = k7_pipe_geometry(B, (int)a_l, c_l, grad, &p->G[i]);
+        if (rc) return rc;
+        p->level[i] = l;
+        p->G[i].cta_off = cta;
+        // the workspace query has no device: assume the largest grid
+        cta += exact_grid ? (uint32_t)p->G[i].grid : (uint32_t)K7_LOSS_MAX_GRID;
+        p->off_lbits[i] = o;
+        if (levels) o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(a_l), 256);
+        p->off_pipe[i] = o;
+        o += k7_align_up(sizeof(float) * (size_t)B * (exact_grid ? (size_t)p->G[i].grid : (size_t)K7_LOSS_MAX_GRID) *
+                             K7_PIPE_MAX_CW, 256);
+    }
+    p->cta_stride = cta;
+    for (int i = 0; i < p->nstreams; ++i) p->G[i].cta_stride = cta;
+    p->off_cta = o;       // [B][cta_stride] stream partials, one per (image, CTA)
+    o += k7_align_up(sizeof(float) * (size_t)B * (cta > 0 ? cta : 1), 256);
+    p->gx = k7_rows_gx(B, A);
+    p->off_rows = o;
+    o += k7_align_up(sizeof(float2) * (size_t)B * p->gx, 256);
+    p->total = o;
+    return K7_OK;
 }
 
 extern "C" size_t k7_loss_workspace_bytes(int B, int A, int C) {
     if (B <= 0 || A <= 0 || C <= 0) return 0;
-    return k7_loss_ws_layout(B, A, (size_t)K7_LOSS_MAX_GRID * K7_PIPE_MAX_CW, (size_t)k7_rows_gx(B, A)).total;
+    K7LossPlan p;
+    if (k7_loss_plan(nullptr, false, B, A, C, true, false, &p)) return 0;
+    return p.total;
+}
+
+extern "C" size_t k7_loss_levels_workspace_bytes(const K7AnchorSpec* spec, int B, int C) {
+    if (!spec || B <= 0 || C <= 0 || k7_check_spec(spec, spec->total)) return 0;
+    K7LossPlan p;
+    if (k7_loss_plan(spec, true, B, spec->total, C, true, false, &p)) return 0;
+    return p.total;
 }
 
 static int k7_env_int(const char* name, int dflt) {
@@ -856,50 +976,34 @@ static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
     return K7_OK;
 }
 
-extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
-                       const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
-                       const int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
-                       float* sums, float* dcls, float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
-    K7_REQUIRE(cls && reg && annotations && assign && num_pos && params && per_image && sums && workspace,
-               "k7_loss: null argument");
-    K7_REQUIRE(spec || anchors, "k7_loss: need an anchor spec or an anchor tensor");
-    K7_REQUIRE((dcls == nullptr) == (dreg == nullptr), "k7_loss: dcls and dreg must be given together");
+static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls,
+                       const float* const* levels, const float* reg, const float* annotations, const int32_t* assign,
+                       const uint32_t* ignore_bits, const int32_t* num_pos, int B, int A, int C, int M,
+                       const K7LossParams* params, float* per_image, float* sums, float* dcls, float* const* dlevels,
+                       float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
+    const bool lv = levels != nullptr;
+    const bool grad = dreg != nullptr;
+    K7_REQUIRE(reg && annotations && assign && num_pos && params && per_image && sums && workspace, "k7_loss: null argument");
     K7_REQUIRE(B > 0 && A > 0 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d", B, A, C, M);
     K7_REQUIRE(B <= 65535, "k7_loss: B > 65535 not supported");
     K7_REQUIRE(params->mean_divisor > 0, "k7_loss: mean_divisor must be positive");
-    K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(reg) & 15) == 0,
-               "k7_loss: cls and reg must be 16-byte aligned");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(reg) & 15) == 0 && (reinterpret_cast<uintptr_t>(dreg) & 15) == 0,
+               "k7_loss: reg and dreg must be 16-byte aligned");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(ignore_bits) & 15) == 0, "k7_loss: ignore_bits must be 16-byte aligned");
-    K7_REQUIRE(!dcls || ((reinterpret_cast<uintptr_t>(dcls) & 15) == 0 && (reinterpret_cast<uintptr_t>(dreg) & 15) == 0),
-               "k7_loss: dcls and dreg must be 16-byte aligned");
-    if (spec) {
-        int rc = k7_check_spec(spec, A);
-        if (rc) return rc;
-        box_order = spec->box_order;
-    } else {
-        K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_loss: anchors must be 16-byte aligned");
-        K7_REQUIRE(box_order == K7_BOX_XYXY || box_order == K7_BOX_YXYX, "k7_loss: bad box_order");
-    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const bool grad = dcls != nullptr;
 
-    K7PipeGeom G;
-    int rc = k7_pipe_geometry(B, A, C, grad, &G);
+    K7LossPlan L;
+    int rc = k7_loss_plan(spec, lv, B, A, C, grad, true, &L);
     if (rc) return rc;
-    const uint32_t pipe_slots = (uint32_t)G.grid * (uint32_t)G.cw;
-    const int gx = k7_rows_gx(B, A);
-
-    const K7LossWs L = k7_loss_ws_layout(B, A, pipe_slots, (size_t)gx);
     if (workspace_bytes < L.total) {
         k7_set_error("k7_loss: workspace %zu < %zu bytes", workspace_bytes, L.total);
         return K7_EWORKSPACE;
     }
     unsigned char* ws = static_cast<unsigned char*>(workspace);
     K7_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "k7_loss: workspace must be 256-byte aligned");
-    unsigned int* counters = reinterpret_cast<unsigned int*>(ws + L.counter);
-    float* pipe_partials = reinterpret_cast<float*>(ws + L.pipe);
-    float* cta_partials = reinterpret_cast<float*>(ws + L.cta);
-    float2* rows_partials = reinterpret_cast<float2*>(ws + L.rows);
+    unsigned int* counters = reinterpret_cast<unsigned int*>(ws + L.off_counter);
+    float* cta_partials = reinterpret_cast<float*>(ws + L.off_cta);
+    float2* rows_partials = reinterpret_cast<float2*>(ws + L.off_rows);
 
     K7LossDev P;
     P.alpha = params->alpha;
@@ -923,19 +1027,46 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     P.B = B; P.A = A; P.C = C; P.M = M;
 
     K7_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * ((size_t)B + 1), st));
+    const int W = (int)K7_IGNORE_WORDS(A);
     if (!ignore_bits) {   // the caller did not keep k7_match's bitmap: derive it from the assignment words
-        uint32_t* bits = reinterpret_cast<uint32_t*>(ws + L.bits);
+        uint32_t* bits = reinterpret_cast<uint32_t*>(ws + L.off_bits);
         dim3 grid((A + K7_ROWS_THREADS - 1) / K7_ROWS_THREADS, B);
-        k7_loss_bits_kernel<<<grid, K7_ROWS_THREADS, 0, st>>>(assign, A, (int)G.W, bits);
+        k7_loss_bits_kernel<<<grid, K7_ROWS_THREADS, 0, st>>>(assign, A, W, bits);
         K7_LAUNCH_CHECK();
         ignore_bits = bits;
     }
 
-    {
+    K7LevelTable LT;
+    memset(&LT, 0, sizeof(LT));
+    for (int i = 0; i < L.nstreams; ++i) {
+        const K7PipeGeom& G = L.G[i];
+        const float* src = cls;
+        float* dst = dcls;
+        const uint32_t* bits = ignore_bits;
+        K7LossDev Ps = P;
+        if (lv) {
+            const int l = L.level[i];
+            const int S = spec->fh[l] * spec->fw[l], K = spec->cell_anchors;
+            src = levels[l];
+            dst = grad ? dlevels[l] : nullptr;
+            K7_REQUIRE(src && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (!grad || (dst && (reinterpret_cast<uintptr_t>(dst) & 15) == 0)),
+                       "k7_loss_levels: level %d: null or unaligned tensor", l);
+            LT.cls[l] = src;
+            LT.dcls[l] = dst;
+            LT.S[l] = S;
+            uint32_t* lbits = reinterpret_cast<uint32_t*>(ws + L.off_lbits[i]);
+            const long long threads = (S & 31) == 0 ? (long long)K * (S >> 5) : ((long long)K * C * S + 31) / 32;
+            dim3 grid((unsigned)((threads + 255) / 256), B);
+            k7_bits_expand_kernel<<<grid, 256, 0, st>>>(ignore_bits, W, spec->offset[l], K, C, S, lbits, (int)G.W);
+            K7_LAUNCH_CHECK();
+            bits = lbits;
+            Ps.A = K * C * S;
+            Ps.C = 1;
+        }
+        float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe[i]);
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(cls, ignore_bits, num_pos, P, G, pipe_partials,
-                                                                  cta_partials, dcls);
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(src, bits, num_pos, Ps, G, pipe_partials, cta_partials, dst);
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
@@ -953,14 +1084,51 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     float4* dreg4 = reinterpret_cast<float4*>(dreg);
-    dim3 rgrid(gx, B);
-#define K7_ROWS_LAUNCH(GR, SP)                                                                                          \
-    k7_loss_rows_kernel<GR, SP><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, anchors, box_order, cls, reg, annotations, assign, \
-                                                                   num_pos, P, cta_partials, (uint32_t)G.grid, rows_partials, \
-                                                                   counters, per_image, sums, dcls, dreg4)
-    if (grad) { if (spec) K7_ROWS_LAUNCH(true, true); else K7_ROWS_LAUNCH(true, false); }
-    else      { if (spec) K7_ROWS_LAUNCH(false, true); else K7_ROWS_LAUNCH(false, false); }
+    dim3 rgrid(L.gx, B);
+#define K7_ROWS_LAUNCH(GR, SP, LV)                                                                                       \
+    k7_loss_rows_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
+                                                                       assign, num_pos, P, cta_partials, L.cta_stride,   \
+                                                                       rows_partials, counters, per_image, sums, dcls,   \
+                                                                       dreg4)
+    if (lv) { if (grad) K7_ROWS_LAUNCH(true, true, true); else K7_ROWS_LAUNCH(false, true, true); }
+    else if (grad) { if (spec) K7_ROWS_LAUNCH(true, true, false); else K7_ROWS_LAUNCH(true, false, false); }
+    else           { if (spec) K7_ROWS_LAUNCH(false, true, false); else K7_ROWS_LAUNCH(false, false, false); }
 #undef K7_ROWS_LAUNCH
     K7_LAUNCH_CHECK();
     return K7_OK;
+}
+
+extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
+                       const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                       const int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
+                       float* sums, float* dcls, float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
+    K7_REQUIRE(cls, "k7_loss: null argument");
+    K7_REQUIRE(spec || anchors, "k7_loss: need an anchor spec or an anchor tensor");
+    K7_REQUIRE((dcls == nullptr) == (dreg == nullptr), "k7_loss: dcls and dreg must be given together");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(cls) & 15) == 0 && (reinterpret_cast<uintptr_t>(dcls) & 15) == 0,
+               "k7_loss: cls and dcls must be 16-byte aligned");
+    if (spec) {
+        int rc = k7_check_spec(spec, A);
+        if (rc) return rc;
+        box_order = spec->box_order;
+    } else {
+        K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_loss: anchors must be 16-byte aligned");
+        K7_REQUIRE(box_order == K7_BOX_XYXY || box_order == K7_BOX_YXYX, "k7_loss: bad box_order");
+    }
+    return k7_loss_run(spec, anchors, box_order, cls, nullptr, reg, annotations, assign, ignore_bits, num_pos, B, A, C, M,
+                       params, per_image, sums, dcls, nullptr, dreg, workspace, workspace_bytes, stream);
+}
+
+extern "C" int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
+                              const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                              const int32_t* num_pos, int B, int C, int M, const K7LossParams* params, float* per_image,
+                              float* sums, float* const* dlevels, float* dreg, void* workspace, size_t workspace_bytes,
+                              void* stream) {
+    K7_REQUIRE(spec && levels, "k7_loss_levels: an anchor spec and the level tensors are required");
+    K7_REQUIRE((dlevels == nullptr) == (dreg == nullptr), "k7_loss_levels: dlevels and dreg must be given together");
+    int rc = k7_check_spec(spec, spec->total);
+    if (rc) return rc;
+    return k7_loss_run(spec, nullptr, spec->box_order, nullptr, levels, reg, annotations, assign, ignore_bits, num_pos, B,
+                       spec->total, C, M, params, per_image, sums, nullptr, dlevels, dreg, workspace, workspace_bytes,
+                       stream);
 }

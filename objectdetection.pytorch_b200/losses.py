@@ -173,6 +173,91 @@ class _FocalLossFn(torch.autograd.Function):
         return dcls, dreg, None, None, None
 
 
+def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets, mean_divisor,
+                      want_grad, dreg_zeroed: Optional[torch.Tensor] = None, ignore_bits: Optional[torch.Tensor] = None,
+                      from_logits: bool = False):
+    """loss_stage on the head's raw per-level NCHW outputs (k7_loss_levels).  Returns
+    (per_image[B,2], sums[4], dlevels|None (list, same layouts as `levels`), dreg|None)."""
+    B, Cn = L.check_levels(levels, spec)
+    M = ann.shape[1]
+    dev = reg.device
+    lib = L.lib()
+    ws = _WS.get("loss_levels", lib.k7_loss_levels_workspace_bytes(C.byref(spec), B, Cn), dev)
+    per_image = torch.empty((B, 2), dtype=torch.float32, device=dev)
+    sums = torch.empty(4, dtype=torch.float32, device=dev)
+    dlevels = [torch.empty_like(t) for t in levels] if want_grad else None
+    dreg = None
+    if want_grad:
+        dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
+    p = L.K7LossParams()
+    p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
+    p.alpha, p.beta = alpha, beta
+    for i in range(4):
+        p.target_div[i] = target_div[i]
+    p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
+    p.from_logits = int(from_logits)
+    lv, dlv = L.ptr_array(levels), L.ptr_array(dlevels)
+    with torch.cuda.device(dev):
+        L.check(lib.k7_loss_levels(C.byref(spec), lv, L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits),
+                                   L.ptr(num_pos), B, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), dlv, L.ptr(dreg),
+                                   L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_loss_levels")
+    return per_image, sums, dlevels, dreg
+
+
+class _FocalLossLevelsFn(torch.autograd.Function):
+    """FocalLoss on per-level NCHW head outputs; inputs (reg, spec, ann, cfg, *levels)."""
+
+    @staticmethod
+    def forward(ctx, reg, spec, ann, cfg, *levels):
+        want_grad = reg.requires_grad or any(t.requires_grad for t in levels)
+        A = spec.total
+        dreg0 = torch.empty_like(reg) if want_grad else None
+        assign, num_pos, bits = match(spec, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"],
+                                      zero_fill=dreg0, with_bits=True)
+        group = cfg.get("process_group")
+        world = 1
+        if group is not None or cfg.get("sharded"):
+            import torch.distributed as dist
+            world = dist.get_world_size(group)
+        B = reg.shape[0]
+        per_image, sums, dlevels, dreg = loss_stage_levels(
+            spec, list(levels), reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
+            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world, want_grad=want_grad,
+            dreg_zeroed=dreg0, ignore_bits=bits, from_logits=cfg.get("from_logits", False))
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+        out = sums[:2] / sums[3]
+        if want_grad:
+            ctx.save_for_backward(dreg, *dlevels)
+        ctx.has_grad = want_grad
+        ctx.n_levels = len(levels)
+        ctx.mark_non_differentiable(num_pos, per_image)
+        return out[0:1], out[1:2], num_pos, per_image
+
+    @staticmethod
+    def backward(ctx, g_cls, g_reg, *_):
+        if not ctx.has_grad:
+            return (None,) * (4 + ctx.n_levels)
+        dreg, *dlevels = ctx.saved_tensors
+        lib = L.lib()
+        dev = dreg.device
+        with torch.cuda.device(dev):
+            st = L.stream_ptr(dev)
+            if g_cls is not None:
+                gc = g_cls.reshape(-1).float().contiguous()
+                for t in dlevels:
+                    L.check(lib.k7_scale_inplace(L.ptr(t), t.numel(), L.ptr(gc), st), "k7_scale_inplace")
+            else:
+                dlevels = [None] * len(dlevels)
+            if g_reg is not None:
+                gr = g_reg.reshape(-1).float().contiguous()
+                L.check(lib.k7_scale_inplace(L.ptr(dreg), dreg.numel(), L.ptr(gr), st), "k7_scale_inplace")
+            else:
+                dreg = None
+        return (dreg, None, None, None, *dlevels)
+
+
 class FocalLoss(nn.Module):
     """Same call signature as the reference.  Constructor keywords expose the constants the
     reference hard-codes; defaults are architectures/losses.py's (0.35/0.45, alpha .25,
@@ -205,6 +290,8 @@ class FocalLoss(nn.Module):
         return cls(neg_thr=0.4, pos_thr=0.5, target_std=None, box_order="yxyx", yx_targets=True, **kw)
 
     def forward(self, classifications, regressions, anchors, annotations, **kwargs):
+        if isinstance(classifications, (list, tuple)):
+            return self._forward_levels(list(classifications), regressions, anchors, annotations)
         L.require_cuda(classifications, regressions, annotations)
         if classifications.dim() != 3 or regressions.dim() != 3 or regressions.shape[2] != 4:
             raise ValueError("classifications must be [B,A,C] and regressions [B,A,4]")
@@ -222,6 +309,23 @@ class FocalLoss(nn.Module):
         # pass the recipe itself when there is one (a plain ctypes struct, not a tensor)
         anchor_src = sp if sp is not None else anchors
         lc, lr, num_pos, per_image, _ = _FocalLossFn.apply(cls, reg, anchor_src, ann, self.cfg)
+        self.last_num_positives = num_pos
+        self.last_per_image = per_image
+        return lc, lr
+
+    def _forward_levels(self, levels, regressions, anchors, annotations):
+        """`classifications` given as the head's raw per-level outputs [B, anchors*classes, H_l, W_l]
+        (what the last convolution writes, before permute/view/cat - SURVEY 8f row 1)."""
+        L.require_cuda(regressions, annotations)
+        sp = spec_of(anchors)
+        B, _ = L.check_levels(levels, sp)
+        if regressions.dim() != 3 or regressions.shape[0] != B or regressions.shape[1] != sp.total or regressions.shape[2] != 4:
+            raise ValueError("regressions must be [B,A,4] with A matching the anchor recipe")
+        if annotations.dim() != 3 or annotations.shape[2] != 5:
+            raise ValueError("annotations must be [B,M,5]")
+        reg = L.as_f32_contig(regressions)
+        ann = L.as_f32_contig(annotations)
+        lc, lr, num_pos, per_image = _FocalLossLevelsFn.apply(reg, sp, ann, self.cfg, *levels)
         self.last_num_positives = num_pos
         self.last_per_image = per_image
         return lc, lr

@@ -130,20 +130,31 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
            cap: Optional[int] = None, sync: bool = True, from_logits: bool = False) -> BatchDetections:
     """Fused decode + clip + threshold + sort + NMS for every image of the batch.
     from_logits: `classifications` are pre-sigmoid logits; scores are torch.sigmoid of the row maxima
-    and threshold / label ties are decided on those float32 probabilities, as the reference would."""
-    L.require_cuda(classifications, regressions)
-    cls = L.as_f32_contig(classifications)
+    and threshold / label ties are decided on those float32 probabilities, as the reference would.
+    `classifications` may also be the LIST of the head's raw per-level NCHW outputs
+    [B, anchors*classes, H_l, W_l] (then `anchors` must come from b200det.Anchors)."""
+    levels = list(classifications) if isinstance(classifications, (list, tuple)) else None
+    L.require_cuda(regressions)
     reg = L.as_f32_contig(regressions)
-    B, A, Cn = cls.shape
-    dev = cls.device
     spec = spec_of(anchors)
     anc_t = None
     order = L.BOX_YXYX if variant == L.DECODE_EFFDET else L.BOX_XYXY
-    if spec is None:
-        L.require_cuda(anchors)
-        anc_t = L.as_f32_contig(anchors.reshape(-1, 4))
-        if anc_t.shape[0] != A:
-            raise ValueError("anchor count mismatch")
+    if levels is not None:
+        # the head's raw per-level outputs [B, anchors*classes, H_l, W_l] (SURVEY 8f row 1)
+        B, Cn = L.check_levels(levels, spec)
+        A = spec.total
+        dev = reg.device
+        cls = None
+    else:
+        L.require_cuda(classifications)
+        cls = L.as_f32_contig(classifications)
+        B, A, Cn = cls.shape
+        dev = cls.device
+        if spec is None:
+            L.require_cuda(anchors)
+            anc_t = L.as_f32_contig(anchors.reshape(-1, 4))
+            if anc_t.shape[0] != A:
+                raise ValueError("anchor count mismatch")
     lib = L.lib()
     ws_bytes = lib.k7_detect_workspace_bytes(B, A, Cn)
     ws = _WS.get("detect", ws_bytes, dev)
@@ -168,9 +179,13 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
         return scores, labels, boxes, aids, ranks
 
     with torch.cuda.device(dev):
-        L.check(lib.k7_detect(C.byref(spec) if spec is not None else None, L.ptr(anc_t), order, L.ptr(cls),
-                              L.ptr(reg), B, A, Cn, C.byref(p), L.ptr(counts), L.ptr(ws), ws.numel(),
-                              L.stream_ptr(dev)), "k7_detect")
+        if levels is not None:
+            L.check(lib.k7_detect_levels(C.byref(spec), L.ptr_array(levels), L.ptr(reg), B, Cn, C.byref(p), L.ptr(counts),
+                                         L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_detect_levels")
+        else:
+            L.check(lib.k7_detect(C.byref(spec) if spec is not None else None, L.ptr(anc_t), order, L.ptr(cls),
+                                  L.ptr(reg), B, A, Cn, C.byref(p), L.ptr(counts), L.ptr(ws), ws.numel(),
+                                  L.stream_ptr(dev)), "k7_detect")
         out = gather(cap)
         if not sync:
             return BatchDetections(counts[:, 1], counts[:, 0], *out)

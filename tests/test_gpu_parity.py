@@ -545,3 +545,116 @@ def test_strip_head_sigmoid_and_head_fixture():
             self.output_act = torch.nn.Sigmoid()
     m = torch.nn.Sequential(Head())
     assert b200det.strip_head_sigmoid(m) and isinstance(m[0].output_act, torch.nn.Identity)
+
+
+# ---------------------------------------------------------------------------------- per-level NCHW head outputs
+def _make_levels(spec, B, C, gen, mean=-3.0, std=2.0):
+    K = spec.cell_anchors
+    return [(torch.randn((B, K * C, spec.fh[l], spec.fw[l]), generator=gen) * std + mean).contiguous()
+            for l in range(spec.num_levels)]
+
+
+@pytest.mark.parametrize("from_logits", [True, False], ids=["logits", "probs"])
+@pytest.mark.parametrize("shape", [(2, 5, 96, 128), (3, 90, 64, 64), (2, 1, 80, 112), (1, 7, 50, 34)],
+                         ids=lambda s: "B%d_C%d_%dx%d" % s)
+def test_focal_loss_on_head_levels(shape, from_logits):
+    """FocalLoss fed with the head's raw per-level NCHW tensors (no permute / view / cat, and with
+    from_logits no sigmoid either) against (a) the oracle on the reference's own layout + activation
+    (oracle head restatement, pinned in test_oracle_golden) and (b) the [B,A,C] path of this library,
+    gradients compared level by level in NCHW."""
+    B, C, H, W = shape
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    spec = b200det.spec_of(anc)
+    K, A = spec.cell_anchors, spec.total
+    gen = torch.Generator().manual_seed(B * 1000 + C * 7 + H)
+    levels = _make_levels(spec, B, C, gen)
+    if not from_logits:
+        levels = [torch.sigmoid(t) for t in levels]
+    ann = b200det.synth.make_annotations(B, 6, C, H, W, gen, gt_min=8.0, gt_max=60.0)
+    reg = torch.randn((B, A, 4), generator=gen) * 0.5
+    anc_cpu = torch.from_numpy(R.retina_anchors(H, W))[None]
+
+    # (a) oracle: layout (+ activation) as the reference head does it, then the reference loss
+    lv0 = [t.clone().requires_grad_(True) for t in levels]
+    r0 = reg.clone().requires_grad_(True)
+    flat = R.head_logits(lv0, K, C)
+    want = R.focal_loss(torch.sigmoid(flat) if from_logits else flat, r0, anc_cpu, ann)
+    (want.cls_mean + want.reg_mean).sum().backward()
+
+    lv1 = [t.to(DEV).requires_grad_(True) for t in levels]
+    r1 = reg.to(DEV).requires_grad_(True)
+    mod = b200det.FocalLoss(from_logits=from_logits)
+    lc, lr = mod(lv1, r1, anc, ann.to(DEV))
+    (lc + lr).sum().backward()
+    np.testing.assert_allclose(lc.item(), want.cls_mean.item(), rtol=1e-5)
+    np.testing.assert_allclose(lr.item(), want.reg_mean.item(), rtol=1e-5)
+    assert mod.last_num_positives.cpu().tolist() == want.num_pos
+    for l in range(spec.num_levels):
+        assert lv1[l].grad.shape == levels[l].shape
+        np.testing.assert_allclose(lv1[l].grad.cpu().numpy(), lv0[l].grad.numpy(), rtol=2e-5, atol=1e-10)
+    want_dreg = r0.grad.numpy() if r0.grad is not None else np.zeros_like(reg.numpy())
+    np.testing.assert_allclose(r1.grad.cpu().numpy(), want_dreg, rtol=1e-5, atol=1e-9)
+
+    # (b) the [B,A,C] path on the tensor torch's permute/view/cat would have produced
+    with torch.no_grad():
+        flat_gpu = R.head_logits([t.to(DEV) for t in levels], K, C)
+        lc2, lr2 = b200det.FocalLoss(from_logits=from_logits)(flat_gpu, reg.to(DEV), anc, ann.to(DEV))
+        lc3, lr3 = mod([t.detach() for t in lv1], reg.to(DEV), anc, ann.to(DEV))
+    np.testing.assert_allclose(lc3.item(), lc2.item(), rtol=2e-6)
+    np.testing.assert_allclose(lr3.item(), lr2.item(), rtol=1e-6)
+
+
+@pytest.mark.parametrize("from_logits", [True, False], ids=["logits", "probs"])
+def test_detect_on_head_levels(from_logits):
+    """detect() on the per-level NCHW tensors == detect() on the [B,A,C] tensor: identical survivors,
+    scores, labels, boxes and keep order (bit for bit), including first-index ties between classes."""
+    B, C, H, W = 3, 11, 160, 224
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    spec = b200det.spec_of(anc)
+    K, A = spec.cell_anchors, spec.total
+    gen = torch.Generator().manual_seed(77)
+    levels = _make_levels(spec, B, C, gen, mean=-4.0, std=1.5)
+    levels[0][1, 3 * C + 2, 5, 7] = levels[0][1, 3 * C + 6, 5, 7] = 3.0      # two classes tie: the first wins
+    levels[1][0, 0 * C + 9, 1, 1], levels[1][0, 0 * C + 4, 1, 1] = 30.0, 20.0  # saturated logits tie at 1.0
+    if not from_logits:
+        levels = [torch.sigmoid(t) for t in levels]
+    reg = (torch.randn((B, A, 4), generator=gen) * 0.5).to(DEV)
+    lv = [t.to(DEV) for t in levels]
+    flat = R.head_logits(lv, K, C)
+    a = b200det.detect(lv, reg, anc, (H, W), from_logits=from_logits)
+    w = b200det.detect(flat, reg, anc, (H, W), from_logits=from_logits)
+    assert a.survivors.tolist() == w.survivors.tolist() and a.count.tolist() == w.count.tolist()
+    assert all(0 < int(x) < A for x in w.survivors)
+    for b in range(B):
+        k = int(w.count[b])
+        assert torch.equal(a.anchor_ids[b, :k], w.anchor_ids[b, :k])
+        assert torch.equal(a.scores[b, :k], w.scores[b, :k])
+        assert torch.equal(a.labels[b, :k], w.labels[b, :k])
+        assert torch.equal(a.boxes[b, :k], w.boxes[b, :k])
+        assert torch.equal(a.survivor_rank[b, :k], w.survivor_rank[b, :k])
+    probs = torch.sigmoid(flat) if from_logits else flat
+    _, dets = R.detect_batch(probs.cpu(), reg.cpu(), anc.cpu(), H, W)
+    for b, d in enumerate(dets):
+        k = int(a.count[b])
+        assert np.array_equal(a.anchor_ids[b, :k].cpu().numpy(), d.keep_anchor.numpy())
+        assert np.array_equal(a.labels[b, :k].cpu().numpy(), d.labels.numpy())
+
+
+def test_head_levels_reject_bad_shapes():
+    img = torch.empty(2, 3, 64, 64, device=DEV)
+    anc = b200det.Anchors()(img)
+    spec = b200det.spec_of(anc)
+    gen = torch.Generator().manual_seed(0)
+    lv = [t.to(DEV) for t in _make_levels(spec, 2, 4, gen)]
+    reg = torch.zeros((2, spec.total, 4), device=DEV)
+    ann = -torch.ones((2, 1, 5), device=DEV)
+    with pytest.raises(ValueError):
+        b200det.FocalLoss()(lv[:-1], reg, anc, ann)                       # a level is missing
+    with pytest.raises(ValueError):
+        b200det.FocalLoss()(lv, reg, anc.clone(), ann)                    # a plain tensor carries no level geometry
+    bad = list(lv)
+    bad[0] = bad[0][:, :, :-1].contiguous()
+    with pytest.raises(ValueError):
+        b200det.detect(bad, reg, anc, (64, 64))
