@@ -468,58 +468,28 @@ static int k7_score_geometry(int B, int A, int C, K7ScoreGeom* g) {
 // levels[l] = [B, K*C, S_l] (layout in k7_loss.cu): the C scores of anchor (s, k) are
 // S_l floats apart, so one THREAD owns an anchor and walks its classes; consecutive threads own
 // consecutive cells of one in-cell anchor plane, i.e. every load instruction of a warp reads 128
-// contiguous bytes.  Running maximum and FIRST arg-max (strict '>'), then exactly the survivor
-// record of k7_score_pipe_kernel's drain.  Plain loads, eight in flight per thread: the kernel is a
-// pure stream.
+// contiguous bytes (512 with the vector walk).  Running maximum and FIRST arg-max (strict '>'), then
+// exactly the survivor record of k7_score_pipe_kernel's drain.  Plain loads, eight in flight per
+// thread: the kernel is a pure stream.
 struct K7ScoreLevels {
     const float* cls[K7_MAX_LEVELS];
     int S[K7_MAX_LEVELS];
-    int blk_off[K7_MAX_LEVELS + 1];   // first block (of 256 anchors) of each level; [num_levels] = grid.x
+    int blk_off[K7_MAX_LEVELS + 1];    // levels with S % 4 == 0: first 256-thread tile (4 cells a thread) of each level
+                                       // within an image; [K7_MAX_LEVELS] = tiles per image
+    int sblk_off[K7_MAX_LEVELS + 1];   // the other levels: first block (a cell a thread); [K7_MAX_LEVELS] = grid.x
 };
 
+// survivor record of one anchor (shared by the vector and the scalar walk)
 template <bool LOGITS>
-__global__ void __launch_bounds__(256)
-k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV,
-                       const float4* __restrict__ reg, int A, int C, float report_thr,
-                       const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
-                       float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
-    const int b = blockIdx.y;
-    int l = 0;
-#pragma unroll
-    for (int i = 1; i < K7_MAX_LEVELS; ++i)
-        if (i < spec.num_levels && (int)blockIdx.x >= LV.blk_off[i]) l = i;
-    const int K = spec.cell_anchors, S = LV.S[l];
-    const int t = ((int)blockIdx.x - LV.blk_off[l]) * 256 + (int)threadIdx.x;
-    if (t >= K * S) return;
-    const int k = t / S, s = t - k * S;
-    const float* base = LV.cls[l] + ((size_t)b * K * C + (size_t)k * C) * (size_t)S + (size_t)s;
-    float m = -INFINITY;
-    int idx = 0;
-    int c = 0;
-    for (; c + 8 <= C; c += 8) {
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __ldg(base + (size_t)(c + j) * S);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-            if (v[j] > m) {
-                m = v[j];
-                idx = c + j;
-            }
-    }
-    for (; c < C; ++c) {
-        const float v = __ldg(base + (size_t)c * S);
-        if (v > m) {
-            m = v;
-            idx = c;
-        }
-    }
-    if (!(m > report_thr)) return;
+__device__ __forceinline__ void k7_levels_emit(const K7AnchorSpec& spec, const K7DetectParams& P, const float* base, int S,
+                                               float m, int idx, bool tie, int b, int a, int A, const float4* __restrict__ reg,
+                                               uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws,
+                                               int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
     if (LOGITS) {
         const float p = k7_sigmoid_precise(m);
         if (!(p > P.score_thr)) return;
         const float lo = fminf(m - 2e-3f, 8.0f);   // see k7_score_pipe_kernel: plateau of the float32 sigmoid
-        for (int q = 0; q < idx; ++q) {
+        for (int q = 0; tie && q < idx; ++q) {   // tie: an earlier class reached lo (tracked by the walk)
             const float v = __ldg(base + (size_t)q * S);
             if (v >= lo && k7_sigmoid_precise(v) == p) {
                 idx = q;
@@ -528,7 +498,6 @@ k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_c
         }
         m = p;
     }
-    const int a = spec.offset[l] + s * K + k;
     float ax1, ay1, ax2, ay2;
     k7_anchor_from_spec(spec, a, ax1, ay1, ax2, ay2);
     const size_t oa = (size_t)b * A + a;
@@ -541,6 +510,182 @@ k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_c
     label_ws[oa] = idx;
     score_ws[oa] = m;
     atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
+}
+
+// The per-level walk.  A thread owns FOUR consecutive cells of one in-cell anchor plane (levels with
+// S % 4 == 0; the others - odd little maps such as 7x7 - go through k7_score_levels_scalar_kernel)
+// and walks the C class planes at stride S.  The kernel is persistent (2 CTAs per SM): CTA i takes the
+// 256-thread tiles i, i + grid, ...; every thread copies its own 16 bytes per class into a shared-
+// memory ring with cp.async and reads them back itself (no block barrier on the data), and the ring
+// runs on across tile boundaries, so (G-1)*U 16-byte loads per thread stay in flight for the whole
+// kernel.  (With register loads ptxas kept two in flight; with one short-lived block per tile the
+// achieved occupancy was a third of the theoretical one.)
+// Rows above the threshold are queued in shared memory and served by dense warps when the queue
+// fills: anchor in float64, decode with two expf, the exact sigmoid ... ~800 instructions that would
+// otherwise run with one or two active lanes in nearly every warp.
+#define K7_LV_G 3
+#define K7_LV_U 6
+#define K7_LV_QCAP 2048
+#define K7_LV_SMEM (K7_LV_G * K7_LV_U * 256 * 16)
+
+// queue entry {k | s << 4, score bits, label | tie << 31, b | l << 24}
+template <bool LOGITS>
+__device__ __forceinline__ void k7_levels_flush(const K7AnchorSpec& spec, const K7ScoreLevels& LV, const K7DetectParams& P,
+                                                const int4* s_q, int qn, int A, int C, const float4* __restrict__ reg,
+                                                uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws,
+                                                int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+    const int K = spec.cell_anchors;
+    for (int i = threadIdx.x; i < qn; i += 256) {   // records are keyed by anchor id: the queue order does not matter
+        const int4 ent = s_q[i];
+        const int k = ent.x & 15, s = ent.x >> 4, b = ent.w & 0xffffff, l = ent.w >> 24;
+        const int S = LV.S[l];
+        const float* base = LV.cls[l] + ((size_t)b * K + k) * (size_t)C * (size_t)S + (size_t)s;
+        k7_levels_emit<LOGITS>(spec, P, base, S, __int_as_float(ent.y), ent.z & 0x7fffffff, ent.z < 0, b,
+                               spec.offset[l] + s * K + k, A, reg, bits, W32, box_ws, label_ws, score_ws);
+    }
+}
+
+template <bool LOGITS>
+__global__ void __launch_bounds__(256, 2)
+k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV, int num_tiles,
+                       const float4* __restrict__ reg, int A, int C, float report_thr,
+                       const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
+                       float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+    extern __shared__ float4 s_ring[];   // [K7_LV_G][K7_LV_U][256]
+    __shared__ int4 s_q[K7_LV_QCAP];
+    __shared__ int s_qn;
+    const int K = spec.cell_anchors;
+    const int tiles_per_image = LV.blk_off[K7_MAX_LEVELS];
+    const int NG = (C + K7_LV_U - 1) / K7_LV_U;   // class groups per tile
+    const int my_tiles = ((int)blockIdx.x < num_tiles) ? (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    if (threadIdx.x == 0) s_qn = 0;
+    __syncthreads();
+
+    // tile v -> this thread's column of planes: image, level, in-cell anchor, first cell
+    auto open_tile = [&](int v, int& b, int& l, int& k, int& s, int& S) -> const float* {
+        b = v / tiles_per_image;
+        const int x = v - b * tiles_per_image;
+        l = 0;
+#pragma unroll
+        for (int i = 1; i < K7_MAX_LEVELS; ++i)
+            if (x >= LV.blk_off[i]) l = i;
+        S = LV.S[l];
+        const int S4 = S >> 2;
+        const int t = (x - LV.blk_off[l]) * 256 + (int)threadIdx.x;
+        if (t >= K * S4) return nullptr;
+        k = t / S4;
+        s = (t - k * S4) << 2;
+        return LV.cls[l] + ((size_t)b * K + k) * (size_t)C * (size_t)S + (size_t)s;
+    };
+
+    const uint32_t slot0 = (uint32_t)__cvta_generic_to_shared(s_ring) + threadIdx.x * 16u;
+    // ---- issue cursor
+    int it = 0, ig = 0, islot = 0;   // tile ordinal of this CTA, class group, ring group
+    const float* ibase = nullptr;
+    int iS = 0;
+    auto issue = [&]() {
+        if (it < my_tiles) {
+            if (ig == 0) {
+                int b_, l_, k_, s_;
+                ibase = open_tile((int)blockIdx.x + it * (int)gridDim.x, b_, l_, k_, s_, iS);
+            }
+            if (ibase) {
+                const int c0 = ig * K7_LV_U;
+#pragma unroll
+                for (int j = 0; j < K7_LV_U; ++j)
+                    if (c0 + j < C)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(slot0 + (uint32_t)((islot * K7_LV_U + j) * 4096)),
+                                     "l"(ibase + (size_t)(c0 + j) * iS)
+                                     : "memory");
+            }
+            if (++ig == NG) {
+                ig = 0;
+                ++it;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");   // also when empty: the group count stays uniform
+        islot = (islot + 1 == K7_LV_G) ? 0 : islot + 1;
+    };
+#pragma unroll
+    for (int g = 0; g < K7_LV_G; ++g) issue();
+
+    // ---- consume cursor
+    int cslot = 0;
+    for (int ct = 0; ct < my_tiles; ++ct) {
+        int b, l, k = 0, s = 0, S;
+        const bool live = open_tile((int)blockIdx.x + ct * (int)gridDim.x, b, l, k, s, S) != nullptr;
+        float m[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float pm[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // largest value before the arg max
+        int idx[4] = {0, 0, 0, 0};
+        for (int c0 = 0; c0 < C; c0 += K7_LV_U) {
+            asm volatile("cp.async.wait_group %0;" ::"n"(K7_LV_G - 1) : "memory");
+            if (live) {
+#pragma unroll
+                for (int j = 0; j < K7_LV_U; ++j) {
+                    if (c0 + j < C) {
+                        const float4 v = s_ring[(cslot * K7_LV_U + j) * 256 + threadIdx.x];
+                        if (v.x > m[0]) { pm[0] = m[0]; m[0] = v.x; idx[0] = c0 + j; }
+                        if (v.y > m[1]) { pm[1] = m[1]; m[1] = v.y; idx[1] = c0 + j; }
+                        if (v.z > m[2]) { pm[2] = m[2]; m[2] = v.z; idx[2] = c0 + j; }
+                        if (v.w > m[3]) { pm[3] = m[3]; m[3] = v.w; idx[3] = c0 + j; }
+                    }
+                }
+            }
+            issue();   // refills the group just read
+            cslot = (cslot + 1 == K7_LV_G) ? 0 : cslot + 1;
+        }
+        if (live) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (m[e] > report_thr) {
+                    const int tie = (LOGITS && pm[e] >= fminf(m[e] - 2e-3f, 8.0f)) ? (int)0x80000000 : 0;
+                    s_q[atomicAdd(&s_qn, 1)] = make_int4(k | ((s + e) << 4), __float_as_int(m[e]), idx[e] | tie, b | (l << 24));
+                }
+        }
+        __syncthreads();
+        const int qn = s_qn;
+        if (qn > K7_LV_QCAP - 1024) {   // the next tile may add up to 1024
+            k7_levels_flush<LOGITS>(spec, LV, P, s_q, qn, A, C, reg, bits, W32, box_ws, label_ws, score_ws);
+            __syncthreads();
+            if (threadIdx.x == 0) s_qn = 0;
+            __syncthreads();
+        }
+    }
+    k7_levels_flush<LOGITS>(spec, LV, P, s_q, s_qn, A, C, reg, bits, W32, box_ws, label_ws, score_ws);
+}
+
+// Levels whose S is not a multiple of four: one thread per anchor, register loads.  These maps are
+// the small ones (7x7, 13x13 ...); grid (blocks, B).
+template <bool LOGITS>
+__global__ void __launch_bounds__(256)
+k7_score_levels_scalar_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV,
+                              const float4* __restrict__ reg, int A, int C, float report_thr,
+                              const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
+                              float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+    const int b = blockIdx.y;
+    int l = 0;
+#pragma unroll
+    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+        if ((int)blockIdx.x >= LV.sblk_off[i]) l = i;
+    const int K = spec.cell_anchors, S = LV.S[l];
+    const int t = ((int)blockIdx.x - LV.sblk_off[l]) * 256 + (int)threadIdx.x;
+    if (t >= K * S) return;
+    const int k = t / S, s = t - k * S;
+    const float* base = LV.cls[l] + ((size_t)b * K + k) * (size_t)C * (size_t)S + (size_t)s;
+    float m = -INFINITY, pm = -INFINITY;
+    int idx = 0;
+#pragma unroll 8
+    for (int c = 0; c < C; ++c) {
+        const float v = __ldg(base + (size_t)c * S);
+        if (v > m) {
+            pm = m;
+            m = v;
+            idx = c;
+        }
+    }
+    if (m > report_thr)
+        k7_levels_emit<LOGITS>(spec, P, base, S, m, idx, LOGITS && pm >= fminf(m - 2e-3f, 8.0f), b, spec.offset[l] + s * K + k, A,
+                               reg, bits, W32, box_ws, label_ws, score_ws);
 }
 
 // ------------------------------------------------------------------ kernel 2: per-image sort + NMS
@@ -1536,25 +1681,38 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
     if (levels) {
         K7ScoreLevels LV;
         memset(&LV, 0, sizeof(LV));
-        int blocks = 0;
+        int tiles = 0, sblocks = 0;
         for (int l = 0; l < spec->num_levels; ++l) {
             const int S = spec->fh[l] * spec->fw[l];
             K7_REQUIRE(S == 0 || (levels[l] && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0),
                        "k7_detect_levels: level %d: null or unaligned tensor", l);
+            K7_REQUIRE(S < (1 << 27) && spec->cell_anchors <= 16, "k7_detect_levels: level %d: map too large", l);
             LV.cls[l] = levels[l];
             LV.S[l] = S;
-            LV.blk_off[l] = blocks;
-            blocks += (spec->cell_anchors * S + 255) / 256;
+            LV.blk_off[l] = tiles;
+            LV.sblk_off[l] = sblocks;
+            if ((S & 3) == 0) tiles += (spec->cell_anchors * (S / 4) + 255) / 256;
+            else sblocks += (spec->cell_anchors * S + 255) / 256;
         }
-        for (int l = spec->num_levels; l <= K7_MAX_LEVELS; ++l) LV.blk_off[l] = blocks;
-        if (blocks > 0) {
-            dim3 grid(blocks, B);
-            if (params->from_logits)
-                k7_score_levels_kernel<true><<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr,
-                                                                   *params, w.bits, w.W32, w.box, w.label, w.score);
-            else
-                k7_score_levels_kernel<false><<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr,
-                                                                    *params, w.bits, w.W32, w.box, w.label, w.score);
+        for (int l = spec->num_levels; l <= K7_MAX_LEVELS; ++l) {
+            LV.blk_off[l] = tiles;
+            LV.sblk_off[l] = sblocks;
+        }
+        K7_REQUIRE((long long)tiles * B < (1ll << 31) && B < (1 << 24), "k7_detect_levels: batch too large");
+        if (tiles > 0) {
+            const int num_tiles = tiles * B;
+            const int grid = num_tiles < 2 * k7_sm_count() ? num_tiles : 2 * k7_sm_count();
+            auto kern = params->from_logits ? k7_score_levels_kernel<true> : k7_score_levels_kernel<false>;
+            K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_LV_SMEM));
+            kern<<<grid, 256, K7_LV_SMEM, st>>>(sp, LV, num_tiles, reinterpret_cast<const float4*>(reg), A, C, report_thr, *params,
+                                                w.bits, w.W32, w.box, w.label, w.score);
+            K7_LAUNCH_CHECK();
+        }
+        if (sblocks > 0) {
+            dim3 grid(sblocks, B);
+            auto kern = params->from_logits ? k7_score_levels_scalar_kernel<true> : k7_score_levels_scalar_kernel<false>;
+            kern<<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr, *params, w.bits, w.W32,
+                                       w.box, w.label, w.score);
             K7_LAUNCH_CHECK();
         }
     } else {

@@ -53,6 +53,26 @@ def main():
             "detect_logits": lambda: b200det.detect(z, reg, anc, (wl.height, wl.width), sync=False, from_logits=True),
             "torch_sigmoid": lambda: torch.sigmoid(z),
         })
+    if "levels" in args.stages:
+        # the head's raw per-level NCHW tensors holding the same logits
+        sp = b200det.spec_of(anc)
+        K, Cn = sp.cell_anchors, wl.classes
+        zz = torch.logit(cls)
+        lv = [zz[:, sp.offset[l]:sp.offset[l + 1], :].reshape(B, sp.fh[l], sp.fw[l], K * Cn).permute(0, 3, 1, 2).contiguous()
+              for l in range(sp.num_levels)]
+        del zz
+
+        def torch_layout():
+            return torch.cat([t.permute(0, 2, 3, 1).contiguous().view(B, -1, Cn) for t in lv], dim=1)
+
+        stages.update({
+            "loss_fwd_levels": lambda: BL.loss_stage_levels(sp, lv, reg, ann, assign, num_pos, want_grad=False,
+                                                            ignore_bits=bits, from_logits=True, **kw),
+            "loss_fwd_bwd_levels": lambda: BL.loss_stage_levels(sp, lv, reg, ann, assign, num_pos, want_grad=True,
+                                                                dreg_zeroed=dreg0, ignore_bits=bits, from_logits=True, **kw),
+            "detect_levels": lambda: b200det.detect(lv, reg, anc, (wl.height, wl.width), sync=False, from_logits=True),
+            "torch_layout": torch_layout,
+        })
     for name in args.stages.split(","):
         fn = stages[name]
         fn()
