@@ -266,16 +266,30 @@ __device__ __forceinline__ uint32_t k7_range_bits(int lo, int hi, int base) {
 // __syncthreads after the prologue.
 #define K7_PIPE_MAX_CW 16
 
-struct K7PipeGeom {
+// One contiguous stream of a launch: the [B,A,C] tensor, or one pyramid level in its C == 1 mode.
+struct K7PipeSeg {
+    const float* cls;
+    float* dcls;
+    const uint32_t* bits;
     unsigned long long N;    // B*A*C elements
     unsigned long long N4;   // N & ~3: the part moved by 16-byte bulk copies
     unsigned long long AC;   // elements per image
+    uint32_t A;              // rows per image
+    uint32_t W;              // ignore-bit words per image, K7_IGNORE_WORDS(A)
+    uint32_t tile0;          // first tile of the stream in the launch's tile order
+    uint32_t pad;
+};
+struct K7PipeSegs {
+    int n, pad;
+    K7PipeSeg s[K7_MAX_LEVELS];
+};
+
+struct K7PipeGeom {
     uint32_t tile_f;         // floats per tile = cw * slice
     uint32_t slice;          // floats per consumer warp and tile: 512 or 1024
-    uint32_t num_tiles;      // ceil(N4 / tile_f)
-    uint32_t W;              // ignore-bit words per image, K7_IGNORE_WORDS(A)
+    uint32_t num_tiles;      // sum over the streams of ceil(N4 / tile_f)
     K7FastDiv div_c;         // / C for tile-local indices
-    uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x] (several launches share one table)
+    uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x]
     uint32_t side_words;     // words reserved per ignore-bit part (two parts per stage)
     uint32_t stage_stride;
     uint32_t off_desc, off_mask, off_bars;
@@ -285,19 +299,19 @@ struct K7PipeGeom {
 
 struct K7TileDesc {   // written by the producer next to each stage, 48 bytes
     uint32_t n, rem, split, b0;     // floats in the tile | position of float 0 in its row | floats that belong to image b0 | image of float 0
-    uint32_t lead, kA, bit1, a0;    // bit of tile row 0 in part 0 | tile row where image b0+1 starts | bit of that row (part 1) | anchor of tile row 0
-    uint32_t off_lo, off_hi, pad0, pad1;   // flat index of float 0
+    uint32_t lead, kA, split2, a0;  // bit of tile row 0 in part 0 | tile row where image b0+1 starts | floats up to the end of image b0+1 | anchor of tile row 0
+    uint32_t off_lo, off_hi, seg, pad1;    // flat index of float 0 in its stream | the stream
 };
 
 template <bool GRAD, int SL, bool LOGITS>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
-k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ bits, const int32_t* __restrict__ num_pos,
+k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __restrict__ num_pos,
                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7PipeGeom G,
-                    float* __restrict__ partials, float* __restrict__ cta_partials, float* __restrict__ dcls) {
+                    float* __restrict__ partials, float* __restrict__ cta_partials) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
-    const int C = P.C, A = P.A;
+    const int C = P.C;
     K7TileDesc* desc = reinterpret_cast<K7TileDesc*>(smem + G.off_desc);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + G.off_bars);
     uint64_t* done = full + NS;
@@ -317,46 +331,70 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
     if (warp == CW) {
         // ================================================================ producer
         if (lane != 0) return;
-        auto load = [&](const uint32_t j) {
-            const unsigned long long g = (unsigned long long)blockIdx.x + (unsigned long long)j * gridDim.x;
-            const int s = (int)(j % (uint32_t)NS);
-            unsigned char* stage = smem + (size_t)s * G.stage_stride;
-            const unsigned long long off = g * G.tile_f;
-            const unsigned long long left = G.N4 - off;
+        // The descriptor of the NEXT tile is worked out (two 64-bit divisions, table look-ups) while the
+        // producer would otherwise wait for a stage: a tile lasts ~0.8 us, the arithmetic must stay off
+        // the path between "stage free" and "copy issued".
+        K7TileDesc nd;
+        const float* n_src = nullptr;
+        const uint32_t *n_bits0 = nullptr, *n_bits1 = nullptr;
+        uint32_t n_words0 = 0u, n_words1 = 0u;
+        auto prepare = [&](const uint32_t j) {
+            const uint32_t g = blockIdx.x + j * gridDim.x;
+            int sg = 0;
+            for (int i = 1; i < SG.n; ++i)
+                if (g >= SG.s[i].tile0) sg = i;
+            const K7PipeSeg& Q = SG.s[sg];
+            const uint32_t A = Q.A;
+            const unsigned long long off = (unsigned long long)(g - Q.tile0) * G.tile_f;
+            const unsigned long long left = Q.N4 - off;
             K7TileDesc d;
             d.n = left < G.tile_f ? (uint32_t)left : G.tile_f;
             const unsigned long long r0 = off / (uint32_t)C;   // first row (batch-global) touching the tile
             d.rem = (uint32_t)(off - r0 * (uint32_t)C);
-            d.b0 = (uint32_t)(r0 / (uint32_t)A);
-            d.a0 = (uint32_t)(r0 - (unsigned long long)d.b0 * (uint32_t)A);
-            const unsigned long long in_img = (unsigned long long)(d.b0 + 1u) * G.AC - off;
+            d.b0 = (uint32_t)(r0 / A);
+            d.a0 = (uint32_t)(r0 - (unsigned long long)d.b0 * A);
+            const unsigned long long in_img = (unsigned long long)(d.b0 + 1u) * Q.AC - off;
             d.split = in_img < d.n ? (uint32_t)in_img : d.n;
             const uint32_t nrows = k7_div(d.rem + d.n - 1u, G.div_c) + 1u;
-            d.kA = (uint32_t)A - d.a0;
+            d.kA = A - d.a0;
             const uint32_t w0 = (d.a0 >> 7) << 2;   // 16-byte aligned first word of part 0
             d.lead = d.a0 - (w0 << 5);
             const uint32_t rows0 = nrows < d.kA ? nrows : d.kA;
-            const uint32_t words0 = ((d.lead + rows0 + 127u) >> 7) << 2;
-            uint32_t words1 = 0u;
+            n_words0 = ((d.lead + rows0 + 127u) >> 7) << 2;
+            n_words1 = 0u;
             if (nrows > d.kA && d.b0 + 1u < (uint32_t)P.B) {
-                const uint32_t rows1 = min(nrows - d.kA, (uint32_t)A);
-                words1 = ((rows1 + 127u) >> 7) << 2;
+                const uint32_t rows1 = min(nrows - d.kA, A);
+                n_words1 = ((rows1 + 127u) >> 7) << 2;
             }
-            d.bit1 = G.side_words * 32u;
+            const unsigned long long in_img2 = in_img + Q.AC;
+            d.split2 = in_img2 < d.n ? (uint32_t)in_img2 : d.n;
             d.off_lo = (uint32_t)off;
             d.off_hi = (uint32_t)(off >> 32);
-            d.pad0 = d.pad1 = 0u;
-            desc[s] = d;
+            d.seg = (uint32_t)sg;
+            d.pad1 = 0u;
+            nd = d;
+            n_src = Q.cls + off;
+            n_bits0 = Q.bits + (size_t)d.b0 * Q.W + w0;
+            n_bits1 = Q.bits + (size_t)(d.b0 + 1u) * Q.W;
+        };
+        auto issue = [&](const uint32_t j) {   // the prepared tile is tile j
+            const int s = (int)(j % (uint32_t)NS);
+            unsigned char* stage = smem + (size_t)s * G.stage_stride;
+            desc[s] = nd;
             uint32_t* side = reinterpret_cast<uint32_t*>(stage + (size_t)G.tile_f * 4);
-            k7_mbar_expect_tx(full + s, d.n * 4u + (words0 + words1) * 4u);   // release: orders the descriptor
-            k7_bulk_g2s(stage, cls + off, d.n * 4u, full + s);
-            k7_bulk_g2s(side, bits + (size_t)d.b0 * G.W + w0, words0 * 4u, full + s);
-            if (words1) k7_bulk_g2s(side + G.side_words, bits + (size_t)(d.b0 + 1u) * G.W, words1 * 4u, full + s);
+            k7_mbar_expect_tx(full + s, nd.n * 4u + (n_words0 + n_words1) * 4u);   // release: orders the descriptor
+            k7_bulk_g2s(stage, n_src, nd.n * 4u, full + s);
+            k7_bulk_g2s(side, n_bits0, n_words0 * 4u, full + s);
+            if (n_words1) k7_bulk_g2s(side + G.side_words, n_bits1, n_words1 * 4u, full + s);
         };
         // with gradients one stage is always draining its store
         const uint32_t ahead = (uint32_t)(GRAD ? NS - 1 : NS);
         uint32_t jl = 0;
-        for (; jl < ntl && jl < ahead; ++jl) load(jl);
+        if (ntl > 0) prepare(0);
+        while (jl < ntl && jl < ahead) {
+            issue(jl++);
+            if (jl < ntl) prepare(jl);
+        }
         int s = 0;
         uint32_t phase = 0;
         for (uint32_t j = 0; j < ntl; ++j) {
@@ -364,14 +402,16 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
             if (GRAD) {
                 const K7TileDesc d = desc[s];
                 const unsigned long long off = ((unsigned long long)d.off_hi << 32) | d.off_lo;
-                k7_bulk_s2g(dcls + off, smem + (size_t)s * G.stage_stride, d.n * 4u);
+                k7_bulk_s2g(SG.s[d.seg].dcls + off, smem + (size_t)s * G.stage_stride, d.n * 4u);
                 k7_bulk_commit();
                 if (jl < ntl) {
                     k7_bulk_wait_read<1>();   // the store of tile j-1 has left its stage
-                    load(jl++);
+                    issue(jl++);
+                    if (jl < ntl) prepare(jl);
                 }
             } else if (jl < ntl) {
-                load(jl++);
+                issue(jl++);
+                if (jl < ntl) prepare(jl);
             }
             if (++s == NS) {
                 s = 0;
@@ -398,11 +438,12 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
     auto flush = [&]() {
         float c = oma * ((acc.x + acc.y) + cslow);
         c = k7_warp_sum(c);
-        if (lane == 0) my_partials[(size_t)cur_b * pstride] = c;
+        if (lane == 0) atomicAdd(my_partials + (size_t)cur_b * pstride, c);   // RED: no round trip; one adder per slot, in program order
         acc = make_float2(0.0f, 0.0f);
         cslow = 0.0f;
     };
-    // A warp meets the images in increasing order, so every (image, CTA, warp) slot is written once.
+    // Within a stream a warp meets the images in increasing order; a later stream (the next pyramid
+    // level) starts over, so a slot accumulates: always by lane 0 of this warp, in program order.
     auto enter = [&](const int b) {
         if (b == cur_b) return;
         if (cur_b >= 0) flush();
@@ -433,15 +474,15 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
             const int len = i_hi - i_lo, n4 = len >> 2;
             float* tile = reinterpret_cast<float*>(stage);
             float* slice = tile + i_lo;
-            const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // lead, kA, bit1, a0
+            const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // lead, kA, split2, a0
             // which image does the slice lie in?  bitbase = bit position of tile row 0 of that image's part
             int img = -1, bitbase = 0;
             if ((uint32_t)i_hi <= d0.z) {
                 img = (int)d0.w;
                 bitbase = (int)d1.x;
-            } else if ((uint32_t)i_lo >= d0.z && (unsigned long long)i_hi <= (unsigned long long)d0.z + G.AC) {
+            } else if ((uint32_t)i_lo >= d0.z && (uint32_t)i_hi <= d1.z) {
                 img = (int)d0.w + 1;
-                bitbase = (int)d1.z - (int)d1.y;
+                bitbase = (int)(G.side_words * 32u) - (int)d1.y;   // part 1 starts at tile row kA
             }
             if (img >= 0) {
                 enter(img);
@@ -497,7 +538,7 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
                     __syncwarp();
                     acc = acc0;
                     const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
-                    const float* src = cls + ((((unsigned long long)d2.y) << 32) | d2.x) + i_lo;
+                    const float* src = SG.s[d2.z].cls + ((((unsigned long long)d2.y) << 32) | d2.x) + i_lo;
                     for (int i = lane; i < len; i += 32) {
                         const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
                         exact(GRAD ? __ldg(src + i) : slice[i], ign, slice + i);
@@ -507,18 +548,20 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
                 // ---- generic path: the slice straddles an image boundary (or the tile spans > 2 images)
                 const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
                 const unsigned long long off = (((unsigned long long)d2.y) << 32) | d2.x;
-                const unsigned long long r0 = (unsigned long long)d0.w * (uint32_t)A + d1.w;
+                const K7PipeSeg& Q = SG.s[d2.z];
+                const uint32_t A = Q.A;
+                const unsigned long long r0 = (unsigned long long)d0.w * A + d1.w;
                 uint32_t i = (uint32_t)i_lo;
                 while (i < (uint32_t)i_hi) {   // warp-uniform: one iteration per image segment
-                    const uint32_t b = (uint32_t)((off + i) / G.AC);
-                    const unsigned long long img_end = (unsigned long long)(b + 1u) * G.AC - off;
+                    const uint32_t b = (uint32_t)((off + i) / Q.AC);
+                    const unsigned long long img_end = (unsigned long long)(b + 1u) * Q.AC - off;
                     const uint32_t seg_end = img_end < (unsigned long long)i_hi ? (uint32_t)img_end : (uint32_t)i_hi;
                     enter((int)b);
-                    const unsigned long long abase = (unsigned long long)b * (uint32_t)A;
+                    const unsigned long long abase = (unsigned long long)b * A;
                     for (uint32_t t = i + lane; t < seg_end; t += 32) {
                         const uint32_t k = k7_div((uint32_t)rem + t, G.div_c);
                         const uint32_t a = (uint32_t)(r0 + k - abase);
-                        const bool ign = (__ldg(bits + (size_t)b * G.W + (a >> 5)) >> (a & 31u)) & 1u;
+                        const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
                         exact(tile[t], ign, tile + t);
                     }
                     i = seg_end;
@@ -531,17 +574,20 @@ k7_loss_pipe_kernel(const float* __restrict__ cls, const uint32_t* __restrict__ 
     }
 
     // the last N % 4 elements cannot be bulk-copied: CTA 0, warp 0 serves them from global memory
-    if (blockIdx.x == 0 && warp == 0 && G.N4 < G.N) {
-        for (unsigned long long e = G.N4; e < G.N; ++e) {
-            const uint32_t b = (uint32_t)(e / G.AC);
-            enter((int)b);
-            if (lane == 0) {
-                const unsigned long long r = e / (uint32_t)C;
-                const uint32_t a = (uint32_t)(r - (unsigned long long)b * (uint32_t)A);
-                const bool ign = (__ldg(bits + (size_t)b * G.W + (a >> 5)) >> (a & 31u)) & 1u;
-                float g = 0.0f;
-                exact(__ldg(cls + e), ign, &g);
-                if (GRAD) dcls[e] = g;
+    if (blockIdx.x == 0 && warp == 0) {
+        for (int sg = 0; sg < SG.n; ++sg) {
+            const K7PipeSeg& Q = SG.s[sg];
+            for (unsigned long long e = Q.N4; e < Q.N; ++e) {
+                const uint32_t b = (uint32_t)(e / Q.AC);
+                enter((int)b);
+                if (lane == 0) {
+                    const unsigned long long r = e / (uint32_t)C;
+                    const uint32_t a = (uint32_t)(r - (unsigned long long)b * Q.A);
+                    const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
+                    float g = 0.0f;
+                    exact(__ldg(Q.cls + e), ign, &g);
+                    if (GRAD) Q.dcls[e] = g;
+                }
             }
         }
     }
@@ -569,18 +615,30 @@ struct K7LevelTable {
     int S[K7_MAX_LEVELS];
 };
 
-// One thread per 32-cell word of an (image, in-cell anchor) plane; the word is the same for all C
-// classes of that anchor.  S % 32 == 0: whole words, written C times.  Otherwise (small levels)
-// one thread per output word gathers its 32 elements individually.
+struct K7ExpandTable {
+    uint32_t* lbits[K7_MAX_LEVELS];
+    int level_off[K7_MAX_LEVELS], S[K7_MAX_LEVELS], Wl[K7_MAX_LEVELS];
+    int blk_off[K7_MAX_LEVELS + 1];   // first block of each level; [K7_MAX_LEVELS] = grid.x
+};
+
+// All levels in one launch, grid (blocks, B).  One thread per 32-cell word of an (image, in-cell
+// anchor) plane; the word is the same for all C classes of that anchor.  S % 32 == 0: whole words,
+// written C times.  Otherwise (small levels) one thread per output word gathers its 32 elements
+// individually.
 __global__ void __launch_bounds__(256)
-k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, int level_off, int K, int C, int S,
-                      uint32_t* __restrict__ lbits, int Wl) {
+k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, const __grid_constant__ K7ExpandTable T, int K, int C) {
     const int b = blockIdx.y;
+    int l = 0;
+#pragma unroll
+    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+        if ((int)blockIdx.x >= T.blk_off[i]) l = i;
+    const int S = T.S[l], level_off = T.level_off[l];
+    const int blk = (int)blockIdx.x - T.blk_off[l];
     const uint32_t* ab = abits + (size_t)b * W;
-    uint32_t* lb = lbits + (size_t)b * Wl;
+    uint32_t* lb = T.lbits[l] + (size_t)b * T.Wl[l];
     if ((S & 31) == 0) {
         const int spw = S >> 5;                       // words per plane
-        const int t = blockIdx.x * blockDim.x + threadIdx.x;
+        const int t = blk * 256 + (int)threadIdx.x;
         if (t >= K * spw) return;
         const int k = t / spw, sw = t - k * spw;
         uint32_t word = 0u;
@@ -590,7 +648,7 @@ k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, int level_off, 
         for (int c = 0; c < C; ++c) lb[(size_t)(k * C + c) * spw + sw] = word;
     } else {
         const long long nel = (long long)K * C * S;
-        const long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        const long long w = (long long)blk * 256 + threadIdx.x;
         if (w * 32 >= nel) return;
         uint32_t word = 0u;
         for (int j = 0; j < 32; ++j) {
@@ -852,55 +910,61 @@ static int k7_rows_gx(int B, int A) {
 // One plan serves both entry points: k7_loss streams ONE tensor [B,A,C]; k7_loss_levels streams
 // one NCHW tensor per pyramid level in the stream kernel's C == 1 mode (see K7LevelTable).
 struct K7LossPlan {
-    int nstreams;
-    K7PipeGeom G[K7_MAX_LEVELS];
+    int nseg;                               // streams of the one launch: 1, or the non-empty pyramid levels
+    K7PipeGeom G;
     int level[K7_MAX_LEVELS];               // pyramid level of each stream (levels mode)
+    unsigned long long AC[K7_MAX_LEVELS];   // elements per image of each stream
+    uint32_t tile0[K7_MAX_LEVELS];
     size_t off_lbits[K7_MAX_LEVELS];        // expanded ignore bits of the level
-    size_t off_pipe[K7_MAX_LEVELS];         // per-warp slots of the stream
+    size_t off_pipe;                        // per-warp slots of the launch
     size_t off_counter, off_bits, off_cta, off_rows, total;
     uint32_t cta_stride;
     int gx;
 };
 
-static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g);
+static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g);
 
-// levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
+// levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`, each
+// in the C == 1 mode (every element its own row).
 static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
                         K7LossPlan* p) {
-    p->nstreams = 0;
+    p->nseg = 0;
     size_t o = 0;
     p->off_counter = o;   // [B] per-image block counters + 1 batch counter
     o += k7_align_up(sizeof(unsigned int) * ((size_t)B + 1), 256);
     p->off_bits = o;      // anchor-ordered ignore bits when the caller did not keep k7_match's
     o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(A), 256);
-    uint32_t cta = 0;
+    int rc = k7_pipe_geometry(levels ? 1 : C, grad, &p->G);
+    if (rc) return rc;
+    unsigned long long tiles = 0;
     const int nl = levels ? spec->num_levels : 1;
     for (int l = 0; l < nl; ++l) {
-        long long a_l = A;
-        int c_l = C;
+        unsigned long long ac = (unsigned long long)A * (unsigned long long)C;
         if (levels) {
-            a_l = (long long)spec->cell_anchors * C * spec->fh[l] * spec->fw[l];   // elements per image, each its own row
-            c_l = 1;
-            if (a_l == 0) continue;
-            K7_REQUIRE(a_l < (1ll << 31), "k7_loss_levels: level %d has %lld elements per image", l, a_l);
+            ac = (unsigned long long)spec->cell_anchors * C * spec->fh[l] * spec->fw[l];
+            if (ac == 0) continue;
+            K7_REQUIRE(ac < (1ull << 31), "k7_loss_levels: level %d has %llu elements per image", l, ac);
         }
-        const int i = p->nstreams++;
-        int rc = k7_pipe_geometry(B, (int)a_l, c_l, grad, &p->G[i]);
-        if (rc) return rc;
+        const int i = p->nseg++;
         p->level[i] = l;
-        p->G[i].cta_off = cta;
-        // the workspace query has no device: assume the largest grid
-        cta += exact_grid ? (uint32_t)p->G[i].grid : (uint32_t)K7_LOSS_MAX_GRID;
+        p->AC[i] = ac;
+        p->tile0[i] = (uint32_t)tiles;
+        tiles += (((ac * (unsigned long long)B) & ~3ull) + p->G.tile_f - 1) / p->G.tile_f;
+        K7_REQUIRE(tiles < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", tiles);
         p->off_lbits[i] = o;
-        if (levels) o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(a_l), 256);
-        p->off_pipe[i] = o;
-        o += k7_align_up(sizeof(float) * (size_t)B * (exact_grid ? (size_t)p->G[i].grid : (size_t)K7_LOSS_MAX_GRID) *
-                             K7_PIPE_MAX_CW, 256);
+        if (levels) o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(ac), 256);
     }
-    p->cta_stride = cta;
-    for (int i = 0; i < p->nstreams; ++i) p->G[i].cta_stride = cta;
+    p->G.num_tiles = (uint32_t)tiles;
+    int grid = exact_grid ? k7_sm_count() : K7_LOSS_MAX_GRID;   // the workspace query has no device: assume the largest grid
+    if (grid > K7_LOSS_MAX_GRID) grid = K7_LOSS_MAX_GRID;
+    if (exact_grid && tiles < (unsigned long long)grid) grid = (int)tiles;
+    p->G.grid = grid < 1 ? 1 : grid;
+    p->G.cta_off = 0;
+    p->G.cta_stride = p->cta_stride = (uint32_t)p->G.grid;
+    p->off_pipe = o;
+    o += k7_align_up(sizeof(float) * (size_t)B * (size_t)p->G.grid * K7_PIPE_MAX_CW, 256);
     p->off_cta = o;       // [B][cta_stride] stream partials, one per (image, CTA)
-    o += k7_align_up(sizeof(float) * (size_t)B * (cta > 0 ? cta : 1), 256);
+    o += k7_align_up(sizeof(float) * (size_t)B * p->cta_stride, 256);
     p->gx = k7_rows_gx(B, A);
     p->off_rows = o;
     o += k7_align_up(sizeof(float2) * (size_t)B * p->gx, 256);
@@ -928,10 +992,7 @@ static int k7_env_int(const char* name, int dflt) {
     return atoi(v);
 }
 
-static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
-    g->AC = (unsigned long long)A * (unsigned long long)C;
-    g->N = g->AC * (unsigned long long)B;
-    g->N4 = g->N & ~3ull;
+static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g) {
     // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass is bound by per-slice bookkeeping and
     // wants long slices (12 warps x 1024 floats); with gradients the stream is a copy and wants
     // the most warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
@@ -943,10 +1004,6 @@ static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
     g->cw = cw;
     g->slice = (uint32_t)slice;
     g->tile_f = (uint32_t)cw * (uint32_t)slice;
-    const unsigned long long nt = (g->N4 + g->tile_f - 1) / g->tile_f;
-    K7_REQUIRE(nt < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", nt);
-    g->num_tiles = (uint32_t)nt;
-    g->W = (uint32_t)K7_IGNORE_WORDS(A);
     g->div_c = k7_fastdiv_make((uint32_t)C);
     // rows touching a tile: (tile_f-1)/C + 2 at most; a part starts up to 127 bits into its first 16 bytes
     const uint32_t nrows_max = (g->tile_f - 1) / (uint32_t)C + 2;
@@ -969,10 +1026,6 @@ static int k7_pipe_geometry(int B, int A, int C, bool grad, K7PipeGeom* g) {
     g->off_bars = (uint32_t)o;
     o += (size_t)stages * 16;
     g->smem_bytes = o;
-    int grid = k7_sm_count();
-    if (grid > K7_LOSS_MAX_GRID) grid = K7_LOSS_MAX_GRID;
-    if (nt < (unsigned long long)grid) grid = (int)nt;
-    g->grid = grid < 1 ? 1 : grid;
     return K7_OK;
 }
 
@@ -1038,35 +1091,63 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
 
     K7LevelTable LT;
     memset(&LT, 0, sizeof(LT));
-    for (int i = 0; i < L.nstreams; ++i) {
-        const K7PipeGeom& G = L.G[i];
-        const float* src = cls;
-        float* dst = dcls;
-        const uint32_t* bits = ignore_bits;
-        K7LossDev Ps = P;
+    K7PipeSegs SG;
+    memset(&SG, 0, sizeof(SG));
+    SG.n = L.nseg;
+    K7ExpandTable ET;
+    memset(&ET, 0, sizeof(ET));
+    int eblocks = 0;
+    for (int i = 0; i < L.nseg; ++i) {
+        K7PipeSeg& Q = SG.s[i];
+        Q.cls = cls;
+        Q.dcls = dcls;
+        Q.bits = ignore_bits;
+        Q.AC = L.AC[i];
+        Q.N = Q.AC * (unsigned long long)B;
+        Q.N4 = Q.N & ~3ull;
+        Q.A = (uint32_t)A;
+        Q.tile0 = L.tile0[i];
         if (lv) {
             const int l = L.level[i];
             const int S = spec->fh[l] * spec->fw[l], K = spec->cell_anchors;
-            src = levels[l];
-            dst = grad ? dlevels[l] : nullptr;
-            K7_REQUIRE(src && (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (!grad || (dst && (reinterpret_cast<uintptr_t>(dst) & 15) == 0)),
+            Q.cls = levels[l];
+            Q.dcls = grad ? dlevels[l] : nullptr;
+            K7_REQUIRE(Q.cls && (reinterpret_cast<uintptr_t>(Q.cls) & 15) == 0 &&
+                           (!grad || (Q.dcls && (reinterpret_cast<uintptr_t>(Q.dcls) & 15) == 0)),
                        "k7_loss_levels: level %d: null or unaligned tensor", l);
-            LT.cls[l] = src;
-            LT.dcls[l] = dst;
+            LT.cls[l] = Q.cls;
+            LT.dcls[l] = Q.dcls;
             LT.S[l] = S;
+            Q.A = (uint32_t)Q.AC;   // C == 1 mode
             uint32_t* lbits = reinterpret_cast<uint32_t*>(ws + L.off_lbits[i]);
+            Q.bits = lbits;
             const long long threads = (S & 31) == 0 ? (long long)K * (S >> 5) : ((long long)K * C * S + 31) / 32;
-            dim3 grid((unsigned)((threads + 255) / 256), B);
-            k7_bits_expand_kernel<<<grid, 256, 0, st>>>(ignore_bits, W, spec->offset[l], K, C, S, lbits, (int)G.W);
-            K7_LAUNCH_CHECK();
-            bits = lbits;
-            Ps.A = K * C * S;
+            ET.lbits[i] = lbits;
+            ET.level_off[i] = spec->offset[l];
+            ET.S[i] = S;
+            ET.Wl[i] = (int)K7_IGNORE_WORDS(Q.A);
+            ET.blk_off[i] = eblocks;
+            eblocks += (int)((threads + 255) / 256);
+        }
+        Q.W = (uint32_t)K7_IGNORE_WORDS(Q.A);
+    }
+    if (lv && eblocks > 0) {
+        for (int i = L.nseg; i <= K7_MAX_LEVELS; ++i) ET.blk_off[i] = eblocks;
+        dim3 grid(eblocks, B);
+        k7_bits_expand_kernel<<<grid, 256, 0, st>>>(ignore_bits, W, ET, spec->cell_anchors, C);
+        K7_LAUNCH_CHECK();
+    }
+    if (L.G.num_tiles > 0 || L.nseg > 0) {
+        const K7PipeGeom& G = L.G;
+        K7LossDev Ps = P;
+        if (lv) {
+            Ps.A = 0;   // per stream: K7PipeSeg::A
             Ps.C = 1;
         }
-        float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe[i]);
+        float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe);
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(src, bits, num_pos, Ps, G, pipe_partials, cta_partials, dst);
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, Ps, G, pipe_partials, cta_partials);
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
