@@ -647,16 +647,24 @@ k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, const __grid_co
         for (int j = 0; j < 32; ++j, a += K) word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
         for (int c = 0; c < C; ++c) lb[(size_t)(k * C + c) * spw + sw] = word;
     } else {
-        const long long nel = (long long)K * C * S;
-        const long long w = (long long)blk * 256 + threadIdx.x;
-        if (w * 32 >= nel) return;
+        const int nel = K * C * S;                    // < 2^31 (checked by the plan)
+        const int w = blk * 256 + (int)threadIdx.x;
+        if (w >= (nel + 31) >> 5) return;
+        const int e0 = w << 5;
+        int ch = e0 / S, s = e0 - ch * S;             // plane (k*C + c) and cell of the word's first element
+        int k = ch / C, c = ch - k * C;
+        const int nb = min(32, nel - e0);
         uint32_t word = 0u;
-        for (int j = 0; j < 32; ++j) {
-            const long long e = w * 32 + j;
-            if (e >= nel) break;
-            const int ch = (int)(e / S), s = (int)(e - (long long)ch * S);
-            const int a = level_off + s * K + ch / C;
+        for (int j = 0; j < nb; ++j) {
+            const int a = level_off + s * K + k;
             word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
+            if (++s == S) {                           // next plane: same anchor plane until the classes run out
+                s = 0;
+                if (++c == C) {
+                    c = 0;
+                    ++k;
+                }
+            }
         }
         lb[w] = word;
     }
