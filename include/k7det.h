@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 4
+#define K7_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -231,6 +231,44 @@ K7_API int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B
 K7_API size_t k7_nms_workspace_bytes(int n);
 K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
            int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- evaluator tails on device
+ * What the reference's evaluators do on the host with every image's (scores, labels, boxes)
+ * after a device->host copy, for a whole batch in three small launches:
+ *   K7_EVAL_COCO  datasettool/coco_eval.py:25-57, ksevendata_eval.py:24-61
+ *       boxes / scale, xyxy -> xywh (float32), labels outside `valid_label` skipped, rows of an
+ *       image stop at the first float(score) < score_thr (float64 comparison, as Python does);
+ *       row = (image_id, x, y, w, h, score, category_of_label[label]), images in order.
+ *   K7_EVAL_CSV   datasettool/csv_eval.py:93-121 (_get_detections)
+ *       boxes / scale, rows with score > (float)score_thr, the first max_detections of them
+ *       (input order = descending score), bucketed by label:
+ *       row = (image index, x1, y1, x2, y2, score, label), ordered by (image, label, rank);
+ *       class_offsets[b*num_classes + c] .. [+1] delimit all_detections[b][c].
+ * Rows are float64 [N,7] (the float32 values widened exactly: what json.dump / np.concatenate
+ * see in the reference); row_offsets[B+1] int32 are the exclusive per-image offsets, N = row_offsets[B].
+ * Inputs are the row-padded outputs of k7_detect_gather (or of any detector): scores [B,cap] f32
+ * descending per image, labels [B,cap] i64, boxes [B,cap,4] f32, counts[b*counts_stride] rows valid.
+ * `scale` holds float32(scale) per image.  Labels outside [0, num_classes) are dropped. */
+#define K7_EVAL_COCO 0
+#define K7_EVAL_CSV 1
+
+typedef struct K7EvalParams {
+    int32_t mode;           /* K7_EVAL_COCO | K7_EVAL_CSV */
+    int32_t max_detections; /* CSV: csv_eval.py:64 default 100; 0 = no cap.  COCO: ignored */
+    int32_t num_classes;
+    int32_t reserved;
+    double score_thr;       /* coco_eval.py:6 / csv_eval.py:64 default 0.05 */
+} K7EvalParams;
+
+K7_API size_t k7_eval_pack_workspace_bytes(int B, int num_classes);
+K7_API int k7_eval_pack(const float* scores, const int64_t* labels, const float* boxes, int cap,
+                 const int32_t* counts, int counts_stride, int B, const float* scale,
+                 const int64_t* image_ids /* NULL: the image index */,
+                 const int32_t* category_of_label /* [num_classes] or NULL: the label */,
+                 const uint8_t* valid_label /* [num_classes] or NULL: all (COCO mode) */,
+                 const K7EvalParams* params, double* rows /* [B*cap,7] */, int32_t* row_offsets /* [B+1] */,
+                 int32_t* class_offsets /* CSV: [B*num_classes+1]; else NULL */,
+                 void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -78,7 +78,18 @@ class K7DetectParams(C.Structure):
     ]
 
 
-ABI_VERSION = 4                      # K7_ABI_VERSION of include/k7det.h
+class K7EvalParams(C.Structure):
+    _fields_ = [
+        ("mode", C.c_int32),
+        ("max_detections", C.c_int32),
+        ("num_classes", C.c_int32),
+        ("reserved", C.c_int32),
+        ("score_thr", C.c_double),
+    ]
+
+
+EVAL_COCO, EVAL_CSV = 0, 1
+ABI_VERSION = 5                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -114,6 +125,9 @@ SYMBOLS = {
                                    _P, _P, _P, _P, _P, _P]),
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_eval_pack_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "k7_eval_pack": (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_int, _P, _P, _P, _P, C.POINTER(K7EvalParams),
+                               _P, _P, _P, _P, C.c_size_t, _P]),
 }
 
 _lib = None

@@ -22,6 +22,7 @@ Reference lines restated (paths relative to /root/reference):
   assignment+loss   architectures/losses.py:30-168; architectures/loss_efficientdet.py:31-160
   decode / clip     architectures/utils.py:26-71; architectures/utils_efficientdet.py:8-50
   eval tail         architectures/retinanet.py:297-318; utils/utils.py:76-114
+  evaluator tails   datasettool/coco_eval.py:25-57; ksevendata_eval.py:24-61; csv_eval.py:93-121
   NMS               torchvision.ops.nms (third party, NOT vendored by the reference;
                     pinned here to torchvision 0.26.0 as installed).  `greedy_nms`
                     restates its published CPU algorithm (stable descending sort,
@@ -431,3 +432,60 @@ def head_probabilities(logits_per_level, num_anchors: int, num_classes: int, act
     if act_first:
         return head_logits([torch.sigmoid(z) for z in logits_per_level], num_anchors, num_classes)
     return torch.sigmoid(head_logits(logits_per_level, num_anchors, num_classes))
+
+
+# ------------------------------------------------------------------ evaluator tails
+def eval_rows_coco(scores, labels, boxes, counts, scales, image_ids, category_of_label,
+                   threshold: float = 0.05, valid_class_id=None) -> np.ndarray:
+    """datasettool/coco_eval.py:25-57 and ksevendata_eval.py:24-61 for a batch: per image the model's
+    (scores[n], labels[n], boxes[n,4]) in descending score order become result rows
+    (image_id, x, y, w, h, score, category_id) — float64 [N,7], images in order.
+      boxes /= scale                      float32 tensor divided by a Python float (coco_eval.py:30)
+      boxes[:, 2] -= boxes[:, 0] ...      xyxy -> xywh in float32 (coco_eval.py:34-35)
+      labels outside valid_class_id are skipped BEFORE the threshold test (ksevendata_eval.py:46-47)
+      the loop BREAKS at the first row whose float(score) < threshold (coco_eval.py:45-46)."""
+    rows = []
+    for b in range(len(counts)):
+        n = int(counts[b])
+        if n == 0:
+            continue
+        sc = torch.as_tensor(np.asarray(scores[b][:n])).float().clone()
+        lb = np.asarray(labels[b][:n])
+        bx = torch.as_tensor(np.asarray(boxes[b][:n])).float().clone()
+        bx /= float(scales[b])
+        bx[:, 2] -= bx[:, 0]
+        bx[:, 3] -= bx[:, 1]
+        for i in range(n):
+            score, label = float(sc[i]), int(lb[i])
+            if valid_class_id is not None and len(valid_class_id) and label not in valid_class_id:
+                continue
+            if score < threshold:
+                break
+            rows.append([float(image_ids[b]), *[float(v) for v in bx[i].tolist()], score, float(category_of_label[label])])
+    return np.array(rows, np.float64).reshape(-1, 7)
+
+
+def eval_rows_csv(scores, labels, boxes, counts, scales, num_classes: int, score_threshold: float = 0.05,
+                  max_detections: int = 100):
+    """datasettool/csv_eval.py:93-121 (_get_detections) for a batch: rows (image index, x1, y1, x2, y2,
+    score, label) float64 [N,7] ordered by (image, label, rank) and the exclusive offsets of every
+    (image, label) bucket [B*num_classes + 1] — all_detections[b][c] == rows[off[b*nc+c]:off[b*nc+c+1], 1:6].
+      boxes /= scale                       float32 numpy array by a Python float (csv_eval.py:96)
+      indices = where(scores > thr)        float32 comparison (the Python float is cast down)
+      argsort(-scores)[:max_detections]    numpy's default sort is not stable; the inputs are already in
+                                           descending order, equal scores keep their input order here."""
+    rows, offs = [], [0]
+    for b in range(len(counts)):
+        n = int(counts[b])
+        sc = np.asarray(scores[b][:n], np.float32)
+        lb = np.asarray(labels[b][:n])
+        bx = np.asarray(boxes[b][:n], np.float32).copy()
+        bx /= np.float32(scales[b])
+        idx = np.where(sc > np.float32(score_threshold))[0]
+        order = np.argsort(-sc[idx], kind="stable")[:max_detections] if max_detections > 0 else np.argsort(-sc[idx], kind="stable")
+        sel = idx[order]
+        for c in range(num_classes):
+            for i in sel[lb[sel] == c]:
+                rows.append([float(b), *[float(v) for v in bx[i]], float(sc[i]), float(c)])
+            offs.append(len(rows))
+    return np.array(rows, np.float64).reshape(-1, 7), np.array(offs, np.int32)

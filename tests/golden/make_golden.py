@@ -16,6 +16,8 @@ and writes
   tests/golden/detect_*.npz        inputs, decoded+clipped boxes, per-image keep / scores / labels / boxes
   tests/golden/head_retina.npz     per-level NCHW logits of the reference's ClassificationModel (captured in
                                    front of its output_act) and the [B,A,C] probabilities it returns
+  tests/golden/eval_tail.npz       detections of 6 images and what datasettool/{coco_eval,ksevendata_eval,csv_eval}.py
+                                   make of them (result rows / per-class detection arrays)
 The reference's hidden intermediates (IoU_max, IoU_argmax, masks) are obtained by
 calling the reference's own calc_iou and repeating losses.py:66,79-82 on its output.
 """
@@ -276,9 +278,122 @@ def gen_head():
     np.savez_compressed(os.path.join(HERE, "head_retina.npz"), **rec)
     print("head_retina", probs.shape, float(probs.min()), float(probs.max()))
 
+def gen_eval_tail():
+    """datasettool/coco_eval.py:6-66, ksevendata_eval.py:8-72, csv_eval.py:64-121: what the evaluators do
+    with the model's (scores, labels, boxes) per image.  The UNMODIFIED reference functions are run on a
+    stub dataset and a stub model that replays fixed detections; pycocotools (absent here, and irrelevant to
+    the tail) is replaced by an empty stand-in so that the modules import, and Tensor.cuda() is the identity
+    on this GPU-less machine (ksevendata_eval.py calls it unconditionally)."""
+    import tempfile
+    import types
+    stub = types.ModuleType("pycocotools")
+    stub_eval = types.ModuleType("pycocotools.cocoeval")
+
+    class COCOeval:                                   # nothing of the tail depends on it
+        def __init__(self, *a, **k):
+            self.params = types.SimpleNamespace()
+
+        def evaluate(self): pass
+        def accumulate(self): pass
+        def summarize(self): pass
+    stub_eval.COCOeval = COCOeval
+    stub.cocoeval = stub_eval
+    sys.modules.setdefault("pycocotools", stub)
+    sys.modules.setdefault("pycocotools.cocoeval", stub_eval)
+    from datasettool import coco_eval as ref_coco_eval
+    from datasettool import ksevendata_eval as ref_k7_eval
+    from datasettool import csv_eval as ref_csv_eval
+
+    rng = np.random.RandomState(20260413)
+    B, Cn, cap = 6, 7, 48
+    counts = np.array([40, 0, 48, 1, 17, 33], dtype=np.int32)
+    scores = np.zeros((B, cap), np.float32)
+    labels = np.zeros((B, cap), np.int64)
+    boxes = np.zeros((B, cap, 4), np.float32)
+    for b in range(B):
+        n = int(counts[b])
+        sc = np.sort(rng.uniform(0.02, 0.99, size=n).astype(np.float32))[::-1]   # descending; a tail below 0.05 / 0.3
+        scores[b, :n] = sc
+        labels[b, :n] = rng.randint(0, Cn, size=n)
+        xy = rng.uniform(0, 400, size=(n, 2)).astype(np.float32)
+        wh = rng.uniform(1, 200, size=(n, 2)).astype(np.float32)
+        boxes[b, :n, :2] = xy
+        boxes[b, :n, 2:] = xy + wh
+    scales = np.array([0.7314, 1.0, 1.6180339887, 0.5, 0.3333333333, 2.25])
+    image_ids = [139, 285, 632, 724, 776, 581929]
+    coco_label = {0: 1, 1: 2, 2: 3, 3: 5, 4: 7, 5: 11, 6: 90}
+
+    class Coco:
+        def loadRes(self, path): return None
+
+    class DS:
+        set_name = "golden"
+        coco = Coco()
+        kseven_data = Coco()
+
+        def __init__(self): self.image_ids = image_ids
+        def __len__(self): return B
+        def __getitem__(self, i): return {"img": torch.zeros(4, 4, 3), "scale": float(scales[i])}
+        def label_to_coco_label(self, label): return coco_label[label]
+        def label_to_ksevendata_label(self, label): return coco_label[label]
+        def num_classes(self): return Cn
+
+    class Model:
+        """Replays the detections: the zeros triple when an image has none (retinanet.py:308)."""
+        def __init__(self): self.i = 0
+        def eval(self): return self
+        def train(self, mode=True): return self
+
+        def __call__(self, x, return_loss=False):
+            b = self.i % B
+            self.i += 1
+            n = int(counts[b])
+            if n == 0:
+                return [torch.zeros(1), torch.zeros(1), torch.zeros(1, 4)]
+            return [torch.from_numpy(scores[b, :n].copy()), torch.from_numpy(labels[b, :n].copy()),
+                    torch.from_numpy(boxes[b, :n].copy())]
+
+    rec = {"scores": scores, "labels": labels, "boxes": boxes, "counts": counts, "scales": scales,
+           "image_ids": np.array(image_ids, np.int64), "category_of_label": np.array([coco_label[i] for i in range(Cn)], np.int32)}
+    had_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    cwd = os.getcwd()
+    try:
+        with tempfile.TemporaryDirectory() as tmp, redirect_stdout(io.StringIO()):
+            os.chdir(tmp)
+            for tag, thr in (("coco_t005", 0.05), ("coco_t030", 0.3)):
+                ref_coco_eval.evaluate_coco(DS(), Model(), threshold=thr)
+                res = json.load(open("golden_bbox_results.json"))
+                rec[tag] = np.array([[r["image_id"], *r["bbox"], r["score"], r["category_id"]] for r in res], np.float64)
+            for tag, thr, valid in (("k7_t005_all", 0.05, None), ("k7_t030_valid", 0.3, [0, 2, 5])):
+                try:
+                    ref_k7_eval.coco_evaluate_ksevendata(DS(), Model(), threshold=thr, valid_class_id=valid)
+                except Exception:          # whatever follows the dump needs a real annotation file
+                    pass
+                res = json.load(open("tmp_bbox_results.json"))
+                rec[tag] = np.array([[r["image_id"], *r["bbox"], r["score"], r["category_id"]] for r in res], np.float64)
+            for tag, thr, md in (("csv_t005_m100", 0.05, 100), ("csv_t030_m10", 0.3, 10)):
+                det = ref_csv_eval._get_detections(DS(), Model(), score_threshold=thr, max_detections=md)
+                rows, offs = [], [0]
+                for b in range(B):
+                    for c in range(Cn):
+                        d = np.asarray(det[b][c], np.float64).reshape(-1, 5)
+                        for r in d:
+                            rows.append([b, *r, c])
+                        offs.append(len(rows))
+                rec[tag] = np.array(rows, np.float64).reshape(-1, 7)
+                rec[tag + "_class_offsets"] = np.array(offs, np.int32)
+    finally:
+        os.chdir(cwd)
+        torch.Tensor.cuda = had_cuda
+    rec["k7_valid"] = np.array([0, 2, 5], np.int32)
+    np.savez_compressed(os.path.join(HERE, "eval_tail.npz"), **rec)
+    print("eval_tail", {k: v.shape for k, v in rec.items() if k.startswith(("coco", "k7_t", "csv"))})
+
 
 if __name__ == "__main__":
     gen_anchors()
     gen_loss()
     gen_detect()
     gen_head()
+    gen_eval_tail()

@@ -663,3 +663,112 @@ def test_head_levels_reject_bad_shapes():
     bad[0] = bad[0][:, :, :-1].contiguous()
     with pytest.raises(ValueError):
         b200det.detect(bad, reg, anc, (64, 64))
+
+
+# ------------------------------------------------------------------ evaluator tails on device
+def _fixture_detections(g):
+    return b200det.BatchDetections(torch.from_numpy(g["counts"]).long(), torch.from_numpy(g["counts"]).long(),
+                                   torch.from_numpy(g["scores"]).to(DEV), torch.from_numpy(g["labels"]).to(DEV),
+                                   torch.from_numpy(g["boxes"]).to(DEV), None, None)
+
+
+def test_eval_pack_matches_reference_fixture():
+    """k7_eval_pack == the rows the reference's evaluate_coco / coco_evaluate_ksevendata / _get_detections
+    built from the same detections (tests/golden/eval_tail.npz), bit for bit, and the host converters
+    rebuild the reference's Python objects."""
+    g = np.load(os.path.join(GOLDEN, "eval_tail.npz"))
+    det = _fixture_detections(g)
+    ids, cat = g["image_ids"].tolist(), g["category_of_label"].tolist()
+    for tag, thr, valid in (("coco_t005", 0.05, None), ("coco_t030", 0.3, None), ("k7_t005_all", 0.05, None),
+                            ("k7_t030_valid", 0.3, g["k7_valid"].tolist())):
+        p = b200det.eval_pack(det, g["scales"], mode="coco", image_ids=ids, category_of_label=cat, valid_class_id=valid,
+                              threshold=thr)
+        assert np.array_equal(p.rows.cpu().numpy(), g[tag]), tag
+        res = b200det.coco_results(p)
+        assert len(res) == len(g[tag])
+        if len(res):
+            assert res[0] == {"image_id": int(g[tag][0, 0]), "category_id": int(g[tag][0, 6]), "score": float(g[tag][0, 5]),
+                              "bbox": [float(v) for v in g[tag][0, 1:5]]}
+    nc = len(cat)
+    for tag, thr, md in (("csv_t005_m100", 0.05, 100), ("csv_t030_m10", 0.3, 10)):
+        p = b200det.eval_pack(det, g["scales"], mode="csv", num_classes=nc, threshold=thr, max_detections=md)
+        assert np.array_equal(p.class_offsets.cpu().numpy(), g[tag + "_class_offsets"]), tag
+        assert np.array_equal(p.rows.cpu().numpy(), g[tag]), tag
+        alld = b200det.csv_all_detections(p)
+        off = g[tag + "_class_offsets"]
+        assert len(alld) == len(g["counts"]) and all(len(a) == nc for a in alld)
+        assert np.array_equal(alld[2][3], g[tag][off[2 * nc + 3]:off[2 * nc + 4], 1:6])
+
+
+@pytest.mark.parametrize("B,cap,nc,max_det", [(1, 1, 1, 100), (37, 300, 80, 100), (5, 1500, 3, 0), (300, 64, 90, 7)])
+def test_eval_pack_vs_oracle_random(B, cap, nc, max_det):
+    """Random batches (empty images, counts above one block, scores straddling the threshold,
+    duplicated scores) against the oracle, both modes, bit for bit."""
+    rng = np.random.RandomState(B * 1000 + cap)
+    counts = rng.randint(0, cap + 1, size=B).astype(np.int32)
+    counts[rng.randint(0, B)] = 0
+    counts[rng.randint(0, B)] = cap
+    scores = np.zeros((B, cap), np.float32)
+    for b in range(B):
+        sc = np.round(rng.uniform(0.0, 1.0, size=counts[b]), 2).astype(np.float32)   # many ties
+        scores[b, :counts[b]] = np.sort(sc)[::-1]
+    labels = rng.randint(0, nc, size=(B, cap)).astype(np.int64)
+    xy = rng.uniform(0, 900, size=(B, cap, 2)).astype(np.float32)
+    boxes = np.concatenate([xy, xy + rng.uniform(0, 300, size=(B, cap, 2)).astype(np.float32)], axis=2)
+    scales = rng.uniform(0.3, 2.5, size=B)
+    ids = rng.randint(1, 600000, size=B).tolist()
+    cat = rng.randint(1, 91, size=nc).tolist()
+    valid = sorted(set(rng.randint(0, nc, size=max(1, nc // 2)).tolist()))
+    det = b200det.BatchDetections(torch.from_numpy(counts).long(), torch.from_numpy(counts).long(),
+                                  torch.from_numpy(scores).to(DEV), torch.from_numpy(labels).to(DEV),
+                                  torch.from_numpy(boxes).to(DEV), None, None)
+    for thr, v in ((0.05, None), (0.5, valid)):
+        p = b200det.eval_pack(det, scales, mode="coco", image_ids=ids, category_of_label=cat, valid_class_id=v, threshold=thr)
+        want = R.eval_rows_coco(scores, labels, boxes, counts, scales, ids, cat, threshold=thr, valid_class_id=v)
+        assert np.array_equal(p.rows.cpu().numpy(), want)
+        off = p.row_offsets.cpu().numpy()
+        assert off[0] == 0 and off[-1] == len(want) and np.all(np.diff(off) >= 0)
+    for thr in (0.05, 0.5):
+        p = b200det.eval_pack(det, scales, mode="csv", num_classes=nc, threshold=thr, max_detections=max_det)
+        want, woff = R.eval_rows_csv(scores, labels, boxes, counts, scales, nc, score_threshold=thr, max_detections=max_det)
+        assert np.array_equal(p.class_offsets.cpu().numpy(), woff)
+        assert np.array_equal(p.rows.cpu().numpy(), want)
+
+
+def test_eval_pack_after_detect_end_to_end():
+    """detect() -> eval_pack() on device == the reference's per-image host loop on the oracle's detections."""
+    B, C, H, W = 4, 6, 128, 160
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    gen = torch.Generator().manual_seed(5)
+    cls = torch.sigmoid(torch.randn((B, anc.shape[1], C), generator=gen) * 1.5 - 4.0).to(DEV)
+    reg = (torch.randn((B, anc.shape[1], 4), generator=gen) * 0.5).to(DEV)
+    det = b200det.detect(cls, reg, anc, (H, W))
+    scales = [0.8, 1.25, 0.5, 1.0]
+    p = b200det.eval_pack(det, scales, mode="coco", image_ids=[11, 12, 13, 14], category_of_label=list(range(1, C + 1)))
+    _, dets = R.detect_batch(cls.cpu(), reg.cpu(), anc.cpu(), H, W)
+    cap = max(1, max(len(d.scores) for d in dets))
+    sc = np.zeros((B, cap), np.float32)
+    lb = np.zeros((B, cap), np.int64)
+    bx = np.zeros((B, cap, 4), np.float32)
+    for b, d in enumerate(dets):
+        k = len(d.scores)
+        sc[b, :k], lb[b, :k], bx[b, :k] = d.scores.numpy(), d.labels.numpy(), d.boxes.numpy()
+    want = R.eval_rows_coco(sc, lb, bx, [len(d.scores) for d in dets], scales, [11, 12, 13, 14], list(range(1, C + 1)))
+    got = p.rows.cpu().numpy()
+    assert got.shape == want.shape and got.shape[0] > 0
+    assert np.array_equal(got[:, [0, 6]], want[:, [0, 6]])
+    np.testing.assert_allclose(got[:, 1:6], want[:, 1:6], rtol=1e-5, atol=1e-3)
+
+
+def test_eval_pack_rejects_bad_arguments():
+    g = np.load(os.path.join(GOLDEN, "eval_tail.npz"))
+    det = _fixture_detections(g)
+    with pytest.raises(ValueError):
+        b200det.eval_pack(det, g["scales"][:2], num_classes=7)
+    with pytest.raises(ValueError):
+        b200det.eval_pack(det, g["scales"], mode="voc", num_classes=7)
+    with pytest.raises(ValueError):
+        b200det.eval_pack(det, g["scales"])
+    with pytest.raises(ValueError):
+        b200det.eval_pack(det, g["scales"], mode="csv", num_classes=10000)

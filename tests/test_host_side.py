@@ -70,14 +70,14 @@ def test_struct_layout_matches_header(tmp_path):
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     src = tmp_path / "sizes.c"
-    src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %d\\n",'
+    src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %d\\n",'
                    'sizeof(K7AnchorSpec),sizeof(K7MatchParams),sizeof(K7LossParams),sizeof(K7DecodeParams),'
-                   'sizeof(K7DetectParams),K7_ABI_VERSION);return 0;}\n')
+                   'sizeof(K7DetectParams),sizeof(K7EvalParams),K7_ABI_VERSION);return 0;}\n')
     exe = tmp_path / "sizes"
     subprocess.run(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(L.K7AnchorSpec), C.sizeof(L.K7MatchParams), C.sizeof(L.K7LossParams), C.sizeof(L.K7DecodeParams),
-            C.sizeof(L.K7DetectParams), L.ABI_VERSION]
+            C.sizeof(L.K7DetectParams), C.sizeof(L.K7EvalParams), L.ABI_VERSION]
     assert got == want
 
 
@@ -91,6 +91,10 @@ def test_no_cpu_fallback():
         b200det.BBoxTransform()(torch.rand(1, 8, 4), torch.rand(1, 8, 4))
     with pytest.raises(RuntimeError):
         b200det.nms(torch.rand(4, 4), torch.rand(4), 0.5)
+    with pytest.raises(RuntimeError):
+        det = b200det.BatchDetections(torch.tensor([1]), torch.tensor([1]), torch.rand(1, 2), torch.zeros(1, 2, dtype=torch.int64),
+                                      torch.rand(1, 2, 4), torch.zeros(1, 2, dtype=torch.int32), torch.zeros(1, 2, dtype=torch.int32))
+        b200det.eval_pack(det, [1.0], num_classes=3)
 
 
 def test_modules_are_stateless():

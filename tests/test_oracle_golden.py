@@ -126,3 +126,20 @@ def test_head_layout_and_activation():
     # the shared-head order (layout, then activation: simple_head.py:307-310) agrees to the last bit or one ulp
     late = R.head_probabilities(levels, int(g["num_anchors"]), int(g["num_classes"]), act_first=False)
     np.testing.assert_allclose(late.numpy(), g["probs"], rtol=2e-7, atol=0)
+
+
+def test_evaluator_tails_match_reference():
+    """oracle eval_rows_coco / eval_rows_csv == what the reference's evaluate_coco,
+    coco_evaluate_ksevendata and _get_detections produced from the same detections (eval_tail.npz)."""
+    g = np.load(os.path.join(GOLDEN, "eval_tail.npz"))
+    args = (g["scores"], g["labels"], g["boxes"], g["counts"], g["scales"])
+    for tag, thr, valid in (("coco_t005", 0.05, None), ("coco_t030", 0.3, None), ("k7_t005_all", 0.05, None),
+                            ("k7_t030_valid", 0.3, [int(v) for v in g["k7_valid"]])):
+        rows = R.eval_rows_coco(*args, g["image_ids"], g["category_of_label"], threshold=thr, valid_class_id=valid)
+        assert rows.shape == g[tag].shape, tag
+        assert np.array_equal(rows, g[tag]), tag          # float32 values carried in float64: exact
+    nc = len(g["category_of_label"])
+    for tag, thr, md in (("csv_t005_m100", 0.05, 100), ("csv_t030_m10", 0.3, 10)):
+        rows, offs = R.eval_rows_csv(*args, nc, score_threshold=thr, max_detections=md)
+        assert np.array_equal(offs, g[tag + "_class_offsets"]), tag
+        assert np.array_equal(rows, g[tag]), tag
