@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 5
+#define K7_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -231,6 +231,13 @@ K7_API int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B
 K7_API size_t k7_nms_workspace_bytes(int n);
 K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
            int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------- annotation packing
+ * collater's annotation half (datasettool/dataloader.py:678-686): rows [N,5] of all images back
+ * to back (device), offsets [B+1] int32 (device) -> out [B,M,5], rows beyond an image's count are
+ * -1 in every field.  M = max(max_b n_b, 1) as the reference (:676, :688); an image with more than
+ * M rows is truncated.  One launch; the host sends one ragged block instead of padding in Python. */
+K7_API int k7_annotations_pad(const float* rows, const int32_t* offsets, int B, int M, float* out, void* stream);
 
 /* ---------------------------------------------------------------- evaluator tails on device
  * What the reference's evaluators do on the host with every image's (scores, labels, boxes)

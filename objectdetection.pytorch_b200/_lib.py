@@ -89,7 +89,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 5                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 6                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -125,6 +125,7 @@ SYMBOLS = {
                                    _P, _P, _P, _P, _P, _P]),
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_annotations_pad": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     "k7_eval_pack_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "k7_eval_pack": (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_int, _P, _P, _P, _P, C.POINTER(K7EvalParams),
                                _P, _P, _P, _P, C.c_size_t, _P]),

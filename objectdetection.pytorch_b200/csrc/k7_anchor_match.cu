@@ -328,3 +328,27 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
+
+// ------------------------------------------------------------------ ragged annotations -> [B,M,5]
+// datasettool/dataloader.py:678-686 pads every image's annotation rows to the batch maximum with -1
+// in a Python loop on the host.  Here the batch travels as one ragged block (rows [N,5] + offsets
+// [B+1]) and the padded tensor the hot path expects is written on the device.
+__global__ void __launch_bounds__(256)
+k7_annotations_pad_kernel(const float* __restrict__ rows, const int32_t* __restrict__ offsets, int M,
+                          float* __restrict__ out) {
+    const int b = blockIdx.y;
+    const int lo = offsets[b], n = offsets[b + 1] - lo;
+    const int e = blockIdx.x * 256 + threadIdx.x;   // element of the image's [M,5] block
+    if (e >= M * 5) return;
+    const int m = e / 5;
+    out[(size_t)b * M * 5 + e] = (m < n) ? __ldg(rows + (size_t)lo * 5 + e) : -1.0f;
+}
+
+extern "C" int k7_annotations_pad(const float* rows, const int32_t* offsets, int B, int M, float* out, void* stream) {
+    K7_REQUIRE(offsets && out, "k7_annotations_pad: null argument");
+    K7_REQUIRE(B > 0 && M > 0 && B <= 65535 && M < (1 << 27), "k7_annotations_pad: bad shape B=%d M=%d", B, M);
+    dim3 grid((M * 5 + 255) / 256, B);
+    k7_annotations_pad_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(rows, offsets, M, out);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}

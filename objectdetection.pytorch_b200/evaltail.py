@@ -1,4 +1,5 @@
-"""Evaluator tails on device.
+"""The two data formats either side of the hot path: evaluator tails on
+device, and the collater's annotation padding.
 
 The reference's evaluators copy every image's (scores, labels, boxes) to the host and loop over the
 detections in Python (datasettool/coco_eval.py:25-57, ksevendata_eval.py:24-61, csv_eval.py:93-121).
@@ -108,3 +109,37 @@ def csv_all_detections(packed: PackedDetections) -> List[List[np.ndarray]]:
     off = packed.class_offsets.cpu().numpy()
     nc = packed.num_classes
     return [[r[off[b * nc + c]:off[b * nc + c + 1], 1:6].copy() for c in range(nc)] for b in range(packed.batch)]
+
+
+# ------------------------------------------------------------------ annotation packing
+def collate_annotations(annots, device, *, return_ragged: bool = False):
+    """The annotation half of the reference's collater (datasettool/dataloader.py:672-688): a list of
+    per-image [n_i,5] arrays/tensors -> annot_padded [B, max(max n_i, 1), 5] float32 with -1 rows, on `device`.
+    The batch crosses PCIe once as a pinned ragged block (rows + offsets); the padding is written on the
+    device (k7_annotations_pad) instead of in a Python loop over a host tensor."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("b200det operators run on CUDA tensors only (there is no CPU path)")
+    B = len(annots)
+    if B == 0:
+        raise ValueError("empty batch")
+    arrs = [np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a, dtype=np.float32).reshape(-1, 5) for a in annots]
+    counts = np.array([a.shape[0] for a in arrs], dtype=np.int64)
+    offsets = np.zeros(B + 1, dtype=np.int32)
+    offsets[1:] = np.cumsum(counts)
+    N, M = int(offsets[-1]), max(int(counts.max()), 1)
+    # one pinned block: [offsets as int32 | rows as float32]
+    block = torch.empty(B + 1 + 5 * max(N, 1), dtype=torch.int32).pin_memory()
+    block[:B + 1] = torch.from_numpy(offsets)
+    if N:
+        block[B + 1:B + 1 + 5 * N] = torch.from_numpy(np.concatenate(arrs, axis=0).reshape(-1)).view(torch.int32)
+    d_block = block.to(dev, non_blocking=True)
+    d_off = d_block[:B + 1]
+    d_rows = d_block[B + 1:].view(torch.float32)
+    out = torch.empty((B, M, 5), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        L.check(L.lib().k7_annotations_pad(L.ptr(d_rows), L.ptr(d_off), B, M, L.ptr(out), L.stream_ptr(dev)),
+                "k7_annotations_pad")
+    if return_ragged:
+        return out, d_rows[:5 * N].view(-1, 5), d_off
+    return out

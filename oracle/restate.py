@@ -489,3 +489,18 @@ def eval_rows_csv(scores, labels, boxes, counts, scales, num_classes: int, score
                 rows.append([float(b), *[float(v) for v in bx[i]], float(sc[i]), float(c)])
             offs.append(len(rows))
     return np.array(rows, np.float64).reshape(-1, 7), np.array(offs, np.int32)
+
+
+# ------------------------------------------------------------------ collater, annotation half
+def collate_annotations(annots) -> torch.Tensor:
+    """datasettool/dataloader.py:672-688: pad every image's [n_i,5] rows to the batch maximum with -1;
+    a batch without any annotation gives [B,1,5] of -1."""
+    annots = [torch.as_tensor(np.asarray(a, dtype=np.float32)).reshape(-1, 5) for a in annots]
+    max_num = max(a.shape[0] for a in annots)
+    if max_num > 0:
+        out = torch.ones((len(annots), max_num, 5)) * -1
+        for i, a in enumerate(annots):
+            if a.shape[0] > 0:
+                out[i, :a.shape[0], :] = a
+        return out
+    return torch.ones((len(annots), 1, 5)) * -1

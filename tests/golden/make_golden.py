@@ -16,6 +16,7 @@ and writes
   tests/golden/detect_*.npz        inputs, decoded+clipped boxes, per-image keep / scores / labels / boxes
   tests/golden/head_retina.npz     per-level NCHW logits of the reference's ClassificationModel (captured in
                                    front of its output_act) and the [B,A,C] probabilities it returns
+  tests/golden/collate.npz         per-image annotation rows and the padded block the reference's collater makes of them
   tests/golden/eval_tail.npz       detections of 6 images and what datasettool/{coco_eval,ksevendata_eval,csv_eval}.py
                                    make of them (result rows / per-class detection arrays)
 The reference's hidden intermediates (IoU_max, IoU_argmax, masks) are obtained by
@@ -390,6 +391,29 @@ def gen_eval_tail():
     np.savez_compressed(os.path.join(HERE, "eval_tail.npz"), **rec)
     print("eval_tail", {k: v.shape for k, v in rec.items() if k.startswith(("coco", "k7_t", "csv"))})
 
+def gen_collate():
+    """datasettool/dataloader.py:655-691 (collater): the annotation block it hands to FocalLoss.  skimage and
+    pycocotools are absent here and irrelevant to collater; empty stand-ins let the module import."""
+    import types
+    for name in ("skimage", "skimage.io", "skimage.transform", "skimage.color", "pycocotools", "pycocotools.coco"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    if not hasattr(sys.modules["pycocotools.coco"], "COCO"):
+        sys.modules["pycocotools.coco"].COCO = object
+    from datasettool.dataloader import collater
+    rng = np.random.RandomState(20260414)
+    rec = {}
+    for tag, counts in (("mixed", [3, 0, 7, 1, 0, 5]), ("all_empty", [0, 0, 0]), ("single", [4])):
+        data = []
+        for i, n in enumerate(counts):
+            a = np.concatenate([rng.uniform(0, 300, size=(n, 4)), rng.randint(0, 9, size=(n, 1))], axis=1).astype(np.float32)
+            data.append({"img": torch.zeros(8 + i, 6 + i, 3), "annot": torch.from_numpy(a), "scale": 1.0})
+            rec[f"{tag}_rows{i}"] = a
+        out = collater(data)
+        rec[f"{tag}_padded"] = out["annot"].numpy()
+        rec[f"{tag}_n"] = np.array(len(counts))
+    np.savez_compressed(os.path.join(HERE, "collate.npz"), **rec)
+    print("collate", {k: v.shape for k, v in rec.items() if k.endswith("_padded")})
+
 
 if __name__ == "__main__":
     gen_anchors()
@@ -397,3 +421,4 @@ if __name__ == "__main__":
     gen_detect()
     gen_head()
     gen_eval_tail()
+    gen_collate()

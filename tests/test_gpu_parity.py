@@ -772,3 +772,26 @@ def test_eval_pack_rejects_bad_arguments():
         b200det.eval_pack(det, g["scales"])
     with pytest.raises(ValueError):
         b200det.eval_pack(det, g["scales"], mode="csv", num_classes=10000)
+
+
+# ------------------------------------------------------------------ annotation packing
+def test_collate_annotations_fixture_and_random():
+    """collate_annotations (ragged block + k7_annotations_pad) == the reference collater's annot_padded
+    (collate.npz) and == the oracle on random ragged batches; the ragged views round-trip."""
+    g = np.load(os.path.join(GOLDEN, "collate.npz"))
+    for tag in ("mixed", "all_empty", "single"):
+        rows = [g[f"{tag}_rows{i}"] for i in range(int(g[f"{tag}_n"]))]
+        out = b200det.collate_annotations(rows, DEV)
+        assert out.dtype == torch.float32 and tuple(out.shape) == g[f"{tag}_padded"].shape, tag
+        assert np.array_equal(out.cpu().numpy(), g[f"{tag}_padded"]), tag
+    rng = np.random.RandomState(3)
+    for B, nmax in ((1, 1), (17, 130), (256, 40)):
+        rows = [np.concatenate([rng.uniform(0, 900, (n, 4)), rng.randint(0, 90, (n, 1))], axis=1).astype(np.float32)
+                for n in rng.randint(0, nmax + 1, size=B)]
+        out, ragged, off = b200det.collate_annotations([torch.from_numpy(r) for r in rows], DEV, return_ragged=True)
+        assert np.array_equal(out.cpu().numpy(), R.collate_annotations(rows).numpy())
+        assert off.cpu().tolist() == np.concatenate([[0], np.cumsum([len(r) for r in rows])]).tolist()
+        if ragged.numel():
+            assert np.array_equal(ragged.cpu().numpy(), np.concatenate(rows, axis=0))
+    with pytest.raises(RuntimeError):
+        b200det.collate_annotations(rows, "cpu")

@@ -143,3 +143,13 @@ def test_evaluator_tails_match_reference():
         rows, offs = R.eval_rows_csv(*args, nc, score_threshold=thr, max_detections=md)
         assert np.array_equal(offs, g[tag + "_class_offsets"]), tag
         assert np.array_equal(rows, g[tag]), tag
+
+
+def test_collate_annotations_matches_reference():
+    """oracle collate_annotations == annot_padded of the reference's collater (collate.npz)."""
+    g = np.load(os.path.join(GOLDEN, "collate.npz"))
+    for tag in ("mixed", "all_empty", "single"):
+        rows = [g[f"{tag}_rows{i}"] for i in range(int(g[f"{tag}_n"]))]
+        out = R.collate_annotations(rows).numpy()
+        assert out.shape == g[f"{tag}_padded"].shape, tag
+        assert np.array_equal(out, g[f"{tag}_padded"]), tag
