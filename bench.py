@@ -49,6 +49,9 @@ def parse():
     ap.add_argument("--shard", action="store_true",
                     help="strong scaling: split the workload's batch over the ranks (BASELINE configs[3], [4]) "
                          "instead of one full batch per rank")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "nccl"],
+                    help="N>1: how the four loss sums are combined: fused into k7_loss over peer memory (auto; "
+                         "falls back to NCCL if the mailboxes cannot be mapped) or NCCL all_reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -241,7 +244,8 @@ def run_b200(args, wl):
     cls, reg, ann = b200det.synth.make_inputs(wl, seed=rank, device=dev, batch=B)
     img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
     anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
-    loss_mod = b200det.FocalLoss(sharded=world > 1)
+    peer = "auto" if args.exchange == "auto" else False
+    loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer)
     cls_g = cls.detach().requires_grad_(True)
     reg_g = reg.detach().requires_grad_(True)
 
@@ -296,6 +300,13 @@ def run_b200(args, wl):
                               "k7_detect(score+sort+mask+resolve+fallback)": 5, "k7_detect_gather": 1},
     }
 
+    if world > 1:
+        ex = loss_mod.exchange
+        out["config"]["loss_exchange"] = ex
+        out["config"]["parallelism"] = (f"image-sharded x{world}; the four loss sums are exchanged " +
+                                        ("inside k7_loss over NVLink peer memory (no collective launch)" if ex == "p2p-fused"
+                                         else "with one 16-byte NCCL all-reduce per step"))
+
     # ---- parts and the roofline of the dominant kernel (every rank runs them; rank 0 reports)
     k = max(args.steps, 10)
     with torch.no_grad():
@@ -331,7 +342,7 @@ def run_b200(args, wl):
     # stock elementwise sigmoid pass (and its autograd backward) that they make unnecessary
     z = torch.logit(cls)
     z_g = z.detach().requires_grad_(True)
-    loss_lg = b200det.FocalLoss(sharded=world > 1, from_logits=True)
+    loss_lg = b200det.FocalLoss(sharded=world > 1, from_logits=True, peer_reduce=peer)
 
     def train_side_logits():
         z_g.grad = None

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 6
+#define K7_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -120,6 +120,33 @@ K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_orde
              int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, float* zero_fill4,
              uint32_t* ignore_bits, void* stream);
 
+/* Multi-GPU: the path's one exchange - the four batch sums {sum cls_i, sum reg_i, sum num_pos_i, B}
+ * of every rank - fused into k7_loss.  mailbox[p] is a device pointer, valid in THIS process, to
+ * rank p's mailbox (peer memory over NVLink: cudaIpcOpenMemHandle / cuMem import; mailbox[rank] is
+ * the local one): 2 * world slots of 8 floats, zero-initialised before the first call.  The last
+ * block of the row kernel posts this rank's sums into every mailbox and adds the world posts it
+ * receives in rank order, so `sums` holds the GLOBAL sums, bit-identical on every rank, with no
+ * separate all-reduce launch.  seq counts the calls (1, 2, ...) and must be the same on every rank.
+ * A peer that does not post within timeout_ms (default 10 000) gives NaN sums, never a hang. */
+#define K7_MAX_PEERS 16
+typedef struct K7PeerReduce {
+    int32_t world, rank;
+    uint32_t seq;
+    int32_t timeout_ms;
+    float* mailbox[K7_MAX_PEERS];
+} K7PeerReduce;
+#define K7_PEER_MAILBOX_FLOATS(world) (2 * (world) * 8)
+#define K7_IPC_HANDLE_BYTES 64
+
+/* Mailbox plumbing (CUDA IPC; one process per GPU on one node).  create: a zeroed mailbox on the
+ * current device + its 64-byte handle, which the host sends to the other ranks by any transport;
+ * open: maps a peer's mailbox into this process and enables peer access from the current device;
+ * close / destroy undo open / create.  Not stream-ordered: set-up time only. */
+K7_API int k7_peer_mailbox_create(int world, float** mailbox, unsigned char* handle /* [K7_IPC_HANDLE_BYTES] */);
+K7_API int k7_peer_mailbox_open(const unsigned char* handle, float** mailbox);
+K7_API int k7_peer_mailbox_close(float* mailbox);
+K7_API int k7_peer_mailbox_destroy(float* mailbox);
+
 typedef struct K7LossParams {
     float alpha;            /* 0.25 (losses.py:31) ; gamma is fixed at 2 (losses.py:32, pow == x*x) */
     float beta;             /* smooth-L1 switch 1/9 (losses.py:157-159) */
@@ -131,6 +158,7 @@ typedef struct K7LossParams {
                              * head's pre-sigmoid logits (output_act of retinanet.py:140,159 / header_act of
                              * simple_head.py:310 removed): the sigmoid is fused into the stream and dcls is
                              * d(loss)/d(logit).  SURVEY 8(f) row 1. */
+    const K7PeerReduce* peer_reduce; /* NULL: `sums` are this rank's own; else see K7PeerReduce */
 } K7LossParams;
 
 K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);

@@ -14,3 +14,4 @@ from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, 
 from .evaltail import (PackedDetections, eval_pack, coco_results, csv_all_detections,  # noqa: F401
                        collate_annotations)
 from . import synth                                          # noqa: F401
+from . import distributed                                    # noqa: F401

@@ -44,6 +44,19 @@ class K7MatchParams(C.Structure):
     _fields_ = [("neg_thr", C.c_float), ("pos_thr", C.c_float)]
 
 
+K7_MAX_PEERS = 16
+
+
+class K7PeerReduce(C.Structure):
+    _fields_ = [
+        ("world", C.c_int32),
+        ("rank", C.c_int32),
+        ("seq", C.c_uint32),
+        ("timeout_ms", C.c_int32),
+        ("mailbox", C.c_void_p * K7_MAX_PEERS),
+    ]
+
+
 class K7LossParams(C.Structure):
     _fields_ = [
         ("alpha", C.c_float),
@@ -53,6 +66,7 @@ class K7LossParams(C.Structure):
         ("mean_divisor", C.c_int32),
         ("dreg_prezeroed", C.c_int32),
         ("from_logits", C.c_int32),
+        ("peer_reduce", C.POINTER(K7PeerReduce)),
     ]
 
 
@@ -89,7 +103,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 6                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 7                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -125,6 +139,10 @@ SYMBOLS = {
                                    _P, _P, _P, _P, _P, _P]),
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_peer_mailbox_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), _P]),
+    "k7_peer_mailbox_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),
+    "k7_peer_mailbox_close": (C.c_int, [_P]),
+    "k7_peer_mailbox_destroy": (C.c_int, [_P]),
     "k7_annotations_pad": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     "k7_eval_pack_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "k7_eval_pack": (C.c_int, [_P, _P, _P, C.c_int, _P, C.c_int, C.c_int, _P, _P, _P, _P, C.POINTER(K7EvalParams),

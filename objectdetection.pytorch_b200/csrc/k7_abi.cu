@@ -46,3 +46,50 @@ int k7_check_spec(const K7AnchorSpec* s, int A) {
     return K7_OK;
 }
 
+
+// ------------------------------------------------------------------ peer mailboxes (K7PeerReduce)
+// The NVLink plumbing of the fused loss-sum exchange: a mailbox is its own cudaMalloc allocation on
+// the caller's current device so that it can be exported with the CUDA IPC API; the host exchanges
+// the 64-byte handles with whatever transport it has (torch.distributed in b200det) and opens the
+// peers' handles, which also enables peer access from the current device.
+static_assert(sizeof(cudaIpcMemHandle_t) == K7_IPC_HANDLE_BYTES, "K7_IPC_HANDLE_BYTES");
+
+extern "C" int k7_peer_mailbox_create(int world, float** mailbox, unsigned char* handle) {
+    K7_REQUIRE(mailbox && handle, "k7_peer_mailbox_create: null argument");
+    K7_REQUIRE(world >= 1 && world <= K7_MAX_PEERS, "k7_peer_mailbox_create: world=%d out of range", world);
+    void* p = nullptr;
+    const size_t bytes = sizeof(float) * K7_PEER_MAILBOX_FLOATS(world);
+    K7_CUDA(cudaMalloc(&p, bytes));
+    cudaError_t e = cudaMemset(p, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        k7_set_error("k7_peer_mailbox_create: %s", cudaGetErrorString(e));
+        return K7_ECUDA;
+    }
+    memcpy(handle, &h, sizeof(h));
+    *mailbox = static_cast<float*>(p);
+    return K7_OK;
+}
+
+extern "C" int k7_peer_mailbox_open(const unsigned char* handle, float** mailbox) {
+    K7_REQUIRE(mailbox && handle, "k7_peer_mailbox_open: null argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    K7_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *mailbox = static_cast<float*>(p);
+    return K7_OK;
+}
+
+extern "C" int k7_peer_mailbox_close(float* mailbox) {
+    if (mailbox) K7_CUDA(cudaIpcCloseMemHandle(mailbox));
+    return K7_OK;
+}
+
+extern "C" int k7_peer_mailbox_destroy(float* mailbox) {
+    if (mailbox) K7_CUDA(cudaFree(mailbox));
+    return K7_OK;
+}

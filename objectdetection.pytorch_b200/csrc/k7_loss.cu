@@ -64,6 +64,15 @@ struct K7LossDev {
     int B, A, C, M;
 };
 
+// The batch sums of the OTHER ranks, exchanged by the last block of the row kernel over peer memory
+// (NVLink P2P stores into every rank's mailbox) instead of a separate all-reduce launch.
+struct K7PeerDev {
+    int world, rank;
+    unsigned int seq;                  // call counter (>= 1), the same on every rank
+    unsigned long long timeout_ns;
+    float* mailbox[K7_MAX_PEERS];      // mailbox[p]: rank p's 2 * world slots of 8 floats {v0..v3, seq, -, -, -}
+};
+
 // per-image gradient scales, from the match stage's num_pos:
 //   x: 1 / (max(num_pos,1) * mean_divisor)      (losses.py:118,168)
 //   y: 1 / (4 * num_pos * mean_divisor) or 0    (losses.py:161,168)
@@ -719,7 +728,8 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                     const float* __restrict__ anchors, int box_order,
                     const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
                     const int32_t* __restrict__ assign, const int32_t* __restrict__ num_pos,
-                    const __grid_constant__ K7LossDev P, const float* __restrict__ pipe_partials, uint32_t pipe_slots,
+                    const __grid_constant__ K7LossDev P, const __grid_constant__ K7PeerDev PR,
+                    const float* __restrict__ pipe_partials, uint32_t pipe_slots,
                     float2* __restrict__ rows_partials, unsigned int* __restrict__ counters /* [B] images, [B] = batch */,
                     float* __restrict__ per_image, float* __restrict__ sums, float* __restrict__ dcls,
                     float4* __restrict__ dreg) {
@@ -872,12 +882,72 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
     }
     k7_block_sum2_f64(c, r, s_red);
     k7_block_sum2_f64(nn, zero, s_red);
+    __shared__ float4 s_mine, s_got[K7_MAX_PEERS];
     if (threadIdx.x == 0) {
-        sums[0] = (float)c;
-        sums[1] = (float)r;
-        sums[2] = (float)nn;
-        sums[3] = (float)P.B;
+        s_mine = make_float4((float)c, (float)r, (float)nn, (float)P.B);
         counters[P.B] = 0u;
+        if (PR.world <= 1) {
+            sums[0] = s_mine.x;
+            sums[1] = s_mine.y;
+            sums[2] = s_mine.z;
+            sums[3] = s_mine.w;
+        }
+    }
+    if (PR.world <= 1) return;
+
+    // ---- the path's only exchange, fused: thread p posts this rank's sums into rank p's mailbox
+    // (16-byte store, system fence, then the sequence word with release semantics) and waits for rank
+    // p's post in its own mailbox.  Two slot sets alternate by call parity: a rank can only be one
+    // call ahead of a peer (it needs the peer's post to finish a call), so a slot is never overwritten
+    // before it was read.  Every rank adds the W posts in rank order: identical bits everywhere.
+    __syncthreads();
+    const int W = PR.world;
+    if ((int)threadIdx.x < W) {
+        const int p = threadIdx.x;
+        const unsigned par = PR.seq & 1u;
+        float* dst = PR.mailbox[p] + (size_t)(par * W + PR.rank) * 8;
+        const float4 mine = s_mine;
+        asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(mine.x), "f"(mine.y), "f"(mine.z),
+                     "f"(mine.w)
+                     : "memory");
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst + 4), "r"(PR.seq) : "memory");
+        const float* src = PR.mailbox[PR.rank] + (size_t)(par * W + p) * 8;
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        unsigned int got = 0u;
+        bool ok = false;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(src + 4) : "memory");
+            if (got == PR.seq) {
+                ok = true;
+                break;
+            }
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > PR.timeout_ns) break;   // a missing peer must not hang the GPU: NaN sums instead
+            __nanosleep(64);
+        }
+        float4 v;
+        asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "l"(src)
+                     : "memory");
+        const float nanv = __int_as_float(0x7fc00000);
+        s_got[p] = ok ? v : make_float4(nanv, nanv, nanv, nanv);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float4 a = s_got[0];
+        for (int p = 1; p < W; ++p) {
+            a.x += s_got[p].x;
+            a.y += s_got[p].y;
+            a.z += s_got[p].z;
+            a.w += s_got[p].w;
+        }
+        sums[0] = a.x;
+        sums[1] = a.y;
+        sums[2] = a.z;
+        sums[3] = a.w;
     }
 }
 
@@ -1170,13 +1240,30 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         K7_LAUNCH_CHECK();
     }
 
+    K7PeerDev PR;
+    memset(&PR, 0, sizeof(PR));
+    PR.world = 1;
+    if (params->peer_reduce && params->peer_reduce->world > 1) {
+        const K7PeerReduce* q = params->peer_reduce;
+        K7_REQUIRE(q->world <= K7_MAX_PEERS && q->rank >= 0 && q->rank < q->world && q->seq >= 1u,
+                   "k7_loss: bad peer_reduce (world=%d rank=%d seq=%u)", q->world, q->rank, q->seq);
+        PR.world = q->world;
+        PR.rank = q->rank;
+        PR.seq = q->seq;
+        PR.timeout_ns = (unsigned long long)(q->timeout_ms > 0 ? q->timeout_ms : 10000) * 1000000ull;
+        for (int i = 0; i < q->world; ++i) {
+            K7_REQUIRE(q->mailbox[i] && (reinterpret_cast<uintptr_t>(q->mailbox[i]) & 31) == 0,
+                       "k7_loss: peer_reduce mailbox %d is null or not 32-byte aligned", i);
+            PR.mailbox[i] = q->mailbox[i];
+        }
+    }
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     float4* dreg4 = reinterpret_cast<float4*>(dreg);
     dim3 rgrid(L.gx, B);
 #define K7_ROWS_LAUNCH(GR, SP, LV)                                                                                       \
     k7_loss_rows_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
-                                                                       assign, num_pos, P, cta_partials, L.cta_stride,   \
+                                                                       assign, num_pos, P, PR, cta_partials, L.cta_stride, \
                                                                        rows_partials, counters, per_image, sums, dcls,   \
                                                                        dreg4)
     if (lv) { if (grad) K7_ROWS_LAUNCH(true, true, true); else K7_ROWS_LAUNCH(false, true, true); }

@@ -40,3 +40,85 @@ def sharded_focal_loss(classifications, regressions, anchors, annotations, group
     """FocalLoss over a batch whose dim 0 is already this rank's shard."""
     from .losses import FocalLoss
     return FocalLoss(process_group=group, sharded=True, **loss_kwargs)(classifications, regressions, anchors, annotations)
+
+
+class PeerMailbox:
+    """Peer-mapped mailboxes for the exchange fused into k7_loss (include/k7det.h: K7PeerReduce).
+
+    Every rank owns a zeroed mailbox of 2*world slots on its GPU (its own cudaMalloc allocation, so
+    that it can be exported with the CUDA IPC API), the 64-byte handles travel once through
+    torch.distributed (all_gather_object: plumbing), and every rank maps the others' mailboxes over
+    NVLink.  After that a training step needs no collective launch: the last block of the loss row
+    kernel posts the four batch sums into every mailbox and adds what it receives in rank order.
+    One process per GPU on ONE node; raises RuntimeError when the IPC mapping is not possible (the
+    caller then keeps the NCCL all-reduce)."""
+
+    def __init__(self, group=None, device=None, timeout_ms: int = 10000):
+        import ctypes as C
+        from . import _lib as L
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("PeerMailbox needs an initialised torch.distributed process group")
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world > L.K7_MAX_PEERS:
+            raise RuntimeError(f"PeerMailbox supports up to {L.K7_MAX_PEERS} ranks")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.timeout_ms = int(timeout_ms)
+        self.seq = 0
+        self._lib = L.lib()
+        self._local = C.c_void_p()
+        self._opened = []
+        handle = (C.c_ubyte * 64)()
+        err = None
+        with torch.cuda.device(self.device):
+            try:
+                L.check(self._lib.k7_peer_mailbox_create(self.world, C.byref(self._local), handle), "k7_peer_mailbox_create")
+            except RuntimeError as e:                      # still take part in the collectives below
+                err = str(e)
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, (self.rank, bytes(handle), err), group=group)
+            self._ptrs = [None] * self.world
+            if all(g[2] is None for g in gathered):
+                for r, hb, _ in gathered:
+                    if r == self.rank:
+                        self._ptrs[r] = self._local.value
+                        continue
+                    p = C.c_void_p()
+                    try:
+                        L.check(self._lib.k7_peer_mailbox_open((C.c_ubyte * 64).from_buffer_copy(hb), C.byref(p)),
+                                "k7_peer_mailbox_open")
+                        self._opened.append(p)
+                        self._ptrs[r] = p.value
+                    except RuntimeError as e:
+                        err = str(e)
+                        break
+            else:
+                err = next(g[2] for g in gathered if g[2] is not None)
+            # everybody must agree before the first post
+            flags = [None] * self.world
+            dist.all_gather_object(flags, err, group=group)
+        bad = next((f for f in flags if f is not None), None)
+        if bad is not None:
+            self.close()
+            raise RuntimeError("peer mailboxes unavailable: " + bad)
+        self._struct = L.K7PeerReduce()
+        self._struct.world, self._struct.rank, self._struct.timeout_ms = self.world, self.rank, self.timeout_ms
+        for r in range(self.world):
+            self._struct.mailbox[r] = self._ptrs[r]
+
+    def next(self):
+        """The K7PeerReduce of the next k7_loss call (the call counter advances on every rank alike)."""
+        self.seq += 1
+        self._struct.seq = self.seq
+        return self._struct
+
+    def close(self):
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            for p in self._opened:
+                self._lib.k7_peer_mailbox_close(p)
+            self._opened = []
+            if self._local:
+                self._lib.k7_peer_mailbox_destroy(self._local)
+                self._local = None

@@ -85,7 +85,7 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
 
 def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
                mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
-               ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False):
+               ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False, peer_reduce=None):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
     dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a 16 B/anchor store);
     ignore_bits: match(with_bits=True)'s bitmap (derived from `assign` by a small kernel when absent);
@@ -115,6 +115,8 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
         p.target_div[i] = target_div[i]
     p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
     p.from_logits = int(from_logits)
+    if peer_reduce is not None:                # K7PeerReduce: `sums` come back as the GLOBAL sums
+        p.peer_reduce = C.pointer(peer_reduce)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
                             L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits), L.ptr(num_pos),
@@ -136,13 +138,14 @@ class _FocalLossFn(torch.autograd.Function):
         if group is not None or cfg.get("sharded"):
             import torch.distributed as dist
             world = dist.get_world_size(group)
+        peer = cfg["peer"]() if world > 1 and cfg.get("peer") else None   # fused exchange over peer memory, or None
         B = cls.shape[0]
         per_image, sums, dcls, dreg = loss_stage(
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
             want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0, ignore_bits=bits,
-            from_logits=cfg.get("from_logits", False))
-        if world > 1:
+            from_logits=cfg.get("from_logits", False), peer_reduce=peer.next() if peer is not None else None)
+        if world > 1 and peer is None:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective
         out = sums[:2] / sums[3]                   # mean over (global) images, losses.py:168
@@ -175,7 +178,7 @@ class _FocalLossFn(torch.autograd.Function):
 
 def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets, mean_divisor,
                       want_grad, dreg_zeroed: Optional[torch.Tensor] = None, ignore_bits: Optional[torch.Tensor] = None,
-                      from_logits: bool = False):
+                      from_logits: bool = False, peer_reduce=None):
     """loss_stage on the head's raw per-level NCHW outputs (k7_loss_levels).  Returns
     (per_image[B,2], sums[4], dlevels|None (list, same layouts as `levels`), dreg|None)."""
     B, Cn = L.check_levels(levels, spec)
@@ -196,6 +199,8 @@ def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, t
         p.target_div[i] = target_div[i]
     p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
     p.from_logits = int(from_logits)
+    if peer_reduce is not None:                # K7PeerReduce: `sums` come back as the GLOBAL sums
+        p.peer_reduce = C.pointer(peer_reduce)
     lv, dlv = L.ptr_array(levels), L.ptr_array(dlevels)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss_levels(C.byref(spec), lv, L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits),
@@ -219,12 +224,14 @@ class _FocalLossLevelsFn(torch.autograd.Function):
         if group is not None or cfg.get("sharded"):
             import torch.distributed as dist
             world = dist.get_world_size(group)
+        peer = cfg["peer"]() if world > 1 and cfg.get("peer") else None
         B = reg.shape[0]
         per_image, sums, dlevels, dreg = loss_stage_levels(
             spec, list(levels), reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world, want_grad=want_grad,
-            dreg_zeroed=dreg0, ignore_bits=bits, from_logits=cfg.get("from_logits", False))
-        if world > 1:
+            dreg_zeroed=dreg0, ignore_bits=bits, from_logits=cfg.get("from_logits", False),
+            peer_reduce=peer.next() if peer is not None else None)
+        if world > 1 and peer is None:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
         out = sums[:2] / sums[3]
@@ -263,6 +270,8 @@ class FocalLoss(nn.Module):
     reference hard-codes; defaults are architectures/losses.py's (0.35/0.45, alpha .25,
     smooth-L1 beta 1/9, targets / [.1,.1,.2,.2], xyxy anchors).  ``FocalLoss.efficientdet()``
     gives architectures/loss_efficientdet.py's (0.4/0.5, yx anchors, unscaled (dy,dx,dh,dw)).
+    ``sharded=True`` / ``process_group=``: one process per GPU, dim 0 is this rank's shard; the four batch
+    sums are exchanged inside k7_loss over NVLink peer memory (``peer_reduce``), gradients need no collective.
     ``from_logits=True``: `classifications` are the head's PRE-sigmoid logits (drop
     ``output_act`` of retinanet.py:140 / ``header_act`` of simple_head.py:310, see
     ``b200det.strip_head_sigmoid``); the sigmoid is fused into the streaming kernel and the gradient
@@ -271,7 +280,7 @@ class FocalLoss(nn.Module):
     def __init__(self, neg_thr: float = 0.35, pos_thr: float = 0.45, alpha: float = 0.25,
                  gamma: float = 2.0, beta: float = 1.0 / 9.0, target_std=(0.1, 0.1, 0.2, 0.2),
                  box_order: str = "xyxy", yx_targets: bool = False, process_group=None,
-                 sharded: bool = False, from_logits: bool = False):
+                 sharded: bool = False, from_logits: bool = False, peer_reduce="auto"):
         super().__init__()
         if gamma != 2.0:
             raise ValueError("only gamma == 2 (the reference's constant, losses.py:32) is implemented")
@@ -282,8 +291,30 @@ class FocalLoss(nn.Module):
                         box_order=L.BOX_XYXY if box_order == "xyxy" else L.BOX_YXYX,
                         yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded),
                         from_logits=bool(from_logits))
+        # sharded: the exchange of the four batch sums.  "auto"/True: fused into k7_loss over peer-mapped
+        # mailboxes (distributed.PeerMailbox), set up at the first call; "auto" keeps NCCL's all_reduce when
+        # the mailboxes cannot be mapped (True raises); False: always all_reduce.
+        self.peer_reduce = peer_reduce
+        self._peer = None
+        self.cfg["peer"] = self._peer_mailbox if peer_reduce in ("auto", True) else None
         self.last_num_positives = None      # [B] int32 device tensor of the last call (for logging)
         self.last_per_image = None          # [B,2] (cls_i, reg_i)
+
+    def _peer_mailbox(self):
+        if self._peer is None:
+            from .distributed import PeerMailbox
+            try:
+                self._peer = PeerMailbox(self.cfg.get("process_group"))
+            except RuntimeError:
+                if self.peer_reduce is True:
+                    raise
+                self._peer = False           # keep the NCCL all-reduce
+        return self._peer or None
+
+    @property
+    def exchange(self) -> str:
+        """How the batch sums of the last sharded call were combined."""
+        return "p2p-fused" if self._peer else ("nccl-allreduce" if self._peer is False or not self.cfg["peer"] else "unset")
 
     @classmethod
     def efficientdet(cls, **kw):

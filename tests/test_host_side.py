@@ -56,7 +56,7 @@ def test_spec_reproduces_reference_anchors(name):
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "k7det.h")).read()
-    declared = set(re.findall(r"K7_API\s+[\w\s\*]+?\b(k7_\w+)\s*\(", hdr))
+    declared = set(re.findall(r"^K7_API\s+[\w\s\*]+?\b(k7_\w+)\s*\(", hdr, flags=re.M))
     assert declared == set(L.SYMBOLS), declared ^ set(L.SYMBOLS)
     lib = C.CDLL(L.LIB_PATH)
     for name in declared:
@@ -70,14 +70,14 @@ def test_struct_layout_matches_header(tmp_path):
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     src = tmp_path / "sizes.c"
-    src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %d\\n",'
+    src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %d\\n",'
                    'sizeof(K7AnchorSpec),sizeof(K7MatchParams),sizeof(K7LossParams),sizeof(K7DecodeParams),'
-                   'sizeof(K7DetectParams),sizeof(K7EvalParams),K7_ABI_VERSION);return 0;}\n')
+                   'sizeof(K7DetectParams),sizeof(K7EvalParams),sizeof(K7PeerReduce),K7_ABI_VERSION);return 0;}\n')
     exe = tmp_path / "sizes"
     subprocess.run(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(L.K7AnchorSpec), C.sizeof(L.K7MatchParams), C.sizeof(L.K7LossParams), C.sizeof(L.K7DecodeParams),
-            C.sizeof(L.K7DetectParams), C.sizeof(L.K7EvalParams), L.ABI_VERSION]
+            C.sizeof(L.K7DetectParams), C.sizeof(L.K7EvalParams), C.sizeof(L.K7PeerReduce), L.ABI_VERSION]
     assert got == want
 
 
