@@ -15,8 +15,8 @@ BASELINE.json shape (default: configs[1], EfficientDet-D0 512x512, batch 64, 90 
 `cpu_baseline` = the oracle port (oracle/restate.py, torch-CPU, all host threads) on a
           bounded sample of the same workload (rank 0, N=1 only).
 N > 1 (torchrun): every rank owns a full batch (weak scaling; `--shard` splits the workload's
-batch over the ranks instead: strong scaling, BASELINE configs[3] and [4]); the loss sums are
-combined with one 16-byte NCCL all-reduce per step.
+batch over the ranks instead: strong scaling, BASELINE configs[3] and [4]); the four loss sums are
+exchanged inside k7_loss over NVLink peer memory (`--exchange nccl`: one 16-byte NCCL all-reduce).
 `--impl reference` times the reference's CPU algorithm for the same step (the oracle port;
 the reference is pure Python/PyTorch, there is nothing to compile) and prints the same line.
 """
