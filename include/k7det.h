@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 7
+#define K7_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -225,6 +225,9 @@ typedef struct K7DetectParams {
     int32_t max_detections; /* 0 = off; otherwise stop after this many kept boxes per image */
     int32_t from_logits;    /* 1: cls holds pre-sigmoid logits; scores are 1/(1+expf(-z)) (torch.sigmoid), the
                              * threshold and the arg-max ties are decided on those float32 probabilities */
+    int32_t class_aware;    /* 0: class-agnostic NMS, the reference (retinanet.py:314); 1: a box is suppressed only by
+                             * a higher-scored box of the SAME arg-max class (torchvision.ops.batched_nms with
+                             * idxs = labels, per-class strategy) - SURVEY 8f row 4 */
 } K7DetectParams;
 
 K7_API size_t k7_detect_workspace_bytes(int B, int A, int C);
@@ -259,6 +262,15 @@ K7_API int k7_detect_gather(const void* workspace, size_t workspace_bytes, int B
 K7_API size_t k7_nms_workspace_bytes(int n);
 K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
            int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Per-class NMS for one image (the reference itself is class-agnostic): the result of
+ * torchvision.ops.batched_nms(boxes, scores, idxs, thr) computed per category ("vanilla" strategy,
+ * torchvision/ops/boxes.py _batched_nms_vanilla): box j is suppressed iff a kept box i of the same idxs value
+ * with a higher score (ties: lower index) has IoU(i, j) > thr.  keep[n] int64 indices in descending-score order
+ * (ties: lower index first), count[1] int32.  idxs [n] int64 (values must fit 32 bits).  Same kernels and
+ * workspace as k7_nms: the category test sits after the division-free filter of the bitmask kernel. */
+K7_API int k7_batched_nms(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr,
+                   int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------- annotation packing
  * collater's annotation half (datasettool/dataloader.py:678-686): rows [N,5] of all images back

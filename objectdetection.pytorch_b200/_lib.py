@@ -89,6 +89,7 @@ class K7DetectParams(C.Structure):
         ("pre_nms_topk", C.c_int32),
         ("max_detections", C.c_int32),
         ("from_logits", C.c_int32),
+        ("class_aware", C.c_int32),
     ]
 
 
@@ -103,7 +104,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 7                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 8                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -139,6 +140,7 @@ SYMBOLS = {
                                    _P, _P, _P, _P, _P, _P]),
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_batched_nms": (C.c_int, [_P, _P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
     "k7_peer_mailbox_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), _P]),
     "k7_peer_mailbox_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),
     "k7_peer_mailbox_close": (C.c_int, [_P]),

@@ -105,6 +105,7 @@ struct K7DetectWs {
     int32_t* nsel;          // [B] survivors handled by the multi-SM NMS path (-1: fallback image)
     float4* sbox;           // [B][cap] boxes in spatial order
     int32_t* srank;         // [B][cap] rank (position in score order) of the box at each spatial index
+    int32_t* slabel;        // [B][cap] class of the box at each spatial index (read by the class-aware NMS only)
     float4* blk;            // [B][cap/32][2] (min x1, max x2, min y1, max y2), (min area, max area, -, -) per 32 boxes
     int32_t* work;          // [B] work-item counter of the mask kernel
     unsigned long long* nz; // [B][cap][nzw] which words of a bitmask row were written
@@ -142,6 +143,7 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
     w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * cap));
     w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
+    w.slabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
     w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * (size_t)B * nbw));
     w.work = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B));
     w.nz = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * cap * nzw));
@@ -707,6 +709,8 @@ struct K7NmsSmem {
     float area[K7_NMS_CHUNK];
     float4 kbox[256];
     float karea[256];
+    int klabel[256];
+    int label[K7_NMS_CHUNK];
     unsigned int alive_bits[K7_NMS_CHUNK / 32];
     int kept_rows[K7_NMS_CHUNK];
     int kcount;
@@ -782,25 +786,116 @@ __device__ uint64_t* k7_block_radix_sort(uint64_t* a, uint64_t* b, int n, K7Sort
 // anchor id), result written to `out`.  ~log2(N)^2/2 barrier-separated steps; for the usual few
 // hundred to few thousand survivors per image this replaces six to eight radix passes.
 #define K7_BITONIC_MAX 4096
-// sorts sk[0..N) ascending; N = power of two >= 64, entries beyond the n real keys hold ~0
-__device__ void k7_bitonic_sort_smem(unsigned long long* sk, int N) {
-    const int tid = threadIdx.x;
-    for (int k = 2; k <= N; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = tid; t < (N >> 1); t += K7_NMS_THREADS) {
-                // t-th pair of this step: i has bit j clear
-                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                const int l = i | j;
-                const unsigned long long a = sk[i], b = sk[l];
-                const bool up = (i & k) == 0;
-                if ((a > b) == up) {
-                    sk[i] = b;
-                    sk[l] = a;
-                }
-            }
-            __syncthreads();
+// sorts sk[0..N) ascending; N = power of two >= 64, entries beyond the n real keys hold ~0.
+//
+// Bitonic network (pair (i, i|j), ascending iff (i & k) == 0), run in as few barrier-separated
+// passes as possible (the plain one-stage-per-barrier loop cost 91 barriers at N = 8192 and was
+// half of k7_sort_kernel):
+//   * a warp owns a block of 32*E consecutive keys, E per lane (key m of lane l = block[32m + l],
+//     conflict-free): strides >= 32 inside the block are compare-exchanges between a lane's own
+//     registers, strides < 32 are 64-bit shuffles with lane ^ j.  All phases k <= 32E (the complete
+//     sort of every block) therefore run without a single barrier, and so do the last
+//     log2(32E) stages of every later phase;
+//   * the remaining strides (>= 32E) are taken up to three at a time: a thread loads the 8 keys
+//     base + m*jl, runs the three stages in registers and writes them back.
+// N = 8192: 13 barriers.
+__device__ __forceinline__ void k7_cx(unsigned long long& lo, unsigned long long& hi, bool up) {
+    const unsigned long long a = lo, b = hi;
+    const bool sw = (a > b) == up;
+    lo = sw ? b : a;
+    hi = sw ? a : b;
+}
+// stages jstart, jstart/2, ..., 1 of phase k on one block; i0 = index in sk of this lane's key 0
+template <int E>
+__device__ __forceinline__ void k7_bitonic_block_stages(unsigned long long (&e)[E], int i0, int k, int jstart, int lane) {
+#pragma unroll
+    for (int dm = E / 2; dm >= 1; dm >>= 1) {
+        if (dm * 32 > jstart) continue;
+#pragma unroll
+        for (int m = 0; m < E; ++m)
+            if ((m & dm) == 0) k7_cx(e[m], e[m | dm], ((i0 + 32 * m) & k) == 0);
+    }
+#pragma unroll
+    for (int j = 16; j >= 1; j >>= 1) {
+        if (j > jstart) continue;
+        const bool lower = (lane & j) == 0;
+#pragma unroll
+        for (int m = 0; m < E; ++m) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, e[m], j);
+            const bool up = ((i0 + 32 * m) & k) == 0;
+            const bool take_min = lower == up;
+            e[m] = ((o < e[m]) == take_min) ? o : e[m];
         }
     }
+}
+// stages j0, j0/2, ..., j0 >> (R-1) of phase k through shared memory, all strides >= 64
+template <int R>
+__device__ __forceinline__ void k7_bitonic_strided_pass(unsigned long long* sk, int N, int k, int j0) {
+    const int jl = j0 >> (R - 1);
+    for (int t = threadIdx.x; t < (N >> R); t += K7_NMS_THREADS) {
+        const int low = t & (jl - 1);
+        const int base = ((t - low) << R) | low;
+        unsigned long long e[1 << R];
+#pragma unroll
+        for (int m = 0; m < (1 << R); ++m) e[m] = sk[base + m * jl];
+        const bool up = (base & k) == 0;
+#pragma unroll
+        for (int dm = (1 << R) >> 1; dm >= 1; dm >>= 1) {
+#pragma unroll
+            for (int m = 0; m < (1 << R); ++m)
+                if ((m & dm) == 0) k7_cx(e[m], e[m | dm], up);
+        }
+#pragma unroll
+        for (int m = 0; m < (1 << R); ++m) sk[base + m * jl] = e[m];
+    }
+    __syncthreads();
+}
+template <int E>
+__device__ void k7_bitonic_sort_smem_e(unsigned long long* sk, int N) {
+    constexpr int BLK = 32 * E;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nblk = N / BLK;
+    // every block sorted (alternating directions): phases k = 2 .. BLK
+    for (int blk = warp; blk < nblk; blk += K7_NMS_THREADS / 32) {
+        const int i0 = blk * BLK + lane;
+        unsigned long long e[E];
+#pragma unroll
+        for (int m = 0; m < E; ++m) e[m] = sk[i0 + 32 * m];
+        for (int k = 2; k <= BLK; k <<= 1) k7_bitonic_block_stages<E>(e, i0, k, k >> 1, lane);
+#pragma unroll
+        for (int m = 0; m < E; ++m) sk[i0 + 32 * m] = e[m];
+    }
+    __syncthreads();
+    for (int k = 2 * BLK; k <= N; k <<= 1) {
+        int j = k >> 1;
+        while (j >= BLK) {   // strides through shared memory, three stages per pass
+            if (j >= 4 * BLK) {
+                k7_bitonic_strided_pass<3>(sk, N, k, j);
+                j >>= 3;
+            } else if (j >= 2 * BLK) {
+                k7_bitonic_strided_pass<2>(sk, N, k, j);
+                j >>= 2;
+            } else {
+                k7_bitonic_strided_pass<1>(sk, N, k, j);
+                j >>= 1;
+            }
+        }
+        for (int blk = warp; blk < nblk; blk += K7_NMS_THREADS / 32) {
+            const int i0 = blk * BLK + lane;
+            unsigned long long e[E];
+#pragma unroll
+            for (int m = 0; m < E; ++m) e[m] = sk[i0 + 32 * m];
+            k7_bitonic_block_stages<E>(e, i0, k, BLK >> 1, lane);
+#pragma unroll
+            for (int m = 0; m < E; ++m) sk[i0 + 32 * m] = e[m];
+        }
+        __syncthreads();
+    }
+}
+__device__ void k7_bitonic_sort_smem(unsigned long long* sk, int N) {
+    // small sorts: 64-key blocks keep every warp busy; large ones: 256-key blocks, fewest barriers
+    if (N >= 4096) k7_bitonic_sort_smem_e<8>(sk, N);
+    else k7_bitonic_sort_smem_e<2>(sk, N);
 }
 __device__ __forceinline__ int k7_bitonic_size(int n) {
     int N = 64;
@@ -825,9 +920,11 @@ __device__ __forceinline__ float k7_key_score(uint64_t key) {
 }
 
 // Greedy NMS over keys sorted in visiting order; box of key k is boxes[k & 0xffffffff].
+// labels != nullptr (class of key k = labels[k & 0xffffffff]): only boxes of the same class suppress each other.
 // Writes kept keys/boxes in keep order, returns the number kept.
-__device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const float4* __restrict__ boxes, float thr,
-                            int max_keep, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, K7NmsSmem& S) {
+__device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const float4* __restrict__ boxes,
+                            const int32_t* __restrict__ labels, float thr, int max_keep, uint64_t* __restrict__ kept_key,
+                            float4* __restrict__ kept_box, K7NmsSmem& S) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int kept0 = 0;
     for (int c0 = 0; c0 < n && kept0 < max_keep; c0 += K7_NMS_CHUNK) {
@@ -836,9 +933,11 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
         const bool valid = tid < cn;
         uint64_t key = 0;
         float4 bx = make_float4(0.f, 0.f, 0.f, 0.f);
+        int mlabel = 0;
         if (valid) {
             key = keys[i];
             bx = __ldg(boxes + (uint32_t)(key & 0xffffffffull));
+            if (labels) mlabel = __ldg(labels + (uint32_t)(key & 0xffffffffull));
         }
         const K7Box me = {bx.x, bx.y, bx.z, bx.w};
         const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
@@ -851,14 +950,15 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
                 const float4 kb = kept_box[k0 + tid];
                 S.kbox[tid] = kb;
                 S.karea[tid] = k7_area(kb.x, kb.y, kb.z, kb.w);
+                S.klabel[tid] = labels ? __ldg(labels + (uint32_t)(kept_key[k0 + tid] & 0xffffffffull)) : 0;
             }
             __syncthreads();
             if (alive) {
                 for (int k = 0; k < kn; ++k) {
                     const float4 kb = S.kbox[k];
                     const K7Box other = {kb.x, kb.y, kb.z, kb.w};
-                    if (fminf(other.x2, me.x2) > fmaxf(other.x1, me.x1) && fminf(other.y2, me.y2) > fmaxf(other.y1, me.y1) &&
-                        k7_nms_suppress(other, S.karea[k], me, area, thr)) {
+                    if (S.klabel[k] == mlabel && fminf(other.x2, me.x2) > fmaxf(other.x1, me.x1) &&
+                        fminf(other.y2, me.y2) > fmaxf(other.y1, me.y1) && k7_nms_suppress(other, S.karea[k], me, area, thr)) {
                         alive = false;
                         break;
                     }
@@ -868,6 +968,7 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
         // (b) bitmask matrix of the chunk
         S.box[tid] = bx;
         S.area[tid] = area;
+        S.label[tid] = mlabel;
         const unsigned ab = __ballot_sync(0xffffffffu, alive);
         if (lane == 0) S.alive_bits[warp] = ab;
         if (tid == 0) S.kcount = 0;
@@ -890,14 +991,15 @@ __device__ int k7_block_nms(const uint64_t* __restrict__ keys, int n, const floa
                 const float4 mb = S.box[row];
                 const K7Box me2 = {mb.x, mb.y, mb.z, mb.w};
                 const float marea = S.area[row];
+                const int rlabel = S.label[row];
                 unsigned long long word = 0ull;
                 const int jbeg = max(w * 64, row + 1), jend = min(w * 64 + 64, cn);
                 for (int j = jbeg; j < jend; ++j) {
                     const float4 ob = S.box[j];
                     const K7Box other = {ob.x, ob.y, ob.z, ob.w};
                     // an empty intersection gives overlap 0 (or NaN), never > thr >= 0: skip the division
-                    if (fminf(me2.x2, other.x2) > fmaxf(me2.x1, other.x1) && fminf(me2.y2, other.y2) > fmaxf(me2.y1, other.y1) &&
-                        k7_nms_suppress(me2, marea, other, S.area[j], thr))
+                    if (S.label[j] == rlabel && fminf(me2.x2, other.x2) > fmaxf(me2.x1, other.x1) &&
+                        fminf(me2.y2, other.y2) > fmaxf(me2.y1, other.y1) && k7_nms_suppress(me2, marea, other, S.area[j], thr))
                         word |= 1ull << (j & 63);
                 }
                 S.mask[w * K7_NMS_PITCH + row] = word;
@@ -988,7 +1090,8 @@ __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
 k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int skip_upto, int32_t* __restrict__ surv_count,
                    int32_t* __restrict__ kept_count, const uint32_t* __restrict__ bits, int32_t* __restrict__ wprefix,
                    uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws,
-                   uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, int32_t* __restrict__ counts_out) {
+                   uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, int32_t* __restrict__ counts_out,
+                   const int32_t* __restrict__ label_ws) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
     __shared__ int s_carry;
@@ -1024,7 +1127,8 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
     int n = n_all;
     if (pre_topk > 0 && n > pre_topk) n = pre_topk;
     const int max_keep = max_det > 0 ? max_det : 0x7fffffff;
-    const int kept = k7_block_nms(sorted, n, box_ws + ob, iou_thr, max_keep, kept_key + ob, kept_box + ob, S.nms);
+    const int kept = k7_block_nms(sorted, n, box_ws + ob, label_ws ? label_ws + ob : nullptr, iou_thr, max_keep,
+                                  kept_key + ob, kept_box + ob, S.nms);
     if (tid == 0) {
         kept_count[b] = kept;
         if (counts_out) {
@@ -1080,7 +1184,8 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
                int32_t* __restrict__ wprefix, const float* __restrict__ score_ws, uint64_t* __restrict__ keys0,
                uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws, float4* __restrict__ sbox,
                int32_t* __restrict__ srank, float4* __restrict__ blk, unsigned long long* __restrict__ nz,
-               int32_t* __restrict__ nsel, int32_t* __restrict__ work) {
+               int32_t* __restrict__ nsel, int32_t* __restrict__ work, const int32_t* __restrict__ label_ws,
+               int32_t* __restrict__ slabel) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned long long* sk = reinterpret_cast<unsigned long long*>(smem_raw);
     __shared__ int s_carry;
@@ -1269,6 +1374,7 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
         const uint64_t key = keys1[ob + i];   // written above by this thread
         sbox[oc + p] = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
         srank[oc + p] = i;
+        if (slabel) slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(key & 0xffffffffull));   // class-aware NMS
         for (int z = 0; z < nzw; ++z) nz[(oc + p) * nzw + z] = 0ull;
     }
     if (tid == 0) work[b] = 0;
@@ -1353,10 +1459,11 @@ __device__ __forceinline__ bool k7_sum_may_overlap(const K7Sum& p, const K7Sum& 
 __global__ void __launch_bounds__(K7_MASK_THREADS)
 k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float4* __restrict__ sbox,
                const int32_t* __restrict__ srank, const float4* __restrict__ blk, unsigned long long* __restrict__ nz,
-               unsigned long long* __restrict__ M, int32_t* __restrict__ work) {
+               unsigned long long* __restrict__ M, int32_t* __restrict__ work, const int32_t* __restrict__ slabel) {
     __shared__ float4 cbox[K7_MASK_GROUPS][64];
     __shared__ float carea[K7_MASK_GROUPS][64];
     __shared__ int crank[K7_MASK_GROUPS][64];
+    __shared__ int clabel[K7_MASK_GROUPS][64];
     __shared__ unsigned long long tword[K7_MASK_GROUPS][64];
     __shared__ unsigned int cand[K7_MASK_GROUPS][2];
     __shared__ int s_item[K7_MASK_GROUPS];
@@ -1372,8 +1479,14 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
     const float4* bx = sbox + oc;
     const float4* bs = blk + 2 * (size_t)b * (cap >> 5);
     const int bar_id = 1 + grp;
-    // work item = (row-block, share of its candidate column-blocks), handed out by a per-image counter
-    const int csplit = nb >= 64 ? 2 : (nb >= 16 ? 4 : 8);
+    // work item = (row-block, share of its candidate column-blocks), handed out by a per-image counter.
+    // At least two items per group of the image's CTAs: with few images per launch (a sharded
+    // batch) the row-blocks alone leave most SMs idle and the heavy ones become the tail.
+    int csplit = nb >= 64 ? 2 : (nb >= 16 ? 4 : 8);
+    {
+        const int want = (2 * (int)gridDim.x * K7_MASK_GROUPS + nb - 1) / nb;
+        csplit = max(csplit, min(want, 16));
+    }
     const int items = nb * csplit;
     for (;;) {
         if (t == 0) s_item[grp] = atomicAdd(work + b, 1);
@@ -1391,6 +1504,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
         const float marea = k7_area(mb.x, mb.y, mb.z, mb.w);
         const float mca = K7_FMUL(c_flt, marea);
         const int mrank = rlive ? __ldg(srank + oc + row) : -1;
+        const int mlabel = (slabel && rlive) ? __ldg(slabel + oc + row) : 0;
         // summaries of the two halves of the row-block; rmine = the half this warp owns
         const K7Sum r0 = k7_sum_load(bs, 2 * rb);
         const bool has_r1 = 2 * rb + 1 < n32;
@@ -1424,6 +1538,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
                     cbox[grp][t] = c;
                     carea[grp][t] = K7_FMUL(c_flt, k7_area(c.x, c.y, c.z, c.w));
                     crank[grp][t] = __ldg(srank + oc + col);
+                    clabel[grp][t] = slabel ? __ldg(slabel + oc + col) : 0;
                 }
                 tword[grp][t] = 0ull;
                 asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
@@ -1458,6 +1573,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
                         const int j = __ffsll((long long)f) - 1;
                         f &= f - 1ull;
                         const float4 c = cbox[grp][j];
+                        if (clabel[grp][j] != mlabel) continue;   // class-aware: other classes never suppress
                         if (!k7_nms_suppress_exact(me, marea, c, k7_area(c.x, c.y, c.z, c.w), thr)) continue;
                         if (crank[grp][j] < mrank)
                             word |= 1ull << j;
@@ -1493,6 +1609,13 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
 // without a flagged word (most) are kept in round 0 without touching the matrix.
 #define K7_RESOLVE_THREADS 1024
 #define K7_RESOLVE_PER (K7_SORT_MAX / K7_RESOLVE_THREADS)
+// The flagged words of an image (index + 64 bits, 10 bytes) are staged ONCE in shared memory:
+// a round then costs shared-memory latency instead of two dependent trips to L2 per undecided
+// row (ncu at EfficientDet-D7: 77 us per image, all of it long-scoreboard and barrier stalls).
+// Images with more flagged words than this, or a row with more than 15 of them, iterate on
+// the matrix in global memory as before.
+#define K7_RESOLVE_LIST 12288
+#define K7_RESOLVE_SMEM (K7_RESOLVE_LIST * (sizeof(unsigned long long) + sizeof(unsigned short)))
 __global__ void __launch_bounds__(K7_RESOLVE_THREADS)
 k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
                   const uint64_t* __restrict__ sorted_keys, const float4* __restrict__ sbox,
@@ -1500,10 +1623,14 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
                   const unsigned long long* __restrict__ M, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
                   int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out) {
     constexpr int WMAX = K7_SORT_MAX / 64;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned long long* s_l = reinterpret_cast<unsigned long long*>(smem_raw);
+    unsigned short* s_w = reinterpret_cast<unsigned short*>(s_l + K7_RESOLVE_LIST);
     __shared__ unsigned long long s_kept[WMAX], s_rem[WMAX], s_krank[WMAX];
     __shared__ int s_prefix[WMAX + 1];
+    __shared__ int s_wtot[32];
     __shared__ int s_undecided;
-    const int b = blockIdx.x, tid = threadIdx.x;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = nsel[b];
     if (n < 0) return;   // fallback image
     const size_t ob = (size_t)b * A, oc = (size_t)b * cap;
@@ -1511,46 +1638,124 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     const int nw = (n + 63) >> 6;
     for (int w = tid; w < WMAX; w += K7_RESOLVE_THREADS) s_kept[w] = s_rem[w] = s_krank[w] = 0ull;
     __syncthreads();
-    uint32_t open_ = 0u;   // bit k: row tid + k*1024 is still undecided
+    uint32_t open_ = 0u;                 // bit k: row tid + k*1024 is still undecided
+    unsigned long long cnts = 0ull;      // 4 bits per k: flagged words of that row (saturating at 15)
+    int mine = 0;
+    bool big = false;
+#pragma unroll
+    for (int k = 0; k < K7_RESOLVE_PER; ++k) {   // independent loads, no atomics in between
+        const int p = tid + k * K7_RESOLVE_THREADS;
+        if (p >= n) continue;
+        int c = 0;
+        for (int z = 0; z < nzw; ++z) c += __popcll(__ldcg(nz + (oc + p) * nzw + z));
+        if (c > 0) {
+            open_ |= 1u << k;
+            big |= c > 15;
+            cnts |= (unsigned long long)min(c, 15) << (4 * k);
+            mine += c;
+        }
+    }
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {
         const int p = tid + k * K7_RESOLVE_THREADS;
-        if (p >= n) continue;
-        unsigned long long any = 0ull;
-        for (int z = 0; z < nzw; ++z) any |= __ldcg(nz + (oc + p) * nzw + z);
-        if (any == 0ull)
+        if (p < n && !((open_ >> k) & 1u))
             atomicOr(&s_kept[p >> 6], 1ull << (p & 63));   // nothing ranked before it overlaps: kept
-        else
-            open_ |= 1u << k;
     }
-    for (int round = 0; round < K7_SORT_MAX; ++round) {
-        if (tid == 0) s_undecided = 0;
-        __syncthreads();
-        uint32_t o = open_;
+    // exclusive scan of the per-thread entry counts
+    int inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_wtot[warp] = inc;
+    const int any_big = __syncthreads_or(big ? 1 : 0);
+    int off = inc - mine, total = 0;
+    for (int w = 0; w < K7_RESOLVE_THREADS / 32; ++w) {
+        const int t = s_wtot[w];
+        if (w < warp) off += t;
+        total += t;
+    }
+    const bool staged = !any_big && total <= K7_RESOLVE_LIST;
+    const uint32_t open0 = open_;
+    if (staged) {
+        int e = off;
+        uint32_t o = open0;
         while (o) {
             const int k = __ffs(o) - 1;
             o &= o - 1u;
             const int p = tid + k * K7_RESOLVE_THREADS;
             const unsigned long long* row = M + (oc + p) * nbw;
-            bool any_kept = false, all_removed = true;
             for (int z = 0; z < nzw; ++z) {
                 unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
                 while (m) {
                     const int w = (z << 6) + __ffsll((long long)m) - 1;
                     m &= m - 1ull;
-                    const unsigned long long l = __ldcg(row + w);
-                    const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
-                    const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
-                    any_kept |= (l & kp) != 0ull;
-                    all_removed &= (l & ~rm) == 0ull;
+                    s_w[e] = (unsigned short)w;
+                    s_l[e] = __ldcg(row + w);
+                    ++e;
                 }
             }
-            if (any_kept) {
-                atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
-                open_ &= ~(1u << k);
-            } else if (all_removed) {
-                atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
-                open_ &= ~(1u << k);
+        }
+    }
+    for (int round = 0; round < K7_SORT_MAX; ++round) {
+        if (tid == 0) s_undecided = 0;
+        __syncthreads();
+        if (staged) {
+            int e = off;
+            uint32_t o = open0;
+            while (o) {
+                const int k = __ffs(o) - 1;
+                o &= o - 1u;
+                const int c = (int)((cnts >> (4 * k)) & 15ull);
+                if ((open_ >> k) & 1u) {
+                    bool any_kept = false, all_removed = true;
+                    for (int i = 0; i < c; ++i) {
+                        const int w = s_w[e + i];
+                        const unsigned long long l = s_l[e + i];
+                        const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
+                        const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
+                        any_kept |= (l & kp) != 0ull;
+                        all_removed &= (l & ~rm) == 0ull;
+                    }
+                    const int p = tid + k * K7_RESOLVE_THREADS;
+                    if (any_kept) {
+                        atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
+                        open_ &= ~(1u << k);
+                    } else if (all_removed) {
+                        atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
+                        open_ &= ~(1u << k);
+                    }
+                }
+                e += c;
+            }
+        } else {
+            uint32_t o = open_;
+            while (o) {
+                const int k = __ffs(o) - 1;
+                o &= o - 1u;
+                const int p = tid + k * K7_RESOLVE_THREADS;
+                const unsigned long long* row = M + (oc + p) * nbw;
+                bool any_kept = false, all_removed = true;
+                for (int z = 0; z < nzw; ++z) {
+                    unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
+                    while (m) {
+                        const int w = (z << 6) + __ffsll((long long)m) - 1;
+                        m &= m - 1ull;
+                        const unsigned long long l = __ldcg(row + w);
+                        const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
+                        const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
+                        any_kept |= (l & kp) != 0ull;
+                        all_removed &= (l & ~rm) == 0ull;
+                    }
+                }
+                if (any_kept) {
+                    atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
+                    open_ &= ~(1u << k);
+                } else if (all_removed) {
+                    atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
+                    open_ &= ~(1u << k);
+                }
             }
         }
         if (open_) s_undecided = 1;
@@ -1735,22 +1940,25 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
 
     // NMS: images with <= cap survivors go through sort -> mask (all SMs) -> resolve (one CTA each),
     // the others through the chunked single-CTA kernel.  Each kernel decides per image on the device.
+    const bool ca = params->class_aware != 0;   // suppression only inside a class (torchvision.ops.batched_nms)
     {
         size_t smem_sort = 64 * 8;
         while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;   // bitonic size of the largest image
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
         k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.cap, w.surv_count, w.bits,
                                                              w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
-                                                             w.blk, w.nz, w.nsel, w.work);
+                                                             w.blk, w.nz, w.nsel, w.work, ca ? w.label : nullptr,
+                                                             ca ? w.slabel : nullptr);
         K7_LAUNCH_CHECK();
         int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
         const int gx_max = (w.cap / 64 + K7_MASK_GROUPS - 1) / K7_MASK_GROUPS * 4;
         if (gx > gx_max) gx = gx_max;
         if (gx < 1) gx = 1;
         k7_mask_kernel<<<dim3(gx, B), K7_MASK_THREADS, 0, st>>>(params->iou_thr, w.cap, w.nsel, w.sbox, w.srank, w.blk, w.nz,
-                                                                w.M, w.work);
+                                                                w.M, w.work, ca ? w.slabel : nullptr);
         K7_LAUNCH_CHECK();
-        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, 0, st>>>(A, params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1,
+        K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
+        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, K7_RESOLVE_SMEM, st>>>(A, params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1,
                                                             w.sbox, w.srank, w.nz, w.M, w.kept_key, w.kept_box, w.kept_count,
                                                             counts, nullptr);
         K7_LAUNCH_CHECK();
@@ -1761,7 +1969,7 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk,
                                                             params->max_detections, w.cap, w.surv_count, w.kept_count,
                                                             w.bits, w.wprefix, w.keys0, w.keys1, w.box, w.kept_key,
-                                                            w.kept_box, counts);
+                                                            w.kept_box, counts, ca ? w.label : nullptr);
     }
     K7_LAUNCH_CHECK();
     return K7_OK;
@@ -1810,8 +2018,10 @@ struct K7NmsWs {
     uint64_t* kept_key;
     float4* kept_box;
     int32_t* small;            // {n, nsel, kept_count, mask work counter}
+    int32_t* label;            // [n] class of each box (k7_batched_nms)
     float4* sbox;              // multi-SM path (n <= K7_SORT_MAX)
     int32_t* srank;
+    int32_t* slabel;
     float4* blk;
     unsigned long long* nz;
     unsigned long long* M;
@@ -1833,8 +2043,10 @@ static K7NmsWs k7_nms_ws(void* base, int n) {
     w.kept_key = reinterpret_cast<uint64_t*>(take(8 * nn));
     w.kept_box = reinterpret_cast<float4*>(take(16 * nn));
     w.small = reinterpret_cast<int32_t*>(take(64));
+    w.label = reinterpret_cast<int32_t*>(take(4 * nn));
     w.sbox = w.kept_box;
     w.srank = nullptr;
+    w.slabel = nullptr;
     w.blk = nullptr;
     w.nz = nullptr;
     w.M = nullptr;
@@ -1843,6 +2055,7 @@ static K7NmsWs k7_nms_ws(void* base, int n) {
         const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
         w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * cap));
         w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * cap));
+        w.slabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * cap));
         w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * nbw));
         w.nz = reinterpret_cast<unsigned long long*>(take(8 * cap * nzw));
         w.M = reinterpret_cast<unsigned long long*>(take(8 * cap * nbw));
@@ -1853,27 +2066,31 @@ static K7NmsWs k7_nms_ws(void* base, int n) {
 extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_nms_ws(nullptr, n).bytes; }
 
 __global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys,
-                                   int32_t* __restrict__ n_dev) {
+                                   int32_t* __restrict__ n_dev, const int64_t* __restrict__ idxs,
+                                   int32_t* __restrict__ labels) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) *n_dev = n;
-    if (i < n) keys[i] = ((uint64_t)k7_score_key_desc(scores[i]) << 32) | (uint32_t)i;
+    if (i < n) {
+        keys[i] = ((uint64_t)k7_score_key_desc(scores[i]) << 32) | (uint32_t)i;
+        if (idxs) labels[i] = (int32_t)idxs[i];   // only equality matters; category ids fit 32 bits
+    }
 }
 
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
 k7_nms_single_kernel(int n, float iou_thr, uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1,
-                     const float4* __restrict__ boxes, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
-                     int64_t* __restrict__ keep, int32_t* __restrict__ count) {
+                     const float4* __restrict__ boxes, const int32_t* __restrict__ labels, uint64_t* __restrict__ kept_key,
+                     float4* __restrict__ kept_box, int64_t* __restrict__ keep, int32_t* __restrict__ count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
     uint64_t* sorted = k7_block_sort(keys0, keys1, n, S);
-    const int kept = k7_block_nms(sorted, n, boxes, iou_thr, 0x7fffffff, kept_key, kept_box, S.nms);
+    const int kept = k7_block_nms(sorted, n, boxes, labels, iou_thr, 0x7fffffff, kept_key, kept_box, S.nms);
     __syncthreads();
     for (int k = threadIdx.x; k < kept; k += K7_NMS_THREADS) keep[k] = (int64_t)(uint32_t)(kept_key[k] & 0xffffffffull);
     if (threadIdx.x == 0) *count = kept;
 }
 
-extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_thr, int64_t* keep, int32_t* count,
-                      void* workspace, size_t workspace_bytes, void* stream) {
+static int k7_nms_run(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr, int64_t* keep,
+                      int32_t* count, void* workspace, size_t workspace_bytes, void* stream) {
     K7_REQUIRE(count && workspace, "k7_nms: null argument");
     K7_REQUIRE(n >= 0 && iou_thr >= 0.0f, "k7_nms: bad argument n=%d iou_thr=%f", n, (double)iou_thr);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1889,7 +2106,7 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
         k7_set_error("k7_nms: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
         return K7_EWORKSPACE;
     }
-    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.small);
+    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.small, idxs, w.label);
     K7_LAUNCH_CHECK();
     if (n <= w.cap) {   // sort -> bitmask on all SMs -> fixed-point resolve (same kernels as k7_detect, B = 1)
         const float4* b4 = reinterpret_cast<const float4*>(boxes);
@@ -1897,15 +2114,17 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
         while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
         k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.cap, w.small, nullptr, nullptr, nullptr, w.keys0,
-                                                             w.keys1, b4, w.sbox, w.srank, w.blk, w.nz, w.small + 1, w.small + 3);
+                                                             w.keys1, b4, w.sbox, w.srank, w.blk, w.nz, w.small + 1, w.small + 3,
+                                                             idxs ? w.label : nullptr, idxs ? w.slabel : nullptr);
         K7_LAUNCH_CHECK();
         const int nb = (n + 63) / 64;
         int gx = 4 * k7_sm_count();   // one image: spread its row-blocks (and their column shares) over every SM
         if (gx > nb * nb) gx = nb * nb;
         k7_mask_kernel<<<dim3(gx, 1), K7_MASK_THREADS, 0, st>>>(iou_thr, w.cap, w.small + 1, w.sbox, w.srank, w.blk, w.nz, w.M,
-                                                                w.small + 3);
+                                                                w.small + 3, idxs ? w.slabel : nullptr);
         K7_LAUNCH_CHECK();
-        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, 0, st>>>(n, 0, w.cap, w.small + 1, w.small, w.keys1, w.sbox, w.srank, w.nz,
+        K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
+        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, K7_RESOLVE_SMEM, st>>>(n, 0, w.cap, w.small + 1, w.small, w.keys1, w.sbox, w.srank, w.nz,
                                                             w.M, w.kept_key, w.kept_box, count, nullptr, keep);
         K7_LAUNCH_CHECK();
         return K7_OK;
@@ -1913,7 +2132,18 @@ extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_
     const size_t smem = sizeof(K7SortNmsSmem);
     K7_CUDA(cudaFuncSetAttribute(k7_nms_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k7_nms_single_kernel<<<1, K7_NMS_THREADS, smem, st>>>(n, iou_thr, w.keys0, w.keys1, reinterpret_cast<const float4*>(boxes),
-                                                          w.kept_key, w.kept_box, keep, count);
+                                                          idxs ? w.label : nullptr, w.kept_key, w.kept_box, keep, count);
     K7_LAUNCH_CHECK();
     return K7_OK;
+}
+
+extern "C" int k7_nms(const float* boxes, const float* scores, int n, float iou_thr, int64_t* keep, int32_t* count,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    return k7_nms_run(boxes, scores, nullptr, n, iou_thr, keep, count, workspace, workspace_bytes, stream);
+}
+
+extern "C" int k7_batched_nms(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr, int64_t* keep,
+                              int32_t* count, void* workspace, size_t workspace_bytes, void* stream) {
+    K7_REQUIRE(n == 0 || idxs, "k7_batched_nms: null argument");
+    return k7_nms_run(boxes, scores, idxs, n, iou_thr, keep, count, workspace, workspace_bytes, stream);
 }

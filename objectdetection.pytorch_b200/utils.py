@@ -127,8 +127,11 @@ class BatchDetections:
 def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, image_hw, *,
            score_thr: float = 0.05, iou_thr: float = 0.5, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0),
            std=(.1, .1, .2, .2), clip: bool = True, pre_nms_topk: int = 0, max_detections: int = 0,
-           cap: Optional[int] = None, sync: bool = True, from_logits: bool = False) -> BatchDetections:
+           cap: Optional[int] = None, sync: bool = True, from_logits: bool = False,
+           class_aware: bool = False) -> BatchDetections:
     """Fused decode + clip + threshold + sort + NMS for every image of the batch.
+    class_aware: suppress only inside a class (torchvision.ops.batched_nms with idxs = labels); the
+    reference's own eval tail is class-agnostic (retinanet.py:314), which is the default.
     from_logits: `classifications` are pre-sigmoid logits; scores are torch.sigmoid of the row maxima
     and threshold / label ties are decided on those float32 probabilities, as the reference would.
     `classifications` may also be the LIST of the head's raw per-level NCHW outputs
@@ -164,6 +167,7 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
     p.score_thr, p.iou_thr = float(score_thr), float(iou_thr)
     p.pre_nms_topk, p.max_detections = int(pre_nms_topk), int(max_detections)
     p.from_logits = int(from_logits)
+    p.class_aware = int(class_aware)
     if cap is None:
         cap = max_detections if max_detections > 0 else min(A, 1024)
     cap = max(1, min(int(cap), A))
@@ -213,13 +217,51 @@ def nms(boxes: torch.Tensor, scores: torch.Tensor, iou_threshold: float) -> torc
     return keep[:int(count.item())]
 
 
+def batched_nms(boxes: torch.Tensor, scores: torch.Tensor, idxs: torch.Tensor, iou_threshold: float,
+                strategy: str = "vanilla") -> torch.Tensor:
+    """torchvision.ops.batched_nms(boxes, scores, idxs, iou_threshold) on device: NMS
+    inside each category, int64 indices in descending-score order.
+    strategy "vanilla": exact per-category NMS (torchvision's _batched_nms_vanilla) in ONE pass of the
+    bitmask kernels, the category test fused behind the overlap filter;
+    "coordinate_trick": torchvision's _batched_nms_coordinate_trick (boxes shifted by
+    idxs * (boxes.max() + 1), then plain NMS) - the float32 shift rounds the coordinates, so its result can
+    differ from the exact one exactly as torchvision's does;
+    "auto": torchvision's own rule on CUDA (boxes.numel() > 20000 -> vanilla)."""
+    L.require_cuda(boxes, scores, idxs)
+    if strategy == "auto":
+        strategy = "vanilla" if boxes.numel() > 20000 else "coordinate_trick"
+    if strategy == "coordinate_trick":
+        if boxes.numel() == 0:
+            return torch.empty((0,), dtype=torch.int64, device=boxes.device)
+        max_coordinate = boxes.max()
+        offsets = idxs.to(boxes) * (max_coordinate + torch.tensor(1).to(boxes))
+        return nms(boxes + offsets[:, None], scores, iou_threshold)
+    if strategy != "vanilla":
+        raise ValueError("strategy must be 'vanilla', 'coordinate_trick' or 'auto'")
+    b = L.as_f32_contig(boxes)
+    s = L.as_f32_contig(scores)
+    i = idxs.to(torch.int64).contiguous()
+    n = b.shape[0]
+    if s.shape[0] != n or i.shape[0] != n:
+        raise ValueError("boxes, scores and idxs must have the same length")
+    dev = b.device
+    lib = L.lib()
+    keep = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    ws = _WS.get("nms", lib.k7_nms_workspace_bytes(n), dev)
+    with torch.cuda.device(dev):
+        L.check(lib.k7_batched_nms(L.ptr(b), L.ptr(s), L.ptr(i), n, float(iou_threshold), L.ptr(keep), L.ptr(count),
+                                   L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_batched_nms")
+    return keep[:int(count.item())]
+
+
 def _variant_of(regressBoxes) -> int:
     return L.DECODE_EFFDET if isinstance(regressBoxes, BBoxTransformYX) or \
         type(regressBoxes).__module__.endswith("utils_efficientdet") else L.DECODE_RETINA
 
 
 def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes, threshold, iou_threshold,
-                from_logits: bool = False):
+                from_logits: bool = False, class_aware: bool = False):
     """utils/utils.py:76-114 — same arguments, same return (list of dicts of numpy arrays).  The
     reference's duplicate empty dict for an all-empty batch (utils.py:83-88) is not reproduced."""
     variant = _variant_of(regressBoxes)
@@ -227,7 +269,7 @@ def postprocess(x, anchors, regression, classification, regressBoxes, clipBoxes,
     std = _to4(getattr(regressBoxes, "std", None), [0.1, 0.1, 0.2, 0.2])
     det = detect(classification, regression, anchors, (int(x.shape[2]), int(x.shape[3])), score_thr=threshold,
                  iou_thr=iou_threshold, variant=variant, mean=mean, std=std, clip=clipBoxes is not None,
-                 from_logits=from_logits)
+                 from_logits=from_logits, class_aware=class_aware)
     out = []
     sc, lb, bx = det.scores.cpu().numpy(), det.labels.cpu().numpy(), det.boxes.cpu().numpy()
     for b in range(classification.shape[0]):

@@ -359,6 +359,33 @@ def greedy_nms(boxes: np.ndarray, scores: np.ndarray, thr: float) -> np.ndarray:
     return np.asarray(keep, dtype=np.int64)
 
 
+def batched_nms(boxes: np.ndarray, scores: np.ndarray, idxs: np.ndarray, thr: float) -> np.ndarray:
+    """Per-category NMS - the reference is class-agnostic, so the behaviour restated is
+    torchvision 0.26.0 ``torchvision/ops/boxes.py::_batched_nms_vanilla``: nms() on the boxes of every
+    category by itself, the union of the kept indices ordered by descending score.  Ties: torchvision's
+    final ``sort(descending=True)`` is not a stable sort; here equal scores keep their index order
+    (what the device path does)."""
+    boxes = np.asarray(boxes, dtype=np.float32).reshape(-1, 4)
+    scores = np.asarray(scores, dtype=np.float32)
+    idxs = np.asarray(idxs)
+    keep_mask = np.zeros(scores.shape[0], dtype=bool)
+    for c in np.unique(idxs):
+        cur = np.nonzero(idxs == c)[0]
+        keep_mask[cur[greedy_nms(boxes[cur], scores[cur], thr)]] = True
+    kept = np.nonzero(keep_mask)[0]
+    return kept[np.argsort(-scores[kept], kind='stable')].astype(np.int64)
+
+
+def batched_nms_coordinate_trick(boxes: np.ndarray, scores: np.ndarray, idxs: np.ndarray, thr: float) -> np.ndarray:
+    """torchvision 0.26.0 ``_batched_nms_coordinate_trick``: boxes shifted by idxs * (max coordinate + 1)
+    in float32, then plain NMS."""
+    boxes = np.asarray(boxes, dtype=np.float32).reshape(-1, 4)
+    if boxes.size == 0:
+        return np.zeros((0,), dtype=np.int64)
+    off = np.asarray(idxs).astype(np.float32) * (boxes.max() + np.float32(1))
+    return greedy_nms(boxes + off[:, None], scores, thr)
+
+
 @dataclass
 class Detections:
     survivors: torch.Tensor      # [S] int64 anchor ids passing the score threshold (ascending)

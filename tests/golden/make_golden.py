@@ -17,6 +17,8 @@ and writes
   tests/golden/head_retina.npz     per-level NCHW logits of the reference's ClassificationModel (captured in
                                    front of its output_act) and the [B,A,C] probabilities it returns
   tests/golden/collate.npz         per-image annotation rows and the padded block the reference's collater makes of them
+  tests/golden/batched_nms.npz     boxes / scores / categories and what torchvision 0.26.0 batched_nms (both
+                                   strategies) keeps - SURVEY 8f row 4; the reference has no per-class NMS
   tests/golden/eval_tail.npz       detections of 6 images and what datasettool/{coco_eval,ksevendata_eval,csv_eval}.py
                                    make of them (result rows / per-class detection arrays)
 The reference's hidden intermediates (IoU_max, IoU_argmax, masks) are obtained by
@@ -415,7 +417,37 @@ def gen_collate():
     print("collate", {k: v.shape for k, v in rec.items() if k.endswith("_padded")})
 
 
+def gen_batched_nms():
+    """torchvision.ops.batched_nms: _batched_nms_vanilla and _batched_nms_coordinate_trick on clustered boxes."""
+    from torchvision.ops import boxes as tvb
+    g = torch.Generator().manual_seed(20260415)
+    rec = {}
+    for tag, n, ncls, span in (("small", 300, 5, 200.0), ("many_classes", 2500, 90, 512.0), ("one_class", 800, 1, 300.0),
+                               ("dense", 1500, 3, 120.0)):
+        centre = torch.rand(n // 6 + 1, 2, generator=g) * span
+        pick = torch.randint(0, centre.shape[0], (n,), generator=g)
+        c = centre[pick] + torch.randn(n, 2, generator=g) * 6.0
+        wh = torch.exp(torch.rand(n, 2, generator=g) * 1.5 + 2.5)
+        boxes = torch.cat([c - wh / 2, c + wh / 2], dim=1).float()
+        scores = ((torch.randperm(n, generator=g) + 1).float() / float(n + 1)) ** 2   # distinct by construction
+        assert torch.unique(scores).numel() == n
+        idxs = torch.randint(0, ncls, (n,), generator=g)
+        rec[f"{tag}_boxes"] = boxes.numpy()
+        rec[f"{tag}_scores"] = scores.numpy()
+        rec[f"{tag}_idxs"] = idxs.numpy()
+        rec[f"{tag}_vanilla"] = tvb._batched_nms_vanilla(boxes, scores, idxs, 0.5).numpy()
+        rec[f"{tag}_trick"] = tvb._batched_nms_coordinate_trick(boxes, scores, idxs, 0.5).numpy()
+        rec[f"{tag}_public"] = tvb.batched_nms(boxes, scores, idxs, 0.5).numpy()
+        rec[f"{tag}_agnostic"] = tv_nms(boxes, scores, 0.5).numpy()
+    np.savez_compressed(os.path.join(HERE, "batched_nms.npz"), **rec)
+    print("batched_nms", {k: v.shape for k, v in rec.items() if k.endswith("_vanilla") or k.endswith("_agnostic")})
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1:                       # python make_golden.py batched_nms collate ...
+        for name in sys.argv[1:]:
+            globals()["gen_" + name]()
+        sys.exit(0)
     gen_anchors()
     gen_loss()
     gen_detect()

@@ -288,6 +288,81 @@ def test_nms_empty():
     assert keep.shape == (0,) and keep.dtype == torch.int64
 
 
+# ------------------------------------------------------------------ per-category NMS
+@pytest.mark.parametrize("tag", ["small", "many_classes", "one_class", "dense"])
+def test_batched_nms_fixture_bit_exact(tag):
+    """k7_batched_nms == torchvision 0.26.0 batched_nms on the committed fixture: the per-category strategy
+    and the coordinate trick, each against torchvision's own output of that strategy."""
+    g = np.load(os.path.join(GOLDEN, "batched_nms.npz"))
+    boxes = torch.from_numpy(g[f"{tag}_boxes"]).to(DEV)
+    scores = torch.from_numpy(g[f"{tag}_scores"]).to(DEV)
+    idxs = torch.from_numpy(g[f"{tag}_idxs"]).to(DEV)
+    got = b200det.batched_nms(boxes, scores, idxs, 0.5)
+    assert got.dtype == torch.int64 and np.array_equal(got.cpu().numpy(), g[f"{tag}_vanilla"])
+    got = b200det.batched_nms(boxes, scores, idxs, 0.5, strategy="coordinate_trick")
+    assert np.array_equal(got.cpu().numpy(), g[f"{tag}_trick"])
+    assert np.array_equal(b200det.nms(boxes, scores, 0.5).cpu().numpy(), g[f"{tag}_agnostic"])
+
+
+@pytest.mark.parametrize("n,ncls", [(1, 1), (65, 2), (1000, 7), (3000, 90), (9000, 4), (17000, 3), (20000, 90)])
+def test_batched_nms_random_vs_oracle(n, ncls):
+    """Clustered boxes of mixed sizes, score ties, negative category ids; n > 16 384 takes the single-CTA
+    chunked kernel.  Oracle = per-category greedy NMS (restatement of torchvision's vanilla strategy);
+    n > 1000 is also what torchvision.ops.batched_nms itself does on CPU."""
+    rng = np.random.default_rng(n + ncls)
+    centers = rng.uniform(0, 800, (max(n // 8, 1), 2))
+    c = centers[rng.integers(0, centers.shape[0], n)] + rng.normal(0, 4, (n, 2))
+    wh = 2.0 ** rng.uniform(3, 7, (n, 2))
+    boxes = np.concatenate([c - wh / 2, c + wh / 2], 1).astype(np.float32)
+    scores = np.round(rng.uniform(0, 1, n), 3).astype(np.float32)      # ties
+    idxs = rng.integers(0, ncls, n).astype(np.int64) - 1               # includes -1
+    for thr in (0.3, 0.5):
+        want = R.batched_nms(boxes, scores, idxs, thr)
+        got = b200det.batched_nms(torch.from_numpy(boxes).to(DEV), torch.from_numpy(scores).to(DEV),
+                                  torch.from_numpy(idxs).to(DEV), thr).cpu().numpy()
+        assert np.array_equal(got, want), (n, ncls, thr)
+    if n > 1000 and np.unique(scores).size == n:                       # torchvision's own public entry point
+        from torchvision.ops import batched_nms as tv_bnms
+        want = tv_bnms(torch.from_numpy(boxes), torch.from_numpy(scores), torch.from_numpy(idxs), 0.5).numpy()
+        assert np.array_equal(got, want)
+
+
+def test_batched_nms_empty_and_errors():
+    z = torch.zeros(0, 4, device=DEV)
+    keep = b200det.batched_nms(z, torch.zeros(0, device=DEV), torch.zeros(0, dtype=torch.int64, device=DEV), 0.5)
+    assert keep.shape == (0,) and keep.dtype == torch.int64
+    with pytest.raises(ValueError):
+        b200det.batched_nms(torch.zeros(3, 4, device=DEV), torch.zeros(3, device=DEV),
+                            torch.zeros(2, dtype=torch.int64, device=DEV), 0.5)
+    with pytest.raises(ValueError):
+        b200det.batched_nms(torch.zeros(3, 4, device=DEV), torch.zeros(3, device=DEV),
+                            torch.zeros(3, dtype=torch.int64, device=DEV), 0.5, strategy="fastest")
+
+
+@pytest.mark.parametrize("name", ["detect_retina_small", "detect_retina_c90"])
+def test_detect_class_aware_vs_oracle(name):
+    """detect(class_aware=True): the eval tail with per-class suppression.  Oracle: the reference's own
+    threshold / arg-max (retinanet.py:300-318) followed by the per-category NMS restatement."""
+    g, yx, anc, img = load_det_case(DET[DIDS.index(name)], True)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    det = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])), class_aware=True)
+    agn = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])))
+    more = 0
+    for b in range(cls.shape[0]):
+        surv = g[f"survivors_{b}"]
+        sc, lb = torch.from_numpy(g["classifications"][b][surv]).max(dim=1)
+        keep = R.batched_nms(g["boxes"][b][surv], sc.numpy(), lb.numpy(), 0.5)
+        k = int(det.count[b])
+        assert k == keep.size
+        assert np.array_equal(det.survivor_rank[b, :k].cpu().numpy(), keep)
+        assert np.array_equal(det.anchor_ids[b, :k].cpu().numpy(), surv[keep])
+        assert np.array_equal(det.labels[b, :k].cpu().numpy(), lb.numpy()[keep])
+        assert np.array_equal(det.scores[b, :k].cpu().numpy(), sc.numpy()[keep])
+        more += k - int(agn.count[b])
+    assert more >= 0            # suppression inside a class only can never keep fewer boxes
+
+
 def check_detect(det, g, exact_boxes_from=None):
     B = g["classifications"].shape[0]
     for b in range(B):

@@ -153,3 +153,17 @@ def test_collate_annotations_matches_reference():
         out = R.collate_annotations(rows).numpy()
         assert out.shape == g[f"{tag}_padded"].shape, tag
         assert np.array_equal(out, g[f"{tag}_padded"]), tag
+
+
+# ------------------------------------------------------------------ per-category NMS
+@pytest.mark.parametrize("tag", ["small", "many_classes", "one_class", "dense"])
+def test_batched_nms_oracle_vs_torchvision_fixture(tag):
+    """oracle batched_nms == torchvision 0.26.0 _batched_nms_vanilla, and the coordinate-trick restatement
+    == _batched_nms_coordinate_trick, on tests/golden/batched_nms.npz (make_golden.py::gen_batched_nms)."""
+    g = np.load(os.path.join(GOLDEN, "batched_nms.npz"))
+    boxes, scores, idxs = g[f"{tag}_boxes"], g[f"{tag}_scores"], g[f"{tag}_idxs"]
+    assert np.array_equal(R.batched_nms(boxes, scores, idxs, 0.5), g[f"{tag}_vanilla"])
+    assert np.array_equal(R.batched_nms_coordinate_trick(boxes, scores, idxs, 0.5), g[f"{tag}_trick"])
+    assert np.array_equal(R.greedy_nms(boxes, scores, 0.5), g[f"{tag}_agnostic"])
+    if tag == "one_class":                       # a single category is plain NMS
+        assert np.array_equal(g[f"{tag}_vanilla"], g[f"{tag}_agnostic"])
