@@ -1185,58 +1185,69 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
                uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws, float4* __restrict__ sbox,
                int32_t* __restrict__ srank, float4* __restrict__ blk, unsigned long long* __restrict__ nz,
                int32_t* __restrict__ nsel, int32_t* __restrict__ work, const int32_t* __restrict__ label_ws,
-               int32_t* __restrict__ slabel) {
+               int32_t* __restrict__ slabel, float4* __restrict__ rbox) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned long long* sk = reinterpret_cast<unsigned long long*>(smem_raw);
-    __shared__ int s_carry;
     __shared__ unsigned int s_wtot[32];
     __shared__ float4 s_wsum[32];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t ob = (size_t)b * A;
     int n_all;
     if (bits) {
-        // exclusive popcount prefix over the survivor bitmap
-        if (tid == 0) s_carry = 0;
-        __syncthreads();
-        for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
-            const int w = w0 + tid;
-            const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
-            int inc = v;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += t;
+        // Survivor ranks and keys.  A thread owns a contiguous chunk of the image's bitmap words:
+        // one block scan gives every chunk its first rank.  The first walk over the bits also
+        // prefetches what the gathers below will want (score and box by anchor id; the score
+        // kernel wrote them long ago, most lines have left L2).
+        const int chunk = (W32 + K7_NMS_THREADS - 1) / K7_NMS_THREADS;
+        const int w_lo = min(tid * chunk, W32), w_hi = min(w_lo + chunk, W32);
+        const uint32_t* brow = bits + (size_t)b * W32;
+        int cnt = 0;
+        for (int w = w_lo; w < w_hi; ++w) {
+            uint32_t word = brow[w];
+            cnt += __popc(word);
+            while (word) {
+                const int a = (w << 5) + __ffs(word) - 1;
+                word &= word - 1;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(score_ws + ob + a));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(box_ws + ob + a));
             }
-            if (lane == 31) s_wtot[warp] = (unsigned)inc;
-            __syncthreads();
-            int woff = 0;
-            for (int k = 0; k < warp; ++k) woff += (int)s_wtot[k];
-            const int carry = s_carry;
-            if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
-            __syncthreads();
-            if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
-            __syncthreads();
         }
-        n_all = s_carry;
+        int inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) s_wtot[warp] = (unsigned)inc;
+        __syncthreads();
+        int slot = inc - cnt;
+        n_all = 0;
+        for (int k = 0; k < K7_NMS_THREADS / 32; ++k) {
+            const int t = (int)s_wtot[k];
+            if (k < warp) slot += t;
+            n_all += t;
+        }
+        __syncthreads();   // s_wtot is reused below
         if (tid == 0) surv_count[b] = n_all;
+        const bool small_ = n_all <= cap;
+        // one key per set bit, written at its rank: shared memory (small image) or keys0 (fallback image)
+        for (int w = w_lo; w < w_hi; ++w) {
+            uint32_t word = brow[w];
+            wprefix[(size_t)b * W32 + w] = slot;
+            while (word) {
+                const int a = (w << 5) + __ffs(word) - 1;
+                word &= word - 1;
+                const uint64_t key = ((uint64_t)k7_score_key_desc(score_ws[ob + a]) << 32) | (uint32_t)a;
+                if (small_) sk[slot] = key; else keys0[ob + slot] = key;
+                ++slot;
+            }
+        }
     } else {
         n_all = surv_count[b];
     }
     const bool small = n_all <= cap;
     int N = k7_bitonic_size(n_all);
     if (bits) {
-        // one key per set bit, written at its rank: shared memory (small image) or keys0 (fallback image)
-        for (int w = tid; w < W32; w += K7_NMS_THREADS) {
-            uint32_t word = bits[(size_t)b * W32 + w];
-            int slot = wprefix[(size_t)b * W32 + w];
-            while (word) {
-                const int a = (w << 5) + __ffs(word) - 1;
-                word &= word - 1;
-                const uint64_t key = ((uint64_t)k7_score_key_desc(score_ws[ob + a]) << 32) | (uint32_t)a;
-                if (small) sk[slot] = key; else keys0[ob + slot] = key;
-                ++slot;
-            }
-        }
         if (small)
             for (int i = n_all + tid; i < N; i += K7_NMS_THREADS) sk[i] = ~0ull;
     } else if (small) {
@@ -1257,6 +1268,9 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     // order gives the same NMS result; this one makes 64 consecutive boxes neighbours in the image
     // (about four cells in a row), so most pairs of 64-blocks are ruled out by their summaries in
     // k7_mask_kernel.
+    // The boxes are gathered by anchor id ONCE (four independent loads in flight per thread) and
+    // left in rank order in `rbox`; what the binning needs of a box - x1, y1 (28 bits each are
+    // plenty for a cell index) and the binade of its area - replaces its key in sk[].
     __shared__ int s_cls[256], s_base[257], s_g[256];
     __shared__ int s_cell[K7_CELLS_MAX + 1];
     __shared__ float s_bnd[4];
@@ -1264,14 +1278,32 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     for (int c = tid; c <= K7_CELLS_MAX; c += K7_NMS_THREADS) s_cell[c] = 0;
     __syncthreads();
     float bx0 = 3.0e38f, bx1 = -3.0e38f, by0 = 3.0e38f, by1 = -3.0e38f;
-    for (int i = tid; i < n; i += K7_NMS_THREADS) {
-        const uint64_t key = sk[i];
-        keys1[ob + i] = key;
-        const float4 bx = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
-        const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
-        atomicAdd(&s_cls[(__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu], 1);   // binade of the area
-        bx0 = fminf(bx0, bx.x); bx1 = fmaxf(bx1, bx.x);
-        by0 = fminf(by0, bx.y); by1 = fmaxf(by1, bx.y);
+    for (int i0 = 0; i0 < n; i0 += 4 * K7_NMS_THREADS) {
+        uint64_t key[4];
+        float4 bx[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * K7_NMS_THREADS + tid;
+            if (i < n) {
+                key[u] = sk[i];
+                bx[u] = __ldg(box_ws + ob + (uint32_t)(key[u] & 0xffffffffull));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * K7_NMS_THREADS + tid;
+            if (i < n) {
+                keys1[ob + i] = key[u];
+                rbox[ob + i] = bx[u];
+                const float area = k7_area(bx[u].x, bx[u].y, bx[u].z, bx[u].w);
+                const unsigned c8 = (__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu;   // binade of the area
+                atomicAdd(&s_cls[c8], 1);
+                bx0 = fminf(bx0, bx[u].x); bx1 = fmaxf(bx1, bx[u].x);
+                by0 = fminf(by0, bx[u].y); by1 = fmaxf(by1, bx[u].y);
+                sk[i] = ((unsigned long long)(__float_as_uint(bx[u].x) & 0xfffffff0u) << 32) |
+                        ((unsigned long long)(__float_as_uint(bx[u].y) & 0xfffffff0u) << 4) | c8;
+            }
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -1326,12 +1358,12 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     __syncthreads();
     // cell of every box (kept in sk[i]) and the cell histogram
     for (int i = tid; i < n; i += K7_NMS_THREADS) {
-        const uint64_t key = sk[i];
-        const float4 bx = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
-        const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
-        const int c8 = (int)((__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu);
+        const unsigned long long v = sk[i];
+        const float x = __uint_as_float((uint32_t)(v >> 32) & 0xfffffff0u);
+        const float y = __uint_as_float((uint32_t)(v >> 4) & 0xfffffff0u);
+        const int c8 = (int)(v & 0xffull);
         const int g = s_g[c8];
-        int cx = (int)((bx.x - s_bnd[0]) * s_bnd[1] * (float)g), cy = (int)((bx.y - s_bnd[2]) * s_bnd[3] * (float)g);
+        int cx = (int)((x - s_bnd[0]) * s_bnd[1] * (float)g), cy = (int)((y - s_bnd[2]) * s_bnd[3] * (float)g);
         cx = max(0, min(cx, g - 1));   // also sends NaN to cell 0
         cy = max(0, min(cy, g - 1));
         if (cy & 1) cx = g - 1 - cx;   // odd rows run backwards
@@ -1371,12 +1403,12 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     const int nzw = (cap / 64 + 63) / 64;
     for (int i = tid; i < n; i += K7_NMS_THREADS) {
         const int p = atomicAdd(&s_cell[(int)sk[i]], 1);
-        const uint64_t key = keys1[ob + i];   // written above by this thread
-        sbox[oc + p] = __ldg(box_ws + ob + (uint32_t)(key & 0xffffffffull));
+        sbox[oc + p] = __ldcg(rbox + ob + i);   // written above by this thread
         srank[oc + p] = i;
-        if (slabel) slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(key & 0xffffffffull));   // class-aware NMS
-        for (int z = 0; z < nzw; ++z) nz[(oc + p) * nzw + z] = 0ull;
+        if (slabel)   // class-aware NMS
+            slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(__ldcg(keys1 + ob + i) & 0xffffffffull));
     }
+    for (int i = tid; i < n * nzw; i += K7_NMS_THREADS) nz[oc * nzw + i] = 0ull;
     if (tid == 0) work[b] = 0;
     __syncthreads();
 
@@ -1483,7 +1515,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
     // At least two items per group of the image's CTAs: with few images per launch (a sharded
     // batch) the row-blocks alone leave most SMs idle and the heavy ones become the tail.
     int csplit = nb >= 64 ? 2 : (nb >= 16 ? 4 : 8);
-    {
+    if (nb >= 32) {
         const int want = (2 * (int)gridDim.x * K7_MASK_GROUPS + nb - 1) / nb;
         csplit = max(csplit, min(want, 16));
     }
@@ -1578,7 +1610,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
                         if (crank[grp][j] < mrank)
                             word |= 1ull << j;
                         else if (!diag)   // in a diagonal block thread q meets this pair itself
-                            atomicOr(&tword[grp][j], 1ull << t);
+                            atomicOr(reinterpret_cast<unsigned int*>(&tword[grp][j]) + (t >> 5), 1u << (t & 31));   // native 32-bit ATOMS
                     }
                     if (word) {
                         M[(oc + row) * nbw + cb] = word;
@@ -1609,6 +1641,12 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
 // without a flagged word (most) are kept in round 0 without touching the matrix.
 #define K7_RESOLVE_THREADS 1024
 #define K7_RESOLVE_PER (K7_SORT_MAX / K7_RESOLVE_THREADS)
+// set bit p of a bit set kept as u64 words in shared memory.  A 64-bit atomicOr on shared memory
+// is a compare-and-swap loop (ncu: 45 % of the old kernel's instructions, 64 threads fighting over
+// one word); the 32-bit form is one native ATOMS.OR on the half that holds the bit (little endian).
+__device__ __forceinline__ void k7_set_bit(unsigned long long* set, int p) {
+    atomicOr(reinterpret_cast<unsigned int*>(set) + (p >> 5), 1u << (p & 31));
+}
 // The flagged words of an image (index + 64 bits, 10 bytes) are staged ONCE in shared memory:
 // a round then costs shared-memory latency instead of two dependent trips to L2 per undecided
 // row (ncu at EfficientDet-D7: 77 us per image, all of it long-scoreboard and barrier stalls).
@@ -1636,6 +1674,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     const size_t ob = (size_t)b * A, oc = (size_t)b * cap;
     const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
     const int nw = (n + 63) >> 6;
+    const int nzu = (nw + 63) >> 6;   // summary words that can hold a flag: column-blocks < nw
     for (int w = tid; w < WMAX; w += K7_RESOLVE_THREADS) s_kept[w] = s_rem[w] = s_krank[w] = 0ull;
     __syncthreads();
     uint32_t open_ = 0u;                 // bit k: row tid + k*1024 is still undecided
@@ -1647,7 +1686,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
         const int p = tid + k * K7_RESOLVE_THREADS;
         if (p >= n) continue;
         int c = 0;
-        for (int z = 0; z < nzw; ++z) c += __popcll(__ldcg(nz + (oc + p) * nzw + z));
+        for (int z = 0; z < nzu; ++z) c += __popcll(__ldcg(nz + (oc + p) * nzw + z));
         if (c > 0) {
             open_ |= 1u << k;
             big |= c > 15;
@@ -1657,9 +1696,10 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     }
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        // nothing ranked before it overlaps: kept.  A warp owns 32 consecutive rows = one 32-bit half-word.
         const int p = tid + k * K7_RESOLVE_THREADS;
-        if (p < n && !((open_ >> k) & 1u))
-            atomicOr(&s_kept[p >> 6], 1ull << (p & 63));   // nothing ranked before it overlaps: kept
+        const unsigned kept0 = __ballot_sync(0xffffffffu, p < n && !((open_ >> k) & 1u));
+        if (lane == 0 && kept0) reinterpret_cast<unsigned int*>(s_kept)[p >> 5] = kept0;
     }
     // exclusive scan of the per-thread entry counts
     int inc = mine;
@@ -1686,7 +1726,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
             o &= o - 1u;
             const int p = tid + k * K7_RESOLVE_THREADS;
             const unsigned long long* row = M + (oc + p) * nbw;
-            for (int z = 0; z < nzw; ++z) {
+            for (int z = 0; z < nzu; ++z) {
                 unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
                 while (m) {
                     const int w = (z << 6) + __ffsll((long long)m) - 1;
@@ -1720,10 +1760,10 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
                     }
                     const int p = tid + k * K7_RESOLVE_THREADS;
                     if (any_kept) {
-                        atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
+                        k7_set_bit(s_rem, p);
                         open_ &= ~(1u << k);
                     } else if (all_removed) {
-                        atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
+                        k7_set_bit(s_kept, p);
                         open_ &= ~(1u << k);
                     }
                 }
@@ -1737,7 +1777,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
                 const int p = tid + k * K7_RESOLVE_THREADS;
                 const unsigned long long* row = M + (oc + p) * nbw;
                 bool any_kept = false, all_removed = true;
-                for (int z = 0; z < nzw; ++z) {
+                for (int z = 0; z < nzu; ++z) {
                     unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
                     while (m) {
                         const int w = (z << 6) + __ffsll((long long)m) - 1;
@@ -1750,10 +1790,10 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
                     }
                 }
                 if (any_kept) {
-                    atomicOr(&s_rem[p >> 6], 1ull << (p & 63));
+                    k7_set_bit(s_rem, p);
                     open_ &= ~(1u << k);
                 } else if (all_removed) {
-                    atomicOr(&s_kept[p >> 6], 1ull << (p & 63));
+                    k7_set_bit(s_kept, p);
                     open_ &= ~(1u << k);
                 }
             }
@@ -1770,7 +1810,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
         if (p >= n) continue;
         if ((s_kept[p >> 6] >> (p & 63)) & 1ull) {
             const int r = srank[oc + p];
-            atomicOr(&s_krank[r >> 6], 1ull << (r & 63));
+            k7_set_bit(s_krank, r);
         }
     }
     __syncthreads();
@@ -1948,7 +1988,7 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.cap, w.surv_count, w.bits,
                                                              w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
                                                              w.blk, w.nz, w.nsel, w.work, ca ? w.label : nullptr,
-                                                             ca ? w.slabel : nullptr);
+                                                             ca ? w.slabel : nullptr, w.kept_box);
         K7_LAUNCH_CHECK();
         int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
         const int gx_max = (w.cap / 64 + K7_MASK_GROUPS - 1) / K7_MASK_GROUPS * 4;
@@ -2115,7 +2155,7 @@ static int k7_nms_run(const float* boxes, const float* scores, const int64_t* id
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
         k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.cap, w.small, nullptr, nullptr, nullptr, w.keys0,
                                                              w.keys1, b4, w.sbox, w.srank, w.blk, w.nz, w.small + 1, w.small + 3,
-                                                             idxs ? w.label : nullptr, idxs ? w.slabel : nullptr);
+                                                             idxs ? w.label : nullptr, idxs ? w.slabel : nullptr, w.kept_box);
         K7_LAUNCH_CHECK();
         const int nb = (n + 63) / 64;
         int gx = 4 * k7_sm_count();   // one image: spread its row-blocks (and their column shares) over every SM
