@@ -1,5 +1,6 @@
 // Shared host/device plumbing for libk7det.so (sm_100a only).
 #pragma once
+#include <cstdlib>
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -36,6 +37,39 @@ int k7_check_spec(const K7AnchorSpec* spec, int A);
 int k7_sm_count();
 
 static inline size_t k7_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ------------------------------------------------------------------ programmatic dependent launch
+// Chains of short dependent kernels (sort -> mask -> resolve) pay a launch gap per link.  A kernel
+// launched with k7_launch_pdl may be scheduled while its predecessor in the stream is still running
+// (once every CTA of the predecessor has called k7_pdl_trigger() or exited); it must call
+// k7_pdl_wait() before it touches anything the predecessor wrote - the wait returns when the
+// predecessor grid has completed and its memory is visible.  Both calls are no-ops in a normal launch.
+#ifdef __CUDACC__
+__device__ __forceinline__ void k7_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void k7_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// experiment switch: K7_PDL=<bitmask>, bit i enables the attribute for the i-th k7_launch_pdl call site class
+static inline int& k7_pdl_site() { static thread_local int site = 0; return site; }
+static inline bool k7_pdl_mask_next() {
+    static const int mask = [] { const char* e = getenv("K7_PDL"); return e ? atoi(e) : 14;   /* measured: not for the sort kernel */ }();
+    return (mask >> k7_pdl_site()) & 1;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t k7_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                        Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = k7_pdl_mask_next() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
 
 // ------------------------------------------------------------------ division by a runtime constant
 struct K7FastDiv {

@@ -17,7 +17,7 @@
 //      in a spatial order; k7_mask_kernel (all SMs) builds a sparse suppression bitmask;
 //      k7_resolve_kernel (one CTA per image) resolves greedy NMS as a fixed point.  The result is
 //      identical to the sequential algorithm.  Images with more survivors than the workspace's cap
-//      go through k7_sort_nms_kernel (one CTA, chunks of 1024 boxes).
+//      go through k7_fallback_image (one CTA, chunks of 1024 boxes) inside the resolve kernel.
 #include <math.h>
 #include <string.h>
 
@@ -204,6 +204,7 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
     constexpr int SL = K7_SPIPE_SLICE;
+    k7_pdl_trigger();   // k7_sort_kernel (a dependent launch) may queue behind this grid's CTAs
     K7ScoreDesc* desc = reinterpret_cast<K7ScoreDesc*>(smem + G.off_desc);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + G.off_bars);
     uint64_t* done = full + NS;
@@ -1086,50 +1087,23 @@ __device__ __forceinline__ uint64_t* k7_block_sort(uint64_t* a, uint64_t* b, int
     return k7_block_radix_sort(a, b, n, S.sort);
 }
 
-__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int skip_upto, int32_t* __restrict__ surv_count,
-                   int32_t* __restrict__ kept_count, const uint32_t* __restrict__ bits, int32_t* __restrict__ wprefix,
-                   uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws,
-                   uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box, int32_t* __restrict__ counts_out,
-                   const int32_t* __restrict__ label_ws) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
-    __shared__ int s_carry;
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// One image with more survivors than the multi-SM path is sized for (n > cap): radix / bitonic sort of
+// the keys k7_sort_kernel left in keys0, then NMS in chunks of 1024 boxes, all by one CTA.  Called by
+// k7_resolve_kernel for those images (no launch of its own: it is almost never needed).
+__device__ void k7_fallback_image(int b, int A, float iou_thr, int pre_topk, int max_det,
+                                  const int32_t* __restrict__ surv_count, int32_t* __restrict__ kept_count, uint64_t* keys0,
+                                  uint64_t* keys1, const float4* __restrict__ box_ws, uint64_t* __restrict__ kept_key,
+                                  float4* __restrict__ kept_box, int32_t* __restrict__ counts_out,
+                                  const int32_t* __restrict__ label_ws, K7SortNmsSmem& S) {
     const int n_all = surv_count[b];
-    if (n_all <= skip_upto) return;   // handled by the multi-SM path
     const size_t ob = (size_t)b * A;
-
-    // exclusive popcount prefix over the survivor bitmap: rank of an anchor in the thresholded list
-    if (tid == 0) s_carry = 0;
-    __syncthreads();
-    for (int w0 = 0; w0 < W32; w0 += K7_NMS_THREADS) {
-        const int w = w0 + tid;
-        const int v = (w < W32) ? __popc(bits[(size_t)b * W32 + w]) : 0;
-        int inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) S.sort.wtot[warp] = (unsigned)inc;
-        __syncthreads();
-        int woff = 0;
-        for (int k = 0; k < warp; ++k) woff += (int)S.sort.wtot[k];
-        const int carry = s_carry;
-        if (w < W32) wprefix[(size_t)b * W32 + w] = carry + woff + inc - v;
-        __syncthreads();
-        if (tid == K7_NMS_THREADS - 1) s_carry = carry + woff + inc;
-        __syncthreads();
-    }
-
     uint64_t* sorted = k7_block_sort(keys0 + ob, keys1 + ob, n_all, S);
     int n = n_all;
     if (pre_topk > 0 && n > pre_topk) n = pre_topk;
     const int max_keep = max_det > 0 ? max_det : 0x7fffffff;
     const int kept = k7_block_nms(sorted, n, box_ws + ob, label_ws ? label_ws + ob : nullptr, iou_thr, max_keep,
                                   kept_key + ob, kept_box + ob, S.nms);
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
         kept_count[b] = kept;
         if (counts_out) {
             counts_out[2 * b + 0] = n_all;
@@ -1156,7 +1130,7 @@ k7_sort_nms_kernel(int A, int W32, float iou_thr, int pre_topk, int max_det, int
 //   k7_resolve_kernel  one CTA per image: greedy NMS as a parallel fixed point over those words.
 // Which boxes share a 64-bit word is irrelevant to the result: every bit still says "a higher
 // scored box overlaps me", so the kept set is exactly torchvision.ops.nms's.  Images with more
-// survivors than the workspace's cap fall back to k7_sort_nms_kernel (chunked, one CTA).
+// survivors than the workspace's cap are served by k7_fallback_image (chunked, one CTA) inside k7_resolve_kernel.
 #define K7_SORT_MAX 16384                       // largest cap: 128 KB of keys in shared memory
 #define K7_NZW_MAX (K7_SORT_MAX / 64 / 64)      // u64 words of the per-row summary
 #define K7_CELLS_MAX 4096                       // grid cells of the spatial order, all area binades together
@@ -1192,6 +1166,8 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     __shared__ float4 s_wsum[32];
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t ob = (size_t)b * A;
+    k7_pdl_trigger();   // the mask kernel's CTAs may take their places
+    k7_pdl_wait();      // the score kernel's records
     int n_all;
     if (bits) {
         // Survivor ranks and keys.  A thread owns a contiguous chunk of the image's bitmap words:
@@ -1500,6 +1476,8 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
     __shared__ unsigned int cand[K7_MASK_GROUPS][2];
     __shared__ int s_item[K7_MASK_GROUPS];
     const int b = blockIdx.y;
+    k7_pdl_trigger();
+    k7_pdl_wait();      // k7_sort_kernel's spatial order
     const int n = nsel[b];
     if (n <= 0) return;
     const int nb = (n + 63) >> 6, n32 = (n + 31) >> 5;
@@ -1653,13 +1631,16 @@ __device__ __forceinline__ void k7_set_bit(unsigned long long* set, int p) {
 // Images with more flagged words than this, or a row with more than 15 of them, iterate on
 // the matrix in global memory as before.
 #define K7_RESOLVE_LIST 12288
-#define K7_RESOLVE_SMEM (K7_RESOLVE_LIST * (sizeof(unsigned long long) + sizeof(unsigned short)))
+#define K7_RESOLVE_LIST_BYTES (K7_RESOLVE_LIST * (sizeof(unsigned long long) + sizeof(unsigned short)))
+#define K7_RESOLVE_SMEM (K7_RESOLVE_LIST_BYTES > sizeof(K7SortNmsSmem) ? K7_RESOLVE_LIST_BYTES : sizeof(K7SortNmsSmem))
 __global__ void __launch_bounds__(K7_RESOLVE_THREADS)
 k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
-                  const uint64_t* __restrict__ sorted_keys, const float4* __restrict__ sbox,
+                  uint64_t* sorted_keys, const float4* __restrict__ sbox,
                   const int32_t* __restrict__ srank, const unsigned long long* __restrict__ nz,
                   const unsigned long long* __restrict__ M, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
-                  int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out) {
+                  int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out,
+                  float iou_thr, int pre_topk, uint64_t* keys0, const float4* __restrict__ box_ws,
+                  const int32_t* __restrict__ label_ws) {
     constexpr int WMAX = K7_SORT_MAX / 64;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     unsigned long long* s_l = reinterpret_cast<unsigned long long*>(smem_raw);
@@ -1669,8 +1650,14 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     __shared__ int s_wtot[32];
     __shared__ int s_undecided;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    k7_pdl_trigger();
+    k7_pdl_wait();      // k7_mask_kernel's words
     const int n = nsel[b];
-    if (n < 0) return;   // fallback image
+    if (n < 0) {   // more survivors than the multi-SM path is sized for
+        k7_fallback_image(b, A, iou_thr, pre_topk, max_det, surv_count, kept_count, keys0, sorted_keys, box_ws, kept_key,
+                          kept_box, counts_out, label_ws, *reinterpret_cast<K7SortNmsSmem*>(smem_raw));
+        return;
+    }
     const size_t ob = (size_t)b * A, oc = (size_t)b * cap;
     const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
     const int nw = (n + 63) >> 6;
@@ -1863,6 +1850,7 @@ k7_gather_kernel(int A, int W32, int cap, const int32_t* __restrict__ kept_count
                  float4* __restrict__ boxes, int32_t* __restrict__ anchor_ids, int32_t* __restrict__ ranks) {
     const int b = blockIdx.y;
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    k7_pdl_wait();      // k7_resolve_kernel's kept lists
     const int kc = min(kept_count[b], cap);
     if (k >= kc) return;
     const size_t ob = (size_t)b * A;
@@ -1985,31 +1973,23 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         size_t smem_sort = 64 * 8;
         while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;   // bitonic size of the largest image
         K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_sort_kernel<<<B, K7_NMS_THREADS, smem_sort, st>>>(A, w.W32, params->pre_nms_topk, w.cap, w.surv_count, w.bits,
-                                                             w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
-                                                             w.blk, w.nz, w.nsel, w.work, ca ? w.label : nullptr,
-                                                             ca ? w.slabel : nullptr, w.kept_box);
-        K7_LAUNCH_CHECK();
+        k7_pdl_site() = 0;
+        K7_CUDA(k7_launch_pdl(k7_sort_kernel, dim3(B), dim3(K7_NMS_THREADS), smem_sort, st, A, w.W32, params->pre_nms_topk,
+                              w.cap, w.surv_count, w.bits, w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
+                              w.blk, w.nz, w.nsel, w.work, ca ? w.label : nullptr, ca ? w.slabel : nullptr, w.kept_box));
         int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
         const int gx_max = (w.cap / 64 + K7_MASK_GROUPS - 1) / K7_MASK_GROUPS * 4;
         if (gx > gx_max) gx = gx_max;
         if (gx < 1) gx = 1;
-        k7_mask_kernel<<<dim3(gx, B), K7_MASK_THREADS, 0, st>>>(params->iou_thr, w.cap, w.nsel, w.sbox, w.srank, w.blk, w.nz,
-                                                                w.M, w.work, ca ? w.slabel : nullptr);
-        K7_LAUNCH_CHECK();
+        k7_pdl_site() = 1;
+        K7_CUDA(k7_launch_pdl(k7_mask_kernel, dim3(gx, B), dim3(K7_MASK_THREADS), 0, st, params->iou_thr, w.cap, w.nsel,
+                              w.sbox, w.srank, w.blk, w.nz, w.M, w.work, ca ? w.slabel : nullptr));
         K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
-        k7_resolve_kernel<<<B, K7_RESOLVE_THREADS, K7_RESOLVE_SMEM, st>>>(A, params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1,
-                                                            w.sbox, w.srank, w.nz, w.M, w.kept_key, w.kept_box, w.kept_count,
-                                                            counts, nullptr);
-        K7_LAUNCH_CHECK();
-    }
-    if (A > w.cap) {   // an image can exceed the cap only then
-        const size_t smem = sizeof(K7SortNmsSmem);
-        K7_CUDA(cudaFuncSetAttribute(k7_sort_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k7_sort_nms_kernel<<<B, K7_NMS_THREADS, smem, st>>>(A, w.W32, params->iou_thr, params->pre_nms_topk,
-                                                            params->max_detections, w.cap, w.surv_count, w.kept_count,
-                                                            w.bits, w.wprefix, w.keys0, w.keys1, w.box, w.kept_key,
-                                                            w.kept_box, counts, ca ? w.label : nullptr);
+        k7_pdl_site() = 2;
+        K7_CUDA(k7_launch_pdl(k7_resolve_kernel, dim3(B), dim3(K7_RESOLVE_THREADS), K7_RESOLVE_SMEM, st, A,
+                              params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1, w.sbox, w.srank, w.nz, w.M,
+                              w.kept_key, w.kept_box, w.kept_count, counts, nullptr, params->iou_thr, params->pre_nms_topk,
+                              w.keys0, w.box, ca ? w.label : nullptr));
     }
     K7_LAUNCH_CHECK();
     return K7_OK;
@@ -2043,10 +2023,10 @@ extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, i
         return K7_EWORKSPACE;
     }
     dim3 grid((cap + 255) / 256, B);
-    k7_gather_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(A, w.W32, cap, w.kept_count, w.kept_key, w.kept_box,
-                                                                         w.label, w.bits, w.wprefix, scores, labels,
-                                                                         reinterpret_cast<float4*>(boxes), anchor_ids,
-                                                                         survivor_rank);
+    k7_pdl_site() = 3;
+    K7_CUDA(k7_launch_pdl(k7_gather_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), A, w.W32, cap, w.kept_count,
+                          w.kept_key, w.kept_box, w.label, w.bits, w.wprefix, scores, labels, reinterpret_cast<float4*>(boxes),
+                          anchor_ids, survivor_rank));
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
@@ -2165,7 +2145,7 @@ static int k7_nms_run(const float* boxes, const float* scores, const int64_t* id
         K7_LAUNCH_CHECK();
         K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
         k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, K7_RESOLVE_SMEM, st>>>(n, 0, w.cap, w.small + 1, w.small, w.keys1, w.sbox, w.srank, w.nz,
-                                                            w.M, w.kept_key, w.kept_box, count, nullptr, keep);
+                                                            w.M, w.kept_key, w.kept_box, count, nullptr, keep, iou_thr, 0, nullptr, nullptr, nullptr);
         K7_LAUNCH_CHECK();
         return K7_OK;
     }
