@@ -1506,7 +1506,7 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
         if (wi >= items) break;   // group-uniform
         // heavy row-blocks (many column-blocks below them) first
         const int rb = nb - 1 - wi / csplit, sub = wi % csplit;
-        int turn = 0;
+        int turn = 0, mine_turn = sub;
         const int row = rb * 64 + t;
         const bool rlive = row < n;
         const float4 mb = rlive ? __ldg(bx + row) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1539,7 +1539,8 @@ k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float
             while (cm) {   // group-uniform
                 const int cb = c0 + __ffsll((long long)cm) - 1;
                 cm &= cm - 1ull;
-                if (turn++ % csplit != sub) continue;
+                if (turn++ != mine_turn) continue;   // every csplit-th candidate is this item's (no modulo in the loop)
+                mine_turn += csplit;
                 const int col = cb * 64 + t;
                 const bool diag = cb == rb;
                 asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // previous column-block fully consumed
@@ -1670,6 +1671,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     bool big = false;
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {   // independent loads, no atomics in between
+        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
         const int p = tid + k * K7_RESOLVE_THREADS;
         if (p >= n) continue;
         int c = 0;
@@ -1683,6 +1685,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     }
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
         // nothing ranked before it overlaps: kept.  A warp owns 32 consecutive rows = one 32-bit half-word.
         const int p = tid + k * K7_RESOLVE_THREADS;
         const unsigned kept0 = __ballot_sync(0xffffffffu, p < n && !((open_ >> k) & 1u));
@@ -1793,6 +1796,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     // kept set by rank, then compaction in rank (= visiting) order
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
         const int p = tid + k * K7_RESOLVE_THREADS;
         if (p >= n) continue;
         if ((s_kept[p >> 6] >> (p & 63)) & 1ull) {
@@ -1821,6 +1825,7 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     const int budget = max_det > 0 ? max_det : 0x7fffffff;
 #pragma unroll
     for (int k = 0; k < K7_RESOLVE_PER; ++k) {
+        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
         const int p = tid + k * K7_RESOLVE_THREADS;
         if (p >= n) continue;
         if (!((s_kept[p >> 6] >> (p & 63)) & 1ull)) continue;
