@@ -1178,14 +1178,20 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
         const int w_lo = min(tid * chunk, W32), w_hi = min(w_lo + chunk, W32);
         const uint32_t* brow = bits + (size_t)b * W32;
         int cnt = 0;
-        for (int w = w_lo; w < w_hi; ++w) {
-            uint32_t word = brow[w];
-            cnt += __popc(word);
-            while (word) {
-                const int a = (w << 5) + __ffs(word) - 1;
-                word &= word - 1;
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(score_ws + ob + a));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(box_ws + ob + a));
+        for (int w = w_lo; w < w_hi; w += 4) {   // four words in flight (a thread's chunk is not coalesced)
+            uint32_t wd[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) wd[u] = (w + u < w_hi) ? brow[w + u] : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t word = wd[u];
+                cnt += __popc(word);
+                while (word) {
+                    const int a = ((w + u) << 5) + __ffs(word) - 1;
+                    word &= word - 1;
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(score_ws + ob + a));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(box_ws + ob + a));
+                }
             }
         }
         int inc = cnt;
@@ -1203,19 +1209,47 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
             if (k < warp) slot += t;
             n_all += t;
         }
-        __syncthreads();   // s_wtot is reused below
         if (tid == 0) surv_count[b] = n_all;
         const bool small_ = n_all <= cap;
-        // one key per set bit, written at its rank: shared memory (small image) or keys0 (fallback image)
-        for (int w = w_lo; w < w_hi; ++w) {
-            uint32_t word = brow[w];
-            wprefix[(size_t)b * W32 + w] = slot;
-            while (word) {
-                const int a = (w << 5) + __ffs(word) - 1;
-                word &= word - 1;
-                const uint64_t key = ((uint64_t)k7_score_key_desc(score_ws[ob + a]) << 32) | (uint32_t)a;
-                if (small_) sk[slot] = key; else keys0[ob + slot] = key;
-                ++slot;
+        // the anchor id of every set bit at its rank: shared memory (small image) or keys0 (fallback image)
+        for (int w = w_lo; w < w_hi; w += 4) {
+            uint32_t wd[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) wd[u] = (w + u < w_hi) ? brow[w + u] : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (w + u >= w_hi) break;
+                uint32_t word = wd[u];
+                wprefix[(size_t)b * W32 + w + u] = slot;
+                while (word) {
+                    const uint64_t a = (uint64_t)(((w + u) << 5) + __ffs(word) - 1);
+                    word &= word - 1;
+                    if (small_) sk[slot] = a; else keys0[ob + slot] = a;
+                    ++slot;
+                }
+            }
+        }
+        __syncthreads();   // also: s_wtot is reused below
+        // keys, every thread the same number of them with four score gathers in flight (walking the
+        // bits and gathering in one loop left the whole CTA waiting for the thread with most bits)
+        for (int i0 = 0; i0 < n_all; i0 += 4 * K7_NMS_THREADS) {
+            uint32_t a[4];
+            float sc[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * K7_NMS_THREADS + tid;
+                if (i < n_all) {
+                    a[u] = (uint32_t)(small_ ? sk[i] : keys0[ob + i]);
+                    sc[u] = score_ws[ob + a[u]];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = i0 + u * K7_NMS_THREADS + tid;
+                if (i < n_all) {
+                    const uint64_t key = ((uint64_t)k7_score_key_desc(sc[u]) << 32) | a[u];
+                    if (small_) sk[i] = key; else keys0[ob + i] = key;
+                }
             }
         }
     } else {
@@ -1377,14 +1411,29 @@ k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv
     // scatter: the order inside a cell is whatever the atomics give (it does not affect the result)
     const size_t oc = (size_t)b * cap;
     const int nzw = (cap / 64 + 63) / 64;
-    for (int i = tid; i < n; i += K7_NMS_THREADS) {
-        const int p = atomicAdd(&s_cell[(int)sk[i]], 1);
-        sbox[oc + p] = __ldcg(rbox + ob + i);   // written above by this thread
-        srank[oc + p] = i;
-        if (slabel)   // class-aware NMS
-            slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(__ldcg(keys1 + ob + i) & 0xffffffffull));
+    for (int i0 = 0; i0 < n; i0 += 4 * K7_NMS_THREADS) {
+        float4 bx[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * K7_NMS_THREADS + tid;
+            if (i < n) bx[u] = __ldcg(rbox + ob + i);   // written above by this thread
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * K7_NMS_THREADS + tid;
+            if (i < n) {
+                const int p = atomicAdd(&s_cell[(int)sk[i]], 1);
+                sbox[oc + p] = bx[u];
+                srank[oc + p] = i;
+                if (slabel)   // class-aware NMS
+                    slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(__ldcg(keys1 + ob + i) & 0xffffffffull));
+            }
+        }
     }
-    for (int i = tid; i < n * nzw; i += K7_NMS_THREADS) nz[oc * nzw + i] = 0ull;
+    {   // flags of the rows' non-zero words: only column-blocks < ceil(n/64) can be flagged
+        const int nzu = ((n + 63) / 64 + 63) / 64;
+        for (int i = tid; i < n * nzu; i += K7_NMS_THREADS) nz[(oc + i / nzu) * nzw + i % nzu] = 0ull;
+    }
     if (tid == 0) work[b] = 0;
     __syncthreads();
 
