@@ -363,6 +363,46 @@ def test_detect_class_aware_vs_oracle(name):
     assert more >= 0            # suppression inside a class only can never keep fewer boxes
 
 
+@pytest.mark.parametrize("class_aware", [False, True], ids=["agnostic", "per-class"])
+def test_detect_image_above_the_multi_sm_cap(class_aware):
+    """An image with more survivors than the multi-SM NMS is sized for (16 384) takes the chunked
+    single-CTA path inside the resolve kernel, next to an ordinary image in the same batch."""
+    wl = b200det.synth.WORKLOADS["c1_retinanet_r50_512"]
+    gen = torch.Generator().manual_seed(11)
+    A, Cn = wl.anchors, 2
+    cls, reg = b200det.synth.make_head_outputs(2, A, Cn, gen, logit_mean=-6.0, logit_std=1.0)
+    z = torch.randn((A, Cn), generator=gen) * 1.5 - 3.0                # image 0: about 40 % of the anchors survive
+    cls[0] = torch.sigmoid(z)
+    anc = torch.from_numpy(R.retina_anchors(wl.height, wl.width))
+    ref_boxes = R.clip_boxes_(R.decode_boxes(anc[None], reg), wl.height, wl.width)
+    img = torch.empty(2, 3, wl.height, wl.width, device=DEV)
+    anc_dev = b200det.Anchors()(img)
+    # the NMS oracle runs on the device's own decoded boxes (40 % of 49 104 boxes: with millions of overlapping
+    # pairs an IoU within one ulp of the threshold is likely, and expf differs between CPU and GPU by an ulp)
+    boxes = b200det.ClipBoxes()(b200det.BBoxTransform()(anc_dev, reg.to(DEV)), img).cpu()
+    np.testing.assert_allclose(boxes.numpy(), ref_boxes.numpy(), rtol=1e-5, atol=2e-4)
+    det = b200det.detect(cls.to(DEV), reg.to(DEV), anc_dev, (wl.height, wl.width), class_aware=class_aware, cap=A)
+    from torchvision.ops import nms as tv_nms
+    for b in range(2):
+        sc, lb = cls[b].max(dim=1)
+        surv = torch.nonzero(sc > 0.05).flatten()
+        assert int(det.survivors[b]) == surv.numel()
+        assert (surv.numel() > 16384) == (b == 0)
+        k = int(det.count[b])
+        dev_boxes = det.boxes[b, :k].cpu()
+        # NMS on the device's own boxes of the survivors (bit-exact stage test; decode has its own tests)
+        ids = det.anchor_ids[b, :k].cpu().long()
+        assert torch.equal(dev_boxes, boxes[b][ids])
+        if class_aware:
+            keep = torch.from_numpy(R.batched_nms(boxes[b][surv].numpy(), sc[surv].numpy(), lb[surv].numpy(), 0.5))
+        else:
+            keep = tv_nms(boxes[b][surv], sc[surv], 0.5)
+        assert k == keep.numel()
+        assert np.array_equal(det.survivor_rank[b, :k].cpu().numpy(), keep.numpy())
+        assert np.array_equal(ids.numpy(), surv[keep].numpy())
+        assert np.array_equal(det.labels[b, :k].cpu().numpy(), lb[surv][keep].numpy())
+
+
 def check_detect(det, g, exact_boxes_from=None):
     B = g["classifications"].shape[0]
     for b in range(B):
