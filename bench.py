@@ -295,8 +295,8 @@ def run_b200(args, wl):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.shard else "weak",
         "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
-        "gpu_launches": 10 * args.steps,
-        "launches_per_step": {"k7_match": 1, "k7_loss(stream+rows)": 2, "k7_scale_inplace": 2,
+        "gpu_launches": 9 * args.steps,
+        "launches_per_step": {"k7_match": 1, "k7_loss(stream+rows)": 2, "k7_scale_inplace_multi": 1,
                               "k7_detect(score+sort+mask+resolve)": 4, "k7_detect_gather": 1},
     }
 

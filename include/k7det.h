@@ -197,6 +197,13 @@ K7_API int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, 
  * when the incoming gradient of a loss output is not 1. */
 K7_API int k7_scale_inplace(float* grad, size_t n, const float* scale, void* stream);
 
+/* The same for up to K7_SCALE_MAX tensors in one launch: grads[i][0..n[i]) *= *scales[i] (host arrays of
+ * device pointers / sizes).  The autograd backward of a step scales d(classifications) and d(regressions)
+ * - or the per-level gradients - with it. */
+#define K7_SCALE_MAX 8
+K7_API int k7_scale_inplace_multi(float* const* grads, const size_t* n, const float* const* scales, int count,
+                           void* stream);
+
 /* ---- inference side ----------------------------------------------------------------- */
 
 #define K7_DECODE_RETINA 0 /* utils.py:26-53: (dx,dy,dw,dh) * std + mean around xyxy anchors */

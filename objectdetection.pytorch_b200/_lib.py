@@ -128,6 +128,7 @@ SYMBOLS = {
     "k7_loss_levels": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int,
                                  C.POINTER(K7LossParams), _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "k7_scale_inplace": (C.c_int, [_P, C.c_size_t, _P, _P]),
+    "k7_scale_inplace_multi": (C.c_int, [_P, _P, _P, C.c_int, _P]),
     "k7_decode": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_size_t, _P, C.c_int, C.c_int,
                             C.POINTER(K7DecodeParams), _P, _P]),
     "k7_clip": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),

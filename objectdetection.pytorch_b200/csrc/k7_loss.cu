@@ -974,6 +974,49 @@ extern "C" int k7_scale_inplace(float* grad, size_t n, const float* scale, void*
     return K7_OK;
 }
 
+// several tensors in ONE launch (the two gradients of a step, or the per-level gradients): blockIdx.y = tensor
+struct K7ScaleMulti {
+    float* g[K7_SCALE_MAX];
+    size_t n[K7_SCALE_MAX];
+    const float* scale[K7_SCALE_MAX];
+};
+__global__ void k7_scale_multi_kernel(const __grid_constant__ K7ScaleMulti P) {
+    const int t = blockIdx.y;
+    const float s = __ldg(P.scale[t]);
+    if (s == 1.0f) return;
+    float* g = P.g[t];
+    const size_t n = P.n[t], n4 = n >> 2;
+    float4* g4 = reinterpret_cast<float4*>(g);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        float4 v = g4[i];
+        v.x *= s; v.y *= s; v.z *= s; v.w *= s;
+        g4[i] = v;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) g[(n4 << 2) + threadIdx.x] *= s;
+}
+
+extern "C" int k7_scale_inplace_multi(float* const* grads, const size_t* n, const float* const* scales, int count,
+                                      void* stream) {
+    K7_REQUIRE(grads && n && scales, "k7_scale_inplace_multi: null argument");
+    K7_REQUIRE(count >= 0 && count <= K7_SCALE_MAX, "k7_scale_inplace_multi: count %d outside [0, %d]", count, K7_SCALE_MAX);
+    K7ScaleMulti P;
+    memset(&P, 0, sizeof(P));
+    int m = 0;
+    for (int i = 0; i < count; ++i) {
+        if (n[i] == 0) continue;
+        K7_REQUIRE(grads[i] && scales[i], "k7_scale_inplace_multi: null tensor %d", i);
+        K7_REQUIRE((reinterpret_cast<uintptr_t>(grads[i]) & 15) == 0, "k7_scale_inplace_multi: grad %d must be 16-byte aligned", i);
+        P.g[m] = grads[i];
+        P.n[m] = n[i];
+        P.scale[m] = scales[i];
+        ++m;
+    }
+    if (m == 0) return K7_OK;
+    k7_scale_multi_kernel<<<dim3(k7_sm_count() * 4, m), 256, 0, static_cast<cudaStream_t>(stream)>>>(P);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
 // ------------------------------------------------------------------ host side
 #define K7_LOSS_MAX_GRID 256   // upper bound on CTAs assumed by the workspace query
 

@@ -125,6 +125,20 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     return per_image, sums, dcls, dreg
 
 
+def _scale_grads(pairs, dev):
+    """grad *= incoming gradient (a device scalar; a no-op inside the kernel when it is 1) for every
+    (grad, scale) pair, one launch per eight tensors."""
+    lib = L.lib()
+    with torch.cuda.device(dev):
+        st = L.stream_ptr(dev)
+        for i in range(0, len(pairs), 8):
+            chunk = pairs[i:i + 8]
+            g = L.ptr_array([t for t, _ in chunk])
+            sc = L.ptr_array([x for _, x in chunk])
+            n = (C.c_size_t * len(chunk))(*[t.numel() for t, _ in chunk])
+            L.check(lib.k7_scale_inplace_multi(g, n, sc, len(chunk), st), "k7_scale_inplace_multi")
+
+
 class _FocalLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, cls, reg, anchors, ann, cfg):
@@ -151,6 +165,8 @@ class _FocalLossFn(torch.autograd.Function):
         out = sums[:2] / sums[3]                   # mean over (global) images, losses.py:168
         ctx.save_for_backward(dcls, dreg) if want_grad else None
         ctx.has_grad = want_grad
+        ctx.device = cls.device
+        ctx.set_materialize_grads(False)    # no zero tensors for the outputs nobody differentiates (assign: 12 MB)
         ctx.mark_non_differentiable(num_pos, per_image, assign)
         return out[0:1], out[1:2], num_pos, per_image, assign
 
@@ -159,20 +175,16 @@ class _FocalLossFn(torch.autograd.Function):
         if not ctx.has_grad:
             return None, None, None, None, None
         dcls, dreg = ctx.saved_tensors
-        lib = L.lib()
-        dev = dcls.device
-        with torch.cuda.device(dev):
-            st = L.stream_ptr(dev)
-            if g_cls is not None:
-                gc = g_cls.reshape(-1).float().contiguous()
-                L.check(lib.k7_scale_inplace(L.ptr(dcls), dcls.numel(), L.ptr(gc), st), "k7_scale_inplace")
-            else:
-                dcls = None
-            if g_reg is not None:
-                gr = g_reg.reshape(-1).float().contiguous()
-                L.check(lib.k7_scale_inplace(L.ptr(dreg), dreg.numel(), L.ptr(gr), st), "k7_scale_inplace")
-            else:
-                dreg = None
+        pairs = []
+        if g_cls is not None:
+            pairs.append((dcls, g_cls.reshape(-1).float().contiguous()))
+        else:
+            dcls = None
+        if g_reg is not None:
+            pairs.append((dreg, g_reg.reshape(-1).float().contiguous()))
+        else:
+            dreg = None
+        _scale_grads(pairs, ctx.device)
         return dcls, dreg, None, None, None
 
 
@@ -238,6 +250,8 @@ class _FocalLossLevelsFn(torch.autograd.Function):
         if want_grad:
             ctx.save_for_backward(dreg, *dlevels)
         ctx.has_grad = want_grad
+        ctx.device = reg.device
+        ctx.set_materialize_grads(False)
         ctx.n_levels = len(levels)
         ctx.mark_non_differentiable(num_pos, per_image)
         return out[0:1], out[1:2], num_pos, per_image
@@ -247,21 +261,17 @@ class _FocalLossLevelsFn(torch.autograd.Function):
         if not ctx.has_grad:
             return (None,) * (4 + ctx.n_levels)
         dreg, *dlevels = ctx.saved_tensors
-        lib = L.lib()
-        dev = dreg.device
-        with torch.cuda.device(dev):
-            st = L.stream_ptr(dev)
-            if g_cls is not None:
-                gc = g_cls.reshape(-1).float().contiguous()
-                for t in dlevels:
-                    L.check(lib.k7_scale_inplace(L.ptr(t), t.numel(), L.ptr(gc), st), "k7_scale_inplace")
-            else:
-                dlevels = [None] * len(dlevels)
-            if g_reg is not None:
-                gr = g_reg.reshape(-1).float().contiguous()
-                L.check(lib.k7_scale_inplace(L.ptr(dreg), dreg.numel(), L.ptr(gr), st), "k7_scale_inplace")
-            else:
-                dreg = None
+        pairs = []
+        if g_cls is not None:
+            gc = g_cls.reshape(-1).float().contiguous()
+            pairs += [(t, gc) for t in dlevels]
+        else:
+            dlevels = [None] * len(dlevels)
+        if g_reg is not None:
+            pairs.append((dreg, g_reg.reshape(-1).float().contiguous()))
+        else:
+            dreg = None
+        _scale_grads(pairs, ctx.device)
         return (dreg, None, None, None, *dlevels)
 
 

@@ -226,10 +226,10 @@ def batched_nms(boxes: torch.Tensor, scores: torch.Tensor, idxs: torch.Tensor, i
     "coordinate_trick": torchvision's _batched_nms_coordinate_trick (boxes shifted by
     idxs * (boxes.max() + 1), then plain NMS) - the float32 shift rounds the coordinates, so its result can
     differ from the exact one exactly as torchvision's does;
-    "auto": torchvision's own rule on CUDA (boxes.numel() > 20000 -> vanilla)."""
+    "auto": torchvision 0.26's own rule on CUDA (boxes.numel() > 100_000 -> vanilla)."""
     L.require_cuda(boxes, scores, idxs)
     if strategy == "auto":
-        strategy = "vanilla" if boxes.numel() > 20000 else "coordinate_trick"
+        strategy = "vanilla" if boxes.numel() > 100_000 else "coordinate_trick"
     if strategy == "coordinate_trick":
         if boxes.numel() == 0:
             return torch.empty((0,), dtype=torch.int64, device=boxes.device)
