@@ -338,6 +338,27 @@ def run_b200(args, wl):
         "k7_match_ms": ms_match, "k7_loss_fwd_ms": ms_k_f, "k7_loss_fwd_bwd_ms": ms_k_fb,
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
+    # the same step captured once in a CUDA graph and replayed: what is left when the launch gaps between the
+    # nine kernels (and autograd's small ones) are gone.  Single GPU only: the fused peer exchange numbers its calls.
+    if world == 1:
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    step()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                step()
+            ms_graph = timed(graph.replay, k, 3)
+            out["parts"]["cuda_graph_step"] = {"ms": ms_graph, "images_per_s": B / ms_graph * 1e3,
+                                               "note": "torch.cuda.CUDAGraph capture of the same step() (FocalLoss fwd+bwd + "
+                                                       "detect), replayed; the headline value is the eager step"}
+            del graph
+        except Exception as e:                                   # never let the extra measurement break the line
+            out["parts"]["cuda_graph_step"] = {"error": str(e)[:200]}
+            torch.cuda.synchronize()
     # the same stages fed with the head's pre-sigmoid logits (sigmoid fused), next to the
     # stock elementwise sigmoid pass (and its autograd backward) that they make unnecessary
     z = torch.logit(cls)
