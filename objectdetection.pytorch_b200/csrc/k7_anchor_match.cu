@@ -15,6 +15,7 @@
 // None of this changes a result bit: skipped pairs have IoU == 0, the running maximum starts at
 // (0, index 0) and is only replaced on a strictly greater value, which is torch.max's
 // first-index-on-ties rule (verified against the reference in tests/golden).
+#include <stdlib.h>
 #include <string.h>
 
 #include "k7_common.cuh"
@@ -252,6 +253,265 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant
     }
 }
 
+// ------------------------------------------------------------------ match, cell-mapped (anchors from a recipe)
+// ncu on the anchor-mapped kernel above (C2): 400 instructions per anchor, of which the IoU tests
+// are ~45 - the rest is per-THREAD fixed cost: anchor index -> (level, cell, shape), the double
+// precision cell centre, the warp hull, the cull rounds over the ground truth.  All of that
+// depends on the CELL, not on the anchor.  Here a lane owns a cell of an 8 x 4 tile of one
+// pyramid level and loops over (a group of) the cell's anchor shapes: level / cell / centre /
+// hull / candidate list once per tile, then per shape four double adds for the box and the IoU
+// tests against the tile's candidates.  Results are bit-identical (same arithmetic per pair, same
+// ascending visiting order -> same first-index ties); the hull and the area window are those of
+// ONE level and one group of shapes, i.e. tighter than the anchor-mapped warp's.
+// Work item = (level, tile, shape group); the groups split a tile when an image has too few tiles
+// for the launch.  Ignore bits are OR-ed into a zeroed bitmap (about 1 % of the anchors).
+#define K7_MT_W 8
+#define K7_MT_H 4
+#define K7_MT_MAXG 4
+struct K7MatchTiles {
+    int item0[K7_MAX_LEVELS + 1];   // first work item of each level
+    int tiles_x[K7_MAX_LEVELS];
+    int groups, gsize;              // shape groups per tile, shapes per group
+    double hb[K7_MAX_LEVELS][K7_MT_MAXG][4];   // hull of the group's shapes around the cell centre (x1, y1, x2, y2)
+    float amin[K7_MAX_LEVELS][K7_MT_MAXG], amax[K7_MAX_LEVELS][K7_MT_MAXG];
+    float wmax[K7_MAX_LEVELS][K7_MT_MAXG], hmax[K7_MAX_LEVELS][K7_MT_MAXG];
+};
+
+template <bool CULL>
+__global__ void __launch_bounds__(K7_MATCH_THREADS)
+k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7MatchTiles T,
+                      const float* __restrict__ annotations, int A, int M, float neg_thr, float pos_thr,
+                      int32_t* __restrict__ assign, int32_t* __restrict__ num_pos, float* __restrict__ iou_max_out,
+                      int32_t* __restrict__ argmax_out, float4* __restrict__ zero_fill4, uint32_t* __restrict__ ignore_bits,
+                      int W) {
+    extern __shared__ float smem[];
+    float4* gbox = reinterpret_cast<float4*>(smem);
+    float* gar = smem + 4 * M;
+    int* grow = reinterpret_cast<int*>(gar + M);
+    __shared__ int s_valid;
+    __shared__ int s_pos[K7_MATCH_THREADS / 32];
+
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int* cl = grow + M + warp * M;   // this warp's candidate list
+    // with one shape group per tile, a tile row is ONE run of 8*K consecutive anchors: the words are
+    // staged here and stored (with the zero fill) as full lines - lane-per-cell stores are 36 / 144
+    // bytes apart and cost more than the kernel at EfficientDet-D7 (28 M anchors per batch)
+    const int K = spec.cell_anchors;
+    const bool staged = T.groups == 1;
+    int* so = grow + M + (K7_MATCH_THREADS / 32) * M + warp * (K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS);
+    const float* ann = annotations + (size_t)b * M * 5;
+
+    // order-preserving compaction of rows with label != -1 (losses.py:50), by warp 0
+    if (warp == 0) {
+        int base = 0;
+        for (int m0 = 0; m0 < M; m0 += 32) {
+            const int m = m0 + lane;
+            float r0 = 0.f, r1 = 0.f, r2 = 0.f, r3 = 0.f, r4 = -1.f;
+            if (m < M) {
+                r0 = __ldg(ann + m * 5 + 0); r1 = __ldg(ann + m * 5 + 1); r2 = __ldg(ann + m * 5 + 2);
+                r3 = __ldg(ann + m * 5 + 3); r4 = __ldg(ann + m * 5 + 4);
+            }
+            const bool ok = (m < M) && (r4 != -1.0f);
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const int p = base + __popc(bal & ((1u << lane) - 1u));
+                gbox[p] = make_float4(r0, r1, r2, r3);
+                gar[p] = k7_area(r0, r1, r2, r3);
+                grow[p] = m;
+            }
+            base += __popc(bal);
+        }
+        if (lane == 0) s_valid = base;
+    }
+    __syncthreads();
+    const int nv = s_valid;
+    if (nv == 0) {   // no annotation: every anchor is ignored (losses.py:52-60 skips the image)
+        for (int a = blockIdx.x * K7_MATCH_THREADS + threadIdx.x; a < A; a += gridDim.x * K7_MATCH_THREADS) {
+            const size_t o = (size_t)b * A + a;
+            assign[o] = K7_STATE_IGNORE;
+            if (iou_max_out) iou_max_out[o] = 0.0f;
+            if (argmax_out) argmax_out[o] = -1;
+            if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (ignore_bits)
+            for (int w = blockIdx.x * K7_MATCH_THREADS + threadIdx.x; w < W; w += gridDim.x * K7_MATCH_THREADS) {
+                const int left = A - (w << 5);
+                ignore_bits[(size_t)b * W + w] = left >= 32 ? 0xffffffffu : (left > 0 ? (1u << left) - 1u : 0u);
+            }
+        return;
+    }
+    const float c_lo = neg_thr * (1.0f - 1e-4f);                      // area window / bound, with margin
+    const float c_in = neg_thr / (1.0f + neg_thr) * (1.0f - 1e-4f);
+    const int total_items = T.item0[spec.num_levels];
+    int pos_total = 0;
+
+    for (int item = blockIdx.x * (K7_MATCH_THREADS / 32) + warp; item < total_items;
+         item += gridDim.x * (K7_MATCH_THREADS / 32)) {
+        int l = 0;
+        while (l + 1 < spec.num_levels && item >= T.item0[l + 1]) ++l;   // warp-uniform
+        int t = item - T.item0[l];
+        const int grp = t % T.groups;
+        t /= T.groups;
+        const int tyi = t / T.tiles_x[l], txi = t - tyi * T.tiles_x[l];
+        const int fw = spec.fw[l], fh = spec.fh[l];
+        const int x = txi * K7_MT_W + (lane & (K7_MT_W - 1)), y = tyi * K7_MT_H + (lane / K7_MT_W);
+        const bool live = x < fw && y < fh;
+        const double st = spec.stride[l];
+        const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), st);
+        const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), st);
+        // hull of the tile's anchors of this group (float rounding is monotone: the hull of the
+        // rounded extremes contains every rounded anchor)
+        float hx1 = live ? __double2float_rn(__dadd_rn(T.hb[l][grp][0], sx)) : 3.0e38f;
+        float hy1 = live ? __double2float_rn(__dadd_rn(T.hb[l][grp][1], sy)) : 3.0e38f;
+        float hx2 = live ? __double2float_rn(__dadd_rn(T.hb[l][grp][2], sx)) : -3.0e38f;
+        float hy2 = live ? __double2float_rn(__dadd_rn(T.hb[l][grp][3], sy)) : -3.0e38f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            hx1 = fminf(hx1, __shfl_xor_sync(0xffffffffu, hx1, o));
+            hy1 = fminf(hy1, __shfl_xor_sync(0xffffffffu, hy1, o));
+            hx2 = fmaxf(hx2, __shfl_xor_sync(0xffffffffu, hx2, o));
+            hy2 = fmaxf(hy2, __shfl_xor_sync(0xffffffffu, hy2, o));
+        }
+        const float amin = T.amin[l][grp], amax = T.amax[l][grp], wmax = T.wmax[l][grp], hmax = T.hmax[l][grp];
+        // candidate ground truth of the tile, ascending
+        int nc = 0;
+        for (int g0 = 0; g0 < nv; g0 += 32) {
+            const int g = g0 + lane;
+            bool cand = false;
+            if (g < nv) {
+                const float4 gb = gbox[g];
+                const float ow = fminf(hx2, gb.z) - fmaxf(hx1, gb.x), oh = fminf(hy2, gb.w) - fmaxf(hy1, gb.y);
+                cand = (ow > 0.0f) && (oh > 0.0f);
+                if (CULL) {
+                    const float ag = gar[g];
+                    const float ub = fminf(ow, wmax) * fminf(oh, hmax);
+                    cand = cand && (ag >= c_lo * amin) && (ag * c_lo <= amax) && (ub >= c_in * (amin + ag));
+                }
+            }
+            const unsigned cm = __ballot_sync(0xffffffffu, cand);
+            if (cand) cl[nc + __popc(cm & ((1u << lane) - 1u))] = g;
+            nc += __popc(cm);
+        }
+        __syncwarp();
+        const int k0 = grp * T.gsize, k1 = min(k0 + T.gsize, K);
+        for (int k = k0; k < k1; ++k) {
+            const double* bb = spec.base[l][k];
+            float ax1, ay1, ax2, ay2;
+            if (spec.box_order == K7_BOX_XYXY) {
+                ax1 = __double2float_rn(__dadd_rn(bb[0], sx));
+                ay1 = __double2float_rn(__dadd_rn(bb[1], sy));
+                ax2 = __double2float_rn(__dadd_rn(bb[2], sx));
+                ay2 = __double2float_rn(__dadd_rn(bb[3], sy));
+            } else {
+                ay1 = __double2float_rn(__dadd_rn(bb[0], sy));
+                ax1 = __double2float_rn(__dadd_rn(bb[1], sx));
+                ay2 = __double2float_rn(__dadd_rn(bb[2], sy));
+                ax2 = __double2float_rn(__dadd_rn(bb[3], sx));
+            }
+            const float area_a = k7_area(ax1, ay1, ax2, ay2);
+            float best = 0.0f;
+            int besti = 0;
+            for (int c = 0; c < nc; ++c) {
+                const int j = cl[c];
+                const float4 gb = gbox[j];
+                const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, area_a, gb.x, gb.y, gb.z, gb.w, gar[j]);
+                if (iou > best) {
+                    best = iou;
+                    besti = j;
+                }
+            }
+            int state = K7_STATE_IGNORE;
+            if (best < neg_thr) state = K7_STATE_NEG;
+            if (best >= pos_thr) state = K7_STATE_POS;
+            if (live) {
+                const int a = spec.offset[l] + (y * fw + x) * K + k;
+                const size_t o = (size_t)b * A + a;
+                const int word = (grow[besti] << 2) | state;
+                if (staged) {
+                    so[((lane / K7_MT_W) * K7_MT_W + (lane & (K7_MT_W - 1))) * K + k] = word;
+                } else {
+                    assign[o] = word;
+                    if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                if (iou_max_out) iou_max_out[o] = best;
+                if (argmax_out) argmax_out[o] = besti;
+                if (ignore_bits && state == K7_STATE_IGNORE) atomicOr(ignore_bits + (size_t)b * W + (a >> 5), 1u << (a & 31));
+                pos_total += state == K7_STATE_POS ? 1 : 0;
+            }
+        }
+        __syncwarp();   // the candidate list is rewritten by the next item
+        if (staged) {
+            const int ncell = min(K7_MT_W, fw - txi * K7_MT_W), run = ncell * K;
+            for (int r = 0; r < K7_MT_H; ++r) {
+                const int yr = tyi * K7_MT_H + r;
+                if (yr >= fh) break;
+                const size_t o0 = (size_t)b * A + spec.offset[l] + (size_t)(yr * fw + txi * K7_MT_W) * K;
+                for (int i = lane; i < run; i += 32) {
+                    assign[o0 + i] = so[r * K7_MT_W * K + i];
+                    if (zero_fill4) zero_fill4[o0 + i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            __syncwarp();
+        }
+    }
+
+    pos_total = k7_warp_sum(pos_total);
+    if (lane == 0) s_pos[warp] = pos_total;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tsum = 0;
+#pragma unroll
+        for (int w = 0; w < K7_MATCH_THREADS / 32; ++w) tsum += s_pos[w];
+        if (tsum) atomicAdd(num_pos + b, tsum);   // integer: order independent, exact
+    }
+}
+
+// work items and per-(level, group) culling extremes of the cell-mapped kernel
+static void k7_match_tiles(const K7AnchorSpec* s, int B, K7MatchTiles* T) {
+    memset(T, 0, sizeof(*T));
+    const int K = s->cell_anchors;
+    int tiles = 0;
+    for (int l = 0; l < s->num_levels; ++l)
+        tiles += ((s->fw[l] + K7_MT_W - 1) / K7_MT_W) * ((s->fh[l] + K7_MT_H - 1) / K7_MT_H);
+    // enough items for three per resident warp of the image's share of the launch
+    const long long warps_per_image = (8ll * k7_sm_count() * (K7_MATCH_THREADS / 32) + B - 1) / B;
+    int groups = 1;
+    while (groups < K && groups < K7_MT_MAXG && (long long)tiles * groups < 3 * warps_per_image) ++groups;
+    T->gsize = (K + groups - 1) / groups;
+    T->groups = (K + T->gsize - 1) / T->gsize;
+    int item = 0;
+    for (int l = 0; l < s->num_levels; ++l) {
+        T->item0[l] = item;
+        T->tiles_x[l] = (s->fw[l] + K7_MT_W - 1) / K7_MT_W;
+        item += T->tiles_x[l] * ((s->fh[l] + K7_MT_H - 1) / K7_MT_H) * T->groups;
+        for (int g = 0; g < T->groups; ++g) {
+            double hx1 = 1e300, hy1 = 1e300, hx2 = -1e300, hy2 = -1e300, amin = 1e300, amax = 0, wmax = 0, hmax = 0;
+            for (int k = g * T->gsize; k < K && k < (g + 1) * T->gsize; ++k) {
+                const double* bq = s->base[l][k];
+                const bool xy = s->box_order == K7_BOX_XYXY;
+                const double x1 = xy ? bq[0] : bq[1], y1 = xy ? bq[1] : bq[0], x2 = xy ? bq[2] : bq[3], y2 = xy ? bq[3] : bq[2];
+                const double w = x2 - x1, h = y2 - y1, ar = w * h;
+                if (x1 < hx1) hx1 = x1;
+                if (y1 < hy1) hy1 = y1;
+                if (x2 > hx2) hx2 = x2;
+                if (y2 > hy2) hy2 = y2;
+                if (ar < amin) amin = ar;
+                if (ar > amax) amax = ar;
+                if (w > wmax) wmax = w;
+                if (h > hmax) hmax = h;
+            }
+            T->hb[l][g][0] = hx1; T->hb[l][g][1] = hy1; T->hb[l][g][2] = hx2; T->hb[l][g][3] = hy2;
+            // outward rounding: the device compares float areas of float-rounded anchors against these
+            T->amin[l][g] = (float)(amin * (1.0 - 1e-5));
+            T->amax[l][g] = (float)(amax * (1.0 + 1e-5));
+            T->wmax[l][g] = (float)(wmax * (1.0 + 1e-5) + 1e-3);
+            T->hmax[l][g] = (float)(hmax * (1.0 + 1e-5) + 1e-3);
+        }
+    }
+    for (int l = s->num_levels; l <= K7_MAX_LEVELS; ++l) T->item0[l] = item;
+}
+
 static void k7_match_aux(const K7AnchorSpec* s, K7MatchAux* x) {
     memset(x, 0, sizeof(*x));
     x->div_k = k7_fastdiv_make((uint32_t)s->cell_anchors);
@@ -310,6 +570,27 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     // the exact arg-max of every anchor is only needed for the debug outputs; thresholds outside (0,1) disable culling
     const bool cull = !iou_max && !argmax && params->neg_thr > 1e-3f && params->neg_thr < 1.0f &&
                       params->pos_thr >= params->neg_thr;
+    static const bool cells_on = [] { const char* e = getenv("K7_MATCH_CELLS"); return !e || atoi(e) != 0; }();
+    if (spec && cells_on && (size_t)M * (6 + K7_MATCH_THREADS / 32) * sizeof(float) <= 160 * 1024) {   // anchors from a recipe: the cell-mapped kernel
+        K7MatchTiles T;
+        k7_match_tiles(spec, B, &T);
+        const size_t smem_c = ((size_t)M * (6 + K7_MATCH_THREADS / 32) +
+                               (K7_MATCH_THREADS / 32) * K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS) * sizeof(float);
+        const int W = (int)K7_IGNORE_WORDS(A);
+        if (ignore_bits) K7_CUDA(cudaMemsetAsync(ignore_bits, 0, sizeof(uint32_t) * (size_t)B * W, st));
+        const int items = T.item0[spec->num_levels];
+        int gxc = (items + K7_MATCH_THREADS / 32 - 1) / (K7_MATCH_THREADS / 32);
+        const int gx_cap = (8 * k7_sm_count() + B - 1) / B;
+        if (gxc > gx_cap) gxc = gx_cap;
+        if (gxc < 1) gxc = 1;
+        auto kern = cull ? k7_match_cells_kernel<true> : k7_match_cells_kernel<false>;
+        if (smem_c > 48 * 1024) K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
+        kern<<<dim3(gxc, B), K7_MATCH_THREADS, smem_c, st>>>(*spec, T, annotations, A, M, params->neg_thr, params->pos_thr,
+                                                              assign, num_pos, iou_max, argmax,
+                                                              reinterpret_cast<float4*>(zero_fill4), ignore_bits, W);
+        K7_LAUNCH_CHECK();
+        return K7_OK;
+    }
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
 #define K7_MATCH_LAUNCH(SP, CU)                                                                                          \
