@@ -302,11 +302,13 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     int* so = grow + M + (K7_MATCH_THREADS / 32) * M + warp * (K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS);
     const float* ann = annotations + (size_t)b * M * 5;
 
-    // order-preserving compaction of rows with label != -1 (losses.py:50), by warp 0
-    if (warp == 0) {
+    // order-preserving compaction of rows with label != -1 (losses.py:50): every warp takes 32 rows per round
+    // (one round for M <= 256: a single load latency instead of one per 32 rows)
+    {
+        __shared__ int s_cnt[K7_MATCH_THREADS / 32];
         int base = 0;
-        for (int m0 = 0; m0 < M; m0 += 32) {
-            const int m = m0 + lane;
+        for (int m0 = 0; m0 < M; m0 += K7_MATCH_THREADS) {
+            const int m = m0 + threadIdx.x;
             float r0 = 0.f, r1 = 0.f, r2 = 0.f, r3 = 0.f, r4 = -1.f;
             if (m < M) {
                 r0 = __ldg(ann + m * 5 + 0); r1 = __ldg(ann + m * 5 + 1); r2 = __ldg(ann + m * 5 + 2);
@@ -314,15 +316,25 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
             }
             const bool ok = (m < M) && (r4 != -1.0f);
             const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) s_cnt[warp] = __popc(bal);
+            __syncthreads();
+            int before = base, total = 0;
+#pragma unroll
+            for (int w = 0; w < K7_MATCH_THREADS / 32; ++w) {
+                const int c = s_cnt[w];
+                if (w < warp) before += c;
+                total += c;
+            }
             if (ok) {
-                const int p = base + __popc(bal & ((1u << lane) - 1u));
+                const int p = before + __popc(bal & ((1u << lane) - 1u));
                 gbox[p] = make_float4(r0, r1, r2, r3);
                 gar[p] = k7_area(r0, r1, r2, r3);
                 grow[p] = m;
             }
-            base += __popc(bal);
+            base += total;
+            __syncthreads();
         }
-        if (lane == 0) s_valid = base;
+        if (threadIdx.x == 0) s_valid = base;
     }
     __syncthreads();
     const int nv = s_valid;
@@ -346,8 +358,10 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     const int total_items = T.item0[spec.num_levels];
     int pos_total = 0;
 
-    for (int item = blockIdx.x * (K7_MATCH_THREADS / 32) + warp; item < total_items;
-         item += gridDim.x * (K7_MATCH_THREADS / 32)) {
+    // coarse levels first: their tiles meet the most ground truth and would otherwise be the tail
+    for (int it = blockIdx.x * (K7_MATCH_THREADS / 32) + warp; it < total_items;
+         it += gridDim.x * (K7_MATCH_THREADS / 32)) {
+        const int item = total_items - 1 - it;
         int l = 0;
         while (l + 1 < spec.num_levels && item >= T.item0[l + 1]) ++l;   // warp-uniform
         int t = item - T.item0[l];

@@ -25,7 +25,7 @@ def main():
     hdr = rows[0]
     ik, iv, ig = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
     seq = [(short(r[ik]), float(r[iv]) / 1e3, r[ig]) for r in rows[1:]]
-    starts = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_match_kernel")]
+    starts = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_match_")]
     ends = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_gather_kernel")]
     print(f"{len(seq)} launches captured; k7_match launches: {len(starts)}")
     if len(starts) >= 5 and len(ends) >= 5:
