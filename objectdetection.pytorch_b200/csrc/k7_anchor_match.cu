@@ -265,6 +265,9 @@ k7_match_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant
 // ONE level and one group of shapes, i.e. tighter than the anchor-mapped warp's.
 // Work item = (level, tile, shape group); the groups split a tile when an image has too few tiles
 // for the launch.  Ignore bits are OR-ed into a zeroed bitmap (about 1 % of the anchors).
+#ifndef K7_MC_THREADS
+#define K7_MC_THREADS 128   // warps of a CTA wait for its slowest one: small CTAs waste less
+#endif
 #define K7_MT_W 8
 #define K7_MT_H 4
 #define K7_MT_MAXG 4
@@ -278,7 +281,7 @@ struct K7MatchTiles {
 };
 
 template <bool CULL>
-__global__ void __launch_bounds__(K7_MATCH_THREADS)
+__global__ void __launch_bounds__(K7_MC_THREADS)
 k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7MatchTiles T,
                       const float* __restrict__ annotations, int A, int M, float neg_thr, float pos_thr,
                       int32_t* __restrict__ assign, int32_t* __restrict__ num_pos, float* __restrict__ iou_max_out,
@@ -289,7 +292,7 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     float* gar = smem + 4 * M;
     int* grow = reinterpret_cast<int*>(gar + M);
     __shared__ int s_valid;
-    __shared__ int s_pos[K7_MATCH_THREADS / 32];
+    __shared__ int s_pos[K7_MC_THREADS / 32];
 
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -299,15 +302,15 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     // bytes apart and cost more than the kernel at EfficientDet-D7 (28 M anchors per batch)
     const int K = spec.cell_anchors;
     const bool staged = T.groups == 1;
-    int* so = grow + M + (K7_MATCH_THREADS / 32) * M + warp * (K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS);
+    int* so = grow + M + (K7_MC_THREADS / 32) * M + warp * (K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS);
     const float* ann = annotations + (size_t)b * M * 5;
 
     // order-preserving compaction of rows with label != -1 (losses.py:50): every warp takes 32 rows per round
     // (one round for M <= 256: a single load latency instead of one per 32 rows)
     {
-        __shared__ int s_cnt[K7_MATCH_THREADS / 32];
+        __shared__ int s_cnt[K7_MC_THREADS / 32];
         int base = 0;
-        for (int m0 = 0; m0 < M; m0 += K7_MATCH_THREADS) {
+        for (int m0 = 0; m0 < M; m0 += K7_MC_THREADS) {
             const int m = m0 + threadIdx.x;
             float r0 = 0.f, r1 = 0.f, r2 = 0.f, r3 = 0.f, r4 = -1.f;
             if (m < M) {
@@ -320,7 +323,7 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
             __syncthreads();
             int before = base, total = 0;
 #pragma unroll
-            for (int w = 0; w < K7_MATCH_THREADS / 32; ++w) {
+            for (int w = 0; w < K7_MC_THREADS / 32; ++w) {
                 const int c = s_cnt[w];
                 if (w < warp) before += c;
                 total += c;
@@ -339,7 +342,7 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     __syncthreads();
     const int nv = s_valid;
     if (nv == 0) {   // no annotation: every anchor is ignored (losses.py:52-60 skips the image)
-        for (int a = blockIdx.x * K7_MATCH_THREADS + threadIdx.x; a < A; a += gridDim.x * K7_MATCH_THREADS) {
+        for (int a = blockIdx.x * K7_MC_THREADS + threadIdx.x; a < A; a += gridDim.x * K7_MC_THREADS) {
             const size_t o = (size_t)b * A + a;
             assign[o] = K7_STATE_IGNORE;
             if (iou_max_out) iou_max_out[o] = 0.0f;
@@ -347,7 +350,7 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
             if (zero_fill4) zero_fill4[o] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (ignore_bits)
-            for (int w = blockIdx.x * K7_MATCH_THREADS + threadIdx.x; w < W; w += gridDim.x * K7_MATCH_THREADS) {
+            for (int w = blockIdx.x * K7_MC_THREADS + threadIdx.x; w < W; w += gridDim.x * K7_MC_THREADS) {
                 const int left = A - (w << 5);
                 ignore_bits[(size_t)b * W + w] = left >= 32 ? 0xffffffffu : (left > 0 ? (1u << left) - 1u : 0u);
             }
@@ -359,8 +362,8 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     int pos_total = 0;
 
     // coarse levels first: their tiles meet the most ground truth and would otherwise be the tail
-    for (int it = blockIdx.x * (K7_MATCH_THREADS / 32) + warp; it < total_items;
-         it += gridDim.x * (K7_MATCH_THREADS / 32)) {
+    for (int it = blockIdx.x * (K7_MC_THREADS / 32) + warp; it < total_items;
+         it += gridDim.x * (K7_MC_THREADS / 32)) {
         const int item = total_items - 1 - it;
         int l = 0;
         while (l + 1 < spec.num_levels && item >= T.item0[l + 1]) ++l;   // warp-uniform
@@ -476,7 +479,7 @@ k7_match_cells_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_co
     if (threadIdx.x == 0) {
         int tsum = 0;
 #pragma unroll
-        for (int w = 0; w < K7_MATCH_THREADS / 32; ++w) tsum += s_pos[w];
+        for (int w = 0; w < K7_MC_THREADS / 32; ++w) tsum += s_pos[w];
         if (tsum) atomicAdd(num_pos + b, tsum);   // integer: order independent, exact
     }
 }
@@ -489,7 +492,7 @@ static void k7_match_tiles(const K7AnchorSpec* s, int B, K7MatchTiles* T) {
     for (int l = 0; l < s->num_levels; ++l)
         tiles += ((s->fw[l] + K7_MT_W - 1) / K7_MT_W) * ((s->fh[l] + K7_MT_H - 1) / K7_MT_H);
     // enough items for three per resident warp of the image's share of the launch
-    const long long warps_per_image = (8ll * k7_sm_count() * (K7_MATCH_THREADS / 32) + B - 1) / B;
+    const long long warps_per_image = (8ll * (256 / K7_MC_THREADS) * k7_sm_count() * (K7_MC_THREADS / 32) + B - 1) / B;
     int groups = 1;
     while (groups < K && groups < K7_MT_MAXG && (long long)tiles * groups < 3 * warps_per_image) ++groups;
     T->gsize = (K + groups - 1) / groups;
@@ -585,21 +588,21 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     const bool cull = !iou_max && !argmax && params->neg_thr > 1e-3f && params->neg_thr < 1.0f &&
                       params->pos_thr >= params->neg_thr;
     static const bool cells_on = [] { const char* e = getenv("K7_MATCH_CELLS"); return !e || atoi(e) != 0; }();
-    if (spec && cells_on && (size_t)M * (6 + K7_MATCH_THREADS / 32) * sizeof(float) <= 160 * 1024) {   // anchors from a recipe: the cell-mapped kernel
+    if (spec && cells_on && (size_t)M * (6 + K7_MC_THREADS / 32) * sizeof(float) <= 160 * 1024) {   // anchors from a recipe: the cell-mapped kernel
         K7MatchTiles T;
         k7_match_tiles(spec, B, &T);
-        const size_t smem_c = ((size_t)M * (6 + K7_MATCH_THREADS / 32) +
-                               (K7_MATCH_THREADS / 32) * K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS) * sizeof(float);
+        const size_t smem_c = ((size_t)M * (6 + K7_MC_THREADS / 32) +
+                               (K7_MC_THREADS / 32) * K7_MT_H * K7_MT_W * K7_MAX_CELL_ANCHORS) * sizeof(float);
         const int W = (int)K7_IGNORE_WORDS(A);
         if (ignore_bits) K7_CUDA(cudaMemsetAsync(ignore_bits, 0, sizeof(uint32_t) * (size_t)B * W, st));
         const int items = T.item0[spec->num_levels];
-        int gxc = (items + K7_MATCH_THREADS / 32 - 1) / (K7_MATCH_THREADS / 32);
-        const int gx_cap = (8 * k7_sm_count() + B - 1) / B;
+        int gxc = (items + K7_MC_THREADS / 32 - 1) / (K7_MC_THREADS / 32);
+        const int gx_cap = (8 * (256 / K7_MC_THREADS) * k7_sm_count() + B - 1) / B;
         if (gxc > gx_cap) gxc = gx_cap;
         if (gxc < 1) gxc = 1;
         auto kern = cull ? k7_match_cells_kernel<true> : k7_match_cells_kernel<false>;
         if (smem_c > 48 * 1024) K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
-        kern<<<dim3(gxc, B), K7_MATCH_THREADS, smem_c, st>>>(*spec, T, annotations, A, M, params->neg_thr, params->pos_thr,
+        kern<<<dim3(gxc, B), K7_MC_THREADS, smem_c, st>>>(*spec, T, annotations, A, M, params->neg_thr, params->pos_thr,
                                                               assign, num_pos, iou_max, argmax,
                                                               reinterpret_cast<float4*>(zero_fill4), ignore_bits, W);
         K7_LAUNCH_CHECK();
