@@ -92,6 +92,11 @@ def test_no_cpu_fallback():
     with pytest.raises(RuntimeError):
         b200det.nms(torch.rand(4, 4), torch.rand(4), 0.5)
     with pytest.raises(RuntimeError):
+        b200det.batched_nms(torch.rand(4, 4), torch.rand(4), torch.zeros(4, dtype=torch.int64), 0.5)
+    for strategy in ("coordinate_trick", "auto"):                 # these reach nms() after a few torch ops
+        with pytest.raises(RuntimeError):
+            b200det.batched_nms(torch.rand(4, 4), torch.rand(4), torch.zeros(4, dtype=torch.int64), 0.5, strategy=strategy)
+    with pytest.raises(RuntimeError):
         det = b200det.BatchDetections(torch.tensor([1]), torch.tensor([1]), torch.rand(1, 2), torch.zeros(1, 2, dtype=torch.int64),
                                       torch.rand(1, 2, 4), torch.zeros(1, 2, dtype=torch.int32), torch.zeros(1, 2, dtype=torch.int32))
         b200det.eval_pack(det, [1.0], num_classes=3)
@@ -106,6 +111,13 @@ def test_argument_validation_without_gpu():
     lib = L.lib()
     assert lib.k7_loss_workspace_bytes(0, 10, 10) == 0
     assert lib.k7_detect_workspace_bytes(2, 1000, 3) > 2 * 1000 * 56
+    # argument checks of the entry points added last (no device work happens before they fail)
+    assert lib.k7_batched_nms(None, None, None, 5, C.c_float(0.5), None, C.c_void_p(16), C.c_void_p(256), 1 << 20, None) == -1
+    assert b"k7_batched_nms" in lib.k7_last_error()
+    assert lib.k7_scale_inplace_multi(None, None, None, 1, None) == -1
+    three = (C.c_void_p * 3)(16, 32, 48)
+    n3 = (C.c_size_t * 3)(4, 4, 4)
+    assert lib.k7_scale_inplace_multi(three, n3, three, 9, None) == -1 and b"count" in lib.k7_last_error()
     sp = b200det.Anchors().spec_for(64, 64)
     sp.total += 1
     rc = lib.k7_anchors_materialize(C.byref(sp), C.c_void_p(16), None)
