@@ -762,6 +762,42 @@ def test_detect_on_head_levels(shape, mean, from_logits):
         assert np.array_equal(a.labels[b, :k].cpu().numpy(), d.labels.numpy())
 
 
+def test_detect_class_aware_on_head_levels_and_options():
+    """Per-class suppression on the head's level tensors == on the flat tensor (logits), keeps at least as many
+    boxes as the class-agnostic form, and composes with max_detections / pre_nms_topk."""
+    B, C, H, W = 3, 11, 160, 224
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    spec = b200det.spec_of(anc)
+    K, A = spec.cell_anchors, spec.total
+    gen = torch.Generator().manual_seed(78)
+    lv = [t.to(DEV) for t in _make_levels(spec, B, C, gen, mean=-3.5, std=1.5)]
+    reg = (torch.randn((B, A, 4), generator=gen) * 0.5).to(DEV)
+    flat = R.head_logits(lv, K, C)
+    a = b200det.detect(lv, reg, anc, (H, W), from_logits=True, class_aware=True)
+    w = b200det.detect(flat, reg, anc, (H, W), from_logits=True, class_aware=True)
+    g = b200det.detect(flat, reg, anc, (H, W), from_logits=True)
+    assert a.count.tolist() == w.count.tolist()
+    assert all(int(x) >= int(y) for x, y in zip(w.count, g.count)) and int(w.count.sum()) > int(g.count.sum())
+    for b in range(B):
+        k = int(w.count[b])
+        assert torch.equal(a.anchor_ids[b, :k], w.anchor_ids[b, :k]) and torch.equal(a.labels[b, :k], w.labels[b, :k])
+        # oracle on the device's own survivors: boxes / scores / labels by anchor id
+        probs = torch.sigmoid(flat[b]).cpu()
+        sc, lb = probs.max(dim=1)
+        surv = torch.nonzero(sc > 0.05).flatten()
+        boxes = b200det.ClipBoxes()(b200det.BBoxTransform()(anc, reg[b:b + 1]), img[b:b + 1])[0].cpu()
+        keep = R.batched_nms(boxes[surv].numpy(), sc[surv].numpy(), lb[surv].numpy(), 0.5)
+        assert np.array_equal(w.anchor_ids[b, :k].cpu().numpy(), surv[keep].numpy())
+    m = b200det.detect(flat, reg, anc, (H, W), from_logits=True, class_aware=True, max_detections=50)
+    t = b200det.detect(flat, reg, anc, (H, W), from_logits=True, class_aware=True, pre_nms_topk=300)
+    for b in range(B):
+        assert int(m.count[b]) == min(50, int(w.count[b]))
+        assert torch.equal(m.anchor_ids[b, :int(m.count[b])], w.anchor_ids[b, :int(m.count[b])])
+        # the top-300 by score, then per-class NMS among them: a prefix-closed subset of the full answer's candidates
+        assert int(t.count[b]) <= 300 and int(t.survivors[b]) == int(w.survivors[b])
+
+
 def test_head_levels_reject_bad_shapes():
     img = torch.empty(2, 3, 64, 64, device=DEV)
     anc = b200det.Anchors()(img)
