@@ -421,18 +421,39 @@ def run_b200(args, wl):
         d_cls, d_reg, d_ann = torch.empty_like(cls), torch.empty_like(reg), torch.empty_like(ann)
         d2h = [0]
 
+        # The copy of the big tensor runs on its own stream in image chunks; decode/NMS (per-image work, the public
+        # detect() on a slice) of a chunk starts as soon as the chunk has landed, so only the last chunk's detect
+        # and the batch-wide FocalLoss are left when the copy ends.  Everything still goes through the modules.
+        copy_stream = torch.cuda.Stream()
+        n_chunks = 8 if B % 8 == 0 and B >= 16 else 1
+        per = B // n_chunks
+
         def e2e_step():
-            d_cls.copy_(h_cls, non_blocking=True)
-            d_reg.copy_(h_reg, non_blocking=True)
-            d_ann.copy_(h_ann, non_blocking=True)
+            cur = torch.cuda.current_stream()
+            copy_stream.wait_stream(cur)                      # the previous step has consumed d_cls / d_reg / d_ann
+            arrived = []
+            with torch.cuda.stream(copy_stream):
+                d_reg.copy_(h_reg, non_blocking=True)
+                d_ann.copy_(h_ann, non_blocking=True)
+                for i in range(n_chunks):
+                    d_cls[i * per:(i + 1) * per].copy_(h_cls[i * per:(i + 1) * per], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(copy_stream)
+                    arrived.append(ev)
+            dets = []
+            for i in range(n_chunks):
+                cur.wait_event(arrived[i])
+                sl = slice(i * per, (i + 1) * per)
+                dets.append(b200det.detect(d_cls[sl], d_reg[sl], anchors_mod(img[sl]), hw, sync=False))
             c = d_cls.detach().requires_grad_(True)
             r = d_reg.detach().requires_grad_(True)
             lc, lr = loss_mod(c, r, anchors_mod(img), d_ann)
             (lc + lr).sum().backward()
             losses = torch.cat([lc.detach(), lr.detach()]).cpu()
-            det = b200det.detect(d_cls, d_reg, anchors_mod(img), hw, sync=True)
-            kmax = max(int(det.count.max()), 1)
-            res = (det.scores[:, :kmax].cpu(), det.labels[:, :kmax].cpu(), det.boxes[:, :kmax].cpu())
+            counts = torch.cat([d.count for d in dets]).cpu()
+            kmax = max(int(counts.max()), 1)
+            res = (torch.cat([d.scores[:, :kmax] for d in dets]).cpu(), torch.cat([d.labels[:, :kmax] for d in dets]).cpu(),
+                   torch.cat([d.boxes[:, :kmax] for d in dets]).cpu())
             d2h[0] = losses.numel() * 4 + B * 2 * 4 + sum(t.numel() * t.element_size() for t in res)
 
         n_e2e = max(3, min(args.steps, 10))
@@ -451,7 +472,8 @@ def run_b200(args, wl):
         out["e2e"] = {"value": world * B / (float(ms_e2e.item()) * 1e-3), "unit": UNIT,
                       "h2d_bytes_per_step": sum(t.numel() * 4 for t in (cls, reg, ann)), "d2h_bytes_per_step": d2h[0],
                       "ms_per_step": float(ms_e2e.item()), "steps": n_e2e,
-                      "note": "pinned host -> device copies + FocalLoss fwd+bwd + detect + results to host; PCIe-bound"}
+                      "note": "pinned host -> device copies (chunked on a copy stream, detect() of a chunk overlaps the next copy) + "
+                              "FocalLoss fwd+bwd + detect + results to host; PCIe-bound: the copy alone is 20.4 ms at 55 GB/s"}
 
     if rank == 0:
         out["clocks"] = sampler.stop()
