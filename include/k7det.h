@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 8
+#define K7_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -278,6 +278,25 @@ K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
  * workspace as k7_nms: the category test sits after the division-free filter of the bitmask kernel. */
 K7_API int k7_batched_nms(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr,
                    int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Soft-NMS for one image (Bodla et al., ICCV 2017; SURVEY 8f row 4 "soft variants" - neither the reference nor
+ * torchvision has one, so the behaviour is the paper's, restated in oracle/restate.py::soft_nms): repeatedly pick
+ * the box with the highest remaining score (ties: lowest index) and decay the scores of the others by their overlap
+ * with it (torchvision.ops.nms's IoU),
+ *     K7_SOFT_LINEAR:   s_j *= 1 - iou  if iou > iou_thr        K7_SOFT_GAUSSIAN:  s_j *= exp(-iou^2 / sigma)
+ * until the best remaining score is below score_thr.  keep[n] int64 indices in pick order, out_scores[n] float32 the
+ * score each box had when it was picked, count[1] int32.  n <= 49 152 (the scores live in shared memory).  One CTA:
+ * the picks are sequential by definition; this is an extension for callers who want it, not part of the hot path. */
+#define K7_SOFT_LINEAR 0
+#define K7_SOFT_GAUSSIAN 1
+typedef struct K7SoftNmsParams {
+    int32_t method;    /* K7_SOFT_LINEAR | K7_SOFT_GAUSSIAN */
+    float iou_thr;     /* linear: overlaps above it decay (0.3 in the paper) */
+    float sigma;       /* gaussian (0.5 in the paper) */
+    float score_thr;   /* stop when the best remaining score is below it (0.001 in the paper) */
+} K7SoftNmsParams;
+K7_API int k7_soft_nms(const float* boxes, const float* scores, int n, const K7SoftNmsParams* params,
+                int64_t* keep, float* out_scores, int32_t* count, void* stream);
 
 /* ---------------------------------------------------------------- annotation packing
  * collater's annotation half (datasettool/dataloader.py:678-686): rows [N,5] of all images back

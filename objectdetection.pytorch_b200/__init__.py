@@ -9,7 +9,7 @@ __version__ = "0.1.0"
 
 from .anchors import Anchors, AnchorsYX, spec_of            # noqa: F401
 from .losses import FocalLoss                                # noqa: F401
-from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, detect, nms, batched_nms,  # noqa: F401
+from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, detect, nms, batched_nms, soft_nms,  # noqa: F401
                     postprocess, eval_tail, patch_model, strip_head_sigmoid)
 from .evaltail import (PackedDetections, eval_pack, coco_results, csv_all_detections,  # noqa: F401
                        collate_annotations)

@@ -93,6 +93,10 @@ class K7DetectParams(C.Structure):
     ]
 
 
+class K7SoftNmsParams(C.Structure):
+    _fields_ = [("method", C.c_int32), ("iou_thr", C.c_float), ("sigma", C.c_float), ("score_thr", C.c_float)]
+
+
 class K7EvalParams(C.Structure):
     _fields_ = [
         ("mode", C.c_int32),
@@ -104,7 +108,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 8                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 9                      # K7_ABI_VERSION of include/k7det.h
 
 
 def ignore_words(A: int) -> int:
@@ -142,6 +146,7 @@ SYMBOLS = {
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
     "k7_batched_nms": (C.c_int, [_P, _P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_soft_nms": (C.c_int, [_P, _P, C.c_int, C.POINTER(K7SoftNmsParams), _P, _P, _P, _P]),
     "k7_peer_mailbox_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), _P]),
     "k7_peer_mailbox_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),
     "k7_peer_mailbox_close": (C.c_int, [_P]),

@@ -2221,3 +2221,131 @@ extern "C" int k7_batched_nms(const float* boxes, const float* scores, const int
     K7_REQUIRE(n == 0 || idxs, "k7_batched_nms: null argument");
     return k7_nms_run(boxes, scores, idxs, n, iou_thr, keep, count, workspace, workspace_bytes, stream);
 }
+
+// ------------------------------------------------------------------ Soft-NMS ("soft variants")
+// Bodla et al., "Soft-NMS - Improving Object Detection With One Line of Code" (ICCV 2017): instead of
+// removing the boxes that overlap the current maximum, their scores decay with the overlap
+//     linear:    s_j *= 1 - iou   if iou > thr            gaussian:  s_j *= exp(-iou^2 / sigma)
+// and the loop ends when the best remaining score is below score_thr.  Neither the reference nor
+// torchvision has it: the restatement in oracle/restate.py follows the paper (parity unpinned, it
+// says so).  The picks are inherently sequential (every pick changes the scores the next one is
+// taken from), so this is one CTA per call: scores live in shared memory, a pick is a block
+// arg-max (ties: lowest index) and a decay pass over the remaining boxes.  Not a bandwidth kernel.
+// The overlap is torchvision.ops.nms's: inter / (area_i + area_j - inter), float32, no FMA.
+#define K7_SOFT_THREADS 1024
+#define K7_SOFT_MAX_N 49152   // scores in shared memory: 192 KB
+__global__ void __launch_bounds__(K7_SOFT_THREADS, 1)
+k7_soft_nms_kernel(const float4* __restrict__ boxes, const float* __restrict__ scores, int n, int method, float iou_thr,
+                   float sigma, float score_thr, int64_t* __restrict__ keep, float* __restrict__ out_scores,
+                   int32_t* __restrict__ count) {
+    extern __shared__ float s_sc[];
+    __shared__ float s_wv[K7_SOFT_THREADS / 32];
+    __shared__ int s_wi[K7_SOFT_THREADS / 32];
+    __shared__ float s_selv;
+    __shared__ int s_sel;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float ninf = -INFINITY;
+    for (int j = tid; j < n; j += K7_SOFT_THREADS) {
+        const float v = scores[j];
+        s_sc[j] = (v == v) ? v : ninf;   // a NaN score is never picked
+    }
+    __syncthreads();
+    int it = 0;
+    for (; it < n; ++it) {
+        // block arg-max over the remaining scores; ties go to the lowest index
+        float bv = ninf;
+        int bi = 0x7fffffff;
+        for (int j = tid; j < n; j += K7_SOFT_THREADS) {
+            const float v = s_sc[j];
+            if (v > bv) {
+                bv = v;
+                bi = j;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_down_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) {
+                bv = ov;
+                bi = oi;
+            }
+        }
+        if (lane == 0) {
+            s_wv[warp] = bv;
+            s_wi[warp] = bi;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            bv = s_wv[lane];
+            bi = s_wi[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_down_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_down_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) {
+                    bv = ov;
+                    bi = oi;
+                }
+            }
+            if (lane == 0) {
+                s_selv = bv;
+                s_sel = bi;
+            }
+        }
+        __syncthreads();
+        const int sel = s_sel;
+        const float sv = s_selv;
+        if (sel == 0x7fffffff || !(sv >= score_thr)) break;   // block-uniform: nothing left worth keeping
+        const float4 bi4 = __ldg(boxes + sel);
+        const K7Box me = {bi4.x, bi4.y, bi4.z, bi4.w};
+        const float area_i = k7_area(bi4.x, bi4.y, bi4.z, bi4.w);
+        if (tid == 0) {
+            keep[it] = (int64_t)sel;
+            out_scores[it] = sv;
+            s_sc[sel] = ninf;
+        }
+        for (int j = tid; j < n; j += K7_SOFT_THREADS) {
+            if (j == sel) continue;
+            const float v = s_sc[j];
+            if (v == ninf) continue;
+            const float4 bj = __ldg(boxes + j);
+            const float w = fmaxf(0.0f, K7_FSUB(fminf(me.x2, bj.z), fmaxf(me.x1, bj.x)));
+            const float h = fmaxf(0.0f, K7_FSUB(fminf(me.y2, bj.w), fmaxf(me.y1, bj.y)));
+            const float inter = K7_FMUL(w, h);
+            const float iou = K7_FDIV(inter, K7_FSUB(K7_FADD(area_i, k7_area(bj.x, bj.y, bj.z, bj.w)), inter));
+            if (!(iou > 0.0f)) continue;   // disjoint or degenerate (NaN): no decay
+            float wgt = 1.0f;
+            if (method == K7_SOFT_LINEAR) {
+                if (iou > iou_thr) wgt = K7_FSUB(1.0f, iou);
+            } else {
+                wgt = expf(-K7_FDIV(K7_FMUL(iou, iou), sigma));
+            }
+            s_sc[j] = K7_FMUL(v, wgt);
+        }
+        __syncthreads();
+    }
+    if (tid == 0) *count = it;
+}
+
+extern "C" int k7_soft_nms(const float* boxes, const float* scores, int n, const K7SoftNmsParams* params, int64_t* keep,
+                           float* out_scores, int32_t* count, void* stream) {
+    K7_REQUIRE(count && params, "k7_soft_nms: null argument");
+    K7_REQUIRE(n >= 0 && n <= K7_SOFT_MAX_N, "k7_soft_nms: n=%d outside [0, %d]", n, K7_SOFT_MAX_N);
+    K7_REQUIRE(params->method == K7_SOFT_LINEAR || params->method == K7_SOFT_GAUSSIAN, "k7_soft_nms: bad method");
+    K7_REQUIRE(params->method == K7_SOFT_LINEAR || params->sigma > 0.0f, "k7_soft_nms: sigma must be > 0");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n == 0) {
+        K7_CUDA(cudaMemsetAsync(count, 0, sizeof(int32_t), st));
+        return K7_OK;
+    }
+    K7_REQUIRE(boxes && scores && keep && out_scores, "k7_soft_nms: null argument");
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "k7_soft_nms: boxes must be 16-byte aligned");
+    const size_t smem = sizeof(float) * (size_t)n;
+    K7_CUDA(cudaFuncSetAttribute(k7_soft_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * K7_SOFT_MAX_N)));
+    k7_soft_nms_kernel<<<1, K7_SOFT_THREADS, smem, st>>>(reinterpret_cast<const float4*>(boxes), scores, n, params->method,
+                                                         params->iou_thr, params->sigma, params->score_thr, keep, out_scores,
+                                                         count);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}

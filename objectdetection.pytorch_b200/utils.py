@@ -255,6 +255,32 @@ def batched_nms(boxes: torch.Tensor, scores: torch.Tensor, idxs: torch.Tensor, i
     return keep[:int(count.item())]
 
 
+def soft_nms(boxes: torch.Tensor, scores: torch.Tensor, method: str = "gaussian", iou_threshold: float = 0.3,
+             sigma: float = 0.5, score_threshold: float = 0.001):
+    """Soft-NMS (Bodla et al., ICCV 2017) on device: returns (keep int64 [K] in pick order, scores float32 [K] - the
+    decayed score each box had when it was picked).  method "linear": s_j *= 1 - iou where iou > iou_threshold;
+    "gaussian": s_j *= exp(-iou^2 / sigma); picking stops below score_threshold.  An extension:
+    the reference's detectors use hard NMS only."""
+    L.require_cuda(boxes, scores)
+    if method not in ("linear", "gaussian"):
+        raise ValueError("method must be 'linear' or 'gaussian'")
+    b = L.as_f32_contig(boxes)
+    s = L.as_f32_contig(scores)
+    n = b.shape[0]
+    if s.shape[0] != n:
+        raise ValueError("boxes and scores must have the same length")
+    dev = b.device
+    keep = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    out = torch.empty(max(n, 1), dtype=torch.float32, device=dev)
+    count = torch.empty(1, dtype=torch.int32, device=dev)
+    p = L.K7SoftNmsParams(0 if method == "linear" else 1, float(iou_threshold), float(sigma), float(score_threshold))
+    with torch.cuda.device(dev):
+        L.check(L.lib().k7_soft_nms(L.ptr(b), L.ptr(s), n, C.byref(p), L.ptr(keep), L.ptr(out), L.ptr(count),
+                                    L.stream_ptr(dev)), "k7_soft_nms")
+    k = int(count.item())
+    return keep[:k], out[:k]
+
+
 def _variant_of(regressBoxes) -> int:
     return L.DECODE_EFFDET if isinstance(regressBoxes, BBoxTransformYX) or \
         type(regressBoxes).__module__.endswith("utils_efficientdet") else L.DECODE_RETINA

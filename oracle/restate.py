@@ -34,6 +34,11 @@ itself: ``tests/golden/make_golden.py`` imports the unmodified reference
 modules from /root/reference (+ torchvision.ops.nms), runs them on seeded
 inputs and commits the results under ``tests/golden/``;
 ``tests/test_oracle_golden.py`` checks this file against those fixtures.
+Per-category NMS (``batched_nms``) is pinned the same way against torchvision
+0.26.0's ``batched_nms`` (tests/golden/batched_nms.npz).
+PARITY UNPINNED for ONE function: ``soft_nms`` - neither the reference nor
+torchvision implements Soft-NMS, so it restates the published algorithm
+(Bodla et al., ICCV 2017) and is checked only on cases with known answers.
 """
 from __future__ import annotations
 
@@ -384,6 +389,47 @@ def batched_nms_coordinate_trick(boxes: np.ndarray, scores: np.ndarray, idxs: np
         return np.zeros((0,), dtype=np.int64)
     off = np.asarray(idxs).astype(np.float32) * (boxes.max() + np.float32(1))
     return greedy_nms(boxes + off[:, None], scores, thr)
+
+
+def soft_nms(boxes: np.ndarray, scores: np.ndarray, method: str = "gaussian", iou_thr: float = 0.3,
+             sigma: float = 0.5, score_thr: float = 0.001):
+    """Soft-NMS as published (Bodla, Singh, Chellappa, Davis: "Soft-NMS - Improving Object Detection With One
+    Line of Code", ICCV 2017, algorithm 1 / eq. 2-3).  PARITY UNPINNED: neither the reference nor torchvision
+    implements it, so there is no third-party output to pin this restatement against; it follows the paper with
+    torchvision.ops.nms's overlap (inter / (area_i + area_j - inter), float32).  Returns (indices in pick order,
+    the score each box had when picked).  Ties: lowest index; disjoint / degenerate pairs do not decay."""
+    boxes = np.asarray(boxes, dtype=np.float32).reshape(-1, 4)
+    s = np.asarray(scores, dtype=np.float32).copy()
+    n = boxes.shape[0]
+    s[np.isnan(s)] = -np.inf
+    x1, y1, x2, y2 = (boxes[:, i] for i in range(4))
+    area = (x2 - x1) * (y2 - y1)
+    keep, out = [], []
+    thr32, sig32, sthr32 = np.float32(iou_thr), np.float32(sigma), np.float32(score_thr)
+    for _ in range(n):
+        i = int(np.argmax(s))                      # first maximum = lowest index on ties
+        if not (s[i] >= sthr32):
+            break
+        keep.append(i)
+        out.append(s[i])
+        s[i] = -np.inf
+        live = np.nonzero(s > -np.inf)[0]
+        if live.size == 0:
+            break
+        w = np.maximum(np.float32(0), np.minimum(x2[i], x2[live]) - np.maximum(x1[i], x1[live]))
+        h = np.maximum(np.float32(0), np.minimum(y2[i], y2[live]) - np.maximum(y1[i], y1[live]))
+        inter = w * h
+        with np.errstate(divide='ignore', invalid='ignore'):
+            iou = inter / (area[i] + area[live] - inter)
+        wgt = np.ones_like(iou)
+        pos = iou > 0
+        if method == "linear":
+            m = pos & (iou > thr32)
+            wgt[m] = np.float32(1) - iou[m]
+        else:
+            wgt[pos] = np.exp(-(iou[pos] * iou[pos]) / sig32).astype(np.float32)
+        s[live] = s[live] * wgt
+    return np.asarray(keep, dtype=np.int64), np.asarray(out, dtype=np.float32)
 
 
 @dataclass

@@ -403,6 +403,45 @@ def test_detect_image_above_the_multi_sm_cap(class_aware):
         assert np.array_equal(det.labels[b, :k].cpu().numpy(), lb[surv][keep].numpy())
 
 
+@pytest.mark.parametrize("n", [1, 50, 1000, 3000])
+def test_soft_nms_vs_oracle(n):
+    """Soft-NMS (soft variants).  Linear decay is plain float32 arithmetic: picks and scores are
+    bit-exact against the restatement of the paper's algorithm.  The gaussian form goes through expf, which differs
+    between host and device by an ulp: same picks, scores to 1e-5."""
+    rng = np.random.default_rng(100 + n)
+    centers = rng.uniform(0, 400, (max(n // 10, 1), 2))
+    c = centers[rng.integers(0, centers.shape[0], n)] + rng.normal(0, 5, (n, 2))
+    wh = 2.0 ** rng.uniform(3, 6, (n, 2))
+    boxes = np.concatenate([c - wh / 2, c + wh / 2], 1).astype(np.float32)
+    boxes[::17, 2:] = boxes[::17, :2]                                  # zero-area boxes: no decay either way
+    scores = (rng.permutation(n).astype(np.float32) + 1) / np.float32(n + 1)
+    tb, ts = torch.from_numpy(boxes).to(DEV), torch.from_numpy(scores).to(DEV)
+    for thr in (0.3, 0.5):
+        want_k, want_s = R.soft_nms(boxes, scores, method="linear", iou_thr=thr, score_thr=0.05)
+        got_k, got_s = b200det.soft_nms(tb, ts, method="linear", iou_threshold=thr, score_threshold=0.05)
+        assert got_k.dtype == torch.int64 and np.array_equal(got_k.cpu().numpy(), want_k)
+        assert np.array_equal(got_s.cpu().numpy(), want_s)
+    want_k, want_s = R.soft_nms(boxes, scores, method="gaussian", sigma=0.5, score_thr=0.01)
+    got_k, got_s = b200det.soft_nms(tb, ts, method="gaussian", sigma=0.5, score_threshold=0.01)
+    gk, gs = got_k.cpu().numpy(), got_s.cpu().numpy()
+    assert gk.size == want_k.size and set(gk.tolist()) == set(want_k.tolist())
+    order_w = np.argsort(want_k)
+    order_g = np.argsort(gk)
+    np.testing.assert_allclose(gs[order_g], want_s[order_w], rtol=1e-5)      # every box: the same decayed score
+    assert np.mean(gk == want_k) > 0.99                                       # and the same pick order but for ulp ties
+
+
+def test_soft_nms_empty_and_errors():
+    k, s = b200det.soft_nms(torch.zeros(0, 4, device=DEV), torch.zeros(0, device=DEV))
+    assert k.shape == (0,) and s.shape == (0,) and k.dtype == torch.int64
+    with pytest.raises(ValueError):
+        b200det.soft_nms(torch.zeros(3, 4, device=DEV), torch.zeros(3, device=DEV), method="hard")
+    with pytest.raises(ValueError):
+        b200det.soft_nms(torch.zeros(3, 4, device=DEV), torch.zeros(2, device=DEV))
+    with pytest.raises(ValueError):
+        b200det.soft_nms(torch.zeros(3, 4, device=DEV), torch.zeros(3, device=DEV), method="gaussian", sigma=0.0)
+
+
 def check_detect(det, g, exact_boxes_from=None):
     B = g["classifications"].shape[0]
     for b in range(B):

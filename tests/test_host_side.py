@@ -72,12 +72,13 @@ def test_struct_layout_matches_header(tmp_path):
     src = tmp_path / "sizes.c"
     src.write_text('#include <stdio.h>\n#include "k7det.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %d\\n",'
                    'sizeof(K7AnchorSpec),sizeof(K7MatchParams),sizeof(K7LossParams),sizeof(K7DecodeParams),'
-                   'sizeof(K7DetectParams),sizeof(K7EvalParams),sizeof(K7PeerReduce),K7_ABI_VERSION);return 0;}\n')
+                   'sizeof(K7DetectParams),sizeof(K7EvalParams),sizeof(K7PeerReduce)+1000*sizeof(K7SoftNmsParams),K7_ABI_VERSION);return 0;}\n')
     exe = tmp_path / "sizes"
     subprocess.run(["gcc", "-I", os.path.join(root, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(L.K7AnchorSpec), C.sizeof(L.K7MatchParams), C.sizeof(L.K7LossParams), C.sizeof(L.K7DecodeParams),
-            C.sizeof(L.K7DetectParams), C.sizeof(L.K7EvalParams), C.sizeof(L.K7PeerReduce), L.ABI_VERSION]
+            C.sizeof(L.K7DetectParams), C.sizeof(L.K7EvalParams), C.sizeof(L.K7PeerReduce) + 1000 * C.sizeof(L.K7SoftNmsParams),
+            L.ABI_VERSION]
     assert got == want
 
 
@@ -96,6 +97,8 @@ def test_no_cpu_fallback():
     for strategy in ("coordinate_trick", "auto"):                 # these reach nms() after a few torch ops
         with pytest.raises(RuntimeError):
             b200det.batched_nms(torch.rand(4, 4), torch.rand(4), torch.zeros(4, dtype=torch.int64), 0.5, strategy=strategy)
+    with pytest.raises(RuntimeError):
+        b200det.soft_nms(torch.rand(4, 4), torch.rand(4))
     with pytest.raises(RuntimeError):
         det = b200det.BatchDetections(torch.tensor([1]), torch.tensor([1]), torch.rand(1, 2), torch.zeros(1, 2, dtype=torch.int64),
                                       torch.rand(1, 2, 4), torch.zeros(1, 2, dtype=torch.int32), torch.zeros(1, 2, dtype=torch.int32))

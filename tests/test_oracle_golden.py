@@ -167,3 +167,39 @@ def test_batched_nms_oracle_vs_torchvision_fixture(tag):
     assert np.array_equal(R.greedy_nms(boxes, scores, 0.5), g[f"{tag}_agnostic"])
     if tag == "one_class":                       # a single category is plain NMS
         assert np.array_equal(g[f"{tag}_vanilla"], g[f"{tag}_agnostic"])
+
+
+def test_soft_nms_oracle_properties():
+    """Soft-NMS has no third-party implementation to pin against (oracle header: parity unpinned); the
+    restatement is checked on the cases where the paper's algorithm has a known answer."""
+    rng = np.random.default_rng(5)
+    n = 200
+    # (1) pairwise disjoint boxes: nothing decays, order = descending score, every box kept
+    xy = np.stack([np.arange(n) * 10.0, np.zeros(n)], 1)
+    boxes = np.concatenate([xy, xy + 5.0], 1).astype(np.float32)
+    scores = rng.uniform(0.1, 1, n).astype(np.float32)
+    for method in ("linear", "gaussian"):
+        keep, sc = R.soft_nms(boxes, scores, method=method)
+        assert np.array_equal(keep, np.argsort(-scores, kind="stable")) and np.array_equal(sc, scores[keep])
+    # (2) two identical boxes: linear weight 1 - 1 = 0 -> the second falls below the score threshold
+    b2 = np.array([[0, 0, 10, 10], [0, 0, 10, 10], [50, 50, 60, 60]], np.float32)
+    s2 = np.array([0.9, 0.8, 0.3], np.float32)
+    keep, sc = R.soft_nms(b2, s2, method="linear", iou_thr=0.3)
+    assert keep.tolist() == [0, 2] and np.allclose(sc, [0.9, 0.3])
+    keep, sc = R.soft_nms(b2, s2, method="gaussian", sigma=0.5)
+    assert keep.tolist() == [0, 2, 1] and np.isclose(sc[2], 0.8 * np.exp(-1 / 0.5), rtol=1e-6)
+    # (3) linear with an overlap below the threshold does not decay; the first pick is always the arg-max;
+    #     a high score threshold ends the loop early
+    b3 = np.array([[0, 0, 10, 10], [8, 0, 18, 10]], np.float32)            # IoU = 20 / 180
+    keep, sc = R.soft_nms(b3, np.array([0.5, 0.6], np.float32), method="linear", iou_thr=0.3)
+    assert keep.tolist() == [1, 0] and np.array_equal(sc, np.array([0.6, 0.5], np.float32))
+    keep, sc = R.soft_nms(boxes, scores, method="gaussian", score_thr=0.5)
+    assert keep.size == int((scores >= 0.5).sum())
+    # (4) as sigma -> 0 the gaussian form tends to "any overlap removes": greedy NMS with threshold 0
+    #     (boxes on a 5-pixel lattice: an overlap is either 0 or at least 25 / 1775, so exp(-iou^2 / 1e-6) underflows)
+    c = rng.integers(0, 20, (300, 2)) * 5.0
+    wh = rng.integers(2, 7, (300, 2)) * 5.0
+    b4 = np.concatenate([c, c + wh], 1).astype(np.float32)
+    s4 = rng.permutation(300).astype(np.float32) / 300 + 0.01
+    keep, _ = R.soft_nms(b4, s4, method="gaussian", sigma=1e-6, score_thr=1e-3)
+    assert np.array_equal(keep, R.greedy_nms(b4, s4, 0.0))
