@@ -314,14 +314,13 @@ def run_b200(args, wl):
     ms_fb = timed(train_side, k, 3)
     ms_det = timed(eval_side, k, 3)
     anc = anchors_mod(img)
-    dreg0 = torch.zeros_like(reg)     # what k7_match(zero_fill4=) hands over in the module path
-    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
+    sp_ = b200det.spec_of(anc)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
-    ms_match = timed(lambda: BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True), k, 3)
-    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0,
-                                          ignore_bits=bits, **kw), k, 3)
-    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw),
-                   k, 3)
+    ms_match = timed(lambda: BL.match_scatter(sp_, ann, A, 0.35, 0.45), k, 3)
+    arr_, gen_, consume_, num_pos = BL.match_scatter(sp_, ann, A, 0.35, 0.45)
+    best_ = (arr_, gen_, consume_, 0.35, 0.45)
+    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=True, best=best_, **kw), k, 3)
+    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=False, best=best_, **kw), k, 3)
     surv = int(eval_side(sync=True).survivors.sum())
     bytes_fwd = B * (A * (4 * C + 16) + 20 * M)
     bytes_fb = B * (A * (8 * C + 32) + 20 * M)

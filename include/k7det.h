@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 9
+#define K7_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -112,13 +112,40 @@ typedef struct K7MatchParams {
  *                         following k7_loss will write positive rows into (the kernel is ALU-bound,
  *                         so the 16 B/anchor store is free here; see K7LossParams.dreg_prezeroed)
  *   ignore_bits [B, K7_IGNORE_WORDS(A)] uint32 (optional, may be NULL; 16-byte aligned) one bit per
- *                         anchor, set = state IGNORE: bit a%32 of word a/32 of the image's row.  k7_loss
- *                         streams it instead of the 4-byte words (it derives it itself when not given). */
+ *                         anchor, set = state IGNORE: bit a%32 of word a/32 of the image's row (a compact
+ *                         form of the states for callers that want it; k7_loss does not need it). */
 #define K7_IGNORE_WORDS(A) (((((size_t)(A)) + 127) >> 7) << 2) /* words per image, a multiple of 16 bytes */
 K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_order,
              const float* annotations, int B, int A, int M, const K7MatchParams* params,
              int32_t* assign, int32_t* num_pos, float* iou_max, int32_t* argmax, float* zero_fill4,
              uint32_t* ignore_bits, void* stream);
+
+/* The same assignment computed GROUND-TRUTH-FIRST - the production path of FocalLoss when the anchors come
+ * from a recipe (calc_iou + IoU-max assignment, losses.py:6-23, 49-82).  An anchor only leaves the NEGATIVE
+ * state through a ground-truth box with IoU >= neg_thr, and for one box those anchors are a few cells
+ * around it on the two or three pyramid levels whose anchor areas are within 1/neg_thr of its own.  One warp
+ * per (image, annotation row, level) enumerates a provable superset of them (area window and the
+ * intersection width / height any pair with IoU >= neg_thr needs, 1e-4 margins), evaluates the reference's
+ * float32 IoU (k7_pair_iou: same operations, same order) and folds pairs with IoU >= neg_thr into
+ *     best[b*A + a] = max( generation << 48 | IoU bits << 16 | (0xFFFF - annotation row) )        (atomicMax)
+ * i.e. the largest IoU and, on ties, the lowest row - torch.max's first index (losses.py:66).  Work is
+ * proportional to the pairs that matter, not to A x M, and nothing per anchor is written: an entry whose
+ * top 16 bits differ from `generation` means "no ground truth reached neg_thr" = NEGATIVE.  k7_loss reads
+ * `best` directly (K7LossParams.match_generation / neg_thr / pos_thr).
+ *   best        [B,A] uint64, caller-owned, ZERO-INITIALISED ONCE; every call on it must pass a LARGER
+ *               generation than the one before (1 .. K7_BEST_GEN_MAX; re-zero before starting over)
+ *   num_pos     [B] int32 (zeroed by the call): anchors whose maximum reached pos_thr - each is counted once,
+ *               by the atomicMax that first lifts it over pos_thr (integer, order independent)
+ * Requires a recipe, 1e-3 < neg_thr <= pos_thr, M <= 65535.  Images without a valid row leave `best`
+ * untouched; k7_loss sees from the annotations that the image is skipped (losses.py:52-60). */
+#define K7_BEST_GEN_MAX 65535u
+#define K7_BEST_GEN(v) ((uint32_t)((v) >> 48))
+#define K7_BEST_IOU_BITS(v) ((uint32_t)((v) >> 16))
+#define K7_BEST_ROW(v) (0xFFFF - (int32_t)((v) & 0xFFFFu))
+K7_API size_t k7_match_scatter_workspace_bytes(int B, int A);
+K7_API int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
+                     const K7MatchParams* params, uint64_t* best, uint32_t generation, int32_t* num_pos,
+                     void* stream);
 
 /* Multi-GPU: the path's one exchange - the four batch sums {sum cls_i, sum reg_i, sum num_pos_i, B}
  * of every rank - fused into k7_loss.  mailbox[p] is a device pointer, valid in THIS process, to
@@ -159,22 +186,35 @@ typedef struct K7LossParams {
                              * simple_head.py:310 removed): the sigmoid is fused into the stream and dcls is
                              * d(loss)/d(logit).  SURVEY 8(f) row 1. */
     const K7PeerReduce* peer_reduce; /* NULL: `sums` are this rank's own; else see K7PeerReduce */
+    uint32_t match_generation; /* `best` given: the generation of the k7_match_scatter call that filled it */
+    float neg_thr, pos_thr;    /* `best` given: the thresholds of that call (the states are decided from the IoU bits) */
+    int32_t* assign_out;       /* optional [B,A] int32: the packed state / row words of k7_match, written on the way */
+    int32_t consume_best;      /* 1: entries of this generation are zeroed as they are read, so the SAME generation can be
+                                * used again by the next k7_match_scatter on this array (a captured CUDA graph replays
+                                * one generation); `best` is then written by k7_loss */
 } K7LossParams;
 
 K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
 
 /* Replaces FocalLoss.forward after assignment (losses.py:62, 94-168) and, when dcls/dreg
- * are given, its autograd backward.  Outputs:
+ * are given, its autograd backward.  The assignment comes either as k7_match's words (`assign`) or as
+ * k7_match_scatter's `best` array (exactly one of the two is non-NULL).  Two kernels: a stream over
+ * `cls` that evaluates EVERY element as "target 0" at HBM speed, then a row kernel that walks the
+ * assignment once and patches the ~2 % of rows that are not plain negatives: positive rows get
+ * smooth-L1 + d(reg) and their label element moves from target 0 to target 1; ignored rows
+ * (neg_thr <= IoU_max < pos_thr, losses.py:79-82) are taken out of the sum again and their gradient is
+ * zeroed.  Row contributions are accumulated as 2^-32 fixed-point integers (order independent), the
+ * stream partials in a fixed order: results are bit-reproducible run to run.  Outputs:
  *   per_image [B,2] float32  (cls_loss_i, reg_loss_i)
  *   sums      [4]   float32  { sum_i cls_loss_i, sum_i reg_loss_i, sum_i num_pos_i, B }  (the NCCL payload)
  *   dcls [B,A,C], dreg [B,A,4] (optional, both or neither): d(mean cls loss)/dcls and
  *   d(mean reg loss)/dreg with the mean taken over params->mean_divisor images.
  * The batch means of losses.py:168 are sums[0]/B and sums[1]/B.
- * ignore_bits: k7_match's bitmap of the same call (or NULL).  Any B, A, C is streamed with bulk
- * copies; only the base pointers of cls / dcls / reg / dreg must be 16-byte aligned. */
+ * Any B, A, C is streamed with bulk copies; only the base pointers of cls / dcls / reg / dreg must be
+ * 16-byte aligned. */
 K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
             const float* cls, const float* reg, const float* annotations,
-            const int32_t* assign, const uint32_t* ignore_bits, const int32_t* num_pos,
+            const int32_t* assign, const uint64_t* best, const int32_t* num_pos,
             int B, int A, int C, int M, const K7LossParams* params,
             float* per_image, float* sums, float* dcls, float* dreg,
             void* workspace, size_t workspace_bytes, void* stream);
@@ -188,7 +228,7 @@ K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order
  * (the level geometry comes from it); regressions stay [B,A,4]. */
 K7_API size_t k7_loss_levels_workspace_bytes(const K7AnchorSpec* spec, int B, int C);
 K7_API int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
-                   const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                   const float* annotations, const int32_t* assign, const uint64_t* best,
                    const int32_t* num_pos, int B, int C, int M, const K7LossParams* params,
                    float* per_image, float* sums, float* const* dlevels, float* dreg,
                    void* workspace, size_t workspace_bytes, void* stream);

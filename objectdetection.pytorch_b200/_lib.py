@@ -67,6 +67,11 @@ class K7LossParams(C.Structure):
         ("dreg_prezeroed", C.c_int32),
         ("from_logits", C.c_int32),
         ("peer_reduce", C.POINTER(K7PeerReduce)),
+        ("match_generation", C.c_uint32),
+        ("neg_thr", C.c_float),
+        ("pos_thr", C.c_float),
+        ("assign_out", C.c_void_p),
+        ("consume_best", C.c_int32),
     ]
 
 
@@ -108,7 +113,10 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 9                      # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 10                     # K7_ABI_VERSION of include/k7det.h
+
+
+BEST_GEN_MAX = 65535                 # K7_BEST_GEN_MAX
 
 
 def ignore_words(A: int) -> int:
@@ -124,6 +132,9 @@ SYMBOLS = {
     "k7_anchors_materialize": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P]),
     "k7_match": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, C.c_int, C.c_int, C.c_int,
                            C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P, _P]),
+    "k7_match_scatter_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "k7_match_scatter": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_int, C.c_int, C.POINTER(K7MatchParams),
+                                   _P, C.c_uint32, _P, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),

@@ -627,6 +627,167 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
     return K7_OK;
 }
 
+// ------------------------------------------------------------------ match, ground-truth-first (the production path)
+// The two kernels above visit every anchor and, per tile, every ground-truth box that survives a
+// cull: A x (a few) IoU tests plus a fixed cost per anchor - 51 us at EfficientDet-D0 (3.1 M
+// anchors), although only ~2 % of the anchors end up in a state other than NEGATIVE.  Here the
+// loop is turned round.  A pair can only matter when IoU >= neg_thr, and
+//     IoU >= t   <=>   inter * (1 + t) >= t * (area_a + area_g)
+// bounds, for one ground-truth box g and one anchor SHAPE (level l, in-cell anchor k: all anchors
+// of a shape are translates of each other),
+//     the areas:          t * area_a <= area_g <= area_a / t                 (IoU <= area ratio)
+//     the intersection:   iw >= imin / min(h_a, h_g),  ih >= imin / min(w_a, w_g),
+//                         imin = t/(1+t) * (area_a + area_g)                 (iw <= min(w), ih <= min(h))
+// and iw >= iw_min is an interval of cell columns, ih >= ih_min an interval of cell rows.  One warp
+// takes (image, annotation row, level), walks the level's shapes that pass the area window and
+// evaluates the reference's exact float32 IoU (k7_pair_iou) on the cells of the two intervals -
+// typically 5 x 5 of them.  Every bound is taken with a 1e-4 relative margin and the intervals are
+// widened by 0.02 cell, against float32 roundings of ~1e-7: no pair that reaches neg_thr is missed,
+// so states, num_pos and the arg-max of every non-negative anchor are those of the exhaustive
+// kernels, bit for bit (tests/test_gpu_parity.py).  Pairs at or above neg_thr are folded into
+// best[] with a 64-bit atomicMax: generation | IoU bits | ~row - the largest IoU, then the lowest
+// row (torch.max returns the first index).  The maximum is order independent, and so is num_pos:
+// an anchor is counted by the one atomicMax that finds it below pos_thr and leaves it at or above.
+struct K7ScatterAux {
+    float wa[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], ha[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];         // extents, rounded up
+    float area_lo[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];                                           // area, rounded down
+    float g_lo[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], g_hi[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];     // window of ground-truth areas
+    float bx1[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], bx2[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];       // shape around the cell centre
+    float by1[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], by2[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];
+    float inv_stride[K7_MAX_LEVELS];
+    float c_in;                                                                                   // t/(1+t) * (1 - 1e-4)
+};
+
+#define K7_SCATTER_THREADS 128
+__global__ void __launch_bounds__(K7_SCATTER_THREADS)
+k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScatterAux X,
+                        const float* __restrict__ annotations, int B, int A, int M, float neg_thr, float pos_thr,
+                        unsigned long long* __restrict__ best, unsigned int gen, int32_t* __restrict__ num_pos) {
+    const int lane = threadIdx.x & 31;
+    const long long gwarp = ((long long)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * K7_SCATTER_THREADS) >> 5;
+    const int L = spec.num_levels, K = spec.cell_anchors;
+    const long long tasks = (long long)B * M * L;
+    const unsigned long long tag = (unsigned long long)gen << 48;
+    const bool xy = spec.box_order == K7_BOX_XYXY;
+    for (long long t = gwarp; t < tasks; t += nwarps) {   // the level runs fastest: neighbouring warps share a box
+        const int l = (int)(t % L);
+        const long long r = t / L;
+        const int m = (int)(r % M), b = (int)(r / M);
+        const float* row = annotations + ((size_t)b * M + m) * 5;
+        if (__ldg(row + 4) == -1.0f) continue;            // pad row (losses.py:50)
+        const float g0 = __ldg(row + 0), g1 = __ldg(row + 1), g2 = __ldg(row + 2), g3 = __ldg(row + 3);
+        const float gw = K7_FSUB(g2, g0), gh = K7_FSUB(g3, g1);
+        if (!(gw > 0.0f && gh > 0.0f)) continue;          // empty box: IoU is 0 with every anchor
+        const float area_g = k7_area(g0, g1, g2, g3);
+        const int fw = spec.fw[l], fh = spec.fh[l];
+        if (fw <= 0 || fh <= 0) continue;
+        const float inv_s = X.inv_stride[l];
+        const double st = spec.stride[l];
+        int pos = 0;
+        for (int k = 0; k < K; ++k) {                     // warp-uniform
+            if (!(area_g >= X.g_lo[l][k] && area_g <= X.g_hi[l][k])) continue;
+            const float imin = X.c_in * (X.area_lo[l][k] + area_g);
+            const float mw = fminf(X.wa[l][k], gw), mh = fminf(X.ha[l][k], gh);
+            if (imin > mw * mh) continue;
+            const float iw_min = imin / mh, ih_min = imin / mw;
+            // cell centre c = (x + 0.5) * stride must satisfy  g0 + iw_min - bx2 <= c <= g2 - iw_min - bx1
+            const float xl = (g0 + iw_min - X.bx2[l][k]) * inv_s - 0.52f, xh = (g2 - iw_min - X.bx1[l][k]) * inv_s - 0.48f;
+            const float yl = (g1 + ih_min - X.by2[l][k]) * inv_s - 0.52f, yh = (g3 - ih_min - X.by1[l][k]) * inv_s - 0.48f;
+            const int xlo = max(0, (int)ceilf(fmaxf(xl, -1.0f))), xhi = min(fw - 1, (int)floorf(fminf(xh, (float)fw)));
+            const int ylo = max(0, (int)ceilf(fmaxf(yl, -1.0f))), yhi = min(fh - 1, (int)floorf(fminf(yh, (float)fh)));
+            if (xlo > xhi || ylo > yhi) continue;
+            const int nx = xhi - xlo + 1, n = nx * (yhi - ylo + 1);
+            const double* bb = spec.base[l][k];
+            for (int i = lane; i < n; i += 32) {
+                const int yy = i / nx, x = xlo + (i - yy * nx), y = ylo + yy;
+                const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), st);
+                const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), st);
+                float ax1, ay1, ax2, ay2;                 // k7_anchor_from_spec: float64 add, one rounding
+                if (xy) {
+                    ax1 = __double2float_rn(__dadd_rn(bb[0], sx));
+                    ay1 = __double2float_rn(__dadd_rn(bb[1], sy));
+                    ax2 = __double2float_rn(__dadd_rn(bb[2], sx));
+                    ay2 = __double2float_rn(__dadd_rn(bb[3], sy));
+                } else {
+                    ay1 = __double2float_rn(__dadd_rn(bb[0], sy));
+                    ax1 = __double2float_rn(__dadd_rn(bb[1], sx));
+                    ay2 = __double2float_rn(__dadd_rn(bb[2], sy));
+                    ax2 = __double2float_rn(__dadd_rn(bb[3], sx));
+                }
+                const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, k7_area(ax1, ay1, ax2, ay2), g0, g1, g2, g3, area_g);
+                if (iou >= neg_thr) {
+                    const int a = spec.offset[l] + (y * fw + x) * K + k;
+                    const unsigned long long v = tag | ((unsigned long long)__float_as_uint(iou) << 16) |
+                                                 (unsigned long long)(0xFFFF - m);
+                    const unsigned long long old = atomicMax(best + (size_t)b * A + a, v);
+                    if (iou >= pos_thr) {
+                        const bool was_pos = K7_BEST_GEN(old) == gen && __uint_as_float(K7_BEST_IOU_BITS(old)) >= pos_thr;
+                        pos += was_pos ? 0 : 1;
+                    }
+                }
+            }
+        }
+        pos = k7_warp_sum(pos);
+        if (lane == 0 && pos) atomicAdd(num_pos + b, pos);   // integer: order independent, exact
+    }
+}
+
+extern "C" size_t k7_match_scatter_workspace_bytes(int B, int A) {
+    if (B <= 0 || A <= 0) return 0;
+    return sizeof(unsigned long long) * (size_t)B * (size_t)A;
+}
+
+extern "C" int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
+                                const K7MatchParams* params, uint64_t* best, uint32_t generation, int32_t* num_pos,
+                                void* stream) {
+    K7_REQUIRE(spec && annotations && params && best && num_pos, "k7_match_scatter: null argument");
+    K7_REQUIRE(B > 0 && A > 0 && M > 0 && M <= 65535, "k7_match_scatter: bad shape B=%d A=%d M=%d", B, A, M);
+    K7_REQUIRE(generation >= 1u && generation <= K7_BEST_GEN_MAX, "k7_match_scatter: generation %u outside [1, %u]",
+               generation, K7_BEST_GEN_MAX);
+    K7_REQUIRE(params->neg_thr > 1e-3f && params->neg_thr < 1.0f && params->pos_thr >= params->neg_thr,
+               "k7_match_scatter: needs 1e-3 < neg_thr <= pos_thr, neg_thr < 1 (got %f, %f): use k7_match",
+               (double)params->neg_thr, (double)params->pos_thr);
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(best) & 7) == 0, "k7_match_scatter: best must be 8-byte aligned");
+    int rc = k7_check_spec(spec, A);
+    if (rc) return rc;
+    K7ScatterAux X;
+    memset(&X, 0, sizeof(X));
+    const double t = (double)params->neg_thr;
+    X.c_in = (float)(t / (1.0 + t) * (1.0 - 1e-4));
+    const bool xy = spec->box_order == K7_BOX_XYXY;
+    for (int l = 0; l < spec->num_levels; ++l) {
+        X.inv_stride[l] = (float)(1.0 / spec->stride[l]);
+        for (int k = 0; k < spec->cell_anchors; ++k) {
+            const double* b = spec->base[l][k];
+            const double x1 = xy ? b[0] : b[1], y1 = xy ? b[1] : b[0], x2 = xy ? b[2] : b[3], y2 = xy ? b[3] : b[2];
+            const double w = x2 - x1, h = y2 - y1, ar = w * h;
+            // outward roundings: the device compares against float32-rounded anchors (coordinates up to ~1e4: 1e-3 px)
+            X.wa[l][k] = (float)(w * (1.0 + 1e-5) + 2e-3);
+            X.ha[l][k] = (float)(h * (1.0 + 1e-5) + 2e-3);
+            const double ar_lo = (w - 2e-3 > 0 ? w - 2e-3 : 0) * (h - 2e-3 > 0 ? h - 2e-3 : 0) * (1.0 - 1e-5);
+            const double ar_hi = (w + 2e-3) * (h + 2e-3) * (1.0 + 1e-5);
+            X.area_lo[l][k] = (float)ar_lo;
+            X.g_lo[l][k] = (float)(t * (1.0 - 1e-4) * ar_lo);
+            X.g_hi[l][k] = (float)(ar_hi / (t * (1.0 - 1e-4)));
+            (void)ar;
+            X.bx1[l][k] = (float)x1; X.bx2[l][k] = (float)x2; X.by1[l][k] = (float)y1; X.by2[l][k] = (float)y2;
+        }
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    K7_CUDA(cudaMemsetAsync(num_pos, 0, sizeof(int32_t) * B, st));
+    const long long tasks = (long long)B * M * spec->num_levels;
+    const int wpb = K7_SCATTER_THREADS / 32;
+    long long blocks = (tasks + wpb - 1) / wpb;
+    const long long cap = 16ll * k7_sm_count();      // 16 resident CTAs of 128 threads per SM; the rest is looped
+    if (blocks > cap) blocks = cap;
+    k7_match_scatter_kernel<<<(unsigned)blocks, K7_SCATTER_THREADS, 0, st>>>(
+        *spec, X, annotations, B, A, M, params->neg_thr, params->pos_thr, reinterpret_cast<unsigned long long*>(best),
+        generation, num_pos);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
+}
+
 // ------------------------------------------------------------------ ragged annotations -> [B,M,5]
 // datasettool/dataloader.py:678-686 pads every image's annotation rows to the batch maximum with -1
 // in a Python loop on the host.  Here the batch travels as one ragged block (rows [N,5] + offsets

@@ -6,17 +6,16 @@
 // The job is "move B*A*C*4 bytes in (and, with gradients, out) at HBM speed".  Profiling history
 // (profiles/): v1 (row-mapped lanes, per-warp rings) was issue-bound at 58 issue slots per element;
 // v2 (flat 4 KB tiles per warp, packed math) reached 27; v3 (warp-specialised CTA pipeline) 13, but
-// its consumer warps still scanned the assignment words of every slice and served the positive rows
-// inline - dependent global loads (annotation row -> label -> classification element) that held a
-// pipeline stage for ~1 us each and left the forward pass at 4.2 TB/s.  This version (v4):
+// its consumer warps still served the positive rows inline - dependent global loads that held a
+// pipeline stage for ~1 us each; v4 moved the positives into a row kernel behind the stream but
+// still streamed one ignore bit per anchor, which tied the stream to the assignment stage.  v5:
 //
 //   * STREAM KERNEL (k7_loss_pipe_kernel).  One CTA per SM.  classifications is ONE flat array of
 //     B*A*C floats cut into tiles of 16 x 512 floats; tiles ignore row AND image boundaries, so any
-//     shape streams through 16-byte aligned bulk copies (v3 needed A*C % 4 == 0 and fell back to a
-//     slow kernel otherwise - EfficientDet-D3 at 896x896 is such a shape).  A producer warp drives
-//     a ring of shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile in, the
-//     ignore bits of the rows touching it in, and - once the 16 consumer warps have signalled the
-//     stage done - gradients out.  full[]/done[] mbarriers; no __syncthreads in the loop.
+//     shape streams through 16-byte aligned bulk copies.  A producer warp drives a ring of
+//     shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile in and - once the
+//     consumer warps have signalled the stage done - gradients out.  full[]/done[] mbarriers; no
+//     __syncthreads in the loop.
 //   * FLAT PASS.  Consumer warp w owns floats [512w, 512w+512) of every tile: LDS.128 -> math ->
 //     STS.128 on float4 number lane+32k (conflict free, balanced whatever C is).  EVERY element is
 //     evaluated as "target 0" (negative / non-label class) with packed f32x2 arithmetic
@@ -26,20 +25,23 @@
 //         grad  = (p == x) ? (1-alpha)*scale * p * (2*nl + p/q) : 0          (MUFU.RCP)
 //     The polynomial is valid for p <= 0.25; the pass tracks max(p) and a slice that saw a larger
 //     value (rare: confident predictions) is redone by an exact scalar path with logf.
-//   * IGNORED ROWS (IoU between the thresholds, ~1-2 %) come as ONE BIT PER ANCHOR (written by
-//     k7_match with a ballot, or derived from the assignment words by a small kernel here); a slice
-//     fetches the 32-bit window of its rows with two broadcast shared-memory loads and only slices
-//     with a set bit build an element mask and take the masked variant.
+//     The stream knows nothing about the assignment except, with gradients, the per-image scale
+//     1 / max(num_pos, 1) (and that an image without ground truth has gradient 0).
 //   * A slice that straddles an image boundary (B-1 of them per batch) or lies in a tile that
 //     spans more than two images (tiny shapes) takes a generic per-element path.
-//   * ROW KERNEL (k7_loss_rows_kernel), after the stream: one thread per anchor re-reads the 4-byte
-//     assignment word; positive anchors (~1-2 %) get smooth-L1 + d(reg), and their label element is
-//     corrected from "target 0" to "target 1" (loss difference into a partial sum, gradient
-//     overwritten in dcls).  Nothing latency-bound is left inside the stream.
-//   * Loss sums stay in registers while a warp works on one image; at an image change they are
-//     reduced with shuffles into one slot per (image, CTA, warp) - no atomics -, folded per CTA at
-//     the end of the stream kernel and summed per image in float64 in CTA order by the last row
-//     block of the image: bit-reproducible run to run.
+//   * ROW KERNEL (k7_loss_rows_kernel), after the stream: blocks walk the assignment (k7_match's
+//     4-byte words or k7_match_scatter's 8-byte maxima) in chunks of 2048 anchors with coalesced
+//     loads and queue the ~2 % of rows that are not plain negatives in shared memory:
+//       positive rows  smooth-L1 + d(reg), and the label element is corrected from "target 0" to
+//                      "target 1" (loss difference, gradient overwritten in dcls) - a thread each;
+//       ignored rows   (losses.py:79-82: neither negative nor positive) are taken out again: the
+//                      C elements of the row are re-evaluated exactly and SUBTRACTED, their
+//                      gradients zeroed - a warp each, lanes across the classes.
+//     Their contributions go into two per-image 64-bit FIXED-POINT accumulators (2^-32 units,
+//     integer atomics): exact and independent of the order in which blocks finish.
+//   * Stream sums stay in registers while a warp works on one image, are folded per (image, CTA)
+//     at the end of the stream kernel and summed per image in float64 in CTA order by the last
+//     block of the row kernel: bit-reproducible run to run.
 //
 // Algorithmic bytes per image: forward A*(4C+16)+20M, forward+backward A*(8C+32)+20M.
 #include <stdlib.h>
@@ -48,9 +50,8 @@
 #include "k7_common.cuh"
 
 #define K7_ROWS_THREADS 256
-#define K7_ROWS_PER 4                                      // anchors per thread and chunk
+#define K7_ROWS_PER 8                                      // anchors per thread and chunk
 #define K7_ROWS_CHUNK (K7_ROWS_THREADS * K7_ROWS_PER)      // anchors per block and chunk
-#define K7_ROWS_MAX_GX 2048
 
 struct K7LossDev {
     float alpha, one_m_alpha;
@@ -62,6 +63,16 @@ struct K7LossDev {
     int dreg_prezeroed;
     int from_logits;
     int B, A, C, M;
+};
+
+// where the row kernel takes the assignment from
+struct K7AssignSrc {
+    const int32_t* words;               // k7_match's packed state / row words, or
+    const unsigned long long* best;     // k7_match_scatter's maxima (generation | IoU bits | ~row)
+    unsigned int gen;
+    float neg_thr, pos_thr;
+    int32_t* words_out;                 // optional: the words, written on the way
+    int consume;                        // best entries of this generation are zeroed once read (graph replay)
 };
 
 // The batch sums of the OTHER ranks, exchanged by the last block of the row kernel over peer memory
@@ -83,15 +94,11 @@ __device__ __forceinline__ float2 k7_loss_scales(const int n, const float mean_d
     return s;
 }
 
-// One bit per anchor: set = the row is ignored (losses.py:79-82: neither negative nor positive).
-// Layout: image b owns words [b*W, (b+1)*W), W = K7_IGNORE_WORDS(A); bit a%32 of word a/32.
-__global__ void __launch_bounds__(K7_ROWS_THREADS)
-k7_loss_bits_kernel(const int32_t* __restrict__ assign, int A, int W, uint32_t* __restrict__ bits) {
-    const int b = blockIdx.y;
-    const int a = blockIdx.x * K7_ROWS_THREADS + threadIdx.x;
-    const int st = (a < A) ? K7_ASSIGN_STATE(__ldg(assign + (size_t)b * A + a)) : K7_STATE_NEG;
-    const unsigned bal = __ballot_sync(0xffffffffu, st == K7_STATE_IGNORE);
-    if ((threadIdx.x & 31) == 0 && a < A) bits[(size_t)b * W + (a >> 5)] = bal;
+// does image b have an annotation row with label != -1 (losses.py:49-60)?  Warp-wide.
+__device__ __forceinline__ bool k7_warp_any_valid(const float* __restrict__ annotations, int M, int b, int lane) {
+    bool v = false;
+    for (int m = lane; m < M; m += 32) v |= __ldg(annotations + ((size_t)b * M + m) * 5 + 4) != -1.0f;
+    return __any_sync(0xffffffffu, v);
 }
 
 // ------------------------------------------------------------------ element math
@@ -139,11 +146,10 @@ __device__ __forceinline__ float2 k7_sigmoid_pair_grad(const float2 z, float2& e
 }
 
 // Two "target 0" elements.  Returns their gradients (GRAD), accumulates p^2 * -log(1-p) into acc
-// and max(p) into pmax.  ign: bit 0 / bit 1 = element belongs to an ignored row.  LOGITS: the
-// inputs are pre-sigmoid logits (the head's sigmoid is fused here) and the gradient is d/dz.
-template <bool GRAD, bool MASKED, bool LOGITS>
-__device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t ign, const float2 sco, float2& acc,
-                                              float& pmax) {
+// and max(p) into pmax.  LOGITS: the inputs are pre-sigmoid logits (the head's sigmoid is fused
+// here) and the gradient is d/dz.
+template <bool GRAD, bool LOGITS>
+__device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const float2 sco, float2& acc, float& pmax) {
     float2 dsig = make_float2(1.0f, 1.0f), ez = make_float2(0.0f, 0.0f);
     const float2 x = LOGITS ? (GRAD ? k7_sigmoid_pair_grad(xin, ez, dsig) : k7_sigmoid_pair(xin)) : xin;
     float2 p;
@@ -160,11 +166,7 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t i
     s = __ffma2_rn(s, pp, make_float2(0.5000072717666626f, 0.5000072717666626f));
     s = __ffma2_rn(s, pp, one);
     const float2 nl = __fmul2_rn(pp, s);           // -log(q)
-    float2 t = __fmul2_rn(p, p);
-    if (MASKED) {
-        if (ign & 1u) t.x = 0.0f;
-        if (ign & 2u) t.y = 0.0f;
-    }
+    const float2 t = __fmul2_rn(p, p);
     acc = __ffma2_rn(t, nl, acc);
     float2 g = make_float2(0.0f, 0.0f);
     if (GRAD) {
@@ -182,43 +184,31 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const uint32_t i
         if (LOGITS) w = __fmul2_rn(w, dsig);                                 // chain rule through the sigmoid
         g = __fmul2_rn(w, v);
         // torch.clamp passes the gradient on the closed interval  <=>  clamp(x) == x
-        const bool k0 = (p.x == x.x) && !(MASKED && (ign & 1u));
-        const bool k1 = (p.y == x.y) && !(MASKED && (ign & 2u));
-        g.x = k0 ? g.x : 0.0f;
-        g.y = k1 ? g.y : 0.0f;
+        g.x = (p.x == x.x) ? g.x : 0.0f;
+        g.y = (p.y == x.y) ? g.y : 0.0f;
     }
     return g;
 }
 
-template <bool GRAD, bool MASKED, bool LOGITS>
-__device__ __forceinline__ void k7_flat4(float4* __restrict__ p4, const uint32_t nib, const float2 sco, float2& acc,
-                                         float& pmax) {
+template <bool GRAD, bool LOGITS>
+__device__ __forceinline__ void k7_flat4(float4* __restrict__ p4, const float2 sco, float2& acc, float& pmax) {
     const float4 x = *p4;
-    const float2 ga = k7_neg_pair<GRAD, MASKED, LOGITS>(make_float2(x.x, x.y), nib & 3u, sco, acc, pmax);
-    const float2 gb = k7_neg_pair<GRAD, MASKED, LOGITS>(make_float2(x.z, x.w), (nib >> 2) & 3u, sco, acc, pmax);
+    const float2 ga = k7_neg_pair<GRAD, LOGITS>(make_float2(x.x, x.y), sco, acc, pmax);
+    const float2 gb = k7_neg_pair<GRAD, LOGITS>(make_float2(x.z, x.w), sco, acc, pmax);
     if (GRAD) *p4 = make_float4(ga.x, ga.y, gb.x, gb.y);
 }
 
-// The flat pass over n4 float4s of a tile.  mask: one bit per element (set = ignored row).
-template <int TILE_F, bool GRAD, bool MASKED, bool LOGITS>
-__device__ __forceinline__ void k7_flat_pass(float* __restrict__ tile, const int n4, const uint32_t* __restrict__ mask,
-                                             const int lane, const float sco1, float2& acc, float& pmax) {
+// The flat pass over the n4 float4s of a slice.
+template <int TILE_F, bool GRAD, bool LOGITS>
+__device__ __forceinline__ void k7_flat_pass(float* __restrict__ tile, const int n4, const int lane, const float sco1,
+                                             float2& acc, float& pmax) {
     float4* t4 = reinterpret_cast<float4*>(tile);
     const float2 sco = make_float2(sco1, sco1);
-    const int sh = (lane & 7) * 4;
     if (n4 == TILE_F / 4) {
 #pragma unroll
-        for (int k = 0; k < TILE_F / 128; ++k) {
-            uint32_t nib = 0;
-            if (MASKED) nib = (mask[(lane >> 3) + 4 * k] >> sh) & 15u;
-            k7_flat4<GRAD, MASKED, LOGITS>(t4 + lane + 32 * k, nib, sco, acc, pmax);
-        }
+        for (int k = 0; k < TILE_F / 128; ++k) k7_flat4<GRAD, LOGITS>(t4 + lane + 32 * k, sco, acc, pmax);
     } else {
-        for (int f = lane; f < n4; f += 32) {
-            uint32_t nib = 0;
-            if (MASKED) nib = (mask[f >> 3] >> sh) & 15u;
-            k7_flat4<GRAD, MASKED, LOGITS>(t4 + f, nib, sco, acc, pmax);
-        }
+        for (int f = lane; f < n4; f += 32) k7_flat4<GRAD, LOGITS>(t4 + f, sco, acc, pmax);
     }
 }
 
@@ -259,32 +249,21 @@ __device__ __forceinline__ float k7_row_smooth_l1(const K7AnchorSpec& spec, cons
     return l;
 }
 
-// bits [lo, hi) of a span of elements -> the 32-bit mask word whose first element is `base`
-__device__ __forceinline__ uint32_t k7_range_bits(int lo, int hi, int base) {
-    const int a = max(lo - base, 0), z = min(hi - base, 32);
-    if (z <= a) return 0u;
-    return (z - a == 32) ? 0xffffffffu : (((1u << (z - a)) - 1u) << a);
-}
-
 // ------------------------------------------------------------------ the stream kernel
 // One CTA per SM.  Warp CW is the PRODUCER: one elected lane cuts the flat batch into tiles of
-// CW*512 floats, issues the TMA loads (classification tile + the ignore bits of the rows it
-// touches) into a ring of NS stages, and, once the CW consumer warps have signalled a stage done,
-// the TMA store of the gradients.  Warps 0..CW-1 are CONSUMERS: warp w owns floats
-// [SL*w, SL*w+SL) of every tile (SL = 512 or 1024).  full[s] / done[s] are mbarriers; there is no
-// __syncthreads after the prologue.
+// CW*SL floats, issues the TMA loads into a ring of NS stages, and, once the CW consumer warps have
+// signalled a stage done, the TMA store of the gradients.  Warps 0..CW-1 are CONSUMERS: warp w owns
+// floats [SL*w, SL*w+SL) of every tile (SL = 512 or 1024).  full[s] / done[s] are mbarriers; there
+// is no __syncthreads after the prologue.
 #define K7_PIPE_MAX_CW 16
 
-// One contiguous stream of a launch: the [B,A,C] tensor, or one pyramid level in its C == 1 mode.
+// One contiguous stream of a launch: the [B,A,C] tensor, or one pyramid level of the per-level layout.
 struct K7PipeSeg {
     const float* cls;
     float* dcls;
-    const uint32_t* bits;
-    unsigned long long N;    // B*A*C elements
+    unsigned long long N;    // B * AC elements
     unsigned long long N4;   // N & ~3: the part moved by 16-byte bulk copies
     unsigned long long AC;   // elements per image
-    uint32_t A;              // rows per image
-    uint32_t W;              // ignore-bit words per image, K7_IGNORE_WORDS(A)
     uint32_t tile0;          // first tile of the stream in the launch's tile order
     uint32_t pad;
 };
@@ -297,30 +276,26 @@ struct K7PipeGeom {
     uint32_t tile_f;         // floats per tile = cw * slice
     uint32_t slice;          // floats per consumer warp and tile: 512 or 1024
     uint32_t num_tiles;      // sum over the streams of ceil(N4 / tile_f)
-    K7FastDiv div_c;         // / C for tile-local indices
     uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x]
-    uint32_t side_words;     // words reserved per ignore-bit part (two parts per stage)
     uint32_t stage_stride;
-    uint32_t off_desc, off_mask, off_bars;
+    uint32_t off_desc, off_bars;
     int stages, cw, grid;
     size_t smem_bytes;
 };
 
-struct K7TileDesc {   // written by the producer next to each stage, 48 bytes
-    uint32_t n, rem, split, b0;     // floats in the tile | position of float 0 in its row | floats that belong to image b0 | image of float 0
-    uint32_t lead, kA, split2, a0;  // bit of tile row 0 in part 0 | tile row where image b0+1 starts | floats up to the end of image b0+1 | anchor of tile row 0
-    uint32_t off_lo, off_hi, seg, pad1;    // flat index of float 0 in its stream | the stream
+struct K7TileDesc {   // written by the producer next to each stage, 32 bytes
+    uint32_t n, b0, split, split2;     // floats in the tile | image of float 0 | floats that belong to image b0 | ... up to the end of image b0+1
+    uint32_t off_lo, off_hi, seg, pad; // flat index of float 0 in its stream | the stream
 };
 
 template <bool GRAD, int SL, bool LOGITS>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
 k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __restrict__ num_pos,
-                    const __grid_constant__ K7LossDev P, const __grid_constant__ K7PipeGeom G,
-                    float* __restrict__ partials, float* __restrict__ cta_partials) {
+                    const float* __restrict__ annotations, const __grid_constant__ K7LossDev P,
+                    const __grid_constant__ K7PipeGeom G, float* __restrict__ partials, float* __restrict__ cta_partials) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
-    const int C = P.C;
     K7TileDesc* desc = reinterpret_cast<K7TileDesc*>(smem + G.off_desc);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + G.off_bars);
     uint64_t* done = full + NS;
@@ -340,61 +315,38 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
     if (warp == CW) {
         // ================================================================ producer
         if (lane != 0) return;
-        // The descriptor of the NEXT tile is worked out (two 64-bit divisions, table look-ups) while the
-        // producer would otherwise wait for a stage: a tile lasts ~0.8 us, the arithmetic must stay off
-        // the path between "stage free" and "copy issued".
+        // The descriptor of the NEXT tile is worked out (64-bit divisions) while the producer would
+        // otherwise wait for a stage: a tile lasts ~0.8 us, the arithmetic must stay off the path
+        // between "stage free" and "copy issued".
         K7TileDesc nd;
         const float* n_src = nullptr;
-        const uint32_t *n_bits0 = nullptr, *n_bits1 = nullptr;
-        uint32_t n_words0 = 0u, n_words1 = 0u;
         auto prepare = [&](const uint32_t j) {
             const uint32_t g = blockIdx.x + j * gridDim.x;
             int sg = 0;
             for (int i = 1; i < SG.n; ++i)
                 if (g >= SG.s[i].tile0) sg = i;
             const K7PipeSeg& Q = SG.s[sg];
-            const uint32_t A = Q.A;
             const unsigned long long off = (unsigned long long)(g - Q.tile0) * G.tile_f;
             const unsigned long long left = Q.N4 - off;
             K7TileDesc d;
             d.n = left < G.tile_f ? (uint32_t)left : G.tile_f;
-            const unsigned long long r0 = off / (uint32_t)C;   // first row (batch-global) touching the tile
-            d.rem = (uint32_t)(off - r0 * (uint32_t)C);
-            d.b0 = (uint32_t)(r0 / A);
-            d.a0 = (uint32_t)(r0 - (unsigned long long)d.b0 * A);
+            d.b0 = (uint32_t)(off / Q.AC);
             const unsigned long long in_img = (unsigned long long)(d.b0 + 1u) * Q.AC - off;
             d.split = in_img < d.n ? (uint32_t)in_img : d.n;
-            const uint32_t nrows = k7_div(d.rem + d.n - 1u, G.div_c) + 1u;
-            d.kA = A - d.a0;
-            const uint32_t w0 = (d.a0 >> 7) << 2;   // 16-byte aligned first word of part 0
-            d.lead = d.a0 - (w0 << 5);
-            const uint32_t rows0 = nrows < d.kA ? nrows : d.kA;
-            n_words0 = ((d.lead + rows0 + 127u) >> 7) << 2;
-            n_words1 = 0u;
-            if (nrows > d.kA && d.b0 + 1u < (uint32_t)P.B) {
-                const uint32_t rows1 = min(nrows - d.kA, A);
-                n_words1 = ((rows1 + 127u) >> 7) << 2;
-            }
             const unsigned long long in_img2 = in_img + Q.AC;
             d.split2 = in_img2 < d.n ? (uint32_t)in_img2 : d.n;
             d.off_lo = (uint32_t)off;
             d.off_hi = (uint32_t)(off >> 32);
             d.seg = (uint32_t)sg;
-            d.pad1 = 0u;
+            d.pad = 0u;
             nd = d;
             n_src = Q.cls + off;
-            n_bits0 = Q.bits + (size_t)d.b0 * Q.W + w0;
-            n_bits1 = Q.bits + (size_t)(d.b0 + 1u) * Q.W;
         };
         auto issue = [&](const uint32_t j) {   // the prepared tile is tile j
             const int s = (int)(j % (uint32_t)NS);
-            unsigned char* stage = smem + (size_t)s * G.stage_stride;
             desc[s] = nd;
-            uint32_t* side = reinterpret_cast<uint32_t*>(stage + (size_t)G.tile_f * 4);
-            k7_mbar_expect_tx(full + s, nd.n * 4u + (n_words0 + n_words1) * 4u);   // release: orders the descriptor
-            k7_bulk_g2s(stage, n_src, nd.n * 4u, full + s);
-            k7_bulk_g2s(side, n_bits0, n_words0 * 4u, full + s);
-            if (n_words1) k7_bulk_g2s(side + G.side_words, n_bits1, n_words1 * 4u, full + s);
+            k7_mbar_expect_tx(full + s, nd.n * 4u);   // release: orders the descriptor
+            k7_bulk_g2s(smem + (size_t)s * G.stage_stride, n_src, nd.n * 4u, full + s);
         };
         // with gradients one stage is always draining its store
         const uint32_t ahead = (uint32_t)(GRAD ? NS - 1 : NS);
@@ -433,7 +385,6 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
     if (warp > CW) return;
 
     // ==================================================================== consumers
-    uint32_t* mask = reinterpret_cast<uint32_t*>(smem + G.off_mask) + warp * (SL / 32);
     float* my_partials = partials + (size_t)blockIdx.x * CW + warp;      // + b * (gridDim.x * CW)
     const size_t pstride = (size_t)gridDim.x * CW;
     for (int b = lane; b < P.B; b += 32) my_partials[(size_t)b * pstride] = 0.0f;
@@ -457,13 +408,13 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         if (b == cur_b) return;
         if (cur_b >= 0) flush();
         cur_b = b;
-        if (GRAD) sco = oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x;
+        if (GRAD)   // an image without ground truth is skipped by the reference (losses.py:52-60): no gradient
+            sco = k7_warp_any_valid(annotations, P.M, b, lane) ? oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x : 0.0f;
     };
-    auto exact = [&](const float x, const bool ign, float* gout) {
+    auto exact = [&](const float x, float* gout) {
         float gr;
-        const float l = k7_neg_exact(x, &gr, LOGITS);
-        if (!ign) cslow += l;
-        if (GRAD) *gout = ign ? 0.0f : sco * gr;
+        cslow += k7_neg_exact(x, &gr, LOGITS);
+        if (GRAD) *gout = sco * gr;
     };
     const int i_lo = warp * SL;
 
@@ -475,104 +426,42 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         if (s == 0) phase ^= 1u;
         unsigned char* stage = smem + (size_t)s * G.stage_stride;
         k7_mbar_wait_u32(full_u32 + 8u * s, phase);
-        const uint4 d0 = *reinterpret_cast<const uint4*>(desc + s);   // n, rem, split, b0
+        const uint4 d0 = *reinterpret_cast<const uint4*>(desc + s);   // n, b0, split, split2
         const int n = (int)d0.x;
         if (i_lo < n) {
-            const int rem = (int)d0.y;
             const int i_hi = min(n, i_lo + SL);
             const int len = i_hi - i_lo, n4 = len >> 2;
             float* tile = reinterpret_cast<float*>(stage);
             float* slice = tile + i_lo;
-            const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // lead, kA, split2, a0
-            // which image does the slice lie in?  bitbase = bit position of tile row 0 of that image's part
-            int img = -1, bitbase = 0;
-            if ((uint32_t)i_hi <= d0.z) {
-                img = (int)d0.w;
-                bitbase = (int)d1.x;
-            } else if ((uint32_t)i_lo >= d0.z && (uint32_t)i_hi <= d1.z) {
-                img = (int)d0.w + 1;
-                bitbase = (int)(G.side_words * 32u) - (int)d1.y;   // part 1 starts at tile row kA
-            }
+            int img = -1;   // which image does the slice lie in?
+            if ((uint32_t)i_hi <= d0.z) img = (int)d0.y;
+            else if ((uint32_t)i_lo >= d0.z && (uint32_t)i_hi <= d0.w) img = (int)d0.y + 1;
             if (img >= 0) {
                 enter(img);
-                const uint32_t* side = reinterpret_cast<const uint32_t*>(stage + (size_t)G.tile_f * 4);
-                const int k_lo = (int)k7_div((uint32_t)(rem + i_lo), G.div_c);
-                const int k_hi = (int)k7_div((uint32_t)(rem + i_hi - 1), G.div_c);
-
-                // ---- ignored rows of the slice -> element mask
-                uint32_t mword = 0u;
-                bool masked = false;
-                if (C == 1) {
-                    // a row is one element: lane L's mask word is 32 consecutive bits of the bitmap
-                    const int k0 = k_lo + 32 * lane;
-                    if (lane < SL / 32 && k0 <= k_hi) {
-                        const int p = bitbase + k0;
-                        mword = __funnelshift_r(side[p >> 5], side[(p >> 5) + 1], (uint32_t)p & 31u);
-                        const int nv = k_hi - k0 + 1;
-                        if (nv < 32) mword &= (1u << nv) - 1u;
-                    }
-                    masked = __any_sync(0xffffffffu, mword != 0u);
-                } else {
-                    for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {   // warp-uniform window reads
-                        const int p = bitbase + k0;
-                        const uint32_t lo = side[p >> 5], hi = side[(p >> 5) + 1];
-                        uint32_t win = __funnelshift_r(lo, hi, (uint32_t)p & 31u);
-                        const int nv = k_hi - k0 + 1;
-                        if (nv < 32) win &= (1u << nv) - 1u;
-                        if (win == 0u) continue;
-                        masked = true;
-                        while (win) {
-                            const int kk = k0 + __ffs(win) - 1;
-                            win &= win - 1u;
-                            const int e_lo = kk * C - rem - i_lo;
-                            mword |= k7_range_bits(max(e_lo, 0), min(e_lo + C, len), 32 * lane);
-                        }
-                    }
-                }
-                if (masked) {
-                    if (lane < SL / 32) mask[lane] = mword;
-                    __syncwarp();
-                }
-
-                // ---- flat pass
                 const float2 acc0 = acc;
                 float pmax = 0.0f;
-                if (masked)
-                    k7_flat_pass<SL, GRAD, true, LOGITS>(slice, n4, mask, lane, sco, acc, pmax);
-                else
-                    k7_flat_pass<SL, GRAD, false, LOGITS>(slice, n4, mask, lane, sco, acc, pmax);
+                k7_flat_pass<SL, GRAD, LOGITS>(slice, n4, lane, sco, acc, pmax);
                 if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
                     // a confident prediction: outside the polynomial's range.  Redo the slice exactly
                     // (with gradients the tile already holds them: the inputs come from global memory again).
                     __syncwarp();
                     acc = acc0;
-                    const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
-                    const float* src = SG.s[d2.z].cls + ((((unsigned long long)d2.y) << 32) | d2.x) + i_lo;
-                    for (int i = lane; i < len; i += 32) {
-                        const bool ign = masked && ((mask[i >> 5] >> (i & 31)) & 1u);
-                        exact(GRAD ? __ldg(src + i) : slice[i], ign, slice + i);
-                    }
+                    const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // off_lo, off_hi, seg
+                    const float* src = SG.s[d1.z].cls + ((((unsigned long long)d1.y) << 32) | d1.x) + i_lo;
+                    for (int i = lane; i < len; i += 32) exact(GRAD ? __ldg(src + i) : slice[i], slice + i);
                 }
             } else {
                 // ---- generic path: the slice straddles an image boundary (or the tile spans > 2 images)
-                const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);
-                const unsigned long long off = (((unsigned long long)d2.y) << 32) | d2.x;
-                const K7PipeSeg& Q = SG.s[d2.z];
-                const uint32_t A = Q.A;
-                const unsigned long long r0 = (unsigned long long)d0.w * A + d1.w;
+                const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);
+                const unsigned long long off = (((unsigned long long)d1.y) << 32) | d1.x;
+                const K7PipeSeg& Q = SG.s[d1.z];
                 uint32_t i = (uint32_t)i_lo;
                 while (i < (uint32_t)i_hi) {   // warp-uniform: one iteration per image segment
                     const uint32_t b = (uint32_t)((off + i) / Q.AC);
                     const unsigned long long img_end = (unsigned long long)(b + 1u) * Q.AC - off;
                     const uint32_t seg_end = img_end < (unsigned long long)i_hi ? (uint32_t)img_end : (uint32_t)i_hi;
                     enter((int)b);
-                    const unsigned long long abase = (unsigned long long)b * A;
-                    for (uint32_t t = i + lane; t < seg_end; t += 32) {
-                        const uint32_t k = k7_div((uint32_t)rem + t, G.div_c);
-                        const uint32_t a = (uint32_t)(r0 + k - abase);
-                        const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
-                        exact(tile[t], ign, tile + t);
-                    }
+                    for (uint32_t t = i + lane; t < seg_end; t += 32) exact(tile[t], tile + t);
                     i = seg_end;
                 }
             }
@@ -587,14 +476,10 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         for (int sg = 0; sg < SG.n; ++sg) {
             const K7PipeSeg& Q = SG.s[sg];
             for (unsigned long long e = Q.N4; e < Q.N; ++e) {
-                const uint32_t b = (uint32_t)(e / Q.AC);
-                enter((int)b);
+                enter((int)(e / Q.AC));
                 if (lane == 0) {
-                    const unsigned long long r = e / (uint32_t)C;
-                    const uint32_t a = (uint32_t)(r - (unsigned long long)b * Q.A);
-                    const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
                     float g = 0.0f;
-                    exact(__ldg(Q.cls + e), ign, &g);
+                    exact(__ldg(Q.cls + e), &g);
                     if (GRAD) Q.dcls[e] = g;
                 }
             }
@@ -614,90 +499,27 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
 // ------------------------------------------------------------------ head outputs per level
 // levels[l] = [B, K*C, S_l] (NCHW, S_l = fh*fw cells, channel = in-cell anchor k * C + class c): the
 // element of anchor a = offset[l] + s*K + k and class c sits at ((b*K*C + k*C + c) * S_l + s).
-// Seen as a flat stream every element is its own "row", so the stream kernel runs on a level in
-// its C == 1 mode with ONE IGNORE BIT PER ELEMENT, laid out like the tensor: bit (b, ch, s) = the
-// anchor's bit.  k7_bits_expand_kernel writes those words (1/32 of the tensor's bytes) from the
-// anchor-ordered bitmap of k7_match.
+// Every element is a "target 0" element whatever the layout, so the stream kernel runs over the
+// levels as ONE launch with a table of streams; the row kernel addresses the label element and
+// the elements of an ignored row through the level table below.
 struct K7LevelTable {
     const float* cls[K7_MAX_LEVELS];
     float* dcls[K7_MAX_LEVELS];
     int S[K7_MAX_LEVELS];
 };
 
-struct K7ExpandTable {
-    uint32_t* lbits[K7_MAX_LEVELS];
-    int level_off[K7_MAX_LEVELS], S[K7_MAX_LEVELS], Wl[K7_MAX_LEVELS];
-    int blk_off[K7_MAX_LEVELS + 1];   // first block of each level; [K7_MAX_LEVELS] = grid.x
-};
-
-// All levels in one launch, grid (blocks, B).  One thread per 32-cell word of an (image, in-cell
-// anchor) plane; the word is the same for all C classes of that anchor.  S % 32 == 0: whole words,
-// written C times.  Otherwise (small levels) one thread per output word gathers its 32 elements
-// individually.
-__global__ void __launch_bounds__(256)
-k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, const __grid_constant__ K7ExpandTable T, int K, int C) {
-    const int b = blockIdx.y;
-    int l = 0;
-#pragma unroll
-    for (int i = 1; i < K7_MAX_LEVELS; ++i)
-        if ((int)blockIdx.x >= T.blk_off[i]) l = i;
-    const int S = T.S[l], level_off = T.level_off[l];
-    const int blk = (int)blockIdx.x - T.blk_off[l];
-    const uint32_t* ab = abits + (size_t)b * W;
-    uint32_t* lb = T.lbits[l] + (size_t)b * T.Wl[l];
-    if ((S & 31) == 0) {
-        const int spw = S >> 5;                       // words per plane
-        const int t = blk * 256 + (int)threadIdx.x;
-        if (t >= K * spw) return;
-        const int k = t / spw, sw = t - k * spw;
-        uint32_t word = 0u;
-        int a = level_off + (sw << 5) * K + k;
-#pragma unroll 8
-        for (int j = 0; j < 32; ++j, a += K) word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
-        for (int c = 0; c < C; ++c) lb[(size_t)(k * C + c) * spw + sw] = word;
-    } else {
-        const int nel = K * C * S;                    // < 2^31 (checked by the plan)
-        const int w = blk * 256 + (int)threadIdx.x;
-        if (w >= (nel + 31) >> 5) return;
-        const int e0 = w << 5;
-        int ch = e0 / S, s = e0 - ch * S;             // plane (k*C + c) and cell of the word's first element
-        int k = ch / C, c = ch - k * C;
-        const int nb = min(32, nel - e0);
-        uint32_t word = 0u;
-        for (int j = 0; j < nb; ++j) {
-            const int a = level_off + s * K + k;
-            word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
-            if (++s == S) {                           // next plane: same anchor plane until the classes run out
-                s = 0;
-                if (++c == C) {
-                    c = 0;
-                    ++k;
-                }
-            }
-        }
-        lb[w] = word;
-    }
-}
-
 // ------------------------------------------------------------------ the row kernel
-// After the stream kernel.  A block re-reads the 4-byte assignment words of a chunk of 1024
-// anchors (four independent coalesced loads per thread); the positive anchors (~1-2 %) are queued
-// in shared memory (ballots + a prefix over the 32 ballot counts: anchor order) and then served by
-// dense warps: smooth-L1 + d(reg) (losses.py:122-166) and the
-// correction of the label element from "target 0" (what the stream computed) to "target 1"
-// (losses.py:94-97, 100-112) - the loss difference goes into the block's partial sum, the
-// gradient overwrites the stream's value in dcls.  Other anchors: d(reg) = 0 unless the caller
-// pre-zeroed it.  Grid (gx, B).
-// The reduction is fused behind it: the last block of an image (per-image counter) sums the
-// image's stream slots and row partials in float64 in slot order and writes (cls_loss_i,
-// reg_loss_i); the last image to finish sums the batch in image order.  No float atomics:
-// bit-reproducible run to run.
-
 __device__ __forceinline__ double k7_warp_sum_f64(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+__device__ __forceinline__ long long k7_warp_sum_i64(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+#define K7_FIX_ONE 4294967296.0   // fixed-point unit of the row accumulators: 2^-32
 
 // Sum of (c, r) over the block, result valid in thread 0.  Fixed order.  s_red: 2 * warps doubles.
 __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* s_red) {
@@ -722,75 +544,116 @@ __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* 
     }
 }
 
-template <bool GRAD, bool FROM_SPEC, bool LEVELS>
+// After the stream kernel.  Work item = a chunk of 2048 consecutive anchors of one image.
+//   scan    every thread reads 8 assignment entries (coalesced: entry j of thread t is anchor
+//           a0 + 256 j + t), zeroes d(reg) of the rows that are not positive, and queues positive
+//           rows from the front and ignored rows from the back of a shared-memory queue;
+//   serve   positive rows, a thread each: smooth-L1 + d(reg) (losses.py:122-166) and the
+//           correction of the label element from "target 0" (what the stream computed) to
+//           "target 1" (losses.py:94-112); ignored rows, a warp each: the row's C elements are
+//           evaluated again, exactly, and SUBTRACTED (the stream counted them), their gradients
+//           become 0 (losses.py:79-82, 114);
+//   fold    every thread turns its float partial sums into 2^-32 fixed point, the warp adds them
+//           (integers: exact) and one lane adds the result to the image's accumulators.
+// The last block to finish sums, per image, the stream's per-CTA partials in float64 in CTA order,
+// adds the accumulators and writes (cls_loss_i, reg_loss_i); then the batch sums in image order.
+// No float atomics anywhere: bit-reproducible run to run.
+template <bool GRAD, bool PACKED, bool FROM_SPEC, bool LEVELS>
 __global__ void __launch_bounds__(K7_ROWS_THREADS)
 k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7LevelTable LT,
                     const float* __restrict__ anchors, int box_order,
                     const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
-                    const int32_t* __restrict__ assign, const int32_t* __restrict__ num_pos,
+                    const __grid_constant__ K7AssignSrc SRC, const int32_t* __restrict__ num_pos,
                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7PeerDev PR,
                     const float* __restrict__ pipe_partials, uint32_t pipe_slots,
-                    float2* __restrict__ rows_partials, unsigned int* __restrict__ counters /* [B] images, [B] = batch */,
+                    long long* __restrict__ acc /* [B][2] */, unsigned int* __restrict__ counter,
                     float* __restrict__ per_image, float* __restrict__ sums, float* __restrict__ dcls,
                     float4* __restrict__ dreg) {
     constexpr int NW = K7_ROWS_THREADS / 32;
-    __shared__ int s_qa[K7_ROWS_CHUNK], s_qw[K7_ROWS_CHUNK];
-    __shared__ int s_off[K7_ROWS_PER * NW + 1];   // queue offset of every (round, warp) ballot; [last] = total
+    __shared__ int s_qa[K7_ROWS_CHUNK];       // anchor (image-local); positives from the front, ignored rows from the back
+    __shared__ int s_qr[K7_ROWS_CHUNK];       // annotation row of a positive
+    __shared__ int s_npos, s_nign;
     __shared__ double s_red[2 * NW];
     __shared__ bool s_last;
-    const int b = blockIdx.y;
     const int A = P.A, C = P.C;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
     const float oma = P.one_m_alpha;
-    float cfix = 0.0f, rsum = 0.0f;
+    const int cpi = (A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK;   // chunks per image
+    const long long total = (long long)P.B * cpi;
 
-    for (int a0 = blockIdx.x * K7_ROWS_CHUNK; a0 < A; a0 += gridDim.x * K7_ROWS_CHUNK) {   // block-uniform
-        // ---- scan: K7_ROWS_PER independent coalesced loads per thread, positives -> queue in anchor order
-        int aw[K7_ROWS_PER];
-        unsigned bal[K7_ROWS_PER];
-#pragma unroll
-        for (int k = 0; k < K7_ROWS_PER; ++k) {
-            const int a = a0 + k * K7_ROWS_THREADS + threadIdx.x;
-            aw[k] = (a < A) ? __ldg(assign + (size_t)b * A + a) : 0;
+    for (long long ch = blockIdx.x; ch < total; ch += gridDim.x) {   // block-uniform
+        const int b = (int)(ch / cpi);
+        const int a0 = (int)(ch - (long long)b * cpi) * K7_ROWS_CHUNK;
+        if (threadIdx.x == 0) {
+            s_npos = 0;
+            s_nign = 0;
         }
+        bool v = false;
+        for (int m = threadIdx.x; m < P.M; m += K7_ROWS_THREADS) v |= __ldg(annotations + ((size_t)b * P.M + m) * 5 + 4) != -1.0f;
+        const bool any_valid = __syncthreads_or(v ? 1 : 0) != 0;   // also: the queue counters are visible
+        const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
+
+        // ---- scan
+        int st[K7_ROWS_PER], rw[K7_ROWS_PER];
+        if (PACKED) {
+            unsigned long long e[K7_ROWS_PER];
 #pragma unroll
-        for (int k = 0; k < K7_ROWS_PER; ++k) {
-            const int a = a0 + k * K7_ROWS_THREADS + threadIdx.x;
-            const bool pos = (a < A) && K7_ASSIGN_STATE(aw[k]) == K7_STATE_POS;
-            if (GRAD && !P.dreg_prezeroed && a < A && !pos) dreg[(size_t)b * A + a] = make_float4(0.f, 0.f, 0.f, 0.f);
-            bal[k] = __ballot_sync(0xffffffffu, pos);
-            if (lane == 0) s_off[k * NW + warp] = __popc(bal[k]);
-        }
-        __syncthreads();
-        if (warp == 0) {   // exclusive scan of the K7_ROWS_PER * NW (= 32) counts
-            static_assert(K7_ROWS_PER * NW == 32, "one count per lane");
-            const int cnt = s_off[lane];
-            int inc = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += v;
+            for (int j = 0; j < K7_ROWS_PER; ++j) {
+                const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
+                e[j] = (a < A && any_valid) ? __ldcg(SRC.best + (size_t)b * A + a) : 0ull;
             }
-            s_off[lane] = inc - cnt;
-            if (lane == 31) s_off[32] = inc;
-        }
-        __syncthreads();
 #pragma unroll
-        for (int k = 0; k < K7_ROWS_PER; ++k) {
-            if ((bal[k] >> lane) & 1u) {
-                const int q = s_off[k * NW + warp] + __popc(bal[k] & ((1u << lane) - 1u));
-                s_qa[q] = a0 + k * K7_ROWS_THREADS + threadIdx.x;
-                s_qw[q] = aw[k];
+            for (int j = 0; j < K7_ROWS_PER; ++j) {
+                st[j] = K7_STATE_NEG;
+                rw[j] = 0;
+                if (K7_BEST_GEN(e[j]) == SRC.gen) {
+                    if (SRC.consume)
+                        const_cast<unsigned long long*>(SRC.best)[(size_t)b * A + a0 + j * K7_ROWS_THREADS + threadIdx.x] = 0ull;
+                    const float iou = __uint_as_float(K7_BEST_IOU_BITS(e[j]));
+                    st[j] = iou >= SRC.pos_thr ? K7_STATE_POS : (iou < SRC.neg_thr ? K7_STATE_NEG : K7_STATE_IGNORE);
+                    rw[j] = K7_BEST_ROW(e[j]);
+                }
+            }
+        } else {
+            int w[K7_ROWS_PER];
+#pragma unroll
+            for (int j = 0; j < K7_ROWS_PER; ++j) {
+                const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
+                w[j] = (a < A && any_valid) ? __ldg(SRC.words + (size_t)b * A + a) : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < K7_ROWS_PER; ++j) {
+                st[j] = K7_ASSIGN_STATE(w[j]);
+                rw[j] = K7_ASSIGN_ROW(w[j]);
             }
         }
-        __syncthreads();
-        // ---- serve the queue with dense warps: thread t takes entries t, t+256, ...
-        const int qn = s_off[32];
-        for (int i = threadIdx.x; i < qn; i += K7_ROWS_THREADS) {
-            const int a = s_qa[i], w = s_qw[i];
+#pragma unroll
+        for (int j = 0; j < K7_ROWS_PER; ++j) {
+            const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
+            if (a >= A) continue;
+            if (!any_valid) st[j] = K7_STATE_IGNORE;   // the whole image is skipped (losses.py:52-60)
             const size_t R = (size_t)b * A + a;
-            const float* arow = annotations + ((size_t)b * P.M + K7_ASSIGN_ROW(w)) * 5;
+            if (SRC.words_out) SRC.words_out[R] = (rw[j] << 2) | st[j];
+            if (GRAD && !P.dreg_prezeroed && st[j] != K7_STATE_POS) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (!any_valid) continue;
+            if (st[j] == K7_STATE_POS) {
+                const int q = atomicAdd(&s_npos, 1);
+                s_qa[q] = a;
+                s_qr[q] = rw[j];
+            } else if (st[j] == K7_STATE_IGNORE) {
+                const int q = atomicAdd(&s_nign, 1);
+                s_qa[K7_ROWS_CHUNK - 1 - q] = a;   // a chunk holds at most K7_ROWS_CHUNK rows: the two ends never meet
+            }
+        }
+        __syncthreads();
+
+        // ---- serve
+        float cfix = 0.0f, rsum = 0.0f;
+        const int npos = s_npos, nign = s_nign;
+        for (int i = threadIdx.x; i < npos; i += K7_ROWS_THREADS) {
+            const int a = s_qa[i];
+            const size_t R = (size_t)b * A + a;
+            const float* arow = annotations + ((size_t)b * P.M + s_qr[i]) * 5;
             rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
             const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
             if (label >= 0 && label < C) {
@@ -800,8 +663,8 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                 if (LEVELS) {   // NCHW per level: ((b*K*C + k*C + label) * S + cell)
                     int l = 0;
 #pragma unroll
-                    for (int i = 1; i < K7_MAX_LEVELS; ++i)
-                        if (i < spec.num_levels && a >= spec.offset[i]) l = i;
+                    for (int i2 = 1; i2 < K7_MAX_LEVELS; ++i2)
+                        if (i2 < spec.num_levels && a >= spec.offset[i2]) l = i2;
                     const int r = a - spec.offset[l], K = spec.cell_anchors;
                     const int cell = r / K, k = r - cell * K;
                     e = ((size_t)b * K * C + (size_t)k * C + (size_t)label) * (size_t)LT.S[l] + (size_t)cell;
@@ -819,65 +682,77 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                 }
             }
         }
+        float csub = 0.0f;   // what the stream added for the ignored rows (without the (1-alpha) factor)
+        for (int i = warp; i < nign; i += NW) {
+            const int a = s_qa[K7_ROWS_CHUNK - 1 - i];
+            if (LEVELS) {
+                int l = 0;
+#pragma unroll
+                for (int i2 = 1; i2 < K7_MAX_LEVELS; ++i2)
+                    if (i2 < spec.num_levels && a >= spec.offset[i2]) l = i2;
+                const int r = a - spec.offset[l], K = spec.cell_anchors;
+                const int cell = r / K, k = r - cell * K;
+                const size_t S = (size_t)LT.S[l];
+                const size_t e0 = ((size_t)b * K * C + (size_t)k * C) * S + (size_t)cell;
+                for (int c = lane; c < C; c += 32) {
+                    csub += k7_neg_exact(__ldg(LT.cls[l] + e0 + (size_t)c * S), nullptr, P.from_logits != 0);
+                    if (GRAD) LT.dcls[l][e0 + (size_t)c * S] = 0.0f;
+                }
+            } else {
+                const size_t e0 = ((size_t)b * A + a) * (size_t)C;
+                for (int c = lane; c < C; c += 32) {
+                    csub += k7_neg_exact(__ldg(cls + e0 + c), nullptr, P.from_logits != 0);
+                    if (GRAD) dcls[e0 + c] = 0.0f;
+                }
+            }
+        }
+
+        // ---- fold: float partials of this thread -> fixed point -> integer sum of the warp -> the image's accumulators
+        if (npos > 0 || nign > 0) {   // block-uniform
+            long long ic = __double2ll_rn(((double)cfix - (double)oma * (double)csub) * K7_FIX_ONE);
+            long long ir = __double2ll_rn((double)rsum * K7_FIX_ONE);
+            ic = k7_warp_sum_i64(ic);
+            ir = k7_warp_sum_i64(ir);
+            if (lane == 0) {
+                if (ic) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b), (unsigned long long)ic);
+                if (ir) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b + 1), (unsigned long long)ir);
+                __threadfence();   // performed before this block's tick of the completion counter
+            }
+        }
         __syncthreads();   // the queue is rewritten by the next chunk
     }
 
-    double c = (double)cfix, r = (double)rsum;
-    {   // block partial in float32, fixed order (warp tree, then warps in order)
-        float cf = k7_warp_sum(cfix), rf = k7_warp_sum(rsum);
-        __shared__ float s_c[NW], s_r[NW];
-        if (lane == 0) {
-            s_c[warp] = cf;
-            s_r[warp] = rf;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            cf = rf = 0.0f;
-#pragma unroll
-            for (int w = 0; w < NW; ++w) {
-                cf += s_c[w];
-                rf += s_r[w];
-            }
-            rows_partials[(size_t)b * gridDim.x + blockIdx.x] = make_float2(cf, rf);
-            __threadfence();
-            s_last = atomicAdd(counters + b, 1u) == gridDim.x - 1u;
-        }
-        __syncthreads();
-    }
-    if (!s_last) return;
-
-    // ---- last block of image b: per-image sums (losses.py:118, 161-166)
-    __threadfence();
-    c = 0.0;
-    r = 0.0;
-    const float* pp = pipe_partials + (size_t)b * pipe_slots;
-    for (uint32_t t = threadIdx.x; t < pipe_slots; t += K7_ROWS_THREADS) c += (double)__ldcg(pp + t);
-    const float2* rp = rows_partials + (size_t)b * gridDim.x;
-    for (uint32_t t = threadIdx.x; t < gridDim.x; t += K7_ROWS_THREADS) {
-        const float2 p = __ldcg(rp + t);
-        c += (double)p.x;
-        r += (double)p.y;
-    }
-    k7_block_sum2_f64(c, r, s_red);
+    // ---- the last block to finish reduces
     if (threadIdx.x == 0) {
-        const int n = num_pos[b];
-        per_image[2 * b + 0] = (float)c / fmaxf((float)n, 1.0f);
-        per_image[2 * b + 1] = n > 0 ? (float)(r / (4.0 * (double)n)) : 0.0f;
-        counters[b] = 0u;   // re-arm for the next call on this workspace
         __threadfence();
-        s_last = atomicAdd(counters + P.B, 1u) == (unsigned int)(P.B - 1);
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1u;
     }
     __syncthreads();
     if (!s_last) return;
-
-    // ---- last image: batch sums in image order
     __threadfence();
-    c = 0.0;
-    r = 0.0;
-    double nn = 0.0, zero = 0.0;
+    // per-image sums (losses.py:118, 161-166): a warp per image, the stream's per-CTA partials in CTA order
+    for (int b = warp; b < P.B; b += NW) {
+        const float* pp = pipe_partials + (size_t)b * pipe_slots;
+        double c = 0.0;
+        for (uint32_t t = lane; t < pipe_slots; t += 32) c += (double)__ldcg(pp + t);
+        c = k7_warp_sum_f64(c);
+        const bool any_valid = k7_warp_any_valid(annotations, P.M, b, lane);
+        if (lane == 0) {
+            const int n = num_pos[b];
+            const double fc = (double)__ldcg(acc + 2 * b) * (1.0 / K7_FIX_ONE);
+            const double fr = (double)__ldcg(acc + 2 * b + 1) * (1.0 / K7_FIX_ONE);
+            per_image[2 * b + 0] = any_valid ? (float)(c + fc) / fmaxf((float)n, 1.0f) : 0.0f;
+            per_image[2 * b + 1] = (any_valid && n > 0) ? (float)(fr / (4.0 * (double)n)) : 0.0f;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *counter = 0u;   // re-armed for the next call on this workspace
+
+    // ---- batch sums in image order
+    double c = 0.0, r = 0.0, nn = 0.0, zero = 0.0;
     for (int i = threadIdx.x; i < P.B; i += K7_ROWS_THREADS) {
-        c += (double)__ldcg(per_image + 2 * i);
-        r += (double)__ldcg(per_image + 2 * i + 1);
+        c += (double)per_image[2 * i];
+        r += (double)per_image[2 * i + 1];
         nn += (double)num_pos[i];
     }
     k7_block_sum2_f64(c, r, s_red);
@@ -885,7 +760,6 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
     __shared__ float4 s_mine, s_got[K7_MAX_PEERS];
     if (threadIdx.x == 0) {
         s_mine = make_float4((float)c, (float)r, (float)nn, (float)P.B);
-        counters[P.B] = 0u;
         if (PR.world <= 1) {
             sums[0] = s_mine.x;
             sums[1] = s_mine.y;
@@ -1020,42 +894,32 @@ extern "C" int k7_scale_inplace_multi(float* const* grads, const size_t* n, cons
 // ------------------------------------------------------------------ host side
 #define K7_LOSS_MAX_GRID 256   // upper bound on CTAs assumed by the workspace query
 
-static int k7_rows_gx(int B, int A) {
-    (void)B;
-    int gx = (A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK;   // one chunk per block unless the image is huge
-    if (gx > K7_ROWS_MAX_GX) gx = K7_ROWS_MAX_GX;
-    return gx < 1 ? 1 : gx;
-}
-
 // ------------------------------------------------------------------ workspace + launch plan
 // One plan serves both entry points: k7_loss streams ONE tensor [B,A,C]; k7_loss_levels streams
-// one NCHW tensor per pyramid level in the stream kernel's C == 1 mode (see K7LevelTable).
+// one NCHW tensor per pyramid level (see K7LevelTable).
 struct K7LossPlan {
     int nseg;                               // streams of the one launch: 1, or the non-empty pyramid levels
     K7PipeGeom G;
     int level[K7_MAX_LEVELS];               // pyramid level of each stream (levels mode)
     unsigned long long AC[K7_MAX_LEVELS];   // elements per image of each stream
     uint32_t tile0[K7_MAX_LEVELS];
-    size_t off_lbits[K7_MAX_LEVELS];        // expanded ignore bits of the level
     size_t off_pipe;                        // per-warp slots of the launch
-    size_t off_counter, off_bits, off_cta, off_rows, total;
+    size_t off_counter, off_acc, off_cta, total;
     uint32_t cta_stride;
-    int gx;
 };
 
-static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g);
+static int k7_pipe_geometry(bool grad, K7PipeGeom* g);
 
-// levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`, each
-// in the C == 1 mode (every element its own row).
+// levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
 static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
                         K7LossPlan* p) {
     p->nseg = 0;
     size_t o = 0;
-    p->off_counter = o;   // [B] per-image block counters + 1 batch counter
-    o += k7_align_up(sizeof(unsigned int) * ((size_t)B + 1), 256);
-    p->off_bits = o;      // anchor-ordered ignore bits when the caller did not keep k7_match's
-    o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(A), 256);
-    int rc = k7_pipe_geometry(levels ? 1 : C, grad, &p->G);
+    p->off_counter = o;   // the row kernel's block counter
+    o += 256;
+    p->off_acc = o;       // [B][2] fixed-point row accumulators
+    o += k7_align_up(sizeof(long long) * 2 * (size_t)B, 256);
+    int rc = k7_pipe_geometry(grad, &p->G);
     if (rc) return rc;
     unsigned long long tiles = 0;
     const int nl = levels ? spec->num_levels : 1;
@@ -1072,8 +936,6 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
         p->tile0[i] = (uint32_t)tiles;
         tiles += (((ac * (unsigned long long)B) & ~3ull) + p->G.tile_f - 1) / p->G.tile_f;
         K7_REQUIRE(tiles < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", tiles);
-        p->off_lbits[i] = o;
-        if (levels) o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(ac), 256);
     }
     p->G.num_tiles = (uint32_t)tiles;
     int grid = exact_grid ? k7_sm_count() : K7_LOSS_MAX_GRID;   // the workspace query has no device: assume the largest grid
@@ -1086,9 +948,6 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
     o += k7_align_up(sizeof(float) * (size_t)B * (size_t)p->G.grid * K7_PIPE_MAX_CW, 256);
     p->off_cta = o;       // [B][cta_stride] stream partials, one per (image, CTA)
     o += k7_align_up(sizeof(float) * (size_t)B * p->cta_stride, 256);
-    p->gx = k7_rows_gx(B, A);
-    p->off_rows = o;
-    o += k7_align_up(sizeof(float2) * (size_t)B * p->gx, 256);
     p->total = o;
     return K7_OK;
 }
@@ -1113,10 +972,10 @@ static int k7_env_int(const char* name, int dflt) {
     return atoi(v);
 }
 
-static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g) {
-    // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass is bound by per-slice bookkeeping and
-    // wants long slices (12 warps x 1024 floats); with gradients the stream is a copy and wants
-    // the most warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
+static int k7_pipe_geometry(bool grad, K7PipeGeom* g) {
+    // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass wants long slices (12 warps x
+    // 1024 floats: fewer per-slice waits); with gradients the stream is a copy and wants the most
+    // warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
     int slice = k7_env_int("K7_SLICE", grad ? 512 : 1024);
     slice = slice >= 1024 ? 1024 : 512;
     int cw = k7_env_int("K7_WARPS", slice == 1024 ? 12 : K7_PIPE_MAX_CW);
@@ -1125,24 +984,17 @@ static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g) {
     g->cw = cw;
     g->slice = (uint32_t)slice;
     g->tile_f = (uint32_t)cw * (uint32_t)slice;
-    g->div_c = k7_fastdiv_make((uint32_t)C);
-    // rows touching a tile: (tile_f-1)/C + 2 at most; a part starts up to 127 bits into its first 16 bytes
-    const uint32_t nrows_max = (g->tile_f - 1) / (uint32_t)C + 2;
-    g->side_words = (((nrows_max + 254u) >> 7) + 1u) << 2;
-    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4 + (size_t)(2 * g->side_words + 4) * 4, 128);
+    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4, 128);
     const size_t budget = 226 * 1024;
-    const size_t fixed = 64 /*alignment slack*/ + (size_t)cw * (slice / 8);
-    int stages = (int)((budget - fixed) / ((size_t)g->stage_stride + sizeof(K7TileDesc) + 16));
+    int stages = (int)((budget - 64) / ((size_t)g->stage_stride + sizeof(K7TileDesc) + 16));
     const int want = k7_env_int("K7_STAGES", 4);
     if (stages > want) stages = want;
     if (stages > 16) stages = 16;
-    K7_REQUIRE(stages >= (grad ? 3 : 2), "k7_loss: C=%d needs %u bytes of shared memory per stage", C, g->stage_stride);
+    K7_REQUIRE(stages >= (grad ? 3 : 2), "k7_loss: a tile of %u bytes leaves no room for the ring", g->stage_stride);
     g->stages = stages;
     size_t o = (size_t)stages * g->stage_stride;
     g->off_desc = (uint32_t)o;
     o += (size_t)stages * sizeof(K7TileDesc);
-    g->off_mask = (uint32_t)o;
-    o += (size_t)cw * (slice / 8);
     o = k7_align_up(o, 16);
     g->off_bars = (uint32_t)o;
     o += (size_t)stages * 16;
@@ -1152,18 +1004,24 @@ static int k7_pipe_geometry(int C, bool grad, K7PipeGeom* g) {
 
 static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls,
                        const float* const* levels, const float* reg, const float* annotations, const int32_t* assign,
-                       const uint32_t* ignore_bits, const int32_t* num_pos, int B, int A, int C, int M,
+                       const uint64_t* best, const int32_t* num_pos, int B, int A, int C, int M,
                        const K7LossParams* params, float* per_image, float* sums, float* dcls, float* const* dlevels,
                        float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
     const bool lv = levels != nullptr;
     const bool grad = dreg != nullptr;
-    K7_REQUIRE(reg && annotations && assign && num_pos && params && per_image && sums && workspace, "k7_loss: null argument");
+    K7_REQUIRE(reg && annotations && num_pos && params && per_image && sums && workspace, "k7_loss: null argument");
+    K7_REQUIRE((assign != nullptr) != (best != nullptr), "k7_loss: give either k7_match's assign words or k7_match_scatter's best array");
     K7_REQUIRE(B > 0 && A > 0 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d", B, A, C, M);
     K7_REQUIRE(B <= 65535, "k7_loss: B > 65535 not supported");
     K7_REQUIRE(params->mean_divisor > 0, "k7_loss: mean_divisor must be positive");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(reg) & 15) == 0 && (reinterpret_cast<uintptr_t>(dreg) & 15) == 0,
                "k7_loss: reg and dreg must be 16-byte aligned");
-    K7_REQUIRE((reinterpret_cast<uintptr_t>(ignore_bits) & 15) == 0, "k7_loss: ignore_bits must be 16-byte aligned");
+    if (best) {
+        K7_REQUIRE(params->match_generation >= 1u && params->match_generation <= K7_BEST_GEN_MAX,
+                   "k7_loss: match_generation %u outside [1, %u]", params->match_generation, K7_BEST_GEN_MAX);
+        K7_REQUIRE(params->pos_thr >= params->neg_thr && params->neg_thr > 0.0f, "k7_loss: bad thresholds for the best array");
+        K7_REQUIRE((reinterpret_cast<uintptr_t>(best) & 7) == 0, "k7_loss: best must be 8-byte aligned");
+    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
 
     K7LossPlan L;
@@ -1175,9 +1033,9 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     }
     unsigned char* ws = static_cast<unsigned char*>(workspace);
     K7_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "k7_loss: workspace must be 256-byte aligned");
-    unsigned int* counters = reinterpret_cast<unsigned int*>(ws + L.off_counter);
+    unsigned int* counter = reinterpret_cast<unsigned int*>(ws + L.off_counter);
+    long long* acc = reinterpret_cast<long long*>(ws + L.off_acc);
     float* cta_partials = reinterpret_cast<float*>(ws + L.off_cta);
-    float2* rows_partials = reinterpret_cast<float2*>(ws + L.off_rows);
 
     K7LossDev P;
     P.alpha = params->alpha;
@@ -1200,37 +1058,24 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     P.from_logits = params->from_logits ? 1 : 0;
     P.B = B; P.A = A; P.C = C; P.M = M;
 
-    K7_CUDA(cudaMemsetAsync(counters, 0, sizeof(unsigned int) * ((size_t)B + 1), st));
-    const int W = (int)K7_IGNORE_WORDS(A);
-    if (!ignore_bits) {   // the caller did not keep k7_match's bitmap: derive it from the assignment words
-        uint32_t* bits = reinterpret_cast<uint32_t*>(ws + L.off_bits);
-        dim3 grid((A + K7_ROWS_THREADS - 1) / K7_ROWS_THREADS, B);
-        k7_loss_bits_kernel<<<grid, K7_ROWS_THREADS, 0, st>>>(assign, A, W, bits);
-        K7_LAUNCH_CHECK();
-        ignore_bits = bits;
-    }
+    // counter + accumulators are contiguous at the start of the workspace
+    K7_CUDA(cudaMemsetAsync(ws + L.off_counter, 0, L.off_acc - L.off_counter + sizeof(long long) * 2 * (size_t)B, st));
 
     K7LevelTable LT;
     memset(&LT, 0, sizeof(LT));
     K7PipeSegs SG;
     memset(&SG, 0, sizeof(SG));
     SG.n = L.nseg;
-    K7ExpandTable ET;
-    memset(&ET, 0, sizeof(ET));
-    int eblocks = 0;
     for (int i = 0; i < L.nseg; ++i) {
         K7PipeSeg& Q = SG.s[i];
         Q.cls = cls;
         Q.dcls = dcls;
-        Q.bits = ignore_bits;
         Q.AC = L.AC[i];
         Q.N = Q.AC * (unsigned long long)B;
         Q.N4 = Q.N & ~3ull;
-        Q.A = (uint32_t)A;
         Q.tile0 = L.tile0[i];
         if (lv) {
             const int l = L.level[i];
-            const int S = spec->fh[l] * spec->fw[l], K = spec->cell_anchors;
             Q.cls = levels[l];
             Q.dcls = grad ? dlevels[l] : nullptr;
             K7_REQUIRE(Q.cls && (reinterpret_cast<uintptr_t>(Q.cls) & 15) == 0 &&
@@ -1238,37 +1083,15 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
                        "k7_loss_levels: level %d: null or unaligned tensor", l);
             LT.cls[l] = Q.cls;
             LT.dcls[l] = Q.dcls;
-            LT.S[l] = S;
-            Q.A = (uint32_t)Q.AC;   // C == 1 mode
-            uint32_t* lbits = reinterpret_cast<uint32_t*>(ws + L.off_lbits[i]);
-            Q.bits = lbits;
-            const long long threads = (S & 31) == 0 ? (long long)K * (S >> 5) : ((long long)K * C * S + 31) / 32;
-            ET.lbits[i] = lbits;
-            ET.level_off[i] = spec->offset[l];
-            ET.S[i] = S;
-            ET.Wl[i] = (int)K7_IGNORE_WORDS(Q.A);
-            ET.blk_off[i] = eblocks;
-            eblocks += (int)((threads + 255) / 256);
+            LT.S[l] = spec->fh[l] * spec->fw[l];
         }
-        Q.W = (uint32_t)K7_IGNORE_WORDS(Q.A);
-    }
-    if (lv && eblocks > 0) {
-        for (int i = L.nseg; i <= K7_MAX_LEVELS; ++i) ET.blk_off[i] = eblocks;
-        dim3 grid(eblocks, B);
-        k7_bits_expand_kernel<<<grid, 256, 0, st>>>(ignore_bits, W, ET, spec->cell_anchors, C);
-        K7_LAUNCH_CHECK();
     }
     if (L.G.num_tiles > 0 || L.nseg > 0) {
         const K7PipeGeom& G = L.G;
-        K7LossDev Ps = P;
-        if (lv) {
-            Ps.A = 0;   // per stream: K7PipeSeg::A
-            Ps.C = 1;
-        }
         float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe);
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, Ps, G, pipe_partials, cta_partials);
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, annotations, P, G, pipe_partials, cta_partials);
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
@@ -1300,25 +1123,44 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
             PR.mailbox[i] = q->mailbox[i];
         }
     }
+    K7AssignSrc SRC;
+    memset(&SRC, 0, sizeof(SRC));
+    SRC.words = assign;
+    SRC.best = reinterpret_cast<const unsigned long long*>(best);
+    SRC.gen = params->match_generation;
+    SRC.neg_thr = params->neg_thr;
+    SRC.pos_thr = params->pos_thr;
+    SRC.words_out = params->assign_out;
+    SRC.consume = params->consume_best ? 1 : 0;
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     float4* dreg4 = reinterpret_cast<float4*>(dreg);
-    dim3 rgrid(L.gx, B);
-#define K7_ROWS_LAUNCH(GR, SP, LV)                                                                                       \
-    k7_loss_rows_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
-                                                                       assign, num_pos, P, PR, cta_partials, L.cta_stride, \
-                                                                       rows_partials, counters, per_image, sums, dcls,   \
-                                                                       dreg4)
-    if (lv) { if (grad) K7_ROWS_LAUNCH(true, true, true); else K7_ROWS_LAUNCH(false, true, true); }
-    else if (grad) { if (spec) K7_ROWS_LAUNCH(true, true, false); else K7_ROWS_LAUNCH(true, false, false); }
-    else           { if (spec) K7_ROWS_LAUNCH(false, true, false); else K7_ROWS_LAUNCH(false, false, false); }
+    const long long chunks = (long long)B * ((A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK);
+    long long rblocks = chunks;
+    const long long rcap = 8ll * k7_sm_count();   // eight resident blocks of 256 threads per SM; the rest is looped
+    if (rblocks > rcap) rblocks = rcap;
+    const dim3 rgrid((unsigned)rblocks);
+#define K7_ROWS_LAUNCH(GR, PK, SP, LV)                                                                                     \
+    k7_loss_rows_kernel<GR, PK, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg,           \
+                                                                           annotations, SRC, num_pos, P, PR, cta_partials, \
+                                                                           L.cta_stride, acc, counter, per_image, sums,    \
+                                                                           dcls, dreg4)
+#define K7_ROWS_PICK(GR, PK)                                                                   \
+    do {                                                                                       \
+        if (lv) K7_ROWS_LAUNCH(GR, PK, true, true);                                            \
+        else if (spec) K7_ROWS_LAUNCH(GR, PK, true, false);                                    \
+        else K7_ROWS_LAUNCH(GR, PK, false, false);                                             \
+    } while (0)
+    if (grad) { if (best) K7_ROWS_PICK(true, true); else K7_ROWS_PICK(true, false); }
+    else      { if (best) K7_ROWS_PICK(false, true); else K7_ROWS_PICK(false, false); }
+#undef K7_ROWS_PICK
 #undef K7_ROWS_LAUNCH
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
 
 extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
-                       const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                       const float* annotations, const int32_t* assign, const uint64_t* best,
                        const int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
                        float* sums, float* dcls, float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
     K7_REQUIRE(cls, "k7_loss: null argument");
@@ -1334,12 +1176,12 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
         K7_REQUIRE((reinterpret_cast<uintptr_t>(anchors) & 15) == 0, "k7_loss: anchors must be 16-byte aligned");
         K7_REQUIRE(box_order == K7_BOX_XYXY || box_order == K7_BOX_YXYX, "k7_loss: bad box_order");
     }
-    return k7_loss_run(spec, anchors, box_order, cls, nullptr, reg, annotations, assign, ignore_bits, num_pos, B, A, C, M,
+    return k7_loss_run(spec, anchors, box_order, cls, nullptr, reg, annotations, assign, best, num_pos, B, A, C, M,
                        params, per_image, sums, dcls, nullptr, dreg, workspace, workspace_bytes, stream);
 }
 
 extern "C" int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
-                              const float* annotations, const int32_t* assign, const uint32_t* ignore_bits,
+                              const float* annotations, const int32_t* assign, const uint64_t* best,
                               const int32_t* num_pos, int B, int C, int M, const K7LossParams* params, float* per_image,
                               float* sums, float* const* dlevels, float* dreg, void* workspace, size_t workspace_bytes,
                               void* stream) {
@@ -1347,7 +1189,7 @@ extern "C" int k7_loss_levels(const K7AnchorSpec* spec, const float* const* leve
     K7_REQUIRE((dlevels == nullptr) == (dreg == nullptr), "k7_loss_levels: dlevels and dreg must be given together");
     int rc = k7_check_spec(spec, spec->total);
     if (rc) return rc;
-    return k7_loss_run(spec, nullptr, spec->box_order, nullptr, levels, reg, annotations, assign, ignore_bits, num_pos, B,
+    return k7_loss_run(spec, nullptr, spec->box_order, nullptr, levels, reg, annotations, assign, best, num_pos, B,
                        spec->total, C, M, params, per_image, sums, nullptr, dlevels, dreg, workspace, workspace_bytes,
                        stream);
 }

@@ -11,6 +11,8 @@ path needs no collective.  The eval side needs no collective at all.
 """
 from __future__ import annotations
 
+import weakref
+
 import torch
 import torch.distributed as dist
 
@@ -36,10 +38,34 @@ def mean_losses(sums: torch.Tensor):
     return m[0:1], m[1:2]
 
 
+_SHARDED = {}      # (process group, device, kwargs) -> FocalLoss: ONE module (and one set of peer mailboxes) per group
+
+
 def sharded_focal_loss(classifications, regressions, anchors, annotations, group=None, **loss_kwargs):
-    """FocalLoss over a batch whose dim 0 is already this rank's shard."""
+    """FocalLoss over a batch whose dim 0 is already this rank's shard.  The module - and with it the
+    peer mailboxes of the fused exchange (a cudaMalloc, IPC handles and two host collectives to set
+    up) - is built once per (group, device, kwargs) and reused by every later call."""
     from .losses import FocalLoss
-    return FocalLoss(process_group=group, sharded=True, **loss_kwargs)(classifications, regressions, anchors, annotations)
+    ref = classifications[0] if isinstance(classifications, (list, tuple)) else classifications
+    key = (id(group) if group is not None else None, ref.device, tuple(sorted((k, repr(v)) for k, v in loss_kwargs.items())))
+    mod = _SHARDED.get(key)
+    if mod is None:
+        mod = _SHARDED[key] = FocalLoss(process_group=group, sharded=True, **loss_kwargs)
+    return mod(classifications, regressions, anchors, annotations)
+
+
+def _release_mailboxes(lib, device, opened, local):
+    """PeerMailbox finalizer (also close()): unmap the peers' mailboxes, free the local one."""
+    try:
+        with torch.cuda.device(device):
+            torch.cuda.synchronize()
+            while opened:
+                lib.k7_peer_mailbox_close(opened.pop())
+            if local[0]:
+                lib.k7_peer_mailbox_destroy(local[0])
+                local[0] = None
+    except Exception:                      # interpreter / context teardown: nothing left to release
+        pass
 
 
 class PeerMailbox:
@@ -69,11 +95,15 @@ class PeerMailbox:
         self._lib = L.lib()
         self._local = C.c_void_p()
         self._opened = []
+        self._local_box = [None]               # what the finalizer frees (it must not hold `self`)
+        self._finalizer = weakref.finalize(self, _release_mailboxes, self._lib, self.device, self._opened, self._local_box)
+        self._finalizer.atexit = False         # at interpreter exit the CUDA context goes away as a whole
         handle = (C.c_ubyte * 64)()
         err = None
         with torch.cuda.device(self.device):
             try:
                 L.check(self._lib.k7_peer_mailbox_create(self.world, C.byref(self._local), handle), "k7_peer_mailbox_create")
+                self._local_box[0] = self._local
             except RuntimeError as e:                      # still take part in the collectives below
                 err = str(e)
             gathered = [None] * self.world
@@ -114,11 +144,6 @@ class PeerMailbox:
         return self._struct
 
     def close(self):
-        with torch.cuda.device(self.device):
-            torch.cuda.synchronize()
-            for p in self._opened:
-                self._lib.k7_peer_mailbox_close(p)
-            self._opened = []
-            if self._local:
-                self._lib.k7_peer_mailbox_destroy(self._local)
-                self._local = None
+        """Unmap and free now (idempotent; also runs when the object is garbage collected)."""
+        _release_mailboxes(self._lib, self.device, self._opened, self._local_box)
+        self._local = None

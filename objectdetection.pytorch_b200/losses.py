@@ -18,7 +18,10 @@ global batch, so backward needs no collective.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
+import threading
+from collections import namedtuple
 from typing import Optional
 
 import torch
@@ -29,21 +32,70 @@ from .anchors import spec_of
 
 
 class _Workspace:
-    """Per-device scratch tensors, grown on demand and reused across calls."""
+    """Scratch tensors, grown on demand and reused across calls.  One set per (device, CUDA stream):
+    two callers that overlap on different streams of one device (an eval thread next to a training
+    thread, detect() of two half batches) never share a buffer - the library itself keeps no state,
+    so this is the only place where calls could meet (re-entrancy)."""
 
     def __init__(self):
         self.bufs = {}
+        self.best = {}
+
+    @staticmethod
+    def _key(name, device):
+        device = torch.device(device)
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        return (name, device, torch.cuda.current_stream(device).cuda_stream)
 
     def get(self, name: str, nbytes: int, device) -> torch.Tensor:
-        key = (name, device)
+        key = self._key(name, device)
         t = self.bufs.get(key)
         if t is None or t.numel() < nbytes:
             t = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
             self.bufs[key] = t
         return t
 
+    def best_array(self, B: int, A: int, device):
+        """The uint64 [B*A] array of k7_match_scatter + the generation of this call + whether k7_loss has
+        to zero what it reads.  Zeroed when created; every call gets the next generation (stale entries
+        are ignored by their tag); after K7_BEST_GEN_MAX calls the array is zeroed again.  While a CUDA
+        graph is being captured the generation would be frozen into the graph, so the replays reuse
+        ONE generation and k7_loss clears the entries it consumes (K7LossParams.consume_best)."""
+        key = self._key("best", device)
+        ent = self.best.get(key)
+        n = B * A
+        if ent is None or ent[0].numel() < n:
+            ent = [torch.zeros(n, dtype=torch.int64, device=device), 0]
+            self.best[key] = ent
+        if ent[1] >= L.BEST_GEN_MAX:
+            ent[0].zero_()
+            ent[1] = 0
+        ent[1] += 1
+        return ent[0], ent[1], bool(torch.cuda.is_current_stream_capturing())
+
 
 _WS = _Workspace()
+
+
+def scatter_ok(spec, M: int, neg_thr: float, pos_thr: float) -> bool:
+    """Can the ground-truth-first assignment (k7_match_scatter) serve this call?"""
+    return spec is not None and M <= 65535 and 1e-3 < neg_thr < 1.0 and pos_thr >= neg_thr
+
+
+def match_scatter(spec, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float):
+    """k7_match_scatter: returns (best [B*A] uint64-as-int64, generation, consume, num_pos [B] int32)."""
+    L.require_cuda(annotations)
+    ann = L.as_f32_contig(annotations)
+    B, M = ann.shape[0], ann.shape[1]
+    dev = ann.device
+    best, gen, consume = _WS.best_array(B, A, dev)
+    num_pos = torch.empty(B, dtype=torch.int32, device=dev)
+    p = L.K7MatchParams(neg_thr, pos_thr)
+    with torch.cuda.device(dev):
+        L.check(L.lib().k7_match_scatter(C.byref(spec), L.ptr(ann), B, A, M, C.byref(p), L.ptr(best), gen,
+                                         L.ptr(num_pos), L.stream_ptr(dev)), "k7_match_scatter")
+    return best, gen, consume, num_pos
 
 
 def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
@@ -83,13 +135,36 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
     return out
 
 
+def _loss_params(*, alpha, beta, target_div, yx_targets, mean_divisor, want_grad, dreg_zeroed, from_logits, peer_reduce,
+                 best, assign_out):
+    p = L.K7LossParams()
+    p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
+    p.alpha, p.beta = alpha, beta
+    for i in range(4):
+        p.target_div[i] = target_div[i]
+    p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
+    p.from_logits = int(from_logits)
+    if peer_reduce is not None:                # K7PeerReduce: `sums` come back as the GLOBAL sums
+        p.peer_reduce = C.pointer(peer_reduce)
+    if best is not None:                       # (array, generation, consume, neg_thr, pos_thr) of match_scatter
+        p.match_generation, p.consume_best = int(best[1]), int(best[2])
+        p.neg_thr, p.pos_thr = float(best[3]), float(best[4])
+    if assign_out is not None:
+        p.assign_out = assign_out.data_ptr()
+    return p
+
+
 def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
                mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
-               ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False, peer_reduce=None):
+               ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False, peer_reduce=None,
+               best=None, assign_out: Optional[torch.Tensor] = None):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
+    The assignment comes as match()'s `assign` words or as match_scatter()'s array:
+    best = (array, generation, consume, neg_thr, pos_thr) with assign=None.
     dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a 16 B/anchor store);
-    ignore_bits: match(with_bits=True)'s bitmap (derived from `assign` by a small kernel when absent);
-    from_logits: `cls` holds pre-sigmoid logits, the sigmoid is fused and dcls is d(loss)/d(logit)."""
+    ignore_bits: accepted for compatibility, unused (ignored rows are handled by the row kernel);
+    from_logits: `cls` holds pre-sigmoid logits, the sigmoid is fused and dcls is d(loss)/d(logit);
+    assign_out: optional [B*A] int32 that receives k7_match's words when the input is `best`."""
     B, A, Cn = cls.shape
     M = ann.shape[1]
     dev = cls.device
@@ -108,19 +183,13 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     dreg = None
     if want_grad:
         dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
-    p = L.K7LossParams()
-    p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
-    p.alpha, p.beta = alpha, beta
-    for i in range(4):
-        p.target_div[i] = target_div[i]
-    p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
-    p.from_logits = int(from_logits)
-    if peer_reduce is not None:                # K7PeerReduce: `sums` come back as the GLOBAL sums
-        p.peer_reduce = C.pointer(peer_reduce)
+    p = _loss_params(alpha=alpha, beta=beta, target_div=target_div, yx_targets=yx_targets, mean_divisor=mean_divisor,
+                     want_grad=want_grad, dreg_zeroed=dreg_zeroed, from_logits=from_logits, peer_reduce=peer_reduce,
+                     best=best, assign_out=assign_out)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
-                            L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits), L.ptr(num_pos),
-                            B, A, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), L.ptr(dcls), L.ptr(dreg),
+                            L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(best[0]) if best is not None else None,
+                            L.ptr(num_pos), B, A, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), L.ptr(dcls), L.ptr(dreg),
                             L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_loss")
     return per_image, sums, dcls, dreg
 
@@ -139,26 +208,45 @@ def _scale_grads(pairs, dev):
             L.check(lib.k7_scale_inplace_multi(g, n, sc, len(chunk), st), "k7_scale_inplace_multi")
 
 
+def _assignment(anchor_src, ann, A, cfg, dreg0):
+    """The assignment stage of a FocalLoss call: (assign|None, best|None, num_pos, dreg_zeroed|None).
+    Anchors from a recipe: ground-truth-first k7_match_scatter; a foreign anchor tensor (or thresholds
+    it cannot serve): the exhaustive k7_match, which also zero-fills d(reg) on its way."""
+    sp = spec_of(anchor_src)
+    if scatter_ok(sp, ann.shape[1], cfg["neg_thr"], cfg["pos_thr"]):
+        arr, gen, consume, num_pos = match_scatter(sp, ann, A, cfg["neg_thr"], cfg["pos_thr"])
+        return None, (arr, gen, consume, cfg["neg_thr"], cfg["pos_thr"]), num_pos, None
+    assign, num_pos = match(anchor_src, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
+    return assign, None, num_pos, dreg0
+
+
+def _exchange(cfg):
+    """(world, peer mailbox|None, group) of a sharded call."""
+    group = cfg.get("process_group")
+    world = 1
+    if group is not None or cfg.get("sharded"):
+        import torch.distributed as dist
+        world = dist.get_world_size(group)
+    peer = cfg["peer"]() if world > 1 and cfg.get("peer") else None   # fused exchange over peer memory, or None
+    return world, peer, group
+
+
 class _FocalLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, cls, reg, anchors, ann, cfg):
         want_grad = cls.requires_grad or reg.requires_grad
         A = cls.shape[1]
         dreg0 = torch.empty_like(reg) if want_grad else None
-        assign, num_pos, bits = match(anchors, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"],
-                                      zero_fill=dreg0, with_bits=True)
-        group = cfg.get("process_group")
-        world = 1
-        if group is not None or cfg.get("sharded"):
-            import torch.distributed as dist
-            world = dist.get_world_size(group)
-        peer = cfg["peer"]() if world > 1 and cfg.get("peer") else None   # fused exchange over peer memory, or None
+        assign, best, num_pos, dreg_zeroed = _assignment(anchors, ann, A, cfg, dreg0)
+        world, peer, group = _exchange(cfg)
         B = cls.shape[0]
         per_image, sums, dcls, dreg = loss_stage(
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
-            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world,
-            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg0, ignore_bits=bits,
+            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=cfg["divisor"](B, world),
+            want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg_zeroed, best=best,
             from_logits=cfg.get("from_logits", False), peer_reduce=peer.next() if peer is not None else None)
+        if want_grad and dreg_zeroed is None:
+            dreg0 = None                         # loss_stage allocated d(reg) itself
         if world > 1 and peer is None:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)   # the path's only collective
@@ -166,14 +254,16 @@ class _FocalLossFn(torch.autograd.Function):
         ctx.save_for_backward(dcls, dreg) if want_grad else None
         ctx.has_grad = want_grad
         ctx.device = cls.device
-        ctx.set_materialize_grads(False)    # no zero tensors for the outputs nobody differentiates (assign: 12 MB)
-        ctx.mark_non_differentiable(num_pos, per_image, assign)
-        return out[0:1], out[1:2], num_pos, per_image, assign
+        ctx.consumed = False
+        ctx.set_materialize_grads(False)    # no zero tensors for the outputs nobody differentiates
+        ctx.mark_non_differentiable(num_pos, per_image, sums)
+        return out[0:1], out[1:2], num_pos, per_image, sums
 
     @staticmethod
     def backward(ctx, g_cls, g_reg, *_):
         if not ctx.has_grad:
             return None, None, None, None, None
+        _once(ctx)
         dcls, dreg = ctx.saved_tensors
         pairs = []
         if g_cls is not None:
@@ -188,9 +278,19 @@ class _FocalLossFn(torch.autograd.Function):
         return dcls, dreg, None, None, None
 
 
+def _once(ctx):
+    """The saved gradients are scaled IN PLACE by the incoming gradient (no second copy of the largest
+    tensor of the step), so a second backward through the same graph (retain_graph=True) would scale
+    them twice: refuse it instead of returning wrong numbers."""
+    if ctx.consumed:
+        raise RuntimeError("b200det.FocalLoss: backward was already run on this graph; its saved gradients were scaled "
+                           "in place.  Call the loss again instead of backward(retain_graph=True) twice.")
+    ctx.consumed = True
+
+
 def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets, mean_divisor,
                       want_grad, dreg_zeroed: Optional[torch.Tensor] = None, ignore_bits: Optional[torch.Tensor] = None,
-                      from_logits: bool = False, peer_reduce=None):
+                      from_logits: bool = False, peer_reduce=None, best=None):
     """loss_stage on the head's raw per-level NCHW outputs (k7_loss_levels).  Returns
     (per_image[B,2], sums[4], dlevels|None (list, same layouts as `levels`), dreg|None)."""
     B, Cn = L.check_levels(levels, spec)
@@ -204,18 +304,13 @@ def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, t
     dreg = None
     if want_grad:
         dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
-    p = L.K7LossParams()
-    p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
-    p.alpha, p.beta = alpha, beta
-    for i in range(4):
-        p.target_div[i] = target_div[i]
-    p.yx_targets, p.mean_divisor = int(yx_targets), int(mean_divisor)
-    p.from_logits = int(from_logits)
-    if peer_reduce is not None:                # K7PeerReduce: `sums` come back as the GLOBAL sums
-        p.peer_reduce = C.pointer(peer_reduce)
+    p = _loss_params(alpha=alpha, beta=beta, target_div=target_div, yx_targets=yx_targets, mean_divisor=mean_divisor,
+                     want_grad=want_grad, dreg_zeroed=dreg_zeroed, from_logits=from_logits, peer_reduce=peer_reduce,
+                     best=best, assign_out=None)
     lv, dlv = L.ptr_array(levels), L.ptr_array(dlevels)
     with torch.cuda.device(dev):
-        L.check(lib.k7_loss_levels(C.byref(spec), lv, L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(ignore_bits),
+        L.check(lib.k7_loss_levels(C.byref(spec), lv, L.ptr(reg), L.ptr(ann), L.ptr(assign),
+                                   L.ptr(best[0]) if best is not None else None,
                                    L.ptr(num_pos), B, Cn, M, C.byref(p), L.ptr(per_image), L.ptr(sums), dlv, L.ptr(dreg),
                                    L.ptr(ws), ws.numel(), L.stream_ptr(dev)), "k7_loss_levels")
     return per_image, sums, dlevels, dreg
@@ -229,19 +324,13 @@ class _FocalLossLevelsFn(torch.autograd.Function):
         want_grad = reg.requires_grad or any(t.requires_grad for t in levels)
         A = spec.total
         dreg0 = torch.empty_like(reg) if want_grad else None
-        assign, num_pos, bits = match(spec, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"],
-                                      zero_fill=dreg0, with_bits=True)
-        group = cfg.get("process_group")
-        world = 1
-        if group is not None or cfg.get("sharded"):
-            import torch.distributed as dist
-            world = dist.get_world_size(group)
-        peer = cfg["peer"]() if world > 1 and cfg.get("peer") else None
+        assign, best, num_pos, dreg_zeroed = _assignment(spec, ann, A, cfg, dreg0)
+        world, peer, group = _exchange(cfg)
         B = reg.shape[0]
         per_image, sums, dlevels, dreg = loss_stage_levels(
             spec, list(levels), reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
-            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=B * world, want_grad=want_grad,
-            dreg_zeroed=dreg0, ignore_bits=bits, from_logits=cfg.get("from_logits", False),
+            target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=cfg["divisor"](B, world),
+            want_grad=want_grad, dreg_zeroed=dreg_zeroed, best=best, from_logits=cfg.get("from_logits", False),
             peer_reduce=peer.next() if peer is not None else None)
         if world > 1 and peer is None:
             import torch.distributed as dist
@@ -251,15 +340,17 @@ class _FocalLossLevelsFn(torch.autograd.Function):
             ctx.save_for_backward(dreg, *dlevels)
         ctx.has_grad = want_grad
         ctx.device = reg.device
+        ctx.consumed = False
         ctx.set_materialize_grads(False)
         ctx.n_levels = len(levels)
-        ctx.mark_non_differentiable(num_pos, per_image)
-        return out[0:1], out[1:2], num_pos, per_image
+        ctx.mark_non_differentiable(num_pos, per_image, sums)
+        return out[0:1], out[1:2], num_pos, per_image, sums
 
     @staticmethod
     def backward(ctx, g_cls, g_reg, *_):
         if not ctx.has_grad:
             return (None,) * (4 + ctx.n_levels)
+        _once(ctx)
         dreg, *dlevels = ctx.saved_tensors
         pairs = []
         if g_cls is not None:
@@ -273,6 +364,17 @@ class _FocalLossLevelsFn(torch.autograd.Function):
             dreg = None
         _scale_grads(pairs, ctx.device)
         return (dreg, None, None, None, *dlevels)
+
+
+HeadOutputs = namedtuple("HeadOutputs", "classification regression anchors")
+_CAPTURE = threading.local()      # ids of the FocalLoss modules in capture mode, per thread (see FocalLoss.capture_head)
+
+
+def _capturing() -> set:
+    s = getattr(_CAPTURE, "ids", None)
+    if s is None:
+        s = _CAPTURE.ids = set()
+    return s
 
 
 class FocalLoss(nn.Module):
@@ -290,7 +392,7 @@ class FocalLoss(nn.Module):
     def __init__(self, neg_thr: float = 0.35, pos_thr: float = 0.45, alpha: float = 0.25,
                  gamma: float = 2.0, beta: float = 1.0 / 9.0, target_std=(0.1, 0.1, 0.2, 0.2),
                  box_order: str = "xyxy", yx_targets: bool = False, process_group=None,
-                 sharded: bool = False, from_logits: bool = False, peer_reduce="auto"):
+                 sharded: bool = False, from_logits: bool = False, peer_reduce="auto", ddp_average: bool = False):
         super().__init__()
         if gamma != 2.0:
             raise ValueError("only gamma == 2 (the reference's constant, losses.py:32) is implemented")
@@ -301,6 +403,14 @@ class FocalLoss(nn.Module):
                         box_order=L.BOX_XYXY if box_order == "xyxy" else L.BOX_YXYX,
                         yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded),
                         from_logits=bool(from_logits))
+        # What the gradients are divided by.  The reference's nn.DataParallel takes the mean of the GLOBAL
+        # batch (train_ksevendet.py:358-361), so a rank's gradient is d(global mean)/d(its shard) =
+        # .../(B_local * world) and the ranks' parameter gradients must be SUMMED.  ddp_average=True is for
+        # torch DistributedDataParallel, which AVERAGES them: each rank then scales by its own B_local only
+        # and the average over ranks is again the gradient of the global mean.  Both need equal shards
+        # (check_equal_shards()).
+        self.ddp_average = bool(ddp_average)
+        self.cfg["divisor"] = (lambda B, world: B) if self.ddp_average else (lambda B, world: B * world)
         # sharded: the exchange of the four batch sums.  "auto"/True: fused into k7_loss over peer-mapped
         # mailboxes (distributed.PeerMailbox), set up at the first call; "auto" keeps NCCL's all_reduce when
         # the mailboxes cannot be mapped (True raises); False: always all_reduce.
@@ -309,6 +419,22 @@ class FocalLoss(nn.Module):
         self.cfg["peer"] = self._peer_mailbox if peer_reduce in ("auto", True) else None
         self.last_num_positives = None      # [B] int32 device tensor of the last call (for logging)
         self.last_per_image = None          # [B,2] (cls_i, reg_i)
+        self.last_sums = None               # [4] {sum cls_i, sum reg_i, sum num_pos_i, images}: global when sharded
+        self._last_local = (0, 1)           # (B_local, world) of the last call
+
+    @contextlib.contextmanager
+    def capture_head(self):
+        """While active (in the calling thread only) forward() computes nothing and returns the
+        HeadOutputs it was called with.  utils.patch_model uses it to take (classification,
+        regression, anchors) out of a reference forward at the one call every detector makes after
+        its conv heads (retinanet.py:294, efficientdet.py:545) - EfficientDet.forward has no
+        return_head switch."""
+        live = _capturing()
+        live.add(id(self))
+        try:
+            yield self
+        finally:
+            live.discard(id(self))
 
     def _peer_mailbox(self):
         if self._peer is None:
@@ -321,6 +447,18 @@ class FocalLoss(nn.Module):
                 self._peer = False           # keep the NCCL all-reduce
         return self._peer or None
 
+    def check_equal_shards(self):
+        """Sharded calls pre-scale the gradients with B_local * world, which is the global batch only if every
+        rank holds the same number of images (DataParallel's scatter, utils/utils.py:184, makes them equal).
+        Reads the exchanged image count of the last call (one host sync) and raises if the shards differed."""
+        if self.last_sums is None:
+            return
+        B, world = self._last_local
+        total = float(self.last_sums[3].item())
+        if total != float(B * world):
+            raise RuntimeError(f"FocalLoss(sharded=True): this rank holds {B} images but the {world} ranks hold {total:g} "
+                               "together; shards must be equal (gradients are scaled with B_local * world)")
+
     @property
     def exchange(self) -> str:
         """How the batch sums of the last sharded call were combined."""
@@ -330,7 +468,12 @@ class FocalLoss(nn.Module):
     def efficientdet(cls, **kw):
         return cls(neg_thr=0.4, pos_thr=0.5, target_std=None, box_order="yxyx", yx_targets=True, **kw)
 
-    def forward(self, classifications, regressions, anchors, annotations, **kwargs):
+    def forward(self, classifications, regressions, anchors, annotations=None, **kwargs):
+        if id(self) in _capturing():
+            return HeadOutputs(classifications, regressions, anchors)
+        if annotations is None:
+            raise ValueError("FocalLoss needs annotations [B,M,5] (a model called with return_loss=True and no "
+                             "annotations, e.g. model(img) on architectures/retinanet.py whose default is return_loss=True)")
         if isinstance(classifications, (list, tuple)):
             return self._forward_levels(list(classifications), regressions, anchors, annotations)
         L.require_cuda(classifications, regressions, annotations)
@@ -349,10 +492,19 @@ class FocalLoss(nn.Module):
         ann = L.as_f32_contig(annotations)
         # pass the recipe itself when there is one (a plain ctypes struct, not a tensor)
         anchor_src = sp if sp is not None else anchors
-        lc, lr, num_pos, per_image, _ = _FocalLossFn.apply(cls, reg, anchor_src, ann, self.cfg)
+        lc, lr, num_pos, per_image, sums = _FocalLossFn.apply(cls, reg, anchor_src, ann, self.cfg)
+        self._remember(num_pos, per_image, sums, cls.shape[0])
+        return lc, lr
+
+    def _remember(self, num_pos, per_image, sums, B):
         self.last_num_positives = num_pos
         self.last_per_image = per_image
-        return lc, lr
+        self.last_sums = sums
+        world = 1
+        if self.cfg.get("process_group") is not None or self.cfg.get("sharded"):
+            import torch.distributed as dist
+            world = dist.get_world_size(self.cfg.get("process_group"))
+        self._last_local = (int(B), world)
 
     def _forward_levels(self, levels, regressions, anchors, annotations):
         """`classifications` given as the head's raw per-level outputs [B, anchors*classes, H_l, W_l]
@@ -366,7 +518,6 @@ class FocalLoss(nn.Module):
             raise ValueError("annotations must be [B,M,5]")
         reg = L.as_f32_contig(regressions)
         ann = L.as_f32_contig(annotations)
-        lc, lr, num_pos, per_image = _FocalLossLevelsFn.apply(reg, sp, ann, self.cfg, *levels)
-        self.last_num_positives = num_pos
-        self.last_per_image = per_image
+        lc, lr, num_pos, per_image, sums = _FocalLossLevelsFn.apply(reg, sp, ann, self.cfg, *levels)
+        self._remember(num_pos, per_image, sums, B)
         return lc, lr

@@ -13,7 +13,6 @@ All of them call libk7det.so; none has a PyTorch/CPU fallback.
 from __future__ import annotations
 
 import ctypes as C
-import types
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -337,14 +336,29 @@ def strip_head_sigmoid(model) -> bool:
 
 
 def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5, fuse_sigmoid: bool = False):
-    """Swap a reference detector's hot-path attributes for the B200 modules and route its
-    eval branch through eval_tail().  The model must expose the reference's attribute names
-    (anchors, focalLoss, regressBoxes, clipBoxes; retinanet.py:220-230) and a
-    forward(img, annotations=None, return_head=False, return_loss=True).
+    """Swap a reference detector's hot-path attributes for the B200 modules and route its eval
+    branch through eval_tail().  Works on every detector forward of the reference:
+
+        retinanet.py:272, architectures/ksevendet.py:282   forward(img, annotations=None, return_head=False, return_loss=True)
+        ksevendet/architecture/ksevendet.py:222            the same with return_loss=False as the default
+        efficientdet.py:528                                forward(images, annotations=None, return_loss=True)   (no return_head)
+
+    The only seam ALL of them share after the conv heads is
+    ``self.focalLoss(classification, regression, anchors, annotations)`` (retinanet.py:294,
+    efficientdet.py:545, ksevendet.py:312 / :274): an eval call runs the model's own forward with
+    return_loss=True while the swapped-in FocalLoss is in capture mode (thread-local), which hands
+    back the head outputs instead of a loss; the fused tail then produces the reference's
+    ``[scores[K], labels[K], boxes[K,4]]`` (or its zeros triple).  The model's own defaults are kept
+    (inspect.signature), ``return_head`` is only forwarded to forwards that have it, and the
+    override lives on a subclass of the model's class, so nn.DataParallel replicas get it too.
     fuse_sigmoid: also remove the classification head's final sigmoid (strip_head_sigmoid) and run
     FocalLoss / the eval tail on the logits; ``return_head=True`` then returns logits."""
+    import inspect
     from .anchors import Anchors
     from .losses import FocalLoss
+    for name in ("anchors", "focalLoss", "regressBoxes", "clipBoxes"):
+        if not hasattr(model, name):
+            raise ValueError(f"patch_model: the model has no attribute '{name}' (retinanet.py:220-230)")
     from_logits = bool(fuse_sigmoid) and strip_head_sigmoid(model)
     old = model.anchors
     model.anchors = Anchors(pyramid_levels=list(old.pyramid_levels), strides=list(old.strides),
@@ -352,14 +366,33 @@ def patch_model(model, score_thr: float = 0.05, iou_thr: float = 0.5, fuse_sigmo
     model.focalLoss = FocalLoss(from_logits=from_logits)
     model.regressBoxes = BBoxTransform()
     model.clipBoxes = ClipBoxes()
-    inner = model.forward
 
-    def forward(self, img_batch, annotations=None, return_head=False, return_loss=True):
-        if return_head or return_loss:
-            return inner(img_batch, annotations, return_head=return_head, return_loss=return_loss)
-        classification, regression = inner(img_batch, annotations, return_head=True)
-        return eval_tail(classification, regression, self.anchors(img_batch), img_batch, self.regressBoxes,
+    base = type(model)
+    if getattr(base, "_k7_patched", False):          # patched twice: rebuild on the original class
+        base = base.__mro__[1]
+    inner = base.forward
+    sig = inspect.signature(inner)
+    names = list(sig.parameters)                      # self, img_batch|images, annotations, ...
+    if "return_loss" not in sig.parameters or len(names) < 3:
+        raise ValueError("patch_model: forward(img, annotations=None, ..., return_loss=...) expected "
+                         f"(retinanet.py:272, efficientdet.py:528); got {sig}")
+    has_head = "return_head" in sig.parameters
+    img_name = names[1]
+
+    def forward(self, *args, **kwargs):
+        bound = sig.bind(self, *args, **kwargs)
+        bound.apply_defaults()                        # the model's OWN defaults (ksevendet: return_loss=False)
+        a = bound.arguments
+        if a["return_loss"] or (has_head and a["return_head"]) or getattr(self, "convert_onnx", False):
+            return inner(self, *args, **kwargs)
+        img_batch = a[img_name]
+        extra = {"return_head": False} if has_head else {}
+        with self.focalLoss.capture_head():           # retinanet.py:294 then returns the head outputs
+            cap = inner(self, img_batch, None, return_loss=True, **extra)
+        return eval_tail(cap.classification, cap.regression, cap.anchors, img_batch, self.regressBoxes,
                          score_thr, iou_thr, from_logits=from_logits)
 
-    model.forward = types.MethodType(forward, model)
+    forward.__signature__ = sig
+    model.__class__ = type(base.__name__, (base,), {"forward": forward, "_k7_patched": True,
+                                                    "__module__": base.__module__})
     return model

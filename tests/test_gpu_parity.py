@@ -125,25 +125,157 @@ def test_focal_loss_and_grads(path, from_spec):
     assert np.array_equal(mod.last_num_positives.cpu().numpy(), (g["state"] == 2).sum(1))
 
 
-def test_loss_stage_derives_ignore_bits_when_not_given():
-    """k7_loss with the bitmap of k7_match and without it (k7_loss_bits_kernel) is the same computation."""
+def test_match_ignore_bitmap():
+    """k7_match's optional one-bit-per-anchor form of the IGNORE state."""
     g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_c90")], True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    B, A = g["state"].shape
+    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, with_bits=True)
+    state = (assign.view(B, A) & 3).cpu().numpy()
+    got_bits = np.unpackbits(bits.cpu().numpy().view(np.uint8), axis=1, bitorder="little").astype(bool)
+    assert np.array_equal(got_bits[:, :A], state == 1)
+
+
+LOSS_KW = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False)
+
+
+def scatter_words(sp, ann, cls, reg, thr, **kw):
+    """match_scatter -> k7_loss(best=..., assign_out=...): (words [B,A], num_pos, loss outputs, best array)."""
+    B, A, _ = cls.shape
+    arr, gen, consume, num_pos = BL.match_scatter(sp, ann, A, thr[0], thr[1])
+    words = torch.empty(B * A, dtype=torch.int32, device=DEV)
+    out = BL.loss_stage(sp, cls, reg, ann, None, num_pos, best=(arr, gen, consume, thr[0], thr[1]), assign_out=words,
+                        mean_divisor=B, **kw)
+    return words.view(B, A), num_pos, out, (arr, gen)
+
+
+@pytest.mark.parametrize("path", LOSS, ids=IDS)
+def test_match_scatter_bit_exact(path):
+    """The ground-truth-first assignment (k7_match_scatter, the production path with recipe anchors): states,
+    num_pos, the IoU maximum of every non-negative anchor and its arg-max row are the reference's."""
+    g, yx, anc = load_loss_case(path, True)
+    sp = b200det.spec_of(anc)
     ann = torch.from_numpy(g["annotations"]).to(DEV)
     cls = torch.from_numpy(g["classifications"]).to(DEV)
     reg = torch.from_numpy(g["regressions"]).to(DEV)
+    thr = (0.4, 0.5) if yx else (0.35, 0.45)
+    B, A = g["state"].shape
+    kw = dict(LOSS_KW, want_grad=False, target_div=(1, 1, 1, 1) if yx else (0.1, 0.1, 0.2, 0.2), yx_targets=yx)
+    words, num_pos, _, (arr, gen) = scatter_words(sp, ann, cls, reg, thr, **kw)
+    w = words.cpu().numpy()
+    state, row = w & 3, w >> 2
+    assert np.array_equal(state, g["state"])
+    assert np.array_equal(num_pos.cpu().numpy(), (g["state"] == 2).sum(1))
+    has_rows = (g["annotations"][:, :, 4] != -1).any(1)          # an image without a row is skipped: all IGNORE, no entry
+    live = (g["state"] != 0) & has_rows[:, None]                 # anchors whose IoU maximum reached neg_thr
+    assert np.array_equal(row[live], g["gt_row"][live])
+    best = arr[:B * A].view(B, A).cpu().numpy().astype(np.uint64)
+    tagged = (best >> np.uint64(48)) == np.uint64(gen)
+    assert np.array_equal(tagged, live)                          # an entry exactly where IoU_max >= neg_thr
+    iou_bits = ((best >> np.uint64(16)) & np.uint64(0xffffffff)).astype(np.uint32)
+    assert np.array_equal(iou_bits[live], g["iou_max"][live].view(np.uint32))
+
+
+@pytest.mark.parametrize("path", LOSS, ids=IDS)
+def test_loss_from_words_and_from_best_agree(path):
+    """k7_loss fed with k7_match's words and with k7_match_scatter's array is the same computation, bit for bit;
+    consume_best leaves the array clean so that a replayed CUDA graph can reuse one generation."""
+    g, yx, anc = load_loss_case(path, True)
+    sp = b200det.spec_of(anc)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    thr = (0.4, 0.5) if yx else (0.35, 0.45)
     B, A, _ = cls.shape
-    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, with_bits=True)
-    state = (assign.view(B, A) & 3).cpu().numpy()
-    want_bits = np.zeros((B, L.ignore_words(A) * 32), dtype=bool)
-    want_bits[:, :A] = state == 1
-    got_bits = np.unpackbits(bits.cpu().numpy().view(np.uint8), axis=1, bitorder="little").astype(bool)
-    assert np.array_equal(got_bits[:, :A], want_bits[:, :A])
-    kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B,
-              want_grad=True)
-    a = BL.loss_stage(anc, cls, reg, ann, assign, num_pos, ignore_bits=bits, **kw)
-    b = BL.loss_stage(anc, cls, reg, ann, assign, num_pos, **kw)
+    kw = dict(LOSS_KW, want_grad=True, target_div=(1, 1, 1, 1) if yx else (0.1, 0.1, 0.2, 0.2), yx_targets=yx)
+    assign, num_pos = BL.match(sp, ann, A, thr[0], thr[1])
+    a = BL.loss_stage(sp, cls, reg, ann, assign, num_pos, mean_divisor=B, **kw)
+    _, num_pos2, b, (arr, gen) = scatter_words(sp, ann, cls, reg, thr, **kw)
+    assert torch.equal(num_pos, num_pos2)
     for x, y in zip(a, b):
         assert torch.equal(x, y)
+    # replay of ONE generation: scatter -> loss(consume) twice on the same array
+    p = L.K7MatchParams(*thr)
+    import ctypes as C
+    for _ in range(2):
+        L.check(L.lib().k7_match_scatter(C.byref(sp), L.ptr(ann), B, A, ann.shape[1], C.byref(p), L.ptr(arr), gen,
+                                         L.ptr(num_pos2), L.stream_ptr(DEV)), "k7_match_scatter")
+        c = BL.loss_stage(sp, cls, reg, ann, None, num_pos2, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
+        for x, y in zip(a, c):
+            assert torch.equal(x, y)
+        assert int((arr[:B * A] >> 48 == gen).sum()) == 0        # consumed: nothing of this generation is left
+
+
+def test_match_scatter_adversarial_vs_exhaustive():
+    """Ground truth that stresses the candidate enumeration: duplicates (arg-max ties -> lowest row), boxes that equal
+    an anchor exactly, empty / inverted / sub-pixel boxes, boxes larger than the image or outside it, extreme aspect
+    ratios, a pad row in the middle, an image without any row.  Reference = the exhaustive kernel in debug mode."""
+    H, W = 256, 320
+    mod = b200det.Anchors()
+    anc = mod(torch.empty(1, 3, H, W, device=DEV))
+    sp = b200det.spec_of(anc)
+    A = sp.total
+    a_np = anc[0].cpu().numpy()
+    rows = [list(a_np[1234]) + [1.0], list(a_np[1234]) + [2.0],                 # the same box twice, on an anchor
+            list(a_np[A - 1]) + [0.0], list(a_np[0]) + [3.0],
+            [10.0, 10.0, 10.0, 50.0, 1.0], [50.0, 60.0, 40.0, 90.0, 1.0],       # empty, inverted
+            [100.2, 100.2, 100.9, 100.7, 2.0],                                  # sub-pixel
+            [-50.0, -80.0, 400.0, 300.0, 0.0], [330.0, 10.0, 390.0, 70.0, 0.0], # larger than / outside the image
+            [5.0, 120.0, 315.0, 131.0, 4.0], [150.0, 3.0, 158.0, 250.0, 4.0],   # 28:1 and 1:31
+            [-1.0, -1.0, -1.0, -1.0, -1.0],                                     # pad row in the middle
+            [30.5, 40.25, 95.75, 101.5, 2.0], [31.0, 41.0, 96.0, 101.0, 3.0]]
+    gen = torch.Generator().manual_seed(5)
+    rnd = b200det.synth.make_annotations(1, len(rows), 5, H, W, gen, mode="fixed", gt_min=4.0, gt_max=200.0)[0]
+    ann = torch.stack([torch.tensor(rows), rnd, torch.full((len(rows), 5), -1.0)]).to(DEV)
+    B = ann.shape[0]
+    cls = torch.full((B, A, 3), 0.01, device=DEV)
+    reg = torch.zeros((B, A, 4), device=DEV)
+    for thr in [(0.35, 0.45), (0.4, 0.5), (0.5, 0.5), (0.05, 0.9)]:
+        assign, num_pos, iou_max, argmax = BL.match(sp, ann, A, thr[0], thr[1], debug=True)
+        words, num_pos2, _, (arr, g_) = scatter_words(sp, ann, cls, reg, thr, want_grad=False, **LOSS_KW)
+        want = assign.view(B, A).cpu().numpy()
+        got = words.cpu().numpy()
+        assert np.array_equal(got & 3, want & 3), thr
+        assert torch.equal(num_pos, num_pos2)
+        live = (want & 3) != 0
+        live[2] = False                                                         # the image without a row: all IGNORE, no entry
+        assert np.array_equal((got >> 2)[live], (want >> 2)[live]), thr
+        best = arr[:B * A].view(B, A).cpu().numpy().astype(np.uint64)
+        bits = ((best >> np.uint64(16)) & np.uint64(0xffffffff)).astype(np.uint32)
+        assert np.array_equal(bits[live], iou_max.cpu().numpy().view(np.uint32)[live]), thr
+
+
+@pytest.mark.parametrize("name", ["c2_effdet_d0_512", "c3_ksevendet_thermal_512x640", "c2_effdet_d0_512_coded"])
+def test_match_scatter_equals_exhaustive_on_workloads(name):
+    """Full-size anchor sets of the BASELINE workloads (8 images each): scatter == exhaustive kernel."""
+    wl = b200det.synth.WORKLOADS[name]
+    B = 8
+    _, reg, ann = b200det.synth.make_inputs(b200det.synth.Workload(**{**wl.__dict__, "classes": 1}), seed=3, device=DEV, batch=B)
+    anc = b200det.Anchors(**wl.anchor_kwargs())(torch.empty(B, 3, wl.height, wl.width, device=DEV))
+    sp = b200det.spec_of(anc)
+    A = sp.total
+    cls = torch.full((B, A, 1), 0.01, device=DEV)
+    assign, num_pos = BL.match(sp, ann, A, 0.35, 0.45)
+    words, num_pos2, _, _ = scatter_words(sp, ann, cls, reg, (0.35, 0.45), want_grad=False, **LOSS_KW)
+    want, got = assign.view(B, A).cpu().numpy(), words.cpu().numpy()
+    assert np.array_equal(got & 3, want & 3)
+    assert torch.equal(num_pos, num_pos2) and int(num_pos.sum()) > 0
+    pos = (want & 3) == 2
+    assert np.array_equal((got >> 2)[pos], (want >> 2)[pos])
+
+
+def test_second_backward_is_refused():
+    """The saved gradients are scaled in place: backward(retain_graph=True) twice would scale them twice."""
+    g, yx, anc = load_loss_case(LOSS[IDS.index("loss_retina_small")], True)
+    ann = torch.from_numpy(g["annotations"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV).requires_grad_(True)
+    reg = torch.from_numpy(g["regressions"]).to(DEV).requires_grad_(True)
+    lc, lr = b200det.FocalLoss()(cls, reg, anc, ann)
+    loss = (2.0 * lc + lr).sum()
+    loss.backward(retain_graph=True)
+    np.testing.assert_allclose(cls.grad.cpu().numpy(), 2.0 * g["dcls"], rtol=1e-5, atol=1e-10)
+    with pytest.raises(RuntimeError, match="already run"):
+        loss.backward()
 
 
 def test_backward_scales_by_incoming_gradient():

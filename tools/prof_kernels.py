@@ -24,7 +24,7 @@ def main():
     ap.add_argument("workload", nargs="?", default="c2_effdet_d0_512")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--stages", default="match,loss_fwd,loss_fwd_bwd,detect")
+    ap.add_argument("--stages", default="match,match_exhaustive,loss_fwd,loss_fwd_bwd,detect")
     args = ap.parse_args()
     wl = b200det.synth.WORKLOADS[args.workload]
     B = args.batch or wl.batch
@@ -34,28 +34,37 @@ def main():
     anc = b200det.Anchors(**wl.anchor_kwargs())(img)
     A = wl.anchors
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
+    sp = b200det.spec_of(anc)
+    thr = (0.35, 0.45)
     dreg0 = torch.empty_like(reg)
-    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
+
+    def best():
+        """A fresh assignment of the production path (every scatter call starts a new generation of the array)."""
+        arr, gen, consume, num_pos = BL.match_scatter(sp, ann, A, *thr)
+        return dict(assign=None, num_pos=num_pos, best=(arr, gen, consume, *thr))
+
+    def loss(c, want_grad, **extra):
+        a = cur[0]
+        return BL.loss_stage(anc, c, reg, ann, a["assign"], a["num_pos"], want_grad=want_grad, best=a["best"], **extra, **kw)
+
+    cur = [best()]
     stages = {
-        "match": lambda: BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True),
-        "loss_fwd": lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw),
-        "loss_fwd_bwd": lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True,
-                                              dreg_zeroed=dreg0, ignore_bits=bits, **kw),
+        "match": lambda: BL.match_scatter(sp, ann, A, *thr),
+        "match_exhaustive": lambda: BL.match(anc, ann, A, *thr, zero_fill=dreg0),
+        "loss_fwd": lambda: loss(cls, False),
+        "loss_fwd_bwd": lambda: loss(cls, True),
         "detect": lambda: b200det.detect(cls, reg, anc, (wl.height, wl.width), sync=False),
     }
     if "logits" in args.stages:
         z = torch.logit(cls)                      # the head's pre-sigmoid tensor (SURVEY 8f row 1)
         stages.update({
-            "loss_fwd_logits": lambda: BL.loss_stage(anc, z, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits,
-                                                     from_logits=True, **kw),
-            "loss_fwd_bwd_logits": lambda: BL.loss_stage(anc, z, reg, ann, assign, num_pos, want_grad=True,
-                                                         dreg_zeroed=dreg0, ignore_bits=bits, from_logits=True, **kw),
+            "loss_fwd_logits": lambda: loss(z, False, from_logits=True),
+            "loss_fwd_bwd_logits": lambda: loss(z, True, from_logits=True),
             "detect_logits": lambda: b200det.detect(z, reg, anc, (wl.height, wl.width), sync=False, from_logits=True),
             "torch_sigmoid": lambda: torch.sigmoid(z),
         })
     if "levels" in args.stages:
         # the head's raw per-level NCHW tensors holding the same logits
-        sp = b200det.spec_of(anc)
         K, Cn = sp.cell_anchors, wl.classes
         zz = torch.logit(cls)
         lv = [zz[:, sp.offset[l]:sp.offset[l + 1], :].reshape(B, sp.fh[l], sp.fw[l], K * Cn).permute(0, 3, 1, 2).contiguous()
@@ -65,16 +74,21 @@ def main():
         def torch_layout():
             return torch.cat([t.permute(0, 2, 3, 1).contiguous().view(B, -1, Cn) for t in lv], dim=1)
 
+        def loss_lv(want_grad):
+            a = cur[0]
+            return BL.loss_stage_levels(sp, lv, reg, ann, None, a["num_pos"], want_grad=want_grad, best=a["best"],
+                                        from_logits=True, **kw)
+
         stages.update({
-            "loss_fwd_levels": lambda: BL.loss_stage_levels(sp, lv, reg, ann, assign, num_pos, want_grad=False,
-                                                            ignore_bits=bits, from_logits=True, **kw),
-            "loss_fwd_bwd_levels": lambda: BL.loss_stage_levels(sp, lv, reg, ann, assign, num_pos, want_grad=True,
-                                                                dreg_zeroed=dreg0, ignore_bits=bits, from_logits=True, **kw),
+            "loss_fwd_levels": lambda: loss_lv(False),
+            "loss_fwd_bwd_levels": lambda: loss_lv(True),
             "detect_levels": lambda: b200det.detect(lv, reg, anc, (wl.height, wl.width), sync=False, from_logits=True),
             "torch_layout": torch_layout,
         })
     for name in args.stages.split(","):
         fn = stages[name]
+        if name.startswith("loss"):
+            cur[0] = best()                       # the match stages above have moved the array on
         fn()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -35,8 +35,8 @@ def main():
     img = torch.empty(B, 3, wl.height, wl.width, device=dev)
     anc = b200det.Anchors(**wl.anchor_kwargs())(img)
     A, C, M = wl.anchors, wl.classes, wl.max_gt
-    dreg0 = torch.empty_like(reg)
-    assign, num_pos, bits = BL.match(anc, ann, A, 0.35, 0.45, zero_fill=dreg0, with_bits=True)
+    arr, gen, consume, num_pos = BL.match_scatter(b200det.spec_of(anc), ann, A, 0.35, 0.45)
+    best = (arr, gen, consume, 0.35, 0.45)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
     bf = B * (A * (4 * C + 16) + 20 * M)
     bb = B * (A * (8 * C + 32) + 20 * M)
@@ -46,9 +46,8 @@ def main():
     for slice_, warps, stages in combos:
         os.environ["K7_SLICE"], os.environ["K7_WARPS"], os.environ["K7_STAGES"] = str(slice_), str(warps), str(stages)
         try:
-            f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=False, ignore_bits=bits, **kw))
-            g = timed(lambda: BL.loss_stage(anc, cls, reg, ann, assign, num_pos, want_grad=True, dreg_zeroed=dreg0,
-                                            ignore_bits=bits, **kw))
+            f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=False, best=best, **kw))
+            g = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=True, best=best, **kw))
         except Exception as e:                     # geometry that does not fit
             print(f"slice={slice_} warps={warps:2d} stages={stages}: {e}")
             continue
