@@ -317,7 +317,8 @@ def run_b200(args, wl):
     sp_ = b200det.spec_of(anc)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
     ms_match = timed(lambda: BL.match_scatter(sp_, ann, A, 0.35, 0.45), k, 3)
-    arr_, gen_, consume_, num_pos = BL.match_scatter(sp_, ann, A, 0.35, 0.45)
+    arr_, gen_, consume_ = BL.match_scatter(sp_, ann, A, 0.35, 0.45)
+    num_pos = None
     best_ = (arr_, gen_, consume_, 0.35, 0.45)
     ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=True, best=best_, **kw), k, 3)
     ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=False, best=best_, **kw), k, 3)

@@ -134,9 +134,8 @@ K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_orde
  * `best` directly (K7LossParams.match_generation / neg_thr / pos_thr).
  *   best        [B,A] uint64, caller-owned, ZERO-INITIALISED ONCE; every call on it must pass a LARGER
  *               generation than the one before (1 .. K7_BEST_GEN_MAX; re-zero before starting over)
- *   num_pos     [B] int32 (zeroed by the call): anchors whose maximum reached pos_thr - each is counted once,
- *               by the atomicMax that first lifts it over pos_thr (integer, order independent)
- * Requires a recipe, 1e-3 < neg_thr <= pos_thr, M <= 65535.  Images without a valid row leave `best`
+ * The atomics return nothing (fire and forget); the positives are counted by k7_loss, which walks the array
+ * anyway.  Requires a recipe, 1e-3 < neg_thr <= pos_thr, M <= 65535.  Images without a valid row leave `best`
  * untouched; k7_loss sees from the annotations that the image is skipped (losses.py:52-60). */
 #define K7_BEST_GEN_MAX 65535u
 #define K7_BEST_GEN(v) ((uint32_t)((v) >> 48))
@@ -144,8 +143,7 @@ K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_orde
 #define K7_BEST_ROW(v) (0xFFFF - (int32_t)((v) & 0xFFFFu))
 K7_API size_t k7_match_scatter_workspace_bytes(int B, int A);
 K7_API int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
-                     const K7MatchParams* params, uint64_t* best, uint32_t generation, int32_t* num_pos,
-                     void* stream);
+                     const K7MatchParams* params, uint64_t* best, uint32_t generation, void* stream);
 
 /* Multi-GPU: the path's one exchange - the four batch sums {sum cls_i, sum reg_i, sum num_pos_i, B}
  * of every rank - fused into k7_loss.  mailbox[p] is a device pointer, valid in THIS process, to
@@ -205,6 +203,8 @@ K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
  * (neg_thr <= IoU_max < pos_thr, losses.py:79-82) are taken out of the sum again and their gradient is
  * zeroed.  Row contributions are accumulated as 2^-32 fixed-point integers (order independent), the
  * stream partials in a fixed order: results are bit-reproducible run to run.  Outputs:
+ *   num_pos   [B]   int32    positives per image, counted while the assignment is walked (it is WRITTEN here,
+ *                            whichever form the assignment comes in)
  *   per_image [B,2] float32  (cls_loss_i, reg_loss_i)
  *   sums      [4]   float32  { sum_i cls_loss_i, sum_i reg_loss_i, sum_i num_pos_i, B }  (the NCCL payload)
  *   dcls [B,A,C], dreg [B,A,4] (optional, both or neither): d(mean cls loss)/dcls and
@@ -214,7 +214,7 @@ K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
  * 16-byte aligned. */
 K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order,
             const float* cls, const float* reg, const float* annotations,
-            const int32_t* assign, const uint64_t* best, const int32_t* num_pos,
+            const int32_t* assign, const uint64_t* best, int32_t* num_pos,
             int B, int A, int C, int M, const K7LossParams* params,
             float* per_image, float* sums, float* dcls, float* dreg,
             void* workspace, size_t workspace_bytes, void* stream);
@@ -229,7 +229,7 @@ K7_API int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order
 K7_API size_t k7_loss_levels_workspace_bytes(const K7AnchorSpec* spec, int B, int C);
 K7_API int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
                    const float* annotations, const int32_t* assign, const uint64_t* best,
-                   const int32_t* num_pos, int B, int C, int M, const K7LossParams* params,
+                   int32_t* num_pos, int B, int C, int M, const K7LossParams* params,
                    float* per_image, float* sums, float* const* dlevels, float* dreg,
                    void* workspace, size_t workspace_bytes, void* stream);
 

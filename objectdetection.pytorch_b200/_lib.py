@@ -134,7 +134,7 @@ SYMBOLS = {
                            C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P, _P]),
     "k7_match_scatter_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "k7_match_scatter": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_int, C.c_int, C.POINTER(K7MatchParams),
-                                   _P, C.c_uint32, _P, _P]),
+                                   _P, C.c_uint32, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),

@@ -646,27 +646,44 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
 // so states, num_pos and the arg-max of every non-negative anchor are those of the exhaustive
 // kernels, bit for bit (tests/test_gpu_parity.py).  Pairs at or above neg_thr are folded into
 // best[] with a 64-bit atomicMax: generation | IoU bits | ~row - the largest IoU, then the lowest
-// row (torch.max returns the first index).  The maximum is order independent, and so is num_pos:
-// an anchor is counted by the one atomicMax that finds it below pos_thr and leaves it at or above.
+// row (torch.max returns the first index).  The maximum is order independent; its result is not
+// needed here, so the atomics are fire-and-forget (the positives are counted by k7_loss's scan).
+struct __align__(16) K7ScatterShape {   // one anchor shape (level l, in-cell anchor k), 80 bytes
+    double base[4];                   // the recipe's in-cell box (spec.base[l][k])
+    float g_lo, g_hi;                 // window of ground-truth areas that can reach neg_thr with this shape
+    float area_lo;                    // its area, rounded down
+    float wa, ha;                     // its extents, rounded up
+    float bx1, bx2, by1, by2;         // its box around the cell centre as (x1, x2, y1, y2)
+    float pad[3];
+};
 struct K7ScatterAux {
-    float wa[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], ha[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];         // extents, rounded up
-    float area_lo[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];                                           // area, rounded down
-    float g_lo[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], g_hi[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];     // window of ground-truth areas
-    float bx1[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], bx2[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];       // shape around the cell centre
-    float by1[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS], by2[K7_MAX_LEVELS][K7_MAX_CELL_ANCHORS];
+    float lvl_lo[K7_MAX_LEVELS], lvl_hi[K7_MAX_LEVELS];   // union of the windows of a level's shapes
     float inv_stride[K7_MAX_LEVELS];
-    float c_in;                                                                                   // t/(1+t) * (1 - 1e-4)
+    float c_in;                                           // t/(1+t) * (1 - 1e-4)
+    int pad[3];
+    K7ScatterShape shapes[K7_MAX_LEVELS * K7_MAX_CELL_ANCHORS];   // [l * cell_anchors + k]
 };
 
 #define K7_SCATTER_THREADS 128
 __global__ void __launch_bounds__(K7_SCATTER_THREADS)
 k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScatterAux X,
-                        const float* __restrict__ annotations, int B, int A, int M, float neg_thr, float pos_thr,
-                        unsigned long long* __restrict__ best, unsigned int gen, int32_t* __restrict__ num_pos) {
+                        const float* __restrict__ annotations, int B, int A, int M, float neg_thr,
+                        unsigned long long* __restrict__ best, unsigned int gen) {
+    // the shape table is copied from the kernel parameters to shared memory once per CTA: read in place it
+    // is an indexed constant load per field (ncu: the address-divergence unit was the busiest pipe)
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    K7ScatterShape* sh = reinterpret_cast<K7ScatterShape*>(smem_raw);
+    const int L = spec.num_levels, K = spec.cell_anchors;
+    {
+        const int n16 = L * K * (int)(sizeof(K7ScatterShape) / 16);
+        const uint4* src = reinterpret_cast<const uint4*>(X.shapes);
+        uint4* dst = reinterpret_cast<uint4*>(sh);
+        for (int i = threadIdx.x; i < n16; i += K7_SCATTER_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
     const int lane = threadIdx.x & 31;
     const long long gwarp = ((long long)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * K7_SCATTER_THREADS) >> 5;
-    const int L = spec.num_levels, K = spec.cell_anchors;
     const long long tasks = (long long)B * M * L;
     const unsigned long long tag = (unsigned long long)gen << 48;
     const bool xy = spec.box_order == K7_BOX_XYXY;
@@ -675,61 +692,57 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
         const long long r = t / L;
         const int m = (int)(r % M), b = (int)(r / M);
         const float* row = annotations + ((size_t)b * M + m) * 5;
-        if (__ldg(row + 4) == -1.0f) continue;            // pad row (losses.py:50)
-        const float g0 = __ldg(row + 0), g1 = __ldg(row + 1), g2 = __ldg(row + 2), g3 = __ldg(row + 3);
+        const float g0 = __ldg(row + 0), g1 = __ldg(row + 1), g2 = __ldg(row + 2), g3 = __ldg(row + 3), g4 = __ldg(row + 4);
+        if (g4 == -1.0f) continue;                        // pad row (losses.py:50)
         const float gw = K7_FSUB(g2, g0), gh = K7_FSUB(g3, g1);
         if (!(gw > 0.0f && gh > 0.0f)) continue;          // empty box: IoU is 0 with every anchor
         const float area_g = k7_area(g0, g1, g2, g3);
+        if (!(area_g >= X.lvl_lo[l] && area_g <= X.lvl_hi[l])) continue;   // no shape of this level can reach neg_thr
         const int fw = spec.fw[l], fh = spec.fh[l];
         if (fw <= 0 || fh <= 0) continue;
         const float inv_s = X.inv_stride[l];
         const double st = spec.stride[l];
-        int pos = 0;
+        const int level_off = spec.offset[l];
         for (int k = 0; k < K; ++k) {                     // warp-uniform
-            if (!(area_g >= X.g_lo[l][k] && area_g <= X.g_hi[l][k])) continue;
-            const float imin = X.c_in * (X.area_lo[l][k] + area_g);
-            const float mw = fminf(X.wa[l][k], gw), mh = fminf(X.ha[l][k], gh);
+            const K7ScatterShape& S = sh[l * K + k];
+            if (!(area_g >= S.g_lo && area_g <= S.g_hi)) continue;
+            const float imin = X.c_in * (S.area_lo + area_g);
+            const float mw = fminf(S.wa, gw), mh = fminf(S.ha, gh);
             if (imin > mw * mh) continue;
             const float iw_min = imin / mh, ih_min = imin / mw;
             // cell centre c = (x + 0.5) * stride must satisfy  g0 + iw_min - bx2 <= c <= g2 - iw_min - bx1
-            const float xl = (g0 + iw_min - X.bx2[l][k]) * inv_s - 0.52f, xh = (g2 - iw_min - X.bx1[l][k]) * inv_s - 0.48f;
-            const float yl = (g1 + ih_min - X.by2[l][k]) * inv_s - 0.52f, yh = (g3 - ih_min - X.by1[l][k]) * inv_s - 0.48f;
+            const float xl = (g0 + iw_min - S.bx2) * inv_s - 0.52f, xh = (g2 - iw_min - S.bx1) * inv_s - 0.48f;
+            const float yl = (g1 + ih_min - S.by2) * inv_s - 0.52f, yh = (g3 - ih_min - S.by1) * inv_s - 0.48f;
             const int xlo = max(0, (int)ceilf(fmaxf(xl, -1.0f))), xhi = min(fw - 1, (int)floorf(fminf(xh, (float)fw)));
             const int ylo = max(0, (int)ceilf(fmaxf(yl, -1.0f))), yhi = min(fh - 1, (int)floorf(fminf(yh, (float)fh)));
             if (xlo > xhi || ylo > yhi) continue;
             const int nx = xhi - xlo + 1, n = nx * (yhi - ylo + 1);
-            const double* bb = spec.base[l][k];
+            const double b0 = S.base[0], b1 = S.base[1], b2 = S.base[2], b3 = S.base[3];
             for (int i = lane; i < n; i += 32) {
                 const int yy = i / nx, x = xlo + (i - yy * nx), y = ylo + yy;
                 const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), st);
                 const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), st);
                 float ax1, ay1, ax2, ay2;                 // k7_anchor_from_spec: float64 add, one rounding
                 if (xy) {
-                    ax1 = __double2float_rn(__dadd_rn(bb[0], sx));
-                    ay1 = __double2float_rn(__dadd_rn(bb[1], sy));
-                    ax2 = __double2float_rn(__dadd_rn(bb[2], sx));
-                    ay2 = __double2float_rn(__dadd_rn(bb[3], sy));
+                    ax1 = __double2float_rn(__dadd_rn(b0, sx));
+                    ay1 = __double2float_rn(__dadd_rn(b1, sy));
+                    ax2 = __double2float_rn(__dadd_rn(b2, sx));
+                    ay2 = __double2float_rn(__dadd_rn(b3, sy));
                 } else {
-                    ay1 = __double2float_rn(__dadd_rn(bb[0], sy));
-                    ax1 = __double2float_rn(__dadd_rn(bb[1], sx));
-                    ay2 = __double2float_rn(__dadd_rn(bb[2], sy));
-                    ax2 = __double2float_rn(__dadd_rn(bb[3], sx));
+                    ay1 = __double2float_rn(__dadd_rn(b0, sy));
+                    ax1 = __double2float_rn(__dadd_rn(b1, sx));
+                    ay2 = __double2float_rn(__dadd_rn(b2, sy));
+                    ax2 = __double2float_rn(__dadd_rn(b3, sx));
                 }
                 const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, k7_area(ax1, ay1, ax2, ay2), g0, g1, g2, g3, area_g);
                 if (iou >= neg_thr) {
-                    const int a = spec.offset[l] + (y * fw + x) * K + k;
+                    const int a = level_off + (y * fw + x) * K + k;
                     const unsigned long long v = tag | ((unsigned long long)__float_as_uint(iou) << 16) |
                                                  (unsigned long long)(0xFFFF - m);
-                    const unsigned long long old = atomicMax(best + (size_t)b * A + a, v);
-                    if (iou >= pos_thr) {
-                        const bool was_pos = K7_BEST_GEN(old) == gen && __uint_as_float(K7_BEST_IOU_BITS(old)) >= pos_thr;
-                        pos += was_pos ? 0 : 1;
-                    }
+                    atomicMax(best + (size_t)b * A + a, v);   // result unused: RED.MAX.64, nothing to wait for
                 }
             }
         }
-        pos = k7_warp_sum(pos);
-        if (lane == 0 && pos) atomicAdd(num_pos + b, pos);   // integer: order independent, exact
     }
 }
 
@@ -739,9 +752,8 @@ extern "C" size_t k7_match_scatter_workspace_bytes(int B, int A) {
 }
 
 extern "C" int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
-                                const K7MatchParams* params, uint64_t* best, uint32_t generation, int32_t* num_pos,
-                                void* stream) {
-    K7_REQUIRE(spec && annotations && params && best && num_pos, "k7_match_scatter: null argument");
+                                const K7MatchParams* params, uint64_t* best, uint32_t generation, void* stream) {
+    K7_REQUIRE(spec && annotations && params && best, "k7_match_scatter: null argument");
     K7_REQUIRE(B > 0 && A > 0 && M > 0 && M <= 65535, "k7_match_scatter: bad shape B=%d A=%d M=%d", B, A, M);
     K7_REQUIRE(generation >= 1u && generation <= K7_BEST_GEN_MAX, "k7_match_scatter: generation %u outside [1, %u]",
                generation, K7_BEST_GEN_MAX);
@@ -753,37 +765,44 @@ extern "C" int k7_match_scatter(const K7AnchorSpec* spec, const float* annotatio
     if (rc) return rc;
     K7ScatterAux X;
     memset(&X, 0, sizeof(X));
+    static_assert(sizeof(K7ScatterShape) == 80, "K7ScatterShape is copied as uint4s");
+    K7ScatterShape* shapes = X.shapes;
     const double t = (double)params->neg_thr;
     X.c_in = (float)(t / (1.0 + t) * (1.0 - 1e-4));
     const bool xy = spec->box_order == K7_BOX_XYXY;
+    const int K = spec->cell_anchors;
     for (int l = 0; l < spec->num_levels; ++l) {
         X.inv_stride[l] = (float)(1.0 / spec->stride[l]);
-        for (int k = 0; k < spec->cell_anchors; ++k) {
+        X.lvl_lo[l] = 3.0e38f;
+        X.lvl_hi[l] = 0.0f;
+        for (int k = 0; k < K; ++k) {
             const double* b = spec->base[l][k];
+            K7ScatterShape& S = shapes[l * K + k];
             const double x1 = xy ? b[0] : b[1], y1 = xy ? b[1] : b[0], x2 = xy ? b[2] : b[3], y2 = xy ? b[3] : b[2];
-            const double w = x2 - x1, h = y2 - y1, ar = w * h;
+            const double w = x2 - x1, h = y2 - y1;
+            for (int c = 0; c < 4; ++c) S.base[c] = b[c];
             // outward roundings: the device compares against float32-rounded anchors (coordinates up to ~1e4: 1e-3 px)
-            X.wa[l][k] = (float)(w * (1.0 + 1e-5) + 2e-3);
-            X.ha[l][k] = (float)(h * (1.0 + 1e-5) + 2e-3);
+            S.wa = (float)(w * (1.0 + 1e-5) + 2e-3);
+            S.ha = (float)(h * (1.0 + 1e-5) + 2e-3);
             const double ar_lo = (w - 2e-3 > 0 ? w - 2e-3 : 0) * (h - 2e-3 > 0 ? h - 2e-3 : 0) * (1.0 - 1e-5);
             const double ar_hi = (w + 2e-3) * (h + 2e-3) * (1.0 + 1e-5);
-            X.area_lo[l][k] = (float)ar_lo;
-            X.g_lo[l][k] = (float)(t * (1.0 - 1e-4) * ar_lo);
-            X.g_hi[l][k] = (float)(ar_hi / (t * (1.0 - 1e-4)));
-            (void)ar;
-            X.bx1[l][k] = (float)x1; X.bx2[l][k] = (float)x2; X.by1[l][k] = (float)y1; X.by2[l][k] = (float)y2;
+            S.area_lo = (float)ar_lo;
+            S.g_lo = (float)(t * (1.0 - 1e-4) * ar_lo);
+            S.g_hi = (float)(ar_hi / (t * (1.0 - 1e-4)));
+            S.bx1 = (float)x1; S.bx2 = (float)x2; S.by1 = (float)y1; S.by2 = (float)y2;
+            if (S.g_lo < X.lvl_lo[l]) X.lvl_lo[l] = S.g_lo;
+            if (S.g_hi > X.lvl_hi[l]) X.lvl_hi[l] = S.g_hi;
         }
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    K7_CUDA(cudaMemsetAsync(num_pos, 0, sizeof(int32_t) * B, st));
+    const size_t tbytes = sizeof(K7ScatterShape) * (size_t)spec->num_levels * K;
     const long long tasks = (long long)B * M * spec->num_levels;
     const int wpb = K7_SCATTER_THREADS / 32;
     long long blocks = (tasks + wpb - 1) / wpb;
     const long long cap = 16ll * k7_sm_count();      // 16 resident CTAs of 128 threads per SM; the rest is looped
     if (blocks > cap) blocks = cap;
-    k7_match_scatter_kernel<<<(unsigned)blocks, K7_SCATTER_THREADS, 0, st>>>(
-        *spec, X, annotations, B, A, M, params->neg_thr, params->pos_thr, reinterpret_cast<unsigned long long*>(best),
-        generation, num_pos);
+    k7_match_scatter_kernel<<<(unsigned)blocks, K7_SCATTER_THREADS, tbytes, st>>>(
+        *spec, X, annotations, B, A, M, params->neg_thr, reinterpret_cast<unsigned long long*>(best), generation);
     K7_LAUNCH_CHECK();
     return K7_OK;
 }

@@ -12,12 +12,13 @@
 //      the score threshold (strict '>') finds the first arg-max class, generates the anchor,
 //      decodes and clips the box and records the survivor by anchor id.  Regression deltas are
 //      read for survivors only.  Bytes: A*C*4 read per image + 32*S written.
-//   2. k7_sort_kernel (one CTA per image) ranks the survivors (the order torchvision.ops.nms's
-//      stable descending sort produces, because the anchor id breaks score ties) and lays them out
-//      in a spatial order; k7_mask_kernel (all SMs) builds a sparse suppression bitmask;
-//      k7_resolve_kernel (one CTA per image) resolves greedy NMS as a fixed point.  The result is
-//      identical to the sequential algorithm.  Images with more survivors than the workspace's cap
-//      go through k7_fallback_image (one CTA, chunks of 1024 boxes) inside the resolve kernel.
+//   2. the survivors' keys (score descending | anchor ascending) are sorted in chunks on all SMs and
+//      merged by ranking (k7_nms_chunksort_kernel, k7_nms_rank_kernel); the ranked boxes are binned on
+//      uniform grids by area class (k7_nms_cellorder_kernel); a thread per box tests the boxes of the
+//      neighbouring cells that rank before it (k7_nms_pairs_kernel) and records the overlaps as edges;
+//      k7_nms_resolve_kernel (one CTA per image) resolves greedy NMS as a fixed point over the edges.
+//      The result is identical to the sequential algorithm.  Images with more survivors than the
+//      workspace's cap go through k7_fallback_image (one CTA, chunks of 1024 boxes) inside the resolve kernel.
 #include <math.h>
 #include <string.h>
 
@@ -91,28 +92,34 @@ extern "C" int k7_clip(float* boxes, int B, int A, int height, int width, void* 
 
 // ------------------------------------------------------------------ workspace of k7_detect
 struct K7DetectWs {
-    int32_t* surv_count;    // [B]
+    // ---- zeroed at the start of every call (contiguous)
+    int32_t* surv_count;    // [B] survivors (counted by the score kernel)
+    int32_t* nedge;         // [B] edges found by the pair kernel
+    unsigned int* bounds;   // [B][4] bounds of the live boxes' centres (k7_f2ord)
+    uint32_t* bits;         // [B][W32] survivor bitmap by anchor id (for the survivor rank)
+    uint2* ctab;            // [B][K7_GRID_CELLS] cell table
+    // ---- not initialised
     int32_t* kept_count;    // [B]
-    uint32_t* bits;         // [B][W32] survivor bitmap by anchor id
+    int32_t* nsel;          // [B] boxes in play (-1: fallback image)
+    int32_t* ccnt;          // [B][K7_NMS_G]
     int32_t* wprefix;       // [B][W32] exclusive popcount prefix of bits
-    uint64_t* keys0;        // [B][A]
-    uint64_t* keys1;        // [B][A]
+    uint64_t* keys0;        // [B][A] survivor keys in arrival order
+    uint64_t* keys1;        // [B][A] keys in rank order
+    uint64_t* keysC;        // [B][cap]
+    uint64_t* ckeyC;        // [B][cap]
     float4* box;            // [B][A] decoded+clipped box of each survivor, by anchor id
     int32_t* label;         // [B][A] arg-max class of each survivor, by anchor id
-    float* score;           // [B][A] class maximum of each survivor, by anchor id
     uint64_t* kept_key;     // [B][A] sort key of each kept box, in keep order
     float4* kept_box;       // [B][A]
-    int32_t* nsel;          // [B] survivors handled by the multi-SM NMS path (-1: fallback image)
-    float4* sbox;           // [B][cap] boxes in spatial order
-    int32_t* srank;         // [B][cap] rank (position in score order) of the box at each spatial index
-    int32_t* slabel;        // [B][cap] class of the box at each spatial index (read by the class-aware NMS only)
-    float4* blk;            // [B][cap/32][2] (min x1, max x2, min y1, max y2), (min area, max area, -, -) per 32 boxes
-    int32_t* work;          // [B] work-item counter of the mask kernel
-    unsigned long long* nz; // [B][cap][nzw] which words of a bitmask row were written
-    unsigned long long* M;  // [B][cap][cap/64] suppression bitmask, sparsely written
-    size_t bytes;
+    float4* rbox;           // [B][cap] boxes in rank order
+    float4* cbox;           // [B][cap] boxes in cell order
+    int32_t* crank;         // [B][cap]
+    int32_t* clabel;        // [B][cap]
+    int32_t* pend;          // [B][cap]
+    unsigned int* edges;    // [B][ecap]
+    size_t bytes, zero_bytes;
     int W32;
-    int cap;                // survivors per image the multi-SM NMS path is sized for
+    int cap, ecap;          // survivors per image the multi-SM NMS path is sized for; edges per image
 };
 static int k7_nms_cap(int B, int n_max);
 
@@ -127,27 +134,33 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
         o += k7_align_up(bytes, 256);
         return r;
     };
+    w.cap = k7_nms_cap(B, A);
+    w.ecap = w.cap * 16;   // K7_EDGE_PER_BOX
+    const size_t cap = (size_t)w.cap;
     w.surv_count = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
-    w.kept_count = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.nedge = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.bounds = reinterpret_cast<unsigned int*>(take(sizeof(unsigned int) * 4 * (size_t)B));
     w.bits = reinterpret_cast<uint32_t*>(take(sizeof(uint32_t) * (size_t)B * w.W32));
+    w.ctab = reinterpret_cast<uint2*>(take(sizeof(uint2) * (size_t)B * (15 * 32 * 32)));   // K7_GRID_CELLS
+    w.zero_bytes = o;
+    w.kept_count = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.nsel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
+    w.ccnt = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * 8 * (size_t)B));            // K7_NMS_G
     w.wprefix = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * w.W32));
     w.keys0 = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.keys1 = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
+    w.keysC = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * (size_t)B * cap));
+    w.ckeyC = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * (size_t)B * cap));
     w.box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
     w.label = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * BA));
-    w.score = reinterpret_cast<float*>(take(sizeof(float) * BA));
     w.kept_key = reinterpret_cast<uint64_t*>(take(sizeof(uint64_t) * BA));
     w.kept_box = reinterpret_cast<float4*>(take(sizeof(float4) * BA));
-    w.nsel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * B));
-    w.cap = k7_nms_cap(B, A);
-    const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
-    w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * cap));
-    w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
-    w.slabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
-    w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * (size_t)B * nbw));
-    w.work = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B));
-    w.nz = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * cap * nzw));
-    w.M = reinterpret_cast<unsigned long long*>(take(8 * (size_t)B * cap * nbw));
+    w.rbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * cap));
+    w.cbox = reinterpret_cast<float4*>(take(sizeof(float4) * (size_t)B * cap));
+    w.crank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
+    w.clabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
+    w.pend = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
+    w.edges = reinterpret_cast<unsigned int*>(take(sizeof(unsigned int) * (size_t)B * w.ecap));
     w.bytes = o;
     return w;
 }
@@ -199,7 +212,7 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                      const float* __restrict__ cls, const float4* __restrict__ reg, int A, int C, float report_thr,
                      const __grid_constant__ K7DetectParams P, const __grid_constant__ K7ScoreGeom G,
                      uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws, int32_t* __restrict__ label_ws,
-                     float* __restrict__ score_ws) {
+                     int32_t* __restrict__ surv_count, uint64_t* __restrict__ keys0) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
@@ -322,7 +335,10 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
             if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
             box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
             label_ws[oa] = idx;
-            score_ws[oa] = m;
+            {   // the survivor's key joins the image's list (arrival order; the sort fixes the order)
+                const int slot = atomicAdd(surv_count + b, 1);
+                keys0[(size_t)b * A + slot] = ((uint64_t)k7_score_key_desc(m) << 32) | (uint32_t)a;
+            }
             atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
         }
         __syncwarp();
@@ -354,7 +370,39 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
                     if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) > thr) hits |= 1u << k;
                 }
             }
-            if (__any_sync(0xffffffffu, hits != 0u)) {   // ~1 slice in 10
+            if (C == 1 && __any_sync(0xffffffffu, hits != 0u)) {
+                // single-class heads (KSevenDet thermal faces): a row is one element, every report IS a survivor
+                // with label 0.  Lanes queue their own reports (ballot prefix) instead of the warp resolving
+                // them one by one - that loop was 170 us for 42 MB at 256 dense images.
+                for (int k = 0; k < SL / 128; ++k) {
+                    const bool mine = (hits >> k) & 1u;
+                    if (!__any_sync(0xffffffffu, mine)) continue;
+                    float v[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+                    if (mine) {
+                        const float4 t = t4[lane + 32 * k];
+                        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const bool rep = v[e] > thr;
+                        const unsigned mb = __ballot_sync(0xffffffffu, rep);
+                        if (!mb) continue;
+                        const int need = __popc(mb);
+                        if (qn + need > K7_SPIPE_QCAP) drain();
+                        if (rep) {
+                            const int i = i_lo + 4 * (lane + 32 * k) + e;
+                            uint32_t bimg = d.y, ge = d.z + (uint32_t)i;
+                            if ((uint32_t)i >= d.w) {
+                                const uint32_t r = (uint32_t)i - d.w, qi = r / G.AC;
+                                bimg = d.y + 1u + qi;
+                                ge = r - qi * G.AC;
+                            }
+                            queue[qn + __popc(mb & ((1u << lane) - 1u))] = make_uint4(bimg, ge, 0u, __float_as_uint(v[e]));
+                        }
+                        qn += need;
+                    }
+                }
+            } else if (__any_sync(0xffffffffu, hits != 0u)) {   // ~1 slice in 10
                 // Every element above the threshold is a report.  The warp resolves it at once from the
                 // tile: class maximum and FIRST arg-max of its row (torch.max, retinanet.py:300,316);
                 // the report that sits on the arg-max element queues the survivor.
@@ -487,7 +535,7 @@ template <bool LOGITS>
 __device__ __forceinline__ void k7_levels_emit(const K7AnchorSpec& spec, const K7DetectParams& P, const float* base, int S,
                                                float m, int idx, bool tie, int b, int a, int A, const float4* __restrict__ reg,
                                                uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws,
-                                               int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+                                               int32_t* __restrict__ label_ws, int32_t* __restrict__ surv_count, uint64_t* __restrict__ keys0) {
     if (LOGITS) {
         const float p = k7_sigmoid_precise(m);
         if (!(p > P.score_thr)) return;
@@ -511,7 +559,10 @@ __device__ __forceinline__ void k7_levels_emit(const K7AnchorSpec& spec, const K
     if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
     box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
     label_ws[oa] = idx;
-    score_ws[oa] = m;
+    {   // the survivor's key joins the image's list (arrival order; the sort fixes the order)
+        const int slot = atomicAdd(surv_count + b, 1);
+        keys0[(size_t)b * A + slot] = ((uint64_t)k7_score_key_desc(m) << 32) | (uint32_t)a;
+    }
     atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
 }
 
@@ -536,7 +587,7 @@ template <bool LOGITS>
 __device__ __forceinline__ void k7_levels_flush(const K7AnchorSpec& spec, const K7ScoreLevels& LV, const K7DetectParams& P,
                                                 const int4* s_q, int qn, int A, int C, const float4* __restrict__ reg,
                                                 uint32_t* __restrict__ bits, int W32, float4* __restrict__ box_ws,
-                                                int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+                                                int32_t* __restrict__ label_ws, int32_t* __restrict__ surv_count, uint64_t* __restrict__ keys0) {
     const int K = spec.cell_anchors;
     for (int i = threadIdx.x; i < qn; i += 256) {   // records are keyed by anchor id: the queue order does not matter
         const int4 ent = s_q[i];
@@ -544,7 +595,7 @@ __device__ __forceinline__ void k7_levels_flush(const K7AnchorSpec& spec, const 
         const int S = LV.S[l];
         const float* base = LV.cls[l] + ((size_t)b * K + k) * (size_t)C * (size_t)S + (size_t)s;
         k7_levels_emit<LOGITS>(spec, P, base, S, __int_as_float(ent.y), ent.z & 0x7fffffff, ent.z < 0, b,
-                               spec.offset[l] + s * K + k, A, reg, bits, W32, box_ws, label_ws, score_ws);
+                               spec.offset[l] + s * K + k, A, reg, bits, W32, box_ws, label_ws, surv_count, keys0);
     }
 }
 
@@ -553,7 +604,7 @@ __global__ void __launch_bounds__(256, 2)
 k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV, int num_tiles,
                        const float4* __restrict__ reg, int A, int C, float report_thr,
                        const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
-                       float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+                       float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, int32_t* __restrict__ surv_count, uint64_t* __restrict__ keys0) {
     extern __shared__ float4 s_ring[];   // [K7_LV_G][K7_LV_U][256]
     __shared__ int4 s_q[K7_LV_QCAP];
     __shared__ int s_qn;
@@ -648,13 +699,13 @@ k7_score_levels_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_c
         __syncthreads();
         const int qn = s_qn;
         if (qn > K7_LV_QCAP - 1024) {   // the next tile may add up to 1024
-            k7_levels_flush<LOGITS>(spec, LV, P, s_q, qn, A, C, reg, bits, W32, box_ws, label_ws, score_ws);
+            k7_levels_flush<LOGITS>(spec, LV, P, s_q, qn, A, C, reg, bits, W32, box_ws, label_ws, surv_count, keys0);
             __syncthreads();
             if (threadIdx.x == 0) s_qn = 0;
             __syncthreads();
         }
     }
-    k7_levels_flush<LOGITS>(spec, LV, P, s_q, s_qn, A, C, reg, bits, W32, box_ws, label_ws, score_ws);
+    k7_levels_flush<LOGITS>(spec, LV, P, s_q, s_qn, A, C, reg, bits, W32, box_ws, label_ws, surv_count, keys0);
 }
 
 // Levels whose S is not a multiple of four: one thread per anchor, register loads.  These maps are
@@ -664,7 +715,7 @@ __global__ void __launch_bounds__(256)
 k7_score_levels_scalar_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScoreLevels LV,
                               const float4* __restrict__ reg, int A, int C, float report_thr,
                               const __grid_constant__ K7DetectParams P, uint32_t* __restrict__ bits, int W32,
-                              float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, float* __restrict__ score_ws) {
+                              float4* __restrict__ box_ws, int32_t* __restrict__ label_ws, int32_t* __restrict__ surv_count, uint64_t* __restrict__ keys0) {
     const int b = blockIdx.y;
     int l = 0;
 #pragma unroll
@@ -688,7 +739,7 @@ k7_score_levels_scalar_kernel(const __grid_constant__ K7AnchorSpec spec, const _
     }
     if (m > report_thr)
         k7_levels_emit<LOGITS>(spec, P, base, S, m, idx, LOGITS && pm >= fminf(m - 2e-3f, 8.0f), b, spec.offset[l] + s * K + k, A,
-                               reg, bits, W32, box_ws, label_ws, score_ws);
+                               reg, bits, W32, box_ws, label_ws, surv_count, keys0);
 }
 
 // ------------------------------------------------------------------ kernel 2: per-image sort + NMS
@@ -1113,366 +1164,285 @@ __device__ void k7_fallback_image(int b, int A, float iou_thr, int pre_topk, int
 }
 
 // ------------------------------------------------------------------ multi-SM NMS for n <= cap survivors
-// Round-1 profiles: with one CTA per image the IoU bitmask (n^2/2 pair tests) and the greedy scan
-// ran on 64 of 148 SMs and took longer than streaming the whole classification tensor; and at
-// EfficientDet-D7 (7 500 survivors per image) even a bitmask built on every SM costs 28 M pair
-// tests per image.  The NMS is therefore three kernels, and the bitmask is SPATIALLY indexed:
-//   k7_sort_kernel   per image: survivor ranks (bitmap prefix), key sort by score (= the visiting
-//                    order "rank"), then a second sort of the ranked boxes by (area class, x1) (=
-//                    the "spatial index" p) with a summary (min x1, max x2, min/max area) of every
-//                    block of 64 consecutive boxes;
-//   k7_mask_kernel   grid (G, B): for every pair of 64-blocks that the summaries cannot rule out
-//                    (x ranges overlap and the areas are within 1/thr of each other - IoU <= the
-//                    area ratio), the 64 x 64 pair tests; row p gets the word of bits q "box q
-//                    overlaps p above thr AND ranks before p".  Only non-zero words are written, each
-//                    flagged in a per-row summary, so the n x n/64 matrix is never initialised or read
-//                    as a whole;
-//   k7_resolve_kernel  one CTA per image: greedy NMS as a parallel fixed point over those words.
-// Which boxes share a 64-bit word is irrelevant to the result: every bit still says "a higher
-// scored box overlaps me", so the kept set is exactly torchvision.ops.nms's.  Images with more
-// survivors than the workspace's cap are served by k7_fallback_image (chunked, one CTA) inside k7_resolve_kernel.
-#define K7_SORT_MAX 16384                       // largest cap: 128 KB of keys in shared memory
-#define K7_NZW_MAX (K7_SORT_MAX / 64 / 64)      // u64 words of the per-row summary
-#define K7_CELLS_MAX 4096                       // grid cells of the spatial order, all area binades together
+// Round-1 design: one CTA per image ranked and ordered the survivors (k7_sort_kernel), a bitmask kernel
+// tested pairs of 64-box blocks that coarse summaries could not rule out, one CTA per image resolved the
+// bit matrix.  ncu (profiles/r4a, r3c): at 8 images per GPU (a sharded EfficientDet-D7 batch) the two
+// one-CTA-per-image kernels ran for 146 us on 8 of 148 SMs; at 256 small dense images (KSevenDet
+// thermal) the block summaries ruled out next to nothing and the bitmask kernel did 2 M pair tests per
+// image for ~60 k that matter.  Round 2: every stage runs on all SMs and work follows the boxes:
+//   k7_nms_chunksort_kernel  grid (chunks, B): a CTA sorts 2048 of the image's keys (score descending,
+//                            anchor ascending) in shared memory; bounds of the box centres (atomics);
+//   k7_nms_rank_kernel       the rank of a key = its index in its chunk + its lower bound in every other
+//                            sorted chunk (keys are unique) - a merge by ranking, no serial step; the box
+//                            goes to its rank; its CELL on a uniform grid chosen by the binade of its area
+//                            (cell size ~ the box size) becomes the next sort key;
+//   k7_nms_cellorder_kernel  the same chunk sort + ranking on (cell, rank) keys: boxes of a cell end up
+//                            contiguous and in rank order, a table holds each cell's [start, end);
+//   k7_nms_pairs_kernel      a THREAD per box: IoU > thr needs overlap > thr * own extent in x and in y and
+//                            areas within 1/thr of each other, so the partners of a box lie in the cells
+//                            within (0.5 - t + 0.5/t) own extents of its centre, in the grids of the
+//                            neighbouring binades; candidates ranked before the box are tested with
+//                            torchvision's arithmetic and every hit is an EDGE (box, suppressor);
+//   k7_nms_resolve_kernel    one CTA per image: greedy NMS as a fixed point over the edges.
+// Work is proportional to the pairs that can overlap; nothing of size n^2 exists any more (the round-1
+// bit matrix took cap^2/8 bytes per image, 4 GB per batch).  The kept set is exactly torchvision.ops.nms's:
+// an edge says "a higher ranked box overlaps me above thr", which is all the greedy rule looks at.
+// Images with more survivors than the workspace's cap, more edges than its edge list, or a threshold
+// below K7_GRID_MIN_THR are served by k7_fallback_image (chunked, one CTA) inside the resolve kernel.
+#define K7_SORT_MAX 16384                       // largest cap
+#define K7_NMS_CH 2048                          // keys per chunk CTA
+#define K7_NMS_G (K7_SORT_MAX / K7_NMS_CH)      // chunks per image at most
+#define K7_GRID_EMIN 6                          // classes: binade of the area, clamped to [2^6, 2^21)
+#define K7_GRID_EMAX 20
+#define K7_GRID_NCLS (K7_GRID_EMAX - K7_GRID_EMIN + 1)
+#define K7_GRID_SIDE 32                         // a class's grid has at most 32 x 32 cells
+#define K7_GRID_CELLS (K7_GRID_NCLS * K7_GRID_SIDE * K7_GRID_SIDE)
+#define K7_GRID_MIN_THR 0.05f
+#define K7_EDGE_PER_BOX 16                      // edge list: K7_EDGE_PER_BOX * cap entries per image
 
-// upper bound on survivors per image the multi-SM path is sized for (multiple of 64)
+// upper bound on survivors per image the multi-SM path is sized for (multiple of K7_NMS_CH)
 static int k7_nms_cap(int B, int n_max) {
-    long long cap = ((long long)n_max + 63) / 64 * 64;
+    (void)B;
+    long long cap = ((long long)n_max + K7_NMS_CH - 1) / K7_NMS_CH * K7_NMS_CH;
     if (cap > K7_SORT_MAX) cap = K7_SORT_MAX;
-    // the bitmask is cap^2/8 bytes per image (sparsely touched): keep the batch under 4 GB
-    const double budget = 4.0 * 1024 * 1024 * 1024;
-    while (cap > 2048 && (double)cap * (double)cap / 8.0 * (double)B > budget) cap -= 64;
     return (int)cap;
 }
 
-// Per image: the survivor list is born here.  The score kernel only marked survivors in a bitmap
-// (and left score / label / box by anchor id); this kernel takes the exclusive popcount prefix of
-// the bitmap (= the index torchvision.ops.nms would return for each survivor), turns every set bit
-// into a 64-bit key (score descending | anchor ascending) and sorts.
-//   bits == nullptr: stand-alone NMS, keys0 already holds surv_count[b] keys.
-// Outputs: surv_count[b]; keys1 = keys in rank order; sbox / srank / blk / nz in spatial order;
-// nsel[b] = survivors the mask/resolve kernels must process, or -1 when the image has more than
-// `cap` of them (then its unsorted keys are left in keys0 for the fallback).
-__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_sort_kernel(int A, int W32, int pre_topk, int cap, int32_t* __restrict__ surv_count, const uint32_t* __restrict__ bits,
-               int32_t* __restrict__ wprefix, const float* __restrict__ score_ws, uint64_t* __restrict__ keys0,
-               uint64_t* __restrict__ keys1, const float4* __restrict__ box_ws, float4* __restrict__ sbox,
-               int32_t* __restrict__ srank, float4* __restrict__ blk, unsigned long long* __restrict__ nz,
-               int32_t* __restrict__ nsel, int32_t* __restrict__ work, const int32_t* __restrict__ label_ws,
-               int32_t* __restrict__ slabel, float4* __restrict__ rbox) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned long long* sk = reinterpret_cast<unsigned long long*>(smem_raw);
-    __shared__ unsigned int s_wtot[32];
-    __shared__ float4 s_wsum[32];
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const size_t ob = (size_t)b * A;
-    k7_pdl_trigger();   // the mask kernel's CTAs may take their places
-    k7_pdl_wait();      // the score kernel's records
-    int n_all;
-    if (bits) {
-        // Survivor ranks and keys.  A thread owns a contiguous chunk of the image's bitmap words:
-        // one block scan gives every chunk its first rank.  The first walk over the bits also
-        // prefetches what the gathers below will want (score and box by anchor id; the score
-        // kernel wrote them long ago, most lines have left L2).
-        const int chunk = (W32 + K7_NMS_THREADS - 1) / K7_NMS_THREADS;
-        const int w_lo = min(tid * chunk, W32), w_hi = min(w_lo + chunk, W32);
-        const uint32_t* brow = bits + (size_t)b * W32;
-        int cnt = 0;
-        for (int w = w_lo; w < w_hi; w += 4) {   // four words in flight (a thread's chunk is not coalesced)
-            uint32_t wd[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) wd[u] = (w + u < w_hi) ? brow[w + u] : 0u;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                uint32_t word = wd[u];
-                cnt += __popc(word);
-                while (word) {
-                    const int a = ((w + u) << 5) + __ffs(word) - 1;
-                    word &= word - 1;
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(score_ws + ob + a));
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(box_ws + ob + a));
-                }
-            }
-        }
-        int inc = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) s_wtot[warp] = (unsigned)inc;
-        __syncthreads();
-        int slot = inc - cnt;
-        n_all = 0;
-        for (int k = 0; k < K7_NMS_THREADS / 32; ++k) {
-            const int t = (int)s_wtot[k];
-            if (k < warp) slot += t;
-            n_all += t;
-        }
-        if (tid == 0) surv_count[b] = n_all;
-        const bool small_ = n_all <= cap;
-        // the anchor id of every set bit at its rank: shared memory (small image) or keys0 (fallback image)
-        for (int w = w_lo; w < w_hi; w += 4) {
-            uint32_t wd[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) wd[u] = (w + u < w_hi) ? brow[w + u] : 0u;
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (w + u >= w_hi) break;
-                uint32_t word = wd[u];
-                wprefix[(size_t)b * W32 + w + u] = slot;
-                while (word) {
-                    const uint64_t a = (uint64_t)(((w + u) << 5) + __ffs(word) - 1);
-                    word &= word - 1;
-                    if (small_) sk[slot] = a; else keys0[ob + slot] = a;
-                    ++slot;
-                }
-            }
-        }
-        __syncthreads();   // also: s_wtot is reused below
-        // keys, every thread the same number of them with four score gathers in flight (walking the
-        // bits and gathering in one loop left the whole CTA waiting for the thread with most bits)
-        for (int i0 = 0; i0 < n_all; i0 += 4 * K7_NMS_THREADS) {
-            uint32_t a[4];
-            float sc[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = i0 + u * K7_NMS_THREADS + tid;
-                if (i < n_all) {
-                    a[u] = (uint32_t)(small_ ? sk[i] : keys0[ob + i]);
-                    sc[u] = score_ws[ob + a[u]];
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int i = i0 + u * K7_NMS_THREADS + tid;
-                if (i < n_all) {
-                    const uint64_t key = ((uint64_t)k7_score_key_desc(sc[u]) << 32) | a[u];
-                    if (small_) sk[i] = key; else keys0[ob + i] = key;
-                }
-            }
-        }
-    } else {
-        n_all = surv_count[b];
-    }
-    const bool small = n_all <= cap;
-    int N = k7_bitonic_size(n_all);
-    if (bits) {
-        if (small)
-            for (int i = n_all + tid; i < N; i += K7_NMS_THREADS) sk[i] = ~0ull;
-    } else if (small) {
-        for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < n_all) ? keys0[ob + i] : ~0ull;
-    }
-    if (!small) {
-        if (tid == 0) nsel[b] = -1;
-        return;
-    }
-    __syncthreads();
-    k7_bitonic_sort_smem(sk, N);   // ends with a barrier
-    int n = n_all;
-    if (pre_topk > 0 && n > pre_topk) n = pre_topk;
-    if (tid == 0) nsel[b] = n;
+// monotone map float -> uint32 for atomicMax; 0 is below every float (the memset value)
+__device__ __forceinline__ unsigned int k7_f2ord(float f) {
+    const unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float k7_ord2f(unsigned int o) {
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
 
-    // ---- spatial order: boxes of one area binade, binned on a grid whose cells hold ~16 of them,
-    // cells visited row by row in alternating direction (consecutive cells always touch).  Any
-    // order gives the same NMS result; this one makes 64 consecutive boxes neighbours in the image
-    // (about four cells in a row), so most pairs of 64-blocks are ruled out by their summaries in
-    // k7_mask_kernel.
-    // The boxes are gathered by anchor id ONCE (four independent loads in flight per thread) and
-    // left in rank order in `rbox`; what the binning needs of a box - x1, y1 (28 bits each are
-    // plenty for a cell index) and the binade of its area - replaces its key in sk[].
-    __shared__ int s_cls[256], s_base[257], s_g[256];
-    __shared__ int s_cell[K7_CELLS_MAX + 1];
-    __shared__ float s_bnd[4];
-    if (tid < 256) s_cls[tid] = 0;
-    for (int c = tid; c <= K7_CELLS_MAX; c += K7_NMS_THREADS) s_cell[c] = 0;
-    __syncthreads();
-    float bx0 = 3.0e38f, bx1 = -3.0e38f, by0 = 3.0e38f, by1 = -3.0e38f;
-    for (int i0 = 0; i0 < n; i0 += 4 * K7_NMS_THREADS) {
-        uint64_t key[4];
-        float4 bx[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int i = i0 + u * K7_NMS_THREADS + tid;
-            if (i < n) {
-                key[u] = sk[i];
-                bx[u] = __ldg(box_ws + ob + (uint32_t)(key[u] & 0xffffffffull));
+// The grids of an image, derived by every kernel from the image's bounds in the same way.
+struct K7Grid {
+    float ox, oy;
+    float inv_cw[K7_GRID_NCLS], inv_ch[K7_GRID_NCLS];
+    int gx[K7_GRID_NCLS], gy[K7_GRID_NCLS], off[K7_GRID_NCLS];
+};
+// bounds: {max cx, max -cx, max cy, max -cy} as k7_f2ord values.  Called by one thread.
+__device__ void k7_grid_setup(const unsigned int* __restrict__ bounds, K7Grid& g) {
+    float x1 = 0.f, x0 = 0.f, y1 = 0.f, y0 = 0.f;
+    if (bounds[0] && bounds[1] && bounds[2] && bounds[3]) {
+        x1 = k7_ord2f(bounds[0]);
+        x0 = -k7_ord2f(bounds[1]);
+        y1 = k7_ord2f(bounds[2]);
+        y0 = -k7_ord2f(bounds[3]);
+    }
+    const float ex = fmaxf(x1 - x0, 1e-3f), ey = fmaxf(y1 - y0, 1e-3f);
+    g.ox = x0;
+    g.oy = y0;
+    int off = 0;
+    for (int c = 0; c < K7_GRID_NCLS; ++c) {
+        const float s = exp2f(0.5f * (float)(K7_GRID_EMIN + c + 1));   // ~ the extent of a box of this class
+        const int gx = max(1, min(K7_GRID_SIDE, (int)ceilf(ex / s)));
+        const int gy = max(1, min(K7_GRID_SIDE, (int)ceilf(ey / s)));
+        g.gx[c] = gx;
+        g.gy[c] = gy;
+        g.inv_cw[c] = (float)gx / ex;
+        g.inv_ch[c] = (float)gy / ey;
+        g.off[c] = off;
+        off += gx * gy;
+    }
+}
+__device__ __forceinline__ int k7_grid_class(float area) {   // area > 0, finite
+    const int e = (int)((__float_as_uint(area) >> 23) & 0xffu) - 127;
+    return max(0, min(K7_GRID_NCLS - 1, e - K7_GRID_EMIN));
+}
+__device__ __forceinline__ bool k7_box_live(const float4 b, float& w, float& h, float& area) {
+    w = K7_FSUB(b.z, b.x);
+    h = K7_FSUB(b.w, b.y);
+    area = K7_FMUL(w, h);
+    // a box with an empty or non-finite extent never suppresses and is never suppressed (torchvision: overlap 0 or NaN)
+    return (w > 0.0f) && (h > 0.0f) && (area > 0.0f) && (area < 3.0e38f) && (fabsf(b.x) < 1.0e18f) && (fabsf(b.y) < 1.0e18f);
+}
+
+// lower bound of `key` in sorted keys[0..n)
+__device__ __forceinline__ int k7_lower_bound(const uint64_t* __restrict__ keys, int n, unsigned long long key) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((unsigned long long)__ldcg(keys + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+struct K7NmsArgs {
+    int A, cap, pre_topk, class_aware;
+    float thr;
+    const int32_t* surv_count;     // [B] survivors
+    uint64_t* keys0;               // [B][A] survivor keys, in arrival order
+    uint64_t* keysC;               // [B][cap] chunk-sorted keys
+    uint64_t* keys1;               // [B][A] keys in rank order
+    const float4* box_ws;          // [B][A] boxes by anchor id
+    const int32_t* label_ws;       // [B][A] classes by anchor id
+    float4* rbox;                  // [B][cap] boxes in rank order
+    unsigned int* bounds;          // [B][4]
+    int32_t* nsel;                 // [B] boxes in play (after pre_topk), -1: fallback image
+    int32_t* ccnt;                 // [B][K7_NMS_G] live boxes per chunk of the cell sort
+    uint64_t* ckeyC;               // [B][cap] chunk-sorted (cell, rank) keys
+    float4* cbox;                  // [B][cap] boxes in cell order
+    int32_t* crank;                // [B][cap] rank of the box at each cell-order index
+    int32_t* clabel;               // [B][cap] class of the box at each cell-order index (class-aware NMS)
+    uint2* ctab;                   // [B][K7_GRID_CELLS] {cap - first index, last index + 1} of each cell, 0 = empty
+    int32_t* pend;                 // [B][cap] suppressors of each box, by rank
+    unsigned int* edges;           // [B][ecap] rank << 16 | suppressor rank
+    int32_t* nedge;                // [B]
+    int ecap;
+};
+
+// ---- chunk sort of the score keys + bounds of the live boxes
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_chunksort_kernel(const __grid_constant__ K7NmsArgs P) {
+    __shared__ unsigned long long sk[K7_NMS_CH];
+    __shared__ unsigned int s_b[4];
+    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    k7_pdl_trigger();
+    k7_pdl_wait();      // the score kernel's keys
+    const int n_all = P.surv_count[b];
+    const bool small = n_all <= P.cap && P.thr >= K7_GRID_MIN_THR;
+    if (c == 0 && tid == 0) P.nsel[b] = small ? ((P.pre_topk > 0 && n_all > P.pre_topk) ? P.pre_topk : n_all) : -1;
+    if (!small) return;
+    const int m = min(K7_NMS_CH, n_all - c * K7_NMS_CH);
+    if (m <= 0) return;
+    const size_t ob = (size_t)b * P.A;
+    if (tid < 4) s_b[tid] = 0u;
+    const int N = k7_bitonic_size(m);
+    float mx = -3.0e38f, nx = -3.0e38f, my = -3.0e38f, ny = -3.0e38f;
+    for (int i = tid; i < N; i += K7_NMS_THREADS) {
+        unsigned long long key = ~0ull;
+        if (i < m) {
+            key = P.keys0[ob + (size_t)c * K7_NMS_CH + i];
+            const float4 bx = __ldg(P.box_ws + ob + (uint32_t)(key & 0xffffffffull));
+            float w, h, ar;
+            if (k7_box_live(bx, w, h, ar)) {
+                const float cx = 0.5f * (bx.x + bx.z), cy = 0.5f * (bx.y + bx.w);
+                mx = fmaxf(mx, cx); nx = fmaxf(nx, -cx); my = fmaxf(my, cy); ny = fmaxf(ny, -cy);
             }
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int i = i0 + u * K7_NMS_THREADS + tid;
-            if (i < n) {
-                keys1[ob + i] = key[u];
-                rbox[ob + i] = bx[u];
-                const float area = k7_area(bx[u].x, bx[u].y, bx[u].z, bx[u].w);
-                const unsigned c8 = (__float_as_uint(fmaxf(area, 0.0f)) >> 23) & 0xffu;   // binade of the area
-                atomicAdd(&s_cls[c8], 1);
-                bx0 = fminf(bx0, bx[u].x); bx1 = fmaxf(bx1, bx[u].x);
-                by0 = fminf(by0, bx[u].y); by1 = fmaxf(by1, bx[u].y);
-                sk[i] = ((unsigned long long)(__float_as_uint(bx[u].x) & 0xfffffff0u) << 32) |
-                        ((unsigned long long)(__float_as_uint(bx[u].y) & 0xfffffff0u) << 4) | c8;
-            }
-        }
+        sk[i] = key;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
-        bx1 = fmaxf(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
-        by0 = fminf(by0, __shfl_xor_sync(0xffffffffu, by0, o));
-        by1 = fmaxf(by1, __shfl_xor_sync(0xffffffffu, by1, o));
-    }
-    if (lane == 0) s_wsum[warp] = make_float4(bx0, bx1, by0, by1);
-    __syncthreads();
-    if (warp == 0) {
-        float4 v = s_wsum[lane];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            v.x = fminf(v.x, __shfl_xor_sync(0xffffffffu, v.x, o));
-            v.y = fmaxf(v.y, __shfl_xor_sync(0xffffffffu, v.y, o));
-            v.z = fminf(v.z, __shfl_xor_sync(0xffffffffu, v.z, o));
-            v.w = fmaxf(v.w, __shfl_xor_sync(0xffffffffu, v.w, o));
-        }
-        if (lane == 0) {
-            s_bnd[0] = v.x;
-            s_bnd[1] = (v.y > v.x) ? 1.0f / (v.y - v.x) : 0.0f;
-            s_bnd[2] = v.z;
-            s_bnd[3] = (v.w > v.z) ? 1.0f / (v.w - v.z) : 0.0f;
-        }
-    }
-    // grid side per binade: g*g cells of ~16 boxes; sum of g*g <= n/16 + 2*sqrt(16n) + 256 <= K7_CELLS_MAX
-    if (tid < 256) {
-        const int c = s_cls[tid];
-        int g = 0;
-        if (c > 0) {
-            g = (int)ceilf(sqrtf((float)c * (1.0f / 16.0f)));
-            g = max(1, min(g, 32));
-        }
-        s_g[tid] = g;
-        int inc = g * g;
-        const int v = inc;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        s_base[tid] = inc - v;
-        if (lane == 31) s_wtot[warp] = (unsigned)inc;
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nx = fmaxf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
+        my = fmaxf(my, __shfl_xor_sync(0xffffffffu, my, o));
+        ny = fmaxf(ny, __shfl_xor_sync(0xffffffffu, ny, o));
     }
     __syncthreads();
-    if (tid < 256) {
-        int off = 0;
-        for (int w = 0; w < warp; ++w) off += (int)s_wtot[w];
-        s_base[tid] += off;
+    if (lane == 0 && mx > -3.0e38f) {
+        atomicMax(&s_b[0], k7_f2ord(mx)); atomicMax(&s_b[1], k7_f2ord(nx));
+        atomicMax(&s_b[2], k7_f2ord(my)); atomicMax(&s_b[3], k7_f2ord(ny));
+    }
+    k7_bitonic_sort_smem(sk, N);   // begins and ends with the block in step
+    if (tid < 4 && s_b[tid]) atomicMax(P.bounds + 4 * b + tid, s_b[tid]);
+    for (int i = tid; i < m; i += K7_NMS_THREADS) P.keysC[(size_t)b * P.cap + (size_t)c * K7_NMS_CH + i] = sk[i];
+}
+
+// ---- ranks, boxes in rank order, (cell, rank) keys sorted per chunk
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_rank_kernel(const __grid_constant__ K7NmsArgs P) {
+    __shared__ unsigned long long sk[K7_NMS_CH];
+    __shared__ K7Grid s_g;
+    __shared__ int s_live;
+    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x;
+    k7_pdl_trigger();
+    k7_pdl_wait();
+    const int n = P.nsel[b];
+    if (n < 0) return;
+    const int n_all = P.surv_count[b];
+    const int m = min(K7_NMS_CH, n_all - c * K7_NMS_CH);
+    if (m <= 0) {
+        if (tid == 0) P.ccnt[b * K7_NMS_G + c] = 0;
+        return;
+    }
+    if (tid == 0) {
+        k7_grid_setup(P.bounds + 4 * b, s_g);
+        s_live = 0;
     }
     __syncthreads();
-    // cell of every box (kept in sk[i]) and the cell histogram
-    for (int i = tid; i < n; i += K7_NMS_THREADS) {
-        const unsigned long long v = sk[i];
-        const float x = __uint_as_float((uint32_t)(v >> 32) & 0xfffffff0u);
-        const float y = __uint_as_float((uint32_t)(v >> 4) & 0xfffffff0u);
-        const int c8 = (int)(v & 0xffull);
-        const int g = s_g[c8];
-        int cx = (int)((x - s_bnd[0]) * s_bnd[1] * (float)g), cy = (int)((y - s_bnd[2]) * s_bnd[3] * (float)g);
-        cx = max(0, min(cx, g - 1));   // also sends NaN to cell 0
-        cy = max(0, min(cy, g - 1));
-        if (cy & 1) cx = g - 1 - cx;   // odd rows run backwards
-        const int cell = min(s_base[c8] + cy * g + cx, K7_CELLS_MAX - 1);
-        sk[i] = (unsigned long long)cell;
-        atomicAdd(&s_cell[cell], 1);
-    }
-    __syncthreads();
-    // exclusive prefix over the cells (K7_CELLS_MAX = 4 * 1024 threads: four cells per thread)
-    {
-        static_assert(K7_CELLS_MAX == 4 * K7_NMS_THREADS, "four cells per thread");
-        int c[4], inc = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            c[k] = s_cell[4 * tid + k];
-            inc += c[k];
-        }
-        const int v = inc;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) s_wtot[warp] = (unsigned)inc;
-        __syncthreads();
-        int run = inc - v;
-        for (int w = 0; w < warp; ++w) run += (int)s_wtot[w];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            s_cell[4 * tid + k] = run;
-            run += c[k];
-        }
-    }
-    __syncthreads();
-    // scatter: the order inside a cell is whatever the atomics give (it does not affect the result)
-    const size_t oc = (size_t)b * cap;
-    const int nzw = (cap / 64 + 63) / 64;
-    for (int i0 = 0; i0 < n; i0 += 4 * K7_NMS_THREADS) {
-        float4 bx[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int i = i0 + u * K7_NMS_THREADS + tid;
-            if (i < n) bx[u] = __ldcg(rbox + ob + i);   // written above by this thread
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int i = i0 + u * K7_NMS_THREADS + tid;
-            if (i < n) {
-                const int p = atomicAdd(&s_cell[(int)sk[i]], 1);
-                sbox[oc + p] = bx[u];
-                srank[oc + p] = i;
-                if (slabel)   // class-aware NMS
-                    slabel[oc + p] = __ldg(label_ws + ob + (uint32_t)(__ldcg(keys1 + ob + i) & 0xffffffffull));
+    const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
+    const int nch = (n_all + K7_NMS_CH - 1) / K7_NMS_CH;
+    const int N = k7_bitonic_size(m);
+    int live = 0;
+    for (int i = tid; i < N; i += K7_NMS_THREADS) {
+        unsigned long long ck = ~0ull;
+        if (i < m) {
+            const unsigned long long key = __ldcg(P.keysC + oc + (size_t)c * K7_NMS_CH + i);
+            int rank = i;
+            for (int c2 = 0; c2 < nch; ++c2) {
+                if (c2 == c) continue;
+                const int m2 = min(K7_NMS_CH, n_all - c2 * K7_NMS_CH);
+                rank += k7_lower_bound(P.keysC + oc + (size_t)c2 * K7_NMS_CH, m2, key);
+            }
+            if (rank < n) {   // pre_nms_topk drops the rest
+                const float4 bx = __ldg(P.box_ws + ob + (uint32_t)(key & 0xffffffffull));
+                P.keys1[ob + rank] = key;
+                P.rbox[oc + rank] = bx;
+                float w, h, ar;
+                if (k7_box_live(bx, w, h, ar)) {
+                    const int cl = k7_grid_class(ar);
+                    const float cx = 0.5f * (bx.x + bx.z), cy = 0.5f * (bx.y + bx.w);
+                    const int ix = max(0, min(s_g.gx[cl] - 1, (int)((cx - s_g.ox) * s_g.inv_cw[cl])));
+                    const int iy = max(0, min(s_g.gy[cl] - 1, (int)((cy - s_g.oy) * s_g.inv_ch[cl])));
+                    ck = ((unsigned long long)(unsigned int)(s_g.off[cl] + iy * s_g.gx[cl] + ix) << 32) | (unsigned int)rank;
+                    ++live;
+                } else {
+                    P.pend[oc + rank] = 0;   // in play, but it has no partner: kept
+                }
             }
         }
+        sk[i] = ck;
     }
-    {   // flags of the rows' non-zero words: only column-blocks < ceil(n/64) can be flagged
-        const int nzu = ((n + 63) / 64 + 63) / 64;
-        for (int i = tid; i < n * nzu; i += K7_NMS_THREADS) nz[(oc + i / nzu) * nzw + i % nzu] = 0ull;
-    }
-    if (tid == 0) work[b] = 0;
+    if (live) atomicAdd(&s_live, live);
     __syncthreads();
+    k7_bitonic_sort_smem(sk, N);
+    const int nl = s_live;   // the live keys sort before the ~0 fillers
+    for (int i = tid; i < nl; i += K7_NMS_THREADS) P.ckeyC[oc + (size_t)c * K7_NMS_CH + i] = sk[i];
+    if (tid == 0) P.ccnt[b * K7_NMS_G + c] = nl;
+}
 
-    // ---- summaries of every 32 consecutive boxes: x range, y range, area range
-    const int n32 = (n + 31) & ~31;
-    for (int p0 = 0; p0 < n32; p0 += K7_NMS_THREADS) {
-        const int p = p0 + tid;
-        if (p0 + (warp << 5) >= n32) break;   // warp-uniform
-        float x1 = 3.0e38f, x2 = -3.0e38f, y1 = 3.0e38f, y2 = -3.0e38f, amin = 3.0e38f, amax = -3.0e38f;
-        if (p < n) {
-            const float4 bx = __ldcg(sbox + oc + p);   // written by this CTA before the barrier
-            const float area = k7_area(bx.x, bx.y, bx.z, bx.w);
-            x1 = bx.x; y1 = bx.y; x2 = bx.z; y2 = bx.w; amin = area; amax = area;   // a NaN drops out of fminf/fmaxf
-        }
+// ---- boxes in cell order + the cell table
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_cellorder_kernel(const __grid_constant__ K7NmsArgs P) {
+    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x;
+    k7_pdl_trigger();
+    k7_pdl_wait();
+    if (P.nsel[b] < 0) return;
+    const int m = P.ccnt[b * K7_NMS_G + c];
+    if (m <= 0) return;
+    const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
+    int cnt[K7_NMS_G];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            x1 = fminf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
-            x2 = fmaxf(x2, __shfl_xor_sync(0xffffffffu, x2, o));
-            y1 = fminf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
-            y2 = fmaxf(y2, __shfl_xor_sync(0xffffffffu, y2, o));
-            amin = fminf(amin, __shfl_xor_sync(0xffffffffu, amin, o));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        }
-        if (lane == 0) {
-            float4* o = blk + 2 * ((size_t)b * (cap / 32) + (p >> 5));
-            o[0] = make_float4(x1, x2, y1, y2);
-            o[1] = make_float4(amin, amax, 0.0f, 0.0f);
-        }
+    for (int c2 = 0; c2 < K7_NMS_G; ++c2) cnt[c2] = P.ccnt[b * K7_NMS_G + c2];
+    for (int i = tid; i < m; i += K7_NMS_THREADS) {
+        const unsigned long long ck = __ldcg(P.ckeyC + oc + (size_t)c * K7_NMS_CH + i);
+        int p = i;
+#pragma unroll
+        for (int c2 = 0; c2 < K7_NMS_G; ++c2)
+            if (c2 != c && cnt[c2] > 0) p += k7_lower_bound(P.ckeyC + oc + (size_t)c2 * K7_NMS_CH, cnt[c2], ck);
+        const int rank = (int)(unsigned int)(ck & 0xffffffffull);
+        const unsigned int cell = (unsigned int)(ck >> 32);
+        P.cbox[oc + p] = __ldcg(P.rbox + oc + rank);
+        P.crank[oc + p] = rank;
+        if (P.class_aware) P.clabel[oc + p] = __ldg(P.label_ws + ob + (uint32_t)(__ldcg(P.keys1 + ob + rank) & 0xffffffffull));
+        uint2* t = P.ctab + (size_t)b * K7_GRID_CELLS + cell;
+        atomicMax(&t->x, (unsigned int)(P.cap - p));   // first index of the cell, as cap - index
+        atomicMax(&t->y, (unsigned int)(p + 1));       // last index + 1
     }
 }
 
-// The exact decision of torchvision.ops.nms is fl(inter / (area_i + area_j - inter)) > thr.  The
-// 64 x 64 pair loop only runs a cheap FILTER that no suppressed pair can fail:
+// ---- pair tests.  The exact decision of torchvision.ops.nms is fl(inter / (area_i + area_j - inter)) > thr.
+// Candidates first meet a cheap FILTER that no suppressed pair can fail:
 //     w > 0, h > 0  and  inter > fl(c*area_i) + fl(c*area_j),   c = thr/(1+thr) * (1 - 1e-5).
 // Proof: a suppressed pair has w, h > 0 (else inter is 0 or NaN and the quotient is not > thr >= 0),
 // hence a positive union u, and fl(inter/u) > thr gives inter > thr*u*(1 - 2^-24), i.e.
 // inter*(1 + thr') > thr'*(area_i + area_j)*(1 - 2^-23) with thr' = thr*(1 - 2^-23); the float32
 // roundings of the two products and the sum are below 2^-22 relative, far inside the 1e-5 margin.
-// Pairs that pass (about 1 in 50 overlapping ones) are re-tested exactly, division included.
+// Pairs that pass are re-tested exactly, division included.
 __device__ __forceinline__ bool k7_nms_filter(const K7Box& a, float ca, const float4 b, float cb) {
     const float w = K7_FSUB(fminf(a.x2, b.z), fmaxf(a.x1, b.x));
     const float h = K7_FSUB(fminf(a.y2, b.w), fmaxf(a.y1, b.y));
@@ -1484,381 +1454,181 @@ __device__ __forceinline__ bool k7_nms_suppress_exact(const K7Box& a, float area
     return k7_nms_suppress(a, area_a, o, area_b, thr);
 }
 
-// Summary test of two sets of boxes: can they hold a pair with IoU > thr?  Exact in the "no"
-// direction: (x, y) if min x1 of one set >= max x2 of the other (same for y), every pair has a
-// non-positive intersection width -> overlap 0; (area) a pair with intersection > 0 has
-// IoU <= min(area)/max(area), so sets whose areas differ by more than thr (1e-4 margin against
-// float32 rounding) hold no pair above thr.  c_area == 0 (thr == 0) disables the area test.
-struct K7Sum {
-    float4 r;   // min x1, max x2, min y1, max y2
-    float4 a;   // min area, max area
-};
-__device__ __forceinline__ K7Sum k7_sum_load(const float4* __restrict__ bs, int i32) {
-    K7Sum s;
-    s.r = __ldg(bs + 2 * i32);
-    s.a = __ldg(bs + 2 * i32 + 1);
-    return s;
-}
-__device__ __forceinline__ bool k7_sum_may_overlap(const K7Sum& p, const K7Sum& q, float c_area) {
-    return (q.r.x < p.r.y) && (p.r.x < q.r.y) && (q.r.z < p.r.w) && (p.r.z < q.r.w) &&
-           !(q.a.y < c_area * p.a.x) && !(p.a.y < c_area * q.a.x);
-}
-
-// A group of 64 threads (two warps) works on a row-block: thread t keeps box p = 64*rb + t in
-// registers.  Candidate column-blocks cb <= rb are found with the 32-box summaries (64 at a time,
-// one per thread, ballots); for every candidate the group stages the 64 column boxes in shared
-// memory and each warp runs its 32 x 32 sub-blocks that the summaries do not rule out: 32 or 64
-// filter tests per thread, exact re-test of the few pairs that pass.  Every unordered pair is
-// tested ONCE: an overlap found by thread p sets bit q in row p when q ranks before p, otherwise
-// bit p in row q (collected per column in shared memory and written by thread q afterwards).
-#define K7_MASK_THREADS 256
-#define K7_MASK_GROUPS (K7_MASK_THREADS / 64)
-__global__ void __launch_bounds__(K7_MASK_THREADS)
-k7_mask_kernel(float thr, int cap, const int32_t* __restrict__ nsel, const float4* __restrict__ sbox,
-               const int32_t* __restrict__ srank, const float4* __restrict__ blk, unsigned long long* __restrict__ nz,
-               unsigned long long* __restrict__ M, int32_t* __restrict__ work, const int32_t* __restrict__ slabel) {
-    __shared__ float4 cbox[K7_MASK_GROUPS][64];
-    __shared__ float carea[K7_MASK_GROUPS][64];
-    __shared__ int crank[K7_MASK_GROUPS][64];
-    __shared__ int clabel[K7_MASK_GROUPS][64];
-    __shared__ unsigned long long tword[K7_MASK_GROUPS][64];
-    __shared__ unsigned int cand[K7_MASK_GROUPS][2];
-    __shared__ int s_item[K7_MASK_GROUPS];
-    const int b = blockIdx.y;
+// Where the partners of box i can be.  IoU > t  =>  inter > t/(1+t) (A_i + A_j) and A_j > t A_i (inter <= A_j),
+// so inter > t A_i; with inter = iw * ih and ih <= h_i:  iw > t w_i, and in the same way ih > t h_i, iw > t w_j,
+// ih > t h_j.  From iw <= w_i:  w_j < w_i / t.  The centres then satisfy
+//     |cx_j - cx_i| < (w_i + w_j)/2 - iw < w_i (1/2 + 1/(2t) - t) =: k w_i      (and the same in y),
+// and the areas A_j in (t A_i, A_i / t).  All of it is evaluated with t lowered by 1e-4 relative and the radius
+// widened by 1e-2 px, against float32 roundings of 1e-7.
+#define K7_PAIRS_THREADS 256
+__global__ void __launch_bounds__(K7_PAIRS_THREADS)
+k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bound above */) {
+    __shared__ K7Grid s_g;
+    const int b = blockIdx.y, tid = threadIdx.x;
     k7_pdl_trigger();
-    k7_pdl_wait();      // k7_sort_kernel's spatial order
-    const int n = nsel[b];
-    if (n <= 0) return;
-    const int nb = (n + 63) >> 6, n32 = (n + 31) >> 5;
-    const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
-    const int grp = threadIdx.x >> 6, t = threadIdx.x & 63, lane = threadIdx.x & 31, half = t >> 5;
-    const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);   // filter constant, see k7_nms_filter
-    const float c_area = thr * (1.0f - 1e-4f);
-    const size_t oc = (size_t)b * cap;
-    const float4* bx = sbox + oc;
-    const float4* bs = blk + 2 * (size_t)b * (cap >> 5);
-    const int bar_id = 1 + grp;
-    // work item = (row-block, share of its candidate column-blocks), handed out by a per-image counter.
-    // At least two items per group of the image's CTAs: with few images per launch (a sharded
-    // batch) the row-blocks alone leave most SMs idle and the heavy ones become the tail.
-    int csplit = nb >= 64 ? 2 : (nb >= 16 ? 4 : 8);
-    if (nb >= 32) {
-        const int want = (2 * (int)gridDim.x * K7_MASK_GROUPS + nb - 1) / nb;
-        csplit = max(csplit, min(want, 16));
-    }
-    const int items = nb * csplit;
-    for (;;) {
-        if (t == 0) s_item[grp] = atomicAdd(work + b, 1);
-        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-        const int wi = s_item[grp];
-        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-        if (wi >= items) break;   // group-uniform
-        // heavy row-blocks (many column-blocks below them) first
-        const int rb = nb - 1 - wi / csplit, sub = wi % csplit;
-        int turn = 0, mine_turn = sub;
-        const int row = rb * 64 + t;
-        const bool rlive = row < n;
-        const float4 mb = rlive ? __ldg(bx + row) : make_float4(0.f, 0.f, 0.f, 0.f);
-        const K7Box me = {mb.x, mb.y, mb.z, mb.w};
-        const float marea = k7_area(mb.x, mb.y, mb.z, mb.w);
-        const float mca = K7_FMUL(c_flt, marea);
-        const int mrank = rlive ? __ldg(srank + oc + row) : -1;
-        const int mlabel = (slabel && rlive) ? __ldg(slabel + oc + row) : 0;
-        // summaries of the two halves of the row-block; rmine = the half this warp owns
-        const K7Sum r0 = k7_sum_load(bs, 2 * rb);
-        const bool has_r1 = 2 * rb + 1 < n32;
-        const K7Sum r1 = has_r1 ? k7_sum_load(bs, 2 * rb + 1) : r0;
-        const K7Sum rmine = half ? r1 : r0;
-        for (int c0 = 0; c0 <= rb; c0 += 64) {
-            // which of column-blocks c0..c0+63 (<= rb) can hold a pair above thr with this row-block?
-            const int cbt = c0 + t;
-            bool ok = false;
-            if (cbt <= rb) {
-                const K7Sum q0 = k7_sum_load(bs, 2 * cbt);
-                ok = k7_sum_may_overlap(r0, q0, c_area) || (has_r1 && k7_sum_may_overlap(r1, q0, c_area));
-                if (2 * cbt + 1 < n32) {
-                    const K7Sum q1 = k7_sum_load(bs, 2 * cbt + 1);
-                    ok = ok || k7_sum_may_overlap(r0, q1, c_area) || (has_r1 && k7_sum_may_overlap(r1, q1, c_area));
+    k7_pdl_wait();
+    if (P.nsel[b] < 0) return;
+    int nc = 0;
+#pragma unroll
+    for (int c2 = 0; c2 < K7_NMS_G; ++c2) nc += P.ccnt[b * K7_NMS_G + c2];
+    if ((int)(blockIdx.x * K7_PAIRS_THREADS) >= nc) return;
+    if (tid == 0) k7_grid_setup(P.bounds + 4 * b, s_g);
+    __syncthreads();
+    const int p = blockIdx.x * K7_PAIRS_THREADS + tid;
+    if (p >= nc) return;
+    const size_t oc = (size_t)b * P.cap;
+    const float4 mb = __ldcg(P.cbox + oc + p);
+    const int ri = __ldcg(P.crank + oc + p);
+    const int mlabel = P.class_aware ? __ldcg(P.clabel + oc + p) : 0;
+    const K7Box me = {mb.x, mb.y, mb.z, mb.w};
+    const float w = K7_FSUB(mb.z, mb.x), h = K7_FSUB(mb.w, mb.y), marea = K7_FMUL(w, h);
+    const float thr = P.thr, tl = thr * (1.0f - 1e-4f);
+    const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);
+    const float mca = K7_FMUL(c_flt, marea);
+    const float cx = 0.5f * (mb.x + mb.z), cy = 0.5f * (mb.y + mb.w);
+    const float rx = kq * w + 1e-2f, ry = kq * h + 1e-2f;
+    const int clo = k7_grid_class(fmaxf(marea * tl * (1.0f - 1e-5f), 1e-30f));
+    const int chi = k7_grid_class(fminf(marea / tl * (1.0f + 1e-5f), 3.0e38f));
+    const uint2* tab = P.ctab + (size_t)b * K7_GRID_CELLS;
+    unsigned int* edges = P.edges + (size_t)b * P.ecap;
+    int count = 0;
+    for (int cl = clo; cl <= chi; ++cl) {
+        const int gx = s_g.gx[cl], gy = s_g.gy[cl];
+        const float icw = s_g.inv_cw[cl], ich = s_g.inv_ch[cl];
+        const int x0 = max(0, min(gx - 1, (int)floorf((cx - rx - s_g.ox) * icw))), x1 = max(0, min(gx - 1, (int)floorf((cx + rx - s_g.ox) * icw)));
+        const int y0 = max(0, min(gy - 1, (int)floorf((cy - ry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((cy + ry - s_g.oy) * ich)));
+        for (int iy = y0; iy <= y1; ++iy) {
+            for (int ix = x0; ix <= x1; ++ix) {
+                const uint2 se = __ldcg(tab + s_g.off[cl] + iy * gx + ix);
+                if (se.y == 0u) continue;
+                const int q1 = (int)se.y;
+                for (int q = P.cap - (int)se.x; q < q1; ++q) {
+                    const int rj = __ldcg(P.crank + oc + q);
+                    if (rj >= ri) break;                     // a cell's boxes are in rank order: the rest ranks after me
+                    const float4 ob = __ldcg(P.cbox + oc + q);
+                    const float oarea = k7_area(ob.x, ob.y, ob.z, ob.w);
+                    if (!k7_nms_filter(me, mca, ob, K7_FMUL(c_flt, oarea))) continue;
+                    if (P.class_aware && __ldcg(P.clabel + oc + q) != mlabel) continue;
+                    if (!k7_nms_suppress_exact(me, marea, ob, oarea, thr)) continue;
+                    const int slot = atomicAdd(P.nedge + b, 1);
+                    if (slot < P.ecap) edges[slot] = ((unsigned int)ri << 16) | (unsigned int)rj;
+                    ++count;
                 }
             }
-            const unsigned bal = __ballot_sync(0xffffffffu, ok);
-            if (lane == 0) cand[grp][half] = bal;
-            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-            unsigned long long cm = (unsigned long long)cand[grp][0] | ((unsigned long long)cand[grp][1] << 32);
-            while (cm) {   // group-uniform
-                const int cb = c0 + __ffsll((long long)cm) - 1;
-                cm &= cm - 1ull;
-                if (turn++ != mine_turn) continue;   // every csplit-th candidate is this item's (no modulo in the loop)
-                mine_turn += csplit;
-                const int col = cb * 64 + t;
-                const bool diag = cb == rb;
-                asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // previous column-block fully consumed
-                if (col < n) {
-                    const float4 c = __ldg(bx + col);
-                    cbox[grp][t] = c;
-                    carea[grp][t] = K7_FMUL(c_flt, k7_area(c.x, c.y, c.z, c.w));
-                    crank[grp][t] = __ldg(srank + oc + col);
-                    clabel[grp][t] = slabel ? __ldg(slabel + oc + col) : 0;
-                }
-                tword[grp][t] = 0ull;
-                asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-                const int jend = min(64, n - cb * 64);
-                if (rlive && (!half || has_r1)) {
-                    uint32_t flo = 0u, fhi = 0u;   // pairs that pass the filter
-                    // warp-uniform: this warp's 32 rows against each half of the column-block
-                    if (k7_sum_may_overlap(rmine, k7_sum_load(bs, 2 * cb), c_area)) {
-                        const int je = min(32, jend);
-                        if (je == 32) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) flo |= 1u << j;
-                        } else {
-                            for (int j = 0; j < je; ++j)
-                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) flo |= 1u << j;
-                        }
-                    }
-                    if (jend > 32 && k7_sum_may_overlap(rmine, k7_sum_load(bs, 2 * cb + 1), c_area)) {
-                        if (jend == 64) {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j)
-                                if (k7_nms_filter(me, mca, cbox[grp][j + 32], carea[grp][j + 32])) fhi |= 1u << j;
-                        } else {
-                            for (int j = 32; j < jend; ++j)
-                                if (k7_nms_filter(me, mca, cbox[grp][j], carea[grp][j])) fhi |= 1u << (j - 32);
-                        }
-                    }
-                    unsigned long long f = (unsigned long long)flo | ((unsigned long long)fhi << 32);
-                    unsigned long long word = 0ull;
-                    while (f) {   // exact test; the box visited earlier suppresses the other one
-                        const int j = __ffsll((long long)f) - 1;
-                        f &= f - 1ull;
-                        const float4 c = cbox[grp][j];
-                        if (clabel[grp][j] != mlabel) continue;   // class-aware: other classes never suppress
-                        if (!k7_nms_suppress_exact(me, marea, c, k7_area(c.x, c.y, c.z, c.w), thr)) continue;
-                        if (crank[grp][j] < mrank)
-                            word |= 1ull << j;
-                        else if (!diag)   // in a diagonal block thread q meets this pair itself
-                            atomicOr(reinterpret_cast<unsigned int*>(&tword[grp][j]) + (t >> 5), 1u << (t & 31));   // native 32-bit ATOMS
-                    }
-                    if (word) {
-                        M[(oc + row) * nbw + cb] = word;
-                        atomicOr(nz + (oc + row) * nzw + (cb >> 6), 1ull << (cb & 63));
-                    }
-                }
-                if (!diag) {   // group-uniform: the transposed bits, one column box per thread
-                    asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-                    const unsigned long long tw = tword[grp][t];
-                    if (tw) {
-                        M[(oc + col) * nbw + rb] = tw;
-                        atomicOr(nz + (oc + col) * nzw + (rb >> 6), 1ull << (rb & 63));
-                    }
-                }
-            }
-            asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");   // cand[] is rewritten by the next round
         }
     }
+    P.pend[oc + ri] = count;
 }
 
-// Greedy NMS as a fixed point, one CTA per image.  Row p holds the boxes q that overlap box p
-// above the threshold and rank before it.  Box p is REMOVED as soon as one of them is known KEPT,
-// and KEPT as soon as all of them are known removed; the undecided box of lowest rank can always be
-// decided, so the iteration ends, and by induction over the rank its result is exactly the
-// sequential greedy answer of torchvision.ops.nms.  The kept/removed sets only grow, so threads may
-// read them while others update them; a round costs one barrier.  Dependency chains between
-// overlapping boxes are short, so a handful of rounds replace the n-step sequential scan; rows
-// without a flagged word (most) are kept in round 0 without touching the matrix.
+// ---- Greedy NMS as a fixed point over the edges, one CTA per image.  Box i is REMOVED as soon as one of
+// its suppressors (edges (i, j): j ranks before i and overlaps it above thr) is known KEPT, and KEPT as
+// soon as all of them are known removed; the undecided box of lowest rank can always be decided (all
+// its suppressors rank before it, hence are decided), so the iteration ends, and by induction over the
+// rank its result is exactly the sequential greedy answer of torchvision.ops.nms.  The kept / removed
+// sets only grow, so threads may read them while others update them; a round costs two barriers.
+// Rounds = longest dependency chain (2-3 on the bench inputs).  An edge whose suppressor was removed is
+// dead; the box's count of live edges drops, and at zero the box is kept.
 #define K7_RESOLVE_THREADS 1024
-#define K7_RESOLVE_PER (K7_SORT_MAX / K7_RESOLVE_THREADS)
-// set bit p of a bit set kept as u64 words in shared memory.  A 64-bit atomicOr on shared memory
-// is a compare-and-swap loop (ncu: 45 % of the old kernel's instructions, 64 threads fighting over
-// one word); the 32-bit form is one native ATOMS.OR on the half that holds the bit (little endian).
-__device__ __forceinline__ void k7_set_bit(unsigned long long* set, int p) {
-    atomicOr(reinterpret_cast<unsigned int*>(set) + (p >> 5), 1u << (p & 31));
-}
-// The flagged words of an image (index + 64 bits, 10 bytes) are staged ONCE in shared memory:
-// a round then costs shared-memory latency instead of two dependent trips to L2 per undecided
-// row (ncu at EfficientDet-D7: 77 us per image, all of it long-scoreboard and barrier stalls).
-// Images with more flagged words than this, or a row with more than 15 of them, iterate on
-// the matrix in global memory as before.
-#define K7_RESOLVE_LIST 12288
-#define K7_RESOLVE_LIST_BYTES (K7_RESOLVE_LIST * (sizeof(unsigned long long) + sizeof(unsigned short)))
-#define K7_RESOLVE_SMEM (K7_RESOLVE_LIST_BYTES > sizeof(K7SortNmsSmem) ? K7_RESOLVE_LIST_BYTES : sizeof(K7SortNmsSmem))
+#define K7_RESOLVE_EDGES 32768      // edges staged in shared memory; longer lists are walked in global memory
+#define K7_RESOLVE_SMEM_NEED (K7_RESOLVE_EDGES * sizeof(unsigned int) + K7_SORT_MAX * sizeof(int))
+#define K7_RESOLVE_SMEM (K7_RESOLVE_SMEM_NEED > sizeof(K7SortNmsSmem) ? K7_RESOLVE_SMEM_NEED : sizeof(K7SortNmsSmem))
+__device__ __forceinline__ void k7_set_bit32(unsigned int* set, int p) { atomicOr(set + (p >> 5), 1u << (p & 31)); }
+
 __global__ void __launch_bounds__(K7_RESOLVE_THREADS)
-k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel, const int32_t* __restrict__ surv_count,
-                  uint64_t* sorted_keys, const float4* __restrict__ sbox,
-                  const int32_t* __restrict__ srank, const unsigned long long* __restrict__ nz,
-                  const unsigned long long* __restrict__ M, uint64_t* __restrict__ kept_key, float4* __restrict__ kept_box,
-                  int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out, int64_t* __restrict__ keep_idx_out,
-                  float iou_thr, int pre_topk, uint64_t* keys0, const float4* __restrict__ box_ws,
-                  const int32_t* __restrict__ label_ws) {
-    constexpr int WMAX = K7_SORT_MAX / 64;
+k7_nms_resolve_kernel(const __grid_constant__ K7NmsArgs P, int max_det, uint64_t* __restrict__ kept_key,
+                      float4* __restrict__ kept_box, int32_t* __restrict__ kept_count, int32_t* __restrict__ counts_out,
+                      int64_t* __restrict__ keep_idx_out) {
+    constexpr int WMAX = K7_SORT_MAX / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    unsigned long long* s_l = reinterpret_cast<unsigned long long*>(smem_raw);
-    unsigned short* s_w = reinterpret_cast<unsigned short*>(s_l + K7_RESOLVE_LIST);
-    __shared__ unsigned long long s_kept[WMAX], s_rem[WMAX], s_krank[WMAX];
+    unsigned int* s_e = reinterpret_cast<unsigned int*>(smem_raw);
+    int* s_pend = reinterpret_cast<int*>(s_e + K7_RESOLVE_EDGES);
+    __shared__ unsigned int s_kept[WMAX], s_rem[WMAX];
     __shared__ int s_prefix[WMAX + 1];
-    __shared__ int s_wtot[32];
-    __shared__ int s_undecided;
+    __shared__ int s_open;
     const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     k7_pdl_trigger();
-    k7_pdl_wait();      // k7_mask_kernel's words
-    const int n = nsel[b];
-    if (n < 0) {   // more survivors than the multi-SM path is sized for
-        k7_fallback_image(b, A, iou_thr, pre_topk, max_det, surv_count, kept_count, keys0, sorted_keys, box_ws, kept_key,
-                          kept_box, counts_out, label_ws, *reinterpret_cast<K7SortNmsSmem*>(smem_raw));
+    k7_pdl_wait();
+    const int n = P.nsel[b];
+    const int E = n >= 0 ? P.nedge[b] : 0;
+    const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
+    if (n < 0 || E > P.ecap) {   // too many survivors / edges for the multi-SM path, or a tiny threshold
+        k7_fallback_image(b, P.A, P.thr, P.pre_topk, max_det, P.surv_count, kept_count, P.keys0, P.keys1, P.box_ws, kept_key,
+                          kept_box, counts_out, P.class_aware ? P.label_ws : nullptr, *reinterpret_cast<K7SortNmsSmem*>(smem_raw));
+        if (keep_idx_out) {
+            __syncthreads();
+            const int kc = kept_count[b];
+            for (int k = tid; k < kc; k += K7_RESOLVE_THREADS) keep_idx_out[k] = (int64_t)(uint32_t)(kept_key[ob + k] & 0xffffffffull);
+        }
         return;
     }
-    const size_t ob = (size_t)b * A, oc = (size_t)b * cap;
-    const int nbw = cap >> 6, nzw = (nbw + 63) >> 6;
-    const int nw = (n + 63) >> 6;
-    const int nzu = (nw + 63) >> 6;   // summary words that can hold a flag: column-blocks < nw
-    for (int w = tid; w < WMAX; w += K7_RESOLVE_THREADS) s_kept[w] = s_rem[w] = s_krank[w] = 0ull;
+    const int nw = (n + 31) >> 5;
+    for (int w = tid; w < WMAX; w += K7_RESOLVE_THREADS) s_kept[w] = s_rem[w] = 0u;
+    if (tid == 0) s_open = 0;
     __syncthreads();
-    uint32_t open_ = 0u;                 // bit k: row tid + k*1024 is still undecided
-    unsigned long long cnts = 0ull;      // 4 bits per k: flagged words of that row (saturating at 15)
-    int mine = 0;
-    bool big = false;
-#pragma unroll
-    for (int k = 0; k < K7_RESOLVE_PER; ++k) {   // independent loads, no atomics in between
-        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
-        const int p = tid + k * K7_RESOLVE_THREADS;
-        if (p >= n) continue;
-        int c = 0;
-        for (int z = 0; z < nzu; ++z) c += __popcll(__ldcg(nz + (oc + p) * nzw + z));
-        if (c > 0) {
-            open_ |= 1u << k;
-            big |= c > 15;
-            cnts |= (unsigned long long)min(c, 15) << (4 * k);
-            mine += c;
+    // boxes without an edge are kept at once; the others wait with their count of live edges
+    int open_mine = 0;
+    for (int r0 = 0; r0 < n; r0 += K7_RESOLVE_THREADS) {
+        const int r = r0 + tid;
+        const int pd = (r < n) ? __ldcg(P.pend + oc + r) : 0;
+        if (r < n) s_pend[r] = pd;
+        const unsigned int k0 = __ballot_sync(0xffffffffu, r < n && pd == 0);
+        if (lane == 0 && (r0 + (warp << 5)) < n) s_kept[(r0 >> 5) + warp] = k0;
+        open_mine += (r < n && pd > 0) ? 1 : 0;
+    }
+    if (open_mine) atomicAdd(&s_open, open_mine);
+    const bool staged = E <= K7_RESOLVE_EDGES;
+    const unsigned int* ge = P.edges + (size_t)b * P.ecap;
+    if (staged)
+        for (int i = tid; i < E; i += K7_RESOLVE_THREADS) s_e[i] = __ldcg(ge + i);
+    for (;;) {
+        __syncthreads();
+        const int open = s_open;   // read by everybody between two barriers
+        __syncthreads();
+        if (open <= 0) break;
+        for (int i = tid; i < E; i += K7_RESOLVE_THREADS) {
+            const unsigned int e = staged ? s_e[i] : __ldcg(ge + i);
+            if (e == 0xffffffffu) continue;                          // dead (only staged lists are marked)
+            const int ri = (int)(e >> 16), rj = (int)(e & 0xffffu);
+            const unsigned int bit_i = 1u << (ri & 31);
+            if ((*((volatile unsigned int*)&s_kept[ri >> 5]) | *((volatile unsigned int*)&s_rem[ri >> 5])) & bit_i) continue;   // decided
+            const unsigned int bit_j = 1u << (rj & 31);
+            if (*((volatile unsigned int*)&s_kept[rj >> 5]) & bit_j) {
+                if (!(atomicOr(&s_rem[ri >> 5], bit_i) & bit_i)) atomicSub(&s_open, 1);     // first to remove it
+            } else if (staged && (*((volatile unsigned int*)&s_rem[rj >> 5]) & bit_j)) {
+                s_e[i] = 0xffffffffu;                                // this suppressor is gone
+                if (atomicSub(&s_pend[ri], 1) == 1) {                // its last live edge: nothing that is kept suppresses it
+                    atomicOr(&s_kept[ri >> 5], bit_i);
+                    atomicSub(&s_open, 1);
+                }
+            }
         }
-    }
-#pragma unroll
-    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
-        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
-        // nothing ranked before it overlaps: kept.  A warp owns 32 consecutive rows = one 32-bit half-word.
-        const int p = tid + k * K7_RESOLVE_THREADS;
-        const unsigned kept0 = __ballot_sync(0xffffffffu, p < n && !((open_ >> k) & 1u));
-        if (lane == 0 && kept0) reinterpret_cast<unsigned int*>(s_kept)[p >> 5] = kept0;
-    }
-    // exclusive scan of the per-thread entry counts
-    int inc = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-    }
-    if (lane == 31) s_wtot[warp] = inc;
-    const int any_big = __syncthreads_or(big ? 1 : 0);
-    int off = inc - mine, total = 0;
-    for (int w = 0; w < K7_RESOLVE_THREADS / 32; ++w) {
-        const int t = s_wtot[w];
-        if (w < warp) off += t;
-        total += t;
-    }
-    const bool staged = !any_big && total <= K7_RESOLVE_LIST;
-    const uint32_t open0 = open_;
-    if (staged) {
-        int e = off;
-        uint32_t o = open0;
-        while (o) {
-            const int k = __ffs(o) - 1;
-            o &= o - 1u;
-            const int p = tid + k * K7_RESOLVE_THREADS;
-            const unsigned long long* row = M + (oc + p) * nbw;
-            for (int z = 0; z < nzu; ++z) {
-                unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
-                while (m) {
-                    const int w = (z << 6) + __ffsll((long long)m) - 1;
-                    m &= m - 1ull;
-                    s_w[e] = (unsigned short)w;
-                    s_l[e] = __ldcg(row + w);
-                    ++e;
+        if (!staged) {
+            // A long edge list stays in global memory and cannot be marked: recount instead.  A box is kept when
+            // every one of its suppressors is removed.
+            __syncthreads();
+            for (int r = tid; r < n; r += K7_RESOLVE_THREADS) s_pend[r] = 0;
+            __syncthreads();
+            for (int i = tid; i < E; i += K7_RESOLVE_THREADS) {
+                const unsigned int e = __ldcg(ge + i);
+                const int ri = (int)(e >> 16), rj = (int)(e & 0xffffu);
+                if (!((s_rem[rj >> 5] >> (rj & 31)) & 1u)) atomicAdd(&s_pend[ri], 1);   // a suppressor that is not removed (yet)
+            }
+            __syncthreads();
+            for (int r = tid; r < n; r += K7_RESOLVE_THREADS) {
+                const unsigned int bit = 1u << (r & 31);
+                if (!((s_kept[r >> 5] | s_rem[r >> 5]) & bit) && s_pend[r] == 0) {
+                    atomicOr(&s_kept[r >> 5], bit);
+                    atomicSub(&s_open, 1);
                 }
             }
         }
     }
-    for (int round = 0; round < K7_SORT_MAX; ++round) {
-        if (tid == 0) s_undecided = 0;
-        __syncthreads();
-        if (staged) {
-            int e = off;
-            uint32_t o = open0;
-            while (o) {
-                const int k = __ffs(o) - 1;
-                o &= o - 1u;
-                const int c = (int)((cnts >> (4 * k)) & 15ull);
-                if ((open_ >> k) & 1u) {
-                    bool any_kept = false, all_removed = true;
-                    for (int i = 0; i < c; ++i) {
-                        const int w = s_w[e + i];
-                        const unsigned long long l = s_l[e + i];
-                        const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
-                        const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
-                        any_kept |= (l & kp) != 0ull;
-                        all_removed &= (l & ~rm) == 0ull;
-                    }
-                    const int p = tid + k * K7_RESOLVE_THREADS;
-                    if (any_kept) {
-                        k7_set_bit(s_rem, p);
-                        open_ &= ~(1u << k);
-                    } else if (all_removed) {
-                        k7_set_bit(s_kept, p);
-                        open_ &= ~(1u << k);
-                    }
-                }
-                e += c;
-            }
-        } else {
-            uint32_t o = open_;
-            while (o) {
-                const int k = __ffs(o) - 1;
-                o &= o - 1u;
-                const int p = tid + k * K7_RESOLVE_THREADS;
-                const unsigned long long* row = M + (oc + p) * nbw;
-                bool any_kept = false, all_removed = true;
-                for (int z = 0; z < nzu; ++z) {
-                    unsigned long long m = __ldcg(nz + (oc + p) * nzw + z);
-                    while (m) {
-                        const int w = (z << 6) + __ffsll((long long)m) - 1;
-                        m &= m - 1ull;
-                        const unsigned long long l = __ldcg(row + w);
-                        const unsigned long long kp = *((volatile unsigned long long*)&s_kept[w]);
-                        const unsigned long long rm = *((volatile unsigned long long*)&s_rem[w]);
-                        any_kept |= (l & kp) != 0ull;
-                        all_removed &= (l & ~rm) == 0ull;
-                    }
-                }
-                if (any_kept) {
-                    k7_set_bit(s_rem, p);
-                    open_ &= ~(1u << k);
-                } else if (all_removed) {
-                    k7_set_bit(s_kept, p);
-                    open_ &= ~(1u << k);
-                }
-            }
-        }
-        if (open_) s_undecided = 1;
-        __syncthreads();
-        if (s_undecided == 0) break;
-        __syncthreads();
-    }
-    // kept set by rank, then compaction in rank (= visiting) order
-#pragma unroll
-    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
-        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
-        const int p = tid + k * K7_RESOLVE_THREADS;
-        if (p >= n) continue;
-        if ((s_kept[p >> 6] >> (p & 63)) & 1ull) {
-            const int r = srank[oc + p];
-            k7_set_bit(s_krank, r);
-        }
-    }
-    __syncthreads();
-    if (tid < 32) {   // exclusive prefix of the popcounts of s_krank[0..nw)
+    // kept set is in rank (= visiting) order: compaction
+    if (tid < 32) {   // exclusive prefix of the popcounts of s_kept[0..nw)
         int carry = 0;
         for (int w0 = 0; w0 < nw; w0 += 32) {
             const int w = w0 + tid;
-            const int v = (w < nw) ? __popcll(s_krank[w]) : 0;
+            const int v = (w < nw) ? __popc(s_kept[w]) : 0;
             int inc = v;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -1872,28 +1642,80 @@ k7_resolve_kernel(int A, int max_det, int cap, const int32_t* __restrict__ nsel,
     }
     __syncthreads();
     const int budget = max_det > 0 ? max_det : 0x7fffffff;
-#pragma unroll
-    for (int k = 0; k < K7_RESOLVE_PER; ++k) {
-        if (k * K7_RESOLVE_THREADS >= n) break;   // block-uniform: no row of this image left
-        const int p = tid + k * K7_RESOLVE_THREADS;
-        if (p >= n) continue;
-        if (!((s_kept[p >> 6] >> (p & 63)) & 1ull)) continue;
-        const int r = srank[oc + p];
-        const int pos = s_prefix[r >> 6] + __popcll(s_krank[r >> 6] & ((1ull << (r & 63)) - 1ull));
+    for (int r = tid; r < n; r += K7_RESOLVE_THREADS) {
+        if (!((s_kept[r >> 5] >> (r & 31)) & 1u)) continue;
+        const int pos = s_prefix[r >> 5] + __popc(s_kept[r >> 5] & ((1u << (r & 31)) - 1u));
         if (pos >= budget) continue;
-        const uint64_t key = sorted_keys[ob + r];
+        const uint64_t key = __ldcg(P.keys1 + ob + r);
         kept_key[ob + pos] = key;
-        kept_box[ob + pos] = sbox[oc + p];
+        kept_box[ob + pos] = __ldcg(P.rbox + oc + r);
         if (keep_idx_out) keep_idx_out[pos] = (int64_t)(uint32_t)(key & 0xffffffffull);
     }
     if (tid == 0) {
         const int kc = min(s_prefix[nw], budget);
         kept_count[b] = kc;
         if (counts_out) {
-            counts_out[2 * b + 0] = surv_count[b];
+            counts_out[2 * b + 0] = P.surv_count[b];
             counts_out[2 * b + 1] = kc;
         }
     }
+}
+
+// exclusive popcount prefix of the survivor bitmap (only when the caller wants survivor ranks)
+__global__ void __launch_bounds__(K7_NMS_THREADS)
+k7_rank_prefix_kernel(int W32, const uint32_t* __restrict__ bits, int32_t* __restrict__ wprefix) {
+    __shared__ int s_w[32];
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    k7_pdl_wait();
+    const int chunk = (W32 + K7_NMS_THREADS - 1) / K7_NMS_THREADS;
+    const int w_lo = min(tid * chunk, W32), w_hi = min(w_lo + chunk, W32);
+    const uint32_t* brow = bits + (size_t)b * W32;
+    int cnt = 0;
+    for (int w = w_lo; w < w_hi; ++w) cnt += __popc(brow[w]);
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_w[warp] = inc;
+    __syncthreads();
+    int run = inc - cnt;
+    for (int k = 0; k < warp; ++k) run += s_w[k];
+    for (int w = w_lo; w < w_hi; ++w) {
+        wprefix[(size_t)b * W32 + w] = run;
+        run += __popc(brow[w]);
+    }
+}
+
+// ------------------------------------------------------------------ host: the NMS chain
+static K7NmsArgs k7_nms_args(const K7DetectWs& w, int A, float thr, int pre_topk, bool class_aware) {
+    K7NmsArgs P;
+    memset(&P, 0, sizeof(P));
+    P.A = A; P.cap = w.cap; P.pre_topk = pre_topk; P.class_aware = class_aware ? 1 : 0; P.thr = thr;
+    P.surv_count = w.surv_count; P.keys0 = w.keys0; P.keysC = w.keysC; P.keys1 = w.keys1; P.box_ws = w.box;
+    P.label_ws = w.label; P.rbox = w.rbox; P.bounds = w.bounds; P.nsel = w.nsel; P.ccnt = w.ccnt; P.ckeyC = w.ckeyC;
+    P.cbox = w.cbox; P.crank = w.crank; P.clabel = w.clabel; P.ctab = w.ctab; P.pend = w.pend; P.edges = w.edges;
+    P.nedge = w.nedge; P.ecap = w.ecap;
+    return P;
+}
+
+static int k7_nms_chain(const K7NmsArgs& P, int B, int max_det, uint64_t* kept_key, float4* kept_box, int32_t* kept_count,
+                        int32_t* counts, int64_t* keep_idx_out, cudaStream_t st) {
+    const int G = P.cap / K7_NMS_CH;
+    const float tl = P.thr * (1.0f - 1e-4f);
+    const float kq = P.thr >= K7_GRID_MIN_THR ? (0.5f + 0.5f / tl - tl) * (1.0f + 1e-4f) : 0.0f;
+    k7_pdl_site() = 0;
+    K7_CUDA(k7_launch_pdl(k7_nms_chunksort_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
+    k7_pdl_site() = 1;
+    K7_CUDA(k7_launch_pdl(k7_nms_rank_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
+    K7_CUDA(k7_launch_pdl(k7_nms_cellorder_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
+    K7_CUDA(k7_launch_pdl(k7_nms_pairs_kernel, dim3(P.cap / K7_PAIRS_THREADS, B), dim3(K7_PAIRS_THREADS), 0, st, P, kq));
+    K7_CUDA(cudaFuncSetAttribute(k7_nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
+    k7_pdl_site() = 2;
+    K7_CUDA(k7_launch_pdl(k7_nms_resolve_kernel, dim3(B), dim3(K7_RESOLVE_THREADS), K7_RESOLVE_SMEM, st, P, max_det, kept_key,
+                          kept_box, kept_count, counts, keep_idx_out));
+    return K7_OK;
 }
 
 // ------------------------------------------------------------------ gather
@@ -1949,9 +1771,8 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         return K7_EWORKSPACE;
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    // surv_count, kept_count and the bitmap are contiguous at the start of the workspace
-    K7_CUDA(cudaMemsetAsync(w.surv_count, 0, (size_t)(reinterpret_cast<unsigned char*>(w.wprefix) -
-                                                      reinterpret_cast<unsigned char*>(w.surv_count)), st));
+    // counters, bounds, the survivor bitmap and the cell table are contiguous at the start of the workspace
+    K7_CUDA(cudaMemsetAsync(w.surv_count, 0, w.zero_bytes, st));
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     float report_thr = params->score_thr;
@@ -1992,14 +1813,14 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
             auto kern = params->from_logits ? k7_score_levels_kernel<true> : k7_score_levels_kernel<false>;
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_LV_SMEM));
             kern<<<grid, 256, K7_LV_SMEM, st>>>(sp, LV, num_tiles, reinterpret_cast<const float4*>(reg), A, C, report_thr, *params,
-                                                w.bits, w.W32, w.box, w.label, w.score);
+                                                w.bits, w.W32, w.box, w.label, w.surv_count, w.keys0);
             K7_LAUNCH_CHECK();
         }
         if (sblocks > 0) {
             dim3 grid(sblocks, B);
             auto kern = params->from_logits ? k7_score_levels_scalar_kernel<true> : k7_score_levels_scalar_kernel<false>;
             kern<<<grid, 256, 0, st>>>(sp, LV, reinterpret_cast<const float4*>(reg), A, C, report_thr, *params, w.bits, w.W32,
-                                       w.box, w.label, w.score);
+                                       w.box, w.label, w.surv_count, w.keys0);
             K7_LAUNCH_CHECK();
         }
     } else {
@@ -2012,7 +1833,7 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GS.smem_bytes));            \
         kern<<<GS.grid, (GS.cw + 1) * 32, GS.smem_bytes, st>>>(sp, anchors, box_order, cls,                              \
                                                                reinterpret_cast<const float4*>(reg), A, C, report_thr,  \
-                                                               *params, GS, w.bits, w.W32, w.box, w.label, w.score);    \
+                                                               *params, GS, w.bits, w.W32, w.box, w.label, w.surv_count, w.keys0);    \
     } while (0)
         if (params->from_logits) { if (spec) K7_SPIPE_LAUNCH(true, true); else K7_SPIPE_LAUNCH(false, true); }
         else                     { if (spec) K7_SPIPE_LAUNCH(true, false); else K7_SPIPE_LAUNCH(false, false); }
@@ -2020,31 +1841,10 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
         K7_LAUNCH_CHECK();
     }
 
-    // NMS: images with <= cap survivors go through sort -> mask (all SMs) -> resolve (one CTA each),
-    // the others through the chunked single-CTA kernel.  Each kernel decides per image on the device.
-    const bool ca = params->class_aware != 0;   // suppression only inside a class (torchvision.ops.batched_nms)
-    {
-        size_t smem_sort = 64 * 8;
-        while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;   // bitonic size of the largest image
-        K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_pdl_site() = 0;
-        K7_CUDA(k7_launch_pdl(k7_sort_kernel, dim3(B), dim3(K7_NMS_THREADS), smem_sort, st, A, w.W32, params->pre_nms_topk,
-                              w.cap, w.surv_count, w.bits, w.wprefix, w.score, w.keys0, w.keys1, w.box, w.sbox, w.srank,
-                              w.blk, w.nz, w.nsel, w.work, ca ? w.label : nullptr, ca ? w.slabel : nullptr, w.kept_box));
-        int gx = (8 * k7_sm_count() + B - 1) / B;   // about eight CTAs per SM over the batch
-        const int gx_max = (w.cap / 64 + K7_MASK_GROUPS - 1) / K7_MASK_GROUPS * 4;
-        if (gx > gx_max) gx = gx_max;
-        if (gx < 1) gx = 1;
-        k7_pdl_site() = 1;
-        K7_CUDA(k7_launch_pdl(k7_mask_kernel, dim3(gx, B), dim3(K7_MASK_THREADS), 0, st, params->iou_thr, w.cap, w.nsel,
-                              w.sbox, w.srank, w.blk, w.nz, w.M, w.work, ca ? w.slabel : nullptr));
-        K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
-        k7_pdl_site() = 2;
-        K7_CUDA(k7_launch_pdl(k7_resolve_kernel, dim3(B), dim3(K7_RESOLVE_THREADS), K7_RESOLVE_SMEM, st, A,
-                              params->max_detections, w.cap, w.nsel, w.surv_count, w.keys1, w.sbox, w.srank, w.nz, w.M,
-                              w.kept_key, w.kept_box, w.kept_count, counts, nullptr, params->iou_thr, params->pre_nms_topk,
-                              w.keys0, w.box, ca ? w.label : nullptr));
-    }
+    // NMS (every kernel decides per image on the device; PDL links: each starts when its predecessor drains)
+    int rc2 = k7_nms_chain(k7_nms_args(w, A, params->iou_thr, params->pre_nms_topk, params->class_aware != 0), B,
+                           params->max_detections, w.kept_key, w.kept_box, w.kept_count, counts, nullptr, st);
+    if (rc2) return rc2;
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
@@ -2078,6 +1878,9 @@ extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, i
     }
     dim3 grid((cap + 255) / 256, B);
     k7_pdl_site() = 3;
+    if (survivor_rank)   // the exclusive popcount prefix of the survivor bitmap is only needed for this output
+        K7_CUDA(k7_launch_pdl(k7_rank_prefix_kernel, dim3(B), dim3(K7_NMS_THREADS), 0, static_cast<cudaStream_t>(stream), w.W32,
+                              w.bits, w.wprefix));
     K7_CUDA(k7_launch_pdl(k7_gather_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), A, w.W32, cap, w.kept_count,
                           w.kept_key, w.kept_box, w.label, w.bits, w.wprefix, scores, labels, reinterpret_cast<float4*>(boxes),
                           anchor_ids, survivor_rank));
@@ -2086,58 +1889,8 @@ extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, i
 }
 
 // ------------------------------------------------------------------ stand-alone NMS (torchvision.ops.nms)
-struct K7NmsWs {
-    uint64_t* keys0;
-    uint64_t* keys1;
-    uint64_t* kept_key;
-    float4* kept_box;
-    int32_t* small;            // {n, nsel, kept_count, mask work counter}
-    int32_t* label;            // [n] class of each box (k7_batched_nms)
-    float4* sbox;              // multi-SM path (n <= K7_SORT_MAX)
-    int32_t* srank;
-    int32_t* slabel;
-    float4* blk;
-    unsigned long long* nz;
-    unsigned long long* M;
-    int cap;
-    size_t bytes;
-};
-static K7NmsWs k7_nms_ws(void* base, int n) {
-    K7NmsWs w;
-    unsigned char* p = static_cast<unsigned char*>(base);
-    size_t o = 0;
-    auto take = [&](size_t bytes) {
-        unsigned char* r = p ? p + o : nullptr;
-        o += k7_align_up(bytes, 256);
-        return r;
-    };
-    const size_t nn = n > 0 ? n : 1;
-    w.keys0 = reinterpret_cast<uint64_t*>(take(8 * nn));
-    w.keys1 = reinterpret_cast<uint64_t*>(take(8 * nn));
-    w.kept_key = reinterpret_cast<uint64_t*>(take(8 * nn));
-    w.kept_box = reinterpret_cast<float4*>(take(16 * nn));
-    w.small = reinterpret_cast<int32_t*>(take(64));
-    w.label = reinterpret_cast<int32_t*>(take(4 * nn));
-    w.sbox = w.kept_box;
-    w.srank = nullptr;
-    w.slabel = nullptr;
-    w.blk = nullptr;
-    w.nz = nullptr;
-    w.M = nullptr;
-    w.cap = k7_nms_cap(1, n);
-    if (n <= w.cap) {
-        const size_t cap = (size_t)w.cap, nbw = cap / 64, nzw = (nbw + 63) / 64;
-        w.sbox = reinterpret_cast<float4*>(take(sizeof(float4) * cap));
-        w.srank = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * cap));
-        w.slabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * cap));
-        w.blk = reinterpret_cast<float4*>(take(sizeof(float4) * 4 * nbw));
-        w.nz = reinterpret_cast<unsigned long long*>(take(8 * cap * nzw));
-        w.M = reinterpret_cast<unsigned long long*>(take(8 * cap * nbw));
-    }
-    w.bytes = o;
-    return w;
-}
-extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_nms_ws(nullptr, n).bytes; }
+// Same kernels as k7_detect with B = 1 and "anchor id" = box index: the workspace is k7_detect's for (1, n).
+extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_detect_ws(nullptr, 1, n > 0 ? n : 1).bytes; }
 
 __global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys,
                                    int32_t* __restrict__ n_dev, const int64_t* __restrict__ idxs,
@@ -2148,19 +1901,6 @@ __global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint
         keys[i] = ((uint64_t)k7_score_key_desc(scores[i]) << 32) | (uint32_t)i;
         if (idxs) labels[i] = (int32_t)idxs[i];   // only equality matters; category ids fit 32 bits
     }
-}
-
-__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_nms_single_kernel(int n, float iou_thr, uint64_t* __restrict__ keys0, uint64_t* __restrict__ keys1,
-                     const float4* __restrict__ boxes, const int32_t* __restrict__ labels, uint64_t* __restrict__ kept_key,
-                     float4* __restrict__ kept_box, int64_t* __restrict__ keep, int32_t* __restrict__ count) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    K7SortNmsSmem& S = *reinterpret_cast<K7SortNmsSmem*>(smem_raw);
-    uint64_t* sorted = k7_block_sort(keys0, keys1, n, S);
-    const int kept = k7_block_nms(sorted, n, boxes, labels, iou_thr, 0x7fffffff, kept_key, kept_box, S.nms);
-    __syncthreads();
-    for (int k = threadIdx.x; k < kept; k += K7_NMS_THREADS) keep[k] = (int64_t)(uint32_t)(kept_key[k] & 0xffffffffull);
-    if (threadIdx.x == 0) *count = kept;
 }
 
 static int k7_nms_run(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr, int64_t* keep,
@@ -2175,38 +1915,18 @@ static int k7_nms_run(const float* boxes, const float* scores, const int64_t* id
     K7_REQUIRE(boxes && scores && keep, "k7_nms: null argument");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
                "k7_nms: boxes must be 16-byte and workspace 256-byte aligned");
-    const K7NmsWs w = k7_nms_ws(workspace, n);
+    const K7DetectWs w = k7_detect_ws(workspace, 1, n);
     if (workspace_bytes < w.bytes) {
         k7_set_error("k7_nms: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
         return K7_EWORKSPACE;
     }
-    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.small, idxs, w.label);
+    K7_CUDA(cudaMemsetAsync(w.surv_count, 0, w.zero_bytes, st));
+    k7_nms_keys_kernel<<<(n + 255) / 256, 256, 0, st>>>(scores, n, w.keys0, w.surv_count, idxs, w.label);
     K7_LAUNCH_CHECK();
-    if (n <= w.cap) {   // sort -> bitmask on all SMs -> fixed-point resolve (same kernels as k7_detect, B = 1)
-        const float4* b4 = reinterpret_cast<const float4*>(boxes);
-        size_t smem_sort = 64 * 8;
-        while (smem_sort < (size_t)w.cap * 8) smem_sort <<= 1;
-        K7_CUDA(cudaFuncSetAttribute(k7_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_sort));
-        k7_sort_kernel<<<1, K7_NMS_THREADS, smem_sort, st>>>(n, 0, 0, w.cap, w.small, nullptr, nullptr, nullptr, w.keys0,
-                                                             w.keys1, b4, w.sbox, w.srank, w.blk, w.nz, w.small + 1, w.small + 3,
-                                                             idxs ? w.label : nullptr, idxs ? w.slabel : nullptr, w.kept_box);
-        K7_LAUNCH_CHECK();
-        const int nb = (n + 63) / 64;
-        int gx = 4 * k7_sm_count();   // one image: spread its row-blocks (and their column shares) over every SM
-        if (gx > nb * nb) gx = nb * nb;
-        k7_mask_kernel<<<dim3(gx, 1), K7_MASK_THREADS, 0, st>>>(iou_thr, w.cap, w.small + 1, w.sbox, w.srank, w.blk, w.nz, w.M,
-                                                                w.small + 3, idxs ? w.slabel : nullptr);
-        K7_LAUNCH_CHECK();
-        K7_CUDA(cudaFuncSetAttribute(k7_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
-        k7_resolve_kernel<<<1, K7_RESOLVE_THREADS, K7_RESOLVE_SMEM, st>>>(n, 0, w.cap, w.small + 1, w.small, w.keys1, w.sbox, w.srank, w.nz,
-                                                            w.M, w.kept_key, w.kept_box, count, nullptr, keep, iou_thr, 0, nullptr, nullptr, nullptr);
-        K7_LAUNCH_CHECK();
-        return K7_OK;
-    }
-    const size_t smem = sizeof(K7SortNmsSmem);
-    K7_CUDA(cudaFuncSetAttribute(k7_nms_single_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k7_nms_single_kernel<<<1, K7_NMS_THREADS, smem, st>>>(n, iou_thr, w.keys0, w.keys1, reinterpret_cast<const float4*>(boxes),
-                                                          idxs ? w.label : nullptr, w.kept_key, w.kept_box, keep, count);
+    K7NmsArgs P = k7_nms_args(w, n, iou_thr, 0, idxs != nullptr);
+    P.box_ws = reinterpret_cast<const float4*>(boxes);
+    int rc = k7_nms_chain(P, 1, 0, w.kept_key, w.kept_box, count, nullptr, keep, st);
+    if (rc) return rc;
     K7_LAUNCH_CHECK();
     return K7_OK;
 }

@@ -94,13 +94,6 @@ __device__ __forceinline__ float2 k7_loss_scales(const int n, const float mean_d
     return s;
 }
 
-// does image b have an annotation row with label != -1 (losses.py:49-60)?  Warp-wide.
-__device__ __forceinline__ bool k7_warp_any_valid(const float* __restrict__ annotations, int M, int b, int lane) {
-    bool v = false;
-    for (int m = lane; m < M; m += 32) v |= __ldg(annotations + ((size_t)b * M + m) * 5 + 4) != -1.0f;
-    return __any_sync(0xffffffffu, v);
-}
-
 // ------------------------------------------------------------------ element math
 __device__ __forceinline__ float k7_rcp_approx(float x) {
     float r;
@@ -272,13 +265,14 @@ struct K7PipeSegs {
     K7PipeSeg s[K7_MAX_LEVELS];
 };
 
+#define K7_PIPE_SCO_MAX 4096   // images whose gradient scale fits the shared-memory table
 struct K7PipeGeom {
     uint32_t tile_f;         // floats per tile = cw * slice
     uint32_t slice;          // floats per consumer warp and tile: 512 or 1024
     uint32_t num_tiles;      // sum over the streams of ceil(N4 / tile_f)
     uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x]
     uint32_t stage_stride;
-    uint32_t off_desc, off_bars;
+    uint32_t off_desc, off_bars, off_sco;   // off_sco: float[B] gradient scale per image (0: not tabulated)
     int stages, cw, grid;
     size_t smem_bytes;
 };
@@ -291,7 +285,7 @@ struct K7TileDesc {   // written by the producer next to each stage, 32 bytes
 template <bool GRAD, int SL, bool LOGITS>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
 k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __restrict__ num_pos,
-                    const float* __restrict__ annotations, const __grid_constant__ K7LossDev P,
+                    const unsigned char* __restrict__ img_valid, const __grid_constant__ K7LossDev P,
                     const __grid_constant__ K7PipeGeom G, float* __restrict__ partials, float* __restrict__ cta_partials) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -307,6 +301,16 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         }
         k7_fence_mbar_init();
         k7_fence_proxy_async();
+    }
+    // The gradient scale of every image, (1-alpha) / (max(num_pos,1) * mean_divisor) - 0 for an image
+    // without ground truth, which the reference skips (losses.py:52-60) -, tabulated once: a warp that
+    // enters a new image must not wait for global memory (all 16 warps of a CTA change image at about
+    // the same tile: the whole CTA would stall, 64 times per kernel).
+    const float* s_sco = (GRAD && G.off_sco) ? reinterpret_cast<const float*>(smem + G.off_sco) : nullptr;
+    if (GRAD && G.off_sco) {
+        float* t = reinterpret_cast<float*>(smem + G.off_sco);
+        for (int b = threadIdx.x; b < P.B; b += blockDim.x)
+            t[b] = img_valid[b] ? P.one_m_alpha * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x : 0.0f;
     }
     __syncthreads();
     if (blockIdx.x >= G.num_tiles && blockIdx.x != 0) return;
@@ -408,8 +412,8 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         if (b == cur_b) return;
         if (cur_b >= 0) flush();
         cur_b = b;
-        if (GRAD)   // an image without ground truth is skipped by the reference (losses.py:52-60): no gradient
-            sco = k7_warp_any_valid(annotations, P.M, b, lane) ? oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x : 0.0f;
+        if (GRAD)
+            sco = s_sco ? s_sco[b] : (img_valid[b] ? oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x : 0.0f);
     };
     auto exact = [&](const float x, float* gout) {
         float gr;
@@ -508,7 +512,7 @@ struct K7LevelTable {
     int S[K7_MAX_LEVELS];
 };
 
-// ------------------------------------------------------------------ the row kernel
+// ------------------------------------------------------------------ the row kernels
 __device__ __forceinline__ double k7_warp_sum_f64(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -544,117 +548,183 @@ __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* 
     }
 }
 
-// After the stream kernel.  Work item = a chunk of 2048 consecutive anchors of one image.
-//   scan    every thread reads 8 assignment entries (coalesced: entry j of thread t is anchor
-//           a0 + 256 j + t), zeroes d(reg) of the rows that are not positive, and queues positive
-//           rows from the front and ignored rows from the back of a shared-memory queue;
-//   serve   positive rows, a thread each: smooth-L1 + d(reg) (losses.py:122-166) and the
-//           correction of the label element from "target 0" (what the stream computed) to
-//           "target 1" (losses.py:94-112); ignored rows, a warp each: the row's C elements are
-//           evaluated again, exactly, and SUBTRACTED (the stream counted them), their gradients
-//           become 0 (losses.py:79-82, 114);
-//   fold    every thread turns its float partial sums into 2^-32 fixed point, the warp adds them
-//           (integers: exact) and one lane adds the result to the image's accumulators.
-// The last block to finish sums, per image, the stream's per-CTA partials in float64 in CTA order,
-// adds the accumulators and writes (cls_loss_i, reg_loss_i); then the batch sums in image order.
-// No float atomics anywhere: bit-reproducible run to run.
-template <bool GRAD, bool PACKED, bool FROM_SPEC, bool LEVELS>
+// SCAN KERNEL, before the stream.  Work item = a chunk of 2048 consecutive anchors of one image;
+// every thread reads 8 assignment entries (coalesced: entry j of thread t is anchor a0 + 256 j + t),
+// zeroes d(reg) of the rows that are not positive, counts the image's positives (num_pos: the
+// stream needs it for the gradient scale) and appends the rows that are not plain negatives to a
+// batch-wide queue in global memory - positive rows from the front, ignored rows (losses.py:79-82)
+// from the back; one block-level prefix and ONE atomicAdd per block and queue end.  The order of
+// the queue depends on the order in which blocks finish; everything computed from it is
+// accumulated with integer atomics, so results do not.
+//   queue entry: x = anchor (image-local), y = image << 16 | annotation row
+struct K7RowQueues {
+    uint2* q;                  // [B*A] entries: positives q[0 .. npos), ignored rows q[cap-1], q[cap-2], ...
+    unsigned int* count;       // [0] positives, [1] ignored rows
+    unsigned long long cap;    // B*A
+    unsigned char* img_valid;  // [B] 1: the image has an annotation row (losses.py:49-60)
+};
+
+template <bool GRAD, bool PACKED>
 __global__ void __launch_bounds__(K7_ROWS_THREADS)
-k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7LevelTable LT,
-                    const float* __restrict__ anchors, int box_order,
-                    const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
-                    const __grid_constant__ K7AssignSrc SRC, const int32_t* __restrict__ num_pos,
-                    const __grid_constant__ K7LossDev P, const __grid_constant__ K7PeerDev PR,
-                    const float* __restrict__ pipe_partials, uint32_t pipe_slots,
-                    long long* __restrict__ acc /* [B][2] */, unsigned int* __restrict__ counter,
-                    float* __restrict__ per_image, float* __restrict__ sums, float* __restrict__ dcls,
-                    float4* __restrict__ dreg) {
+k7_loss_scan_kernel(const float* __restrict__ annotations, const __grid_constant__ K7AssignSrc SRC,
+                    const __grid_constant__ K7LossDev P, const __grid_constant__ K7RowQueues Q,
+                    int32_t* __restrict__ num_pos, float4* __restrict__ dreg) {
     constexpr int NW = K7_ROWS_THREADS / 32;
-    __shared__ int s_qa[K7_ROWS_CHUNK];       // anchor (image-local); positives from the front, ignored rows from the back
-    __shared__ int s_qr[K7_ROWS_CHUNK];       // annotation row of a positive
-    __shared__ int s_npos, s_nign;
-    __shared__ double s_red[2 * NW];
-    __shared__ bool s_last;
-    const int A = P.A, C = P.C;
+    __shared__ int s_wp[NW], s_wi[NW];
+    __shared__ unsigned int s_base[2];
+    const int A = P.A;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const float oma = P.one_m_alpha;
     const int cpi = (A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK;   // chunks per image
     const long long total = (long long)P.B * cpi;
 
     for (long long ch = blockIdx.x; ch < total; ch += gridDim.x) {   // block-uniform
         const int b = (int)(ch / cpi);
         const int a0 = (int)(ch - (long long)b * cpi) * K7_ROWS_CHUNK;
-        if (threadIdx.x == 0) {
-            s_npos = 0;
-            s_nign = 0;
-        }
-        bool v = false;
-        for (int m = threadIdx.x; m < P.M; m += K7_ROWS_THREADS) v |= __ldg(annotations + ((size_t)b * P.M + m) * 5 + 4) != -1.0f;
-        const bool any_valid = __syncthreads_or(v ? 1 : 0) != 0;   // also: the queue counters are visible
-        const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
-
-        // ---- scan
-        int st[K7_ROWS_PER], rw[K7_ROWS_PER];
-        if (PACKED) {
-            unsigned long long e[K7_ROWS_PER];
-#pragma unroll
-            for (int j = 0; j < K7_ROWS_PER; ++j) {
-                const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
-                e[j] = (a < A && any_valid) ? __ldcg(SRC.best + (size_t)b * A + a) : 0ull;
-            }
-#pragma unroll
-            for (int j = 0; j < K7_ROWS_PER; ++j) {
-                st[j] = K7_STATE_NEG;
-                rw[j] = 0;
-                if (K7_BEST_GEN(e[j]) == SRC.gen) {
-                    if (SRC.consume)
-                        const_cast<unsigned long long*>(SRC.best)[(size_t)b * A + a0 + j * K7_ROWS_THREADS + threadIdx.x] = 0ull;
-                    const float iou = __uint_as_float(K7_BEST_IOU_BITS(e[j]));
-                    st[j] = iou >= SRC.pos_thr ? K7_STATE_POS : (iou < SRC.neg_thr ? K7_STATE_NEG : K7_STATE_IGNORE);
-                    rw[j] = K7_BEST_ROW(e[j]);
-                }
-            }
-        } else {
-            int w[K7_ROWS_PER];
-#pragma unroll
-            for (int j = 0; j < K7_ROWS_PER; ++j) {
-                const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
-                w[j] = (a < A && any_valid) ? __ldg(SRC.words + (size_t)b * A + a) : 0;
-            }
-#pragma unroll
-            for (int j = 0; j < K7_ROWS_PER; ++j) {
-                st[j] = K7_ASSIGN_STATE(w[j]);
-                rw[j] = K7_ASSIGN_ROW(w[j]);
-            }
-        }
+        // the assignment entries first: their latency overlaps the look at the annotations
+        unsigned long long e[K7_ROWS_PER];
+        int w[K7_ROWS_PER];
 #pragma unroll
         for (int j = 0; j < K7_ROWS_PER; ++j) {
             const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
+            if (PACKED) e[j] = (a < A) ? __ldcg(SRC.best + (size_t)b * A + a) : 0ull;
+            else w[j] = (a < A) ? __ldg(SRC.words + (size_t)b * A + a) : 0;
+        }
+        bool v = false;
+        for (int m = threadIdx.x; m < P.M; m += K7_ROWS_THREADS) v |= __ldg(annotations + ((size_t)b * P.M + m) * 5 + 4) != -1.0f;
+        const bool any_valid = __syncthreads_or(v ? 1 : 0) != 0;   // also: s_wp / s_wi / s_base of the previous chunk are consumed
+        if (a0 == 0 && threadIdx.x == 0) Q.img_valid[b] = any_valid ? 1 : 0;
+
+        unsigned int pm = 0u, im = 0u;   // bit j: entry j is a positive / an ignored row
+        int rw[K7_ROWS_PER];
+#pragma unroll
+        for (int j = 0; j < K7_ROWS_PER; ++j) {
+            const int a = a0 + j * K7_ROWS_THREADS + threadIdx.x;
+            int st = K7_STATE_NEG;
+            rw[j] = 0;
+            if (PACKED) {
+                if (K7_BEST_GEN(e[j]) == SRC.gen) {
+                    if (SRC.consume) const_cast<unsigned long long*>(SRC.best)[(size_t)b * A + a] = 0ull;
+                    const float iou = __uint_as_float(K7_BEST_IOU_BITS(e[j]));
+                    st = iou >= SRC.pos_thr ? K7_STATE_POS : (iou < SRC.neg_thr ? K7_STATE_NEG : K7_STATE_IGNORE);
+                    rw[j] = K7_BEST_ROW(e[j]);
+                }
+            } else {
+                st = K7_ASSIGN_STATE(w[j]);
+                rw[j] = K7_ASSIGN_ROW(w[j]);
+            }
             if (a >= A) continue;
-            if (!any_valid) st[j] = K7_STATE_IGNORE;   // the whole image is skipped (losses.py:52-60)
+            if (!any_valid) {   // the whole image is skipped (losses.py:52-60): nothing to patch, no gradient
+                st = K7_STATE_IGNORE;
+                rw[j] = 0;
+            }
             const size_t R = (size_t)b * A + a;
-            if (SRC.words_out) SRC.words_out[R] = (rw[j] << 2) | st[j];
-            if (GRAD && !P.dreg_prezeroed && st[j] != K7_STATE_POS) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (!any_valid) continue;
-            if (st[j] == K7_STATE_POS) {
-                const int q = atomicAdd(&s_npos, 1);
-                s_qa[q] = a;
-                s_qr[q] = rw[j];
-            } else if (st[j] == K7_STATE_IGNORE) {
-                const int q = atomicAdd(&s_nign, 1);
-                s_qa[K7_ROWS_CHUNK - 1 - q] = a;   // a chunk holds at most K7_ROWS_CHUNK rows: the two ends never meet
+            if (SRC.words_out) SRC.words_out[R] = (rw[j] << 2) | st;
+            if (GRAD && !P.dreg_prezeroed && st != K7_STATE_POS) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (any_valid) {
+                pm |= (st == K7_STATE_POS ? 1u : 0u) << j;
+                im |= (st == K7_STATE_IGNORE ? 1u : 0u) << j;
             }
         }
+        // block-level exclusive prefix of (positives, ignored rows) per thread
+        const int cp = __popc(pm), ci = __popc(im);
+        int ip = cp, ii = ci;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int tp = __shfl_up_sync(0xffffffffu, ip, o), ti = __shfl_up_sync(0xffffffffu, ii, o);
+            if (lane >= o) {
+                ip += tp;
+                ii += ti;
+            }
+        }
+        if (lane == 31) {
+            s_wp[warp] = ip;
+            s_wi[warp] = ii;
+        }
         __syncthreads();
+        int op = ip - cp, oi = ii - ci, tp = 0, ti = 0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (k < warp) {
+                op += s_wp[k];
+                oi += s_wi[k];
+            }
+            tp += s_wp[k];
+            ti += s_wi[k];
+        }
+        if (threadIdx.x == 0) {
+            s_base[0] = tp ? atomicAdd(Q.count + 0, (unsigned int)tp) : 0u;
+            s_base[1] = ti ? atomicAdd(Q.count + 1, (unsigned int)ti) : 0u;
+            if (tp) atomicAdd(num_pos + b, tp);   // integer: order independent, exact
+        }
+        __syncthreads();
+        if (pm | im) {
+            const unsigned int bp = s_base[0] + (unsigned int)op, bi = s_base[1] + (unsigned int)oi;
+            int kp = 0, ki = 0;
+#pragma unroll
+            for (int j = 0; j < K7_ROWS_PER; ++j) {
+                const unsigned int a = (unsigned int)(a0 + j * K7_ROWS_THREADS + threadIdx.x);
+                if ((pm >> j) & 1u) Q.q[bp + kp++] = make_uint2(a, ((unsigned int)b << 16) | (unsigned int)rw[j]);
+                if ((im >> j) & 1u) Q.q[Q.cap - 1ull - (bi + ki++)] = make_uint2(a, (unsigned int)b << 16);
+            }
+        }
+    }
+}
 
-        // ---- serve
+// SERVE KERNEL, after the stream: the two queues, densely.
+//   positive rows, a thread each: smooth-L1 + d(reg) (losses.py:122-166) and the correction of the
+//           label element from "target 0" (what the stream computed) to "target 1" (losses.py:94-112);
+//   ignored rows, a warp each (lanes across the classes, all loads of a row in flight at once): the
+//           row's C elements are evaluated again, exactly, and SUBTRACTED - the stream counted them -
+//           and their gradients become 0 (losses.py:79-82, 114).
+// Contributions are added to the image's two accumulators as 2^-32 fixed-point integers (integer
+// atomics: exact, independent of the order).  The last block to finish sums, per image, the
+// stream's per-CTA partials in float64 in CTA order, adds the accumulators and writes
+// (cls_loss_i, reg_loss_i); then the batch sums in image order.  No float atomics anywhere:
+// bit-reproducible run to run.
+__device__ __forceinline__ void k7_acc_add(long long* __restrict__ acc, int b, int which, double v, int lane) {
+    // one atomic per warp when the warp's lanes work on one image (the usual case), else one per lane
+    long long iv = __double2ll_rn(v * K7_FIX_ONE);
+    const int b0 = __shfl_sync(0xffffffffu, b, 0);
+    if (__all_sync(0xffffffffu, b == b0)) {
+        iv = k7_warp_sum_i64(iv);
+        if (lane == 0 && iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b0 + which), (unsigned long long)iv);
+    } else if (b >= 0 && iv) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b + which), (unsigned long long)iv);
+    }
+}
+
+template <bool GRAD, bool FROM_SPEC, bool LEVELS>
+__global__ void __launch_bounds__(K7_ROWS_THREADS)
+k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7LevelTable LT,
+                     const float* __restrict__ anchors, int box_order,
+                     const float* __restrict__ cls, const float* __restrict__ reg, const float* __restrict__ annotations,
+                     const __grid_constant__ K7RowQueues Q, const int32_t* __restrict__ num_pos,
+                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7PeerDev PR,
+                     const float* __restrict__ pipe_partials, uint32_t pipe_slots,
+                     long long* __restrict__ acc /* [B][2] */, unsigned int* __restrict__ counter,
+                     float* __restrict__ per_image, float* __restrict__ sums, float* __restrict__ dcls,
+                     float4* __restrict__ dreg) {
+    constexpr int NW = K7_ROWS_THREADS / 32;
+    __shared__ double s_red[2 * NW];
+    __shared__ bool s_last;
+    const int A = P.A, C = P.C;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float oma = P.one_m_alpha;
+    const unsigned int npos = __ldcg(Q.count + 0), nign = __ldcg(Q.count + 1);
+
+    // ---- positive rows: a thread each (whole warps stay in the loop: the fold below is warp-wide)
+    for (unsigned int i0 = blockIdx.x * K7_ROWS_THREADS; i0 < npos; i0 += gridDim.x * K7_ROWS_THREADS) {
+        const unsigned int i = i0 + threadIdx.x;
+        int b = -1;
         float cfix = 0.0f, rsum = 0.0f;
-        const int npos = s_npos, nign = s_nign;
-        for (int i = threadIdx.x; i < npos; i += K7_ROWS_THREADS) {
-            const int a = s_qa[i];
+        if (i < npos) {
+            const uint2 ent = __ldcg(Q.q + i);
+            const int a = (int)ent.x;
+            b = (int)(ent.y >> 16);
             const size_t R = (size_t)b * A + a;
-            const float* arow = annotations + ((size_t)b * P.M + s_qr[i]) * 5;
-            rsum += k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
+            const float* arow = annotations + ((size_t)b * P.M + (ent.y & 0xffffu)) * 5;
+            const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
+            rsum = k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
             const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
             if (label >= 0 && label < C) {
                 size_t e = R * (size_t)C + (size_t)label;
@@ -674,7 +744,7 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                 const float zl = __ldg(src + e);
                 const float xl = P.from_logits ? k7_sigmoid_precise(zl) : zl;
                 const float p = k7_clamp_p(xl);
-                cfix += k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
+                cfix = k7_focal_pos(p, P.alpha) - oma * k7_neg_exact(xl, nullptr);
                 if (GRAD) {
                     float g = (p == xl) ? k7_focal_pos_grad(p, P.alpha) * sc.x : 0.0f;
                     if (P.from_logits) g *= xl * (1.0f - xl);   // d/dz through the fused sigmoid
@@ -682,9 +752,33 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                 }
             }
         }
-        float csub = 0.0f;   // what the stream added for the ignored rows (without the (1-alpha) factor)
-        for (int i = warp; i < nign; i += NW) {
-            const int a = s_qa[K7_ROWS_CHUNK - 1 - i];
+        k7_acc_add(acc, b, 0, (double)cfix, lane);
+        k7_acc_add(acc, b, 1, (double)rsum, lane);
+    }
+
+    // ---- ignored rows: a warp each, eight consecutive queue entries per visit.  Neighbours in the queue come from
+    // one block of the scan, i.e. from one image: their contributions are added up (as integers) and leave the warp
+    // with ONE atomic per run - a quarter of a million atomics on 64 addresses was what this kernel waited for.
+    const unsigned int gw = (blockIdx.x * K7_ROWS_THREADS + threadIdx.x) >> 5, nw = (gridDim.x * K7_ROWS_THREADS) >> 5;
+    constexpr unsigned int RUN = 8;
+    for (unsigned int base = gw * RUN; base < nign; base += nw * RUN) {
+        long long run_iv = 0;
+        int run_b = -1;
+        const unsigned int rend = min(base + RUN, nign);
+        for (unsigned int i = base; i < rend; ++i) {
+            const uint2 ent = __ldcg(Q.q + (Q.cap - 1ull - i));
+            const int a = (int)ent.x, b = (int)(ent.y >> 16);
+            if (b != run_b) {   // warp-uniform
+                if (run_b >= 0) {
+                    run_iv = k7_warp_sum_i64(run_iv);
+                    if (lane == 0 && run_iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * run_b), (unsigned long long)run_iv);
+                }
+                run_b = b;
+                run_iv = 0;
+            }
+            const float* src;
+            float* dst;
+            size_t e0, stride = 1;
             if (LEVELS) {
                 int l = 0;
 #pragma unroll
@@ -692,41 +786,45 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
                     if (i2 < spec.num_levels && a >= spec.offset[i2]) l = i2;
                 const int r = a - spec.offset[l], K = spec.cell_anchors;
                 const int cell = r / K, k = r - cell * K;
-                const size_t S = (size_t)LT.S[l];
-                const size_t e0 = ((size_t)b * K * C + (size_t)k * C) * S + (size_t)cell;
-                for (int c = lane; c < C; c += 32) {
-                    csub += k7_neg_exact(__ldg(LT.cls[l] + e0 + (size_t)c * S), nullptr, P.from_logits != 0);
-                    if (GRAD) LT.dcls[l][e0 + (size_t)c * S] = 0.0f;
-                }
+                stride = (size_t)LT.S[l];
+                e0 = ((size_t)b * K * C + (size_t)k * C) * stride + (size_t)cell;
+                src = LT.cls[l];
+                dst = LT.dcls[l];
             } else {
-                const size_t e0 = ((size_t)b * A + a) * (size_t)C;
-                for (int c = lane; c < C; c += 32) {
-                    csub += k7_neg_exact(__ldg(cls + e0 + c), nullptr, P.from_logits != 0);
-                    if (GRAD) dcls[e0 + c] = 0.0f;
+                e0 = ((size_t)b * A + a) * (size_t)C;
+                src = cls;
+                dst = dcls;
+            }
+            float csub = 0.0f;
+            for (int c0 = 0; c0 < C; c0 += 128) {   // four loads per lane in flight
+                float x[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int c = c0 + 32 * u + lane;
+                    x[u] = (c < C) ? __ldg(src + e0 + (size_t)c * stride) : 0.0f;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int c = c0 + 32 * u + lane;
+                    if (c < C) {
+                        csub += k7_neg_exact(x[u], nullptr, P.from_logits != 0);
+                        if (GRAD) dst[e0 + (size_t)c * stride] = 0.0f;
+                    }
                 }
             }
+            // what the stream added for this row, taken out again (this lane's share, 2^-32 fixed point)
+            run_iv += __double2ll_rn(-(double)oma * (double)csub * K7_FIX_ONE);
         }
-
-        // ---- fold: float partials of this thread -> fixed point -> integer sum of the warp -> the image's accumulators
-        if (npos > 0 || nign > 0) {   // block-uniform
-            long long ic = __double2ll_rn(((double)cfix - (double)oma * (double)csub) * K7_FIX_ONE);
-            long long ir = __double2ll_rn((double)rsum * K7_FIX_ONE);
-            ic = k7_warp_sum_i64(ic);
-            ir = k7_warp_sum_i64(ir);
-            if (lane == 0) {
-                if (ic) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b), (unsigned long long)ic);
-                if (ir) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b + 1), (unsigned long long)ir);
-                __threadfence();   // performed before this block's tick of the completion counter
-            }
+        if (run_b >= 0) {
+            run_iv = k7_warp_sum_i64(run_iv);
+            if (lane == 0 && run_iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * run_b), (unsigned long long)run_iv);
         }
-        __syncthreads();   // the queue is rewritten by the next chunk
     }
 
     // ---- the last block to finish reduces
-    if (threadIdx.x == 0) {
-        __threadfence();
-        s_last = atomicAdd(counter, 1u) == gridDim.x - 1u;
-    }
+    __threadfence();   // this thread's accumulator updates are performed before the block's tick
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == gridDim.x - 1u;
     __syncthreads();
     if (!s_last) return;
     __threadfence();
@@ -736,8 +834,8 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
         double c = 0.0;
         for (uint32_t t = lane; t < pipe_slots; t += 32) c += (double)__ldcg(pp + t);
         c = k7_warp_sum_f64(c);
-        const bool any_valid = k7_warp_any_valid(annotations, P.M, b, lane);
         if (lane == 0) {
+            const bool any_valid = Q.img_valid[b] != 0;
             const int n = num_pos[b];
             const double fc = (double)__ldcg(acc + 2 * b) * (1.0 / K7_FIX_ONE);
             const double fr = (double)__ldcg(acc + 2 * b + 1) * (1.0 / K7_FIX_ONE);
@@ -746,7 +844,6 @@ k7_loss_rows_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_cons
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) *counter = 0u;   // re-armed for the next call on this workspace
 
     // ---- batch sums in image order
     double c = 0.0, r = 0.0, nn = 0.0, zero = 0.0;
@@ -904,22 +1001,24 @@ struct K7LossPlan {
     unsigned long long AC[K7_MAX_LEVELS];   // elements per image of each stream
     uint32_t tile0[K7_MAX_LEVELS];
     size_t off_pipe;                        // per-warp slots of the launch
-    size_t off_counter, off_acc, off_cta, total;
+    size_t off_counter, off_acc, off_valid, off_cta, off_queue, total;
     uint32_t cta_stride;
 };
 
-static int k7_pipe_geometry(bool grad, K7PipeGeom* g);
+static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g);
 
 // levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
 static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
                         K7LossPlan* p) {
     p->nseg = 0;
     size_t o = 0;
-    p->off_counter = o;   // the row kernel's block counter
+    p->off_counter = o;   // [0] the serve kernel's block counter, [4], [5] the lengths of the two row queues
     o += 256;
     p->off_acc = o;       // [B][2] fixed-point row accumulators
     o += k7_align_up(sizeof(long long) * 2 * (size_t)B, 256);
-    int rc = k7_pipe_geometry(grad, &p->G);
+    p->off_valid = o;     // [B] the image has an annotation row
+    o += k7_align_up((size_t)B, 256);
+    int rc = k7_pipe_geometry(grad, B, &p->G);
     if (rc) return rc;
     unsigned long long tiles = 0;
     const int nl = levels ? spec->num_levels : 1;
@@ -948,6 +1047,8 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
     o += k7_align_up(sizeof(float) * (size_t)B * (size_t)p->G.grid * K7_PIPE_MAX_CW, 256);
     p->off_cta = o;       // [B][cta_stride] stream partials, one per (image, CTA)
     o += k7_align_up(sizeof(float) * (size_t)B * p->cta_stride, 256);
+    p->off_queue = o;     // [B*A] row queue: positives from the front, ignored rows from the back
+    o += k7_align_up(sizeof(uint2) * (size_t)B * (size_t)A, 256);
     p->total = o;
     return K7_OK;
 }
@@ -972,7 +1073,7 @@ static int k7_env_int(const char* name, int dflt) {
     return atoi(v);
 }
 
-static int k7_pipe_geometry(bool grad, K7PipeGeom* g) {
+static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g) {
     // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass wants long slices (12 warps x
     // 1024 floats: fewer per-slice waits); with gradients the stream is a copy and wants the most
     // warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
@@ -985,7 +1086,8 @@ static int k7_pipe_geometry(bool grad, K7PipeGeom* g) {
     g->slice = (uint32_t)slice;
     g->tile_f = (uint32_t)cw * (uint32_t)slice;
     g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4, 128);
-    const size_t budget = 226 * 1024;
+    const size_t sco_bytes = (grad && B <= K7_PIPE_SCO_MAX) ? k7_align_up(sizeof(float) * (size_t)B, 16) : 0;
+    const size_t budget = 226 * 1024 - sco_bytes;
     int stages = (int)((budget - 64) / ((size_t)g->stage_stride + sizeof(K7TileDesc) + 16));
     const int want = k7_env_int("K7_STAGES", 4);
     if (stages > want) stages = want;
@@ -998,18 +1100,21 @@ static int k7_pipe_geometry(bool grad, K7PipeGeom* g) {
     o = k7_align_up(o, 16);
     g->off_bars = (uint32_t)o;
     o += (size_t)stages * 16;
+    g->off_sco = sco_bytes ? (uint32_t)o : 0u;
+    o += sco_bytes;
     g->smem_bytes = o;
     return K7_OK;
 }
 
 static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls,
                        const float* const* levels, const float* reg, const float* annotations, const int32_t* assign,
-                       const uint64_t* best, const int32_t* num_pos, int B, int A, int C, int M,
+                       const uint64_t* best, int32_t* num_pos, int B, int A, int C, int M,
                        const K7LossParams* params, float* per_image, float* sums, float* dcls, float* const* dlevels,
                        float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
     const bool lv = levels != nullptr;
     const bool grad = dreg != nullptr;
     K7_REQUIRE(reg && annotations && num_pos && params && per_image && sums && workspace, "k7_loss: null argument");
+    K7_REQUIRE(M <= 65535, "k7_loss: M > 65535 annotation rows per image not supported");
     K7_REQUIRE((assign != nullptr) != (best != nullptr), "k7_loss: give either k7_match's assign words or k7_match_scatter's best array");
     K7_REQUIRE(B > 0 && A > 0 && C > 0 && M > 0, "k7_loss: bad shape B=%d A=%d C=%d M=%d", B, A, C, M);
     K7_REQUIRE(B <= 65535, "k7_loss: B > 65535 not supported");
@@ -1058,8 +1163,40 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     P.from_logits = params->from_logits ? 1 : 0;
     P.B = B; P.A = A; P.C = C; P.M = M;
 
-    // counter + accumulators are contiguous at the start of the workspace
+    // counters + accumulators are contiguous at the start of the workspace
     K7_CUDA(cudaMemsetAsync(ws + L.off_counter, 0, L.off_acc - L.off_counter + sizeof(long long) * 2 * (size_t)B, st));
+    K7_CUDA(cudaMemsetAsync(num_pos, 0, sizeof(int32_t) * (size_t)B, st));
+
+    K7AssignSrc SRC;
+    memset(&SRC, 0, sizeof(SRC));
+    SRC.words = assign;
+    SRC.best = reinterpret_cast<const unsigned long long*>(best);
+    SRC.gen = params->match_generation;
+    SRC.neg_thr = params->neg_thr;
+    SRC.pos_thr = params->pos_thr;
+    SRC.words_out = params->assign_out;
+    SRC.consume = params->consume_best ? 1 : 0;
+    K7RowQueues RQ;
+    RQ.q = reinterpret_cast<uint2*>(ws + L.off_queue);
+    RQ.count = counter + 4;
+    RQ.cap = (unsigned long long)B * (unsigned long long)A;
+    RQ.img_valid = ws + L.off_valid;
+    float4* dreg4 = reinterpret_cast<float4*>(dreg);
+    {   // the scan: num_pos, the row queues, the zeros of d(reg)
+        const long long chunks = (long long)B * ((A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK);
+        long long blocks = chunks;
+        const long long cap = 8ll * k7_sm_count();   // eight resident blocks of 256 threads per SM; the rest is looped
+        if (blocks > cap) blocks = cap;
+        const dim3 sgrid((unsigned)blocks);
+        if (grad) {
+            if (best) k7_loss_scan_kernel<true, true><<<sgrid, K7_ROWS_THREADS, 0, st>>>(annotations, SRC, P, RQ, num_pos, dreg4);
+            else      k7_loss_scan_kernel<true, false><<<sgrid, K7_ROWS_THREADS, 0, st>>>(annotations, SRC, P, RQ, num_pos, dreg4);
+        } else {
+            if (best) k7_loss_scan_kernel<false, true><<<sgrid, K7_ROWS_THREADS, 0, st>>>(annotations, SRC, P, RQ, num_pos, dreg4);
+            else      k7_loss_scan_kernel<false, false><<<sgrid, K7_ROWS_THREADS, 0, st>>>(annotations, SRC, P, RQ, num_pos, dreg4);
+        }
+        K7_LAUNCH_CHECK();
+    }
 
     K7LevelTable LT;
     memset(&LT, 0, sizeof(LT));
@@ -1091,7 +1228,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe);
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, annotations, P, G, pipe_partials, cta_partials);
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, RQ.img_valid, P, G, pipe_partials, cta_partials);
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
@@ -1123,45 +1260,24 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
             PR.mailbox[i] = q->mailbox[i];
         }
     }
-    K7AssignSrc SRC;
-    memset(&SRC, 0, sizeof(SRC));
-    SRC.words = assign;
-    SRC.best = reinterpret_cast<const unsigned long long*>(best);
-    SRC.gen = params->match_generation;
-    SRC.neg_thr = params->neg_thr;
-    SRC.pos_thr = params->pos_thr;
-    SRC.words_out = params->assign_out;
-    SRC.consume = params->consume_best ? 1 : 0;
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-    float4* dreg4 = reinterpret_cast<float4*>(dreg);
-    const long long chunks = (long long)B * ((A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK);
-    long long rblocks = chunks;
-    const long long rcap = 8ll * k7_sm_count();   // eight resident blocks of 256 threads per SM; the rest is looped
-    if (rblocks > rcap) rblocks = rcap;
-    const dim3 rgrid((unsigned)rblocks);
-#define K7_ROWS_LAUNCH(GR, PK, SP, LV)                                                                                     \
-    k7_loss_rows_kernel<GR, PK, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg,           \
-                                                                           annotations, SRC, num_pos, P, PR, cta_partials, \
-                                                                           L.cta_stride, acc, counter, per_image, sums,    \
-                                                                           dcls, dreg4)
-#define K7_ROWS_PICK(GR, PK)                                                                   \
-    do {                                                                                       \
-        if (lv) K7_ROWS_LAUNCH(GR, PK, true, true);                                            \
-        else if (spec) K7_ROWS_LAUNCH(GR, PK, true, false);                                    \
-        else K7_ROWS_LAUNCH(GR, PK, false, false);                                             \
-    } while (0)
-    if (grad) { if (best) K7_ROWS_PICK(true, true); else K7_ROWS_PICK(true, false); }
-    else      { if (best) K7_ROWS_PICK(false, true); else K7_ROWS_PICK(false, false); }
-#undef K7_ROWS_PICK
-#undef K7_ROWS_LAUNCH
+    const dim3 rgrid((unsigned)(8 * k7_sm_count()));   // the queue lengths are only known on the device: grid-stride loops
+#define K7_SERVE_LAUNCH(GR, SP, LV)                                                                                      \
+    k7_loss_serve_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
+                                                                        RQ, num_pos, P, PR, cta_partials, L.cta_stride,   \
+                                                                        acc, counter, per_image, sums, dcls, dreg4)
+    if (lv) { if (grad) K7_SERVE_LAUNCH(true, true, true); else K7_SERVE_LAUNCH(false, true, true); }
+    else if (grad) { if (spec) K7_SERVE_LAUNCH(true, true, false); else K7_SERVE_LAUNCH(true, false, false); }
+    else           { if (spec) K7_SERVE_LAUNCH(false, true, false); else K7_SERVE_LAUNCH(false, false, false); }
+#undef K7_SERVE_LAUNCH
     K7_LAUNCH_CHECK();
     return K7_OK;
 }
 
 extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls, const float* reg,
                        const float* annotations, const int32_t* assign, const uint64_t* best,
-                       const int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
+                       int32_t* num_pos, int B, int A, int C, int M, const K7LossParams* params, float* per_image,
                        float* sums, float* dcls, float* dreg, void* workspace, size_t workspace_bytes, void* stream) {
     K7_REQUIRE(cls, "k7_loss: null argument");
     K7_REQUIRE(spec || anchors, "k7_loss: need an anchor spec or an anchor tensor");
@@ -1182,7 +1298,7 @@ extern "C" int k7_loss(const K7AnchorSpec* spec, const float* anchors, int box_o
 
 extern "C" int k7_loss_levels(const K7AnchorSpec* spec, const float* const* levels, const float* reg,
                               const float* annotations, const int32_t* assign, const uint64_t* best,
-                              const int32_t* num_pos, int B, int C, int M, const K7LossParams* params, float* per_image,
+                              int32_t* num_pos, int B, int C, int M, const K7LossParams* params, float* per_image,
                               float* sums, float* const* dlevels, float* dreg, void* workspace, size_t workspace_bytes,
                               void* stream) {
     K7_REQUIRE(spec && levels, "k7_loss_levels: an anchor spec and the level tensors are required");

@@ -84,18 +84,18 @@ def scatter_ok(spec, M: int, neg_thr: float, pos_thr: float) -> bool:
 
 
 def match_scatter(spec, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float):
-    """k7_match_scatter: returns (best [B*A] uint64-as-int64, generation, consume, num_pos [B] int32)."""
+    """k7_match_scatter: returns (best [B*A] uint64-as-int64, generation, consume).  The positives are counted
+    by the loss stage, which walks the array anyway."""
     L.require_cuda(annotations)
     ann = L.as_f32_contig(annotations)
     B, M = ann.shape[0], ann.shape[1]
     dev = ann.device
     best, gen, consume = _WS.best_array(B, A, dev)
-    num_pos = torch.empty(B, dtype=torch.int32, device=dev)
     p = L.K7MatchParams(neg_thr, pos_thr)
     with torch.cuda.device(dev):
         L.check(L.lib().k7_match_scatter(C.byref(spec), L.ptr(ann), B, A, M, C.byref(p), L.ptr(best), gen,
-                                         L.ptr(num_pos), L.stream_ptr(dev)), "k7_match_scatter")
-    return best, gen, consume, num_pos
+                                         L.stream_ptr(dev)), "k7_match_scatter")
+    return best, gen, consume
 
 
 def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
@@ -154,12 +154,13 @@ def _loss_params(*, alpha, beta, target_div, yx_targets, mean_divisor, want_grad
     return p
 
 
-def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets,
+def loss_stage(anchors, cls, reg, ann, assign, num_pos=None, *, alpha, beta, target_div, yx_targets,
                mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
                ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False, peer_reduce=None,
                best=None, assign_out: Optional[torch.Tensor] = None):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
-    The assignment comes as match()'s `assign` words or as match_scatter()'s array:
+    `num_pos` [B] int32 is an OUTPUT (the positives are counted while the assignment is walked); pass a
+    tensor to receive it.  The assignment comes as match()'s `assign` words or as match_scatter()'s array:
     best = (array, generation, consume, neg_thr, pos_thr) with assign=None.
     dreg_zeroed: a [B,A,4] buffer match() already filled with zeros (saves a 16 B/anchor store);
     ignore_bits: accepted for compatibility, unused (ignored rows are handled by the row kernel);
@@ -179,6 +180,8 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos, *, alpha, beta, target_d
     ws = _WS.get("loss", ws_bytes, dev)
     per_image = torch.empty((B, 2), dtype=torch.float32, device=dev)
     sums = torch.empty(4, dtype=torch.float32, device=dev)
+    if num_pos is None:
+        num_pos = torch.empty(B, dtype=torch.int32, device=dev)
     dcls = torch.empty_like(cls) if want_grad else None
     dreg = None
     if want_grad:
@@ -213,10 +216,11 @@ def _assignment(anchor_src, ann, A, cfg, dreg0):
     Anchors from a recipe: ground-truth-first k7_match_scatter; a foreign anchor tensor (or thresholds
     it cannot serve): the exhaustive k7_match, which also zero-fills d(reg) on its way."""
     sp = spec_of(anchor_src)
+    num_pos = torch.empty(ann.shape[0], dtype=torch.int32, device=ann.device)     # written by the loss stage
     if scatter_ok(sp, ann.shape[1], cfg["neg_thr"], cfg["pos_thr"]):
-        arr, gen, consume, num_pos = match_scatter(sp, ann, A, cfg["neg_thr"], cfg["pos_thr"])
+        arr, gen, consume = match_scatter(sp, ann, A, cfg["neg_thr"], cfg["pos_thr"])
         return None, (arr, gen, consume, cfg["neg_thr"], cfg["pos_thr"]), num_pos, None
-    assign, num_pos = match(anchor_src, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
+    assign, _ = match(anchor_src, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
     return assign, None, num_pos, dreg0
 
 
@@ -288,7 +292,7 @@ def _once(ctx):
     ctx.consumed = True
 
 
-def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, target_div, yx_targets, mean_divisor,
+def loss_stage_levels(spec, levels, reg, ann, assign, num_pos=None, *, alpha, beta, target_div, yx_targets, mean_divisor,
                       want_grad, dreg_zeroed: Optional[torch.Tensor] = None, ignore_bits: Optional[torch.Tensor] = None,
                       from_logits: bool = False, peer_reduce=None, best=None):
     """loss_stage on the head's raw per-level NCHW outputs (k7_loss_levels).  Returns
@@ -300,6 +304,8 @@ def loss_stage_levels(spec, levels, reg, ann, assign, num_pos, *, alpha, beta, t
     ws = _WS.get("loss_levels", lib.k7_loss_levels_workspace_bytes(C.byref(spec), B, Cn), dev)
     per_image = torch.empty((B, 2), dtype=torch.float32, device=dev)
     sums = torch.empty(4, dtype=torch.float32, device=dev)
+    if num_pos is None:
+        num_pos = torch.empty(B, dtype=torch.int32, device=dev)
     dlevels = [torch.empty_like(t) for t in levels] if want_grad else None
     dreg = None
     if want_grad:

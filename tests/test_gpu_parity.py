@@ -142,8 +142,9 @@ LOSS_KW = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_t
 def scatter_words(sp, ann, cls, reg, thr, **kw):
     """match_scatter -> k7_loss(best=..., assign_out=...): (words [B,A], num_pos, loss outputs, best array)."""
     B, A, _ = cls.shape
-    arr, gen, consume, num_pos = BL.match_scatter(sp, ann, A, thr[0], thr[1])
+    arr, gen, consume = BL.match_scatter(sp, ann, A, thr[0], thr[1])
     words = torch.empty(B * A, dtype=torch.int32, device=DEV)
+    num_pos = torch.empty(B, dtype=torch.int32, device=DEV)
     out = BL.loss_stage(sp, cls, reg, ann, None, num_pos, best=(arr, gen, consume, thr[0], thr[1]), assign_out=words,
                         mean_divisor=B, **kw)
     return words.view(B, A), num_pos, out, (arr, gen)
@@ -189,18 +190,24 @@ def test_loss_from_words_and_from_best_agree(path):
     B, A, _ = cls.shape
     kw = dict(LOSS_KW, want_grad=True, target_div=(1, 1, 1, 1) if yx else (0.1, 0.1, 0.2, 0.2), yx_targets=yx)
     assign, num_pos = BL.match(sp, ann, A, thr[0], thr[1])
-    a = BL.loss_stage(sp, cls, reg, ann, assign, num_pos, mean_divisor=B, **kw)
+    num_pos1 = torch.empty_like(num_pos)
+    a = BL.loss_stage(sp, cls, reg, ann, assign, num_pos1, mean_divisor=B, **kw)
     _, num_pos2, b, (arr, gen) = scatter_words(sp, ann, cls, reg, thr, **kw)
-    assert torch.equal(num_pos, num_pos2)
+    assert torch.equal(num_pos, num_pos1) and torch.equal(num_pos, num_pos2)
     for x, y in zip(a, b):
         assert torch.equal(x, y)
-    # replay of ONE generation: scatter -> loss(consume) twice on the same array
+    # replay of ONE generation (what a captured CUDA graph does): scatter -> loss(consume), three times on the same
+    # array with the same generation number; the consuming call leaves nothing of that generation behind
     p = L.K7MatchParams(*thr)
     import ctypes as C
+    arr, gen, _ = BL.match_scatter(sp, ann, A, thr[0], thr[1])             # a fresh generation, consumed below
+    BL.loss_stage(sp, cls, reg, ann, None, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
     for _ in range(2):
         L.check(L.lib().k7_match_scatter(C.byref(sp), L.ptr(ann), B, A, ann.shape[1], C.byref(p), L.ptr(arr), gen,
-                                         L.ptr(num_pos2), L.stream_ptr(DEV)), "k7_match_scatter")
-        c = BL.loss_stage(sp, cls, reg, ann, None, num_pos2, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
+                                         L.stream_ptr(DEV)), "k7_match_scatter")
+        num_pos3 = torch.empty_like(num_pos)
+        c = BL.loss_stage(sp, cls, reg, ann, None, num_pos3, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
+        assert torch.equal(num_pos, num_pos3)
         for x, y in zip(a, c):
             assert torch.equal(x, y)
         assert int((arr[:B * A] >> 48 == gen).sum()) == 0        # consumed: nothing of this generation is left

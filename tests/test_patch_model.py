@@ -259,7 +259,7 @@ def test_patched_eval_equals_the_reference_tail(cls):
     assert len(got) == 3 and want[0].numel() > 4                 # a real NMS problem, not the empty triple
     assert torch.equal(got[0], want[0])                          # scores are copies of the class maxima
     assert got[1].dtype == torch.int64 and torch.equal(got[1], want[1])
-    np.testing.assert_allclose(got[2].cpu().numpy(), want[2].cpu().numpy(), rtol=1e-5, atol=1e-4)
+    np.testing.assert_allclose(got[2].detach().cpu().numpy(), want[2].detach().cpu().numpy(), rtol=1e-5, atol=1e-4)
     if cls is KSevenStub:
         again = patched(img)                                     # its default IS the eval branch
         assert torch.equal(again[0], want[0]) and torch.equal(again[1], want[1])

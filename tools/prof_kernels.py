@@ -40,8 +40,8 @@ def main():
 
     def best():
         """A fresh assignment of the production path (every scatter call starts a new generation of the array)."""
-        arr, gen, consume, num_pos = BL.match_scatter(sp, ann, A, *thr)
-        return dict(assign=None, num_pos=num_pos, best=(arr, gen, consume, *thr))
+        arr, gen, consume = BL.match_scatter(sp, ann, A, *thr)
+        return dict(assign=None, num_pos=None, best=(arr, gen, consume, *thr))
 
     def loss(c, want_grad, **extra):
         a = cur[0]

@@ -35,7 +35,8 @@ def main():
     img = torch.empty(B, 3, wl.height, wl.width, device=dev)
     anc = b200det.Anchors(**wl.anchor_kwargs())(img)
     A, C, M = wl.anchors, wl.classes, wl.max_gt
-    arr, gen, consume, num_pos = BL.match_scatter(b200det.spec_of(anc), ann, A, 0.35, 0.45)
+    arr, gen, consume = BL.match_scatter(b200det.spec_of(anc), ann, A, 0.35, 0.45)
+    num_pos = None
     best = (arr, gen, consume, 0.35, 0.45)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
     bf = B * (A * (4 * C + 16) + 20 * M)
