@@ -1415,9 +1415,10 @@ k7_nms_cellorder_kernel(const __grid_constant__ K7NmsArgs P) {
     const int m = P.ccnt[b * K7_NMS_G + c];
     if (m <= 0) return;
     const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
+    const int G = P.cap / K7_NMS_CH;   // chunks of this workspace
     int cnt[K7_NMS_G];
 #pragma unroll
-    for (int c2 = 0; c2 < K7_NMS_G; ++c2) cnt[c2] = P.ccnt[b * K7_NMS_G + c2];
+    for (int c2 = 0; c2 < K7_NMS_G; ++c2) cnt[c2] = c2 < G ? P.ccnt[b * K7_NMS_G + c2] : 0;
     for (int i = tid; i < m; i += K7_NMS_THREADS) {
         const unsigned long long ck = __ldcg(P.ckeyC + oc + (size_t)c * K7_NMS_CH + i);
         int p = i;
@@ -1469,8 +1470,7 @@ k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bo
     k7_pdl_wait();
     if (P.nsel[b] < 0) return;
     int nc = 0;
-#pragma unroll
-    for (int c2 = 0; c2 < K7_NMS_G; ++c2) nc += P.ccnt[b * K7_NMS_G + c2];
+    for (int c2 = 0; c2 < P.cap / K7_NMS_CH; ++c2) nc += P.ccnt[b * K7_NMS_G + c2];
     if ((int)(blockIdx.x * K7_PAIRS_THREADS) >= nc) return;
     if (tid == 0) k7_grid_setup(P.bounds + 4 * b, s_g);
     __syncthreads();
@@ -1580,7 +1580,7 @@ k7_nms_resolve_kernel(const __grid_constant__ K7NmsArgs P, int max_det, uint64_t
     const unsigned int* ge = P.edges + (size_t)b * P.ecap;
     if (staged)
         for (int i = tid; i < E; i += K7_RESOLVE_THREADS) s_e[i] = __ldcg(ge + i);
-    for (;;) {
+    for (int round = 0; round <= n + 1; ++round) {   // every round decides at least the lowest-ranked open box
         __syncthreads();
         const int open = s_open;   // read by everybody between two barriers
         __syncthreads();

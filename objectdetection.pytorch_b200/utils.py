@@ -127,14 +127,20 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
            score_thr: float = 0.05, iou_thr: float = 0.5, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0),
            std=(.1, .1, .2, .2), clip: bool = True, pre_nms_topk: int = 0, max_detections: int = 0,
            cap: Optional[int] = None, sync: bool = True, from_logits: bool = False,
-           class_aware: bool = False) -> BatchDetections:
+           class_aware: bool = False, want_rank: Optional[bool] = None) -> BatchDetections:
     """Fused decode + clip + threshold + sort + NMS for every image of the batch.
     class_aware: suppress only inside a class (torchvision.ops.batched_nms with idxs = labels); the
     reference's own eval tail is class-agnostic (retinanet.py:314), which is the default.
     from_logits: `classifications` are pre-sigmoid logits; scores are torch.sigmoid of the row maxima
     and threshold / label ties are decided on those float32 probabilities, as the reference would.
     `classifications` may also be the LIST of the head's raw per-level NCHW outputs
-    [B, anchors*classes, H_l, W_l] (then `anchors` must come from b200det.Anchors)."""
+    [B, anchors*classes, H_l, W_l] (then `anchors` must come from b200det.Anchors).
+    want_rank: also return survivor_rank (the index torchvision.ops.nms would have returned: one more small
+    kernel for the popcount prefix of the survivor bitmap); default: only when sync=True.
+    sync=False returns at once, count / survivors stay on the device and at most `cap` (default 1024) kept
+    boxes per image are returned - a larger count[b] says how many there were."""
+    if want_rank is None:
+        want_rank = bool(sync)
     levels = list(classifications) if isinstance(classifications, (list, tuple)) else None
     L.require_cuda(regressions)
     reg = L.as_f32_contig(regressions)
@@ -176,7 +182,7 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
         labels = torch.empty((B, capn), dtype=torch.int64, device=dev)
         boxes = torch.empty((B, capn, 4), dtype=torch.float32, device=dev)
         aids = torch.empty((B, capn), dtype=torch.int32, device=dev)
-        ranks = torch.empty((B, capn), dtype=torch.int32, device=dev)
+        ranks = torch.empty((B, capn), dtype=torch.int32, device=dev) if want_rank else None
         L.check(lib.k7_detect_gather(L.ptr(ws), ws.numel(), B, A, Cn, capn, L.ptr(scores), L.ptr(labels),
                                      L.ptr(boxes), L.ptr(aids), L.ptr(ranks), L.stream_ptr(dev)), "k7_detect_gather")
         return scores, labels, boxes, aids, ranks
