@@ -117,6 +117,7 @@ struct K7DetectWs {
     int32_t* clabel;        // [B][cap]
     int32_t* pend;          // [B][cap]
     unsigned int* edges;    // [B][ecap]
+    void* ginfo;            // [B] K7Grid
     size_t bytes, zero_bytes;
     int W32;
     int cap, ecap;          // survivors per image the multi-SM NMS path is sized for; edges per image
@@ -161,6 +162,7 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.clabel = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
     w.pend = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
     w.edges = reinterpret_cast<unsigned int*>(take(sizeof(unsigned int) * (size_t)B * w.ecap));
+    w.ginfo = take(320 * (size_t)B);   // sizeof(K7Grid) <= 320
     w.bytes = o;
     return w;
 }
@@ -280,66 +282,78 @@ k7_score_pipe_kernel(const __grid_constant__ K7AnchorSpec spec, const float* __r
     // take their row from global memory.
     auto drain = [&]() {
         __syncwarp();
-        for (int base = 0; base < qn; base += 32) {
-            if (base + lane >= qn) continue;
-            const uint4 ent = queue[base + lane];
-            const uint32_t b = ent.x & 0x7fffffffu;
-            uint32_t a = ent.y;
-            int idx = (int)(ent.z & 0x7fffffffu);
-            bool tie_scan = (ent.z >> 31) != 0u;   // LOGITS: an earlier class may round to the same probability
-            float m = __uint_as_float(ent.w);
-            if (ent.x >> 31) {
-                tie_scan = true;
-                a = k7_div(ent.y, G.div_c);
-                const int c = (int)(ent.y - a * (uint32_t)C);
-                const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
-                m = -INFINITY;
-                idx = 0;
-#pragma unroll 8
-                for (int q = 0; q < C; ++q) {
-                    const float v = __ldg(row + q);
-                    if (v > m) {
-                        m = v;
-                        idx = q;
-                    }
-                }
-                if (idx != c) continue;
-            }
-            if (LOGITS) {
-                const float p = k7_sigmoid_precise(m);
-                if (!(p > P.score_thr)) continue;   // a report inside the safety margin of logit(thr)
-                // torch.max over the PROBABILITIES returns the first class with the maximal float32 value:
-                // an earlier class with a slightly lower logit may round to the same probability.  Such a
-                // logit lies within 2^-23/(1-p) of m; beyond z = 8 the plateau widens, so every earlier
-                // logit above 8 is checked.
-                if (tie_scan) {   // rare: flagged when the row was reduced in shared memory
+        for (int base = 0; base < qn; base += 32) {   // warp-uniform
+            bool ok = base + lane < qn;
+            uint32_t b = 0u, a = 0u;
+            int idx = 0;
+            float m = 0.0f;
+            if (ok) {
+                const uint4 ent = queue[base + lane];
+                b = ent.x & 0x7fffffffu;
+                a = ent.y;
+                idx = (int)(ent.z & 0x7fffffffu);
+                bool tie_scan = (ent.z >> 31) != 0u;   // LOGITS: an earlier class may round to the same probability
+                m = __uint_as_float(ent.w);
+                if (ent.x >> 31) {
+                    tie_scan = true;
+                    a = k7_div(ent.y, G.div_c);
+                    const int c = (int)(ent.y - a * (uint32_t)C);
                     const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
-                    const float lo = fminf(m - 2e-3f, 8.0f);
-                    for (int q = 0; q < idx; ++q) {
+                    m = -INFINITY;
+                    idx = 0;
+#pragma unroll 8
+                    for (int q = 0; q < C; ++q) {
                         const float v = __ldg(row + q);
-                        if (v >= lo && k7_sigmoid_precise(v) == p) {
+                        if (v > m) {
+                            m = v;
                             idx = q;
-                            break;
                         }
                     }
+                    ok = idx == c;
                 }
-                m = p;
+                if (LOGITS && ok) {
+                    const float p = k7_sigmoid_precise(m);
+                    ok = p > P.score_thr;   // else: a report inside the safety margin of logit(thr)
+                    // torch.max over the PROBABILITIES returns the first class with the maximal float32 value:
+                    // an earlier class with a slightly lower logit may round to the same probability.  Such a
+                    // logit lies within 2^-23/(1-p) of m; beyond z = 8 the plateau widens, so every earlier
+                    // logit above 8 is checked.
+                    if (ok && tie_scan) {   // rare: flagged when the row was reduced in shared memory
+                        const float* row = cls + (size_t)b * G.AC + (size_t)a * C;
+                        const float lo = fminf(m - 2e-3f, 8.0f);
+                        for (int q = 0; q < idx; ++q) {
+                            const float v = __ldg(row + q);
+                            if (v >= lo && k7_sigmoid_precise(v) == p) {
+                                idx = q;
+                                break;
+                            }
+                        }
+                    }
+                    m = p;
+                }
             }
-            float ax1, ay1, ax2, ay2;
-            k7_anchor<FROM_SPEC>(spec, anchors, box_order, (int)a, ax1, ay1, ax2, ay2);
-            const size_t oa = (size_t)b * A + a;
-            const float4 dl = __ldg(reg + oa);
-            K7Box o = (P.decode.variant == K7_DECODE_RETINA)
-                          ? k7_decode_retina(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w, P.decode.mean, P.decode.std)
-                          : k7_decode_effdet(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w);
-            if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
-            box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
-            label_ws[oa] = idx;
-            {   // the survivor's key joins the image's list (arrival order; the sort fixes the order)
-                const int slot = atomicAdd(surv_count + b, 1);
+            // one slot reservation per image and round: the lanes of an image add up (a same-address atomic per
+            // lane serialises in the L2: 512 k of them cost the single-class workload 90 us)
+            const unsigned peers = __match_any_sync(0xffffffffu, ok ? b : (0x80000000u | (uint32_t)lane));
+            if (ok) {
+                const int leader = __ffs(peers) - 1;
+                int slot = 0;
+                if (lane == leader) slot = atomicAdd(surv_count + b, __popc(peers));
+                slot = __shfl_sync(peers, slot, leader) + __popc(peers & ((1u << lane) - 1u));
+                float ax1, ay1, ax2, ay2;
+                k7_anchor<FROM_SPEC>(spec, anchors, box_order, (int)a, ax1, ay1, ax2, ay2);
+                const size_t oa = (size_t)b * A + a;
+                const float4 dl = __ldg(reg + oa);
+                K7Box o = (P.decode.variant == K7_DECODE_RETINA)
+                              ? k7_decode_retina(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w, P.decode.mean, P.decode.std)
+                              : k7_decode_effdet(ax1, ay1, ax2, ay2, dl.x, dl.y, dl.z, dl.w);
+                if (P.decode.clip) o = k7_clip_box(o, P.decode.height, P.decode.width);
+                box_ws[oa] = make_float4(o.x1, o.y1, o.x2, o.y2);
+                label_ws[oa] = idx;
+                // the survivor's key joins the image's list (arrival order; the sort fixes the order)
                 keys0[(size_t)b * A + slot] = ((uint64_t)k7_score_key_desc(m) << 32) | (uint32_t)a;
+                atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
             }
-            atomicOr(bits + (size_t)b * W32 + (a >> 5), 1u << (a & 31));
         }
         __syncwarp();
         qn = 0;
@@ -1180,8 +1194,8 @@ __device__ void k7_fallback_image(int b, int A, float iou_thr, int pre_topk, int
 //                            contiguous and in rank order, a table holds each cell's [start, end);
 //   k7_nms_pairs_kernel      a THREAD per box: IoU > thr needs overlap > thr * own extent in x and in y and
 //                            areas within 1/thr of each other, so the partners of a box lie in the cells
-//                            within (0.5 - t + 0.5/t) own extents of its centre, in the grids of the
-//                            neighbouring binades; candidates ranked before the box are tested with
+//                            within max(1 - t, 1/(2t) - 1/2) own extents of its centre (half an extent at
+//                            t = 0.5), in the grids of the neighbouring binades; candidates ranked before the box are tested with
 //                            torchvision's arithmetic and every hit is an EDGE (box, suppressor);
 //   k7_nms_resolve_kernel    one CTA per image: greedy NMS as a fixed point over the edges.
 // Work is proportional to the pairs that can overlap; nothing of size n^2 exists any more (the round-1
@@ -1292,20 +1306,20 @@ struct K7NmsArgs {
     unsigned int* edges;           // [B][ecap] rank << 16 | suppressor rank
     int32_t* nedge;                // [B]
     int ecap;
+    K7Grid* ginfo;                 // [B] the image's grids (written by the rank kernels, read by the pair kernel)
 };
 
 // ---- chunk sort of the score keys + bounds of the live boxes
-__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_nms_chunksort_kernel(const __grid_constant__ K7NmsArgs P) {
+// The chunk kernels are launched with a grid of a few CTAs per SM that loop over the (image, chunk) items: most
+// items are empty (an image with 850 survivors has one chunk of the eight its workspace could hold), and 2048 CTAs
+// of 1024 threads that only find that out cost 20 us per launch.
+__device__ void k7_nms_chunksort_item(const K7NmsArgs& P, const int b, const int c) {
     __shared__ unsigned long long sk[K7_NMS_CH];
     __shared__ unsigned int s_b[4];
-    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
-    k7_pdl_trigger();
-    k7_pdl_wait();      // the score kernel's keys
+    const int tid = threadIdx.x, lane = tid & 31;
     const int n_all = P.surv_count[b];
     const bool small = n_all <= P.cap && P.thr >= K7_GRID_MIN_THR;
-    if (c == 0 && tid == 0) P.nsel[b] = small ? ((P.pre_topk > 0 && n_all > P.pre_topk) ? P.pre_topk : n_all) : -1;
-    if (!small) return;
+    if (!small || n_all <= K7_NMS_CH) return;   // one chunk: k7_nms_rank_kernel does everything in one CTA
     const int m = min(K7_NMS_CH, n_all - c * K7_NMS_CH);
     if (m <= 0) return;
     const size_t ob = (size_t)b * P.A;
@@ -1341,81 +1355,206 @@ k7_nms_chunksort_kernel(const __grid_constant__ K7NmsArgs P) {
     if (tid < 4 && s_b[tid]) atomicMax(P.bounds + 4 * b + tid, s_b[tid]);
     for (int i = tid; i < m; i += K7_NMS_THREADS) P.keysC[(size_t)b * P.cap + (size_t)c * K7_NMS_CH + i] = sk[i];
 }
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_chunksort_kernel(const __grid_constant__ K7NmsArgs P, int B) {
+    k7_pdl_trigger();
+    k7_pdl_wait();      // the score kernel's keys
+    // boxes in play per image (after pre_nms_topk), -1: the image goes to the single-CTA path
+    for (int b = blockIdx.x * K7_NMS_THREADS + threadIdx.x; b < B; b += gridDim.x * K7_NMS_THREADS) {
+        const int n_all = P.surv_count[b];
+        const bool small = n_all <= P.cap && P.thr >= K7_GRID_MIN_THR;
+        P.nsel[b] = small ? ((P.pre_topk > 0 && n_all > P.pre_topk) ? P.pre_topk : n_all) : -1;
+    }
+    const int G = P.cap / K7_NMS_CH;
+    if (G <= 1) return;
+    for (int item = blockIdx.x; item < G * B; item += gridDim.x) {   // chunk-major: the busy items first, spread over the CTAs
+        k7_nms_chunksort_item(P, item % B, item / B);
+        __syncthreads();
+    }
+}
 
 // ---- ranks, boxes in rank order, (cell, rank) keys sorted per chunk
-__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_nms_rank_kernel(const __grid_constant__ K7NmsArgs P) {
+// cell key of a live box (its grid cell << 32 | rank), ~0 for a box without partners
+__device__ __forceinline__ unsigned long long k7_cell_key(const K7Grid& g, const float4 bx, int rank) {
+    float w, h, ar;
+    if (!k7_box_live(bx, w, h, ar)) return ~0ull;
+    const int cl = k7_grid_class(ar);
+    const float cx = 0.5f * (bx.x + bx.z), cy = 0.5f * (bx.y + bx.w);
+    const int ix = max(0, min(g.gx[cl] - 1, (int)((cx - g.ox) * g.inv_cw[cl])));
+    const int iy = max(0, min(g.gy[cl] - 1, (int)((cy - g.oy) * g.inv_ch[cl])));
+    return ((unsigned long long)(unsigned int)(g.off[cl] + iy * g.gx[cl] + ix) << 32) | (unsigned int)rank;
+}
+
+// Images whose survivors fit ONE chunk (the usual case: a few hundred to 2048 boxes) are served by one CTA
+// from the unsorted keys to the cell table - score sort, ranks, bounds, cell sort, cell order - with nothing
+// but shared memory between the steps.  Larger images: this kernel ranks the chunk-sorted keys against the
+// other chunks (all of the image's keys are staged in shared memory for the binary searches: in global memory
+// a search is eleven dependent trips to the L2) and sorts its chunk's cell keys; k7_nms_cellorder_kernel merges.
+template <bool MULTI>   // two launches: a CTA per one-chunk image, and looping CTAs with the staging buffer for the others
+__device__ void k7_nms_rank_item(const K7NmsArgs& P, const int b, const int c, unsigned long long* s_all /* multi: all chunk-sorted keys */) {
     __shared__ unsigned long long sk[K7_NMS_CH];
     __shared__ K7Grid s_g;
+    __shared__ unsigned int s_b[4];
     __shared__ int s_live;
-    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x;
-    k7_pdl_trigger();
-    k7_pdl_wait();
+    const int tid = threadIdx.x, lane = tid & 31;
     const int n = P.nsel[b];
     if (n < 0) return;
     const int n_all = P.surv_count[b];
-    const int m = min(K7_NMS_CH, n_all - c * K7_NMS_CH);
+    const bool single = n_all <= K7_NMS_CH;
+    if (single == MULTI) {   // the other launch's image
+        if (MULTI && c > 0 && tid == 0) P.ccnt[b * K7_NMS_G + c] = 0;
+        return;
+    }
+    const int m = single ? n_all : min(K7_NMS_CH, n_all - c * K7_NMS_CH);
     if (m <= 0) {
         if (tid == 0) P.ccnt[b * K7_NMS_G + c] = 0;
         return;
     }
-    if (tid == 0) {
-        k7_grid_setup(P.bounds + 4 * b, s_g);
-        s_live = 0;
-    }
-    __syncthreads();
     const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
-    const int nch = (n_all + K7_NMS_CH - 1) / K7_NMS_CH;
     const int N = k7_bitonic_size(m);
-    int live = 0;
-    for (int i = tid; i < N; i += K7_NMS_THREADS) {
-        unsigned long long ck = ~0ull;
-        if (i < m) {
-            const unsigned long long key = __ldcg(P.keysC + oc + (size_t)c * K7_NMS_CH + i);
-            int rank = i;
-            for (int c2 = 0; c2 < nch; ++c2) {
-                if (c2 == c) continue;
-                const int m2 = min(K7_NMS_CH, n_all - c2 * K7_NMS_CH);
-                rank += k7_lower_bound(P.keysC + oc + (size_t)c2 * K7_NMS_CH, m2, key);
-            }
-            if (rank < n) {   // pre_nms_topk drops the rest
+    if (tid == 0) s_live = 0;
+    if (tid < 4) s_b[tid] = 0u;
+    constexpr int PER = K7_NMS_CH / K7_NMS_THREADS;   // keys per thread
+    float4 bxs[PER];
+    int ranks[PER];
+
+    if (!MULTI) {
+        // ---- score sort in place: rank = position
+        for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = (i < m) ? P.keys0[ob + i] : ~0ull;
+        __syncthreads();
+        k7_bitonic_sort_smem(sk, N);
+        float mx = -3.0e38f, nx = -3.0e38f, my = -3.0e38f, ny = -3.0e38f;
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int i = tid + u * K7_NMS_THREADS;
+            ranks[u] = -1;
+            if (i < m && i < n) {   // pre_nms_topk drops the rest
+                const unsigned long long key = sk[i];
                 const float4 bx = __ldg(P.box_ws + ob + (uint32_t)(key & 0xffffffffull));
-                P.keys1[ob + rank] = key;
-                P.rbox[oc + rank] = bx;
+                bxs[u] = bx;
+                ranks[u] = i;
+                P.keys1[ob + i] = key;
+                P.rbox[oc + i] = bx;
                 float w, h, ar;
                 if (k7_box_live(bx, w, h, ar)) {
-                    const int cl = k7_grid_class(ar);
                     const float cx = 0.5f * (bx.x + bx.z), cy = 0.5f * (bx.y + bx.w);
-                    const int ix = max(0, min(s_g.gx[cl] - 1, (int)((cx - s_g.ox) * s_g.inv_cw[cl])));
-                    const int iy = max(0, min(s_g.gy[cl] - 1, (int)((cy - s_g.oy) * s_g.inv_ch[cl])));
-                    ck = ((unsigned long long)(unsigned int)(s_g.off[cl] + iy * s_g.gx[cl] + ix) << 32) | (unsigned int)rank;
-                    ++live;
-                } else {
-                    P.pend[oc + rank] = 0;   // in play, but it has no partner: kept
+                    mx = fmaxf(mx, cx); nx = fmaxf(nx, -cx); my = fmaxf(my, cy); ny = fmaxf(ny, -cy);
                 }
             }
         }
-        sk[i] = ck;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            nx = fmaxf(nx, __shfl_xor_sync(0xffffffffu, nx, o));
+            my = fmaxf(my, __shfl_xor_sync(0xffffffffu, my, o));
+            ny = fmaxf(ny, __shfl_xor_sync(0xffffffffu, ny, o));
+        }
+        if (lane == 0 && mx > -3.0e38f) {
+            atomicMax(&s_b[0], k7_f2ord(mx)); atomicMax(&s_b[1], k7_f2ord(nx));
+            atomicMax(&s_b[2], k7_f2ord(my)); atomicMax(&s_b[3], k7_f2ord(ny));
+        }
+        __syncthreads();   // also: every thread has taken its keys out of sk
+        if (tid == 0) k7_grid_setup(s_b, s_g);
+        __syncthreads();
+        if (tid < (int)(sizeof(K7Grid) / 4)) reinterpret_cast<int*>(P.ginfo + b)[tid] = reinterpret_cast<const int*>(&s_g)[tid];
+    } else {
+        // ---- all chunk-sorted keys of the image -> shared memory; rank = index in the own chunk + lower bounds in the others
+        const int nch = (n_all + K7_NMS_CH - 1) / K7_NMS_CH;
+        for (int i = tid; i < n_all; i += K7_NMS_THREADS) s_all[i] = __ldcg(P.keysC + oc + i);
+        if (tid == 0) k7_grid_setup(P.bounds + 4 * b, s_g);
+        __syncthreads();
+        if (c == 0 && tid < (int)(sizeof(K7Grid) / 4)) reinterpret_cast<int*>(P.ginfo + b)[tid] = reinterpret_cast<const int*>(&s_g)[tid];
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int i = tid + u * K7_NMS_THREADS;
+            ranks[u] = -1;
+            if (i < m) {
+                const unsigned long long key = s_all[c * K7_NMS_CH + i];
+                int rank = i;
+                for (int c2 = 0; c2 < nch; ++c2) {
+                    if (c2 == c) continue;
+                    const unsigned long long* ch = s_all + c2 * K7_NMS_CH;
+                    int lo = 0, hi = min(K7_NMS_CH, n_all - c2 * K7_NMS_CH);
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (ch[mid] < key) lo = mid + 1; else hi = mid;
+                    }
+                    rank += lo;
+                }
+                if (rank < n) {   // pre_nms_topk drops the rest
+                    const float4 bx = __ldg(P.box_ws + ob + (uint32_t)(key & 0xffffffffull));
+                    bxs[u] = bx;
+                    ranks[u] = rank;
+                    P.keys1[ob + rank] = key;
+                    P.rbox[oc + rank] = bx;
+                }
+            }
+        }
+    }
+
+    // ---- cell keys of this CTA's boxes, sorted
+    int live = 0;
+    for (int i = tid; i < N; i += K7_NMS_THREADS) sk[i] = ~0ull;
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+        const int i = tid + u * K7_NMS_THREADS;
+        if (ranks[u] >= 0) {
+            const unsigned long long ck = k7_cell_key(s_g, bxs[u], ranks[u]);
+            sk[i] = ck;
+            if (ck != ~0ull) ++live;
+            else P.pend[oc + ranks[u]] = 0;   // in play, but it has no partner: kept
+        }
     }
     if (live) atomicAdd(&s_live, live);
     __syncthreads();
     k7_bitonic_sort_smem(sk, N);
     const int nl = s_live;   // the live keys sort before the ~0 fillers
-    for (int i = tid; i < nl; i += K7_NMS_THREADS) P.ckeyC[oc + (size_t)c * K7_NMS_CH + i] = sk[i];
     if (tid == 0) P.ccnt[b * K7_NMS_G + c] = nl;
+    if (MULTI) {
+        for (int i = tid; i < nl; i += K7_NMS_THREADS) P.ckeyC[oc + (size_t)c * K7_NMS_CH + i] = sk[i];
+        return;
+    }
+    // ---- one chunk: the sorted position IS the cell-order index
+    uint2* tab = P.ctab + (size_t)b * K7_GRID_CELLS;
+    for (int i = tid; i < nl; i += K7_NMS_THREADS) {
+        const unsigned long long ck = sk[i];
+        const int rank = (int)(unsigned int)(ck & 0xffffffffull);
+        const unsigned int cell = (unsigned int)(ck >> 32);
+        P.cbox[oc + i] = __ldcg(P.rbox + oc + rank);   // written by this CTA (L2)
+        P.crank[oc + i] = rank;
+        if (P.class_aware) P.clabel[oc + i] = __ldg(P.label_ws + ob + (uint32_t)(__ldcg(P.keys1 + ob + rank) & 0xffffffffull));
+        if (i == 0 || (unsigned int)(sk[i - 1] >> 32) != cell) tab[cell].x = (unsigned int)(P.cap - i);
+        if (i == nl - 1 || (unsigned int)(sk[i + 1] >> 32) != cell) tab[cell].y = (unsigned int)(i + 1);
+    }
+}
+template <bool MULTI>
+__global__ void __launch_bounds__(K7_NMS_THREADS, 1)
+k7_nms_rank_kernel(const __grid_constant__ K7NmsArgs P, int B) {
+    extern __shared__ __align__(16) unsigned char dyn_raw[];
+    k7_pdl_trigger();
+    k7_pdl_wait();
+    const int G = MULTI ? P.cap / K7_NMS_CH : 1;
+    for (int item = blockIdx.x; item < G * B; item += gridDim.x) {
+        k7_nms_rank_item<MULTI>(P, item % B, item / B, reinterpret_cast<unsigned long long*>(dyn_raw));
+        __syncthreads();
+    }
 }
 
 // ---- boxes in cell order + the cell table
 __global__ void __launch_bounds__(K7_NMS_THREADS, 1)
-k7_nms_cellorder_kernel(const __grid_constant__ K7NmsArgs P) {
-    const int b = blockIdx.y, c = blockIdx.x, tid = threadIdx.x;
+k7_nms_cellorder_kernel(const __grid_constant__ K7NmsArgs P, int B) {
     k7_pdl_trigger();
     k7_pdl_wait();
-    if (P.nsel[b] < 0) return;
+    const int tid = threadIdx.x;
+    const int G0 = P.cap / K7_NMS_CH;
+    for (int item = blockIdx.x; item < G0 * B; item += gridDim.x) {
+    const int b = item % B, c = item / B;
+    if (P.nsel[b] < 0 || P.surv_count[b] <= K7_NMS_CH) continue;   // one chunk: already in cell order
     const int m = P.ccnt[b * K7_NMS_G + c];
-    if (m <= 0) return;
+    if (m <= 0) continue;
     const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
-    const int G = P.cap / K7_NMS_CH;   // chunks of this workspace
+    const int G = G0;   // chunks of this workspace
     int cnt[K7_NMS_G];
 #pragma unroll
     for (int c2 = 0; c2 < K7_NMS_G; ++c2) cnt[c2] = c2 < G ? P.ccnt[b * K7_NMS_G + c2] : 0;
@@ -1433,6 +1572,7 @@ k7_nms_cellorder_kernel(const __grid_constant__ K7NmsArgs P) {
         uint2* t = P.ctab + (size_t)b * K7_GRID_CELLS + cell;
         atomicMax(&t->x, (unsigned int)(P.cap - p));   // first index of the cell, as cap - index
         atomicMax(&t->y, (unsigned int)(p + 1));       // last index + 1
+    }
     }
 }
 
@@ -1457,67 +1597,221 @@ __device__ __forceinline__ bool k7_nms_suppress_exact(const K7Box& a, float area
 
 // Where the partners of box i can be.  IoU > t  =>  inter > t/(1+t) (A_i + A_j) and A_j > t A_i (inter <= A_j),
 // so inter > t A_i; with inter = iw * ih and ih <= h_i:  iw > t w_i, and in the same way ih > t h_i, iw > t w_j,
-// ih > t h_j.  From iw <= w_i:  w_j < w_i / t.  The centres then satisfy
-//     |cx_j - cx_i| < (w_i + w_j)/2 - iw < w_i (1/2 + 1/(2t) - t) =: k w_i      (and the same in y),
-// and the areas A_j in (t A_i, A_i / t).  All of it is evaluated with t lowered by 1e-4 relative and the radius
-// widened by 1e-2 px, against float32 roundings of 1e-7.
+// ih > t h_j.  With iw <= min(w_i, w_j) that gives w_j in (t w_i, w_i / t), and the centres satisfy
+//     |cx_j - cx_i| <= (w_i + w_j)/2 - iw < (w_i + w_j)/2 - t max(w_i, w_j) <= k w_i,   k = max(1 - t, 1/(2t) - 1/2)
+// (the middle term is largest at w_j = w_i for t >= 1/2 and at w_j = w_i / t below), the same in y, and the areas
+// A_j in (t A_i, A_i / t).  At t = 0.5: centres within HALF an own extent, areas within a factor two.  All of it is
+// evaluated with t lowered by 1e-4 relative and the radius widened by 1e-2 px, against float32 roundings of 1e-7.
+// A CTA takes 256 consecutive boxes of the cell order.  Their partners lie, per class, in a band of grid rows - ONE
+// contiguous run of the cell order: the runs (boxes, ranks, classes) and the rows' cell-table slices are staged in
+// shared memory with coalesced loads, then every thread walks the cells of ITS OWN neighbourhood and tests the boxes
+// that rank before its own - exact neighbourhoods (the work is the ~50 - 150 candidates a box really has), shared-
+// memory latency.  History (profiles/r4g - r4i): a thread walking its cells in global memory spent 600 cycles of L2
+// latency per candidate, twice (127 us for 54 k boxes); a warp testing the union of its lanes' neighbourhoods ran
+// 8 x more tests than needed on small dense images (650 us at 256 x 2000 faces); and an atomicAdd on the image's
+// edge counter per edge serialised in the L2 (10 k edges on 8 addresses cost more than all pair tests): hits now
+// wait in a shared-memory buffer and leave with one reservation per CTA.
 #define K7_PAIRS_THREADS 256
+#define K7_PAIRS_SCAP 2048      // staged candidate boxes
+#define K7_PAIRS_TCAP 1024      // staged cell-table entries
+#define K7_PAIRS_EBUF 1024      // buffered edges
+#define K7_PAIRS_MAXCLS 6       // classes a CTA's boxes can look into: 3 - 4 binades for one box, one more across a boundary
+struct K7PairsCls {
+    int row0, nrows, gx, tab_off, run_lo, run_hi, box_off, pad;
+};
+#define K7_PAIRS_SMEM (K7_PAIRS_SCAP * (sizeof(float4) + 2 * sizeof(int)) + K7_PAIRS_TCAP * sizeof(uint2) + K7_PAIRS_EBUF * sizeof(unsigned int))
 __global__ void __launch_bounds__(K7_PAIRS_THREADS)
-k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bound above */) {
+k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bound above */, int B) {
+    extern __shared__ __align__(16) unsigned char dyn_raw[];
+    float4* s_cbox = reinterpret_cast<float4*>(dyn_raw);
+    int* s_crank = reinterpret_cast<int*>(s_cbox + K7_PAIRS_SCAP);
+    int* s_clab = s_crank + K7_PAIRS_SCAP;
+    uint2* s_tab = reinterpret_cast<uint2*>(s_clab + K7_PAIRS_SCAP);
+    unsigned int* s_edge = reinterpret_cast<unsigned int*>(s_tab + K7_PAIRS_TCAP);
     __shared__ K7Grid s_g;
-    const int b = blockIdx.y, tid = threadIdx.x;
+    __shared__ K7PairsCls s_cls[K7_PAIRS_MAXCLS];
+    __shared__ int s_y0[K7_GRID_NCLS], s_y1[K7_GRID_NCLS];
+    __shared__ int s_clo, s_chi, s_en, s_ok, s_ebase;
+    const int tid = threadIdx.x;
     k7_pdl_trigger();
     k7_pdl_wait();
-    if (P.nsel[b] < 0) return;
-    int nc = 0;
-    for (int c2 = 0; c2 < P.cap / K7_NMS_CH; ++c2) nc += P.ccnt[b * K7_NMS_G + c2];
-    if ((int)(blockIdx.x * K7_PAIRS_THREADS) >= nc) return;
-    if (tid == 0) k7_grid_setup(P.bounds + 4 * b, s_g);
-    __syncthreads();
-    const int p = blockIdx.x * K7_PAIRS_THREADS + tid;
-    if (p >= nc) return;
-    const size_t oc = (size_t)b * P.cap;
-    const float4 mb = __ldcg(P.cbox + oc + p);
-    const int ri = __ldcg(P.crank + oc + p);
-    const int mlabel = P.class_aware ? __ldcg(P.clabel + oc + p) : 0;
-    const K7Box me = {mb.x, mb.y, mb.z, mb.w};
-    const float w = K7_FSUB(mb.z, mb.x), h = K7_FSUB(mb.w, mb.y), marea = K7_FMUL(w, h);
-    const float thr = P.thr, tl = thr * (1.0f - 1e-4f);
-    const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);
-    const float mca = K7_FMUL(c_flt, marea);
-    const float cx = 0.5f * (mb.x + mb.z), cy = 0.5f * (mb.y + mb.w);
-    const float rx = kq * w + 1e-2f, ry = kq * h + 1e-2f;
-    const int clo = k7_grid_class(fmaxf(marea * tl * (1.0f - 1e-5f), 1e-30f));
-    const int chi = k7_grid_class(fminf(marea / tl * (1.0f + 1e-5f), 3.0e38f));
-    const uint2* tab = P.ctab + (size_t)b * K7_GRID_CELLS;
-    unsigned int* edges = P.edges + (size_t)b * P.ecap;
-    int count = 0;
-    for (int cl = clo; cl <= chi; ++cl) {
-        const int gx = s_g.gx[cl], gy = s_g.gy[cl];
-        const float icw = s_g.inv_cw[cl], ich = s_g.inv_ch[cl];
-        const int x0 = max(0, min(gx - 1, (int)floorf((cx - rx - s_g.ox) * icw))), x1 = max(0, min(gx - 1, (int)floorf((cx + rx - s_g.ox) * icw)));
-        const int y0 = max(0, min(gy - 1, (int)floorf((cy - ry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((cy + ry - s_g.oy) * ich)));
-        for (int iy = y0; iy <= y1; ++iy) {
-            for (int ix = x0; ix <= x1; ++ix) {
-                const uint2 se = __ldcg(tab + s_g.off[cl] + iy * gx + ix);
-                if (se.y == 0u) continue;
-                const int q1 = (int)se.y;
-                for (int q = P.cap - (int)se.x; q < q1; ++q) {
-                    const int rj = __ldcg(P.crank + oc + q);
-                    if (rj >= ri) break;                     // a cell's boxes are in rank order: the rest ranks after me
-                    const float4 ob = __ldcg(P.cbox + oc + q);
-                    const float oarea = k7_area(ob.x, ob.y, ob.z, ob.w);
-                    if (!k7_nms_filter(me, mca, ob, K7_FMUL(c_flt, oarea))) continue;
-                    if (P.class_aware && __ldcg(P.clabel + oc + q) != mlabel) continue;
-                    if (!k7_nms_suppress_exact(me, marea, ob, oarea, thr)) continue;
-                    const int slot = atomicAdd(P.nedge + b, 1);
-                    if (slot < P.ecap) edges[slot] = ((unsigned int)ri << 16) | (unsigned int)rj;
-                    ++count;
+    const int per_img = P.cap / K7_PAIRS_THREADS;   // items (256 boxes of the cell order) per image
+    const int BIG = 0x3fffffff;
+    for (int item = blockIdx.x; item < per_img * B; item += gridDim.x) {   // block-uniform; block-major: the busy items first
+        const int blk = item / B, b = item - blk * B;
+        if (P.nsel[b] < 0) continue;
+        int nc = 0;
+        for (int c2 = 0; c2 < P.cap / K7_NMS_CH; ++c2) nc += P.ccnt[b * K7_NMS_G + c2];
+        if (blk * K7_PAIRS_THREADS >= nc) continue;
+        __syncthreads();   // the previous item is done with shared memory
+        if (tid < (int)(sizeof(K7Grid) / 4)) reinterpret_cast<int*>(&s_g)[tid] = reinterpret_cast<const int*>(P.ginfo + b)[tid];
+        if (tid < K7_GRID_NCLS) {
+            s_y0[tid] = BIG;
+            s_y1[tid] = -1;
+        }
+        if (tid == 0) {
+            s_clo = BIG;
+            s_chi = -1;
+            s_en = 0;
+            s_ok = 1;
+        }
+        __syncthreads();
+        const int p = blk * K7_PAIRS_THREADS + tid;
+        const bool valid = p < nc;
+        const size_t oc = (size_t)b * P.cap;
+        const float4 mb = valid ? __ldcg(P.cbox + oc + p) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const int ri = valid ? __ldcg(P.crank + oc + p) : -1;
+        const int mlabel = (valid && P.class_aware) ? __ldcg(P.clabel + oc + p) : 0;
+        const K7Box me = {mb.x, mb.y, mb.z, mb.w};
+        const float w = K7_FSUB(mb.z, mb.x), h = K7_FSUB(mb.w, mb.y), marea = K7_FMUL(w, h);
+        const float thr = P.thr, tl = thr * (1.0f - 1e-4f);
+        const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);
+        const float mca = K7_FMUL(c_flt, marea);
+        const float cx = 0.5f * (mb.x + mb.z), cy = 0.5f * (mb.y + mb.w);
+        const float rx = kq * w + 1e-2f, ry = kq * h + 1e-2f;
+        const int clo = valid ? k7_grid_class(fmaxf(marea * tl * (1.0f - 1e-5f), 1e-30f)) : BIG;
+        const int chi = valid ? k7_grid_class(fminf(marea / tl * (1.0f + 1e-5f), 3.0e38f)) : -1;
+        // ---- the CTA's bands: classes, and per class the rows its boxes look into
+        if (valid) {
+            atomicMin(&s_clo, clo);
+            atomicMax(&s_chi, chi);
+            for (int cl = clo; cl <= chi; ++cl) {
+                const int gy = s_g.gy[cl];
+                const float ich = s_g.inv_ch[cl];
+                atomicMin(&s_y0[cl], max(0, min(gy - 1, (int)floorf((cy - ry - s_g.oy) * ich))));
+                atomicMax(&s_y1[cl], max(0, min(gy - 1, (int)floorf((cy + ry - s_g.oy) * ich))));
+            }
+        }
+        __syncthreads();
+        const int CLO = s_clo, CHI = s_chi;
+        const uint2* tab = P.ctab + (size_t)b * K7_GRID_CELLS;
+        if (tid == 0) {   // layout of the staged table slices
+            int toff = 0;
+            if (CHI - CLO + 1 > K7_PAIRS_MAXCLS) s_ok = 0;
+            for (int cl = CLO; cl <= CHI && cl - CLO < K7_PAIRS_MAXCLS; ++cl) {
+                K7PairsCls& D = s_cls[cl - CLO];
+                D.gx = s_g.gx[cl];
+                D.row0 = s_y0[cl];
+                D.nrows = max(0, s_y1[cl] - s_y0[cl] + 1);
+                D.tab_off = toff;
+                D.run_lo = BIG;
+                D.run_hi = 0;
+                toff += D.nrows * D.gx;
+            }
+            if (toff > K7_PAIRS_TCAP) s_ok = 0;
+        }
+        __syncthreads();
+        const bool staged_tab = s_ok != 0;
+        if (staged_tab) {   // the table slices, and from them each class's run of the cell order
+            for (int cl = CLO; cl <= CHI; ++cl) {
+                K7PairsCls& D = s_cls[cl - CLO];
+                const int ne = D.nrows * D.gx;
+                const uint2* src = tab + s_g.off[cl] + D.row0 * D.gx;
+                int lo = BIG, hi = 0;
+                for (int i = tid; i < ne; i += K7_PAIRS_THREADS) {
+                    const uint2 se = __ldcg(src + i);
+                    s_tab[D.tab_off + i] = se;
+                    if (se.y) {
+                        lo = min(lo, P.cap - (int)se.x);
+                        hi = max(hi, (int)se.y);
+                    }
+                }
+                if (hi) {
+                    atomicMin(&D.run_lo, lo);
+                    atomicMax(&D.run_hi, hi);
                 }
             }
         }
+        __syncthreads();
+        if (tid == 0 && staged_tab) {   // layout of the staged runs
+            int boff = 0;
+            for (int cl = CLO; cl <= CHI; ++cl) {
+                K7PairsCls& D = s_cls[cl - CLO];
+                D.box_off = boff;
+                boff += max(0, D.run_hi - D.run_lo);
+            }
+            if (boff > K7_PAIRS_SCAP) s_ok = 0;
+        }
+        __syncthreads();
+        const bool staged = s_ok != 0;   // else: a pathological item, walked in global memory
+        if (staged) {
+            for (int cl = CLO; cl <= CHI; ++cl) {
+                const K7PairsCls D = s_cls[cl - CLO];
+                const int nb = D.run_hi - D.run_lo;
+                for (int i = tid; i < nb; i += K7_PAIRS_THREADS) {
+                    s_cbox[D.box_off + i] = __ldcg(P.cbox + oc + D.run_lo + i);
+                    s_crank[D.box_off + i] = __ldcg(P.crank + oc + D.run_lo + i);
+                    if (P.class_aware) s_clab[D.box_off + i] = __ldcg(P.clabel + oc + D.run_lo + i);
+                }
+            }
+        }
+        __syncthreads();
+        // ---- every thread walks its own neighbourhood
+        int count = 0;
+        unsigned int* edges = P.edges + (size_t)b * P.ecap;
+        auto hit = [&](const int rj) {
+            const unsigned int e = ((unsigned int)ri << 16) | (unsigned int)rj;
+            const int at = atomicAdd(&s_en, 1);
+            if (at < K7_PAIRS_EBUF) s_edge[at] = e;
+            else {   // the buffer is full (a cluster of duplicates): straight to the list
+                const int slot = atomicAdd(P.nedge + b, 1);
+                if (slot < P.ecap) edges[slot] = e;
+            }
+            ++count;
+        };
+        if (valid) {
+            for (int cl = clo; cl <= chi; ++cl) {
+                const int gx = s_g.gx[cl], gy = s_g.gy[cl];
+                const float icw = s_g.inv_cw[cl], ich = s_g.inv_ch[cl];
+                const int x0 = max(0, min(gx - 1, (int)floorf((cx - rx - s_g.ox) * icw))), x1 = max(0, min(gx - 1, (int)floorf((cx + rx - s_g.ox) * icw)));
+                const int y0 = max(0, min(gy - 1, (int)floorf((cy - ry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((cy + ry - s_g.oy) * ich)));
+                const K7PairsCls D = staged_tab ? s_cls[cl - CLO] : K7PairsCls{};
+                for (int iy = y0; iy <= y1; ++iy) {
+                    // cells (iy, x0 .. x1) are consecutive in the cell order: one run
+                    int lo = BIG, hi = 0;
+                    for (int ix = x0; ix <= x1; ++ix) {
+                        const uint2 se = staged_tab ? s_tab[D.tab_off + (iy - D.row0) * gx + ix] : __ldcg(tab + s_g.off[cl] + iy * gx + ix);
+                        if (se.y) {
+                            lo = min(lo, P.cap - (int)se.x);
+                            hi = max(hi, (int)se.y);
+                        }
+                    }
+                    for (int q = lo; q < hi; ++q) {
+                        int rj, lab = 0;
+                        float4 ob;
+                        if (staged) {
+                            const int i = D.box_off + (q - D.run_lo);
+                            rj = s_crank[i];
+                            if (rj >= ri) continue;                          // only boxes visited before me can suppress me
+                            ob = s_cbox[i];
+                            if (P.class_aware) lab = s_clab[i];
+                        } else {
+                            rj = __ldcg(P.crank + oc + q);
+                            if (rj >= ri) continue;
+                            ob = __ldcg(P.cbox + oc + q);
+                            if (P.class_aware) lab = __ldcg(P.clabel + oc + q);
+                        }
+                        const float oarea = k7_area(ob.x, ob.y, ob.z, ob.w);
+                        if (!k7_nms_filter(me, mca, ob, K7_FMUL(c_flt, oarea))) continue;
+                        if (lab != mlabel) continue;                         // class-aware: other classes never suppress
+                        if (!k7_nms_suppress_exact(me, marea, ob, oarea, thr)) continue;
+                        hit(rj);
+                    }
+                }
+            }
+            P.pend[oc + ri] = count;
+        }
+        __syncthreads();
+        // ---- the CTA's edges leave with one reservation
+        const int en = min(s_en, K7_PAIRS_EBUF);
+        if (tid == 0 && en > 0) s_ebase = atomicAdd(P.nedge + b, en);
+        __syncthreads();
+        if (en > 0) {
+            const int base = s_ebase;
+            for (int i = tid; i < en; i += K7_PAIRS_THREADS)
+                if (base + i < P.ecap) edges[base + i] = s_edge[i];
+        }
     }
-    P.pend[oc + ri] = count;
 }
 
 // ---- Greedy NMS as a fixed point over the edges, one CTA per image.  Box i is REMOVED as soon as one of
@@ -1697,6 +1991,8 @@ static K7NmsArgs k7_nms_args(const K7DetectWs& w, int A, float thr, int pre_topk
     P.label_ws = w.label; P.rbox = w.rbox; P.bounds = w.bounds; P.nsel = w.nsel; P.ccnt = w.ccnt; P.ckeyC = w.ckeyC;
     P.cbox = w.cbox; P.crank = w.crank; P.clabel = w.clabel; P.ctab = w.ctab; P.pend = w.pend; P.edges = w.edges;
     P.nedge = w.nedge; P.ecap = w.ecap;
+    static_assert(sizeof(K7Grid) <= 320 && sizeof(K7Grid) % 4 == 0 && sizeof(K7Grid) / 4 <= K7_PAIRS_THREADS, "K7Grid is copied by one thread per word");
+    P.ginfo = static_cast<K7Grid*>(w.ginfo);
     return P;
 }
 
@@ -1704,13 +2000,21 @@ static int k7_nms_chain(const K7NmsArgs& P, int B, int max_det, uint64_t* kept_k
                         int32_t* counts, int64_t* keep_idx_out, cudaStream_t st) {
     const int G = P.cap / K7_NMS_CH;
     const float tl = P.thr * (1.0f - 1e-4f);
-    const float kq = P.thr >= K7_GRID_MIN_THR ? (0.5f + 0.5f / tl - tl) * (1.0f + 1e-4f) : 0.0f;
+    const float kq = P.thr >= K7_GRID_MIN_THR ? fmaxf(1.0f - tl, 0.5f / tl - 0.5f) * (1.0f + 1e-4f) : 0.0f;
+    const int sms = k7_sm_count();
+    auto grid1 = [&](long long items, int per_sm) { return dim3((unsigned)(items < (long long)per_sm * sms ? (items > 0 ? items : 1) : (long long)per_sm * sms)); };
     k7_pdl_site() = 0;
-    K7_CUDA(k7_launch_pdl(k7_nms_chunksort_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
+    K7_CUDA(k7_launch_pdl(k7_nms_chunksort_kernel, grid1((long long)G * B, 2), dim3(K7_NMS_THREADS), 0, st, P, B));   // also sets nsel
     k7_pdl_site() = 1;
-    K7_CUDA(k7_launch_pdl(k7_nms_rank_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
-    K7_CUDA(k7_launch_pdl(k7_nms_cellorder_kernel, dim3(G, B), dim3(K7_NMS_THREADS), 0, st, P));
-    K7_CUDA(k7_launch_pdl(k7_nms_pairs_kernel, dim3(P.cap / K7_PAIRS_THREADS, B), dim3(K7_PAIRS_THREADS), 0, st, P, kq));
+    K7_CUDA(k7_launch_pdl(k7_nms_rank_kernel<false>, grid1(B, 2), dim3(K7_NMS_THREADS), 0, st, P, B));
+    if (G > 1) {
+        const size_t smem_rank = (size_t)P.cap * sizeof(unsigned long long);   // all keys of a multi-chunk image
+        K7_CUDA(cudaFuncSetAttribute(k7_nms_rank_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rank));
+        K7_CUDA(k7_launch_pdl(k7_nms_rank_kernel<true>, grid1((long long)G * B, 1), dim3(K7_NMS_THREADS), smem_rank, st, P, B));
+        K7_CUDA(k7_launch_pdl(k7_nms_cellorder_kernel, grid1((long long)G * B, 2), dim3(K7_NMS_THREADS), 0, st, P, B));
+    }
+    K7_CUDA(cudaFuncSetAttribute(k7_nms_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_PAIRS_SMEM));
+    K7_CUDA(k7_launch_pdl(k7_nms_pairs_kernel, grid1((long long)(P.cap / K7_PAIRS_THREADS) * B, 3), dim3(K7_PAIRS_THREADS), K7_PAIRS_SMEM, st, P, kq, B));
     K7_CUDA(cudaFuncSetAttribute(k7_nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
     k7_pdl_site() = 2;
     K7_CUDA(k7_launch_pdl(k7_nms_resolve_kernel, dim3(B), dim3(K7_RESOLVE_THREADS), K7_RESOLVE_SMEM, st, P, max_det, kept_key,
