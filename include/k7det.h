@@ -319,6 +319,20 @@ K7_API int k7_nms(const float* boxes, const float* scores, int n, float iou_thr,
 K7_API int k7_batched_nms(const float* boxes, const float* scores, const int64_t* idxs, int n, float iou_thr,
                    int64_t* keep, int32_t* count, void* workspace, size_t workspace_bytes, void* stream);
 
+/* k7_nms for callers that may not allocate device memory (code under CUDA graph capture, serving loops, harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and results as k7_nms, but the scratch is a fixed device array inside the library
+ * (1 MiB, held by every GPU that loads the library until the process exits), so the entry point takes no
+ * workspace and calls no cudaMalloc / cudaFree / allocating routine.  Limit: n <= K7_NMS_STATIC_MAX_N
+ * (= k7_nms_static_max_n()); a larger n returns K7_EINVAL with a message naming the limit.  All calls on one
+ * device share the array: it is cleared where it must start at zero by every call, and two calls that overlap
+ * on the GPU (different streams, no ordering between them) race - serialise them, or use k7_nms with one
+ * workspace per stream. */
+#define K7_NMS_STATIC_MAX_N 4096
+K7_API int k7_nms_static_max_n(void);
+K7_API int k7_nms_static(const float* boxes, const float* scores, int n, float iou_thr,
+                  int64_t* keep, int32_t* count, void* stream);
+
 /* Soft-NMS for one image (Bodla et al., ICCV 2017; SURVEY 8f row 4 "soft variants" - neither the reference nor
  * torchvision has one, so the behaviour is the paper's, restated in oracle/restate.py::soft_nms): repeatedly pick
  * the box with the highest remaining score (ties: lowest index) and decay the scores of the others by their overlap

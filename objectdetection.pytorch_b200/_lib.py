@@ -157,6 +157,8 @@ SYMBOLS = {
     "k7_nms_workspace_bytes": (C.c_size_t, [C.c_int]),
     "k7_nms": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
     "k7_batched_nms": (C.c_int, [_P, _P, _P, C.c_int, C.c_float, _P, _P, _P, C.c_size_t, _P]),
+    "k7_nms_static_max_n": (C.c_int, []),
+    "k7_nms_static": (C.c_int, [_P, _P, C.c_int, C.c_float, _P, _P, _P]),
     "k7_soft_nms": (C.c_int, [_P, _P, C.c_int, C.POINTER(K7SoftNmsParams), _P, _P, _P, _P]),
     "k7_peer_mailbox_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), _P]),
     "k7_peer_mailbox_open": (C.c_int, [_P, C.POINTER(C.c_void_p)]),

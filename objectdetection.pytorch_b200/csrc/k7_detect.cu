@@ -21,6 +21,7 @@
 //      workspace's cap go through k7_fallback_image (one CTA, chunks of 1024 boxes) inside the resolve kernel.
 #include <math.h>
 #include <string.h>
+#include <mutex>
 
 #include "k7_common.cuh"
 
@@ -2244,6 +2245,48 @@ extern "C" int k7_batched_nms(const float* boxes, const float* scores, const int
                               int32_t* count, void* workspace, size_t workspace_bytes, void* stream) {
     K7_REQUIRE(n == 0 || idxs, "k7_batched_nms: null argument");
     return k7_nms_run(boxes, scores, idxs, n, iou_thr, keep, count, workspace, workspace_bytes, stream);
+}
+
+// ------------------------------------------------------------------ k7_nms without a caller workspace
+// For callers that may not allocate (graph capture, serving loops): k7_nms with its scratch in a file-scope device
+// array.  Every GPU that loads the library holds the K7_NMS_STATIC_BYTES below until exit.  The array's name is only
+// a stand-in on the host, so the device address is looked up once per device with cudaGetSymbolAddress (with that
+// device current) and kept.  All calls on one device share the array: calls that overlap on the GPU race.
+#define K7_NMS_STATIC_BYTES (1u << 20)
+static __device__ __align__(256) unsigned char k7_nms_static_scratch[K7_NMS_STATIC_BYTES];
+
+static int k7_nms_static_address(void** out) {
+    static std::mutex mu;
+    static void* addr[64] = {};
+    int dev = -1;
+    K7_CUDA(cudaGetDevice(&dev));
+    K7_REQUIRE(dev >= 0 && dev < 64, "k7_nms_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        K7_CUDA(cudaGetSymbolAddress(&p, k7_nms_static_scratch));
+        K7_REQUIRE(p != nullptr, "k7_nms_static: no device address for the scratch array");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return K7_OK;
+}
+
+extern "C" int k7_nms_static_max_n(void) { return K7_NMS_STATIC_MAX_N; }
+
+extern "C" int k7_nms_static(const float* boxes, const float* scores, int n, float iou_thr, int64_t* keep, int32_t* count,
+                             void* stream) {
+    static_assert(K7_NMS_STATIC_BYTES % 256 == 0, "scratch size");
+    K7_REQUIRE(n <= K7_NMS_STATIC_MAX_N, "k7_nms_static: n=%d exceeds the built-in scratch (at most %d boxes); use k7_nms",
+               n, K7_NMS_STATIC_MAX_N);
+    const size_t need = k7_nms_workspace_bytes(K7_NMS_STATIC_MAX_N);
+    K7_REQUIRE(need <= K7_NMS_STATIC_BYTES, "k7_nms_static: scratch array of %u bytes is smaller than the %zu needed",
+               K7_NMS_STATIC_BYTES, need);
+    void* scratch = nullptr;
+    int rc = k7_nms_static_address(&scratch);
+    if (rc) return rc;
+    // k7_nms_run clears the part of the scratch that must start at zero (counters, bounds, bit rows, cell tables).
+    return k7_nms_run(boxes, scores, nullptr, n, iou_thr, keep, count, scratch, K7_NMS_STATIC_BYTES, stream);
 }
 
 // ------------------------------------------------------------------ Soft-NMS ("soft variants")
