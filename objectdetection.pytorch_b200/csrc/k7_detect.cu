@@ -1288,6 +1288,7 @@ __device__ __forceinline__ int k7_lower_bound(const uint64_t* __restrict__ keys,
 struct K7NmsArgs {
     int A, cap, pre_topk, class_aware;
     float thr;
+    int brute_n;                   // images with at most this many survivors: all pairs are tested (k7_nms_brute_kernel), no grid
     const int32_t* surv_count;     // [B] survivors
     uint64_t* keys0;               // [B][A] survivor keys, in arrival order
     uint64_t* keysC;               // [B][cap] chunk-sorted keys
@@ -1450,6 +1451,10 @@ __device__ void k7_nms_rank_item(const K7NmsArgs& P, const int b, const int c, u
             my = fmaxf(my, __shfl_xor_sync(0xffffffffu, my, o));
             ny = fmaxf(ny, __shfl_xor_sync(0xffffffffu, ny, o));
         }
+        if (n_all <= P.brute_n) {   // few boxes: k7_nms_brute_kernel tests all pairs, no cells needed
+            if (tid == 0) P.ccnt[b * K7_NMS_G] = 0;
+            return;
+        }
         if (lane == 0 && mx > -3.0e38f) {
             atomicMax(&s_b[0], k7_f2ord(mx)); atomicMax(&s_b[1], k7_f2ord(nx));
             atomicMax(&s_b[2], k7_f2ord(my)); atomicMax(&s_b[3], k7_f2ord(ny));
@@ -1596,6 +1601,23 @@ __device__ __forceinline__ bool k7_nms_suppress_exact(const K7Box& a, float area
     return k7_nms_suppress(a, area_a, o, area_b, thr);
 }
 
+// The decision with the division only where it matters.  Besides the necessary condition above there is a
+// SUFFICIENT one: inter > K * (fl(c*area_i) + fl(c*area_j)) with K = 1.0000221 means
+// inter > thr/(1+thr) * (1 + 1.19e-5) * (area_i + area_j), i.e. inter / u > thr * (1 + 1.19e-5) for the real union
+// u = area_i + area_j - inter >= (area_i + area_j)/2 (inter <= min(area_i, area_j) holds for the rounded values
+// too: rounding is monotone); the two roundings of u (<= 2^-21 of u) and the one of the quotient (2^-24) cannot
+// bring it down to thr.  An overflowed inter is left to the exact test (inf / (inf - inf) is NaN: kept).  Dense
+// clusters pass the filter by the thousand; only pairs within 2.2e-5 of the threshold reach the division.
+__device__ __forceinline__ bool k7_nms_decide(const K7Box& a, float area_a, float ca, const float4 b, float cb, float thr) {
+    const float w = K7_FSUB(fminf(a.x2, b.z), fmaxf(a.x1, b.x));
+    const float h = K7_FSUB(fminf(a.y2, b.w), fmaxf(a.y1, b.y));
+    if (!((w > 0.0f) && (h > 0.0f))) return false;
+    const float inter = K7_FMUL(w, h), s = K7_FADD(ca, cb);
+    if (!(inter > s)) return false;
+    if (inter > K7_FMUL(s, 1.0000221f) && inter <= 3.0e38f) return true;
+    return k7_nms_suppress_exact(a, area_a, b, k7_area(b.x, b.y, b.z, b.w), thr);
+}
+
 // Where the partners of box i can be.  IoU > t  =>  inter > t/(1+t) (A_i + A_j) and A_j > t A_i (inter <= A_j),
 // so inter > t A_i; with inter = iw * ih and ih <= h_i:  iw > t w_i, and in the same way ih > t h_i, iw > t w_j,
 // ih > t h_j.  With iw <= min(w_i, w_j) that gives w_j in (t w_i, w_i / t), and the centres satisfy
@@ -1615,12 +1637,14 @@ __device__ __forceinline__ bool k7_nms_suppress_exact(const K7Box& a, float area
 #define K7_PAIRS_THREADS 256
 #define K7_PAIRS_SCAP 2048      // staged candidate boxes
 #define K7_PAIRS_TCAP 1024      // staged cell-table entries
-#define K7_PAIRS_EBUF 1024      // buffered edges
+#define K7_PAIRS_EBUF 2048      // buffered edges, split between the groups
+#define K7_PAIRS_GW 8           // lanes that share a box
 #define K7_PAIRS_MAXCLS 6       // classes a CTA's boxes can look into: 3 - 4 binades for one box, one more across a boundary
 struct K7PairsCls {
     int row0, nrows, gx, tab_off, run_lo, run_hi, box_off, pad;
 };
-#define K7_PAIRS_SMEM (K7_PAIRS_SCAP * (sizeof(float4) + 2 * sizeof(int)) + K7_PAIRS_TCAP * sizeof(uint2) + K7_PAIRS_EBUF * sizeof(unsigned int))
+#define K7_PAIRS_SMEM (K7_PAIRS_SCAP * (sizeof(float4) + 2 * sizeof(int)) + K7_PAIRS_TCAP * sizeof(uint2) + K7_PAIRS_EBUF * sizeof(unsigned int) + \
+                       K7_PAIRS_THREADS * (sizeof(float4) + 2 * sizeof(int) + sizeof(uint2)))
 __global__ void __launch_bounds__(K7_PAIRS_THREADS)
 k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bound above */, int B) {
     extern __shared__ __align__(16) unsigned char dyn_raw[];
@@ -1629,10 +1653,14 @@ k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bo
     int* s_clab = s_crank + K7_PAIRS_SCAP;
     uint2* s_tab = reinterpret_cast<uint2*>(s_clab + K7_PAIRS_SCAP);
     unsigned int* s_edge = reinterpret_cast<unsigned int*>(s_tab + K7_PAIRS_TCAP);
+    float4* s_mb = reinterpret_cast<float4*>(s_edge + K7_PAIRS_EBUF);       // the CTA's own boxes
+    uint2* s_grun = reinterpret_cast<uint2*>(s_mb + K7_PAIRS_THREADS);      // run tables of the groups (32 entries per warp)
+    int* s_mri = reinterpret_cast<int*>(s_grun + K7_PAIRS_THREADS);
+    int* s_mlab = s_mri + K7_PAIRS_THREADS;
     __shared__ K7Grid s_g;
     __shared__ K7PairsCls s_cls[K7_PAIRS_MAXCLS];
     __shared__ int s_y0[K7_GRID_NCLS], s_y1[K7_GRID_NCLS];
-    __shared__ int s_clo, s_chi, s_en, s_ok, s_ebase;
+    __shared__ int s_clo, s_chi, s_ok;
     const int tid = threadIdx.x;
     k7_pdl_trigger();
     k7_pdl_wait();
@@ -1653,7 +1681,6 @@ k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bo
         if (tid == 0) {
             s_clo = BIG;
             s_chi = -1;
-            s_en = 0;
             s_ok = 1;
         }
         __syncthreads();
@@ -1663,13 +1690,11 @@ k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bo
         const float4 mb = valid ? __ldcg(P.cbox + oc + p) : make_float4(0.f, 0.f, 0.f, 0.f);
         const int ri = valid ? __ldcg(P.crank + oc + p) : -1;
         const int mlabel = (valid && P.class_aware) ? __ldcg(P.clabel + oc + p) : 0;
-        const K7Box me = {mb.x, mb.y, mb.z, mb.w};
-        const float w = K7_FSUB(mb.z, mb.x), h = K7_FSUB(mb.w, mb.y), marea = K7_FMUL(w, h);
+        const float h = K7_FSUB(mb.w, mb.y), marea = K7_FMUL(K7_FSUB(mb.z, mb.x), h);
         const float thr = P.thr, tl = thr * (1.0f - 1e-4f);
         const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);
-        const float mca = K7_FMUL(c_flt, marea);
-        const float cx = 0.5f * (mb.x + mb.z), cy = 0.5f * (mb.y + mb.w);
-        const float rx = kq * w + 1e-2f, ry = kq * h + 1e-2f;
+        const float cy = 0.5f * (mb.y + mb.w);
+        const float ry = kq * h + 1e-2f;
         const int clo = valid ? k7_grid_class(fmaxf(marea * tl * (1.0f - 1e-5f), 1e-30f)) : BIG;
         const int chi = valid ? k7_grid_class(fminf(marea / tl * (1.0f + 1e-5f), 3.0e38f)) : -1;
         // ---- the CTA's bands: classes, and per class the rows its boxes look into
@@ -1747,70 +1772,248 @@ k7_nms_pairs_kernel(const __grid_constant__ K7NmsArgs P, float kq /* k of the bo
             }
         }
         __syncthreads();
-        // ---- every thread walks its own neighbourhood
-        int count = 0;
+        // ---- groups of K7_PAIRS_GW lanes take the CTA's boxes one at a time (all control flow is uniform in a group)
+        s_mb[tid] = mb;
+        s_mri[tid] = ri;
+        s_mlab[tid] = mlabel;
+        __syncthreads();
+        constexpr int GW = K7_PAIRS_GW, NG = 32 / GW, GBUF = K7_PAIRS_EBUF / ((K7_PAIRS_THREADS / 32) * NG);
+        const int lane = tid & 31, warp = tid >> 5, gl = lane & (GW - 1), grp = lane / GW;
+        const unsigned int gmask = (GW == 32) ? 0xffffffffu : (((1u << GW) - 1u) << (grp * GW));
+        const unsigned int lt_mask = ((1u << lane) - 1u) & gmask;     // the group's lanes below mine
+        unsigned int* gbuf = s_edge + (warp * NG + grp) * GBUF;
+        uint2* grun = s_grun + (warp * NG + grp) * GW;                // the group's runs: {start index, inclusive prefix}
         unsigned int* edges = P.edges + (size_t)b * P.ecap;
-        auto hit = [&](const int rj) {
-            const unsigned int e = ((unsigned int)ri << 16) | (unsigned int)rj;
-            const int at = atomicAdd(&s_en, 1);
-            if (at < K7_PAIRS_EBUF) s_edge[at] = e;
-            else {   // the buffer is full (a cluster of duplicates): straight to the list
-                const int slot = atomicAdd(P.nedge + b, 1);
-                if (slot < P.ecap) edges[slot] = e;
-            }
-            ++count;
+        int fill = 0;                                                 // group-uniform
+        auto flush = [&]() {
+            int base = 0;
+            __syncwarp(gmask);            // the lanes' buffered edges are visible
+            if (gl == 0) base = atomicAdd(P.nedge + b, fill);
+            base = __shfl_sync(gmask, base, grp * GW);
+            for (int i = gl; i < fill; i += GW)
+                if (base + i < P.ecap) edges[base + i] = gbuf[i];
+            __syncwarp(gmask);
+            fill = 0;
         };
-        if (valid) {
-            for (int cl = clo; cl <= chi; ++cl) {
-                const int gx = s_g.gx[cl], gy = s_g.gy[cl];
-                const float icw = s_g.inv_cw[cl], ich = s_g.inv_ch[cl];
-                const int x0 = max(0, min(gx - 1, (int)floorf((cx - rx - s_g.ox) * icw))), x1 = max(0, min(gx - 1, (int)floorf((cx + rx - s_g.ox) * icw)));
-                const int y0 = max(0, min(gy - 1, (int)floorf((cy - ry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((cy + ry - s_g.oy) * ich)));
-                const K7PairsCls D = staged_tab ? s_cls[cl - CLO] : K7PairsCls{};
-                for (int iy = y0; iy <= y1; ++iy) {
-                    // cells (iy, x0 .. x1) are consecutive in the cell order: one run
-                    int lo = BIG, hi = 0;
-                    for (int ix = x0; ix <= x1; ++ix) {
-                        const uint2 se = staged_tab ? s_tab[D.tab_off + (iy - D.row0) * gx + ix] : __ldcg(tab + s_g.off[cl] + iy * gx + ix);
-                        if (se.y) {
-                            lo = min(lo, P.cap - (int)se.x);
-                            hi = max(hi, (int)se.y);
+        for (int it = 0; it < GW; ++it) {   // 32 boxes per warp, NG at a time
+            const int q = (warp << 5) + it * NG + grp;
+            const int bri = s_mri[q];
+            if (bri < 0) continue;          // group-uniform
+            const float4 bb = s_mb[q];
+            const int blabel = s_mlab[q];
+            const K7Box me2 = {bb.x, bb.y, bb.z, bb.w};
+            const float bw = K7_FSUB(bb.z, bb.x), bh = K7_FSUB(bb.w, bb.y), barea = K7_FMUL(bw, bh);
+            const float bca = K7_FMUL(c_flt, barea);
+            const float bcx = 0.5f * (bb.x + bb.z), bcy = 0.5f * (bb.y + bb.w);
+            const float brx = kq * bw + 1e-2f, bry = kq * bh + 1e-2f;
+            const int bclo = k7_grid_class(fmaxf(barea * tl * (1.0f - 1e-5f), 1e-30f));
+            const int bchi = k7_grid_class(fminf(barea / tl * (1.0f + 1e-5f), 3.0e38f));
+            int R = 0;                      // row runs of the neighbourhood: one per (class, grid row)
+            for (int cl = bclo; cl <= bchi; ++cl) {
+                const int gy = s_g.gy[cl];
+                const float ich = s_g.inv_ch[cl];
+                const int y0 = max(0, min(gy - 1, (int)floorf((bcy - bry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((bcy + bry - s_g.oy) * ich)));
+                R += y1 - y0 + 1;
+            }
+            int count = 0;
+            for (int r0 = 0; r0 < R; r0 += GW) {
+                // ---- my row run: cells (iy, x0 .. x1) of one class are consecutive in the cell order
+                int lo = BIG, hi = 0, start = 0;
+                {
+                    int rr = r0 + gl;
+                    for (int cl = bclo; cl <= bchi; ++cl) {
+                        const int gx = s_g.gx[cl], gy = s_g.gy[cl];
+                        const float icw = s_g.inv_cw[cl], ich = s_g.inv_ch[cl];
+                        const int y0 = max(0, min(gy - 1, (int)floorf((bcy - bry - s_g.oy) * ich))), y1 = max(0, min(gy - 1, (int)floorf((bcy + bry - s_g.oy) * ich)));
+                        const int nrows = y1 - y0 + 1;
+                        if (rr >= nrows) {
+                            rr -= nrows;
+                            continue;
                         }
-                    }
-                    for (int q = lo; q < hi; ++q) {
-                        int rj, lab = 0;
-                        float4 ob;
-                        if (staged) {
-                            const int i = D.box_off + (q - D.run_lo);
-                            rj = s_crank[i];
-                            if (rj >= ri) continue;                          // only boxes visited before me can suppress me
-                            ob = s_cbox[i];
-                            if (P.class_aware) lab = s_clab[i];
-                        } else {
-                            rj = __ldcg(P.crank + oc + q);
-                            if (rj >= ri) continue;
-                            ob = __ldcg(P.cbox + oc + q);
-                            if (P.class_aware) lab = __ldcg(P.clabel + oc + q);
+                        const int iy = y0 + rr;
+                        const int x0 = max(0, min(gx - 1, (int)floorf((bcx - brx - s_g.ox) * icw))), x1 = max(0, min(gx - 1, (int)floorf((bcx + brx - s_g.ox) * icw)));
+                        const K7PairsCls D = staged_tab ? s_cls[cl - CLO] : K7PairsCls{};
+                        for (int ix = x0; ix <= x1; ++ix) {
+                            const uint2 se = staged_tab ? s_tab[D.tab_off + (iy - D.row0) * gx + ix] : __ldcg(tab + s_g.off[cl] + iy * gx + ix);
+                            if (se.y) {
+                                lo = min(lo, P.cap - (int)se.x);
+                                hi = max(hi, (int)se.y);
+                            }
                         }
-                        const float oarea = k7_area(ob.x, ob.y, ob.z, ob.w);
-                        if (!k7_nms_filter(me, mca, ob, K7_FMUL(c_flt, oarea))) continue;
-                        if (lab != mlabel) continue;                         // class-aware: other classes never suppress
-                        if (!k7_nms_suppress_exact(me, marea, ob, oarea, thr)) continue;
-                        hit(rj);
+                        start = staged ? D.box_off + (lo - D.run_lo) : lo;
+                        break;
                     }
                 }
+                const int len = max(0, hi - lo);
+                int inc = len;
+#pragma unroll
+                for (int o = 1; o < GW; o <<= 1) {
+                    const int t = __shfl_up_sync(gmask, inc, o, GW);
+                    if (gl >= o) inc += t;
+                }
+                const int T = __shfl_sync(gmask, inc, GW - 1, GW);
+                if (T == 0) continue;       // group-uniform
+                __syncwarp(gmask);          // the previous pass is done with the run table
+                grun[gl] = make_uint2((unsigned int)start, (unsigned int)inc);
+                __syncwarp(gmask);
+                // ---- the T candidates of this pass, cut into GW equal parts
+                int t = (int)(((long long)T * gl) / GW);
+                const int t_end = (int)(((long long)T * (gl + 1)) / GW);
+                int r = 0;
+                while (r < GW - 1 && (int)grun[r].y <= t) ++r;
+                int run_end = (int)grun[r].y;
+                int idx = (int)grun[r].x + (t - (r ? (int)grun[r - 1].y : 0));
+                const int steps = (T + GW - 1) / GW;
+                for (int sidx = 0; sidx < steps; ++sidx) {   // group-uniform trip count
+                    bool hit = false;
+                    int rj = 0;
+                    if (t < t_end) {
+                        float4 ob;
+                        int lab = 0;
+                        if (staged) {
+                            rj = s_crank[idx];
+                            ob = s_cbox[idx];
+                            if (P.class_aware) lab = s_clab[idx];
+                        } else {
+                            rj = __ldcg(P.crank + oc + idx);
+                            ob = __ldcg(P.cbox + oc + idx);
+                            if (P.class_aware) lab = __ldcg(P.clabel + oc + idx);
+                        }
+                        // only boxes visited before mine can suppress it; class-aware: other classes never do
+                        hit = rj < bri && lab == blabel &&
+                              k7_nms_decide(me2, barea, bca, ob, K7_FMUL(c_flt, k7_area(ob.x, ob.y, ob.z, ob.w)), thr);
+                        ++t;
+                        ++idx;
+                        if (t == run_end && t < t_end) {   // on to the next run that has boxes
+                            do ++r; while (r < GW - 1 && (int)grun[r].y <= t);
+                            run_end = (int)grun[r].y;
+                            idx = (int)grun[r].x;
+                        }
+                    }
+                    const unsigned int m = __ballot_sync(gmask, hit);
+                    if (m == 0u) continue;
+                    const int c = __popc(m);
+                    if (fill + c > GBUF) flush();
+                    if (hit) gbuf[fill + __popc(m & lt_mask)] = ((unsigned int)bri << 16) | (unsigned int)rj;
+                    fill += c;
+                    count += c;
+                }
             }
-            P.pend[oc + ri] = count;
+            if (gl == 0) P.pend[oc + bri] = count;
+        }
+        __syncwarp(gmask);
+        if (fill > 0) flush();
+    }
+}
+
+// ---- pair tests for images with few boxes (n <= brute_n <= 2048, the usual detector image: a few hundred
+// survivors).  All n(n-1)/2 pairs are cheaper than building cells: 345 k tests for 831 boxes, spread over 13 CTAs.
+// A CTA takes 64 consecutive ranks; the boxes ranked before its last row wait in shared memory.  A thread owns a
+// row and every fourth 64-candidate WORD of its suppression bit row (a warp's lanes share the candidate: one
+// broadcast load per test); the word is built in a register, so a test is ~16 instructions and no atomic - the
+// first version appended every hit to a buffer (one shared-memory atomic per warp and test with a hit, and a
+// global one once 2048 edges were in: 67 us for 64 x 831 boxes, ten times the arithmetic).  The bit rows then
+// become edges of the format k7_nms_pairs_kernel writes: row counts -> scan -> ONE reservation of the exact size.
+// Same filter and exact test as the grid kernel; blocks with many candidates are handed out first.
+#define K7_BRUTE_N 1024          // default brute_n
+#define K7_BRUTE_THREADS 256
+#define K7_BRUTE_ROWS 64
+#define K7_BRUTE_PARTS (K7_BRUTE_THREADS / K7_BRUTE_ROWS)
+static size_t k7_brute_smem(int brute_n) {
+    const size_t ncap = (size_t)(brute_n + K7_BRUTE_ROWS - 1) / K7_BRUTE_ROWS * K7_BRUTE_ROWS;
+    return ncap * (sizeof(float4) + sizeof(float) + sizeof(int)) + (size_t)K7_BRUTE_ROWS * (ncap / 64 + 1) * sizeof(unsigned long long);
+}
+__global__ void __launch_bounds__(K7_BRUTE_THREADS)
+k7_nms_brute_kernel(const __grid_constant__ K7NmsArgs P, int B) {
+    extern __shared__ __align__(16) unsigned char dyn_raw[];   // k7_brute_smem(brute_n) bytes
+    const int ncap = (P.brute_n + K7_BRUTE_ROWS - 1) / K7_BRUTE_ROWS * K7_BRUTE_ROWS;
+    const int pitch = ncap / 64 + 1;                           // u64 words per bit row (+1: rows fall on different banks)
+    float4* s_box = reinterpret_cast<float4*>(dyn_raw);
+    unsigned long long* s_mask = reinterpret_cast<unsigned long long*>(s_box + ncap);
+    float* s_ca = reinterpret_cast<float*>(s_mask + K7_BRUTE_ROWS * pitch);
+    int* s_lab = reinterpret_cast<int*>(s_ca + ncap);
+    __shared__ int s_cnt[K7_BRUTE_ROWS], s_off[K7_BRUTE_ROWS];
+    __shared__ int s_ebase;
+    const int tid = threadIdx.x, lane = tid & 31;
+    k7_pdl_trigger();
+    k7_pdl_wait();
+    const int per_img = ncap / K7_BRUTE_ROWS;
+    const float thr = P.thr;
+    const float c_flt = thr / (1.0f + thr) * (1.0f - 1e-5f);
+    for (int item = blockIdx.x; item < per_img * B; item += gridDim.x) {   // block-uniform
+        const int blk = per_img - 1 - item / B, b = item % B;              // the longest rows first
+        const int n = P.nsel[b];
+        if (n < 0 || P.surv_count[b] > P.brute_n) continue;
+        const int i0 = blk * K7_BRUTE_ROWS;
+        if (i0 >= n) continue;
+        const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
+        const int nj = min(n, i0 + K7_BRUTE_ROWS);
+        __syncthreads();   // the previous item is done with shared memory
+        for (int j = tid; j < nj; j += K7_BRUTE_THREADS) {
+            const float4 bx = __ldcg(P.rbox + oc + j);
+            s_box[j] = bx;
+            s_ca[j] = K7_FMUL(c_flt, k7_area(bx.x, bx.y, bx.z, bx.w));
+            if (P.class_aware) s_lab[j] = __ldg(P.label_ws + ob + (uint32_t)(__ldcg(P.keys1 + ob + j) & 0xffffffffull));
         }
         __syncthreads();
-        // ---- the CTA's edges leave with one reservation
-        const int en = min(s_en, K7_PAIRS_EBUF);
-        if (tid == 0 && en > 0) s_ebase = atomicAdd(P.nedge + b, en);
+        const int r = tid & (K7_BRUTE_ROWS - 1), ri = i0 + r, part = tid / K7_BRUTE_ROWS;
+        const bool row = ri < n;
+        const int nw = blk + 1;   // words 0 .. blk hold the candidates ranked before the CTA's rows
+        {
+            const float4 mb = row ? s_box[ri] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const K7Box me = {mb.x, mb.y, mb.z, mb.w};
+            const float marea = k7_area(mb.x, mb.y, mb.z, mb.w), mca = row ? s_ca[ri] : 0.0f;
+            const int mlabel = (row && P.class_aware) ? s_lab[ri] : 0;
+            const int rlast = min(n, (ri | 31));   // warp-uniform: candidates below the warp's last row
+            for (int w = part; w < nw; w += K7_BRUTE_PARTS) {
+                unsigned long long word = 0ull;
+                const int j0 = w << 6, j1 = min(j0 + 64, rlast);
+                for (int rj = j0; rj < j1; ++rj) {
+                    const float4 cb = s_box[rj];                               // one address per warp: a broadcast
+                    bool hit = rj < ri && k7_nms_decide(me, marea, mca, cb, s_ca[rj], thr);
+                    if (P.class_aware) hit = hit && s_lab[rj] == mlabel;
+                    word |= (unsigned long long)hit << (rj & 63);
+                }
+                s_mask[r * pitch + w] = row ? word : 0ull;
+            }
+        }
         __syncthreads();
-        if (en > 0) {
-            const int base = s_ebase;
-            for (int i = tid; i < en; i += K7_PAIRS_THREADS)
-                if (base + i < P.ecap) edges[base + i] = s_edge[i];
+        // ---- bit rows -> edges: counts per row, scan, one reservation
+        if (tid < K7_BRUTE_ROWS) {
+            int c = 0;
+            for (int w = 0; w < nw; ++w) c += __popcll(s_mask[tid * pitch + w]);
+            s_cnt[tid] = c;
+            if (i0 + tid < n) P.pend[oc + i0 + tid] = c;
+            int inc = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += t;
+            }
+            s_off[tid] = inc - c;   // exclusive within the warp; the second warp adds the first one's total below
+        }
+        __syncthreads();
+        const int half = s_off[31] + s_cnt[31];
+        const int total = half + s_off[63] + s_cnt[63];
+        if (total == 0) continue;   // block-uniform
+        if (tid == 0) s_ebase = atomicAdd(P.nedge + b, total);
+        __syncthreads();
+        unsigned int* edges = P.edges + (size_t)b * P.ecap;
+        {
+            int at = s_ebase + s_off[r] + (r >= 32 ? half : 0);
+            for (int w = 0; w < nw; ++w) {
+                unsigned long long word = s_mask[r * pitch + w];
+                if ((w & (K7_BRUTE_PARTS - 1)) != part) {   // another thread's word
+                    at += __popcll(word);
+                    continue;
+                }
+                while (word) {
+                    const int k = __ffsll((long long)word) - 1;
+                    word &= word - 1ull;
+                    if (at < P.ecap) edges[at] = ((unsigned int)ri << 16) | (unsigned int)((w << 6) | k);
+                    ++at;
+                }
+            }
         }
     }
 }
@@ -1992,6 +2195,7 @@ static K7NmsArgs k7_nms_args(const K7DetectWs& w, int A, float thr, int pre_topk
     P.label_ws = w.label; P.rbox = w.rbox; P.bounds = w.bounds; P.nsel = w.nsel; P.ccnt = w.ccnt; P.ckeyC = w.ckeyC;
     P.cbox = w.cbox; P.crank = w.crank; P.clabel = w.clabel; P.ctab = w.ctab; P.pend = w.pend; P.edges = w.edges;
     P.nedge = w.nedge; P.ecap = w.ecap;
+    { static int sn = -2; if (sn == -2) { const char* e = getenv("K7_NMS_BRUTE_N"); sn = e ? atoi(e) : K7_BRUTE_N; if (sn > K7_NMS_CH) sn = K7_NMS_CH; } P.brute_n = sn; }
     static_assert(sizeof(K7Grid) <= 320 && sizeof(K7Grid) % 4 == 0 && sizeof(K7Grid) / 4 <= K7_PAIRS_THREADS, "K7Grid is copied by one thread per word");
     P.ginfo = static_cast<K7Grid*>(w.ginfo);
     return P;
@@ -2016,6 +2220,12 @@ static int k7_nms_chain(const K7NmsArgs& P, int B, int max_det, uint64_t* kept_k
     }
     K7_CUDA(cudaFuncSetAttribute(k7_nms_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_PAIRS_SMEM));
     K7_CUDA(k7_launch_pdl(k7_nms_pairs_kernel, grid1((long long)(P.cap / K7_PAIRS_THREADS) * B, 3), dim3(K7_PAIRS_THREADS), K7_PAIRS_SMEM, st, P, kq, B));
+    if (P.brute_n > 0) {
+        const size_t smem_b = k7_brute_smem(P.brute_n);
+        K7_CUDA(cudaFuncSetAttribute(k7_nms_brute_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+        K7_CUDA(k7_launch_pdl(k7_nms_brute_kernel, grid1((long long)((P.brute_n + K7_BRUTE_ROWS - 1) / K7_BRUTE_ROWS) * B, 6),
+                              dim3(K7_BRUTE_THREADS), smem_b, st, P, B));
+    }
     K7_CUDA(cudaFuncSetAttribute(k7_nms_resolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K7_RESOLVE_SMEM));
     k7_pdl_site() = 2;
     K7_CUDA(k7_launch_pdl(k7_nms_resolve_kernel, dim3(B), dim3(K7_RESOLVE_THREADS), K7_RESOLVE_SMEM, st, P, max_det, kept_key,
