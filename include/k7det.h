@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 10
+#define K7_ABI_VERSION 11
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -124,26 +124,40 @@ K7_API int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_orde
  * from a recipe (calc_iou + IoU-max assignment, losses.py:6-23, 49-82).  An anchor only leaves the NEGATIVE
  * state through a ground-truth box with IoU >= neg_thr, and for one box those anchors are a few cells
  * around it on the two or three pyramid levels whose anchor areas are within 1/neg_thr of its own.  One warp
- * per (image, annotation row, level) enumerates a provable superset of them (area window and the
- * intersection width / height any pair with IoU >= neg_thr needs, 1e-4 margins), evaluates the reference's
- * float32 IoU (k7_pair_iou: same operations, same order) and folds pairs with IoU >= neg_thr into
+ * per (image, annotation row) enumerates a provable superset of them (area window and the intersection
+ * width / height any pair with IoU >= neg_thr needs, 1e-4 margins; all shapes' candidate cells as one flat
+ * range over the lanes), evaluates the reference's float32 IoU (k7_pair_iou: same operations, same order)
+ * and folds pairs with IoU >= neg_thr into
  *     best[b*A + a] = max( generation << 48 | IoU bits << 16 | (0xFFFF - annotation row) )        (atomicMax)
  * i.e. the largest IoU and, on ties, the lowest row - torch.max's first index (losses.py:66).  Work is
  * proportional to the pairs that matter, not to A x M, and nothing per anchor is written: an entry whose
- * top 16 bits differ from `generation` means "no ground truth reached neg_thr" = NEGATIVE.  k7_loss reads
- * `best` directly (K7LossParams.match_generation / neg_thr / pos_thr).
- *   best        [B,A] uint64, caller-owned, ZERO-INITIALISED ONCE; every call on it must pass a LARGER
- *               generation than the one before (1 .. K7_BEST_GEN_MAX; re-zero before starting over)
- * The atomics return nothing (fire and forget); the positives are counted by k7_loss, which walks the array
- * anyway.  Requires a recipe, 1e-3 < neg_thr <= pos_thr, M <= 65535.  Images without a valid row leave `best`
- * untouched; k7_loss sees from the annotations that the image is skipped (losses.py:52-60). */
+ * top 16 bits differ from `generation` means "no ground truth reached neg_thr" = NEGATIVE.
+ *   best        caller-owned buffer of k7_match_scatter_workspace_bytes(B, A) bytes, 256-byte aligned,
+ *               ZERO-INITIALISED ONCE (and again whenever B or A change); every call on it must pass a LARGER
+ *               generation than the one before (1 .. K7_BEST_GEN_MAX; re-zero before starting over).  Layout:
+ *               [B*A] uint64 maxima, then - at K7_BEST_LIST_OFFSET(B, A) - a header with one uint32 counter per
+ *               image, K7_BEST_COUNT_STRIDE words apart (atomics on one address serialise; one counter per
+ *               image keeps them parallel), then - K7_BEST_LIST_HEADER(B) bytes further - B lists of up to A
+ *               uint32 anchor indices: list b holds the anchors of image b whose entry was written for the
+ *               first time in this generation (the value atomicMax returns tells), in no particular order.
+ *               k7_loss reads the lists (K7LossParams.match_generation / neg_thr / pos_thr) and through them
+ *               only the few per cent of entries that matter; nothing walks the B*A array.
+ *   zero_fill4  [B,A,4] float32 (optional, may be NULL; 16-byte aligned) is filled with zeros: the d(reg)
+ *               buffer of the k7_loss call that follows (K7LossParams.dreg_prezeroed).  The kernel is
+ *               latency-bound, idle warps do the stores.
+ * Requires a recipe, 1e-3 < neg_thr <= pos_thr, M <= 65535, B <= 65535.  Images without a valid row leave
+ * `best` untouched; k7_loss sees from the annotations that the image is skipped (losses.py:52-60). */
 #define K7_BEST_GEN_MAX 65535u
 #define K7_BEST_GEN(v) ((uint32_t)((v) >> 48))
 #define K7_BEST_IOU_BITS(v) ((uint32_t)((v) >> 16))
 #define K7_BEST_ROW(v) (0xFFFF - (int32_t)((v) & 0xFFFFu))
+#define K7_BEST_LIST_OFFSET(B, A) ((((size_t)8 * (size_t)(B) * (size_t)(A)) + 255) / 256 * 256)
+#define K7_BEST_COUNT_STRIDE 16
+#define K7_BEST_LIST_HEADER(B) ((((size_t)4 * K7_BEST_COUNT_STRIDE * (size_t)(B)) + 255) / 256 * 256)
 K7_API size_t k7_match_scatter_workspace_bytes(int B, int A);
 K7_API int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
-                     const K7MatchParams* params, uint64_t* best, uint32_t generation, void* stream);
+                     const K7MatchParams* params, uint64_t* best, uint32_t generation, float* zero_fill4,
+                     void* stream);
 
 /* Multi-GPU: the path's one exchange - the four batch sums {sum cls_i, sum reg_i, sum num_pos_i, B}
  * of every rank - fused into k7_loss.  mailbox[p] is a device pointer, valid in THIS process, to

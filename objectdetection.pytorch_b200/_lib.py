@@ -113,7 +113,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 10                     # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 11                     # K7_ABI_VERSION of include/k7det.h
 
 
 BEST_GEN_MAX = 65535                 # K7_BEST_GEN_MAX
@@ -134,7 +134,7 @@ SYMBOLS = {
                            C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P, _P]),
     "k7_match_scatter_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "k7_match_scatter": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_int, C.c_int, C.POINTER(K7MatchParams),
-                                   _P, C.c_uint32, _P]),
+                                   _P, C.c_uint32, _P, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),

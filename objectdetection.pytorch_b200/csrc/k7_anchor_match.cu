@@ -639,15 +639,17 @@ extern "C" int k7_match(const K7AnchorSpec* spec, const float* anchors, int box_
 //     the intersection:   iw >= imin / min(h_a, h_g),  ih >= imin / min(w_a, w_g),
 //                         imin = t/(1+t) * (area_a + area_g)                 (iw <= min(w), ih <= min(h))
 // and iw >= iw_min is an interval of cell columns, ih >= ih_min an interval of cell rows.  One warp
-// takes (image, annotation row, level), walks the level's shapes that pass the area window and
-// evaluates the reference's exact float32 IoU (k7_pair_iou) on the cells of the two intervals -
-// typically 5 x 5 of them.  Every bound is taken with a 1e-4 relative margin and the intervals are
+// takes (image, annotation row), works out those rectangles for all (level, shape) pairs at once and
+// evaluates the reference's exact float32 IoU (k7_pair_iou) on their cells - typically 5 x 5 per
+// shape that passes the area window.  Every bound is taken with a 1e-4 relative margin and the intervals are
 // widened by 0.02 cell, against float32 roundings of ~1e-7: no pair that reaches neg_thr is missed,
 // so states, num_pos and the arg-max of every non-negative anchor are those of the exhaustive
 // kernels, bit for bit (tests/test_gpu_parity.py).  Pairs at or above neg_thr are folded into
 // best[] with a 64-bit atomicMax: generation | IoU bits | ~row - the largest IoU, then the lowest
-// row (torch.max returns the first index).  The maximum is order independent; its result is not
-// needed here, so the atomics are fire-and-forget (the positives are counted by k7_loss's scan).
+// row (torch.max returns the first index).  The maximum is order independent.  The value the atomic
+// returns tells whether the entry was written for the first time in this generation: those anchors
+// (~2-3 % of A) are appended to the TOUCHED list behind the array, which is all k7_loss reads - no
+// pass over the B*A entries anywhere.
 struct __align__(16) K7ScatterShape {   // one anchor shape (level l, in-cell anchor k), 80 bytes
     double base[4];                   // the recipe's in-cell box (spec.base[l][k])
     float g_lo, g_hi;                 // window of ground-truth areas that can reach neg_thr with this shape
@@ -665,96 +667,179 @@ struct K7ScatterAux {
 };
 
 #define K7_SCATTER_THREADS 128
+#define K7_SCATTER_PAIRS (K7_MAX_LEVELS * K7_MAX_CELL_ANCHORS)
+
+struct K7ScatterLevel {   // per pyramid level, in shared memory
+    double stride;
+    float inv_stride, lvl_lo, lvl_hi;
+    int fw, fh, offset;
+};
+
+// Work item = (image, annotation row), one warp.  Lane p (two rounds when levels * shapes > 32) looks at
+// anchor shape p = level * K + k and works out the rectangle of cells whose anchors of that shape can reach
+// neg_thr; a warp scan turns the rectangle sizes into offsets, and then ALL candidate cells of ALL shapes
+// are one flat range that the 32 lanes walk together (a box has ~50-150 candidates on 2-3 levels: two to
+// five trips instead of one trip per shape with most lanes idle).  Warps without a work item - and every warp
+// once its items are done - zero the d(reg) buffer of the loss stage (16 B per anchor: the kernel is latency
+// bound, the stores are free here).
 __global__ void __launch_bounds__(K7_SCATTER_THREADS)
 k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScatterAux X,
                         const float* __restrict__ annotations, int B, int A, int M, float neg_thr,
-                        unsigned long long* __restrict__ best, unsigned int gen) {
-    // the shape table is copied from the kernel parameters to shared memory once per CTA: read in place it
-    // is an indexed constant load per field (ncu: the address-divergence unit was the busiest pipe)
+                        unsigned long long* __restrict__ best, unsigned int gen, unsigned int* __restrict__ touched_count,
+                        unsigned int* __restrict__ touched, float4* __restrict__ zero_fill4) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int L = spec.num_levels, K = spec.cell_anchors, LK = L * K;
     K7ScatterShape* sh = reinterpret_cast<K7ScatterShape*>(smem_raw);
-    const int L = spec.num_levels, K = spec.cell_anchors;
+    K7ScatterLevel* lv = reinterpret_cast<K7ScatterLevel*>(smem_raw + sizeof(K7ScatterShape) * (size_t)LK);
+    __shared__ int s_pref[K7_SCATTER_THREADS / 32][K7_SCATTER_PAIRS];        // inclusive prefix of the candidate counts
+    __shared__ uint2 s_rect[K7_SCATTER_THREADS / 32][K7_SCATTER_PAIRS];      // x: xlo | ylo << 16, y: cells per row
     {
-        const int n16 = L * K * (int)(sizeof(K7ScatterShape) / 16);
+        const int n16 = LK * (int)(sizeof(K7ScatterShape) / 16);
         const uint4* src = reinterpret_cast<const uint4*>(X.shapes);
         uint4* dst = reinterpret_cast<uint4*>(sh);
         for (int i = threadIdx.x; i < n16; i += K7_SCATTER_THREADS) dst[i] = src[i];
+        if ((int)threadIdx.x < L) {
+            const int l = threadIdx.x;
+            K7ScatterLevel v;
+            v.stride = spec.stride[l];
+            v.inv_stride = X.inv_stride[l];
+            v.lvl_lo = X.lvl_lo[l];
+            v.lvl_hi = X.lvl_hi[l];
+            v.fw = spec.fw[l];
+            v.fh = spec.fh[l];
+            v.offset = spec.offset[l];
+            lv[l] = v;
+        }
     }
     __syncthreads();
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const long long gwarp = ((long long)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * K7_SCATTER_THREADS) >> 5;
-    const long long tasks = (long long)B * M * L;
+    const long long tasks = (long long)B * M;
     const unsigned long long tag = (unsigned long long)gen << 48;
     const bool xy = spec.box_order == K7_BOX_XYXY;
-    for (long long t = gwarp; t < tasks; t += nwarps) {   // the level runs fastest: neighbouring warps share a box
-        const int l = (int)(t % L);
-        const long long r = t / L;
-        const int m = (int)(r % M), b = (int)(r / M);
-        const float* row = annotations + ((size_t)b * M + m) * 5;
-        const float g0 = __ldg(row + 0), g1 = __ldg(row + 1), g2 = __ldg(row + 2), g3 = __ldg(row + 3), g4 = __ldg(row + 4);
+    int* pref = s_pref[wib];
+    uint2* rect = s_rect[wib];
+    for (long long t = gwarp; t < tasks; t += nwarps) {
+        const int m = (int)(t % M), b = (int)(t / M);
+        const float* row = annotations + (size_t)t * 5;
+        float gv = lane < 5 ? __ldg(row + lane) : 0.0f;
+        const float g0 = __shfl_sync(0xffffffffu, gv, 0), g1 = __shfl_sync(0xffffffffu, gv, 1);
+        const float g2 = __shfl_sync(0xffffffffu, gv, 2), g3 = __shfl_sync(0xffffffffu, gv, 3);
+        const float g4 = __shfl_sync(0xffffffffu, gv, 4);
         if (g4 == -1.0f) continue;                        // pad row (losses.py:50)
         const float gw = K7_FSUB(g2, g0), gh = K7_FSUB(g3, g1);
         if (!(gw > 0.0f && gh > 0.0f)) continue;          // empty box: IoU is 0 with every anchor
         const float area_g = k7_area(g0, g1, g2, g3);
-        if (!(area_g >= X.lvl_lo[l] && area_g <= X.lvl_hi[l])) continue;   // no shape of this level can reach neg_thr
-        const int fw = spec.fw[l], fh = spec.fh[l];
-        if (fw <= 0 || fh <= 0) continue;
-        const float inv_s = X.inv_stride[l];
-        const double st = spec.stride[l];
-        const int level_off = spec.offset[l];
-        for (int k = 0; k < K; ++k) {                     // warp-uniform
-            const K7ScatterShape& S = sh[l * K + k];
-            if (!(area_g >= S.g_lo && area_g <= S.g_hi)) continue;
-            const float imin = X.c_in * (S.area_lo + area_g);
-            const float mw = fminf(S.wa, gw), mh = fminf(S.ha, gh);
-            if (imin > mw * mh) continue;
-            const float iw_min = imin / mh, ih_min = imin / mw;
-            // cell centre c = (x + 0.5) * stride must satisfy  g0 + iw_min - bx2 <= c <= g2 - iw_min - bx1
-            const float xl = (g0 + iw_min - S.bx2) * inv_s - 0.52f, xh = (g2 - iw_min - S.bx1) * inv_s - 0.48f;
-            const float yl = (g1 + ih_min - S.by2) * inv_s - 0.52f, yh = (g3 - ih_min - S.by1) * inv_s - 0.48f;
-            const int xlo = max(0, (int)ceilf(fmaxf(xl, -1.0f))), xhi = min(fw - 1, (int)floorf(fminf(xh, (float)fw)));
-            const int ylo = max(0, (int)ceilf(fmaxf(yl, -1.0f))), yhi = min(fh - 1, (int)floorf(fminf(yh, (float)fh)));
-            if (xlo > xhi || ylo > yhi) continue;
-            const int nx = xhi - xlo + 1, n = nx * (yhi - ylo + 1);
-            const double b0 = S.base[0], b1 = S.base[1], b2 = S.base[2], b3 = S.base[3];
-            for (int i = lane; i < n; i += 32) {
-                const int yy = i / nx, x = xlo + (i - yy * nx), y = ylo + yy;
-                const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), st);
-                const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), st);
+        int total = 0;
+        __syncwarp();                                     // the previous item's tables are no longer read
+        for (int p0 = 0; p0 < LK; p0 += 32) {             // warp-uniform
+            const int p = p0 + lane;
+            int n = 0, nx = 0, xlo = 0, ylo = 0;
+            if (p < LK) {
+                const int l = p / K;
+                const K7ScatterLevel& V = lv[l];
+                const K7ScatterShape& S = sh[p];
+                if (V.fw > 0 && V.fh > 0 && area_g >= S.g_lo && area_g <= S.g_hi) {
+                    const float imin = X.c_in * (S.area_lo + area_g);
+                    const float mw = fminf(S.wa, gw), mh = fminf(S.ha, gh);
+                    if (!(imin > mw * mh)) {
+                        const float iw_min = imin / mh, ih_min = imin / mw;
+                        const float inv_s = V.inv_stride;
+                        // cell centre c = (x + 0.5) * stride must satisfy  g0 + iw_min - bx2 <= c <= g2 - iw_min - bx1
+                        const float xl = (g0 + iw_min - S.bx2) * inv_s - 0.52f, xh = (g2 - iw_min - S.bx1) * inv_s - 0.48f;
+                        const float yl = (g1 + ih_min - S.by2) * inv_s - 0.52f, yh = (g3 - ih_min - S.by1) * inv_s - 0.48f;
+                        xlo = max(0, (int)ceilf(fmaxf(xl, -1.0f)));
+                        ylo = max(0, (int)ceilf(fmaxf(yl, -1.0f)));
+                        const int xhi = min(V.fw - 1, (int)floorf(fminf(xh, (float)V.fw)));
+                        const int yhi = min(V.fh - 1, (int)floorf(fminf(yh, (float)V.fh)));
+                        if (xlo <= xhi && ylo <= yhi) {
+                            nx = xhi - xlo + 1;
+                            n = nx * (yhi - ylo + 1);
+                        }
+                    }
+                }
+            }
+            int inc = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            if (p < LK) {
+                pref[p] = total + inc;
+                rect[p] = make_uint2((unsigned)xlo | ((unsigned)ylo << 16), (unsigned)nx);
+            }
+            total += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        __syncwarp();
+        for (int i0 = 0; i0 < total; i0 += 32) {          // warp-uniform
+            const int i = i0 + lane;
+            bool first = false;
+            int a = 0;
+            if (i < total) {
+                int lo = 0, hi = LK - 1;                  // the first shape whose inclusive prefix exceeds i
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (pref[mid] > i) hi = mid; else lo = mid + 1;
+                }
+                const int p = lo, l = p / K, k = p - l * K;
+                const uint2 rc = rect[p];
+                const int nx = (int)rc.y, j = i - (p ? pref[p - 1] : 0);
+                const int yy = j / nx, x = (int)(rc.x & 0xffffu) + (j - yy * nx), y = (int)(rc.x >> 16) + yy;
+                const K7ScatterLevel& V = lv[l];
+                const K7ScatterShape& S = sh[p];
+                const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), V.stride);
+                const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), V.stride);
                 float ax1, ay1, ax2, ay2;                 // k7_anchor_from_spec: float64 add, one rounding
                 if (xy) {
-                    ax1 = __double2float_rn(__dadd_rn(b0, sx));
-                    ay1 = __double2float_rn(__dadd_rn(b1, sy));
-                    ax2 = __double2float_rn(__dadd_rn(b2, sx));
-                    ay2 = __double2float_rn(__dadd_rn(b3, sy));
+                    ax1 = __double2float_rn(__dadd_rn(S.base[0], sx));
+                    ay1 = __double2float_rn(__dadd_rn(S.base[1], sy));
+                    ax2 = __double2float_rn(__dadd_rn(S.base[2], sx));
+                    ay2 = __double2float_rn(__dadd_rn(S.base[3], sy));
                 } else {
-                    ay1 = __double2float_rn(__dadd_rn(b0, sy));
-                    ax1 = __double2float_rn(__dadd_rn(b1, sx));
-                    ay2 = __double2float_rn(__dadd_rn(b2, sy));
-                    ax2 = __double2float_rn(__dadd_rn(b3, sx));
+                    ay1 = __double2float_rn(__dadd_rn(S.base[0], sy));
+                    ax1 = __double2float_rn(__dadd_rn(S.base[1], sx));
+                    ay2 = __double2float_rn(__dadd_rn(S.base[2], sy));
+                    ax2 = __double2float_rn(__dadd_rn(S.base[3], sx));
                 }
                 const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, k7_area(ax1, ay1, ax2, ay2), g0, g1, g2, g3, area_g);
                 if (iou >= neg_thr) {
-                    const int a = level_off + (y * fw + x) * K + k;
+                    a = V.offset + (y * V.fw + x) * K + k;
                     const unsigned long long v = tag | ((unsigned long long)__float_as_uint(iou) << 16) |
                                                  (unsigned long long)(0xFFFF - m);
-                    atomicMax(best + (size_t)b * A + a, v);   // result unused: RED.MAX.64, nothing to wait for
+                    const unsigned long long old = atomicMax(best + (size_t)b * A + a, v);
+                    first = K7_BEST_GEN(old) != gen;      // nobody wrote this entry in this generation before
                 }
             }
+            const unsigned int fm = __ballot_sync(0xffffffffu, first);
+            if (fm) {
+                unsigned int base = 0u;
+                if (lane == 0) base = atomicAdd(touched_count + (size_t)b * K7_BEST_CNT_STRIDE, (unsigned int)__popc(fm));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (first) touched[(size_t)b * A + base + (unsigned int)__popc(fm & ((1u << lane) - 1u))] = (unsigned int)a;
+            }
         }
+    }
+    if (zero_fill4) {
+        const size_t n = (size_t)B * (size_t)A;
+        const size_t step = (size_t)gridDim.x * K7_SCATTER_THREADS;
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (size_t i = (size_t)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x; i < n; i += step) __stcs(zero_fill4 + i, z);
     }
 }
 
 extern "C" size_t k7_match_scatter_workspace_bytes(int B, int A) {
     if (B <= 0 || A <= 0) return 0;
-    return sizeof(unsigned long long) * (size_t)B * (size_t)A;
+    return k7_best_list_off(B, A) + k7_best_list_hdr(B) + sizeof(unsigned int) * (size_t)B * (size_t)A;
 }
 
 extern "C" int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, int B, int A, int M,
-                                const K7MatchParams* params, uint64_t* best, uint32_t generation, void* stream) {
+                                const K7MatchParams* params, uint64_t* best, uint32_t generation, float* zero_fill4,
+                                void* stream) {
     K7_REQUIRE(spec && annotations && params && best, "k7_match_scatter: null argument");
-    K7_REQUIRE(B > 0 && A > 0 && M > 0 && M <= 65535, "k7_match_scatter: bad shape B=%d A=%d M=%d", B, A, M);
+    K7_REQUIRE((reinterpret_cast<uintptr_t>(zero_fill4) & 15) == 0, "k7_match_scatter: zero_fill4 must be 16-byte aligned");
+    K7_REQUIRE(B > 0 && B <= 65535 && A > 0 && M > 0 && M <= 65535, "k7_match_scatter: bad shape B=%d A=%d M=%d", B, A, M);
     K7_REQUIRE(generation >= 1u && generation <= K7_BEST_GEN_MAX, "k7_match_scatter: generation %u outside [1, %u]",
                generation, K7_BEST_GEN_MAX);
     K7_REQUIRE(params->neg_thr > 1e-3f && params->neg_thr < 1.0f && params->pos_thr >= params->neg_thr,
@@ -795,14 +880,20 @@ extern "C" int k7_match_scatter(const K7AnchorSpec* spec, const float* annotatio
         }
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const size_t tbytes = sizeof(K7ScatterShape) * (size_t)spec->num_levels * K;
-    const long long tasks = (long long)B * M * spec->num_levels;
+    const size_t tbytes = sizeof(K7ScatterShape) * (size_t)spec->num_levels * K + sizeof(K7ScatterLevel) * K7_MAX_LEVELS;
+    const long long tasks = (long long)B * M;
     const int wpb = K7_SCATTER_THREADS / 32;
     long long blocks = (tasks + wpb - 1) / wpb;
-    const long long cap = 16ll * k7_sm_count();      // 16 resident CTAs of 128 threads per SM; the rest is looped
+    const long long cap = 12ll * k7_sm_count();      // 12 resident CTAs of 128 threads per SM; the rest is looped
     if (blocks > cap) blocks = cap;
+    if (zero_fill4 && blocks < 4ll * k7_sm_count()) blocks = 4ll * k7_sm_count();   // enough threads for the zero fill
+    unsigned char* raw = reinterpret_cast<unsigned char*>(best);
+    unsigned int* tcount = reinterpret_cast<unsigned int*>(raw + k7_best_list_off(B, A));
+    unsigned int* tlist = reinterpret_cast<unsigned int*>(raw + k7_best_list_off(B, A) + k7_best_list_hdr(B));
+    K7_CUDA(cudaMemsetAsync(tcount, 0, k7_best_list_hdr(B), st));
     k7_match_scatter_kernel<<<(unsigned)blocks, K7_SCATTER_THREADS, tbytes, st>>>(
-        *spec, X, annotations, B, A, M, params->neg_thr, reinterpret_cast<unsigned long long*>(best), generation);
+        *spec, X, annotations, B, A, M, params->neg_thr, reinterpret_cast<unsigned long long*>(best), generation,
+        tcount, tlist, reinterpret_cast<float4*>(zero_fill4));
     K7_LAUNCH_CHECK();
     return K7_OK;
 }

@@ -141,6 +141,18 @@ __device__ __forceinline__ void k7_anchor(const K7AnchorSpec& s, const float* __
         k7_anchor_from_tensor(anchors, box_order, a, x1, y1, x2, y2);
 }
 
+// Layout of the caller's `best` buffer: [B*A] uint64 maxima, then (256-byte aligned) a header with one
+// counter per image (K7_BEST_CNT_STRIDE words apart: atomics on ONE address serialise at ~7 ns each, measured;
+// one counter per image keeps them parallel), then B lists of up to A anchors: the anchors of image b whose
+// entry was written for the first time in this generation.  k7_loss walks the lists, not the array.
+#define K7_BEST_CNT_STRIDE 16
+__host__ __device__ inline size_t k7_best_list_off(int B, int A) {
+    return ((sizeof(unsigned long long) * (size_t)B * (size_t)A + 255) / 256) * 256;
+}
+__host__ __device__ inline size_t k7_best_list_hdr(int B) {
+    return ((sizeof(unsigned int) * K7_BEST_CNT_STRIDE * (size_t)B + 255) / 256) * 256;
+}
+
 // ------------------------------------------------------------------ warp helpers
 __device__ __forceinline__ float k7_warp_sum(float v) {
 #pragma unroll

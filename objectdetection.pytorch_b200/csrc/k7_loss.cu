@@ -50,6 +50,7 @@
 #include "k7_common.cuh"
 
 #define K7_ROWS_THREADS 256
+#define K7_FIX_ONE 4294967296.0                         // fixed-point unit of the per-image accumulators: 2^-32
 #define K7_ROWS_PER 8                                      // anchors per thread and chunk
 #define K7_ROWS_CHUNK (K7_ROWS_THREADS * K7_ROWS_PER)      // anchors per block and chunk
 
@@ -254,9 +255,12 @@ __device__ __forceinline__ float k7_row_smooth_l1(const K7AnchorSpec& spec, cons
 struct K7PipeSeg {
     const float* cls;
     float* dcls;
+    const uint32_t* bits;    // one bit per ROW of the stream, set = ignored (losses.py:79-82); image b owns words [b*W, (b+1)*W)
     unsigned long long N;    // B * AC elements
     unsigned long long N4;   // N & ~3: the part moved by 16-byte bulk copies
     unsigned long long AC;   // elements per image
+    uint32_t A;              // rows per image (a row = C elements; per-level streams run with C == 1: a row per element)
+    uint32_t W;              // bitmap words per image, K7_IGNORE_WORDS(A)
     uint32_t tile0;          // first tile of the stream in the launch's tile order
     uint32_t pad;
 };
@@ -270,23 +274,26 @@ struct K7PipeGeom {
     uint32_t tile_f;         // floats per tile = cw * slice
     uint32_t slice;          // floats per consumer warp and tile: 512 or 1024
     uint32_t num_tiles;      // sum over the streams of ceil(N4 / tile_f)
-    uint32_t cta_stride, cta_off;   // cta_partials[b * cta_stride + cta_off + blockIdx.x]
+    K7FastDiv div_c;         // / C for tile-local indices
+    uint32_t cta_stride, cta_off;   // (unused since the stream folds into the per-image accumulators)
+    uint32_t side_words;     // words reserved per ignore-bit part (two parts per stage: image b0 and image b0 + 1)
     uint32_t stage_stride;
     uint32_t off_desc, off_bars, off_sco;   // off_sco: float[B] gradient scale per image (0: not tabulated)
     int stages, cw, grid;
     size_t smem_bytes;
 };
 
-struct K7TileDesc {   // written by the producer next to each stage, 32 bytes
+struct K7TileDesc {   // written by the producer next to each stage, 48 bytes
     uint32_t n, b0, split, split2;     // floats in the tile | image of float 0 | floats that belong to image b0 | ... up to the end of image b0+1
     uint32_t off_lo, off_hi, seg, pad; // flat index of float 0 in its stream | the stream
+    uint32_t rem, lead, kA, a0;        // position of float 0 in its row | bit of tile row 0 in part 0 | tile row where image b0+1 starts | row (in image b0) of tile row 0
 };
 
 template <bool GRAD, int SL, bool LOGITS>
 __global__ void __launch_bounds__((K7_PIPE_MAX_CW + 1) * 32, 1)
 k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __restrict__ num_pos,
                     const unsigned char* __restrict__ img_valid, const __grid_constant__ K7LossDev P,
-                    const __grid_constant__ K7PipeGeom G, float* __restrict__ partials, float* __restrict__ cta_partials) {
+                    const __grid_constant__ K7PipeGeom G, float* __restrict__ partials, long long* __restrict__ img_acc) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int NS = G.stages, CW = G.cw;
@@ -324,6 +331,8 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         // between "stage free" and "copy issued".
         K7TileDesc nd;
         const float* n_src = nullptr;
+        const uint32_t *n_bits0 = nullptr, *n_bits1 = nullptr;
+        uint32_t n_words0 = 0u, n_words1 = 0u;
         auto prepare = [&](const uint32_t j) {
             const uint32_t g = blockIdx.x + j * gridDim.x;
             int sg = 0;
@@ -343,14 +352,36 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
             d.off_hi = (uint32_t)(off >> 32);
             d.seg = (uint32_t)sg;
             d.pad = 0u;
+            // the ignore bits of the rows touching the tile: part 0 = rows of image b0, part 1 = rows of image b0 + 1
+            const uint32_t A = Q.A;
+            const unsigned long long r0 = off / (uint32_t)P.C;   // first row (batch-global) touching the tile
+            d.rem = (uint32_t)(off - r0 * (uint32_t)P.C);
+            d.a0 = (uint32_t)(r0 - (unsigned long long)d.b0 * A);
+            const uint32_t nrows = k7_div(d.rem + d.n - 1u, G.div_c) + 1u;
+            d.kA = A - d.a0;
+            const uint32_t w0 = (d.a0 >> 7) << 2;   // 16-byte aligned first word of part 0
+            d.lead = d.a0 - (w0 << 5);
+            const uint32_t rows0 = nrows < d.kA ? nrows : d.kA;
+            n_words0 = ((d.lead + rows0 + 127u) >> 7) << 2;
+            n_words1 = 0u;
+            if (nrows > d.kA && d.b0 + 1u < (uint32_t)P.B) {
+                const uint32_t rows1 = min(nrows - d.kA, A);
+                n_words1 = ((rows1 + 127u) >> 7) << 2;
+            }
             nd = d;
             n_src = Q.cls + off;
+            n_bits0 = Q.bits + (size_t)d.b0 * Q.W + w0;
+            n_bits1 = Q.bits + (size_t)(d.b0 + 1u) * Q.W;
         };
         auto issue = [&](const uint32_t j) {   // the prepared tile is tile j
             const int s = (int)(j % (uint32_t)NS);
+            unsigned char* stage = smem + (size_t)s * G.stage_stride;
             desc[s] = nd;
-            k7_mbar_expect_tx(full + s, nd.n * 4u);   // release: orders the descriptor
-            k7_bulk_g2s(smem + (size_t)s * G.stage_stride, n_src, nd.n * 4u, full + s);
+            uint32_t* side = reinterpret_cast<uint32_t*>(stage + (size_t)G.tile_f * 4);
+            k7_mbar_expect_tx(full + s, nd.n * 4u + (n_words0 + n_words1) * 4u);   // release: orders the descriptor
+            k7_bulk_g2s(stage, n_src, nd.n * 4u, full + s);
+            k7_bulk_g2s(side, n_bits0, n_words0 * 4u, full + s);
+            if (n_words1) k7_bulk_g2s(side + G.side_words, n_bits1, n_words1 * 4u, full + s);
         };
         // with gradients one stage is always draining its store
         const uint32_t ahead = (uint32_t)(GRAD ? NS - 1 : NS);
@@ -415,11 +446,18 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         if (GRAD)
             sco = s_sco ? s_sco[b] : (img_valid[b] ? oma * k7_loss_scales(__ldg(num_pos + b), P.mean_div).x : 0.0f);
     };
-    auto exact = [&](const float x, float* gout) {
+    auto exact = [&](const float x, const bool ign, float* gout) {
         float gr;
-        cslow += k7_neg_exact(x, &gr, LOGITS);
-        if (GRAD) *gout = sco * gr;
+        const float l = k7_neg_exact(x, &gr, LOGITS);
+        if (!ign) cslow += l;
+        if (GRAD) *gout = ign ? 0.0f : sco * gr;
     };
+    // An element of an IGNORED row (losses.py:79-82) is overwritten in the shared-memory tile, before the flat
+    // pass, by a value whose clamped probability differs from it: clamp(0) = 1e-4 != 0 gives gradient 0
+    // (torch.clamp's rule) and a loss term p^2 * -log(1-p) = 1e-12 - below half an ulp of any sum it is added
+    // to, < 1e-9 relative in total.  The flat pass itself knows nothing about rows: no mask, no second variant.
+    const float SENT = LOGITS ? -1.0e30f : 0.0f;
+    const int C = P.C;
     const int i_lo = warp * SL;
 
     const uint32_t full_u32 = k7_smem_u32(full), done_u32 = k7_smem_u32(done);
@@ -440,8 +478,50 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
             int img = -1;   // which image does the slice lie in?
             if ((uint32_t)i_hi <= d0.z) img = (int)d0.y;
             else if ((uint32_t)i_lo >= d0.z && (uint32_t)i_hi <= d0.w) img = (int)d0.y + 1;
+            const uint4 d2 = *(reinterpret_cast<const uint4*>(desc + s) + 2);   // rem, lead, kA, a0
+            const int rem = (int)d2.x;
+            int bitbase = 0;   // bit position of tile row 0 in the part of the slice's image
+            if (img == (int)d0.y) bitbase = (int)d2.y;
+            else if (img >= 0) bitbase = (int)(G.side_words * 32u) - (int)d2.z;   // part 1 starts at tile row kA
             if (img >= 0) {
                 enter(img);
+                const uint32_t* side = reinterpret_cast<const uint32_t*>(stage + (size_t)G.tile_f * 4);
+                const int k_lo = (int)k7_div((uint32_t)(rem + i_lo), G.div_c);
+                const int k_hi = (int)k7_div((uint32_t)(rem + i_hi - 1), G.div_c);
+                // ---- ignored rows of the slice: their elements become SENT
+                bool masked = false;
+                if (C == 1) {
+                    // a row is one element: 32 consecutive bits of the bitmap per 32 elements
+                    for (int k0 = k_lo + 32 * lane; k0 <= k_hi; k0 += 1024) {
+                        const int p = bitbase + k0;
+                        uint32_t w = __funnelshift_r(side[p >> 5], side[(p >> 5) + 1], (uint32_t)p & 31u);
+                        const int nv = k_hi - k0 + 1;
+                        if (nv < 32) w &= (1u << nv) - 1u;
+                        if (w) masked = true;
+                        while (w) {
+                            const int j = __ffs(w) - 1;
+                            w &= w - 1u;
+                            slice[k0 - k_lo + j] = SENT;
+                        }
+                    }
+                    masked = __any_sync(0xffffffffu, masked);
+                } else {
+                    for (int k0 = k_lo; k0 <= k_hi; k0 += 32) {   // warp-uniform window reads
+                        const int p = bitbase + k0;
+                        uint32_t win = __funnelshift_r(side[p >> 5], side[(p >> 5) + 1], (uint32_t)p & 31u);
+                        const int nv = k_hi - k0 + 1;
+                        if (nv < 32) win &= (1u << nv) - 1u;
+                        if (win == 0u) continue;
+                        masked = true;
+                        while (win) {
+                            const int kk = k0 + __ffs(win) - 1;
+                            win &= win - 1u;
+                            const int e_lo = kk * C - rem - i_lo;
+                            for (int e = max(e_lo, 0) + lane; e < min(e_lo + C, len); e += 32) slice[e] = SENT;
+                        }
+                    }
+                }
+                if (masked) __syncwarp();
                 const float2 acc0 = acc;
                 float pmax = 0.0f;
                 k7_flat_pass<SL, GRAD, LOGITS>(slice, n4, lane, sco, acc, pmax);
@@ -452,20 +532,35 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
                     acc = acc0;
                     const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // off_lo, off_hi, seg
                     const float* src = SG.s[d1.z].cls + ((((unsigned long long)d1.y) << 32) | d1.x) + i_lo;
-                    for (int i = lane; i < len; i += 32) exact(GRAD ? __ldg(src + i) : slice[i], slice + i);
+                    for (int i = lane; i < len; i += 32) {
+                        bool ign = false;
+                        if (GRAD && masked) {   // without gradients the tile still holds SENT for those elements
+                            const int p = bitbase + (int)k7_div((uint32_t)(rem + i_lo + i), G.div_c);
+                            ign = (side[p >> 5] >> (p & 31)) & 1u;
+                        }
+                        exact(GRAD ? __ldg(src + i) : slice[i], ign, slice + i);
+                    }
                 }
             } else {
                 // ---- generic path: the slice straddles an image boundary (or the tile spans > 2 images)
                 const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);
                 const unsigned long long off = (((unsigned long long)d1.y) << 32) | d1.x;
                 const K7PipeSeg& Q = SG.s[d1.z];
+                const uint32_t A = Q.A;
+                const unsigned long long r0 = (unsigned long long)d0.y * A + d2.w;
                 uint32_t i = (uint32_t)i_lo;
                 while (i < (uint32_t)i_hi) {   // warp-uniform: one iteration per image segment
                     const uint32_t b = (uint32_t)((off + i) / Q.AC);
                     const unsigned long long img_end = (unsigned long long)(b + 1u) * Q.AC - off;
                     const uint32_t seg_end = img_end < (unsigned long long)i_hi ? (uint32_t)img_end : (uint32_t)i_hi;
                     enter((int)b);
-                    for (uint32_t t = i + lane; t < seg_end; t += 32) exact(tile[t], tile + t);
+                    const unsigned long long abase = (unsigned long long)b * A;
+                    for (uint32_t t = i + lane; t < seg_end; t += 32) {
+                        const uint32_t k = k7_div((uint32_t)rem + t, G.div_c);
+                        const uint32_t a = (uint32_t)(r0 + k - abase);
+                        const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
+                        exact(tile[t], ign, tile + t);
+                    }
                     i = seg_end;
                 }
             }
@@ -480,10 +575,14 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         for (int sg = 0; sg < SG.n; ++sg) {
             const K7PipeSeg& Q = SG.s[sg];
             for (unsigned long long e = Q.N4; e < Q.N; ++e) {
-                enter((int)(e / Q.AC));
+                const uint32_t b = (uint32_t)(e / Q.AC);
+                enter((int)b);
                 if (lane == 0) {
+                    const unsigned long long r = e / (uint32_t)C;
+                    const uint32_t a = (uint32_t)(r - (unsigned long long)b * Q.A);
+                    const bool ign = (__ldg(Q.bits + (size_t)b * Q.W + (a >> 5)) >> (a & 31u)) & 1u;
                     float g = 0.0f;
-                    exact(__ldg(Q.cls + e), &g);
+                    exact(__ldg(Q.cls + e), ign, &g);
                     if (GRAD) Q.dcls[e] = g;
                 }
             }
@@ -491,12 +590,14 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
     }
     if (cur_b >= 0) flush();
 
-    // ---- fold the CTA's (image, warp) slots into one value per (image, CTA): consumer warps only
+    // ---- fold the CTA's (image, warp) slots into the image's fixed-point accumulator (2^-32 units, integer
+    // atomics: exact, whatever the order in which CTAs finish - nobody has to sum 148 partials per image later)
     asm volatile("bar.sync 1, %0;" ::"r"(CW * 32) : "memory");
     for (int b = warp; b < P.B; b += CW) {
         float v = (lane < CW) ? __ldcg(partials + (size_t)b * pstride + (size_t)blockIdx.x * CW + lane) : 0.0f;
         v = k7_warp_sum(v);
-        if (lane == 0) cta_partials[(size_t)b * G.cta_stride + G.cta_off + blockIdx.x] = v;
+        if (lane == 0 && v != 0.0f)
+            atomicAdd(reinterpret_cast<unsigned long long*>(img_acc + 2 * b), (unsigned long long)__double2ll_rn((double)v * K7_FIX_ONE));
     }
 }
 
@@ -512,6 +613,65 @@ struct K7LevelTable {
     int S[K7_MAX_LEVELS];
 };
 
+// Seen as a flat stream every element of a per-level tensor is its own "row": the stream kernel runs on a
+// level in its C == 1 mode with ONE IGNORE BIT PER ELEMENT, laid out like the tensor: bit (b, ch, s) = the
+// anchor's bit.  k7_bits_expand_kernel writes those words (1/32 of the tensor's bytes) from the
+// anchor-ordered bitmap.
+struct K7ExpandTable {
+    uint32_t* lbits[K7_MAX_LEVELS];
+    int level_off[K7_MAX_LEVELS], S[K7_MAX_LEVELS], Wl[K7_MAX_LEVELS];
+    int blk_off[K7_MAX_LEVELS + 1];   // first block of each level; [K7_MAX_LEVELS] = grid.x
+};
+
+// All levels in one launch, grid (blocks, B).  One thread per 32-cell word of an (image, in-cell
+// anchor) plane; the word is the same for all C classes of that anchor.  S % 32 == 0: whole words,
+// written C times.  Otherwise (small levels) one thread per output word gathers its 32 elements
+// individually.
+__global__ void __launch_bounds__(256)
+k7_bits_expand_kernel(const uint32_t* __restrict__ abits, int W, const __grid_constant__ K7ExpandTable T, int K, int C) {
+    const int b = blockIdx.y;
+    int l = 0;
+#pragma unroll
+    for (int i = 1; i < K7_MAX_LEVELS; ++i)
+        if ((int)blockIdx.x >= T.blk_off[i]) l = i;
+    const int S = T.S[l], level_off = T.level_off[l];
+    const int blk = (int)blockIdx.x - T.blk_off[l];
+    const uint32_t* ab = abits + (size_t)b * W;
+    uint32_t* lb = T.lbits[l] + (size_t)b * T.Wl[l];
+    if ((S & 31) == 0) {
+        const int spw = S >> 5;                       // words per plane
+        const int t = blk * 256 + (int)threadIdx.x;
+        if (t >= K * spw) return;
+        const int k = t / spw, sw = t - k * spw;
+        uint32_t word = 0u;
+        int a = level_off + (sw << 5) * K + k;
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j, a += K) word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
+        for (int c = 0; c < C; ++c) lb[(size_t)(k * C + c) * spw + sw] = word;
+    } else {
+        const int nel = K * C * S;                    // < 2^31 (checked by the plan)
+        const int w = blk * 256 + (int)threadIdx.x;
+        if (w >= (nel + 31) >> 5) return;
+        const int e0 = w << 5;
+        int ch = e0 / S, s = e0 - ch * S;             // plane (k*C + c) and cell of the word's first element
+        int k = ch / C, c = ch - k * C;
+        const int nb = min(32, nel - e0);
+        uint32_t word = 0u;
+        for (int j = 0; j < nb; ++j) {
+            const int a = level_off + s * K + k;
+            word |= ((__ldg(ab + (a >> 5)) >> (a & 31)) & 1u) << j;
+            if (++s == S) {                           // next plane: same anchor plane until the classes run out
+                s = 0;
+                if (++c == C) {
+                    c = 0;
+                    ++k;
+                }
+            }
+        }
+        lb[w] = word;
+    }
+}
+
 // ------------------------------------------------------------------ the row kernels
 __device__ __forceinline__ double k7_warp_sum_f64(double v) {
 #pragma unroll
@@ -523,7 +683,6 @@ __device__ __forceinline__ long long k7_warp_sum_i64(long long v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
-#define K7_FIX_ONE 4294967296.0   // fixed-point unit of the row accumulators: 2^-32
 
 // Sum of (c, r) over the block, result valid in thread 0.  Fixed order.  s_red: 2 * warps doubles.
 __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* s_red) {
@@ -558,10 +717,13 @@ __device__ __forceinline__ void k7_block_sum2_f64(double& c, double& r, double* 
 // accumulated with integer atomics, so results do not.
 //   queue entry: x = anchor (image-local), y = image << 16 | annotation row
 struct K7RowQueues {
-    uint2* q;                  // [B*A] entries: positives q[0 .. npos), ignored rows q[cap-1], q[cap-2], ...
-    unsigned int* count;       // [0] positives, [1] ignored rows
+    uint2* q;                  // [B][A] entries (anchor, annotation row): the positive rows of image b are q[b*A .. b*A + count_b)
+    unsigned int* count;       // count[b * K7_BEST_CNT_STRIDE]: positives of image b (one counter per image, apart: atomics
+                               // on one address serialise)
     unsigned long long cap;    // B*A
     unsigned char* img_valid;  // [B] 1: the image has an annotation row (losses.py:49-60)
+    uint32_t* bits;            // [B][W] one bit per anchor, set = ignored row (losses.py:79-82): what the stream reads
+    int W;                     // K7_IGNORE_WORDS(A)
 };
 
 template <bool GRAD, bool PACKED>
@@ -570,7 +732,7 @@ k7_loss_scan_kernel(const float* __restrict__ annotations, const __grid_constant
                     const __grid_constant__ K7LossDev P, const __grid_constant__ K7RowQueues Q,
                     int32_t* __restrict__ num_pos, float4* __restrict__ dreg) {
     constexpr int NW = K7_ROWS_THREADS / 32;
-    __shared__ int s_wp[NW], s_wi[NW];
+    __shared__ int s_wp[NW];
     __shared__ unsigned int s_base[2];
     const int A = P.A;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -594,7 +756,7 @@ k7_loss_scan_kernel(const float* __restrict__ annotations, const __grid_constant
         const bool any_valid = __syncthreads_or(v ? 1 : 0) != 0;   // also: s_wp / s_wi / s_base of the previous chunk are consumed
         if (a0 == 0 && threadIdx.x == 0) Q.img_valid[b] = any_valid ? 1 : 0;
 
-        unsigned int pm = 0u, im = 0u;   // bit j: entry j is a positive / an ignored row
+        unsigned int pm = 0u;   // bit j: entry j is a positive
         int rw[K7_ROWS_PER];
 #pragma unroll
         for (int j = 0; j < K7_ROWS_PER; ++j) {
@@ -612,84 +774,140 @@ k7_loss_scan_kernel(const float* __restrict__ annotations, const __grid_constant
                 st = K7_ASSIGN_STATE(w[j]);
                 rw[j] = K7_ASSIGN_ROW(w[j]);
             }
-            if (a >= A) continue;
-            if (!any_valid) {   // the whole image is skipped (losses.py:52-60): nothing to patch, no gradient
+            if (a < A && !any_valid) {   // the whole image is skipped (losses.py:52-60): nothing to patch, no gradient
                 st = K7_STATE_IGNORE;
                 rw[j] = 0;
             }
+            // the stream's bitmap: 32 consecutive anchors per warp and entry -> one word (a0 is a multiple of 2048)
+            const unsigned int bal = __ballot_sync(0xffffffffu, a < A && st == K7_STATE_IGNORE && any_valid);
+            const int aw = a0 + j * K7_ROWS_THREADS + warp * 32;
+            if (lane == 0 && aw < A) Q.bits[(size_t)b * Q.W + (aw >> 5)] = bal;
+            if (a >= A) continue;
             const size_t R = (size_t)b * A + a;
             if (SRC.words_out) SRC.words_out[R] = (rw[j] << 2) | st;
             if (GRAD && !P.dreg_prezeroed && st != K7_STATE_POS) dreg[R] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (any_valid) {
-                pm |= (st == K7_STATE_POS ? 1u : 0u) << j;
-                im |= (st == K7_STATE_IGNORE ? 1u : 0u) << j;
-            }
+            if (any_valid) pm |= (st == K7_STATE_POS ? 1u : 0u) << j;
         }
-        // block-level exclusive prefix of (positives, ignored rows) per thread
-        const int cp = __popc(pm), ci = __popc(im);
-        int ip = cp, ii = ci;
+        // block-level exclusive prefix of the positives per thread
+        const int cp = __popc(pm);
+        int ip = cp;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int tp = __shfl_up_sync(0xffffffffu, ip, o), ti = __shfl_up_sync(0xffffffffu, ii, o);
-            if (lane >= o) {
-                ip += tp;
-                ii += ti;
-            }
+            const int tp = __shfl_up_sync(0xffffffffu, ip, o);
+            if (lane >= o) ip += tp;
         }
-        if (lane == 31) {
-            s_wp[warp] = ip;
-            s_wi[warp] = ii;
-        }
+        if (lane == 31) s_wp[warp] = ip;
         __syncthreads();
-        int op = ip - cp, oi = ii - ci, tp = 0, ti = 0;
+        int op = ip - cp, tp = 0;
 #pragma unroll
         for (int k = 0; k < NW; ++k) {
-            if (k < warp) {
-                op += s_wp[k];
-                oi += s_wi[k];
-            }
+            if (k < warp) op += s_wp[k];
             tp += s_wp[k];
-            ti += s_wi[k];
         }
         if (threadIdx.x == 0) {
-            s_base[0] = tp ? atomicAdd(Q.count + 0, (unsigned int)tp) : 0u;
-            s_base[1] = ti ? atomicAdd(Q.count + 1, (unsigned int)ti) : 0u;
+            s_base[0] = tp ? atomicAdd(Q.count + (size_t)b * K7_BEST_CNT_STRIDE, (unsigned int)tp) : 0u;
             if (tp) atomicAdd(num_pos + b, tp);   // integer: order independent, exact
         }
         __syncthreads();
-        if (pm | im) {
-            const unsigned int bp = s_base[0] + (unsigned int)op, bi = s_base[1] + (unsigned int)oi;
-            int kp = 0, ki = 0;
+        if (pm) {
+            const size_t bp = (size_t)b * A + s_base[0] + (unsigned int)op;
+            int kp = 0;
 #pragma unroll
             for (int j = 0; j < K7_ROWS_PER; ++j) {
                 const unsigned int a = (unsigned int)(a0 + j * K7_ROWS_THREADS + threadIdx.x);
-                if ((pm >> j) & 1u) Q.q[bp + kp++] = make_uint2(a, ((unsigned int)b << 16) | (unsigned int)rw[j]);
-                if ((im >> j) & 1u) Q.q[Q.cap - 1ull - (bi + ki++)] = make_uint2(a, (unsigned int)b << 16);
+                if ((pm >> j) & 1u) Q.q[bp + kp++] = make_uint2(a, (unsigned int)rw[j]);
             }
         }
     }
 }
 
-// SERVE KERNEL, after the stream: the two queues, densely.
-//   positive rows, a thread each: smooth-L1 + d(reg) (losses.py:122-166) and the correction of the
-//           label element from "target 0" (what the stream computed) to "target 1" (losses.py:94-112);
-//   ignored rows, a warp each (lanes across the classes, all loads of a row in flight at once): the
-//           row's C elements are evaluated again, exactly, and SUBTRACTED - the stream counted them -
-//           and their gradients become 0 (losses.py:79-82, 114).
+// LIST KERNEL - the scan's job when the assignment comes from k7_match_scatter: that kernel leaves, behind
+// its array of maxima, the list of anchors it TOUCHED (IoU_max >= neg_thr: every row that is not a plain
+// negative, a few per cent of A), so nothing has to walk the B*A entries.  A thread per list entry reads the
+// final maximum; a positive is counted for its image and appended to the queue (one atomicAdd per warp), an
+// ignored row sets its bit in the stream's bitmap (zeroed at the start of the call).  No block-wide step.
+// Also: img_valid[b].
+#define K7_LIST_PER 4   // entries per thread and trip: four independent load chains in flight
+__global__ void __launch_bounds__(K7_ROWS_THREADS)
+k7_loss_list_kernel(const float* __restrict__ annotations, const __grid_constant__ K7AssignSrc SRC,
+                    const __grid_constant__ K7LossDev P, const __grid_constant__ K7RowQueues Q,
+                    int32_t* __restrict__ num_pos, const unsigned int* __restrict__ tcount,
+                    const unsigned int* __restrict__ tlist) {
+    const int lane = threadIdx.x & 31;
+    const unsigned int b = blockIdx.y;   // grid (blocks per image, B)
+    const unsigned int gw = (blockIdx.x * K7_ROWS_THREADS + threadIdx.x) >> 5, nw = (gridDim.x * K7_ROWS_THREADS) >> 5;
+    if (gw == 0) {
+        bool v = false;
+        for (int m = lane; m < P.M; m += 32) v |= __ldg(annotations + ((size_t)b * P.M + m) * 5 + 4) != -1.0f;
+        v = __any_sync(0xffffffffu, v);
+        if (lane == 0) Q.img_valid[b] = v ? 1 : 0;
+    }
+    const unsigned int n = __ldcg(tcount + (size_t)b * K7_BEST_CNT_STRIDE);
+    const unsigned int* list = tlist + (size_t)b * P.A;
+    const unsigned long long* best = SRC.best + (size_t)b * P.A;
+    for (unsigned int i0 = gw * (32 * K7_LIST_PER); i0 < n; i0 += nw * (32 * K7_LIST_PER)) {   // warp-uniform
+        unsigned int an[K7_LIST_PER];
+        unsigned long long e[K7_LIST_PER];
+#pragma unroll
+        for (int u = 0; u < K7_LIST_PER; ++u) {
+            const unsigned int i = i0 + 32 * u + lane;
+            an[u] = i < n ? __ldcg(list + i) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < K7_LIST_PER; ++u) {
+            const unsigned int i = i0 + 32 * u + lane;
+            e[u] = i < n ? __ldcg(best + an[u]) : 0ull;
+        }
+        bool pos[K7_LIST_PER];
+        int npos = 0;
+#pragma unroll
+        for (int u = 0; u < K7_LIST_PER; ++u) {
+            const unsigned int a = an[u];
+            bool ign = false;
+            pos[u] = false;
+            if (K7_BEST_GEN(e[u]) == SRC.gen) {   // (an entry beyond n reads 0: generation 0 is never used)
+                if (SRC.consume) const_cast<unsigned long long*>(best)[a] = 0ull;
+                const float iou = __uint_as_float(K7_BEST_IOU_BITS(e[u]));
+                pos[u] = iou >= SRC.pos_thr;
+                ign = !pos[u] && !(iou < SRC.neg_thr);
+            }
+            if (ign) atomicOr(Q.bits + (size_t)b * Q.W + (a >> 5), 1u << (a & 31u));
+            npos += __popc(__ballot_sync(0xffffffffu, pos[u]));
+        }
+        if (npos == 0) continue;   // warp-uniform
+        unsigned int base = 0u;    // ONE atomic per warp and trip, on the image's own counter
+        if (lane == 0) {
+            base = atomicAdd(Q.count + (size_t)b * K7_BEST_CNT_STRIDE, (unsigned int)npos);
+            atomicAdd(num_pos + b, npos);
+        }
+        base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+        for (int u = 0; u < K7_LIST_PER; ++u) {
+            const unsigned int pm = __ballot_sync(0xffffffffu, pos[u]);
+            if (pos[u]) Q.q[(size_t)b * P.A + base + (unsigned int)__popc(pm & ((1u << lane) - 1u))] = make_uint2(an[u], (unsigned int)K7_BEST_ROW(e[u]));
+            base += (unsigned int)__popc(pm);
+        }
+    }
+}
+
+// SERVE KERNEL, after the stream: the queue of positive rows, densely, a thread each: smooth-L1 + d(reg)
+// (losses.py:122-166) and the correction of the label element from "target 0" (what the stream computed)
+// to "target 1" (losses.py:94-112).  (Ignored rows never reach it: the stream skips them by the bitmap.)
 // Contributions are added to the image's two accumulators as 2^-32 fixed-point integers (integer
-// atomics: exact, independent of the order).  The last block to finish sums, per image, the
-// stream's per-CTA partials in float64 in CTA order, adds the accumulators and writes
-// (cls_loss_i, reg_loss_i); then the batch sums in image order.  No float atomics anywhere:
-// bit-reproducible run to run.
+// atomics: exact, independent of the order) - the stream's CTAs added theirs the same way.  The last
+// block to finish turns the accumulators into (cls_loss_i, reg_loss_i), then the batch sums in image
+// order.  No float atomics anywhere: bit-reproducible run to run.
 __device__ __forceinline__ void k7_acc_add(long long* __restrict__ acc, int b, int which, double v, int lane) {
-    // one atomic per warp when the warp's lanes work on one image (the usual case), else one per lane
-    long long iv = __double2ll_rn(v * K7_FIX_ONE);
-    const int b0 = __shfl_sync(0xffffffffu, b, 0);
-    if (__all_sync(0xffffffffu, b == b0)) {
-        iv = k7_warp_sum_i64(iv);
-        if (lane == 0 && iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b0 + which), (unsigned long long)iv);
-    } else if (b >= 0 && iv) {
-        atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * b + which), (unsigned long long)iv);
+    // one atomic per image present in the warp (neighbours in the queue mostly share their image; b < 0: no row)
+    const long long iv = b >= 0 ? __double2ll_rn(v * K7_FIX_ONE) : 0ll;
+    unsigned int left = __ballot_sync(0xffffffffu, b >= 0);
+    while (left) {   // warp-uniform
+        const int leader = __ffs(left) - 1;
+        const int gb = __shfl_sync(0xffffffffu, b, leader);
+        const bool mine = b == gb;
+        const long long sum = k7_warp_sum_i64(mine ? iv : 0ll);
+        if (lane == leader && sum) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * gb + which), (unsigned long long)sum);
+        left &= ~__ballot_sync(0xffffffffu, mine);
     }
 }
 
@@ -710,19 +928,20 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
     const int A = P.A, C = P.C;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float oma = P.one_m_alpha;
-    const unsigned int npos = __ldcg(Q.count + 0), nign = __ldcg(Q.count + 1);
+    const int img = blockIdx.y;   // grid (blocks per image, B)
+    const unsigned int npos = __ldcg(Q.count + (size_t)img * K7_BEST_CNT_STRIDE);
 
-    // ---- positive rows: a thread each (whole warps stay in the loop: the fold below is warp-wide)
+    // ---- positive rows of image `img`: a thread each (whole warps stay in the loop: the fold below is warp-wide)
     for (unsigned int i0 = blockIdx.x * K7_ROWS_THREADS; i0 < npos; i0 += gridDim.x * K7_ROWS_THREADS) {
         const unsigned int i = i0 + threadIdx.x;
         int b = -1;
         float cfix = 0.0f, rsum = 0.0f;
         if (i < npos) {
-            const uint2 ent = __ldcg(Q.q + i);
+            const uint2 ent = __ldcg(Q.q + (size_t)img * A + i);
             const int a = (int)ent.x;
-            b = (int)(ent.y >> 16);
+            b = img;
             const size_t R = (size_t)b * A + a;
-            const float* arow = annotations + ((size_t)b * P.M + (ent.y & 0xffffu)) * 5;
+            const float* arow = annotations + ((size_t)b * P.M + ent.y) * 5;
             const float2 sc = k7_loss_scales(__ldg(num_pos + b), P.mean_div);
             rsum = k7_row_smooth_l1<GRAD, FROM_SPEC>(spec, anchors, box_order, P, a, R, arow, reg, sc.y, dreg);
             const int label = (int)__ldg(arow + 4);   // .long() truncation, losses.py:97
@@ -756,92 +975,21 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
         k7_acc_add(acc, b, 1, (double)rsum, lane);
     }
 
-    // ---- ignored rows: a warp each, eight consecutive queue entries per visit.  Neighbours in the queue come from
-    // one block of the scan, i.e. from one image: their contributions are added up (as integers) and leave the warp
-    // with ONE atomic per run - a quarter of a million atomics on 64 addresses was what this kernel waited for.
-    const unsigned int gw = (blockIdx.x * K7_ROWS_THREADS + threadIdx.x) >> 5, nw = (gridDim.x * K7_ROWS_THREADS) >> 5;
-    constexpr unsigned int RUN = 8;
-    for (unsigned int base = gw * RUN; base < nign; base += nw * RUN) {
-        long long run_iv = 0;
-        int run_b = -1;
-        const unsigned int rend = min(base + RUN, nign);
-        for (unsigned int i = base; i < rend; ++i) {
-            const uint2 ent = __ldcg(Q.q + (Q.cap - 1ull - i));
-            const int a = (int)ent.x, b = (int)(ent.y >> 16);
-            if (b != run_b) {   // warp-uniform
-                if (run_b >= 0) {
-                    run_iv = k7_warp_sum_i64(run_iv);
-                    if (lane == 0 && run_iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * run_b), (unsigned long long)run_iv);
-                }
-                run_b = b;
-                run_iv = 0;
-            }
-            const float* src;
-            float* dst;
-            size_t e0, stride = 1;
-            if (LEVELS) {
-                int l = 0;
-#pragma unroll
-                for (int i2 = 1; i2 < K7_MAX_LEVELS; ++i2)
-                    if (i2 < spec.num_levels && a >= spec.offset[i2]) l = i2;
-                const int r = a - spec.offset[l], K = spec.cell_anchors;
-                const int cell = r / K, k = r - cell * K;
-                stride = (size_t)LT.S[l];
-                e0 = ((size_t)b * K * C + (size_t)k * C) * stride + (size_t)cell;
-                src = LT.cls[l];
-                dst = LT.dcls[l];
-            } else {
-                e0 = ((size_t)b * A + a) * (size_t)C;
-                src = cls;
-                dst = dcls;
-            }
-            float csub = 0.0f;
-            for (int c0 = 0; c0 < C; c0 += 128) {   // four loads per lane in flight
-                float x[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int c = c0 + 32 * u + lane;
-                    x[u] = (c < C) ? __ldg(src + e0 + (size_t)c * stride) : 0.0f;
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int c = c0 + 32 * u + lane;
-                    if (c < C) {
-                        csub += k7_neg_exact(x[u], nullptr, P.from_logits != 0);
-                        if (GRAD) dst[e0 + (size_t)c * stride] = 0.0f;
-                    }
-                }
-            }
-            // what the stream added for this row, taken out again (this lane's share, 2^-32 fixed point)
-            run_iv += __double2ll_rn(-(double)oma * (double)csub * K7_FIX_ONE);
-        }
-        if (run_b >= 0) {
-            run_iv = k7_warp_sum_i64(run_iv);
-            if (lane == 0 && run_iv) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 2 * run_b), (unsigned long long)run_iv);
-        }
-    }
-
     // ---- the last block to finish reduces
     __threadfence();   // this thread's accumulator updates are performed before the block's tick
     __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == gridDim.x - 1u;
+    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1u;
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    // per-image sums (losses.py:118, 161-166): a warp per image, the stream's per-CTA partials in CTA order
-    for (int b = warp; b < P.B; b += NW) {
-        const float* pp = pipe_partials + (size_t)b * pipe_slots;
-        double c = 0.0;
-        for (uint32_t t = lane; t < pipe_slots; t += 32) c += (double)__ldcg(pp + t);
-        c = k7_warp_sum_f64(c);
-        if (lane == 0) {
-            const bool any_valid = Q.img_valid[b] != 0;
-            const int n = num_pos[b];
-            const double fc = (double)__ldcg(acc + 2 * b) * (1.0 / K7_FIX_ONE);
-            const double fr = (double)__ldcg(acc + 2 * b + 1) * (1.0 / K7_FIX_ONE);
-            per_image[2 * b + 0] = any_valid ? (float)(c + fc) / fmaxf((float)n, 1.0f) : 0.0f;
-            per_image[2 * b + 1] = (any_valid && n > 0) ? (float)(fr / (4.0 * (double)n)) : 0.0f;
-        }
+    // per-image losses (losses.py:118, 161-166): everything - the stream's share too - is in the two accumulators
+    for (int b = threadIdx.x; b < P.B; b += K7_ROWS_THREADS) {
+        const bool any_valid = Q.img_valid[b] != 0;
+        const int n = num_pos[b];
+        const double fc = (double)__ldcg(acc + 2 * b) * (1.0 / K7_FIX_ONE);
+        const double fr = (double)__ldcg(acc + 2 * b + 1) * (1.0 / K7_FIX_ONE);
+        per_image[2 * b + 0] = any_valid ? (float)fc / fmaxf((float)n, 1.0f) : 0.0f;
+        per_image[2 * b + 1] = (any_valid && n > 0) ? (float)(fr / (4.0 * (double)n)) : 0.0f;
     }
     __syncthreads();
 
@@ -1001,11 +1149,13 @@ struct K7LossPlan {
     unsigned long long AC[K7_MAX_LEVELS];   // elements per image of each stream
     uint32_t tile0[K7_MAX_LEVELS];
     size_t off_pipe;                        // per-warp slots of the launch
-    size_t off_counter, off_acc, off_valid, off_cta, off_queue, total;
+    size_t off_counter, off_acc, off_valid, off_poscnt, off_bits, off_cta, off_queue, total;
+    size_t zero_bytes;                      // counters .. anchor bitmap: cleared at the start of every call
+    size_t off_lbits[K7_MAX_LEVELS];        // per-level streams: the ignore bits expanded to one per element
     uint32_t cta_stride;
 };
 
-static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g);
+static int k7_pipe_geometry(bool grad, int B, int C, K7PipeGeom* g);
 
 // levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
 static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
@@ -1018,7 +1168,12 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
     o += k7_align_up(sizeof(long long) * 2 * (size_t)B, 256);
     p->off_valid = o;     // [B] the image has an annotation row
     o += k7_align_up((size_t)B, 256);
-    int rc = k7_pipe_geometry(grad, B, &p->G);
+    p->off_poscnt = o;    // [B] positives per image, K7_BEST_CNT_STRIDE words apart (the row queues' lengths)
+    o += k7_align_up(sizeof(unsigned int) * K7_BEST_CNT_STRIDE * (size_t)B, 256);
+    p->off_bits = o;      // [B][K7_IGNORE_WORDS(A)] one bit per anchor: the row is ignored (losses.py:79-82)
+    o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(A), 256);
+    p->zero_bytes = o - p->off_counter;
+    int rc = k7_pipe_geometry(grad, B, levels ? 1 : C, &p->G);
     if (rc) return rc;
     unsigned long long tiles = 0;
     const int nl = levels ? spec->num_levels : 1;
@@ -1035,6 +1190,8 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
         p->tile0[i] = (uint32_t)tiles;
         tiles += (((ac * (unsigned long long)B) & ~3ull) + p->G.tile_f - 1) / p->G.tile_f;
         K7_REQUIRE(tiles < (1ull << 31), "k7_loss: %llu tiles exceed the 32-bit tile index", tiles);
+        p->off_lbits[i] = o;
+        if (levels) o += k7_align_up(sizeof(uint32_t) * (size_t)B * K7_IGNORE_WORDS(ac), 256);
     }
     p->G.num_tiles = (uint32_t)tiles;
     int grid = exact_grid ? k7_sm_count() : K7_LOSS_MAX_GRID;   // the workspace query has no device: assume the largest grid
@@ -1073,7 +1230,7 @@ static int k7_env_int(const char* name, int dflt) {
     return atoi(v);
 }
 
-static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g) {
+static int k7_pipe_geometry(bool grad, int B, int C, K7PipeGeom* g) {
     // Tuned on B200 (tools/tune_loss.py, C2 and C5): the forward pass wants long slices (12 warps x
     // 1024 floats: fewer per-slice waits); with gradients the stream is a copy and wants the most
     // warps on short slices (16 x 512) and no more than four 32 KB stages in flight.
@@ -1085,7 +1242,11 @@ static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g) {
     g->cw = cw;
     g->slice = (uint32_t)slice;
     g->tile_f = (uint32_t)cw * (uint32_t)slice;
-    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4, 128);
+    g->div_c = k7_fastdiv_make((uint32_t)C);
+    // rows touching a tile: (tile_f-1)/C + 2 at most; a part starts up to 127 bits into its first 16 bytes
+    const uint32_t nrows_max = (g->tile_f - 1) / (uint32_t)C + 2;
+    g->side_words = (((nrows_max + 254u) >> 7) + 1u) << 2;
+    g->stage_stride = (uint32_t)k7_align_up((size_t)g->tile_f * 4 + (size_t)(2 * g->side_words + 4) * 4, 128);
     const size_t sco_bytes = (grad && B <= K7_PIPE_SCO_MAX) ? k7_align_up(sizeof(float) * (size_t)B, 16) : 0;
     const size_t budget = 226 * 1024 - sco_bytes;
     int stages = (int)((budget - 64) / ((size_t)g->stage_stride + sizeof(K7TileDesc) + 16));
@@ -1104,6 +1265,13 @@ static int k7_pipe_geometry(bool grad, int B, K7PipeGeom* g) {
     o += sco_bytes;
     g->smem_bytes = o;
     return K7_OK;
+}
+
+// blocks per image of the per-image row kernels: about `per_sm` blocks per SM in total
+static unsigned k7_rows_gx(int B, int per_sm) {
+    const int want = per_sm * k7_sm_count();
+    int gx = (want + B - 1) / B;
+    return (unsigned)(gx < 1 ? 1 : gx);
 }
 
 static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_order, const float* cls,
@@ -1164,7 +1332,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     P.B = B; P.A = A; P.C = C; P.M = M;
 
     // counters + accumulators are contiguous at the start of the workspace
-    K7_CUDA(cudaMemsetAsync(ws + L.off_counter, 0, L.off_acc - L.off_counter + sizeof(long long) * 2 * (size_t)B, st));
+    K7_CUDA(cudaMemsetAsync(ws + L.off_counter, 0, L.zero_bytes, st));   // counters, accumulators, img_valid, the anchor bitmap
     K7_CUDA(cudaMemsetAsync(num_pos, 0, sizeof(int32_t) * (size_t)B, st));
 
     K7AssignSrc SRC;
@@ -1178,11 +1346,21 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     SRC.consume = params->consume_best ? 1 : 0;
     K7RowQueues RQ;
     RQ.q = reinterpret_cast<uint2*>(ws + L.off_queue);
-    RQ.count = counter + 4;
+    RQ.count = reinterpret_cast<unsigned int*>(ws + L.off_poscnt);
     RQ.cap = (unsigned long long)B * (unsigned long long)A;
     RQ.img_valid = ws + L.off_valid;
+    RQ.bits = reinterpret_cast<uint32_t*>(ws + L.off_bits);
+    RQ.W = (int)K7_IGNORE_WORDS(A);
     float4* dreg4 = reinterpret_cast<float4*>(dreg);
-    {   // the scan: num_pos, the row queues, the zeros of d(reg)
+    if (best && !SRC.words_out) {
+        // the list: k7_match_scatter left the anchors it touched behind its array (K7_BEST_LIST_OFFSET)
+        const unsigned char* raw = reinterpret_cast<const unsigned char*>(best);
+        const unsigned int* tcount = reinterpret_cast<const unsigned int*>(raw + k7_best_list_off(B, A));
+        const unsigned int* tlist = reinterpret_cast<const unsigned int*>(raw + k7_best_list_off(B, A) + k7_best_list_hdr(B));
+        if (grad && !P.dreg_prezeroed) K7_CUDA(cudaMemsetAsync(dreg, 0, sizeof(float4) * (size_t)B * (size_t)A, st));
+        k7_loss_list_kernel<<<dim3(k7_rows_gx(B, 4), B), K7_ROWS_THREADS, 0, st>>>(annotations, SRC, P, RQ, num_pos, tcount, tlist);
+        K7_LAUNCH_CHECK();
+    } else {   // the scan: num_pos, the row queues, the zeros of d(reg)
         const long long chunks = (long long)B * ((A + K7_ROWS_CHUNK - 1) / K7_ROWS_CHUNK);
         long long blocks = chunks;
         const long long cap = 8ll * k7_sm_count();   // eight resident blocks of 256 threads per SM; the rest is looped
@@ -1203,16 +1381,22 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     K7PipeSegs SG;
     memset(&SG, 0, sizeof(SG));
     SG.n = L.nseg;
+    K7ExpandTable ET;
+    memset(&ET, 0, sizeof(ET));
+    int eblocks = 0;
     for (int i = 0; i < L.nseg; ++i) {
         K7PipeSeg& Q = SG.s[i];
         Q.cls = cls;
         Q.dcls = dcls;
+        Q.bits = RQ.bits;
         Q.AC = L.AC[i];
         Q.N = Q.AC * (unsigned long long)B;
         Q.N4 = Q.N & ~3ull;
+        Q.A = (uint32_t)A;
         Q.tile0 = L.tile0[i];
         if (lv) {
             const int l = L.level[i];
+            const int S = spec->fh[l] * spec->fw[l], K = spec->cell_anchors;
             Q.cls = levels[l];
             Q.dcls = grad ? dlevels[l] : nullptr;
             K7_REQUIRE(Q.cls && (reinterpret_cast<uintptr_t>(Q.cls) & 15) == 0 &&
@@ -1220,15 +1404,37 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
                        "k7_loss_levels: level %d: null or unaligned tensor", l);
             LT.cls[l] = Q.cls;
             LT.dcls[l] = Q.dcls;
-            LT.S[l] = spec->fh[l] * spec->fw[l];
+            LT.S[l] = S;
+            Q.A = (uint32_t)Q.AC;   // C == 1 mode: a row per element
+            uint32_t* lbits = reinterpret_cast<uint32_t*>(ws + L.off_lbits[i]);
+            Q.bits = lbits;
+            const long long threads = (S & 31) == 0 ? (long long)K * (S >> 5) : ((long long)K * C * S + 31) / 32;
+            ET.lbits[i] = lbits;
+            ET.level_off[i] = spec->offset[l];
+            ET.S[i] = S;
+            ET.Wl[i] = (int)K7_IGNORE_WORDS(Q.A);
+            ET.blk_off[i] = eblocks;
+            eblocks += (int)((threads + 255) / 256);
         }
+        Q.W = (uint32_t)K7_IGNORE_WORDS(Q.A);
+    }
+    if (lv && eblocks > 0) {
+        for (int i = L.nseg; i <= K7_MAX_LEVELS; ++i) ET.blk_off[i] = eblocks;
+        dim3 grid(eblocks, B);
+        k7_bits_expand_kernel<<<grid, 256, 0, st>>>(RQ.bits, RQ.W, ET, spec->cell_anchors, C);
+        K7_LAUNCH_CHECK();
     }
     if (L.G.num_tiles > 0 || L.nseg > 0) {
         const K7PipeGeom& G = L.G;
         float* pipe_partials = reinterpret_cast<float*>(ws + L.off_pipe);
+        K7LossDev Ps = P;
+        if (lv) {
+            Ps.A = 0;   // per stream: K7PipeSeg::A
+            Ps.C = 1;
+        }
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, RQ.img_valid, P, G, pipe_partials, cta_partials);
+            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, RQ.img_valid, Ps, G, pipe_partials, acc);
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
@@ -1262,7 +1468,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     }
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
-    const dim3 rgrid((unsigned)(8 * k7_sm_count()));   // the queue lengths are only known on the device: grid-stride loops
+    const dim3 rgrid(k7_rows_gx(B, 4), B);   // the queue lengths are only known on the device: grid-stride loops per image
 #define K7_SERVE_LAUNCH(GR, SP, LV)                                                                                      \
     k7_loss_serve_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
                                                                         RQ, num_pos, P, PR, cta_partials, L.cta_stride,   \

@@ -57,20 +57,23 @@ class _Workspace:
         return t
 
     def best_array(self, B: int, A: int, device):
-        """The uint64 [B*A] array of k7_match_scatter + the generation of this call + whether k7_loss has
-        to zero what it reads.  Zeroed when created; every call gets the next generation (stale entries
-        are ignored by their tag); after K7_BEST_GEN_MAX calls the array is zeroed again.  While a CUDA
-        graph is being captured the generation would be frozen into the graph, so the replays reuse
-        ONE generation and k7_loss clears the entries it consumes (K7LossParams.consume_best)."""
+        """The buffer of k7_match_scatter (uint64 [B*A] maxima + the list of touched anchors behind them, as
+        int64 words) + the generation of this call + whether k7_loss has to zero what it reads.  Zeroed when
+        created and whenever B or A change (the list of one shape must not be read as maxima of another);
+        every call gets the next generation (stale entries are ignored by their tag); after K7_BEST_GEN_MAX
+        calls the array is zeroed again.  While a CUDA graph is being captured the generation would be frozen
+        into the graph, so the replays reuse ONE generation and k7_loss clears the entries it consumes
+        (K7LossParams.consume_best)."""
         key = self._key("best", device)
         ent = self.best.get(key)
-        n = B * A
-        if ent is None or ent[0].numel() < n:
-            ent = [torch.zeros(n, dtype=torch.int64, device=device), 0]
+        words = (L.lib().k7_match_scatter_workspace_bytes(B, A) + 7) // 8
+        if ent is None or ent[0].numel() < words:
+            ent = [torch.zeros(words, dtype=torch.int64, device=device), 0, (B, A)]
             self.best[key] = ent
-        if ent[1] >= L.BEST_GEN_MAX:
+        if ent[1] >= L.BEST_GEN_MAX or ent[2] != (B, A):
             ent[0].zero_()
             ent[1] = 0
+            ent[2] = (B, A)
         ent[1] += 1
         return ent[0], ent[1], bool(torch.cuda.is_current_stream_capturing())
 
@@ -83,9 +86,12 @@ def scatter_ok(spec, M: int, neg_thr: float, pos_thr: float) -> bool:
     return spec is not None and M <= 65535 and 1e-3 < neg_thr < 1.0 and pos_thr >= neg_thr
 
 
-def match_scatter(spec, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float):
-    """k7_match_scatter: returns (best [B*A] uint64-as-int64, generation, consume).  The positives are counted
-    by the loss stage, which walks the array anyway."""
+def match_scatter(spec, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: float,
+                  zero_fill: Optional[torch.Tensor] = None):
+    """k7_match_scatter: returns (best buffer as int64 words - [B*A] maxima, then the touched list -, generation,
+    consume).  The positives are counted by the loss stage, which walks the touched list.
+    zero_fill: optional [B,A,4] float32 tensor the kernel fills with zeros on the way (the d(reg) buffer of the
+    loss stage that follows)."""
     L.require_cuda(annotations)
     ann = L.as_f32_contig(annotations)
     B, M = ann.shape[0], ann.shape[1]
@@ -94,7 +100,7 @@ def match_scatter(spec, annotations: torch.Tensor, A: int, neg_thr: float, pos_t
     p = L.K7MatchParams(neg_thr, pos_thr)
     with torch.cuda.device(dev):
         L.check(L.lib().k7_match_scatter(C.byref(spec), L.ptr(ann), B, A, M, C.byref(p), L.ptr(best), gen,
-                                         L.stream_ptr(dev)), "k7_match_scatter")
+                                         L.ptr(zero_fill), L.stream_ptr(dev)), "k7_match_scatter")
     return best, gen, consume
 
 
@@ -218,8 +224,8 @@ def _assignment(anchor_src, ann, A, cfg, dreg0):
     sp = spec_of(anchor_src)
     num_pos = torch.empty(ann.shape[0], dtype=torch.int32, device=ann.device)     # written by the loss stage
     if scatter_ok(sp, ann.shape[1], cfg["neg_thr"], cfg["pos_thr"]):
-        arr, gen, consume = match_scatter(sp, ann, A, cfg["neg_thr"], cfg["pos_thr"])
-        return None, (arr, gen, consume, cfg["neg_thr"], cfg["pos_thr"]), num_pos, None
+        arr, gen, consume = match_scatter(sp, ann, A, cfg["neg_thr"], cfg["pos_thr"], zero_fill=dreg0)
+        return None, (arr, gen, consume, cfg["neg_thr"], cfg["pos_thr"]), num_pos, dreg0
     assign, _ = match(anchor_src, ann, A, cfg["neg_thr"], cfg["pos_thr"], cfg["box_order"], zero_fill=dreg0)
     return assign, None, num_pos, dreg0
 

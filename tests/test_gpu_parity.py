@@ -204,7 +204,7 @@ def test_loss_from_words_and_from_best_agree(path):
     BL.loss_stage(sp, cls, reg, ann, None, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
     for _ in range(2):
         L.check(L.lib().k7_match_scatter(C.byref(sp), L.ptr(ann), B, A, ann.shape[1], C.byref(p), L.ptr(arr), gen,
-                                         L.stream_ptr(DEV)), "k7_match_scatter")
+                                         None, L.stream_ptr(DEV)), "k7_match_scatter")
         num_pos3 = torch.empty_like(num_pos)
         c = BL.loss_stage(sp, cls, reg, ann, None, num_pos3, best=(arr, gen, True, thr[0], thr[1]), mean_divisor=B, **kw)
         assert torch.equal(num_pos, num_pos3)

@@ -40,16 +40,33 @@ def main():
 
     def best():
         """A fresh assignment of the production path (every scatter call starts a new generation of the array)."""
-        arr, gen, consume = BL.match_scatter(sp, ann, A, *thr)
+        arr, gen, consume = BL.match_scatter(sp, ann, A, *thr, zero_fill=dreg0)
         return dict(assign=None, num_pos=None, best=(arr, gen, consume, *thr))
 
     def loss(c, want_grad, **extra):
         a = cur[0]
-        return BL.loss_stage(anc, c, reg, ann, a["assign"], a["num_pos"], want_grad=want_grad, best=a["best"], **extra, **kw)
+        return BL.loss_stage(anc, c, reg, ann, a["assign"], a["num_pos"], want_grad=want_grad, best=a["best"],
+                             dreg_zeroed=dreg0 if want_grad else None, **extra, **kw)
+
+    loss_mod = b200det.FocalLoss()
+    cls_g, reg_g = cls.detach().requires_grad_(True), reg.detach().requires_grad_(True)
+
+    def train():
+        cls_g.grad = None
+        reg_g.grad = None
+        lc, lr = loss_mod(cls_g, reg_g, anc, ann)
+        (lc + lr).sum().backward()
+
+    def fwd_only():
+        with torch.no_grad():
+            return loss_mod(cls, reg, anc, ann)
 
     cur = [best()]
     stages = {
         "match": lambda: BL.match_scatter(sp, ann, A, *thr),
+        "match_zero": lambda: BL.match_scatter(sp, ann, A, *thr, zero_fill=dreg0),
+        "module_fwd": fwd_only,
+        "module_fwd_bwd": train,
         "match_exhaustive": lambda: BL.match(anc, ann, A, *thr, zero_fill=dreg0),
         "loss_fwd": lambda: loss(cls, False),
         "loss_fwd_bwd": lambda: loss(cls, True),
