@@ -54,6 +54,9 @@ def parse():
                          "falls back to NCCL if the mailboxes cannot be mapped) or NCCL all_reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip parts.configs (stage times of the other BASELINE configs)")
+    ap.add_argument("--no-shard-part", action="store_true", help="skip parts.c5_shard (EfficientDet-D7 batch 64 split over the ranks)")
+    ap.add_argument("--serial", action="store_true", help="run both halves of the step on one stream")
     return ap.parse_args()
 
 
@@ -185,7 +188,7 @@ def run_reference(args, wl):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": dict(workload_config(wl, wl.batch, args.gpus), sample_images_per_step=n),
+        "config": workload_config(wl, wl.batch, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -193,13 +196,14 @@ def run_reference(args, wl):
 
 
 def workload_config(wl, batch, gpus):
+    """The `config` object: identical in both arms (b200 / reference) for the same command line."""
     return {"workload": wl.name, "image": [wl.height, wl.width], "batch_per_gpu": batch, "global_batch": batch * gpus,
             "classes": wl.classes, "anchors_per_image": wl.anchors, "max_gt_per_image": wl.max_gt,
             "step": "FocalLoss fwd+bwd + decode/clip/threshold/sort/NMS on every image",
             "cache": (f"inputs ({batch * wl.anchors * (4 * wl.classes + 16) / 1e9:.2f} GB per rank and pass) are larger than "
                       "the 126 MB L2; no flush needed") if batch * wl.anchors * (4 * wl.classes + 16) > 4 * 126e6 else
                      "inputs fit (partly) in the 126 MB L2: L2-warm numbers, not comparable with the HBM roofline",
-            "parallelism": f"image-sharded x{gpus}, one 16-byte all-reduce per step" if gpus > 1 else "single GPU"}
+            "parallelism": f"image-sharded x{gpus}, the four loss sums exchanged once per step" if gpus > 1 else "single GPU"}
 
 
 # ------------------------------------------------------------------------------ B200 arm
@@ -217,6 +221,107 @@ def timed(fn, steps, warmup, stream_sync=True):
     return e0.elapsed_time(e1) / steps
 
 
+def bind_to_gpu_numa(local, local_world):
+    """Bind this process (and with it the first-touch placement of its pinned host buffers) to a disjoint share of
+    the cores of the NUMA node its GPU hangs on.  Returns a description for the JSON line."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = -1
+        try:
+            with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+                node = int(f.read().strip())
+        except Exception:
+            pass
+        allowed = sorted(os.sched_getaffinity(0))
+        cores = allowed
+        if node >= 0:
+            with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                lst = []
+                for part in f.read().strip().split(","):
+                    a, _, b = part.partition("-")
+                    lst += list(range(int(a), int(b or a) + 1))
+            cores = [c for c in lst if c in set(allowed)] or allowed
+        # the ranks whose GPUs share the node split its cores; without topology knowledge: an even split by local rank
+        per = max(1, len(cores) // max(1, local_world))
+        mine = cores[(local * per) % len(cores):][:per] or cores
+        os.sched_setaffinity(0, mine)
+        torch.set_num_threads(max(1, min(len(mine), 8)))
+        return {"gpu_pci": bdf, "numa_node": node, "cores": f"{mine[0]}-{mine[-1]} ({len(mine)})"}
+    except Exception as e:
+        return {"error": str(e)[:120]}
+
+
+class HotPath:
+    """One workload on one GPU: inputs, modules and the step of the bench."""
+
+    def __init__(self, wl, B, dev, seed, world=1, peer="auto"):
+        import b200det
+        self.b200det, self.wl, self.B, self.dev = b200det, wl, B, dev
+        self.hw = (wl.height, wl.width)
+        self.cls, self.reg, self.ann = b200det.synth.make_inputs(wl, seed=seed, device=dev, batch=B)
+        self.img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
+        self.anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
+        self.loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer)
+        self.cls_g = self.cls.detach().requires_grad_(True)
+        self.reg_g = self.reg.detach().requires_grad_(True)
+        self.side = torch.cuda.Stream(device=dev)
+
+    def train_side(self):
+        self.cls_g.grad = None
+        self.reg_g.grad = None
+        lc, lr = self.loss_mod(self.cls_g, self.reg_g, self.anchors_mod(self.img), self.ann)
+        (lc + lr).sum().backward()
+        return lc, lr
+
+    def fwd_only(self):
+        with torch.no_grad():
+            return self.loss_mod(self.cls, self.reg, self.anchors_mod(self.img), self.ann)
+
+    def eval_side(self, sync=False):
+        return self.b200det.detect(self.cls, self.reg, self.anchors_mod(self.img), self.hw, sync=sync)
+
+    def step_serial(self):
+        self.train_side()
+        self.eval_side()
+
+    def step(self):
+        """The two halves of a step are independent: decode/NMS runs on a second stream, so its latency-bound tail
+        (sort / pair tests / resolve: SM-light) overlaps the training side's streaming kernels and vice versa.
+        Workspaces are per stream (losses._Workspace), results are joined before the step ends."""
+        cur = torch.cuda.current_stream(self.dev)
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            self.eval_side()
+        self.train_side()
+        cur.wait_stream(self.side)
+
+    def bytes(self, surv=0):
+        wl, B = self.wl, self.B
+        A, C, M = wl.anchors, wl.classes, wl.max_gt
+        return (B * (A * (4 * C + 16) + 20 * M), B * (A * (8 * C + 32) + 20 * M), B * A * (4 * C + 16) + 32 * surv)
+
+    def stage_times(self, k, peak):
+        """Stage times of this workload (ms) and their fraction of the HBM peak (SURVEY 8d bytes)."""
+        from b200det import losses as BL
+        A = self.wl.anchors
+        anc = self.anchors_mod(self.img)
+        sp = self.b200det.spec_of(anc)
+        ms_fwd = timed(self.fwd_only, k, 3)
+        ms_fb = timed(self.train_side, k, 3)
+        ms_det = timed(self.eval_side, k, 3)
+        ms_step = timed(self.step, k, 3)
+        ms_match = timed(lambda: BL.match_scatter(sp, self.ann, A, 0.35, 0.45), k, 3)
+        surv = int(self.eval_side(sync=True).survivors.sum())
+        bf, bfb, bd = self.bytes(surv)
+        g = lambda nbytes, ms: nbytes / (ms * 1e-3) / 1e9 / peak
+        return {"batch": self.B, "anchors_per_image": A, "classes": self.wl.classes,
+                "k7_match_ms": ms_match, "match_loss_fwd_ms": ms_fwd, "match_loss_fwd_hbm_frac": g(bf, ms_fwd),
+                "match_loss_fwd_bwd_ms": ms_fb, "match_loss_fwd_bwd_hbm_frac": g(bfb, ms_fb),
+                "decode_nms_ms": ms_det, "decode_nms_hbm_frac": g(bd, ms_det), "survivors_per_image": surv / self.B,
+                "step_ms": ms_step, "images_per_s": self.B / ms_step * 1e3}
+
+
 def run_b200(args, wl):
     import torch.distributed as dist
     import b200det
@@ -226,13 +331,15 @@ def run_b200(args, wl):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (b200det has no CPU path); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    binding = bind_to_gpu_numa(local, local_world) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    L.lib()                                                    # fail loudly if libk7det.so is missing
+    lib = L.lib()                                              # fail loudly if libk7det.so is missing
 
     B = args.batch or wl.batch
     if args.shard:
@@ -240,49 +347,51 @@ def run_b200(args, wl):
             raise SystemExit(f"--shard: batch {B} does not divide over {world} ranks")
         B //= world                                            # rank r owns images [r*B, (r+1)*B) of the global batch
     A, C, M = wl.anchors, wl.classes, wl.max_gt
-    hw = (wl.height, wl.width)
-    cls, reg, ann = b200det.synth.make_inputs(wl, seed=rank, device=dev, batch=B)
-    img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
-    anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
     peer = "auto" if args.exchange == "auto" else False
-    loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer)
-    cls_g = cls.detach().requires_grad_(True)
-    reg_g = reg.detach().requires_grad_(True)
+    hp = HotPath(wl, B, dev, seed=rank, world=world, peer=peer)
+    cls, reg, ann, img, hw = hp.cls, hp.reg, hp.ann, hp.img, hp.hw
+    anchors_mod, loss_mod = hp.anchors_mod, hp.loss_mod
+    step = hp.step_serial if args.serial else hp.step
 
-    def train_side():
-        cls_g.grad = None
-        reg_g.grad = None
-        lc, lr = loss_mod(cls_g, reg_g, anchors_mod(img), ann)
-        (lc + lr).sum().backward()
-        return lc, lr
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
 
-    def eval_side(sync=False):
-        return b200det.detect(cls, reg, anchors_mod(img), hw, sync=sync)
-
-    def step():
-        train_side()
-        eval_side()
+    def timed_ranks(fn, steps, warmup):
+        """ms per call, barrier + synchronize on both sides, max over ranks."""
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
 
     # ---- value: K steps, device resident, barrier + synchronize on both sides, max over ranks
-    for _ in range(max(args.warmup, 3)):
+    W = max(args.warmup, 3)
+    for _ in range(W):
         step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    barrier()
+    n0 = lib.k7_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
         step()
     e1.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    barrier()
+    launches = int(lib.k7_launch_count() - n0)
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
@@ -291,41 +400,52 @@ def run_b200(args, wl):
 
     peak, peak_src = peaks()
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.shard else "weak",
         "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
-        "gpu_launches": 9 * args.steps,
-        "launches_per_step": {"k7_match": 1, "k7_loss(stream+rows)": 2, "k7_scale_inplace_multi": 1,
-                              "k7_detect(score+sort+mask+resolve)": 4, "k7_detect_gather": 1},
+        "gpu_launches": launches,
+        "gpu_launches_note": "counted by libk7det (k7_launch_count) over the timed region: every kernel of the library; "
+                             "autograd adds a few tiny ATen kernels per step, memsets are not kernels",
+        "step_schedule": "serial (one stream)" if args.serial else
+                         "decode/NMS on a second CUDA stream next to FocalLoss fwd+bwd, joined at the end of the step",
     }
-
     if world > 1:
-        ex = loss_mod.exchange
-        out["config"]["loss_exchange"] = ex
-        out["config"]["parallelism"] = (f"image-sharded x{world}; the four loss sums are exchanged " +
-                                        ("inside k7_loss over NVLink peer memory (no collective launch)" if ex == "p2p-fused"
-                                         else "with one 16-byte NCCL all-reduce per step"))
+        out["loss_exchange"] = loss_mod.exchange
+        out["host_binding"] = binding
+
+    # ---- exchange check (N > 1): the fused sums of one call against an all-reduce of the ranks' own sums
+    if world > 1:
+        hp.train_side()
+        fused = loss_mod.last_sums.detach().clone()
+        local_mod = b200det.FocalLoss()
+        with torch.no_grad():
+            local_mod(cls, reg, anchors_mod(img), ann)
+        ref = local_mod.last_sums.detach().clone()
+        dist.all_reduce(ref, op=dist.ReduceOp.SUM)
+        ok = bool(torch.isfinite(fused).all()) and bool(torch.allclose(fused, ref, rtol=1e-6, atol=0.0))
+        okt = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        out["exchange_check"] = bool(okt.item())
+        out["exchange_sums"] = {"fused": [float(x) for x in fused.tolist()], "all_reduce_of_local": [float(x) for x in ref.tolist()]}
 
     # ---- parts and the roofline of the dominant kernel (every rank runs them; rank 0 reports)
     k = max(args.steps, 10)
-    with torch.no_grad():
-        ms_fwd = timed(lambda: loss_mod(cls, reg, anchors_mod(img), ann), k, 3)
-    ms_fb = timed(train_side, k, 3)
-    ms_det = timed(eval_side, k, 3)
+    ms_fwd = timed(hp.fwd_only, k, 3)
+    ms_fb = timed(hp.train_side, k, 3)
+    ms_det = timed(hp.eval_side, k, 3)
+    ms_serial = timed(hp.step_serial, k, 3)
     anc = anchors_mod(img)
     sp_ = b200det.spec_of(anc)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
-    ms_match = timed(lambda: BL.match_scatter(sp_, ann, A, 0.35, 0.45), k, 3)
-    arr_, gen_, consume_ = BL.match_scatter(sp_, ann, A, 0.35, 0.45)
-    num_pos = None
+    dreg0 = torch.empty_like(reg)
+    ms_match = timed(lambda: BL.match_scatter(sp_, ann, A, 0.35, 0.45, zero_fill=dreg0), k, 3)
+    arr_, gen_, consume_ = BL.match_scatter(sp_, ann, A, 0.35, 0.45, zero_fill=dreg0)
     best_ = (arr_, gen_, consume_, 0.35, 0.45)
-    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=True, best=best_, **kw), k, 3)
-    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, num_pos, want_grad=False, best=best_, **kw), k, 3)
-    surv = int(eval_side(sync=True).survivors.sum())
-    bytes_fwd = B * (A * (4 * C + 16) + 20 * M)
-    bytes_fb = B * (A * (8 * C + 32) + 20 * M)
-    bytes_det = B * A * (4 * C + 16) + 32 * surv
+    ms_k_fb = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, None, want_grad=True, best=best_, dreg_zeroed=dreg0, **kw), k, 3)
+    ms_k_f = timed(lambda: BL.loss_stage(anc, cls, reg, ann, None, None, want_grad=False, best=best_, **kw), k, 3)
+    surv = int(hp.eval_side(sync=True).survivors.sum())
+    bytes_fwd, bytes_fb, bytes_det = hp.bytes(surv)
 
     def gbs(nbytes, ms):
         return nbytes / (ms * 1e-3) / 1e9
@@ -335,25 +455,28 @@ def run_b200(args, wl):
         "match_loss_fwd_bwd": {"ms": ms_fb, "images_per_s": B / ms_fb * 1e3, "hbm_frac": gbs(bytes_fb, ms_fb) / peak},
         "decode_nms": {"ms": ms_det, "images_per_s": B / ms_det * 1e3, "hbm_frac": gbs(bytes_det, ms_det) / peak,
                        "survivors_per_image": surv / B},
+        "step_one_stream": {"ms": ms_serial, "images_per_s": B / ms_serial * 1e3,
+                            "note": "the same step with both halves on one stream (what the previous round reported)"},
         "k7_match_ms": ms_match, "k7_loss_fwd_ms": ms_k_f, "k7_loss_fwd_bwd_ms": ms_k_fb,
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
+    del dreg0, arr_, best_
     # the same step captured once in a CUDA graph and replayed: what is left when the launch gaps between the
-    # nine kernels (and autograd's small ones) are gone.  Single GPU only: the fused peer exchange numbers its calls.
+    # kernels (and autograd's small ones) are gone.  Single GPU only: the fused peer exchange numbers its calls.
     if world == 1:
         try:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 for _ in range(3):
-                    step()
+                    hp.step_serial()
             torch.cuda.current_stream().wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                step()
+                hp.step_serial()
             ms_graph = timed(graph.replay, k, 3)
             out["parts"]["cuda_graph_step"] = {"ms": ms_graph, "images_per_s": B / ms_graph * 1e3,
-                                               "note": "torch.cuda.CUDAGraph capture of the same step() (FocalLoss fwd+bwd + "
+                                               "note": "torch.cuda.CUDAGraph capture of the one-stream step (FocalLoss fwd+bwd + "
                                                        "detect), replayed; the headline value is the eager step"}
             del graph
         except Exception as e:                                   # never let the extra measurement break the line
@@ -363,7 +486,8 @@ def run_b200(args, wl):
     # stock elementwise sigmoid pass (and its autograd backward) that they make unnecessary
     z = torch.logit(cls)
     z_g = z.detach().requires_grad_(True)
-    loss_lg = b200det.FocalLoss(sharded=world > 1, from_logits=True, peer_reduce=peer)
+    reg_g = hp.reg_g
+    loss_lg = b200det.FocalLoss(from_logits=True)
 
     def train_side_logits():
         z_g.grad = None
@@ -399,9 +523,12 @@ def run_b200(args, wl):
         "match_loss_fwd_bwd_ms": ms_fb_lv, "decode_nms_ms": ms_det_lv,
         "torch_layout_pass_ms_saved_per_side": ms_layout,
         "note": "FocalLoss / detect on the list of per-level [B, K*C, fh, fw] logits (retinanet.py:159-178 layout code skipped)"}
+    for t in lv_g:
+        t.grad = None
+    z_g.grad = None
     del z, z_g, lv, lv_g
     # the evaluators' per-image host loops (coco_eval.py:25-57) as one device call
-    det_e = eval_side(sync=True)
+    det_e = hp.eval_side(sync=True)
     scales_e = [1.0 + 0.01 * i for i in range(B)]
     ms_pack = timed(lambda: b200det.eval_pack(det_e, scales_e, mode="coco", num_classes=C), k, 3)
     out["parts"]["eval_tail"] = {"eval_pack_coco_ms": ms_pack, "detections": int(det_e.count.sum()),
@@ -409,11 +536,18 @@ def run_b200(args, wl):
                                          "3 launches + 1 sync); the host loop it replaces is timed in cpu_baseline.eval_tail_ms"}
     eval_inputs = (det_e.scores.cpu().numpy(), det_e.labels.cpu().numpy(), det_e.boxes.cpu().numpy(),
                    det_e.count.cpu().numpy(), scales_e, list(range(B)), list(range(C)))
-    ach = gbs(bytes_fb, ms_k_fb)
-    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: stream kernel + row/reduction kernel)",
+    del det_e
+    # the dominant kernel: the k7_loss call with gradients (list + stream + serve kernels).  Its bytes: classifications
+    # in, their gradient out (8 C per anchor) + the annotations; the 16 B/anchor zero fill of d(reg) is k7_match_scatter's
+    # and reg / d(reg) are touched for the ~3 % positive rows only, so neither is counted here.
+    bytes_loss = B * (A * 8 * C + 20 * M)
+    ach = gbs(bytes_loss, ms_k_fb)
+    traffic = ncu_traffic(wl.name, B)
+    out["roofline"] = {"bound": "hbm", "kernel": "k7_loss_pipe_kernel<grad> (timed as the k7_loss call: list kernel + stream kernel + serve/reduction kernel)",
                        "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                       "traffic": ncu_traffic(wl.name, B),
-                       "algorithmic_bytes_per_launch": bytes_fb, "avg_launch_ms": ms_k_fb, "peak_source": peak_src}
+                       "traffic": traffic,
+                       "traffic_source": "committed ncu --set full capture (profiles/traffic.json), not measured in this run" if traffic else None,
+                       "algorithmic_bytes_per_launch": bytes_loss, "avg_launch_ms": ms_k_fb, "peak_source": peak_src}
 
     # ---- e2e: pinned host inputs -> H2D -> public modules -> D2H of the results, every step
     if not args.no_e2e:
@@ -452,6 +586,7 @@ def run_b200(args, wl):
             losses = torch.cat([lc.detach(), lr.detach()]).cpu()
             counts = torch.cat([d.count for d in dets]).cpu()
             kmax = max(int(counts.max()), 1)
+            assert kmax <= dets[0].scores.shape[1], "detect(sync=False) returned fewer rows than an image kept: pass cap="
             res = (torch.cat([d.scores[:, :kmax] for d in dets]).cpu(), torch.cat([d.labels[:, :kmax] for d in dets]).cpu(),
                    torch.cat([d.boxes[:, :kmax] for d in dets]).cpu())
             d2h[0] = losses.numel() * 4 + B * 2 * 4 + sum(t.numel() * t.element_size() for t in res)
@@ -459,9 +594,7 @@ def run_b200(args, wl):
         n_e2e = max(3, min(args.steps, 10))
         for _ in range(2):
             e2e_step()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        barrier()
         t0 = time.perf_counter()
         for _ in range(n_e2e):
             e2e_step()
@@ -469,11 +602,70 @@ def run_b200(args, wl):
         ms_e2e = torch.tensor([(time.perf_counter() - t0) * 1e3 / n_e2e], device=dev)
         if world > 1:
             dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+        h2d = sum(t.numel() * 4 for t in (cls, reg, ann))
         out["e2e"] = {"value": world * B / (float(ms_e2e.item()) * 1e-3), "unit": UNIT,
-                      "h2d_bytes_per_step": sum(t.numel() * 4 for t in (cls, reg, ann)), "d2h_bytes_per_step": d2h[0],
+                      "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h[0],
                       "ms_per_step": float(ms_e2e.item()), "steps": n_e2e,
+                      "h2d_gb_per_s_all_ranks": world * h2d / (float(ms_e2e.item()) * 1e-3) / 1e9,
                       "note": "pinned host -> device copies (chunked on a copy stream, detect() of a chunk overlaps the next copy) + "
-                              "FocalLoss fwd+bwd + detect + results to host; PCIe-bound: the copy alone is 20.4 ms at 55 GB/s"}
+                              "FocalLoss fwd+bwd + detect + results to host; PCIe-bound: the copy alone is 20.4 ms at 55 GB/s per GPU"}
+        del h_cls, h_reg, h_ann, d_cls, d_reg, d_ann
+
+    # ---- the other BASELINE configurations on one GPU, at their BASELINE batch (stage times, not bench lines)
+    del hp, cls, reg, ann, img, anchors_mod, loss_mod, loss_lg, reg_g
+    torch.cuda.empty_cache()
+    if world == 1 and not args.no_configs and not args.batch and not args.shard:
+        out["parts"]["configs"] = {}
+        for name in ("c1_retinanet_r50_512", "c3_ksevendet_thermal_512x640", "c4_effdet_d3_896", "c5_effdet_d7_1536"):
+            if name == wl.name:
+                continue
+            try:
+                w2 = b200det.synth.WORKLOADS[name]
+                h2 = HotPath(w2, w2.batch, dev, seed=0)
+                out["parts"]["configs"][name] = h2.stage_times(10, peak)
+                del h2
+            except Exception as e:
+                out["parts"]["configs"][name] = {"error": str(e)[:200]}
+            torch.cuda.empty_cache()
+
+    # ---- north_star's multi-GPU target: EfficientDet-D7 1536^2, batch 64 SPLIT over the ranks (strong scaling),
+    # with the same run's one-GPU time of the whole batch next to it
+    if not args.no_shard_part and not args.batch and not args.shard:
+        try:
+            w5 = b200det.synth.WORKLOADS["c5_effdet_d7_1536"]
+            if w5.batch % world == 0:
+                Bs = w5.batch // world
+                h5 = HotPath(w5, Bs, dev, seed=rank, world=world, peer=peer)
+                ms_n = timed_ranks(h5.step, 10, 3)
+                rec = {"workload": w5.name, "global_batch": w5.batch, "images_per_gpu": Bs, "n_gpus": world,
+                       "ms_per_step": ms_n, "images_per_s": w5.batch / ms_n * 1e3, "scaling": "strong"}
+                if world > 1:
+                    rec["loss_exchange"] = h5.loss_mod.exchange
+                del h5
+                torch.cuda.empty_cache()
+                hs = HotPath(w5, Bs, dev, seed=rank)             # the rank's shard without the exchange: stage times
+                st = hs.stage_times(10, peak)
+                del hs
+                torch.cuda.empty_cache()
+                rec["stages_rank0"] = st
+                ms_1 = ms_n
+                if world > 1:
+                    dist.barrier()
+                    if rank == 0:                                   # the whole batch on ONE GPU, same run, same code
+                        h1 = HotPath(w5, w5.batch, dev, seed=0)
+                        ms_1 = timed(h1.step, 5, 2)
+                        del h1
+                        torch.cuda.empty_cache()
+                    dist.barrier()
+                rec["one_gpu_ms_per_step"] = ms_1
+                rec["speedup_vs_one_gpu"] = ms_1 / ms_n
+                rec["efficiency"] = ms_1 / ms_n / world
+                out["parts"]["c5_shard"] = rec
+        except Exception as e:
+            out["parts"]["c5_shard"] = {"error": str(e)[:300]}
+            if world > 1:
+                raise
+        torch.cuda.empty_cache()
 
     if rank == 0:
         out["clocks"] = sampler.stop()
@@ -484,9 +676,12 @@ def run_b200(args, wl):
             R_.eval_rows_coco(*eval_inputs)
             out["cpu_baseline"]["eval_tail_ms"] = (time.perf_counter() - t0) * 1e3
         print(json.dumps(out))
+    bad = world > 1 and not out.get("exchange_check", True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if bad:
+        raise SystemExit("bench.py: the fused loss-sum exchange disagrees with the all-reduce of the ranks' sums")
 
 
 def main():

@@ -81,6 +81,10 @@ typedef struct K7AnchorSpec {
 
 K7_API int k7_version(void);
 K7_API const char* k7_last_error(void);
+/* Kernels this library has launched in this process so far (all entry points, all threads): what a caller
+ * subtracts around a region to count launches.  Memsets and copies are not kernels and not counted.  No
+ * counterpart in the reference (measurement aid, bench.py's gpu_launches). */
+K7_API unsigned long long k7_launch_count(void);
 
 /* Replaces Anchors.forward (architectures/anchors.py:38-60; utils_efficientdet.py:74-137):
  * writes out[A,4] float32. */

@@ -129,6 +129,7 @@ _P = C.c_void_p
 SYMBOLS = {
     "k7_version": (C.c_int, []),
     "k7_last_error": (C.c_char_p, []),
+    "k7_launch_count": (C.c_ulonglong, []),
     "k7_anchors_materialize": (C.c_int, [C.POINTER(K7AnchorSpec), _P, _P]),
     "k7_match": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, C.c_int, C.c_int, C.c_int,
                            C.POINTER(K7MatchParams), _P, _P, _P, _P, _P, _P, _P]),

@@ -16,6 +16,10 @@ void k7_set_error(const char* fmt, ...) {
 extern "C" const char* k7_last_error(void) { return g_err; }
 extern "C" int k7_version(void) { return K7_ABI_VERSION; }
 
+static unsigned long long g_launches = 0;
+void k7_count_launch() { __atomic_fetch_add(&g_launches, 1ull, __ATOMIC_RELAXED); }
+extern "C" unsigned long long k7_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 int k7_sm_count() {
     static int cached[64] = {0};
     int dev = 0;

@@ -31,12 +31,18 @@ void k7_set_error(const char* fmt, ...);
         }                                                                              \
     } while (0)
 
-#define K7_LAUNCH_CHECK() K7_CUDA(cudaGetLastError())
+#define K7_LAUNCH_CHECK()              \
+    do {                               \
+        k7_count_launch();             \
+        K7_CUDA(cudaGetLastError());   \
+    } while (0)
 
 int k7_check_spec(const K7AnchorSpec* spec, int A);
 int k7_sm_count();
 
 static inline size_t k7_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+void k7_count_launch();   // every kernel launch of the library ticks k7_launch_count()
 
 // ------------------------------------------------------------------ programmatic dependent launch
 // Chains of short dependent kernels (sort -> mask -> resolve) pay a launch gap per link.  A kernel
@@ -67,6 +73,7 @@ static inline cudaError_t k7_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = k7_pdl_mask_next() ? 1 : 0;
+    k7_count_launch();
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 #endif

@@ -1949,11 +1949,11 @@ k7_nms_brute_kernel(const __grid_constant__ K7NmsArgs P, int B) {
         const size_t ob = (size_t)b * P.A, oc = (size_t)b * P.cap;
         const int nj = min(n, i0 + K7_BRUTE_ROWS);
         __syncthreads();   // the previous item is done with shared memory
-        for (int j = tid; j < nj; j += K7_BRUTE_THREADS) {
-            const float4 bx = __ldcg(P.rbox + oc + j);
+        for (int j = tid; j < ((nj + 63) & ~63); j += K7_BRUTE_THREADS) {
+            const float4 bx = j < nj ? __ldcg(P.rbox + oc + j) : make_float4(0.f, 0.f, 0.f, 0.f);   // padding: never hits
             s_box[j] = bx;
             s_ca[j] = K7_FMUL(c_flt, k7_area(bx.x, bx.y, bx.z, bx.w));
-            if (P.class_aware) s_lab[j] = __ldg(P.label_ws + ob + (uint32_t)(__ldcg(P.keys1 + ob + j) & 0xffffffffull));
+            if (P.class_aware) s_lab[j] = j < nj ? __ldg(P.label_ws + ob + (uint32_t)(__ldcg(P.keys1 + ob + j) & 0xffffffffull)) : -1;
         }
         __syncthreads();
         const int r = tid & (K7_BRUTE_ROWS - 1), ri = i0 + r, part = tid / K7_BRUTE_ROWS;
@@ -1964,15 +1964,47 @@ k7_nms_brute_kernel(const __grid_constant__ K7NmsArgs P, int B) {
             const K7Box me = {mb.x, mb.y, mb.z, mb.w};
             const float marea = k7_area(mb.x, mb.y, mb.z, mb.w), mca = row ? s_ca[ri] : 0.0f;
             const int mlabel = (row && P.class_aware) ? s_lab[ri] : 0;
-            const int rlast = min(n, (ri | 31));   // warp-uniform: candidates below the warp's last row
+            // Fast path per candidate: no branch, no division.  `yes` = suppressed for sure (the sufficient condition of
+            // k7_nms_decide), `maybe` = passed the necessary filter only: those few (within 2.2e-5 of the threshold, or
+            // overflowed) get the exact test afterwards.  32 candidates per register word with compile-time bit positions.
             for (int w = part; w < nw; w += K7_BRUTE_PARTS) {
-                unsigned long long word = 0ull;
-                const int j0 = w << 6, j1 = min(j0 + 64, rlast);
-                for (int rj = j0; rj < j1; ++rj) {
-                    const float4 cb = s_box[rj];                               // one address per warp: a broadcast
-                    bool hit = rj < ri && k7_nms_decide(me, marea, mca, cb, s_ca[rj], thr);
-                    if (P.class_aware) hit = hit && s_lab[rj] == mlabel;
-                    word |= (unsigned long long)hit << (rj & 63);
+                unsigned int yes[2] = {0u, 0u}, maybe[2] = {0u, 0u};
+                const int j0 = w << 6;
+#pragma unroll
+                for (int hw = 0; hw < 2; ++hw) {
+                    const int jb = j0 + 32 * hw;
+                    if (jb >= nj) break;   // block-uniform
+#pragma unroll 8
+                    for (int k = 0; k < 32; ++k) {
+                        const float4 cb = s_box[jb + k];                       // one address per warp: a broadcast
+                        const float cca = s_ca[jb + k];                        // (beyond nj: zero boxes, never hit: w <= 0)
+                        const float iw = K7_FSUB(fminf(me.x2, cb.z), fmaxf(me.x1, cb.x));
+                        const float ih = K7_FSUB(fminf(me.y2, cb.w), fmaxf(me.y1, cb.y));
+                        const float inter = K7_FMUL(iw, ih), sm = K7_FADD(mca, cca);
+                        const bool cand = (iw > 0.0f) & (ih > 0.0f) & (inter > sm);
+                        const bool sure = cand & (inter > K7_FMUL(sm, 1.0000221f)) & (inter <= 3.0e38f);
+                        yes[hw] |= sure ? (1u << k) : 0u;
+                        maybe[hw] |= (cand & !sure) ? (1u << k) : 0u;
+                    }
+                }
+                unsigned long long word = ((unsigned long long)yes[1] << 32) | yes[0];
+                unsigned long long mb2 = ((unsigned long long)maybe[1] << 32) | maybe[0];
+                while (mb2) {   // rare
+                    const int k = __ffsll((long long)mb2) - 1;
+                    mb2 &= mb2 - 1ull;
+                    const float4 cb = s_box[j0 + k];
+                    if (k7_nms_suppress_exact(me, marea, cb, k7_area(cb.x, cb.y, cb.z, cb.w), thr)) word |= 1ull << k;
+                }
+                if (w == blk) {   // the diagonal word: only boxes ranked before mine
+                    word &= (r == 0) ? 0ull : (~0ull >> (64 - r));
+                }
+                if (P.class_aware) {
+                    unsigned long long t = word;
+                    while (t) {
+                        const int k = __ffsll((long long)t) - 1;
+                        t &= t - 1ull;
+                        if (s_lab[j0 + k] != mlabel) word &= ~(1ull << k);
+                    }
                 }
                 s_mask[r * pitch + w] = row ? word : 0ull;
             }
@@ -2360,7 +2392,7 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
     int rc2 = k7_nms_chain(k7_nms_args(w, A, params->iou_thr, params->pre_nms_topk, params->class_aware != 0), B,
                            params->max_detections, w.kept_key, w.kept_box, w.kept_count, counts, nullptr, st);
     if (rc2) return rc2;
-    K7_LAUNCH_CHECK();
+    K7_CUDA(cudaGetLastError());
     return K7_OK;
 }
 
@@ -2399,7 +2431,7 @@ extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, i
     K7_CUDA(k7_launch_pdl(k7_gather_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream), A, w.W32, cap, w.kept_count,
                           w.kept_key, w.kept_box, w.label, w.bits, w.wprefix, scores, labels, reinterpret_cast<float4*>(boxes),
                           anchor_ids, survivor_rank));
-    K7_LAUNCH_CHECK();
+    K7_CUDA(cudaGetLastError());
     return K7_OK;
 }
 
@@ -2442,7 +2474,7 @@ static int k7_nms_run(const float* boxes, const float* scores, const int64_t* id
     P.box_ws = reinterpret_cast<const float4*>(boxes);
     int rc = k7_nms_chain(P, 1, 0, w.kept_key, w.kept_box, count, nullptr, keep, st);
     if (rc) return rc;
-    K7_LAUNCH_CHECK();
+    K7_CUDA(cudaGetLastError());
     return K7_OK;
 }
 

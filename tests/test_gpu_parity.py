@@ -1124,3 +1124,62 @@ def test_collate_annotations_fixture_and_random():
             assert np.array_equal(ragged.cpu().numpy(), np.concatenate(rows, axis=0))
     with pytest.raises(RuntimeError):
         b200det.collate_annotations(rows, "cpu")
+
+
+# ---------------------------------------------------------------------------------- boxes: the reference ON CUDA
+# On a GPU box the reference itself runs its box arithmetic on CUDA (architectures/utils.py:26-71 after .cuda(),
+# retinanet.py:297-298).  The same restatement on device="cuda" tensors is therefore the exact target: every ATen
+# kernel rounds once per operation and uses CUDA's expf, as k7_decode does (-fmad=false, explicit __f*_rn) - BIT
+# equality, no tolerance.  The comparison with the torch-CPU fixtures keeps a small absolute slack (host libm expf
+# differs from CUDA's by an ulp and x1 = cx - w/2 cancels); the worst deviation seen is part of the message.
+def _cuda_reference_boxes(anc, reg, yx, H, W):
+    a = anc if anc.dim() == 3 else anc[None]
+    boxes = R.decode_boxes_yx(a, reg) if yx else R.decode_boxes(a, reg)
+    return R.clip_boxes_(boxes.contiguous(), H, W)
+
+
+def _worst(got, want):
+    d = np.abs(got.astype(np.float64) - want.astype(np.float64))
+    rel = d / np.maximum(np.abs(want.astype(np.float64)), 1e-30)
+    return float(d.max()) if d.size else 0.0, float(rel[np.abs(want) > 1.0].max()) if (np.abs(want) > 1.0).any() else 0.0
+
+
+@pytest.mark.parametrize("path", DET, ids=DIDS)
+def test_boxes_bit_equal_to_the_reference_on_cuda(path):
+    g, yx, anc, img = load_det_case(path, True)
+    H, W = int(g["height"]), int(g["width"])
+    reg = torch.from_numpy(g["regressions"]).to(DEV)
+    cls = torch.from_numpy(g["classifications"]).to(DEV)
+    anc_t = torch.from_numpy(g["anchors"]).to(DEV)
+    want = _cuda_reference_boxes(anc_t, reg, yx, H, W)
+    rb = b200det.BBoxTransformYX() if yx else b200det.BBoxTransform()
+    got = b200det.ClipBoxes()(rb(anc, reg), img)
+    assert torch.equal(got, want), "decode+clip differs from the reference's own ops on CUDA: worst abs %g rel %g" % _worst(
+        got.cpu().numpy(), want.cpu().numpy())
+    # the fused tail returns those very boxes for the anchors it keeps
+    det = b200det.detect(cls, reg, anc, (H, W), score_thr=float(g["score_thr"]), iou_thr=float(g["iou_thr"]),
+                         variant=L.DECODE_EFFDET if yx else L.DECODE_RETINA)
+    for b in range(cls.shape[0]):
+        k = int(det.count[b])
+        ids = det.anchor_ids[b, :k].long()
+        assert torch.equal(det.boxes[b, :k], want[b, ids])
+    # against the torch-CPU fixture: the deviation is host expf vs CUDA expf, recorded here
+    worst_abs, worst_rel = _worst(got.cpu().numpy(), g["boxes"])
+    assert worst_abs <= 1.3e-4, f"worst deviation from the CPU fixture: abs {worst_abs:g} px, rel {worst_rel:g}"
+    print(f"[{os.path.basename(path)}] vs torch-CPU fixture: worst abs {worst_abs:.3g} px, worst rel (|x|>1) {worst_rel:.3g}")
+
+
+@pytest.mark.parametrize("name", ["c1_retinanet_r50_512", "c3_ksevendet_thermal_512x640", "c4_effdet_d3_896", "c5_effdet_d7_1536"])
+def test_boxes_bit_equal_on_baseline_shapes(name):
+    """The BASELINE shapes (two images each): decode + clip bit-equal to the reference's ops on CUDA, for the anchors of
+    a recipe and for large deltas (dw, dh up to +-3: widths from 5 % to 20 x the anchor)."""
+    wl = b200det.synth.WORKLOADS[name]
+    B = 2
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    img = torch.empty(B, 3, wl.height, wl.width, device=DEV)
+    anc = b200det.Anchors(**wl.anchor_kwargs())(img)
+    A = anc.shape[1]
+    reg = torch.randn((B, A, 4), generator=gen, device=DEV) * torch.tensor([2.0, 2.0, 1.5, 1.5], device=DEV)
+    want = _cuda_reference_boxes(anc.clone(), reg, False, wl.height, wl.width)
+    got = b200det.ClipBoxes()(b200det.BBoxTransform()(anc, reg), img)
+    assert torch.equal(got, want), "worst abs %g rel %g" % _worst(got.cpu().numpy(), want.cpu().numpy())
