@@ -24,6 +24,7 @@
 #include <mutex>
 
 #include "k7_common.cuh"
+#include "k7_nms_v1.cuh"
 
 // ------------------------------------------------------------------ stand-alone decode / clip
 template <bool FROM_SPEC>
@@ -122,6 +123,8 @@ struct K7DetectWs {
     size_t bytes, zero_bytes;
     int W32;
     int cap, ecap;          // survivors per image the multi-SM NMS path is sized for; edges per image
+    bool use_v1;            // many images: the per-image chain of k7_nms_v1.cu (its areas follow)
+    K7V1Ws v1;
 };
 static int k7_nms_cap(int B, int n_max);
 
@@ -164,6 +167,13 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.pend = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
     w.edges = reinterpret_cast<unsigned int*>(take(sizeof(unsigned int) * (size_t)B * w.ecap));
     w.ginfo = take(320 * (size_t)B);   // sizeof(K7Grid) <= 320
+    static const int v1_min = [] { const char* e = getenv("K7_V1_MIN_IMAGES"); return e ? atoi(e) : K7_V1_MIN_IMAGES; }();
+    w.use_v1 = B >= v1_min;
+    w.v1.bytes = 0;
+    if (w.use_v1) {
+        w.v1 = k7v1::workspace(p ? p + o : nullptr, B, A);
+        o += w.v1.bytes;
+    }
     w.bytes = o;
     return w;
 }
@@ -2389,7 +2399,13 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
     }
 
     // NMS (every kernel decides per image on the device; PDL links: each starts when its predecessor drains)
-    int rc2 = k7_nms_chain(k7_nms_args(w, A, params->iou_thr, params->pre_nms_topk, params->class_aware != 0), B,
+    int rc2;
+    if (w.use_v1)
+        rc2 = k7v1::chain(B, A, params->iou_thr, params->pre_nms_topk, params->max_detections, params->class_aware != 0,
+                          w.surv_count, w.keys0, w.keys1, w.box, w.label, w.nsel, w.kept_key, w.kept_box, w.kept_count, counts,
+                          w.v1, st);
+    else
+        rc2 = k7_nms_chain(k7_nms_args(w, A, params->iou_thr, params->pre_nms_topk, params->class_aware != 0), B,
                            params->max_detections, w.kept_key, w.kept_box, w.kept_count, counts, nullptr, st);
     if (rc2) return rc2;
     K7_CUDA(cudaGetLastError());
