@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--no-configs", action="store_true", help="skip parts.configs (stage times of the other BASELINE configs)")
     ap.add_argument("--no-shard-part", action="store_true", help="skip parts.c5_shard (EfficientDet-D7 batch 64 split over the ranks)")
     ap.add_argument("--serial", action="store_true", help="run both halves of the step on one stream")
+    ap.add_argument("--eager", action="store_true", help="launch the timed steps eagerly instead of replaying the captured graph")
     return ap.parse_args()
 
 
@@ -296,6 +297,15 @@ class HotPath:
         self.train_side()
         cur.wait_stream(self.side)
 
+    def graphed(self, fn=None):
+        """The step captured once in a CUDA graph (b200det.GraphedStep) - None when the capture fails."""
+        try:
+            return self.b200det.GraphedStep(fn or self.step, warmup=3, device=self.dev)
+        except Exception as e:                                   # never let the capture break the line
+            self.graph_error = str(e)[:200]
+            torch.cuda.synchronize()
+            return None
+
     def bytes(self, surv=0):
         wl, B = self.wl, self.B
         A, C, M = wl.anchors, wl.classes, wl.max_gt
@@ -311,6 +321,11 @@ class HotPath:
         ms_fb = timed(self.train_side, k, 3)
         ms_det = timed(self.eval_side, k, 3)
         ms_step = timed(self.step, k, 3)
+        g_step = self.graphed()
+        ms_graph = timed(g_step, k, 3) if g_step is not None else None
+        g_train = self.graphed(self.train_side)
+        ms_graph_fb = timed(g_train, k, 3) if g_train is not None else None
+        del g_step, g_train
         ms_match = timed(lambda: BL.match_scatter(sp, self.ann, A, 0.35, 0.45), k, 3)
         surv = int(self.eval_side(sync=True).survivors.sum())
         bf, bfb, bd = self.bytes(surv)
@@ -319,7 +334,10 @@ class HotPath:
                 "k7_match_ms": ms_match, "match_loss_fwd_ms": ms_fwd, "match_loss_fwd_hbm_frac": g(bf, ms_fwd),
                 "match_loss_fwd_bwd_ms": ms_fb, "match_loss_fwd_bwd_hbm_frac": g(bfb, ms_fb),
                 "decode_nms_ms": ms_det, "decode_nms_hbm_frac": g(bd, ms_det), "survivors_per_image": surv / self.B,
-                "step_ms": ms_step, "images_per_s": self.B / ms_step * 1e3}
+                "step_ms": ms_step, "step_graph_ms": ms_graph,
+                "match_loss_fwd_bwd_graph_ms": ms_graph_fb,
+                "match_loss_fwd_bwd_graph_hbm_frac": g(bfb, ms_graph_fb) if ms_graph_fb else None,
+                "images_per_s": self.B / (ms_graph or ms_step) * 1e3}
 
 
 def run_b200(args, wl):
@@ -351,7 +369,9 @@ def run_b200(args, wl):
     hp = HotPath(wl, B, dev, seed=rank, world=world, peer=peer)
     cls, reg, ann, img, hw = hp.cls, hp.reg, hp.ann, hp.img, hp.hw
     anchors_mod, loss_mod = hp.anchors_mod, hp.loss_mod
-    step = hp.step_serial if args.serial else hp.step
+    step_eager = hp.step_serial if args.serial else hp.step
+    graphed = None if args.eager else hp.graphed(step_eager)
+    step = graphed if graphed is not None else step_eager
 
     def barrier():
         torch.cuda.synchronize()
@@ -392,6 +412,8 @@ def run_b200(args, wl):
     e1.record()
     barrier()
     launches = int(lib.k7_launch_count() - n0)
+    if graphed is not None:
+        launches = graphed.launches * args.steps                # a replay makes no API call: the graph holds them
     ms_total = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
@@ -405,11 +427,16 @@ def run_b200(args, wl):
         "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(wl, B, world),
         "gpu_launches": launches,
-        "gpu_launches_note": "counted by libk7det (k7_launch_count) over the timed region: every kernel of the library; "
-                             "autograd adds a few tiny ATen kernels per step, memsets are not kernels",
+        "gpu_launches_note": "counted by libk7det (k7_launch_count): every kernel of the library launched in the timed region "
+                             "(graph replay: the kernels recorded in the captured step x steps); autograd adds a few tiny "
+                             "ATen kernels per step, memsets are not kernels",
         "step_schedule": "serial (one stream)" if args.serial else
                          "decode/NMS on a second CUDA stream next to FocalLoss fwd+bwd, joined at the end of the step",
+        "step_launch": "CUDA graph replay of the step through the public modules (b200det.GraphedStep); static input tensors, "
+                       "all work redone every replay" if graphed is not None else "eager",
     }
+    if graphed is None and not args.eager:
+        out["graph_error"] = getattr(hp, "graph_error", None)
     if world > 1:
         out["loss_exchange"] = loss_mod.exchange
         out["host_binding"] = binding
@@ -435,6 +462,7 @@ def run_b200(args, wl):
     ms_fb = timed(hp.train_side, k, 3)
     ms_det = timed(hp.eval_side, k, 3)
     ms_serial = timed(hp.step_serial, k, 3)
+    ms_eager = timed(hp.step, k, 3)
     anc = anchors_mod(img)
     sp_ = b200det.spec_of(anc)
     kw = dict(alpha=0.25, beta=1.0 / 9.0, target_div=(0.1, 0.1, 0.2, 0.2), yx_targets=False, mean_divisor=B)
@@ -455,33 +483,22 @@ def run_b200(args, wl):
         "match_loss_fwd_bwd": {"ms": ms_fb, "images_per_s": B / ms_fb * 1e3, "hbm_frac": gbs(bytes_fb, ms_fb) / peak},
         "decode_nms": {"ms": ms_det, "images_per_s": B / ms_det * 1e3, "hbm_frac": gbs(bytes_det, ms_det) / peak,
                        "survivors_per_image": surv / B},
+        "step_eager": {"ms": ms_eager, "images_per_s": B / ms_eager * 1e3,
+                       "note": "the two-stream step launched eagerly from Python (the host sets the pace at small batches)"},
         "step_one_stream": {"ms": ms_serial, "images_per_s": B / ms_serial * 1e3,
-                            "note": "the same step with both halves on one stream (what the previous round reported)"},
+                            "note": "the same step, eager, with both halves on one stream (what the previous round reported)"},
         "k7_match_ms": ms_match, "k7_loss_fwd_ms": ms_k_f, "k7_loss_fwd_bwd_ms": ms_k_fb,
         "k7_loss_fwd_hbm_frac": gbs(bytes_fwd, ms_k_f) / peak,
     }
     del dreg0, arr_, best_
-    # the same step captured once in a CUDA graph and replayed: what is left when the launch gaps between the
-    # kernels (and autograd's small ones) are gone.  Single GPU only: the fused peer exchange numbers its calls.
     if world == 1:
-        try:
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(side):
-                for _ in range(3):
-                    hp.step_serial()
-            torch.cuda.current_stream().wait_stream(side)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                hp.step_serial()
-            ms_graph = timed(graph.replay, k, 3)
-            out["parts"]["cuda_graph_step"] = {"ms": ms_graph, "images_per_s": B / ms_graph * 1e3,
-                                               "note": "torch.cuda.CUDAGraph capture of the one-stream step (FocalLoss fwd+bwd + "
-                                                       "detect), replayed; the headline value is the eager step"}
-            del graph
-        except Exception as e:                                   # never let the extra measurement break the line
-            out["parts"]["cuda_graph_step"] = {"error": str(e)[:200]}
-            torch.cuda.synchronize()
+        g1 = hp.graphed(hp.step_serial)
+        if g1 is not None:
+            ms_graph = timed(g1, k, 3)
+            out["parts"]["cuda_graph_step_one_stream"] = {"ms": ms_graph, "images_per_s": B / ms_graph * 1e3,
+                                                         "note": "graph replay of the ONE-stream step: what the second stream buys is "
+                                                                 "the difference to the headline"}
+        del g1
     # the same stages fed with the head's pre-sigmoid logits (sigmoid fused), next to the
     # stock elementwise sigmoid pass (and its autograd backward) that they make unnecessary
     z = torch.logit(cls)
@@ -612,6 +629,7 @@ def run_b200(args, wl):
         del h_cls, h_reg, h_ann, d_cls, d_reg, d_ann
 
     # ---- the other BASELINE configurations on one GPU, at their BASELINE batch (stage times, not bench lines)
+    del graphed, step, step_eager
     del hp, cls, reg, ann, img, anchors_mod, loss_mod, loss_lg, reg_g
     torch.cuda.empty_cache()
     if world == 1 and not args.no_configs and not args.batch and not args.shard:
@@ -636,9 +654,17 @@ def run_b200(args, wl):
             if w5.batch % world == 0:
                 Bs = w5.batch // world
                 h5 = HotPath(w5, Bs, dev, seed=rank, world=world, peer=peer)
-                ms_n = timed_ranks(h5.step, 10, 3)
+                g5 = None if args.eager else h5.graphed()
+                ok5 = torch.tensor([1 if (g5 is not None or args.eager) else 0], device=dev)
+                if world > 1:
+                    dist.all_reduce(ok5, op=dist.ReduceOp.MIN)   # every rank replays, or none does
+                if not int(ok5.item()):
+                    g5 = None
+                ms_n = timed_ranks(g5 if g5 is not None else h5.step, 10, 3)
+                del g5
                 rec = {"workload": w5.name, "global_batch": w5.batch, "images_per_gpu": Bs, "n_gpus": world,
-                       "ms_per_step": ms_n, "images_per_s": w5.batch / ms_n * 1e3, "scaling": "strong"}
+                       "ms_per_step": ms_n, "images_per_s": w5.batch / ms_n * 1e3, "scaling": "strong",
+                       "step_launch": "eager" if (args.eager or not int(ok5.item())) else "CUDA graph replay"}
                 if world > 1:
                     rec["loss_exchange"] = h5.loss_mod.exchange
                 del h5
@@ -653,7 +679,9 @@ def run_b200(args, wl):
                     dist.barrier()
                     if rank == 0:                                   # the whole batch on ONE GPU, same run, same code
                         h1 = HotPath(w5, w5.batch, dev, seed=0)
-                        ms_1 = timed(h1.step, 5, 2)
+                        g1 = None if args.eager else h1.graphed()
+                        ms_1 = timed(g1 if g1 is not None else h1.step, 5, 2)
+                        del g1
                         del h1
                         torch.cuda.empty_cache()
                     dist.barrier()

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 11
+#define K7_ABI_VERSION 12
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -169,7 +169,8 @@ K7_API int k7_match_scatter(const K7AnchorSpec* spec, const float* annotations, 
  * the local one): 2 * world slots of 8 floats, zero-initialised before the first call.  The last
  * block of the row kernel posts this rank's sums into every mailbox and adds the world posts it
  * receives in rank order, so `sums` holds the GLOBAL sums, bit-identical on every rank, with no
- * separate all-reduce launch.  seq counts the calls (1, 2, ...) and must be the same on every rank.
+ * separate all-reduce launch.  seq counts the calls (1, 2, ...) and must be the same on every rank (or give
+ * seq_counter and let the kernel count).
  * A peer that does not post within timeout_ms (default 10 000) gives NaN sums, never a hang. */
 #define K7_MAX_PEERS 16
 typedef struct K7PeerReduce {
@@ -177,6 +178,9 @@ typedef struct K7PeerReduce {
     uint32_t seq;
     int32_t timeout_ms;
     float* mailbox[K7_MAX_PEERS];
+    uint32_t* seq_counter; /* optional device word (4-byte aligned, zero before the first call): when given, the call
+                            * number is taken from it and advanced by the kernel, `seq` is ignored - a CUDA graph that
+                            * captured the call can then be replayed (a kernel argument would be frozen into the graph) */
 } K7PeerReduce;
 #define K7_PEER_MAILBOX_FLOATS(world) (2 * (world) * 8)
 #define K7_IPC_HANDLE_BYTES 64

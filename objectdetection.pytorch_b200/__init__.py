@@ -13,5 +13,6 @@ from .utils import (BBoxTransform, BBoxTransformYX, ClipBoxes, BatchDetections, 
                     postprocess, eval_tail, patch_model, strip_head_sigmoid)
 from .evaltail import (PackedDetections, eval_pack, coco_results, csv_all_detections,  # noqa: F401
                        collate_annotations)
+from .graphs import GraphedStep                              # noqa: F401
 from . import synth                                          # noqa: F401
 from . import distributed                                    # noqa: F401

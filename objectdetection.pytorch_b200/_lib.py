@@ -54,6 +54,7 @@ class K7PeerReduce(C.Structure):
         ("seq", C.c_uint32),
         ("timeout_ms", C.c_int32),
         ("mailbox", C.c_void_p * K7_MAX_PEERS),
+        ("seq_counter", C.c_void_p),
     ]
 
 
@@ -113,7 +114,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 11                     # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 12                     # K7_ABI_VERSION of include/k7det.h
 
 
 BEST_GEN_MAX = 65535                 # K7_BEST_GEN_MAX

@@ -81,6 +81,7 @@ struct K7AssignSrc {
 struct K7PeerDev {
     int world, rank;
     unsigned int seq;                  // call counter (>= 1), the same on every rank
+    unsigned int* seq_counter;         // device word holding the number of calls so far, or NULL (then `seq` is used)
     unsigned long long timeout_ns;
     float* mailbox[K7_MAX_PEERS];      // mailbox[p]: rank p's 2 * world slots of 8 floats {v0..v3, seq, -, -, -}
 };
@@ -1019,18 +1020,23 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
     // p's post in its own mailbox.  Two slot sets alternate by call parity: a rank can only be one
     // call ahead of a peer (it needs the peer's post to finish a call), so a slot is never overwritten
     // before it was read.  Every rank adds the W posts in rank order: identical bits everywhere.
+    // The call number: a kernel argument, or - so that a captured CUDA graph can be replayed - a device counter
+    // this block advances (every rank makes the same calls, so the counters agree).
+    __shared__ unsigned int s_seq;
+    if (threadIdx.x == 0) s_seq = PR.seq_counter ? atomicAdd(PR.seq_counter, 1u) + 1u : PR.seq;
     __syncthreads();
+    const unsigned int seq = s_seq;
     const int W = PR.world;
     if ((int)threadIdx.x < W) {
         const int p = threadIdx.x;
-        const unsigned par = PR.seq & 1u;
+        const unsigned par = seq & 1u;
         float* dst = PR.mailbox[p] + (size_t)(par * W + PR.rank) * 8;
         const float4 mine = s_mine;
         asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(mine.x), "f"(mine.y), "f"(mine.z),
                      "f"(mine.w)
                      : "memory");
         __threadfence_system();
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst + 4), "r"(PR.seq) : "memory");
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst + 4), "r"(seq) : "memory");
         const float* src = PR.mailbox[PR.rank] + (size_t)(par * W + p) * 8;
         unsigned long long t0, t1;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -1038,7 +1044,7 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
         bool ok = false;
         for (;;) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(src + 4) : "memory");
-            if (got == PR.seq) {
+            if (got == seq) {
                 ok = true;
                 break;
             }
@@ -1454,11 +1460,12 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     PR.world = 1;
     if (params->peer_reduce && params->peer_reduce->world > 1) {
         const K7PeerReduce* q = params->peer_reduce;
-        K7_REQUIRE(q->world <= K7_MAX_PEERS && q->rank >= 0 && q->rank < q->world && q->seq >= 1u,
+        K7_REQUIRE(q->world <= K7_MAX_PEERS && q->rank >= 0 && q->rank < q->world && (q->seq >= 1u || q->seq_counter),
                    "k7_loss: bad peer_reduce (world=%d rank=%d seq=%u)", q->world, q->rank, q->seq);
         PR.world = q->world;
         PR.rank = q->rank;
         PR.seq = q->seq;
+        PR.seq_counter = q->seq_counter;
         PR.timeout_ns = (unsigned long long)(q->timeout_ms > 0 ? q->timeout_ms : 10000) * 1000000ull;
         for (int i = 0; i < q->world; ++i) {
             K7_REQUIRE(q->mailbox[i] && (reinterpret_cast<uintptr_t>(q->mailbox[i]) & 31) == 0,

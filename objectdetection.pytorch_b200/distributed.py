@@ -134,11 +134,16 @@ class PeerMailbox:
             raise RuntimeError("peer mailboxes unavailable: " + bad)
         self._struct = L.K7PeerReduce()
         self._struct.world, self._struct.rank, self._struct.timeout_ms = self.world, self.rank, self.timeout_ms
+        # the call counter lives on the device and is advanced by the kernel: a captured CUDA graph can be replayed
+        self._calls = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._struct.seq_counter = self._calls.data_ptr()
         for r in range(self.world):
             self._struct.mailbox[r] = self._ptrs[r]
 
     def next(self):
-        """The K7PeerReduce of the next k7_loss call (the call counter advances on every rank alike)."""
+        """The K7PeerReduce of the next k7_loss call.  The call number is counted on the device
+        (K7PeerReduce.seq_counter: every rank makes the same calls), so nothing per-call is frozen into a
+        captured CUDA graph; `seq` mirrors the number of calls ENQUEUED from this object."""
         self.seq += 1
         self._struct.seq = self.seq
         return self._struct
