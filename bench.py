@@ -256,14 +256,17 @@ def bind_to_gpu_numa(local, local_world):
 class HotPath:
     """One workload on one GPU: inputs, modules and the step of the bench."""
 
-    def __init__(self, wl, B, dev, seed, world=1, peer="auto"):
+    def __init__(self, wl, B, dev, seed, world=1, peer="auto", spare_sms=None):
         import b200det
         self.b200det, self.wl, self.B, self.dev = b200det, wl, B, dev
         self.hw = (wl.height, wl.width)
         self.cls, self.reg, self.ann = b200det.synth.make_inputs(wl, seed=seed, device=dev, batch=B)
         self.img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
         self.anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
-        self.loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer)
+        # few images per GPU: the NMS kernels (multi-SM chain, 1024-thread CTAs) cannot share an SM with the loss stage's
+        # streaming CTAs, so the stream leaves them 24 SMs (it stays HBM-bound) and both run side by side in step()
+        self.spare_sms = (24 if B < 12 else 0) if spare_sms is None else spare_sms
+        self.loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer, spare_sms=self.spare_sms)
         self.cls_g = self.cls.detach().requires_grad_(True)
         self.reg_g = self.reg.detach().requires_grad_(True)
         self.side = torch.cuda.Stream(device=dev)
@@ -371,7 +374,6 @@ def run_b200(args, wl):
     anchors_mod, loss_mod = hp.anchors_mod, hp.loss_mod
     step_eager = hp.step_serial if args.serial else hp.step
     graphed = None if args.eager else hp.graphed(step_eager)
-    step = graphed if graphed is not None else step_eager
 
     def barrier():
         torch.cuda.synchronize()
@@ -394,6 +396,22 @@ def run_b200(args, wl):
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()) / steps
+
+    def pick(g, eager):
+        """Graph replay or eager launches, whichever is faster for this step on these ranks (max over ranks): replay
+        removes the host from the loop, but the graph executor interleaves the two branches of a two-stream step in
+        its own order, which at few images per GPU can be the worse one."""
+        ok = torch.tensor([1 if g is not None else 0], device=dev)
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if not int(ok.item()):
+            return eager, False
+        tg, te = timed_ranks(g, 5, 3), timed_ranks(eager, 5, 3)
+        return (g, True) if tg <= te else (eager, False)
+
+    step, use_graph = pick(graphed, step_eager)
+    if not use_graph:
+        graphed = None
 
     sampler = ClockSampler(local)
     if rank == 0:
@@ -655,16 +673,13 @@ def run_b200(args, wl):
                 Bs = w5.batch // world
                 h5 = HotPath(w5, Bs, dev, seed=rank, world=world, peer=peer)
                 g5 = None if args.eager else h5.graphed()
-                ok5 = torch.tensor([1 if (g5 is not None or args.eager) else 0], device=dev)
-                if world > 1:
-                    dist.all_reduce(ok5, op=dist.ReduceOp.MIN)   # every rank replays, or none does
-                if not int(ok5.item()):
-                    g5 = None
-                ms_n = timed_ranks(g5 if g5 is not None else h5.step, 10, 3)
-                del g5
+                step5, graph5 = pick(g5, h5.step)
+                ms_n = timed_ranks(step5, 10, 3)
+                del g5, step5
                 rec = {"workload": w5.name, "global_batch": w5.batch, "images_per_gpu": Bs, "n_gpus": world,
                        "ms_per_step": ms_n, "images_per_s": w5.batch / ms_n * 1e3, "scaling": "strong",
-                       "step_launch": "eager" if (args.eager or not int(ok5.item())) else "CUDA graph replay"}
+                       "step_launch": "CUDA graph replay" if graph5 else "eager",
+                       "spare_sms": h5.spare_sms}
                 if world > 1:
                     rec["loss_exchange"] = h5.loss_mod.exchange
                 del h5
@@ -680,7 +695,9 @@ def run_b200(args, wl):
                     if rank == 0:                                   # the whole batch on ONE GPU, same run, same code
                         h1 = HotPath(w5, w5.batch, dev, seed=0)
                         g1 = None if args.eager else h1.graphed()
-                        ms_1 = timed(g1 if g1 is not None else h1.step, 5, 2)
+                        ms_1 = timed(h1.step, 5, 2)
+                        if g1 is not None:
+                            ms_1 = min(ms_1, timed(g1, 5, 2))      # the better of the two, as for the sharded step
                         del g1
                         del h1
                         torch.cuda.empty_cache()

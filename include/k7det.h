@@ -209,6 +209,10 @@ typedef struct K7LossParams {
     uint32_t match_generation; /* `best` given: the generation of the k7_match_scatter call that filled it */
     float neg_thr, pos_thr;    /* `best` given: the thresholds of that call (the states are decided from the IoU bits) */
     int32_t* assign_out;       /* optional [B,A] int32: the packed state / row words of k7_match, written on the way */
+    int32_t spare_sms;         /* the stream kernel (one persistent CTA per SM) leaves this many SMs unused: a caller that
+                                * overlaps the call with SM-bound work of another stream (the NMS kernels of a k7_detect
+                                * on few images: their 1024-thread CTAs cannot share an SM with a stream CTA) gives them
+                                * room at no cost - up to ~16 of 148 SMs the stream stays HBM-bound.  0: all SMs. */
     int32_t consume_best;      /* 1: entries of this generation are zeroed as they are read, so the SAME generation can be
                                 * used again by the next k7_match_scatter on this array (a captured CUDA graph replays
                                 * one generation); `best` is then written by k7_loss */

@@ -72,6 +72,7 @@ class K7LossParams(C.Structure):
         ("neg_thr", C.c_float),
         ("pos_thr", C.c_float),
         ("assign_out", C.c_void_p),
+        ("spare_sms", C.c_int32),
         ("consume_best", C.c_int32),
     ]
 

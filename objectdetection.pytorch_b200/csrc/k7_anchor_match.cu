@@ -679,9 +679,9 @@ struct K7ScatterLevel {   // per pyramid level, in shared memory
 // anchor shape p = level * K + k and works out the rectangle of cells whose anchors of that shape can reach
 // neg_thr; a warp scan turns the rectangle sizes into offsets, and then ALL candidate cells of ALL shapes
 // are one flat range that the 32 lanes walk together (a box has ~50-150 candidates on 2-3 levels: two to
-// five trips instead of one trip per shape with most lanes idle).  Warps without a work item - and every warp
-// once its items are done - zero the d(reg) buffer of the loss stage (16 B per anchor: the kernel is latency
-// bound, the stores are free here).
+// five trips instead of one trip per shape with most lanes idle).  Every warp - also those without a work item -
+// first - zero the d(reg) buffer of the loss stage (16 B per anchor: the kernel is latency bound, the stores
+// drain while the work items run).
 __global__ void __launch_bounds__(K7_SCATTER_THREADS)
 k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7ScatterAux X,
                         const float* __restrict__ annotations, int B, int A, int M, float neg_thr,
@@ -720,6 +720,13 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
     const bool xy = spec.box_order == K7_BOX_XYXY;
     int* pref = s_pref[wib];
     uint2* rect = s_rect[wib];
+    // the zero fill first: the stores drain while the (latency-bound) work items below run
+    if (zero_fill4) {
+        const size_t n = (size_t)B * (size_t)A;
+        const size_t step = (size_t)gridDim.x * K7_SCATTER_THREADS;
+        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (size_t i = (size_t)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x; i < n; i += step) __stcs(zero_fill4 + i, z);
+    }
     for (long long t = gwarp; t < tasks; t += nwarps) {
         const int m = (int)(t % M), b = (int)(t / M);
         const float* row = annotations + (size_t)t * 5;
@@ -820,12 +827,6 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
                 if (first) touched[(size_t)b * A + base + (unsigned int)__popc(fm & ((1u << lane) - 1u))] = (unsigned int)a;
             }
         }
-    }
-    if (zero_fill4) {
-        const size_t n = (size_t)B * (size_t)A;
-        const size_t step = (size_t)gridDim.x * K7_SCATTER_THREADS;
-        const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        for (size_t i = (size_t)blockIdx.x * K7_SCATTER_THREADS + threadIdx.x; i < n; i += step) __stcs(zero_fill4 + i, z);
     }
 }
 

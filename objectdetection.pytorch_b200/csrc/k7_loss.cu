@@ -594,10 +594,12 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
     // ---- fold the CTA's (image, warp) slots into the image's fixed-point accumulator (2^-32 units, integer
     // atomics: exact, whatever the order in which CTAs finish - nobody has to sum 148 partials per image later)
     asm volatile("bar.sync 1, %0;" ::"r"(CW * 32) : "memory");
-    for (int b = warp; b < P.B; b += CW) {
-        float v = (lane < CW) ? __ldcg(partials + (size_t)b * pstride + (size_t)blockIdx.x * CW + lane) : 0.0f;
-        v = k7_warp_sum(v);
-        if (lane == 0 && v != 0.0f)
+    // a lane per image (the CW slots of an image are contiguous): one trip for up to CW * 32 images
+    for (int b = warp * 32 + lane; b < P.B; b += CW * 32) {
+        const float* sl = partials + (size_t)b * pstride + (size_t)blockIdx.x * CW;
+        float v = 0.0f;
+        for (int w = 0; w < CW; ++w) v += __ldcg(sl + w);   // fixed order
+        if (v != 0.0f)
             atomicAdd(reinterpret_cast<unsigned long long*>(img_acc + 2 * b), (unsigned long long)__double2ll_rn((double)v * K7_FIX_ONE));
     }
 }
@@ -1162,10 +1164,11 @@ struct K7LossPlan {
 };
 
 static int k7_pipe_geometry(bool grad, int B, int C, K7PipeGeom* g);
+static int k7_env_int(const char* name, int dflt);
 
 // levels == false: shape (B, A, C).  levels == true: one stream per non-empty level of `spec`.
 static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int C, bool grad, bool exact_grid,
-                        K7LossPlan* p) {
+                        K7LossPlan* p, int spare_sms = 0) {
     p->nseg = 0;
     size_t o = 0;
     p->off_counter = o;   // [0] the serve kernel's block counter, [4], [5] the lengths of the two row queues
@@ -1201,6 +1204,10 @@ static int k7_loss_plan(const K7AnchorSpec* spec, bool levels, int B, int A, int
     }
     p->G.num_tiles = (uint32_t)tiles;
     int grid = exact_grid ? k7_sm_count() : K7_LOSS_MAX_GRID;   // the workspace query has no device: assume the largest grid
+    if (exact_grid) {   // K7LossParams.spare_sms: leave some SMs to kernels of other streams
+        const int spare = k7_env_int("K7_PIPE_SPARE_SMS", spare_sms);
+        if (spare > 0 && grid - spare >= 16) grid -= spare;
+    }
     if (grid > K7_LOSS_MAX_GRID) grid = K7_LOSS_MAX_GRID;
     if (exact_grid && tiles < (unsigned long long)grid) grid = (int)tiles;
     p->G.grid = grid < 1 ? 1 : grid;
@@ -1304,7 +1311,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     cudaStream_t st = static_cast<cudaStream_t>(stream);
 
     K7LossPlan L;
-    int rc = k7_loss_plan(spec, lv, B, A, C, grad, true, &L);
+    int rc = k7_loss_plan(spec, lv, B, A, C, grad, true, &L, params->spare_sms);
     if (rc) return rc;
     if (workspace_bytes < L.total) {
         k7_set_error("k7_loss: workspace %zu < %zu bytes", workspace_bytes, L.total);

@@ -142,8 +142,9 @@ def match(anchors, annotations: torch.Tensor, A: int, neg_thr: float, pos_thr: f
 
 
 def _loss_params(*, alpha, beta, target_div, yx_targets, mean_divisor, want_grad, dreg_zeroed, from_logits, peer_reduce,
-                 best, assign_out):
+                 best, assign_out, spare_sms=0):
     p = L.K7LossParams()
+    p.spare_sms = int(spare_sms)
     p.dreg_prezeroed = int(want_grad and dreg_zeroed is not None)
     p.alpha, p.beta = alpha, beta
     for i in range(4):
@@ -163,7 +164,7 @@ def _loss_params(*, alpha, beta, target_div, yx_targets, mean_divisor, want_grad
 def loss_stage(anchors, cls, reg, ann, assign, num_pos=None, *, alpha, beta, target_div, yx_targets,
                mean_divisor, want_grad, box_order=L.BOX_XYXY, dreg_zeroed: Optional[torch.Tensor] = None,
                ignore_bits: Optional[torch.Tensor] = None, from_logits: bool = False, peer_reduce=None,
-               best=None, assign_out: Optional[torch.Tensor] = None):
+               best=None, assign_out: Optional[torch.Tensor] = None, spare_sms: int = 0):
     """Streaming loss stage.  Returns (per_image[B,2], sums[4], dcls|None, dreg|None).
     `num_pos` [B] int32 is an OUTPUT (the positives are counted while the assignment is walked); pass a
     tensor to receive it.  The assignment comes as match()'s `assign` words or as match_scatter()'s array:
@@ -194,7 +195,7 @@ def loss_stage(anchors, cls, reg, ann, assign, num_pos=None, *, alpha, beta, tar
         dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
     p = _loss_params(alpha=alpha, beta=beta, target_div=target_div, yx_targets=yx_targets, mean_divisor=mean_divisor,
                      want_grad=want_grad, dreg_zeroed=dreg_zeroed, from_logits=from_logits, peer_reduce=peer_reduce,
-                     best=best, assign_out=assign_out)
+                     best=best, assign_out=assign_out, spare_sms=spare_sms)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss(C.byref(spec) if spec is not None else None, L.ptr(anc_t), box_order,
                             L.ptr(cls), L.ptr(reg), L.ptr(ann), L.ptr(assign), L.ptr(best[0]) if best is not None else None,
@@ -254,7 +255,8 @@ class _FocalLossFn(torch.autograd.Function):
             anchors, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=cfg["divisor"](B, world),
             want_grad=want_grad, box_order=cfg["box_order"], dreg_zeroed=dreg_zeroed, best=best,
-            from_logits=cfg.get("from_logits", False), peer_reduce=peer.next() if peer is not None else None)
+            from_logits=cfg.get("from_logits", False), peer_reduce=peer.next() if peer is not None else None,
+            spare_sms=cfg.get("spare_sms", 0))
         if want_grad and dreg_zeroed is None:
             dreg0 = None                         # loss_stage allocated d(reg) itself
         if world > 1 and peer is None:
@@ -300,7 +302,7 @@ def _once(ctx):
 
 def loss_stage_levels(spec, levels, reg, ann, assign, num_pos=None, *, alpha, beta, target_div, yx_targets, mean_divisor,
                       want_grad, dreg_zeroed: Optional[torch.Tensor] = None, ignore_bits: Optional[torch.Tensor] = None,
-                      from_logits: bool = False, peer_reduce=None, best=None):
+                      from_logits: bool = False, peer_reduce=None, best=None, spare_sms: int = 0):
     """loss_stage on the head's raw per-level NCHW outputs (k7_loss_levels).  Returns
     (per_image[B,2], sums[4], dlevels|None (list, same layouts as `levels`), dreg|None)."""
     B, Cn = L.check_levels(levels, spec)
@@ -318,7 +320,7 @@ def loss_stage_levels(spec, levels, reg, ann, assign, num_pos=None, *, alpha, be
         dreg = dreg_zeroed if dreg_zeroed is not None else torch.empty_like(reg)
     p = _loss_params(alpha=alpha, beta=beta, target_div=target_div, yx_targets=yx_targets, mean_divisor=mean_divisor,
                      want_grad=want_grad, dreg_zeroed=dreg_zeroed, from_logits=from_logits, peer_reduce=peer_reduce,
-                     best=best, assign_out=None)
+                     best=best, assign_out=None, spare_sms=spare_sms)
     lv, dlv = L.ptr_array(levels), L.ptr_array(dlevels)
     with torch.cuda.device(dev):
         L.check(lib.k7_loss_levels(C.byref(spec), lv, L.ptr(reg), L.ptr(ann), L.ptr(assign),
@@ -343,7 +345,7 @@ class _FocalLossLevelsFn(torch.autograd.Function):
             spec, list(levels), reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"],
             target_div=cfg["target_div"], yx_targets=cfg["yx_targets"], mean_divisor=cfg["divisor"](B, world),
             want_grad=want_grad, dreg_zeroed=dreg_zeroed, best=best, from_logits=cfg.get("from_logits", False),
-            peer_reduce=peer.next() if peer is not None else None)
+            peer_reduce=peer.next() if peer is not None else None, spare_sms=cfg.get("spare_sms", 0))
         if world > 1 and peer is None:
             import torch.distributed as dist
             dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
@@ -396,6 +398,8 @@ class FocalLoss(nn.Module):
     gives architectures/loss_efficientdet.py's (0.4/0.5, yx anchors, unscaled (dy,dx,dh,dw)).
     ``sharded=True`` / ``process_group=``: one process per GPU, dim 0 is this rank's shard; the four batch
     sums are exchanged inside k7_loss over NVLink peer memory (``peer_reduce``), gradients need no collective.
+    ``spare_sms=n``: the streaming kernel leaves n SMs free (K7LossParams.spare_sms) for SM-bound work the caller
+    overlaps on another stream - the NMS kernels of a ``detect`` on few images; up to ~16 cost nothing.
     ``from_logits=True``: `classifications` are the head's PRE-sigmoid logits (drop
     ``output_act`` of retinanet.py:140 / ``header_act`` of simple_head.py:310, see
     ``b200det.strip_head_sigmoid``); the sigmoid is fused into the streaming kernel and the gradient
@@ -404,7 +408,8 @@ class FocalLoss(nn.Module):
     def __init__(self, neg_thr: float = 0.35, pos_thr: float = 0.45, alpha: float = 0.25,
                  gamma: float = 2.0, beta: float = 1.0 / 9.0, target_std=(0.1, 0.1, 0.2, 0.2),
                  box_order: str = "xyxy", yx_targets: bool = False, process_group=None,
-                 sharded: bool = False, from_logits: bool = False, peer_reduce="auto", ddp_average: bool = False):
+                 sharded: bool = False, from_logits: bool = False, peer_reduce="auto", ddp_average: bool = False,
+                 spare_sms: int = 0):
         super().__init__()
         if gamma != 2.0:
             raise ValueError("only gamma == 2 (the reference's constant, losses.py:32) is implemented")
@@ -414,7 +419,7 @@ class FocalLoss(nn.Module):
                         target_div=tuple(float(x) for x in (target_std if target_std is not None else (1, 1, 1, 1))),
                         box_order=L.BOX_XYXY if box_order == "xyxy" else L.BOX_YXYX,
                         yx_targets=bool(yx_targets), process_group=process_group, sharded=bool(sharded),
-                        from_logits=bool(from_logits))
+                        from_logits=bool(from_logits), spare_sms=int(spare_sms))
         # What the gradients are divided by.  The reference's nn.DataParallel takes the mean of the GLOBAL
         # batch (train_ksevendet.py:358-361), so a rank's gradient is d(global mean)/d(its shard) =
         # .../(B_local * world) and the ranks' parameter gradients must be SUMMED.  ddp_average=True is for

@@ -1183,3 +1183,90 @@ def test_boxes_bit_equal_on_baseline_shapes(name):
     want = _cuda_reference_boxes(anc.clone(), reg, False, wl.height, wl.width)
     got = b200det.ClipBoxes()(b200det.BBoxTransform()(anc, reg), img)
     assert torch.equal(got, want), "worst abs %g rel %g" % _worst(got.cpu().numpy(), want.cpu().numpy())
+
+
+# ---------------------------------------------------------------------------------- streams and graphs
+def _small_case(seed, B=6, C=7, H=192, W=256, M=9):
+    gen = torch.Generator().manual_seed(seed)
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    A = anc.shape[1]
+    ann = b200det.synth.make_annotations(B, M, C, H, W, gen, gt_min=8.0, gt_max=90.0).to(DEV)
+    cls, reg = b200det.synth.make_head_outputs(B, A, C, gen, logit_mean=-3.5, logit_std=1.5)
+    return img, anc, ann, cls.to(DEV), reg.to(DEV), (H, W)
+
+
+def test_two_streams_do_not_share_workspaces():
+    """Two callers overlapped on two streams of one device (decode/NMS of two batches; a FocalLoss next to a detect):
+    workspaces are per (device, stream), so the results are those of the calls run one after the other."""
+    img, anc, ann, cls1, reg1, hw = _small_case(1)
+    _, _, _, cls2, reg2, _ = _small_case(2)
+    want1 = b200det.detect(cls1, reg1, anc, hw)
+    want2 = b200det.detect(cls2, reg2, anc, hw)
+    loss = b200det.FocalLoss()
+    with torch.no_grad():
+        lw = [t.clone() for t in loss(cls1, reg1, anc, ann)]
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(20):                                  # many rounds: any sharing would show as a flipped keep
+        with torch.cuda.stream(s1):
+            got1 = b200det.detect(cls1, reg1, anc, hw, sync=False, want_rank=True)
+            with torch.no_grad():
+                lg = loss(cls1, reg1, anc, ann)
+        with torch.cuda.stream(s2):
+            got2 = b200det.detect(cls2, reg2, anc, hw, sync=False, want_rank=True)
+        torch.cuda.synchronize()
+        for got, want in ((got1, want1), (got2, want2)):
+            assert got.count.cpu().tolist() == want.count.tolist()
+            for b in range(cls1.shape[0]):
+                k = int(want.count[b])
+                assert torch.equal(got.anchor_ids[b, :k], want.anchor_ids[b, :k])
+                assert torch.equal(got.boxes[b, :k], want.boxes[b, :k])
+        assert torch.equal(lg[0], lw[0]) and torch.equal(lg[1], lw[1])
+
+
+def test_graphed_step_replays_with_new_inputs():
+    """b200det.GraphedStep: FocalLoss forward+backward and detect (on a second stream) captured once, replayed on
+    inputs copied into the static tensors; losses, gradients and detections equal the eager calls bit for bit."""
+    img, anc, ann, cls, reg, hw = _small_case(3)
+    _, _, ann2, cls2, reg2, _ = _small_case(4)
+    loss = b200det.FocalLoss()
+    c = cls.clone().requires_grad_(True)
+    r = reg.clone().requires_grad_(True)
+    a = ann.clone()
+    side = torch.cuda.Stream()
+    out = {}
+
+    def step():
+        cur = torch.cuda.current_stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            out["det"] = b200det.detect(c.detach(), r.detach(), anc, hw, sync=False, want_rank=True)
+        c.grad = None
+        r.grad = None
+        lc, lr = loss(c, r, anc, a)
+        (lc + lr).sum().backward()
+        out["loss"] = (lc.detach(), lr.detach())
+        cur.wait_stream(side)
+
+    g = b200det.GraphedStep(step)
+    assert g.launches >= 6
+    for cc, rr, aa in ((cls, reg, ann), (cls2, reg2, ann2), (cls, reg, ann)):
+        with torch.no_grad():
+            c.copy_(cc)
+            r.copy_(rr)
+            a.copy_(aa)
+        g()
+        torch.cuda.synchronize()
+        got_det, got_loss, got_gc, got_gr = out["det"], out["loss"], c.grad.clone(), r.grad.clone()
+        c0, r0 = cc.clone().requires_grad_(True), rr.clone().requires_grad_(True)
+        lc, lr = b200det.FocalLoss()(c0, r0, anc, aa)
+        (lc + lr).sum().backward()
+        want = b200det.detect(cc, rr, anc, hw)
+        assert torch.equal(got_loss[0], lc.detach()) and torch.equal(got_loss[1], lr.detach())
+        assert torch.equal(got_gc, c0.grad) and torch.equal(got_gr, r0.grad)
+        assert got_det.count.cpu().tolist() == want.count.tolist()
+        for b in range(cc.shape[0]):
+            k = int(want.count[b])
+            assert torch.equal(got_det.anchor_ids[b, :k], want.anchor_ids[b, :k])
+            assert torch.equal(got_det.scores[b, :k], want.scores[b, :k])
