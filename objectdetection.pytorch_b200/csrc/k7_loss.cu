@@ -310,6 +310,8 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
         k7_fence_mbar_init();
         k7_fence_proxy_async();
     }
+    k7_pdl_trigger();   // programmatic dependent launch (no-ops in a plain launch): the serve kernel's CTAs may take
+    k7_pdl_wait();      // their places; the list kernel's outputs (num_pos, img_valid, the bitmap) are complete
     // The gradient scale of every image, (1-alpha) / (max(num_pos,1) * mean_divisor) - 0 for an image
     // without ground truth, which the reference skips (losses.py:52-60) -, tabulated once: a warp that
     // enters a new image must not wait for global memory (all 16 warps of a CTA change image at about
@@ -932,6 +934,8 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float oma = P.one_m_alpha;
     const int img = blockIdx.y;   // grid (blocks per image, B)
+    k7_pdl_trigger();
+    k7_pdl_wait();      // the stream kernel's gradients and partial sums are complete
     const unsigned int npos = __ldcg(Q.count + (size_t)img * K7_BEST_CNT_STRIDE);
 
     // ---- positive rows of image `img`: a thread each (whole warps stay in the loop: the fold below is warp-wide)
@@ -1389,6 +1393,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         K7_LAUNCH_CHECK();
     }
 
+    static const bool loss_pdl = [] { const char* e = getenv("K7_LOSS_PDL"); return e ? atoi(e) != 0 : true; }();
     K7LevelTable LT;
     memset(&LT, 0, sizeof(LT));
     K7PipeSegs SG;
@@ -1447,7 +1452,9 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         }
         auto launch = [&](auto kern) -> int {
             K7_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G.smem_bytes));
-            kern<<<G.grid, (G.cw + 1) * 32, G.smem_bytes, st>>>(SG, num_pos, RQ.img_valid, Ps, G, pipe_partials, acc);
+            k7_pdl_site() = loss_pdl ? 1 : 0;   // site 0: plain launch
+            K7_CUDA(k7_launch_pdl(kern, dim3(G.grid), dim3((G.cw + 1) * 32), G.smem_bytes, st, SG, (const int32_t*)num_pos,
+                                  (const unsigned char*)RQ.img_valid, Ps, G, pipe_partials, acc));
             return K7_OK;
         };
         const bool lg = P.from_logits != 0;
@@ -1459,7 +1466,7 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
             else    rc = grad ? launch(k7_loss_pipe_kernel<true, 512, false>) : launch(k7_loss_pipe_kernel<false, 512, false>);
         }
         if (rc) return rc;
-        K7_LAUNCH_CHECK();
+        K7_CUDA(cudaGetLastError());
     }
 
     K7PeerDev PR;
@@ -1483,15 +1490,16 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
     static const K7AnchorSpec kEmpty = {};
     const K7AnchorSpec& sp = spec ? *spec : kEmpty;
     const dim3 rgrid(k7_rows_gx(B, 4), B);   // the queue lengths are only known on the device: grid-stride loops per image
-#define K7_SERVE_LAUNCH(GR, SP, LV)                                                                                      \
-    k7_loss_serve_kernel<GR, SP, LV><<<rgrid, K7_ROWS_THREADS, 0, st>>>(sp, LT, anchors, box_order, cls, reg, annotations, \
-                                                                        RQ, num_pos, P, PR, cta_partials, L.cta_stride,   \
-                                                                        acc, counter, per_image, sums, dcls, dreg4)
+    k7_pdl_site() = loss_pdl ? 2 : 0;
+#define K7_SERVE_LAUNCH(GR, SP, LV)                                                                                          \
+    K7_CUDA(k7_launch_pdl(k7_loss_serve_kernel<GR, SP, LV>, rgrid, dim3(K7_ROWS_THREADS), 0, st, sp, LT, anchors, box_order, \
+                          cls, reg, annotations, RQ, (const int32_t*)num_pos, P, PR, (const float*)cta_partials,              \
+                          L.cta_stride, acc, counter, per_image, sums, dcls, dreg4))
     if (lv) { if (grad) K7_SERVE_LAUNCH(true, true, true); else K7_SERVE_LAUNCH(false, true, true); }
     else if (grad) { if (spec) K7_SERVE_LAUNCH(true, true, false); else K7_SERVE_LAUNCH(true, false, false); }
     else           { if (spec) K7_SERVE_LAUNCH(false, true, false); else K7_SERVE_LAUNCH(false, false, false); }
 #undef K7_SERVE_LAUNCH
-    K7_LAUNCH_CHECK();
+    K7_CUDA(cudaGetLastError());
     return K7_OK;
 }
 

@@ -1270,3 +1270,20 @@ def test_graphed_step_replays_with_new_inputs():
             k = int(want.count[b])
             assert torch.equal(got_det.anchor_ids[b, :k], want.anchor_ids[b, :k])
             assert torch.equal(got_det.scores[b, :k], want.scores[b, :k])
+
+
+def test_spare_sms_changes_no_result():
+    """FocalLoss(spare_sms=n): the streaming kernel runs on fewer SMs (room for another stream's NMS kernels);
+    gradients stay bit-identical, the losses equal to the last bit or two (the stream's partial sums are grouped
+    by CTA before they enter the integer accumulators)."""
+    img, anc, ann, cls, reg, hw = _small_case(5, B=5, C=11)
+    outs = []
+    for spare in (0, 24, 100):
+        c, r = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+        lc, lr = b200det.FocalLoss(spare_sms=spare)(c, r, anc, ann)
+        (lc + lr).sum().backward()
+        outs.append((lc.detach(), lr.detach(), c.grad, r.grad))
+    for o in outs[1:]:
+        assert torch.equal(o[2], outs[0][2]) and torch.equal(o[3], outs[0][3])
+        np.testing.assert_allclose(o[0].item(), outs[0][0].item(), rtol=1e-6)
+        np.testing.assert_allclose(o[1].item(), outs[0][1].item(), rtol=1e-6)

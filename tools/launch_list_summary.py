@@ -25,11 +25,14 @@ def main():
     hdr = rows[0]
     ik, iv, ig = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size")
     seq = [(short(r[ik]), float(r[iv]) / 1e3, r[ig]) for r in rows[1:]]
-    starts = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_match_")]
-    ends = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_gather_kernel")]
-    print(f"{len(seq)} launches captured; k7_match launches: {len(starts)}")
+    starts = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_score_pipe")]
+    ends = [i for i, (k, _, _) in enumerate(seq) if k.startswith("k7_scale_multi")]
+    print(f"{len(seq)} launches captured; score-kernel launches: {len(starts)}")
     if len(starts) >= 5 and len(ends) >= 5:
-        s, e = starts[4], ends[4]
+        # one step of the main loop as the profiler serialises it: from a score kernel (the step's first launch, on the
+        # second stream) to the backward's scale kernel (its last)
+        s = starts[4]
+        e = next(i for i in ends if i > s)
         step = seq[s:e + 1]
         tot = sum(t for _, t, _ in step)
         print(f"\none step of the main loop (launches {s}..{e}): {len(step)} launches, {tot:.1f} us serialised")
