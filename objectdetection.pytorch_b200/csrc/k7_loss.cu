@@ -1393,7 +1393,10 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         K7_LAUNCH_CHECK();
     }
 
-    static const bool loss_pdl = [] { const char* e = getenv("K7_LOSS_PDL"); return e ? atoi(e) != 0 : true; }();
+    // programmatic dependent launch of the stream and serve kernels: measured (K7_LOSS_PDL=1) -1..-4 us on the k7_loss
+    // call alone, +15..25 us on the eager FocalLoss forward+backward (the extended launch costs the host more than
+    // the GPU gains) - off by default
+    static const bool loss_pdl = [] { const char* e = getenv("K7_LOSS_PDL"); return e ? atoi(e) != 0 : false; }();
     K7LevelTable LT;
     memset(&LT, 0, sizeof(LT));
     K7PipeSegs SG;
