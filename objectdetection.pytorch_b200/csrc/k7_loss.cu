@@ -185,6 +185,28 @@ __device__ __forceinline__ float2 k7_neg_pair(const float2 xin, const float2 sco
     return g;
 }
 
+// One element as the flat pass sees it: the clamped probability p (for logits: through the same approximate sigmoid)
+// and the polynomial loss term p^2 * (pp * S(pp)).  Used to take a CONFIDENT element (p > K7_POLY_MAX, outside the
+// polynomial's range) out of the flat pass's sum again before it is added exactly.
+template <bool GRAD, bool LOGITS>
+__device__ __forceinline__ float k7_flat_term(const float xin, float& p_out) {
+    float x = xin;
+    if (LOGITS) {
+        if (GRAD) {
+            const float t = fminf(xin * 1.4426950408889634f, 126.0f);
+            const float ez = k7_ex2_approx(t);
+            x = ez * k7_rcp_approx(ez + 1.0f);
+        } else {
+            const float e = k7_ex2_approx(xin * -1.4426950408889634f);
+            x = k7_rcp_approx(e + 1.0f);
+        }
+    }
+    const float p = fminf(fmaxf(x, K7_P_LO), K7_P_HI);
+    p_out = p;
+    const float q = 1.0f - p, pp = 1.0f - q;
+    return (p * p) * k7_neg_log1m_poly(pp);
+}
+
 template <bool GRAD, bool LOGITS>
 __device__ __forceinline__ void k7_flat4(float4* __restrict__ p4, const float2 sco, float2& acc, float& pmax) {
     const float4 x = *p4;
@@ -525,24 +547,40 @@ k7_loss_pipe_kernel(const __grid_constant__ K7PipeSegs SG, const int32_t* __rest
                     }
                 }
                 if (masked) __syncwarp();
-                const float2 acc0 = acc;
                 float pmax = 0.0f;
                 k7_flat_pass<SL, GRAD, LOGITS>(slice, n4, lane, sco, acc, pmax);
                 if (__any_sync(0xffffffffu, pmax > K7_POLY_MAX)) {
-                    // a confident prediction: outside the polynomial's range.  Redo the slice exactly
-                    // (with gradients the tile already holds them: the inputs come from global memory again).
+                    // Confident predictions (p > 0.25: outside the polynomial's range) in this slice.  Only THOSE elements
+                    // are redone: their polynomial term leaves the sum again and the exact one (logf) enters, their
+                    // gradient is overwritten.  With gradients the tile already holds gradients, so the inputs come from
+                    // global memory again (L2: the tile was loaded a moment ago).  (Redoing the whole slice exactly, as
+                    // before, cost 7 x the flat pass per slice: at C3 - one slice in five - it was half of the kernel.)
                     __syncwarp();
-                    acc = acc0;
                     const uint4 d1 = *(reinterpret_cast<const uint4*>(desc + s) + 1);   // off_lo, off_hi, seg
                     const float* src = SG.s[d1.z].cls + ((((unsigned long long)d1.y) << 32) | d1.x) + i_lo;
-                    for (int i = lane; i < len; i += 32) {
-                        bool ign = false;
-                        if (GRAD && masked) {   // without gradients the tile still holds SENT for those elements
-                            const int p = bitbase + (int)k7_div((uint32_t)(rem + i_lo + i), G.div_c);
-                            ign = (side[p >> 5] >> (p & 31)) & 1u;
+                    float fix = 0.0f;
+                    for (int i0 = lane; i0 < len; i0 += 128) {
+                        float xv[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int i = i0 + 32 * u;
+                            xv[u] = i < len ? (GRAD ? __ldg(src + i) : slice[i]) : 0.0f;   // (0: never confident)
                         }
-                        exact(GRAD ? __ldg(src + i) : slice[i], ign, slice + i);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int i = i0 + 32 * u;
+                            float pf;
+                            const float term = k7_flat_term<GRAD, LOGITS>(xv[u], pf);
+                            if (!(pf > K7_POLY_MAX) || i >= len) continue;
+                            if (GRAD && masked) {   // an ignored row: the tile holds its zero gradient, its term was ~0
+                                const int p = bitbase + (int)k7_div((uint32_t)(rem + i_lo + i), G.div_c);
+                                if ((side[p >> 5] >> (p & 31)) & 1u) continue;
+                            }
+                            fix -= term;
+                            exact(xv[u], false, slice + i);
+                        }
                     }
+                    acc.x += fix;
                 }
             } else {
                 // ---- generic path: the slice straddles an image boundary (or the tile spans > 2 images)
