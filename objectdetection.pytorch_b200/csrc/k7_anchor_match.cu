@@ -667,10 +667,12 @@ struct K7ScatterAux {
 };
 
 #define K7_SCATTER_THREADS 128
+#define K7_SCATTER_U 1             // candidates per lane and trip (4 measured: no faster - the kernel is not bound by the atomics round trips)
 #define K7_SCATTER_PAIRS (K7_MAX_LEVELS * K7_MAX_CELL_ANCHORS)
 
 struct K7ScatterLevel {   // per pyramid level, in shared memory
     double stride;
+    float stride_f;
     float inv_stride, lvl_lo, lvl_hi;
     int fw, fh, offset;
 };
@@ -702,6 +704,7 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
             const int l = threadIdx.x;
             K7ScatterLevel v;
             v.stride = spec.stride[l];
+            v.stride_f = (float)spec.stride[l];
             v.inv_stride = X.inv_stride[l];
             v.lvl_lo = X.lvl_lo[l];
             v.lvl_hi = X.lvl_hi[l];
@@ -738,6 +741,8 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
         const float gw = K7_FSUB(g2, g0), gh = K7_FSUB(g3, g1);
         if (!(gw > 0.0f && gh > 0.0f)) continue;          // empty box: IoU is 0 with every anchor
         const float area_g = k7_area(g0, g1, g2, g3);
+        const bool fast_gt = gw >= 8.0f && gh >= 8.0f;
+        const float thr_lo = neg_thr - 1e-3f;
         int total = 0;
         __syncwarp();                                     // the previous item's tables are no longer read
         for (int p0 = 0; p0 < LK; p0 += 32) {             // warp-uniform
@@ -780,11 +785,20 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
             total += __shfl_sync(0xffffffffu, inc, 31);
         }
         __syncwarp();
-        for (int i0 = 0; i0 < total; i0 += 32) {          // warp-uniform
-            const int i = i0 + lane;
-            bool first = false;
-            int a = 0;
-            if (i < total) {
+        // K7_SCATTER_U candidates per lane and trip: their atomics are issued back to back and answered together, and
+        // the list takes ONE reservation per trip.
+        constexpr int U = K7_SCATTER_U;
+        for (int i0 = 0; i0 < total; i0 += 32 * U) {      // warp-uniform
+            int an[U];
+            unsigned long long val[U];
+            bool hit[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + 32 * u + lane;
+                hit[u] = false;
+                an[u] = 0;
+                val[u] = 0ull;
+                if (i >= total) continue;
                 int lo = 0, hi = LK - 1;                  // the first shape whose inclusive prefix exceeds i
                 while (lo < hi) {
                     const int mid = (lo + hi) >> 1;
@@ -796,6 +810,18 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
                 const int yy = j / nx, x = (int)(rc.x & 0xffffu) + (j - yy * nx), y = (int)(rc.x >> 16) + yy;
                 const K7ScatterLevel& V = lv[l];
                 const K7ScatterShape& S = sh[p];
+                // A cheap float32 look first (most candidates of the superset fail): the anchor from float32 parts is
+                // within 1e-4 px of the reference's, so for extents >= 8 px its IoU is within 1e-4 of the exact one;
+                // pairs below neg_thr - 1e-3 leave here, division-free.  The exact float64 / reference-order path
+                // below decides everything that stays.
+                if (fast_gt && S.wa >= 8.0f && S.ha >= 8.0f) {
+                    const float cxf = ((float)x + 0.5f) * V.stride_f, cyf = ((float)y + 0.5f) * V.stride_f;
+                    const float fw_ = fminf(cxf + S.bx2, g2) - fmaxf(cxf + S.bx1, g0);
+                    const float fh_ = fminf(cyf + S.by2, g3) - fmaxf(cyf + S.by1, g1);
+                    const float fi = fw_ * fh_;
+                    const float fu = (S.bx2 - S.bx1) * (S.by2 - S.by1) + area_g - fi;
+                    if (!(fw_ > 0.0f && fh_ > 0.0f) || fi < thr_lo * fu) continue;
+                }
                 const double sx = __dmul_rn(__dadd_rn((double)x, 0.5), V.stride);
                 const double sy = __dmul_rn(__dadd_rn((double)y, 0.5), V.stride);
                 float ax1, ay1, ax2, ay2;                 // k7_anchor_from_spec: float64 add, one rounding
@@ -812,19 +838,30 @@ k7_match_scatter_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_
                 }
                 const float iou = k7_pair_iou(ax1, ay1, ax2, ay2, k7_area(ax1, ay1, ax2, ay2), g0, g1, g2, g3, area_g);
                 if (iou >= neg_thr) {
-                    a = V.offset + (y * V.fw + x) * K + k;
-                    const unsigned long long v = tag | ((unsigned long long)__float_as_uint(iou) << 16) |
-                                                 (unsigned long long)(0xFFFF - m);
-                    const unsigned long long old = atomicMax(best + (size_t)b * A + a, v);
-                    first = K7_BEST_GEN(old) != gen;      // nobody wrote this entry in this generation before
+                    hit[u] = true;
+                    an[u] = V.offset + (y * V.fw + x) * K + k;
+                    val[u] = tag | ((unsigned long long)__float_as_uint(iou) << 16) | (unsigned long long)(0xFFFF - m);
                 }
             }
-            const unsigned int fm = __ballot_sync(0xffffffffu, first);
-            if (fm) {
-                unsigned int base = 0u;
-                if (lane == 0) base = atomicAdd(touched_count + (size_t)b * K7_BEST_CNT_STRIDE, (unsigned int)__popc(fm));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (first) touched[(size_t)b * A + base + (unsigned int)__popc(fm & ((1u << lane) - 1u))] = (unsigned int)a;
+            unsigned long long old[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) old[u] = hit[u] ? atomicMax(best + (size_t)b * A + an[u], val[u]) : ~0ull;
+            unsigned int fm[U];
+            int nfirst = 0;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                // nobody wrote this entry in this generation before (a lane that did not hit reads ~0: never first)
+                fm[u] = __ballot_sync(0xffffffffu, hit[u] && K7_BEST_GEN(old[u]) != gen);
+                nfirst += __popc(fm[u]);
+            }
+            if (nfirst == 0) continue;                    // warp-uniform
+            unsigned int base = 0u;
+            if (lane == 0) base = atomicAdd(touched_count + (size_t)b * K7_BEST_CNT_STRIDE, (unsigned int)nfirst);
+            base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if ((fm[u] >> lane) & 1u) touched[(size_t)b * A + base + (unsigned int)__popc(fm[u] & ((1u << lane) - 1u))] = (unsigned int)an[u];
+                base += (unsigned int)__popc(fm[u]);
             }
         }
     }
