@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 12
+#define K7_ABI_VERSION 13
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -178,9 +178,17 @@ typedef struct K7PeerReduce {
     uint32_t seq;
     int32_t timeout_ms;
     float* mailbox[K7_MAX_PEERS];
-    uint32_t* seq_counter; /* optional device word (4-byte aligned, zero before the first call): when given, the call
-                            * number is taken from it and advanced by the kernel, `seq` is ignored - a CUDA graph that
-                            * captured the call can then be replayed (a kernel argument would be frozen into the graph) */
+    uint32_t* seq_counter; /* optional: TWO device words (4-byte aligned, zero before the first call) - calls posted, calls
+                            * collected.  When given, the call number is taken from them and advanced by the kernels,
+                            * `seq` is ignored - a CUDA graph that captured the call can then be replayed (a kernel
+                            * argument would be frozen into the graph) */
+    int32_t post_only;     /* 1: k7_loss only POSTS this rank's sums into the mailboxes and writes its OWN sums to `sums`;
+                            * nothing in the call waits for a peer.  The global sums are fetched later, off the critical
+                            * path, with k7_peer_collect (the gradients never need them: they are pre-scaled with the
+                            * statically known global batch).  Needs seq_counter; the word behind it (seq_counter[1])
+                            * counts the collects.  Order: collect k must be enqueued before k7_loss call k+1 on streams
+                            * that order them (two slot sets alternate: a rank must not post call k+2 before it has
+                            * collected call k+1). */
 } K7PeerReduce;
 #define K7_PEER_MAILBOX_FLOATS(world) (2 * (world) * 8)
 #define K7_IPC_HANDLE_BYTES 64
@@ -193,6 +201,11 @@ K7_API int k7_peer_mailbox_create(int world, float** mailbox, unsigned char* han
 K7_API int k7_peer_mailbox_open(const unsigned char* handle, float** mailbox);
 K7_API int k7_peer_mailbox_close(float* mailbox);
 K7_API int k7_peer_mailbox_destroy(float* mailbox);
+/* The second half of a post_only exchange: one small kernel (W threads) that waits - on `stream`, which may be any
+ * stream - until every rank's post of the next uncollected call has arrived in this rank's mailbox and writes the
+ * four GLOBAL sums, added in rank order (the same bits on every rank), to sums[4].  NaN after timeout_ms.
+ * Replaces the gather + .mean() of nn.DataParallel (train_ksevendet.py:358-361) like K7PeerReduce itself. */
+K7_API int k7_peer_collect(const K7PeerReduce* reduce, float* sums, void* stream);
 
 typedef struct K7LossParams {
     float alpha;            /* 0.25 (losses.py:31) ; gamma is fixed at 2 (losses.py:32, pow == x*x) */

@@ -55,6 +55,7 @@ class K7PeerReduce(C.Structure):
         ("timeout_ms", C.c_int32),
         ("mailbox", C.c_void_p * K7_MAX_PEERS),
         ("seq_counter", C.c_void_p),
+        ("post_only", C.c_int32),
     ]
 
 
@@ -115,7 +116,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 12                     # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 13                     # K7_ABI_VERSION of include/k7det.h
 
 
 BEST_GEN_MAX = 65535                 # K7_BEST_GEN_MAX
@@ -138,6 +139,7 @@ SYMBOLS = {
     "k7_match_scatter_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "k7_match_scatter": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, C.c_int, C.c_int, C.POINTER(K7MatchParams),
                                    _P, C.c_uint32, _P, _P]),
+    "k7_peer_collect": (C.c_int, [C.POINTER(K7PeerReduce), _P, _P]),
     "k7_loss_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "k7_loss": (C.c_int, [C.POINTER(K7AnchorSpec), _P, C.c_int, _P, _P, _P, _P, _P, _P,
                           C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(K7LossParams),

@@ -82,6 +82,7 @@ struct K7PeerDev {
     int world, rank;
     unsigned int seq;                  // call counter (>= 1), the same on every rank
     unsigned int* seq_counter;         // device word holding the number of calls so far, or NULL (then `seq` is used)
+    int post_only;                     // post and return: the collection is k7_peer_collect's
     unsigned long long timeout_ns;
     float* mailbox[K7_MAX_PEERS];      // mailbox[p]: rank p's 2 * world slots of 8 floats {v0..v3, seq, -, -, -}
 };
@@ -954,6 +955,58 @@ __device__ __forceinline__ void k7_acc_add(long long* __restrict__ acc, int b, i
     }
 }
 
+// ---- the exchange over peer memory.  Thread p posts this rank's sums into rank p's mailbox (16-byte store, system
+// fence, then the sequence word with release semantics); a wait polls the own mailbox for rank p's post of the same
+// call.  Two slot sets alternate by call parity: a rank can only be one call ahead of a peer (it needs the peer's
+// post to finish - or, post_only, to collect - a call), so a slot is never overwritten before it was read.  Every
+// rank adds the W posts in rank order: identical bits everywhere.
+__device__ __forceinline__ void k7_peer_post(const K7PeerDev& PR, unsigned int seq, int p, const float4 mine) {
+    const int W = PR.world;
+    float* dst = PR.mailbox[p] + (size_t)((seq & 1u) * W + PR.rank) * 8;
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(mine.x), "f"(mine.y), "f"(mine.z),
+                 "f"(mine.w)
+                 : "memory");
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst + 4), "r"(seq) : "memory");
+}
+__device__ __forceinline__ float4 k7_peer_wait(const K7PeerDev& PR, unsigned int seq, int p) {
+    const float* src = PR.mailbox[PR.rank] + (size_t)((seq & 1u) * PR.world + p) * 8;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned int got = 0u;
+    bool ok = false;
+    for (;;) {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(src + 4) : "memory");
+        if (got == seq) {
+            ok = true;
+            break;
+        }
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > PR.timeout_ns) break;   // a missing peer must not hang the GPU: NaN sums instead
+        __nanosleep(64);
+    }
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(src)
+                 : "memory");
+    const float nanv = __int_as_float(0x7fc00000);
+    return ok ? v : make_float4(nanv, nanv, nanv, nanv);
+}
+__device__ __forceinline__ void k7_peer_sum(const float4* got, int W, float* __restrict__ sums) {
+    float4 a = got[0];
+    for (int p = 1; p < W; ++p) {
+        a.x += got[p].x;
+        a.y += got[p].y;
+        a.z += got[p].z;
+        a.w += got[p].w;
+    }
+    sums[0] = a.x;
+    sums[1] = a.y;
+    sums[2] = a.z;
+    sums[3] = a.w;
+}
+
 template <bool GRAD, bool FROM_SPEC, bool LEVELS>
 __global__ void __launch_bounds__(K7_ROWS_THREADS)
 k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_constant__ K7LevelTable LT,
@@ -1071,53 +1124,33 @@ k7_loss_serve_kernel(const __grid_constant__ K7AnchorSpec spec, const __grid_con
     __syncthreads();
     const unsigned int seq = s_seq;
     const int W = PR.world;
-    if ((int)threadIdx.x < W) {
-        const int p = threadIdx.x;
-        const unsigned par = seq & 1u;
-        float* dst = PR.mailbox[p] + (size_t)(par * W + PR.rank) * 8;
-        const float4 mine = s_mine;
-        asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(mine.x), "f"(mine.y), "f"(mine.z),
-                     "f"(mine.w)
-                     : "memory");
-        __threadfence_system();
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst + 4), "r"(seq) : "memory");
-        const float* src = PR.mailbox[PR.rank] + (size_t)(par * W + p) * 8;
-        unsigned long long t0, t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        unsigned int got = 0u;
-        bool ok = false;
-        for (;;) {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(src + 4) : "memory");
-            if (got == seq) {
-                ok = true;
-                break;
-            }
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > PR.timeout_ns) break;   // a missing peer must not hang the GPU: NaN sums instead
-            __nanosleep(64);
+    if ((int)threadIdx.x < W) k7_peer_post(PR, seq, threadIdx.x, s_mine);
+    if (PR.post_only) {   // nobody waits here: the rank's own sums for now, the global ones through k7_peer_collect
+        if (threadIdx.x == 0) {
+            sums[0] = s_mine.x;
+            sums[1] = s_mine.y;
+            sums[2] = s_mine.z;
+            sums[3] = s_mine.w;
         }
-        float4 v;
-        asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                     : "l"(src)
-                     : "memory");
-        const float nanv = __int_as_float(0x7fc00000);
-        s_got[p] = ok ? v : make_float4(nanv, nanv, nanv, nanv);
+        return;
     }
+    if (threadIdx.x == 0 && PR.seq_counter) atomicAdd(PR.seq_counter + 1, 1u);   // this call collects itself
+    if ((int)threadIdx.x < W) s_got[threadIdx.x] = k7_peer_wait(PR, seq, threadIdx.x);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        float4 a = s_got[0];
-        for (int p = 1; p < W; ++p) {
-            a.x += s_got[p].x;
-            a.y += s_got[p].y;
-            a.z += s_got[p].z;
-            a.w += s_got[p].w;
-        }
-        sums[0] = a.x;
-        sums[1] = a.y;
-        sums[2] = a.z;
-        sums[3] = a.w;
-    }
+    if (threadIdx.x == 0) k7_peer_sum(s_got, W, sums);
+}
+
+// The second half of a post_only exchange (k7_peer_collect): W threads wait for the W posts of the next
+// uncollected call, thread 0 adds them in rank order.
+__global__ void k7_peer_collect_kernel(const __grid_constant__ K7PeerDev PR, float* __restrict__ sums) {
+    __shared__ float4 s_got[K7_MAX_PEERS];
+    __shared__ unsigned int s_seq;
+    if (threadIdx.x == 0) s_seq = atomicAdd(PR.seq_counter + 1, 1u) + 1u;
+    __syncthreads();
+    const int W = PR.world;
+    if ((int)threadIdx.x < W) s_got[threadIdx.x] = k7_peer_wait(PR, s_seq, threadIdx.x);
+    __syncthreads();
+    if (threadIdx.x == 0) k7_peer_sum(s_got, W, sums);
 }
 
 __global__ void k7_scale_kernel(float* __restrict__ g, size_t n, const float* __restrict__ scale) {
@@ -1521,6 +1554,9 @@ static int k7_loss_run(const K7AnchorSpec* spec, const float* anchors, int box_o
         PR.rank = q->rank;
         PR.seq = q->seq;
         PR.seq_counter = q->seq_counter;
+        PR.post_only = q->post_only ? 1 : 0;
+        K7_REQUIRE(!PR.post_only || (q->seq_counter && (reinterpret_cast<uintptr_t>(q->seq_counter) & 3) == 0),
+                   "k7_loss: peer_reduce.post_only needs seq_counter (two device words: calls, collects)");
         PR.timeout_ns = (unsigned long long)(q->timeout_ms > 0 ? q->timeout_ms : 10000) * 1000000ull;
         for (int i = 0; i < q->world; ++i) {
             K7_REQUIRE(q->mailbox[i] && (reinterpret_cast<uintptr_t>(q->mailbox[i]) & 31) == 0,
@@ -1577,4 +1613,24 @@ extern "C" int k7_loss_levels(const K7AnchorSpec* spec, const float* const* leve
     return k7_loss_run(spec, nullptr, spec->box_order, nullptr, levels, reg, annotations, assign, best, num_pos, B,
                        spec->total, C, M, params, per_image, sums, nullptr, dlevels, dreg, workspace, workspace_bytes,
                        stream);
+}
+
+extern "C" int k7_peer_collect(const K7PeerReduce* q, float* sums, void* stream) {
+    K7_REQUIRE(q && sums, "k7_peer_collect: null argument");
+    K7_REQUIRE(q->world >= 1 && q->world <= K7_MAX_PEERS && q->rank >= 0 && q->rank < q->world && q->seq_counter,
+               "k7_peer_collect: bad peer_reduce (world=%d rank=%d) or no seq_counter", q->world, q->rank);
+    K7PeerDev PR;
+    memset(&PR, 0, sizeof(PR));
+    PR.world = q->world;
+    PR.rank = q->rank;
+    PR.seq_counter = q->seq_counter;
+    PR.timeout_ns = (unsigned long long)(q->timeout_ms > 0 ? q->timeout_ms : 10000) * 1000000ull;
+    for (int i = 0; i < q->world; ++i) {
+        K7_REQUIRE(q->mailbox[i] && (reinterpret_cast<uintptr_t>(q->mailbox[i]) & 31) == 0,
+                   "k7_peer_collect: mailbox %d is null or not 32-byte aligned", i);
+        PR.mailbox[i] = q->mailbox[i];
+    }
+    k7_peer_collect_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(PR, sums);
+    K7_LAUNCH_CHECK();
+    return K7_OK;
 }

@@ -135,8 +135,10 @@ class PeerMailbox:
         self._struct = L.K7PeerReduce()
         self._struct.world, self._struct.rank, self._struct.timeout_ms = self.world, self.rank, self.timeout_ms
         # the call counter lives on the device and is advanced by the kernel: a captured CUDA graph can be replayed
-        self._calls = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._calls = torch.zeros(2, dtype=torch.int32, device=self.device)      # [calls posted, calls collected]
         self._struct.seq_counter = self._calls.data_ptr()
+        self.collect_stream = torch.cuda.Stream(device=self.device)               # where deferred collections wait
+        self.last_collect = None                                                   # (event, captured?) of the last deferred collection
         for r in range(self.world):
             self._struct.mailbox[r] = self._ptrs[r]
 
@@ -147,6 +149,34 @@ class PeerMailbox:
         self.seq += 1
         self._struct.seq = self.seq
         return self._struct
+
+    def post_only(self):
+        """The K7PeerReduce of a k7_loss call that only POSTS (FocalLoss.start): a copy of the struct with
+        post_only set."""
+        import ctypes as C
+        from . import _lib as L
+        st = L.K7PeerReduce()
+        C.memmove(C.byref(st), C.byref(self.next()), C.sizeof(L.K7PeerReduce))
+        st.post_only = 1
+        return st
+
+    def collect(self, after: "torch.cuda.Event") -> "torch.Tensor":
+        """Enqueue k7_peer_collect on the collection stream, behind `after` (recorded behind the posting k7_loss):
+        returns the [4] tensor the global sums will be in; self.last_collect is recorded behind it."""
+        from . import _lib as L
+        import ctypes as C
+        with torch.cuda.stream(self.collect_stream):
+            self.collect_stream.wait_event(after)
+            sums = torch.empty(4, dtype=torch.float32, device=self.device)
+            with torch.cuda.device(self.device):
+                L.check(self._lib.k7_peer_collect(C.byref(self._struct), L.ptr(sums), L.stream_ptr(self.device)),
+                        "k7_peer_collect")
+            ev = torch.cuda.Event()
+            ev.record(self.collect_stream)
+        # (event, recorded under stream capture?): an event of the capture must not be waited for outside it and
+        # vice versa; replays are ordered by their launches and join their collection before they end
+        self.last_collect = (ev, bool(torch.cuda.is_current_stream_capturing()))
+        return sums
 
     def close(self):
         """Unmap and free now (idempotent; also runs when the object is garbage collected)."""

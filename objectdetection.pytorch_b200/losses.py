@@ -380,6 +380,44 @@ class _FocalLossLevelsFn(torch.autograd.Function):
         return (dreg, None, None, None, *dlevels)
 
 
+class PendingLoss:
+    """What FocalLoss.start() returns: the loss stage has run (gradients are ready, this rank's sums are posted to the
+    peers); the GLOBAL sums are being collected on another stream.
+
+      backward(scale=1.0)   feed d(loss)/d(classifications|regressions) to autograd (those inputs that require grad)
+      losses()              (classification_loss[1], regression_loss[1]) of the global batch: makes the CURRENT stream
+                            wait for the collection - call it where the value is needed (logging, the end of the step)"""
+
+    def __init__(self, inputs, grads, sums, event, B_global_fn, module):
+        self._inputs, self._grads, self._sums, self._event, self._module = inputs, grads, sums, event, module
+        self.num_positives = module.last_num_positives
+        self.per_image = module.last_per_image
+
+    def backward(self, scale: float = 1.0):
+        ts, gs = [], []
+        grads, self._grads = self._grads, (None, None)
+        for t, g in zip(self._inputs, grads):
+            if t is None or g is None or not t.requires_grad:
+                continue
+            if scale != 1.0:
+                g = g * scale
+            if t.is_leaf and t.grad is None and g.shape == t.shape:
+                t.grad = g                     # a leaf: the buffer itself (autograd would copy it: 8 C bytes per anchor)
+            else:
+                ts.append(t)
+                gs.append(g)
+        if ts:
+            torch.autograd.backward(ts, gs)
+
+    def losses(self):
+        if self._event is not None:
+            torch.cuda.current_stream(self._sums.device).wait_event(self._event)
+            self._event = None
+        m = self._sums[:2] / self._sums[3]
+        self._module.last_sums = self._sums
+        return m[0:1], m[1:2]
+
+
 HeadOutputs = namedtuple("HeadOutputs", "classification regression anchors")
 _CAPTURE = threading.local()      # ids of the FocalLoss modules in capture mode, per thread (see FocalLoss.capture_head)
 
@@ -484,6 +522,53 @@ class FocalLoss(nn.Module):
     @classmethod
     def efficientdet(cls, **kw):
         return cls(neg_thr=0.4, pos_thr=0.5, target_std=None, box_order="yxyx", yx_targets=True, **kw)
+
+    def start(self, classifications, regressions, anchors, annotations) -> PendingLoss:
+        """Two-phase form of forward() for sharded training (one process per GPU): the loss stage runs and posts this
+        rank's four sums to the peers, but NOTHING on the calling stream waits for a peer - the gradients do not need
+        the global sums (they are pre-scaled with the statically known global batch, losses.py:168), only the two
+        reported scalars do, and those are collected on another stream (K7PeerReduce.post_only + k7_peer_collect).
+        Returns a PendingLoss: ``.backward()`` now, ``.losses()`` where the values are wanted.  The next start() waits
+        for this call's collection (the mailboxes hold two calls).  Single GPU / no peer mailboxes: same interface,
+        nothing deferred.  Flat [B,A,C] classifications only."""
+        if isinstance(classifications, (list, tuple)):
+            raise ValueError("FocalLoss.start: per-level inputs are not supported, use forward()")
+        L.require_cuda(classifications, regressions, annotations)
+        cls_in, reg_in = classifications, regressions
+        cls = L.as_f32_contig(classifications.detach())
+        reg = L.as_f32_contig(regressions.detach())
+        ann = L.as_f32_contig(annotations)
+        B, A = cls.shape[0], cls.shape[1]
+        sp = spec_of(anchors)
+        anchor_src = sp if sp is not None else anchors
+        cfg = self.cfg
+        want_grad = cls_in.requires_grad or reg_in.requires_grad
+        dreg0 = torch.empty_like(reg) if want_grad else None
+        assign, best, num_pos, dreg_zeroed = _assignment(anchor_src, ann, A, cfg, dreg0)
+        world, peer, group = _exchange(cfg)
+        dev = cls.device
+        cur = torch.cuda.current_stream(dev)
+        pr = None
+        if peer is not None:
+            if peer.last_collect is not None and peer.last_collect[1] == bool(torch.cuda.is_current_stream_capturing()):
+                cur.wait_event(peer.last_collect[0])       # two slot sets: collect k before post k+2
+            pr = peer.post_only()
+        per_image, sums, dcls, dreg = loss_stage(
+            anchor_src, cls, reg, ann, assign, num_pos, alpha=cfg["alpha"], beta=cfg["beta"], target_div=cfg["target_div"],
+            yx_targets=cfg["yx_targets"], mean_divisor=cfg["divisor"](B, world), want_grad=want_grad,
+            box_order=cfg["box_order"], dreg_zeroed=dreg_zeroed, best=best, from_logits=cfg.get("from_logits", False),
+            peer_reduce=pr, spare_sms=cfg.get("spare_sms", 0))
+        event = None
+        if peer is not None:
+            posted = torch.cuda.Event()
+            posted.record(cur)
+            sums = peer.collect(posted)
+            event = peer.last_collect[0]
+        elif world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+        self._remember(num_pos, per_image, sums, B)
+        return PendingLoss((cls_in, reg_in), (dcls, dreg), sums, event, None, self)
 
     def forward(self, classifications, regressions, anchors, annotations=None, **kwargs):
         if id(self) in _capturing():

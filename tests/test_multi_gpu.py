@@ -59,6 +59,26 @@ def _worker(rank, world, port, out_dir):
             np.testing.assert_allclose(lr.item(), lrf.item(), rtol=2e-6)
             np.testing.assert_allclose(c.grad.cpu().numpy(), cf.grad[lo:hi].cpu().numpy(), rtol=1e-6, atol=1e-12)
     assert fused.exchange == "p2p-fused" and nccl.exchange == "nccl-allreduce"
+    # the two-phase form (post now, collect on another stream), mixed with ordinary calls on the same mailboxes
+    for step in range(6):
+        scale = 1.0 + 0.125 * step
+        c = (cls[lo:hi] * (1.0 / scale)).to(dev).requires_grad_(True)
+        r = (reg[lo:hi] * scale).to(dev).requires_grad_(True)
+        a = ann[lo:hi].to(dev)
+        if step == 3:                                         # an ordinary call in between
+            lc, lr = fused(c, r, anchors, a)
+            (lc + lr).sum().backward()
+        else:
+            pend = fused.start(c, r, anchors, a)
+            pend.backward()
+            lc, lr = pend.losses()
+        c2 = c.detach().clone().requires_grad_(True)
+        r2 = r.detach().clone().requires_grad_(True)
+        lc2, lr2 = nccl(c2, r2, anchors, a)
+        (lc2 + lr2).sum().backward()
+        assert torch.equal(lc, lc2) and torch.equal(lr, lr2), ("deferred", step, lc, lc2)
+        assert torch.equal(c.grad, c2.grad) and torch.equal(r.grad, r2.grad)
+        rec[f"dlc{step}"] = lc.item()
     # per-level head outputs through the same exchange
     sp = b200det.spec_of(anchors)
     K = sp.cell_anchors
