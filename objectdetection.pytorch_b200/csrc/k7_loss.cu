@@ -7,15 +7,20 @@
 // (profiles/): v1 (row-mapped lanes, per-warp rings) was issue-bound at 58 issue slots per element;
 // v2 (flat 4 KB tiles per warp, packed math) reached 27; v3 (warp-specialised CTA pipeline) 13, but
 // its consumer warps still served the positive rows inline - dependent global loads that held a
-// pipeline stage for ~1 us each; v4 moved the positives into a row kernel behind the stream but
-// still streamed one ignore bit per anchor, which tied the stream to the assignment stage.  v5:
+// pipeline stage for ~1 us each; v4 moved the positives into a row kernel behind the stream, fed by an
+// exhaustive assignment kernel and a row kernel that re-read all B*A assignment words.  v5:
 //
+//   * LIST KERNEL (k7_loss_list_kernel): the assignment comes from k7_match_scatter as per-image lists
+//     of the anchors a ground-truth box reached (a few per cent of A).  A thread per entry: positives go
+//     to the image's queue (one returning atomic per warp, on the IMAGE's own counter - atomics on one
+//     address serialise at ~7 ns each), ignored rows (losses.py:79-82) set a bit in the ignore bitmap.
+//     Nothing walks the B*A anchors.  (k7_match's words instead: k7_loss_scan_kernel, one pass.)
 //   * STREAM KERNEL (k7_loss_pipe_kernel).  One CTA per SM.  classifications is ONE flat array of
 //     B*A*C floats cut into tiles of 16 x 512 floats; tiles ignore row AND image boundaries, so any
 //     shape streams through 16-byte aligned bulk copies.  A producer warp drives a ring of
-//     shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile in and - once the
-//     consumer warps have signalled the stage done - gradients out.  full[]/done[] mbarriers; no
-//     __syncthreads in the loop.
+//     shared-memory stages with 1-D bulk async copies (TMA, SASS UBLKCP): tile + the ignore bits of
+//     its rows in and - once the consumer warps have signalled the stage done - gradients out.
+//     full[]/done[] mbarriers; no __syncthreads in the loop.
 //   * FLAT PASS.  Consumer warp w owns floats [512w, 512w+512) of every tile: LDS.128 -> math ->
 //     STS.128 on float4 number lane+32k (conflict free, balanced whatever C is).  EVERY element is
 //     evaluated as "target 0" (negative / non-label class) with packed f32x2 arithmetic
@@ -23,25 +28,23 @@
 //         p = clamp(x); q = fl(1-p); pp = 1-q; nl = pp*S(pp) ~ -log(q)      (degree-5 minimax)
 //         loss += p*p*nl                                  (x (1-alpha) once per image)
 //         grad  = (p == x) ? (1-alpha)*scale * p * (2*nl + p/q) : 0          (MUFU.RCP)
-//     The polynomial is valid for p <= 0.25; the pass tracks max(p) and a slice that saw a larger
-//     value (rare: confident predictions) is redone by an exact scalar path with logf.
-//     The stream knows nothing about the assignment except, with gradients, the per-image scale
-//     1 / max(num_pos, 1) (and that an image without ground truth has gradient 0).
+//     The polynomial is valid for p <= 0.25; the pass tracks max(p), and in a slice that saw a larger
+//     value the CONFIDENT elements alone are redone: their polynomial term leaves the sum, the exact
+//     one (logf) enters, their gradient is overwritten.
+//   * IGNORED ROWS never reach the arithmetic as such: before the flat pass the few elements of an
+//     ignored row are overwritten IN THE TILE by a sentinel (0, or -1e30 for logits) whose clamped
+//     probability differs from it - gradient 0 by torch.clamp's rule, loss term 1e-12.
 //   * A slice that straddles an image boundary (B-1 of them per batch) or lies in a tile that
 //     spans more than two images (tiny shapes) takes a generic per-element path.
-//   * ROW KERNEL (k7_loss_rows_kernel), after the stream: blocks walk the assignment (k7_match's
-//     4-byte words or k7_match_scatter's 8-byte maxima) in chunks of 2048 anchors with coalesced
-//     loads and queue the ~2 % of rows that are not plain negatives in shared memory:
-//       positive rows  smooth-L1 + d(reg), and the label element is corrected from "target 0" to
-//                      "target 1" (loss difference, gradient overwritten in dcls) - a thread each;
-//       ignored rows   (losses.py:79-82: neither negative nor positive) are taken out again: the
-//                      C elements of the row are re-evaluated exactly and SUBTRACTED, their
-//                      gradients zeroed - a warp each, lanes across the classes.
-//     Their contributions go into two per-image 64-bit FIXED-POINT accumulators (2^-32 units,
-//     integer atomics): exact and independent of the order in which blocks finish.
-//   * Stream sums stay in registers while a warp works on one image, are folded per (image, CTA)
-//     at the end of the stream kernel and summed per image in float64 in CTA order by the last
-//     block of the row kernel: bit-reproducible run to run.
+//   * SERVE KERNEL (k7_loss_serve_kernel), after the stream: a thread per queued positive row:
+//     smooth-L1 + d(reg), and the label element is corrected from "target 0" to "target 1" (loss
+//     difference, gradient overwritten in dcls).
+//   * Every contribution - the stream's per-(image, CTA) partials too - goes into two per-image
+//     64-bit FIXED-POINT accumulators (2^-32 units, integer atomics): exact and independent of the
+//     order in which blocks finish; the last block of the serve kernel turns them into the
+//     per-image losses and the batch sums: bit-reproducible run to run, no reduction pass.
+//   * The exchange of the batch sums between ranks rides on the serve kernel's last block (peer
+//     memory over NVLink): fused (post + wait) or post-only with k7_peer_collect on another stream.
 //
 // Algorithmic bytes per image: forward A*(4C+16)+20M, forward+backward A*(8C+32)+20M.
 #include <stdlib.h>

@@ -1287,3 +1287,29 @@ def test_spare_sms_changes_no_result():
         assert torch.equal(o[2], outs[0][2]) and torch.equal(o[3], outs[0][3])
         np.testing.assert_allclose(o[0].item(), outs[0][0].item(), rtol=1e-6)
         np.testing.assert_allclose(o[1].item(), outs[0][1].item(), rtol=1e-6)
+
+
+def test_start_is_forward_in_two_phases():
+    """FocalLoss.start() -> PendingLoss on one GPU (nothing to defer): losses and gradients are those of forward() +
+    backward(), for leaf inputs (the gradient buffer itself becomes .grad) and for non-leaf inputs (autograd)."""
+    img, anc, ann, cls, reg, hw = _small_case(6, B=4, C=9)
+    c0, r0 = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    lc0, lr0 = b200det.FocalLoss()(c0, r0, anc, ann)
+    (lc0 + lr0).sum().backward()
+    c1, r1 = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    loss = b200det.FocalLoss()
+    pend = loss.start(c1, r1, anc, ann)
+    pend.backward()
+    lc1, lr1 = pend.losses()
+    assert torch.equal(lc1, lc0.detach()) and torch.equal(lr1, lr0.detach())
+    assert torch.equal(c1.grad, c0.grad) and torch.equal(r1.grad, r0.grad)
+    assert torch.equal(pend.num_positives, loss.last_num_positives)
+    # non-leaf inputs: the gradients flow on through autograd (here: through a scaling of the leaves)
+    c2, r2 = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    pend = loss.start(c2 * 1.0, r2 * 2.0, anc, ann)
+    pend.backward(scale=0.5)
+    c3, r3 = cls.clone().requires_grad_(True), reg.clone().requires_grad_(True)
+    lc3, lr3 = b200det.FocalLoss()(c3 * 1.0, r3 * 2.0, anc, ann)
+    (0.5 * (lc3 + lr3)).sum().backward()
+    np.testing.assert_allclose(c2.grad.cpu().numpy(), c3.grad.cpu().numpy(), rtol=1e-6, atol=1e-12)
+    np.testing.assert_allclose(r2.grad.cpu().numpy(), r3.grad.cpu().numpy(), rtol=1e-6, atol=1e-12)
