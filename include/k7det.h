@@ -235,13 +235,13 @@ K7_API size_t k7_loss_workspace_bytes(int B, int A, int C);
 
 /* Replaces FocalLoss.forward after assignment (losses.py:62, 94-168) and, when dcls/dreg
  * are given, its autograd backward.  The assignment comes either as k7_match's words (`assign`) or as
- * k7_match_scatter's `best` array (exactly one of the two is non-NULL).  Two kernels: a stream over
- * `cls` that evaluates EVERY element as "target 0" at HBM speed, then a row kernel that walks the
- * assignment once and patches the ~2 % of rows that are not plain negatives: positive rows get
- * smooth-L1 + d(reg) and their label element moves from target 0 to target 1; ignored rows
- * (neg_thr <= IoU_max < pos_thr, losses.py:79-82) are taken out of the sum again and their gradient is
- * zeroed.  Row contributions are accumulated as 2^-32 fixed-point integers (order independent), the
- * stream partials in a fixed order: results are bit-reproducible run to run.  Outputs:
+ * k7_match_scatter's `best` buffer (exactly one of the two is non-NULL).  Three kernels: a list kernel that turns
+ * the touched lists of `best` (or, for `assign`, one pass over the words) into a queue of positive rows and a
+ * one-bit-per-anchor bitmap of ignored rows (neg_thr <= IoU_max < pos_thr, losses.py:79-82); a stream over `cls`
+ * that evaluates every element as "target 0" at HBM speed and skips the ignored rows by the bitmap; a serve kernel
+ * that gives the positive rows smooth-L1 + d(reg) and moves their label element from target 0 to target 1.  All
+ * contributions are accumulated as 2^-32 fixed-point integers per image (order independent): results are
+ * bit-reproducible run to run.  Outputs:
  *   num_pos   [B]   int32    positives per image, counted while the assignment is walked (it is WRITTEN here,
  *                            whichever form the assignment comes in)
  *   per_image [B,2] float32  (cls_loss_i, reg_loss_i)
