@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define K7_ABI_VERSION 13
+#define K7_ABI_VERSION 14
 
 #if defined(__GNUC__)
 #define K7_API __attribute__((visibility("default")))
@@ -314,7 +314,14 @@ typedef struct K7DetectParams {
     int32_t class_aware;    /* 0: class-agnostic NMS, the reference (retinanet.py:314); 1: a box is suppressed only by
                              * a higher-scored box of the SAME arg-max class (torchvision.ops.batched_nms with
                              * idxs = labels, per-class strategy) - SURVEY 8f row 4 */
+    int32_t nms_chain;      /* which NMS kernels run (same result): 0 = automatic - the per-image chain (one CTA per image
+                             * sorts and resolves, k7_nms_v1.cu) when the batch has >= 12 images or images are small
+                             * (A < 262 144), else the multi-SM chain (every image spread over all SMs: a few images
+                             * with thousands of survivors each, a shard of a large batch); 1 = per-image, 2 = multi-SM */
 } K7DetectParams;
+#define K7_NMS_CHAIN_AUTO 0
+#define K7_NMS_CHAIN_PER_IMAGE 1
+#define K7_NMS_CHAIN_MULTI_SM 2
 
 K7_API size_t k7_detect_workspace_bytes(int B, int A, int C);
 

@@ -98,6 +98,7 @@ class K7DetectParams(C.Structure):
         ("max_detections", C.c_int32),
         ("from_logits", C.c_int32),
         ("class_aware", C.c_int32),
+        ("nms_chain", C.c_int32),
     ]
 
 
@@ -116,7 +117,7 @@ class K7EvalParams(C.Structure):
 
 
 EVAL_COCO, EVAL_CSV = 0, 1
-ABI_VERSION = 13                     # K7_ABI_VERSION of include/k7det.h
+ABI_VERSION = 14                     # K7_ABI_VERSION of include/k7det.h
 
 
 BEST_GEN_MAX = 65535                 # K7_BEST_GEN_MAX

@@ -128,7 +128,7 @@ struct K7DetectWs {
 };
 static int k7_nms_cap(int B, int n_max);
 
-static K7DetectWs k7_detect_ws(void* base, int B, int A) {
+static K7DetectWs k7_detect_ws(void* base, int B, int A, bool with_v1 = true) {
     K7DetectWs w;
     unsigned char* p = static_cast<unsigned char*>(base);
     size_t o = 0;
@@ -167,10 +167,11 @@ static K7DetectWs k7_detect_ws(void* base, int B, int A) {
     w.pend = reinterpret_cast<int32_t*>(take(sizeof(int32_t) * (size_t)B * cap));
     w.edges = reinterpret_cast<unsigned int*>(take(sizeof(unsigned int) * (size_t)B * w.ecap));
     w.ginfo = take(320 * (size_t)B);   // sizeof(K7Grid) <= 320
-    static const int v1_min = [] { const char* e = getenv("K7_V1_MIN_IMAGES"); return e ? atoi(e) : K7_V1_MIN_IMAGES; }();
-    w.use_v1 = B >= v1_min;
+    // the areas of the per-image chain are always there: the chain is a per-call choice (K7DetectParams.nms_chain)
+    static const int v1_min = [] { const char* e = getenv("K7_V1_MIN_IMAGES"); return e ? atoi(e) : -1; }();
+    w.use_v1 = v1_min >= 0 ? B >= v1_min : (B >= K7_V1_MIN_IMAGES || A < K7_V1_SMALL_IMAGE);   // the automatic choice
     w.v1.bytes = 0;
-    if (w.use_v1) {
+    if (with_v1) {   // (the stand-alone k7_nms family always runs the multi-SM chain)
         w.v1 = k7v1::workspace(p ? p + o : nullptr, B, A);
         o += w.v1.bytes;
     }
@@ -2400,7 +2401,9 @@ static int k7_detect_run(const K7AnchorSpec* spec, const float* anchors, int box
 
     // NMS (every kernel decides per image on the device; PDL links: each starts when its predecessor drains)
     int rc2;
-    if (w.use_v1)
+    K7_REQUIRE(params->nms_chain >= 0 && params->nms_chain <= 2, "k7_detect: bad nms_chain %d", params->nms_chain);
+    const bool per_image = params->nms_chain == K7_NMS_CHAIN_AUTO ? w.use_v1 : params->nms_chain == K7_NMS_CHAIN_PER_IMAGE;
+    if (per_image)
         rc2 = k7v1::chain(B, A, params->iou_thr, params->pre_nms_topk, params->max_detections, params->class_aware != 0,
                           w.surv_count, w.keys0, w.keys1, w.box, w.label, w.nsel, w.kept_key, w.kept_box, w.kept_count, counts,
                           w.v1, st);
@@ -2453,7 +2456,7 @@ extern "C" int k7_detect_gather(const void* workspace, size_t workspace_bytes, i
 
 // ------------------------------------------------------------------ stand-alone NMS (torchvision.ops.nms)
 // Same kernels as k7_detect with B = 1 and "anchor id" = box index: the workspace is k7_detect's for (1, n).
-extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_detect_ws(nullptr, 1, n > 0 ? n : 1).bytes; }
+extern "C" size_t k7_nms_workspace_bytes(int n) { return k7_detect_ws(nullptr, 1, n > 0 ? n : 1, false).bytes; }
 
 __global__ void k7_nms_keys_kernel(const float* __restrict__ scores, int n, uint64_t* __restrict__ keys,
                                    int32_t* __restrict__ n_dev, const int64_t* __restrict__ idxs,
@@ -2478,7 +2481,7 @@ static int k7_nms_run(const float* boxes, const float* scores, const int64_t* id
     K7_REQUIRE(boxes && scores && keep, "k7_nms: null argument");
     K7_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0 && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0,
                "k7_nms: boxes must be 16-byte and workspace 256-byte aligned");
-    const K7DetectWs w = k7_detect_ws(workspace, 1, n);
+    const K7DetectWs w = k7_detect_ws(workspace, 1, n, false);
     if (workspace_bytes < w.bytes) {
         k7_set_error("k7_nms: workspace %zu < %zu bytes", workspace_bytes, w.bytes);
         return K7_EWORKSPACE;

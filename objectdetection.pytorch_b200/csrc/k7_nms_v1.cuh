@@ -2,7 +2,8 @@
 #pragma once
 #include "k7_common.cuh"
 
-#define K7_V1_MIN_IMAGES 12   // batches of at least this many images take the per-image chain
+#define K7_V1_MIN_IMAGES 12        // automatic choice: batches of at least this many images take the per-image chain,
+#define K7_V1_SMALL_IMAGE 262144   // and so do images with fewer anchors than this (few survivors per image)
 
 struct K7V1Ws {             // its workspace areas (behind the areas of k7_detect.cu)
     float4* sbox;           // [B][cap] boxes in spatial order

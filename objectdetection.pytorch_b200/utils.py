@@ -127,7 +127,7 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
            score_thr: float = 0.05, iou_thr: float = 0.5, variant=L.DECODE_RETINA, mean=(0, 0, 0, 0),
            std=(.1, .1, .2, .2), clip: bool = True, pre_nms_topk: int = 0, max_detections: int = 0,
            cap: Optional[int] = None, sync: bool = True, from_logits: bool = False,
-           class_aware: bool = False, want_rank: Optional[bool] = None) -> BatchDetections:
+           class_aware: bool = False, want_rank: Optional[bool] = None, nms_chain: str = "auto") -> BatchDetections:
     """Fused decode + clip + threshold + sort + NMS for every image of the batch.
     class_aware: suppress only inside a class (torchvision.ops.batched_nms with idxs = labels); the
     reference's own eval tail is class-agnostic (retinanet.py:314), which is the default.
@@ -137,6 +137,8 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
     [B, anchors*classes, H_l, W_l] (then `anchors` must come from b200det.Anchors).
     want_rank: also return survivor_rank (the index torchvision.ops.nms would have returned: one more small
     kernel for the popcount prefix of the survivor bitmap); default: only when sync=True.
+    nms_chain: "auto" (per-image kernels for many or small images, multi-SM kernels for a few large ones),
+    "per_image" or "multi_sm" - same result, K7DetectParams.nms_chain.
     sync=False returns at once, count / survivors stay on the device and at most `cap` (default 1024) kept
     boxes per image are returned - a larger count[b] says how many there were."""
     if want_rank is None:
@@ -173,6 +175,10 @@ def detect(classifications: torch.Tensor, regressions: torch.Tensor, anchors, im
     p.pre_nms_topk, p.max_detections = int(pre_nms_topk), int(max_detections)
     p.from_logits = int(from_logits)
     p.class_aware = int(class_aware)
+    try:
+        p.nms_chain = {"auto": 0, "per_image": 1, "multi_sm": 2}[nms_chain]
+    except KeyError:
+        raise ValueError("nms_chain must be 'auto', 'per_image' or 'multi_sm'")
     if cap is None:
         cap = max_detections if max_detections > 0 else min(A, 1024)
     cap = max(1, min(int(cap), A))

@@ -593,14 +593,16 @@ def check_detect(det, g, exact_boxes_from=None):
         np.testing.assert_allclose(det.boxes[b, :k].cpu().numpy(), g[f"boxes_{b}"], rtol=1e-5, atol=1e-4)
 
 
+@pytest.mark.parametrize("chain", ["auto", "per_image", "multi_sm"])
 @pytest.mark.parametrize("from_spec", [True, False], ids=["spec", "tensor"])
 @pytest.mark.parametrize("path", DET, ids=DIDS)
-def test_detect_end_to_end(path, from_spec):
+def test_detect_end_to_end(path, from_spec, chain):
     g, yx, anc, img = load_det_case(path, from_spec)
     cls = torch.from_numpy(g["classifications"]).to(DEV)
     reg = torch.from_numpy(g["regressions"]).to(DEV)
     det = b200det.detect(cls, reg, anc, (int(g["height"]), int(g["width"])), score_thr=float(g["score_thr"]),
-                         iou_thr=float(g["iou_thr"]), variant=L.DECODE_EFFDET if yx else L.DECODE_RETINA, cap=8)
+                         iou_thr=float(g["iou_thr"]), variant=L.DECODE_EFFDET if yx else L.DECODE_RETINA, cap=8,
+                         nms_chain=chain)
     check_detect(det, g)
 
 
@@ -1313,3 +1315,31 @@ def test_start_is_forward_in_two_phases():
     (0.5 * (lc3 + lr3)).sum().backward()
     np.testing.assert_allclose(c2.grad.cpu().numpy(), c3.grad.cpu().numpy(), rtol=1e-6, atol=1e-12)
     np.testing.assert_allclose(r2.grad.cpu().numpy(), r3.grad.cpu().numpy(), rtol=1e-6, atol=1e-12)
+
+
+@pytest.mark.parametrize("opts", [dict(), dict(class_aware=True), dict(max_detections=37), dict(pre_nms_topk=500),
+                                  dict(class_aware=True, max_detections=5, pre_nms_topk=900)],
+                         ids=["plain", "per-class", "maxdet", "topk", "all"])
+def test_both_nms_chains_agree(opts):
+    """K7DetectParams.nms_chain: the per-image chain and the multi-SM chain give the same detections, bit for bit -
+    dense images (thousands of survivors, clustered boxes), an empty image, options."""
+    B, C, H, W = 5, 6, 384, 512
+    gen = torch.Generator().manual_seed(21)
+    img = torch.empty(B, 3, H, W, device=DEV)
+    anc = b200det.Anchors()(img)
+    A = anc.shape[1]
+    cls, reg = b200det.synth.make_head_outputs(B, A, C, gen, logit_mean=-2.2, logit_std=1.3)
+    reg = reg * 0.3                                          # neighbours overlap a lot: long suppression chains
+    cls[3] = 0.001                                           # an image without survivors
+    cls, reg = cls.to(DEV), reg.to(DEV)
+    a = b200det.detect(cls, reg, anc, (H, W), nms_chain="per_image", **opts)
+    b = b200det.detect(cls, reg, anc, (H, W), nms_chain="multi_sm", **opts)
+    assert a.count.tolist() == b.count.tolist() and a.survivors.tolist() == b.survivors.tolist()
+    assert int(a.survivors.max()) > 3000 and int(a.count[3]) == 0
+    for i in range(B):
+        k = int(a.count[i])
+        for x, y in ((a.anchor_ids, b.anchor_ids), (a.scores, b.scores), (a.labels, b.labels), (a.boxes, b.boxes),
+                     (a.survivor_rank, b.survivor_rank)):
+            assert torch.equal(x[i, :k], y[i, :k])
+    with pytest.raises(ValueError):
+        b200det.detect(cls, reg, anc, (H, W), nms_chain="fastest")
