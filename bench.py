@@ -264,9 +264,13 @@ class HotPath:
         self.cls, self.reg, self.ann = b200det.synth.make_inputs(wl, seed=seed, device=dev, batch=B)
         self.img = torch.empty(B, 3, wl.height, wl.width, device=dev)   # only its shape is read (anchors.py:40)
         self.anchors_mod = b200det.Anchors(**wl.anchor_kwargs())
-        # few images per GPU: the NMS kernels (multi-SM chain, 1024-thread CTAs) cannot share an SM with the loss stage's
-        # streaming CTAs, so the stream leaves them 24 SMs (it stays HBM-bound) and both run side by side in step()
-        self.spare_sms = (24 if B < 12 else 0) if spare_sms is None else spare_sms
+        # large images: the NMS kernels (1024-thread CTAs) cannot share an SM with the loss stage's streaming CTAs,
+        # so the stream leaves them a few SMs (it stays HBM-bound) and both run side by side in step()
+        # (measured on D7, two-stream step: 8 images 0.763 -> 0.685 ms with 24, 16 images 1.364 -> 1.284 with 12,
+        # 32 images 2.585 -> 2.465 with 16; at 64 images the gain is inside the run-to-run spread, and small images
+        # (C2) lose: their NMS tail is short and their loss stream needs every SM)
+        large = wl.anchors >= 262144
+        self.spare_sms = ((24 if B < 12 else 16 if B <= 32 else 0) if large else 0) if spare_sms is None else spare_sms
         self.loss_mod = b200det.FocalLoss(sharded=world > 1, peer_reduce=peer, spare_sms=self.spare_sms)
         self.cls_g = self.cls.detach().requires_grad_(True)
         self.reg_g = self.reg.detach().requires_grad_(True)
@@ -334,15 +338,18 @@ class HotPath:
         A = self.wl.anchors
         anc = self.anchors_mod(self.img)
         sp = self.b200det.spec_of(anc)
+        self.loss_mod.cfg["spare_sms"] = 0            # the stages by themselves: the loss stream on all SMs
         ms_fwd = timed(self.fwd_only, k, 3)
         ms_fb = timed(self.train_side, k, 3)
         ms_det = timed(self.eval_side, k, 3)
+        g_train = self.graphed(self.train_side)
+        ms_graph_fb = timed(g_train, k, 3) if g_train is not None else None
+        del g_train
+        self.loss_mod.cfg["spare_sms"] = self.spare_sms   # the step: both halves side by side
         ms_step = timed(self.step, k, 3)
         g_step = self.graphed()
         ms_graph = timed(g_step, k, 3) if g_step is not None else None
-        g_train = self.graphed(self.train_side)
-        ms_graph_fb = timed(g_train, k, 3) if g_train is not None else None
-        del g_step, g_train
+        del g_step
         ms_match = timed(lambda: BL.match_scatter(sp, self.ann, A, 0.35, 0.45), k, 3)
         surv = int(self.eval_side(sync=True).survivors.sum())
         bf, bfb, bd = self.bytes(surv)
